@@ -1,0 +1,491 @@
+// TEST INFRASTRUCTURE ONLY -- not part of the product path.
+//
+// C harness around the UNMODIFIED reference CPU classes of HOOMD-blue 2.3.0, compiled from the
+// sources where they lie under /root/reference (see oracle/Makefile, target _ref/libhoomd_ref.so).
+// It drives the reference's own CellList / NeighborListBinned / PotentialPairLJ / IntegratorTwoStep /
+// TwoStepNVE / TwoStepLangevin / SFCPackUpdater / ComputeThermo objects exactly as the reference's unit
+// tests do (hoomd/md/test/test_lj_force.cc:51-70, hoomd/md/test/test_nve_integrator.cc:262-300) and
+// exposes their arrays through a flat C API so that tests/ and bench.py (cpu_baseline / --impl reference)
+// can compare the CUDA path and the C restatement (oracle/oracle.c) against the real thing.
+//
+// Nothing in hoomd_b200/ may link or load this file.
+
+#include "hoomd/ExecutionConfiguration.h"
+#include "hoomd/SystemDefinition.h"
+#include "hoomd/ParticleData.h"
+#include "hoomd/ParticleGroup.h"
+#include "hoomd/CellList.h"
+#include "hoomd/Variant.h"
+#include "hoomd/SFCPackUpdater.h"
+#include "hoomd/ComputeThermo.h"
+#include "hoomd/Saru.h"
+#include "hoomd/md/NeighborListBinned.h"
+#include "hoomd/md/AllPairPotentials.h"
+#include "hoomd/md/IntegratorTwoStep.h"
+#include "hoomd/md/TwoStepNVE.h"
+#include "hoomd/md/TwoStepLangevin.h"
+
+#include <memory>
+#include <vector>
+#include <cstring>
+#include <chrono>
+
+namespace
+{
+struct RefSystem
+    {
+    std::shared_ptr<ExecutionConfiguration> exec_conf;
+    std::shared_ptr<SystemDefinition> sysdef;
+    std::shared_ptr<ParticleData> pdata;
+    std::shared_ptr<ParticleGroup> group_all;
+    std::shared_ptr<CellList> cl;
+    std::shared_ptr<NeighborListBinned> nlist;
+    std::shared_ptr<PotentialPairLJ> lj;
+    std::shared_ptr<IntegratorTwoStep> integrator;
+    std::shared_ptr<TwoStepNVE> nve;
+    std::shared_ptr<TwoStepLangevin> langevin;
+    std::shared_ptr<SFCPackUpdater> sorter;
+    std::shared_ptr<ComputeThermo> thermo;
+    unsigned int sorter_period = 0;
+    unsigned int sorter_next = 0;
+    unsigned int timestep = 0;
+    bool virial = false;
+    std::string error;
+    };
+
+void apply_flags(RefSystem* s)
+    {
+    PDataFlags flags(0);
+    flags[pdata_flag::potential_energy] = 1;
+    if (s->virial)
+        {
+        flags[pdata_flag::pressure_tensor] = 1;
+        flags[pdata_flag::isotropic_virial] = 1;
+        }
+    s->pdata->setFlags(flags);
+    }
+} // namespace
+
+#define REF_TRY(s) try {
+#define REF_CATCH(s, rv) } catch (const std::exception& e) { (s)->error = e.what(); return rv; }
+
+extern "C"
+{
+
+//! Create a system of N particles of \a ntypes types in an orthorhombic periodic box (tilts 0)
+void* ref_create(unsigned int N, float Lx, float Ly, float Lz, unsigned int ntypes)
+    {
+    RefSystem* s = new RefSystem;
+    try
+        {
+        std::shared_ptr<Messenger> msg(new Messenger());
+        msg->setNoticeLevel(0);
+        s->exec_conf = std::shared_ptr<ExecutionConfiguration>(
+            new ExecutionConfiguration(ExecutionConfiguration::CPU, -1, false, false, msg));
+        BoxDim box(Lx, Ly, Lz);
+        s->sysdef = std::shared_ptr<SystemDefinition>(new SystemDefinition(N, box, ntypes, 0, 0, 0, 0, s->exec_conf));
+        s->pdata = s->sysdef->getParticleData();
+        std::shared_ptr<ParticleSelector> sel(new ParticleSelectorTag(s->sysdef, 0, N - 1));
+        s->group_all = std::shared_ptr<ParticleGroup>(new ParticleGroup(s->sysdef, sel));
+        apply_flags(s);
+        }
+    catch (const std::exception& e)
+        {
+        s->error = e.what();
+        }
+    return s;
+    }
+
+void ref_destroy(void* h)
+    {
+    delete static_cast<RefSystem*>(h);
+    }
+
+const char* ref_last_error(void* h)
+    {
+    return static_cast<RefSystem*>(h)->error.c_str();
+    }
+
+//! Non-periodic directions (used to emulate a domain-decomposed local box)
+void ref_set_periodic(void* h, int px, int py, int pz)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    BoxDim box = s->pdata->getGlobalBox();
+    box.setPeriodic(make_uchar3(px, py, pz));
+    s->pdata->setGlobalBox(box);
+    }
+
+//! Set particle state in index order; tags are the identity at this point (tag == index)
+void ref_set_particles(void* h, const float* pos4, const float* vel4, const int* image3)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int N = s->pdata->getN();
+    ArrayHandle<Scalar4> h_pos(s->pdata->getPositions(), access_location::host, access_mode::readwrite);
+    ArrayHandle<Scalar4> h_vel(s->pdata->getVelocities(), access_location::host, access_mode::readwrite);
+    ArrayHandle<int3> h_img(s->pdata->getImages(), access_location::host, access_mode::readwrite);
+    if (pos4) memcpy(h_pos.data, pos4, sizeof(Scalar4) * N);
+    if (vel4) memcpy(h_vel.data, vel4, sizeof(Scalar4) * N);
+    if (image3) memcpy(h_img.data, image3, sizeof(int3) * N);
+    if (s->nlist) s->nlist->forceUpdate();
+    }
+
+void ref_set_accel(void* h, const float* accel3)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    ArrayHandle<Scalar3> h_accel(s->pdata->getAccelerations(), access_location::host, access_mode::readwrite);
+    memcpy(h_accel.data, accel3, sizeof(Scalar3) * s->pdata->getN());
+    s->pdata->notifyAccelSet();
+    }
+
+//! md.nlist.cell + md.pair.lj
+/*! \param rcut, lj1, lj2 ntypes x ntypes matrices (row-major, symmetric)
+    \param shift_mode 0 none, 1 shift, 2 xplor (hoomd/md/PotentialPair.h:109-114)
+    \param full_storage 1 = full neighbor list (what every GPU class forces), 0 = half (CPU default) */
+int ref_setup_lj(void* h, float r_buff, int check_period, int full_storage, const float* rcut,
+                 const float* lj1, const float* lj2, const float* ron, int shift_mode)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    unsigned int nt = s->pdata->getNTypes();
+    s->cl = std::shared_ptr<CellList>(new CellList(s->sysdef));
+    s->nlist = std::shared_ptr<NeighborListBinned>(new NeighborListBinned(s->sysdef, Scalar(0.0), r_buff, s->cl));
+    s->nlist->setEvery(check_period, true);
+    s->nlist->setStorageMode(full_storage ? NeighborList::full : NeighborList::half);
+    s->lj = std::shared_ptr<PotentialPairLJ>(new PotentialPairLJ(s->sysdef, s->nlist));
+    for (unsigned int i = 0; i < nt; i++)
+        for (unsigned int j = i; j < nt; j++)
+            {
+            s->lj->setParams(i, j, make_scalar2(lj1[i * nt + j], lj2[i * nt + j]));
+            s->lj->setRcut(i, j, rcut[i * nt + j]);
+            if (ron) s->lj->setRon(i, j, ron[i * nt + j]);
+            s->nlist->setRCutPair(i, j, rcut[i * nt + j]);
+            }
+    s->lj->setShiftMode((PotentialPairLJ::energyShiftMode)shift_mode);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+void ref_set_virial(void* h, int on)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    s->virial = on;
+    apply_flags(s);
+    }
+
+int ref_setup_integrator(void* h, float dt)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->integrator = std::shared_ptr<IntegratorTwoStep>(new IntegratorTwoStep(s->sysdef, dt));
+    if (s->lj) s->integrator->addForceCompute(s->lj);
+    s->thermo = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, s->group_all, ""));
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+int ref_add_nve(void* h, int limit, float limit_val, int zero_force)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->nve = std::shared_ptr<TwoStepNVE>(new TwoStepNVE(s->sysdef, s->group_all, true));
+    if (limit) s->nve->setLimit(limit_val);
+    s->nve->setZeroForce(zero_force);
+    s->integrator->removeAllIntegrationMethods();
+    s->integrator->addIntegrationMethod(s->nve);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+int ref_add_langevin(void* h, float kT, unsigned int seed, const float* gamma, int noiseless_t)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<Variant> T(new VariantConst(kT));
+    s->langevin = std::shared_ptr<TwoStepLangevin>(
+        new TwoStepLangevin(s->sysdef, s->group_all, T, seed, false, Scalar(0.0), noiseless_t, false, ""));
+    if (gamma)
+        for (unsigned int t = 0; t < s->pdata->getNTypes(); t++)
+            s->langevin->setGamma(t, gamma[t]);
+    s->integrator->removeAllIntegrationMethods();
+    s->integrator->addIntegrationMethod(s->langevin);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! hoomd.update.sort (period 0 disables); the first sort happens at the first step run, like System::run
+void ref_set_sorter(void* h, unsigned int period)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    s->sorter_period = period;
+    s->sorter_next = s->timestep;
+    if (period && !s->sorter)
+        s->sorter = std::shared_ptr<SFCPackUpdater>(new SFCPackUpdater(s->sysdef));
+    }
+
+void ref_set_timestep(void* h, unsigned int ts)
+    {
+    static_cast<RefSystem*>(h)->timestep = ts;
+    }
+
+unsigned int ref_get_timestep(void* h)
+    {
+    return static_cast<RefSystem*>(h)->timestep;
+    }
+
+//! Only the neighbor list (and the cell list under it) at timestep ts
+int ref_compute_nlist(void* h, unsigned int ts)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->nlist->compute(ts);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! ForceCompute::compute(ts) of the LJ pair force (builds the nlist first if needed)
+int ref_compute_forces(void* h, unsigned int ts)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->lj->compute(ts);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! System::run(nsteps): prepRun at the current step, then updaters + integrator->update per step
+/*! Follows hoomd/System.cc:484-599. Returns elapsed seconds of the step loop (excluding prepRun) in *elapsed */
+int ref_run(void* h, unsigned int nsteps, double* elapsed)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->integrator->prepRun(s->timestep);
+    auto t0 = std::chrono::steady_clock::now();
+    for (unsigned int k = 0; k < nsteps; k++)
+        {
+        if (s->sorter && s->sorter_period && s->timestep == s->sorter_next)
+            {
+            s->sorter->update(s->timestep);
+            s->sorter_next += s->sorter_period;
+            }
+        s->integrator->update(s->timestep);
+        s->timestep++;
+        }
+    auto t1 = std::chrono::steady_clock::now();
+    if (elapsed) *elapsed = std::chrono::duration<double>(t1 - t0).count();
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! One isolated integration half step on the current state (for kernel-level parity of step one / two)
+int ref_step_one(void* h, unsigned int ts)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    if (s->langevin) s->langevin->integrateStepOne(ts); else s->nve->integrateStepOne(ts);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+int ref_step_two(void* h, unsigned int ts, const float* net_force4)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+        {
+        ArrayHandle<Scalar4> h_nf(s->pdata->getNetForce(), access_location::host, access_mode::readwrite);
+        memcpy(h_nf.data, net_force4, sizeof(Scalar4) * s->pdata->getN());
+        }
+    if (s->langevin) s->langevin->integrateStepTwo(ts); else s->nve->integrateStepTwo(ts);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+// ---------------------------------------------------------------- getters
+unsigned int ref_get_N(void* h)
+    {
+    return static_cast<RefSystem*>(h)->pdata->getN();
+    }
+
+void ref_get_particles(void* h, float* pos4, float* vel4, float* accel3, int* image3, unsigned int* tag,
+                       unsigned int* rtag)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int N = s->pdata->getN();
+    if (pos4)
+        {
+        ArrayHandle<Scalar4> a(s->pdata->getPositions(), access_location::host, access_mode::read);
+        memcpy(pos4, a.data, sizeof(Scalar4) * N);
+        }
+    if (vel4)
+        {
+        ArrayHandle<Scalar4> a(s->pdata->getVelocities(), access_location::host, access_mode::read);
+        memcpy(vel4, a.data, sizeof(Scalar4) * N);
+        }
+    if (accel3)
+        {
+        ArrayHandle<Scalar3> a(s->pdata->getAccelerations(), access_location::host, access_mode::read);
+        memcpy(accel3, a.data, sizeof(Scalar3) * N);
+        }
+    if (image3)
+        {
+        ArrayHandle<int3> a(s->pdata->getImages(), access_location::host, access_mode::read);
+        memcpy(image3, a.data, sizeof(int3) * N);
+        }
+    if (tag)
+        {
+        ArrayHandle<unsigned int> a(s->pdata->getTags(), access_location::host, access_mode::read);
+        memcpy(tag, a.data, sizeof(unsigned int) * N);
+        }
+    if (rtag)
+        {
+        ArrayHandle<unsigned int> a(s->pdata->getRTags(), access_location::host, access_mode::read);
+        memcpy(rtag, a.data, sizeof(unsigned int) * N);
+        }
+    }
+
+//! force (fx,fy,fz,pe) per particle and the 6 x pitch virial of the LJ force compute
+unsigned int ref_get_virial_pitch(void* h)
+    {
+    return static_cast<RefSystem*>(h)->lj->getVirialArray().getPitch();
+    }
+
+void ref_get_forces(void* h, float* force4, float* virial6)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int N = s->pdata->getN();
+    ArrayHandle<Scalar4> f(s->lj->getForceArray(), access_location::host, access_mode::read);
+    memcpy(force4, f.data, sizeof(Scalar4) * N);
+    if (virial6)
+        {
+        unsigned int pitch = s->lj->getVirialArray().getPitch();
+        ArrayHandle<Scalar> v(s->lj->getVirialArray(), access_location::host, access_mode::read);
+        for (unsigned int k = 0; k < 6; k++)
+            memcpy(virial6 + k * N, v.data + k * pitch, sizeof(Scalar) * N);
+        }
+    }
+
+void ref_get_net_force(void* h, float* force4)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    ArrayHandle<Scalar4> f(s->pdata->getNetForce(), access_location::host, access_mode::read);
+    memcpy(force4, f.data, sizeof(Scalar4) * s->pdata->getN());
+    }
+
+//! Neighbor list allocation size (per-type Nmax is recovered from head-list differences by the caller)
+unsigned int ref_get_nlist_size(void* h)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    return s->nlist->getNListArray().getNumElements();
+    }
+
+void ref_get_nlist(void* h, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist, unsigned int nlist_len)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int N = s->pdata->getN();
+    if (n_neigh)
+        {
+        ArrayHandle<unsigned int> a(s->nlist->getNNeighArray(), access_location::host, access_mode::read);
+        memcpy(n_neigh, a.data, sizeof(unsigned int) * N);
+        }
+    if (head)
+        {
+        ArrayHandle<unsigned int> a(s->nlist->getHeadList(), access_location::host, access_mode::read);
+        memcpy(head, a.data, sizeof(unsigned int) * N);
+        }
+    if (nlist)
+        {
+        ArrayHandle<unsigned int> a(s->nlist->getNListArray(), access_location::host, access_mode::read);
+        unsigned int n = std::min(nlist_len, (unsigned int)s->nlist->getNListArray().getNumElements());
+        memcpy(nlist, a.data, sizeof(unsigned int) * n);
+        }
+    }
+
+void ref_get_nlist_stats(void* h, unsigned long long* out3)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    out3[0] = s->nlist->getNumUpdates();
+    out3[1] = s->nlist->getSmallestRebuild();
+    out3[2] = 0;
+    }
+
+//! Cell list geometry: dim[3], Nmax, n_adj
+void ref_get_cell_dims(void* h, unsigned int* out5)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    uint3 dim = s->cl->getDim();
+    out5[0] = dim.x; out5[1] = dim.y; out5[2] = dim.z;
+    out5[3] = s->cl->getNmax();
+    out5[4] = s->cl->getCellAdjIndexer().getW();
+    }
+
+void ref_get_cell_list(void* h, unsigned int* cell_size, float* xyzf4, unsigned int* cell_adj)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int ncell = s->cl->getCellIndexer().getNumElements();
+    if (cell_size)
+        {
+        ArrayHandle<unsigned int> a(s->cl->getCellSizeArray(), access_location::host, access_mode::read);
+        memcpy(cell_size, a.data, sizeof(unsigned int) * ncell);
+        }
+    if (xyzf4)
+        {
+        ArrayHandle<Scalar4> a(s->cl->getXYZFArray(), access_location::host, access_mode::read);
+        memcpy(xyzf4, a.data, sizeof(Scalar4) * s->cl->getCellListIndexer().getNumElements());
+        }
+    if (cell_adj)
+        {
+        ArrayHandle<unsigned int> a(s->cl->getCellAdjArray(), access_location::host, access_mode::read);
+        memcpy(cell_adj, a.data, sizeof(unsigned int) * s->cl->getCellAdjIndexer().getNumElements());
+        }
+    }
+
+//! ComputeThermo at timestep ts: out = {KE, PE, temperature, pressure, ndof}
+int ref_get_thermo(void* h, unsigned int ts, double* out5)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->thermo->setNDOF(s->integrator->getNDOF(s->group_all));
+    s->thermo->compute(ts);
+    out5[0] = s->thermo->getKineticEnergy();
+    out5[1] = s->thermo->getPotentialEnergy();
+    out5[2] = s->thermo->getTemperature();
+    out5[3] = s->virial ? s->thermo->getPressure() : 0.0;
+    out5[4] = s->thermo->getNDOF();
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! Double-precision sum of the LJ per-particle energies (ForceCompute::calcEnergySum, hoomd/ForceCompute.cc:82-102)
+double ref_get_lj_energy(void* h)
+    {
+    return static_cast<RefSystem*>(h)->lj->calcEnergySum();
+    }
+
+// ---------------------------------------------------------------- stand-alone pieces of the reference headers
+//! hoomd/Saru.h: n draws of u32() and of s<float>(-1,1) from Saru(seed1, seed2, seed3)
+void ref_saru(unsigned int seed1, unsigned int seed2, unsigned int seed3, unsigned int n, unsigned int* u32_out,
+              float* f_out)
+    {
+    if (u32_out)
+        {
+        hoomd::detail::Saru saru(seed1, seed2, seed3);
+        for (unsigned int i = 0; i < n; i++) u32_out[i] = saru.u32();
+        }
+    if (f_out)
+        {
+        hoomd::detail::Saru saru(seed1, seed2, seed3);
+        for (unsigned int i = 0; i < n; i++) f_out[i] = saru.s<float>(-1, 1);
+        }
+    }
+
+//! hoomd/SFCPackUpdater: run one sort now (whatever the period) -- particle order afterwards via ref_get_particles(tag)
+int ref_sort_now(void* h)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    if (!s->sorter) s->sorter = std::shared_ptr<SFCPackUpdater>(new SFCPackUpdater(s->sysdef));
+    s->sorter->update(s->timestep);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+} // extern "C"
