@@ -1,0 +1,324 @@
+// CellList for sm_100a: count -> scan -> scatter -> in-cell rank.  Replaces hoomd/CellListGPU.cu:40-219 (atomicInc into a
+// padded Ncells x Nmax array) with contiguous, index-ordered cell ranges.  See include/hoomd_b200.h for the layout.
+#include "common.cuh"
+
+namespace b200
+{
+// ---- K1: bin every particle, count cell occupancies ---------------------------------------------------------------
+// 1 thread / particle, coalesced float4 load.  atomicAdd on cell_count returns an arbitrary slot; the final in-cell
+// order is fixed later by rank (k_cell_rank), so the result is deterministic.
+__global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cell_count,
+                                                  unsigned int* __restrict__ particle_cell,
+                                                  unsigned int* __restrict__ particle_slot,
+                                                  unsigned int* __restrict__ conditions,
+                                                  const float4* __restrict__ pos, unsigned int N, unsigned int n_ghost,
+                                                  Box box, uint3 dim, float3 ghost_width)
+    {
+    unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N + n_ghost) return;
+    float4 p = pos[n];
+    unsigned int cell = B200_NOT_BINNED, slot = 0;
+    if (isnan(p.x) || isnan(p.y) || isnan(p.z))
+        atomicMax(&conditions[1], n + 1);
+    else
+        {
+        int3 b;
+        if (particle_bin(make_float3(p.x, p.y, p.z), box, ghost_width, dim, b))
+            {
+            cell = ((unsigned int)b.z * dim.y + (unsigned int)b.y) * dim.x + (unsigned int)b.x;
+            slot = atomicAdd(&cell_count[cell], 1u);
+            }
+        else if (n < N)
+            atomicMax(&conditions[2], n + 1); // ghosts out of range are silently ignored (CellList.cc:494-498)
+        }
+    particle_cell[n] = cell;
+    particle_slot[n] = slot;
+    }
+
+// ---- K2: exclusive scan of the occupancies (single CTA, 1024 threads, warp-shuffle scan, sequential tiles) --------
+// ncells is 8e3 (64k particles) .. 1e6 (8M particles); the scan reads 4 B/cell once and is far off the critical path.
+__global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ cell_start,
+                                                    const unsigned int* __restrict__ cell_count, unsigned int ncells,
+                                                    unsigned int* __restrict__ conditions)
+    {
+    __shared__ unsigned int warp_sums[32];
+    __shared__ unsigned int carry_s;
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    unsigned int max_occ = 0;
+    __syncthreads();
+    // each thread owns 4 consecutive cells per tile (16 B vector load when aligned)
+    for (unsigned int base = 0; base < ncells; base += 4096)
+        {
+        unsigned int i0 = base + threadIdx.x * 4;
+        const unsigned int carry = carry_s; // read before the barrier below; warp 0 rewrites it after that barrier
+        unsigned int c[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) c[k] = (i0 + k < ncells) ? cell_count[i0 + k] : 0u;
+        max_occ = max(max(max_occ, max(c[0], c[1])), max(c[2], c[3]));
+        unsigned int tsum = c[0] + c[1] + c[2] + c[3];
+        unsigned int incl = tsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+            }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0)
+            {
+            unsigned int w = warp_sums[lane];
+            unsigned int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+                {
+                unsigned int v = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += v;
+                }
+            warp_sums[lane] = wi - w; // exclusive
+            if (lane == 31) carry_s = carry + wi;
+            }
+        __syncthreads();
+        unsigned int excl = carry + warp_sums[warp] + incl - tsum;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            {
+            if (i0 + k < ncells) cell_start[i0 + k] = excl;
+            excl += c[k];
+            }
+        __syncthreads();
+        }
+    if (threadIdx.x == 0) cell_start[ncells] = carry_s;
+    // conditions.x = largest occupancy (what the reference's overflow protocol would grow Nmax to)
+    for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
+    if (lane == 0 && max_occ) atomicMax(&conditions[0], max_occ);
+    }
+
+// ---- K3: scatter particle indices to their (arbitrary) slot inside the cell range ----------------------------------
+__global__ void __launch_bounds__(256) k_cell_scatter(unsigned int* __restrict__ scratch_idx,
+                                                      const unsigned int* __restrict__ cell_start,
+                                                      const unsigned int* __restrict__ particle_cell,
+                                                      const unsigned int* __restrict__ particle_slot, unsigned int ntot)
+    {
+    unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= ntot) return;
+    unsigned int cell = particle_cell[n];
+    if (cell == B200_NOT_BINNED) return;
+    scratch_idx[cell_start[cell] + particle_slot[n]] = n;
+    }
+
+// ---- K4: rank every entry inside its cell by particle index and emit the final cell-sorted arrays -------------------
+// 1 thread / entry.  A cell holds ~8 (rho=0.2) .. ~30 (rho=1.2) entries, so the rank loop is a handful of L1-resident
+// 4 B loads; output writes are 16 B and land inside one contiguous cell range.
+__global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyzf, unsigned int* __restrict__ cell_type,
+                                                   unsigned int* __restrict__ cell_idx,
+                                                   const unsigned int* __restrict__ scratch_idx,
+                                                   const unsigned int* __restrict__ cell_start,
+                                                   const unsigned int* __restrict__ particle_cell,
+                                                   const float4* __restrict__ pos, const float* __restrict__ charge,
+                                                   unsigned int ncells, int flag_charge, int flag_type)
+    {
+    unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int nbinned = cell_start[ncells];
+    if (e >= nbinned) return;
+    unsigned int n = scratch_idx[e];
+    unsigned int cell = particle_cell[n];
+    unsigned int s = cell_start[cell], t = cell_start[cell + 1];
+    unsigned int rank = 0;
+    for (unsigned int k = s; k < t; k++) rank += (scratch_idx[k] < n) ? 1u : 0u;
+    float4 p = pos[n];
+    float flag;
+    if (flag_charge) flag = charge[n];
+    else if (flag_type) flag = p.w;
+    else flag = __int_as_float((int)n);
+    cell_xyzf[s + rank] = make_float4(p.x, p.y, p.z, flag);
+    if (cell_type) cell_type[s + rank] = (unsigned int)__float_as_int(p.w);
+    if (cell_idx) cell_idx[s + rank] = n;
+    }
+
+// ---- export to the reference's padded layout ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_cell_export(unsigned int* __restrict__ cell_size, float4* __restrict__ xyzf,
+                                                     float4* __restrict__ tdb, unsigned int* __restrict__ conditions,
+                                                     const unsigned int* __restrict__ cell_start,
+                                                     const float4* __restrict__ cell_xyzf,
+                                                     const unsigned int* __restrict__ cell_idx,
+                                                     const float4* __restrict__ pos, const float* __restrict__ diameter,
+                                                     const unsigned int* __restrict__ body, unsigned int ncells,
+                                                     unsigned int Nmax)
+    {
+    // one warp per cell: lanes stride the cell's entries
+    unsigned int cell = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    unsigned int lane = threadIdx.x & 31;
+    if (cell >= ncells) return;
+    unsigned int s = cell_start[cell], size = cell_start[cell + 1] - s;
+    if (lane == 0)
+        {
+        cell_size[cell] = size;
+        if (size > Nmax) atomicMax(&conditions[0], size);
+        }
+    for (unsigned int o = lane; o < size && o < Nmax; o += 32)
+        {
+        xyzf[(size_t)cell * Nmax + o] = cell_xyzf[s + o];
+        if (tdb)
+            {
+            unsigned int n = cell_idx[s + o];
+            tdb[(size_t)cell * Nmax + o] = make_float4(pos[n].w, diameter ? diameter[n] : 1.0f,
+                                                       __int_as_float(body ? (int)body[n] : -1), 0.0f);
+            }
+        }
+    }
+
+// ---- adjacency list on the device (CellList::initializeCellAdj) -----------------------------------------------------
+__device__ __forceinline__ int sorted_unique_axis(int c, int r, int m, int* out)
+    {
+    // wrapped indices c-r..c+r mod m, sorted ascending and de-duplicated; at most 2r+1 <= 7 values
+    int n = 0;
+    for (int d = -r; d <= r; d++)
+        {
+        int w = (c + d) % m;
+        if (w < 0) w += m;
+        int k = 0;
+        while (k < n && out[k] < w) k++;
+        if (k < n && out[k] == w) continue;
+        for (int q = n; q > k; q--) out[q] = out[q - 1];
+        out[k] = w;
+        n++;
+        }
+    return n;
+    }
+
+__global__ void __launch_bounds__(128) k_cell_adj(unsigned int* __restrict__ cell_adj, uint3 dim, int radius,
+                                                  unsigned int n_adj)
+    {
+    unsigned int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int ncells = dim.x * dim.y * dim.z;
+    if (cell >= ncells) return;
+    int i = cell % dim.x, j = (cell / dim.x) % dim.y, k = cell / (dim.x * dim.y);
+    int xi[7], yj[7], zk[7];
+    int nx = sorted_unique_axis(i, radius, dim.x, xi);
+    int ny = sorted_unique_axis(j, radius, dim.y, yj);
+    int nz = sorted_unique_axis(k, radius, dim.z, zk);
+    // id = (k*dimy + j)*dimx + i is lexicographic in (k,j,i): the sorted unique id list is the product of the sorted axes
+    unsigned int a = 0;
+    for (int c = 0; c < nz; c++)
+        for (int b = 0; b < ny; b++)
+            for (int q = 0; q < nx; q++)
+                if (a < n_adj)
+                    cell_adj[(size_t)cell * n_adj + a++] = ((unsigned int)zk[c] * dim.y + yj[b]) * dim.x + xi[q];
+    }
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+void b200_box_init(b200_box* box, float Lx, float Ly, float Lz)
+    {
+    const float L[3] = {Lx, Ly, Lz};
+    for (int d = 0; d < 3; d++)
+        {
+        box->L[d] = L[d];
+        box->hi[d] = L[d] / 2.0f;
+        box->lo[d] = -box->hi[d];
+        box->Linv[d] = 1.0f / L[d];
+        box->periodic[d] = 1;
+        }
+    box->xy = box->xz = box->yz = 0.0f;
+    box->_pad = 0;
+    }
+
+void b200_box_init_lohi(b200_box* box, const float lo[3], const float hi[3], const unsigned char periodic[3])
+    {
+    for (int d = 0; d < 3; d++)
+        {
+        box->lo[d] = lo[d];
+        box->hi[d] = hi[d];
+        box->Linv[d] = 1.0f / (hi[d] - lo[d]);
+        box->L[d] = hi[d] - lo[d];
+        box->periodic[d] = periodic[d];
+        }
+    box->xy = box->xz = box->yz = 0.0f;
+    box->_pad = 0;
+    }
+
+void b200_cell_list_dimensions(const b200_box* box, float nominal_width, unsigned int multiple,
+                               float ghost_layer_width, b200_dim3* dim, float ghost_width[3])
+    {
+    // hoomd/CellList.cc:69-131 (3D).  L = nearest plane distance = box length for an orthorhombic box.
+    unsigned int d[3];
+    if (multiple == 0) multiple = 1;
+    for (int a = 0; a < 3; a++)
+        {
+        unsigned int v = (unsigned int)(box->L[a] / nominal_width);
+        d[a] = (v / multiple) * multiple;
+        ghost_width[a] = 0.0f;
+        }
+    if (ghost_layer_width > 0.0f)
+        {
+        for (int a = 0; a < 3; a++)
+            if (!box->periodic[a]) ghost_width[a] = ghost_layer_width;
+        for (int a = 0; a < 3; a++)
+            if (!box->periodic[a])
+                {
+                float cell_size = box->L[a] / (float)d[a];
+                d[a] += (unsigned int)(int)ceilf(ghost_width[a] / cell_size);
+                }
+        }
+    for (int a = 0; a < 3; a++)
+        if (d[a] == 0) d[a] = 1;
+    dim->x = d[0]; dim->y = d[1]; dim->z = d[2];
+    }
+
+int b200_compute_cell_list(const b200_cell_list_args* a, b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!box_is_orthorhombic(a->box)) return (int)cudaErrorNotSupported;
+    const unsigned int ntot = a->N + a->n_ghost;
+    const unsigned int ncells = a->dim.x * a->dim.y * a->dim.z;
+    Box box = make_box(a->box);
+    uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
+    float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
+    cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
+    if (ntot)
+        k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
+                                                            a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
+                                                            box, dim, gw);
+    k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions);
+    if (ntot)
+        {
+        k_cell_scatter<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
+                                                                a->d_particle_slot, ntot);
+        k_cell_rank<<<(ntot + 255) / 256, 256, 0, stream>>>((float4*)a->d_cell_xyzf, a->d_cell_type, a->d_cell_idx,
+                                                             a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
+                                                             (const float4*)a->d_pos, a->d_charge, ncells,
+                                                             a->flag_charge, a->flag_type);
+        }
+    return (int)cudaGetLastError();
+    }
+
+int b200_cell_list_export_padded(unsigned int* d_cell_size, float* d_xyzf, float* d_tdb, unsigned int* d_conditions,
+                                 const unsigned int* d_cell_start, const float* d_cell_xyzf,
+                                 const unsigned int* d_cell_idx, const float* d_pos, const float* d_diameter,
+                                 const unsigned int* d_body, unsigned int ncells, unsigned int Nmax,
+                                 b200_stream_t stream)
+    {
+    if (d_tdb && !d_cell_idx) return (int)cudaErrorInvalidValue;
+    unsigned int threads = ncells * 32;
+    k_cell_export<<<(threads + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        d_cell_size, (float4*)d_xyzf, (float4*)d_tdb, d_conditions, d_cell_start, (const float4*)d_cell_xyzf,
+        d_cell_idx, (const float4*)d_pos, d_diameter, d_body, ncells, Nmax);
+    return (int)cudaGetLastError();
+    }
+
+int b200_cell_list_build_adjacency(unsigned int* d_cell_adj, b200_dim3 dim, unsigned int radius, unsigned int n_adj,
+                                   b200_stream_t stream)
+    {
+    if (radius > 3) return (int)cudaErrorInvalidValue;
+    unsigned int ncells = dim.x * dim.y * dim.z;
+    k_cell_adj<<<(ncells + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_cell_adj, make_uint3(dim.x, dim.y, dim.z),
+                                                                        (int)radius, n_adj);
+    return (int)cudaGetLastError();
+    }
+
+} // extern "C"

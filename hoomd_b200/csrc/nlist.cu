@@ -1,0 +1,319 @@
+// NeighborListBinned for sm_100a.  One warp per particle walks the <=27 adjacent cells as <=9+ contiguous ranges of the
+// cell-sorted array (x-adjacent cells are adjacent in memory), 32 candidates per coalesced 512 B load, ballot/popc
+// compaction into the CSR list.  Membership arithmetic and entry order are those of the CPU oracle
+// hoomd/md/NeighborListBinned.cc:144-236 (see include/hoomd_b200.h).
+#include "common.cuh"
+
+namespace b200
+{
+// sorted, de-duplicated {c-1, c, c+1} wrapped into [0,m) (periodic) or clipped (non-periodic: the reference wraps these
+// too, hoomd/CellList.cc:399-411, but a wrapped cell of a non-periodic direction is >= one cell width away and can never
+// pass the distance test, so skipping it changes nothing)
+__device__ __forceinline__ int axis_set(int c, int m, bool periodic, int out[3])
+    {
+    int n = 0;
+#pragma unroll
+    for (int d = -1; d <= 1; d++)
+        {
+        int w = c + d;
+        if (w < 0) { if (!periodic) continue; w += m; if (w < 0) w += m; }
+        if (w >= m) { if (!periodic) continue; w -= m; if (w >= m) w -= m; }
+        // insert into the sorted unique list
+        bool dup = false;
+        for (int k = 0; k < n; k++) dup |= (out[k] == w);
+        if (dup) continue;
+        int k = n;
+        while (k > 0 && out[k - 1] > w) { out[k] = out[k - 1]; k--; }
+        out[k] = w;
+        n++;
+        }
+    return n;
+    }
+
+template<bool MULTI_TYPE>
+__global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__ nlist,
+                                                      unsigned int* __restrict__ n_neigh,
+                                                      float4* __restrict__ last_pos,
+                                                      unsigned int* __restrict__ conditions,
+                                                      const unsigned int* __restrict__ Nmax,
+                                                      const unsigned int* __restrict__ head_list,
+                                                      const float4* __restrict__ pos, unsigned int N,
+                                                      const unsigned int* __restrict__ cell_start,
+                                                      const float4* __restrict__ cell_xyzf,
+                                                      const unsigned int* __restrict__ cell_type, uint3 dim, Box box,
+                                                      float3 ghost_width, const float* __restrict__ r_cut,
+                                                      const float* __restrict__ r_listsq, unsigned int ntypes,
+                                                      int half_storage)
+    {
+    const unsigned int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned int lane = threadIdx.x & 31;
+    if (i >= N) return;
+    const float4 pi4 = pos[i];
+    const float3 pi = make_float3(pi4.x, pi4.y, pi4.z);
+    const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
+    const unsigned int Nmax_i = Nmax[type_i];
+    const unsigned int head_i = head_list[i];
+    // single-type fast path keeps the two table entries in registers
+    const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
+    const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
+
+    int3 b;
+    unsigned int n = 0;
+    if (particle_bin(pi, box, ghost_width, dim, b))
+        {
+        int xs[3], ys[3], zs[3];
+        const int nx = axis_set(b.x, dim.x, box.periodic.x, xs);
+        const int ny = axis_set(b.y, dim.y, box.periodic.y, ys);
+        const int nz = axis_set(b.z, dim.z, box.periodic.z, zs);
+        const unsigned int lanemask_lt = (1u << lane) - 1u;
+        for (int c = 0; c < nz; c++)
+            for (int q = 0; q < ny; q++)
+                {
+                const unsigned int row = ((unsigned int)zs[c] * dim.y + (unsigned int)ys[q]) * dim.x;
+                int r0 = 0;
+                while (r0 < nx)
+                    {
+                    int r1 = r0;
+                    while (r1 + 1 < nx && xs[r1 + 1] == xs[r1] + 1) r1++;
+                    const unsigned int beg = cell_start[row + xs[r0]];
+                    const unsigned int end = cell_start[row + xs[r1] + 1];
+                    for (unsigned int base = beg; base < end; base += 32)
+                        {
+                        const unsigned int e = base + lane;
+                        bool hit = false;
+                        unsigned int j = 0;
+                        if (e < end)
+                            {
+                            const float4 cj = cell_xyzf[e];
+                            j = (unsigned int)__float_as_int(cj.w);
+                            float rc, rlsq;
+                            if (MULTI_TYPE)
+                                {
+                                const unsigned int tj = cell_type[e];
+                                rc = __ldg(&r_cut[type_i * ntypes + tj]);
+                                rlsq = __ldg(&r_listsq[type_i * ntypes + tj]);
+                                }
+                            else
+                                {
+                                rc = rcut_00;
+                                rlsq = rlsq_00;
+                                }
+                            const bool excluded = (j == i) || (rc <= 0.0f);
+                            float3 dx = make_float3(__fsub_rn(pi.x, cj.x), __fsub_rn(pi.y, cj.y), __fsub_rn(pi.z, cj.z));
+                            dx = min_image_exact(dx, box);
+                            const float drsq = dot_exact(dx);
+                            hit = !excluded && (drsq <= rlsq) && (!half_storage || i < j);
+                            }
+                        const unsigned int mask = __ballot_sync(0xffffffffu, hit);
+                        if (hit)
+                            {
+                            const unsigned int k = n + __popc(mask & lanemask_lt);
+                            if (k < Nmax_i) nlist[head_i + k] = j;
+                            }
+                        n += __popc(mask);
+                        }
+                    r0 = r1 + 1;
+                    }
+                }
+        }
+    if (lane == 0)
+        {
+        n_neigh[i] = n;
+        if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+        if (last_pos) last_pos[i] = make_float4(pi.x, pi.y, pi.z, 0.0f);
+        }
+    }
+
+// ---- distance check (NeighborList::distanceCheck) -----------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_nlist_dist_check(unsigned int* __restrict__ result,
+                                                          const float4* __restrict__ last_pos,
+                                                          const float4* __restrict__ pos, unsigned int N, Box box,
+                                                          const float* __restrict__ rcut_max, float r_buff,
+                                                          float lambda_min, float3 lambda, unsigned int checkn)
+    {
+    unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool moved = false;
+    if (i < N)
+        {
+        const float4 p = pos[i];
+        const float4 lp = last_pos[i];
+        const float old_rmin = rcut_max[(unsigned int)__float_as_int(p.w)];
+        const float rmax = __fadd_rn(old_rmin, r_buff);
+        const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(rmax, lambda_min), old_rmin), 2.0f);
+        const float maxsq = (delta_max > 0.0f) ? __fmul_rn(delta_max, delta_max) : 0.0f;
+        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(lambda.x, lp.x)), __fsub_rn(p.y, __fmul_rn(lambda.y, lp.y)),
+                                __fsub_rn(p.z, __fmul_rn(lambda.z, lp.z)));
+        dx = min_image_exact(dx, box);
+        moved = dot_exact(dx) >= maxsq;
+        }
+    // one write per warp that saw a mover (all writers store the same value)
+    if (__any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) atomicMax(result, checkn);
+    }
+
+// ---- head list: exclusive scan of Nmax[type_i] -----------------------------------------------------------------------
+// Tile = 256 threads x 8 particles.  reduce -> single-CTA scan of tile sums -> apply.
+constexpr int HL_ITEMS = 8;
+constexpr int HL_TILE = 256 * HL_ITEMS;
+
+__device__ __forceinline__ unsigned int block_exclusive_scan_256(unsigned int v, unsigned int* total)
+    {
+    __shared__ unsigned int ws[8];
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+        }
+    if (lane == 31) ws[warp] = incl;
+    __syncthreads();
+    unsigned int off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        {
+        unsigned int s = ws[w];
+        if (w < (int)warp) off += s;
+        tot += s;
+        }
+    __syncthreads();
+    *total = tot;
+    return off + incl - v;
+    }
+
+__global__ void __launch_bounds__(256) k_head_reduce(unsigned int* __restrict__ tile_sums,
+                                                     const unsigned int* __restrict__ Nmax,
+                                                     const float4* __restrict__ pos, unsigned int N)
+    {
+    unsigned int base = blockIdx.x * HL_TILE + threadIdx.x * HL_ITEMS;
+    unsigned int s = 0;
+#pragma unroll
+    for (int k = 0; k < HL_ITEMS; k++)
+        if (base + k < N) s += Nmax[(unsigned int)__float_as_int(pos[base + k].w)];
+    unsigned int tot;
+    block_exclusive_scan_256(s, &tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+    }
+
+__global__ void __launch_bounds__(256) k_head_scan_tiles(unsigned int* __restrict__ tile_sums, unsigned int ntiles,
+                                                         unsigned int* __restrict__ req_size)
+    {
+    unsigned int carry = 0;
+    for (unsigned int base = 0; base < ntiles; base += 256)
+        {
+        unsigned int v = (base + threadIdx.x < ntiles) ? tile_sums[base + threadIdx.x] : 0u;
+        unsigned int tot;
+        unsigned int ex = block_exclusive_scan_256(v, &tot);
+        if (base + threadIdx.x < ntiles) tile_sums[base + threadIdx.x] = carry + ex;
+        carry += tot;
+        }
+    if (threadIdx.x == 0 && req_size) *req_size = carry;
+    }
+
+__global__ void __launch_bounds__(256) k_head_apply(unsigned int* __restrict__ head_list,
+                                                    const unsigned int* __restrict__ tile_sums,
+                                                    const unsigned int* __restrict__ Nmax,
+                                                    const float4* __restrict__ pos, unsigned int N)
+    {
+    unsigned int base = blockIdx.x * HL_TILE + threadIdx.x * HL_ITEMS;
+    unsigned int v[HL_ITEMS];
+    unsigned int s = 0;
+#pragma unroll
+    for (int k = 0; k < HL_ITEMS; k++)
+        {
+        v[k] = (base + k < N) ? Nmax[(unsigned int)__float_as_int(pos[base + k].w)] : 0u;
+        s += v[k];
+        }
+    unsigned int tot;
+    unsigned int ex = block_exclusive_scan_256(s, &tot) + tile_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < HL_ITEMS; k++)
+        {
+        if (base + k < N) head_list[base + k] = ex;
+        ex += v[k];
+        }
+    }
+
+// single-type closed form: head[i] = i * Nmax[0]
+__global__ void __launch_bounds__(256) k_head_uniform(unsigned int* __restrict__ head_list,
+                                                      unsigned int* __restrict__ req_size,
+                                                      const unsigned int* __restrict__ Nmax, unsigned int N)
+    {
+    unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int m = Nmax[0];
+    if (i < N) head_list[i] = i * m;
+    if (i == 0 && req_size) *req_size = N * m;
+    }
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_nlist_build_head_list(unsigned int* d_head_list, unsigned int* d_req_size_nlist, const unsigned int* d_Nmax,
+                               const float* d_pos, unsigned int N, unsigned int ntypes, b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (N == 0)
+        {
+        if (d_req_size_nlist) cudaMemsetAsync(d_req_size_nlist, 0, sizeof(unsigned int), stream);
+        return (int)cudaGetLastError();
+        }
+    if (ntypes == 1)
+        {
+        k_head_uniform<<<(N + 255) / 256, 256, 0, stream>>>(d_head_list, d_req_size_nlist, d_Nmax, N);
+        return (int)cudaGetLastError();
+        }
+    // the tile sums live at the tail of the head list's own allocation?  No: callers own memory; use a small
+    // stream-ordered allocation (ntiles * 4 B, e.g. 16 kB at 8M particles).
+    const unsigned int ntiles = (N + HL_TILE - 1) / HL_TILE;
+    unsigned int* d_tiles = nullptr;
+    cudaError_t err = cudaMallocAsync((void**)&d_tiles, sizeof(unsigned int) * ntiles, stream);
+    if (err != cudaSuccess) return (int)err;
+    k_head_reduce<<<ntiles, 256, 0, stream>>>(d_tiles, d_Nmax, (const float4*)d_pos, N);
+    k_head_scan_tiles<<<1, 256, 0, stream>>>(d_tiles, ntiles, d_req_size_nlist);
+    k_head_apply<<<ntiles, 256, 0, stream>>>(d_head_list, d_tiles, d_Nmax, (const float4*)d_pos, N);
+    cudaFreeAsync(d_tiles, stream);
+    return (int)cudaGetLastError();
+    }
+
+int b200_compute_nlist_binned(const b200_nlist_args* a, b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!box_is_orthorhombic(a->box)) return (int)cudaErrorNotSupported;
+    if (a->N == 0) return 0;
+    if (a->ntypes > 1 && !a->d_cell_type) return (int)cudaErrorInvalidValue;
+    Box box = make_box(a->box);
+    uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
+    float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
+    const unsigned int warps_per_block = 4;
+    const unsigned int grid = (a->N + warps_per_block - 1) / warps_per_block;
+    if (a->ntypes > 1)
+        k_nlist_binned<true><<<grid, 128, 0, stream>>>(a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions,
+                                                       a->d_Nmax, a->d_head_list, (const float4*)a->d_pos, a->N,
+                                                       a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type,
+                                                       dim, box, gw, a->d_r_cut, a->d_r_listsq, a->ntypes,
+                                                       a->half_storage);
+    else
+        k_nlist_binned<false><<<grid, 128, 0, stream>>>(a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos,
+                                                        a->d_conditions, a->d_Nmax, a->d_head_list,
+                                                        (const float4*)a->d_pos, a->N, a->d_cell_start,
+                                                        (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, gw,
+                                                        a->d_r_cut, a->d_r_listsq, a->ntypes, a->half_storage);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nlist_needs_update_check(unsigned int* d_result, const float* d_last_pos, const float* d_pos, unsigned int N,
+                                  const b200_box* box, const float* d_rcut_max, float r_buff, unsigned int ntypes,
+                                  float lambda_min, const float lambda[3], unsigned int checkn, b200_stream_t stream)
+    {
+    (void)ntypes;
+    if (!box_is_orthorhombic(*box)) return (int)cudaErrorNotSupported;
+    if (N == 0) return 0;
+    k_nlist_dist_check<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        d_result, (const float4*)d_last_pos, (const float4*)d_pos, N, make_box(*box), d_rcut_max, r_buff, lambda_min,
+        make_float3(lambda[0], lambda[1], lambda[2]), checkn);
+    return (int)cudaGetLastError();
+    }
+
+} // extern "C"

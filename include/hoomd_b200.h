@@ -1,0 +1,343 @@
+/* hoomd_b200.h -- C ABI of the B200-native HOOMD-blue MD inner loop.
+ *
+ * Two layers, both plain C (pointers, sizes, POD structs; no C++/torch types):
+ *
+ *  1. KERNEL DRIVERS (b200_*): one entry point per reference GPU driver `gpu_*()`.  The reference's `...GPU.cc`
+ *     host classes call these with raw device pointers taken from ArrayHandle<T>(..., access_location::device).
+ *     Same convention as the reference drivers: return cudaError_t-compatible int (0 = cudaSuccess), never throw,
+ *     never synchronise, caller owns every buffer, everything is enqueued on the given stream (0 = legacy default
+ *     stream, which is what the reference uses everywhere).
+ *
+ *  2. ENGINE (b200_sys_*): a device-resident system (ParticleData + CellList + NeighborListBinned +
+ *     PotentialPairLJ + IntegratorTwoStep{TwoStepNVE|TwoStepLangevin} + SFCPackUpdater + ComputeThermo) with the
+ *     reference's step semantics (hoomd/System.cc:484-599, hoomd/md/IntegratorTwoStep.cc:96-161), driven without a
+ *     host round trip per step (rebuild decision consumed on the device, whole step captured in a CUDA graph).
+ *     This is what the python job-script surface (hoomd_b200.md.nlist.cell / md.pair.lj / md.integrate.*) drives.
+ *
+ * All floating point is FP32 (the reference's SINGLE_PRECISION build), indices/tags/counts are uint32, images int32x3.
+ * Citations are relative to the reference tree (HOOMD-blue 2.3.0).
+ */
+#ifndef HOOMD_B200_H_
+#define HOOMD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * POD mirrors of the reference's by-value kernel arguments
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* BoxDim (hoomd/BoxDim.h:568-576).  Orthorhombic only in this round: xy = xz = yz = 0 (every BASELINE config);
+ * a non-zero tilt makes the drivers return cudaErrorNotSupported (801). */
+typedef struct b200_box
+    {
+    float lo[3];
+    float hi[3];
+    float L[3];
+    float Linv[3];
+    float xy, xz, yz;
+    unsigned char periodic[3];
+    unsigned char _pad;
+    } b200_box;
+
+/* BoxDim(Lx,Ly,Lz): hi = L/2, lo = -hi, Linv = 1/L in FP32, periodic = (1,1,1)  (hoomd/BoxDim.h:93-98,165-171) */
+B200_API void b200_box_init(b200_box* box, float Lx, float Ly, float Lz);
+/* BoxDim(lo,hi,periodic)  (hoomd/BoxDim.h:129-134,193-199) */
+B200_API void b200_box_init_lohi(b200_box* box, const float lo[3], const float hi[3], const unsigned char periodic[3]);
+
+/* Index3D(w,h,d): (i,j,k) -> (k*h + j)*w + i  (hoomd/Index1D.h) */
+typedef struct b200_dim3 { unsigned int x, y, z; } b200_dim3;
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * CellList  -- replaces gpu_compute_cell_list (hoomd/CellListGPU.cuh:21-41, kernel hoomd/CellListGPU.cu:40-156)
+ * and gpu_sort_cell_list (hoomd/CellListGPU.cuh:43-56).
+ *
+ * B200 layout: cells are CONTIGUOUS RANGES of a cell-sorted particle array (count -> scan -> scatter), no Nmax
+ * padding and therefore no overflow/retry loop (hoomd/CellList.cc:181-196).  Inside a cell, entries are ordered by
+ * particle index, i.e. the order the CPU reference produces (hoomd/CellList.cc:474-563) and the order
+ * nlist.cell(deterministic=True) restores on the GPU (hoomd/CellListGPU.cc:92-118).
+ *
+ *   cell_start[ncells+1]   exclusive prefix sum of the cell occupancies (cell c = [cell_start[c], cell_start[c+1]))
+ *   cell_xyzf [N+n_ghost]  (x, y, z, flag) per cell-sorted entry; flag = particle index bits (default), type or charge
+ *   cell_type [N+n_ghost]  type of each entry (the .x of the reference's tdb array), optional
+ *   cell_idx  [N+n_ghost]  particle index of each entry, optional (reference: getIndexArray)
+ *
+ * conditions (uint3, same meaning as hoomd/CellList.cc:575-621): .x = largest cell occupancy seen,
+ * .y = index+1 of a particle with a NaN coordinate, .z = index+1 of a local particle outside the box.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct b200_cell_list_args
+    {
+    /* outputs */
+    unsigned int* d_cell_start;   /* [ncells + 1] */
+    float*        d_cell_xyzf;    /* [4 * (N + n_ghost)] */
+    unsigned int* d_cell_type;    /* [N + n_ghost] or NULL */
+    unsigned int* d_cell_idx;     /* [N + n_ghost] or NULL */
+    unsigned int* d_conditions;   /* [3] ; caller zeroes it (resetConditions) */
+    /* scratch owned by the caller */
+    unsigned int* d_cell_count;   /* [ncells] */
+    unsigned int* d_particle_cell;/* [N + n_ghost] cell of every particle (0xffffffff = not binned) */
+    unsigned int* d_particle_slot;/* [N + n_ghost] */
+    unsigned int* d_scratch_idx;  /* [N + n_ghost] */
+    /* inputs */
+    const float*  d_pos;          /* Scalar4[N + n_ghost] */
+    const float*  d_charge;       /* Scalar[N + n_ghost] or NULL (needed when flag_charge) */
+    unsigned int  N;
+    unsigned int  n_ghost;
+    int           flag_charge;    /* CellList::setFlagCharge */
+    int           flag_type;      /* CellList::setFlagType */
+    b200_box      box;
+    b200_dim3     dim;            /* CellList::getDim() */
+    float         ghost_width[3]; /* CellList::getGhostWidth() */
+    } b200_cell_list_args;
+
+B200_API int b200_compute_cell_list(const b200_cell_list_args* args, b200_stream_t stream);
+
+/* CellList::computeDimensions (hoomd/CellList.cc:69-131), host arithmetic only.  n_extra_ghost_cells: whether the box
+ * is a domain-decomposed local box whose non-periodic directions get extra ghost cells (hoomd/CellList.cc:103-118). */
+B200_API void b200_cell_list_dimensions(const b200_box* box, float nominal_width, unsigned int multiple,
+                                        float ghost_layer_width, b200_dim3* dim, float ghost_width[3]);
+
+/* Reference-layout export: cell_size[ncells], xyzf[Nmax*ncells] (cli(offset,cell) = cell*Nmax + offset), and the
+ * (type, diameter, body, 0) tdb array, exactly as getCellSizeArray()/getXYZFArray()/getTDBArray() hold them
+ * (hoomd/CellList.h:263-300).  Entries beyond Nmax are dropped and conditions.x records the needed Nmax, like the
+ * reference's overflow protocol. */
+B200_API int b200_cell_list_export_padded(unsigned int* d_cell_size, float* d_xyzf, float* d_tdb,
+                                          unsigned int* d_conditions, const unsigned int* d_cell_start,
+                                          const float* d_cell_xyzf, const unsigned int* d_cell_idx,
+                                          const float* d_pos, const float* d_diameter, const unsigned int* d_body,
+                                          unsigned int ncells, unsigned int Nmax, b200_stream_t stream);
+
+/* CellList::initializeCellAdj (hoomd/CellList.cc:373-436) on the device: per cell the sorted, de-duplicated list of
+ * the (2r+1)^3 wrapped neighbor cells; n_adj = prod(min(dim, 2r+1)); layout cadji(a, cell) = cell*n_adj + a. */
+B200_API int b200_cell_list_build_adjacency(unsigned int* d_cell_adj, b200_dim3 dim, unsigned int radius,
+                                            unsigned int n_adj, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * NeighborList  -- replaces gpu_nlist_build_head_list (hoomd/md/NeighborListGPU.cu:400-433),
+ * gpu_compute_nlist_binned (hoomd/md/NeighborListGPUBinned.cu:570-628), gpu_nlist_needs_update_check_new
+ * (hoomd/md/NeighborListGPU.cu:84-113).  Results follow the CPU oracle hoomd/md/NeighborListBinned.cc:79-240 bit for
+ * bit: dx = pos_i - pos_j, host-form minImage (hoomd/BoxDim.h:301-348), dr^2 = (dx*dx + dy*dy) + dz*dz without FMA
+ * contraction, inclusion iff dr^2 <= r_listsq(type_i,type_j), full storage mode, and the same ENTRY ORDER as the CPU
+ * loop (neighbor cells in ascending cell id, occupants in ascending particle index).
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* head[i] = exclusive scan of Nmax[type_i]; *d_req_size = total (NeighborList::buildHeadList, NeighborList.cc:1336-1357) */
+B200_API int b200_nlist_build_head_list(unsigned int* d_head_list, unsigned int* d_req_size_nlist,
+                                        const unsigned int* d_Nmax, const float* d_pos, unsigned int N,
+                                        unsigned int ntypes, b200_stream_t stream);
+
+typedef struct b200_nlist_args
+    {
+    /* outputs */
+    unsigned int* d_nlist;        /* [>= head[N-1] + Nmax[type_{N-1}]] */
+    unsigned int* d_n_neigh;      /* [N] */
+    float*        d_last_pos;     /* Scalar4[N] or NULL: (x,y,z,0) at build time (setLastUpdatedPos, NeighborList.cc:1044-1066) */
+    unsigned int* d_conditions;   /* [ntypes]: max(n_neigh) per type where it exceeded Nmax[type] (NeighborListBinned.cc:225) */
+    /* inputs */
+    const unsigned int* d_Nmax;      /* [ntypes] */
+    const unsigned int* d_head_list; /* [N] */
+    const float*  d_pos;             /* Scalar4[N + n_ghost] */
+    unsigned int  N;                 /* local particles (lists are built for these only) */
+    const unsigned int* d_cell_start;
+    const float*  d_cell_xyzf;       /* flag must be the particle index */
+    const unsigned int* d_cell_type; /* may be NULL when ntypes == 1 */
+    b200_dim3     dim;
+    b200_box      box;
+    float         ghost_width[3];
+    const float*  d_r_cut;           /* [ntypes*ntypes] r_cut(i,j); <= 0 disables the pair (NeighborListBinned.cc:193) */
+    const float*  d_r_listsq;        /* [ntypes*ntypes] (r_cut+r_buff)^2 computed like NeighborList::updateRList (NeighborList.cc:354-400) */
+    unsigned int  ntypes;
+    int           half_storage;      /* 1: keep only i<j (NeighborList::half); GPU classes always use 0 */
+    } b200_nlist_args;
+
+B200_API int b200_compute_nlist_binned(const b200_nlist_args* args, b200_stream_t stream);
+
+/* *d_result = checkn if any particle moved >= its threshold since d_last_pos (NeighborList::distanceCheck,
+ * NeighborList.cc:964-1040): |minImage(pos - lambda*last_pos)|^2 >= max(0,((rcut_max_i+r_buff)*lambda_min - rcut_max_i)/2)^2 */
+B200_API int b200_nlist_needs_update_check(unsigned int* d_result, const float* d_last_pos, const float* d_pos,
+                                           unsigned int N, const b200_box* box, const float* d_rcut_max, float r_buff,
+                                           unsigned int ntypes, float lambda_min, const float lambda[3],
+                                           unsigned int checkn, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * PotentialPair<EvaluatorPairLJ>  -- replaces gpu_compute_ljtemp_forces(const pair_args_t&, const Scalar2*)
+ * (hoomd/md/AllDriverPotentialPairGPU.cuh:20-22, hoomd/md/PotentialPairGPU.cuh:26-98,579-689); arithmetic of
+ * hoomd/md/PotentialPair.h:309-522 + hoomd/md/EvaluatorPairLJ.h:137-158.
+ * ------------------------------------------------------------------------------------------------------------- */
+enum { B200_SHIFT_NONE = 0, B200_SHIFT_SHIFT = 1, B200_SHIFT_XPLOR = 2 }; /* PotentialPair::energyShiftMode */
+
+typedef struct b200_pair_args
+    {
+    float*        d_force;        /* Scalar4[N]: (fx, fy, fz, pe_i = sum_j V_ij/2) */
+    float*        d_virial;       /* [6*virial_pitch]: xx,xy,xz,yy,yz,zz at [k*pitch + i]; may be NULL if !compute_virial */
+    unsigned int  virial_pitch;
+    unsigned int  N;
+    const float*  d_pos;          /* Scalar4[N + n_ghost] */
+    b200_box      box;
+    const unsigned int* d_n_neigh;
+    const unsigned int* d_nlist;
+    const unsigned int* d_head_list;
+    const float*  d_rcutsq;       /* [ntypes*ntypes] */
+    const float*  d_ronsq;        /* [ntypes*ntypes] (xplor only) */
+    unsigned int  ntypes;
+    unsigned int  shift_mode;
+    unsigned int  compute_virial;
+    unsigned int  threads_per_particle; /* 0 = pick (1,2,4,8,16,32 accepted; the reference autotunes this) */
+    unsigned int  block_size;           /* 0 = pick */
+    } b200_pair_args;
+
+/* d_params: Scalar2[ntypes*ntypes] = (lj1, lj2) = (4 eps sigma^12, 4 alpha eps sigma^6) (hoomd/md/pair.py:602-609) */
+B200_API int b200_compute_lj_forces(const b200_pair_args* args, const float* d_params, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Integrator  -- replaces gpu_integrator_sum_net_force (hoomd/Integrator.cu:115-153), gpu_nve_step_one/two
+ * (hoomd/md/TwoStepNVEGPU.cu:120-150,392-430), gpu_langevin_step_two (hoomd/md/TwoStepLangevinGPU.cu:444-500).
+ * Arithmetic follows the CPU oracle (hoomd/md/TwoStepNVE.cc:77-122,255-300, hoomd/md/TwoStepLangevin.cc:86-125,
+ * 240-330) operation by operation with FMA contraction disabled, so one half step is bit-identical to the reference.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct b200_force_list /* gpu_force_list, hoomd/Integrator.cuh:22-58 (torques: out of scope, point particles) */
+    {
+    const float* f[6];            /* Scalar4 force arrays, NULL = unused */
+    const float* v[6];            /* virial arrays */
+    unsigned int vpitch[6];
+    } b200_force_list;
+
+B200_API int b200_integrator_sum_net_force(float* d_net_force, float* d_net_virial, unsigned int net_virial_pitch,
+                                           const b200_force_list* force_list, unsigned int nparticles, int clear,
+                                           int compute_virial, b200_stream_t stream);
+
+B200_API int b200_nve_step_one(float* d_pos, float* d_vel, const float* d_accel, int* d_image,
+                               const unsigned int* d_group_members, unsigned int group_size, const b200_box* box,
+                               float deltaT, int limit, float limit_val, int zero_force, b200_stream_t stream);
+
+B200_API int b200_nve_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members,
+                               unsigned int group_size, const float* d_net_force, float deltaT, int limit,
+                               float limit_val, int zero_force, b200_stream_t stream);
+
+typedef struct b200_langevin_args /* langevin_step_two_args, hoomd/md/TwoStepLangevinGPU.cuh:18-34 */
+    {
+    const float*  d_gamma;        /* [n_types] */
+    unsigned int  n_types;
+    int           use_lambda;
+    float         lambda;
+    float         T;              /* kT at this timestep */
+    unsigned int  timestep;
+    unsigned int  seed;           /* ALREADY hashed as in TwoStepLangevinBase ctor (TwoStepLangevinBase.cc:54) */
+    float*        d_sum_bdenergy; /* [1] or NULL; reservoir energy transfer of this step when tally */
+    int           noiseless_t;
+    int           tally;
+    } b200_langevin_args;
+
+/* The user-seed hash of the TwoStepLangevinBase constructor (hoomd/md/TwoStepLangevinBase.cc:54) */
+B200_API unsigned int b200_langevin_hash_seed(unsigned int user_seed);
+
+B200_API int b200_langevin_step_two(const float* d_pos, float* d_vel, float* d_accel, const float* d_diameter,
+                                    const unsigned int* d_tag, const unsigned int* d_group_members,
+                                    unsigned int group_size, const float* d_net_force,
+                                    const b200_langevin_args* args, float deltaT, unsigned int D,
+                                    b200_stream_t stream);
+
+/* n draws of Saru(seed1,seed2,seed3).u32() and .s<float>(-1,1) per triple, evaluated on the device
+ * (hoomd/Saru.h:324-340,417-441,603-640) -- used by the RNG parity tests. */
+B200_API int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3,
+                            unsigned int ntriples, unsigned int ndraws, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * SFCPackUpdater -- replaces gpu_generate_sorted_order / gpu_apply_sorted_order (hoomd/SFCPackUpdaterGPU.cuh).
+ * Order = 3D Hilbert curve over a grid^3 binning of the fractional coordinates (hoomd/SFCPackUpdater.cc:112-250,
+ * 490-583), ties broken by particle index (stable).
+ * ------------------------------------------------------------------------------------------------------------- */
+B200_API int b200_sfc_generate_sorted_order(unsigned int* d_sort_order, unsigned int* d_keys_scratch,
+                                            unsigned int* d_scratch2x, void* d_temp, uint64_t temp_bytes,
+                                            uint64_t* temp_bytes_needed, const float* d_pos, unsigned int N,
+                                            const b200_box* box, unsigned int grid, b200_stream_t stream);
+
+typedef struct b200_pdata_arrays /* the per-particle arrays of hoomd/ParticleData.h:1118-1165 that the path carries */
+    {
+    float* pos; float* vel; float* accel; int* image; unsigned int* tag; float* net_force; float* charge;
+    float* diameter; unsigned int* body;     /* any pointer may be NULL = not carried */
+    } b200_pdata_arrays;
+
+/* out[i] = in[order[i]] for every carried array, rtag[tag[i]] = i  (hoomd/SFCPackUpdater.cc:111-243) */
+B200_API int b200_sfc_apply_sorted_order(const b200_pdata_arrays* out, const b200_pdata_arrays* in,
+                                         unsigned int* d_rtag, const unsigned int* d_sort_order, unsigned int N,
+                                         b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * ComputeThermo -- replaces gpu_compute_thermo (hoomd/ComputeThermoGPU.cu:45-560): double-precision sums of
+ * KE = sum m v^2/2, PE = sum net_force.w, W = sum (vxx+vyy+vzz) of the net virial.  d_out: double[3+6]
+ * (ke, pe, virial trace, then the 6 pressure-tensor virial sums).  Two-pass, fixed order => deterministic.
+ * ------------------------------------------------------------------------------------------------------------- */
+B200_API int b200_compute_thermo(double* d_out, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                                 const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                                 const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * ENGINE: device-resident system with the reference's object graph and step semantics
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct b200_system b200_system;
+
+/* hoomd.context.initialize + SystemDefinition(N, box, ntypes): one system per process / GPU (device = cuda ordinal) */
+B200_API b200_system* b200_sys_create(unsigned int N, const b200_box* box, unsigned int ntypes, int device);
+B200_API void b200_sys_destroy(b200_system* s);
+B200_API const char* b200_sys_last_error(b200_system* s);
+
+/* Particle state in index order (tag == index at creation), HOST pointers; NULL = leave unchanged.
+ * pos4 = (x,y,z,type bits), vel4 = (vx,vy,vz,mass), image3 int.  Forces a neighbor list rebuild. */
+B200_API int b200_sys_set_particles(b200_system* s, const float* pos4, const float* vel4, const int* image3);
+B200_API int b200_sys_set_accel(b200_system* s, const float* accel3);  /* + notifyAccelSet() */
+/* Current state in INDEX order (use tag/rtag to key comparisons); any pointer may be NULL */
+B200_API int b200_sys_get_particles(b200_system* s, float* pos4, float* vel4, float* accel3, int* image3,
+                                    unsigned int* tag, unsigned int* rtag);
+
+/* md.nlist.cell(r_buff, check_period) + md.pair.lj(r_cut, nlist) + pair_coeff + set_params(mode).
+ * rcut/lj1/lj2/ron: ntypes x ntypes row-major (ron may be NULL). */
+B200_API int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut,
+                               const float* lj1, const float* lj2, const float* ron, int shift_mode);
+/* pdata flags pressure_tensor | isotropic_virial (hoomd/md/PotentialPair.h:342-343) */
+B200_API int b200_sys_set_virial(b200_system* s, int on);
+/* md.integrate.mode_standard(dt) */
+B200_API int b200_sys_setup_integrator(b200_system* s, float dt);
+/* md.integrate.nve(group=all, limit, zero_force) */
+B200_API int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force);
+/* md.integrate.langevin(group=all, kT, seed) + set_gamma per type (gamma NULL = 1.0) */
+B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
+/* hoomd.update.sort period (0 = disabled) */
+B200_API int b200_sys_set_sorter(b200_system* s, unsigned int period);
+B200_API int b200_sys_sort_now(b200_system* s);
+B200_API void b200_sys_set_timestep(b200_system* s, unsigned int ts);
+B200_API unsigned int b200_sys_get_timestep(b200_system* s);
+/* Launch tuning: threads per particle of the pair kernel (0 = auto), fused device-driven stepping on/off */
+B200_API int b200_sys_set_tuning(b200_system* s, unsigned int pair_tpp, int use_graph);
+
+/* NeighborList::compute(ts) / ForceCompute::compute(ts) in isolation (kernel-level parity) */
+B200_API int b200_sys_compute_nlist(b200_system* s, unsigned int ts);
+B200_API int b200_sys_compute_forces(b200_system* s, unsigned int ts);
+/* System::run(nsteps): prepRun, then per step updaters (sorter) + IntegratorTwoStep::update.  Blocks until done.
+ * *elapsed_s = wall seconds of the step loop (excluding prepRun), like System.cc:622-637; *gpu_ms = CUDA-event time. */
+B200_API int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double* gpu_ms);
+/* Isolated half steps on the current state (host net_force4 may be NULL = use the device net force) */
+B200_API int b200_sys_step_one(b200_system* s, unsigned int ts);
+B200_API int b200_sys_step_two(b200_system* s, unsigned int ts, const float* net_force4);
+
+B200_API int b200_sys_get_forces(b200_system* s, float* force4, float* virial6 /* [6*N], pitch N */);
+B200_API unsigned int b200_sys_get_nlist_size(b200_system* s);
+B200_API int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist,
+                                unsigned int nlist_len);
+/* out: {num updates (distance-check triggered), forced updates, nlist overflows, kernels launched in the last run,
+ *       dim.x, dim.y, dim.z, Nmax[0]} */
+B200_API int b200_sys_get_stats(b200_system* s, unsigned long long* out8);
+/* ComputeThermo at the current step: out = {KE, PE, temperature, pressure, ndof} */
+B200_API int b200_sys_get_thermo(b200_system* s, double* out5);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HOOMD_B200_H_ */
