@@ -12,8 +12,10 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
                                                   unsigned int* __restrict__ particle_slot,
                                                   unsigned int* __restrict__ conditions,
                                                   const float4* __restrict__ pos, unsigned int N, unsigned int n_ghost,
-                                                  Box box, uint3 dim, float3 ghost_width)
+                                                  Box box, uint3 dim, float3 ghost_width,
+                                                  const unsigned int* __restrict__ enable)
     {
+    if (enable && !*enable) return; // device-driven stepping: the rebuild was not requested this step
     unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N + n_ghost) return;
     float4 p = pos[n];
@@ -38,9 +40,11 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
 // ---- K2: exclusive scan of the occupancies (single CTA, 1024 threads, warp-shuffle scan, sequential tiles) --------
 // ncells is 8e3 (64k particles) .. 1e6 (8M particles); the scan reads 4 B/cell once and is far off the critical path.
 __global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ cell_start,
-                                                    const unsigned int* __restrict__ cell_count, unsigned int ncells,
-                                                    unsigned int* __restrict__ conditions)
+                                                    unsigned int* __restrict__ cell_count, unsigned int ncells,
+                                                    unsigned int* __restrict__ conditions,
+                                                    const unsigned int* __restrict__ enable)
     {
+    if (enable && !*enable) return;
     __shared__ unsigned int warp_sums[32];
     __shared__ unsigned int carry_s;
     const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -54,7 +58,12 @@ __global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ c
         const unsigned int carry = carry_s; // read before the barrier below; warp 0 rewrites it after that barrier
         unsigned int c[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) c[k] = (i0 + k < ncells) ? cell_count[i0 + k] : 0u;
+        for (int k = 0; k < 4; k++)
+            {
+            c[k] = (i0 + k < ncells) ? cell_count[i0 + k] : 0u;
+            // self-cleaning: the counts are consumed here, leave zeros behind for the next build (no memset node needed)
+            if (i0 + k < ncells) cell_count[i0 + k] = 0u;
+            }
         max_occ = max(max(max_occ, max(c[0], c[1])), max(c[2], c[3]));
         unsigned int tsum = c[0] + c[1] + c[2] + c[3];
         unsigned int incl = tsum;
@@ -99,8 +108,10 @@ __global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ c
 __global__ void __launch_bounds__(256) k_cell_scatter(unsigned int* __restrict__ scratch_idx,
                                                       const unsigned int* __restrict__ cell_start,
                                                       const unsigned int* __restrict__ particle_cell,
-                                                      const unsigned int* __restrict__ particle_slot, unsigned int ntot)
+                                                      const unsigned int* __restrict__ particle_slot, unsigned int ntot,
+                                                      const unsigned int* __restrict__ enable)
     {
+    if (enable && !*enable) return;
     unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= ntot) return;
     unsigned int cell = particle_cell[n];
@@ -117,8 +128,10 @@ __global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyz
                                                    const unsigned int* __restrict__ cell_start,
                                                    const unsigned int* __restrict__ particle_cell,
                                                    const float4* __restrict__ pos, const float* __restrict__ charge,
-                                                   unsigned int ncells, int flag_charge, int flag_type)
+                                                   unsigned int ncells, int flag_charge, int flag_type,
+                                                   const unsigned int* __restrict__ enable)
     {
+    if (enable && !*enable) return;
     unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int nbinned = cell_start[ncells];
     if (e >= nbinned) return;
@@ -270,31 +283,44 @@ void b200_cell_list_dimensions(const b200_box* box, float nominal_width, unsigne
     dim->x = d[0]; dim->y = d[1]; dim->z = d[2];
     }
 
-int b200_compute_cell_list(const b200_cell_list_args* a, b200_stream_t stream_)
+} // extern "C" (reopened below)
+
+namespace b200
+{
+// enable == NULL: unconditional (driver entry point, zeroes cell_count itself).  enable != NULL: every kernel returns
+// at once unless *enable != 0, and cell_count must already be zero (k_cell_scan leaves it zeroed).
+cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream)
     {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    if (!box_is_orthorhombic(a->box)) return (int)cudaErrorNotSupported;
+    if (!box_is_orthorhombic(a->box)) return cudaErrorNotSupported;
     const unsigned int ntot = a->N + a->n_ghost;
     const unsigned int ncells = a->dim.x * a->dim.y * a->dim.z;
     Box box = make_box(a->box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
-    cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
+    if (!enable) cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
     if (ntot)
         k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
                                                             a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
-                                                            box, dim, gw);
-    k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions);
+                                                            box, dim, gw, enable);
+    k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions, enable);
     if (ntot)
         {
         k_cell_scatter<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
-                                                                a->d_particle_slot, ntot);
+                                                                a->d_particle_slot, ntot, enable);
         k_cell_rank<<<(ntot + 255) / 256, 256, 0, stream>>>((float4*)a->d_cell_xyzf, a->d_cell_type, a->d_cell_idx,
                                                              a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
                                                              (const float4*)a->d_pos, a->d_charge, ncells,
-                                                             a->flag_charge, a->flag_type);
+                                                             a->flag_charge, a->flag_type, enable);
         }
-    return (int)cudaGetLastError();
+    return cudaGetLastError();
+    }
+} // namespace b200
+
+extern "C" {
+
+int b200_compute_cell_list(const b200_cell_list_args* a, b200_stream_t stream)
+    {
+    return (int)b200::launch_cell_list(a, nullptr, (cudaStream_t)stream);
     }
 
 int b200_cell_list_export_padded(unsigned int* d_cell_size, float* d_xyzf, float* d_tdb, unsigned int* d_conditions,

@@ -163,14 +163,12 @@ struct Saru
         const unsigned int v = (x ^ (x >> 26)) + y;
         return (v ^ (v >> 20)) * 0x6957f5a7u;
         }
-#ifdef __CUDA_ARCH__
     __device__ inline float f()
         {
         // (int)u32 * 2^-32 is exact (power-of-two scale), so the single rounding is the + 0.5f: FMA-safe
         return __fadd_rn(__fmul_rn((float)(int)u32(), 2.32830643653869628906250e-10f), 0.5f);
         }
     __device__ inline float s(float a, float b) { return __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), f())); }
-#endif
     };
 
 #define B200_CHECK_LAUNCH() cudaGetLastError()

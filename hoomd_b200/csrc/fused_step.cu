@@ -1,0 +1,173 @@
+// Kernels of the device-driven step loop (engine only; group = all particles).
+//   k_fused_step_one : IntegrationMethodTwoStep::integrateStepOne + NeighborList::distanceCheck in one pass over the
+//                      particles (the check re-uses the freshly written position: +16 B/particle instead of a second
+//                      32 B/particle kernel, hoomd/md/NeighborListGPU.cu:32-82)
+//   k_decide         : NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163) on the device, 1 thread
+//   k_post_rebuild   : overflow detection after a rebuild (hoomd/md/NeighborList.cc:1389-1405 needs the host: sticky flag)
+//   k_fused_step_two : integrateStepTwo with the timestep read from the control block
+// Per-particle arithmetic is the shared body of integrate_body.cuh => bit-identical to the driver kernels.
+#include "common.cuh"
+#include "integrate_body.cuh"
+#include "kernels.h"
+
+namespace b200
+{
+__global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos, float4* __restrict__ vel,
+                                                        const float3s* __restrict__ accel, int3* __restrict__ image,
+                                                        const float4* __restrict__ last_pos,
+                                                        const float* __restrict__ rcut_max, unsigned int N, Box box,
+                                                        float dt, float r_buff, bool limit, float limit_val,
+                                                        bool zero_force, StepState* __restrict__ st)
+    {
+    unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
+    bool moved = false;
+    if (j < N)
+        {
+        float4 p = pos[j];
+        float4 v = vel[j];
+        float3s a = accel[j];
+        if (zero_force) a.x = a.y = a.z = 0.0f;
+        int3 img = image[j];
+        nve_step_one_body(p, v, a, img, box, dt, limit, limit_val);
+        pos[j] = p;
+        vel[j] = v;
+        image[j] = img;
+        // NeighborList::distanceCheck with a fixed box (lambda = 1): hoomd/md/NeighborList.cc:992-1016
+        const float4 lp = last_pos[j];
+        const float old_rmin = rcut_max[(unsigned int)__float_as_int(p.w)];
+        const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(old_rmin, r_buff), 1.0f), old_rmin), 2.0f);
+        const float maxsq = (delta_max > 0.0f) ? __fmul_rn(delta_max, delta_max) : 0.0f;
+        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
+                                __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
+        dx = min_image_exact(dx, box);
+        moved = dot_exact(dx) >= maxsq;
+        }
+    if (__any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) st->moved = 1u; // benign same-value race
+    }
+
+__global__ void k_decide(StepState* st, cudaGraphConditionalHandle handle, int use_cond)
+    {
+    // update(ts): forces are computed at ts+1 => needsUpdating(ts+1)
+    const unsigned int ts1 = st->timestep + 1u;
+    bool result;
+    if (st->force_update)
+        {
+        result = true;
+        st->force_update = 0u;
+        st->num_forced += 1u;
+        st->last_updated = ts1;
+        }
+    else if (ts1 < st->last_updated + st->every) // !shouldCheckDistance
+        result = false;
+    else
+        {
+        result = st->r_buff_tiny || st->moved;
+        if (result)
+            {
+            st->last_updated = ts1;
+            st->num_updates += 1u;
+            }
+        }
+    st->moved = 0u;
+    st->need_rebuild = result ? 1u : 0u;
+    st->ts_step_two = st->timestep;
+    st->timestep = ts1;
+#if (CUDART_VERSION >= 12040)
+    if (use_cond) cudaGraphSetConditional(handle, result ? 1u : 0u);
+#endif
+    }
+
+__global__ void k_post_rebuild(StepState* st, unsigned int* __restrict__ conditions,
+                               const unsigned int* __restrict__ Nmax)
+    {
+    if (!st->need_rebuild) return;
+    for (unsigned int t = 0; t < st->ntypes; t++)
+        {
+        if (conditions[t] > Nmax[t]) st->overflow = 1u;
+        }
+    }
+
+__global__ void __launch_bounds__(256) k_fused_step_two(float4* __restrict__ vel, float3s* __restrict__ accel,
+                                                        const float4* __restrict__ pos,
+                                                        const float4* __restrict__ net_force,
+                                                        const unsigned int* __restrict__ tag,
+                                                        const float* __restrict__ gamma_tab, unsigned int N, float dt,
+                                                        int method, bool limit, float limit_val, bool zero_force,
+                                                        float kT, unsigned int seed, bool noiseless_t,
+                                                        const StepState* __restrict__ st)
+    {
+    unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    float4 v = vel[j];
+    float3s a;
+    if (method == 2)
+        {
+        const float gamma = gamma_tab[(unsigned int)__float_as_int(pos[j].w)];
+        langevin_step_two_body(v, a, net_force[j], tag[j], st->ts_step_two, seed, gamma, kT, dt, noiseless_t, 3u);
+        }
+    else
+        {
+        a = accel[j];
+        nve_step_two_body(v, a, net_force[j], dt, limit, limit_val, zero_force);
+        }
+    vel[j] = v;
+    accel[j] = a;
+    }
+
+__global__ void __launch_bounds__(256) k_compute_accel(float3s* __restrict__ accel,
+                                                       const float4* __restrict__ net_force,
+                                                       const float4* __restrict__ vel, unsigned int N)
+    {
+    unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    const float minv = __fdiv_rn(1.0f, vel[j].w);
+    const float4 f = net_force[j];
+    float3s a;
+    a.x = __fmul_rn(f.x, minv);
+    a.y = __fmul_rn(f.y, minv);
+    a.z = __fmul_rn(f.z, minv);
+    accel[j] = a;
+    }
+
+cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream)
+    {
+    if (a.N == 0) return cudaSuccess;
+    // Langevin step one == NVE step one without limit / zero_force (hoomd/md/TwoStepLangevin.cc:86-125)
+    const bool nve = a.method == 1;
+    k_fused_step_one<<<(a.N + 255) / 256, 256, 0, stream>>>(a.pos, a.vel, (const float3s*)a.accel, (int3*)a.image,
+                                                            a.last_pos, a.rcut_max, a.N, make_box(a.box), a.dt,
+                                                            a.r_buff, nve && a.limit, a.limit_val, nve && a.zero_force,
+                                                            st);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_decide(StepState* st, unsigned long long cond_handle, int use_cond, cudaStream_t stream)
+    {
+    k_decide<<<1, 1, 0, stream>>>(st, (cudaGraphConditionalHandle)cond_handle, use_cond);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
+                                cudaStream_t stream)
+    {
+    k_post_rebuild<<<1, 1, 0, stream>>>(st, nlist_conditions, Nmax);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_fused_step_two(const FusedStepArgs& a, const StepState* st, cudaStream_t stream)
+    {
+    if (a.N == 0) return cudaSuccess;
+    k_fused_step_two<<<(a.N + 255) / 256, 256, 0, stream>>>(a.vel, (float3s*)a.accel, a.pos, a.net_force, a.tag, a.gamma,
+                                                            a.N, a.dt, a.method, a.limit != 0, a.limit_val,
+                                                            a.zero_force != 0, a.kT, a.seed, a.noiseless_t != 0, st);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,
+                                 cudaStream_t stream)
+    {
+    if (N == 0) return cudaSuccess;
+    k_compute_accel<<<(N + 255) / 256, 256, 0, stream>>>((float3s*)accel, net_force, vel, N);
+    return cudaGetLastError();
+    }
+} // namespace b200

@@ -1,0 +1,288 @@
+// Integrator kernels for sm_100a: net-force sum, TwoStepNVE step one/two, TwoStepLangevin step two, Saru probe.
+// These are pure streaming kernels (HBM-bound, ~60-100 B per particle); one thread per group member,
+// 16 B vector loads/stores for pos/vel/net_force.  Arithmetic follows the CPU oracle operation by operation
+// (hoomd/md/TwoStepNVE.cc:77-122,255-300, hoomd/md/TwoStepLangevin.cc:86-125,240-330) with explicit *_rn intrinsics so
+// nothing is contracted into FMAs: one half step is bit-identical to the reference.
+#include "common.cuh"
+#include "integrate_body.cuh"
+
+namespace b200
+{
+
+// ---- Integrator::computeNetForceGPU (hoomd/Integrator.cu:57-113) --------------------------------------------------
+template<bool VIRIAL>
+__global__ void __launch_bounds__(256) k_sum_net_force(float4* __restrict__ net_force, float* __restrict__ net_virial,
+                                                       unsigned int net_virial_pitch, b200_force_list fl,
+                                                       unsigned int n, int clear)
+    {
+    unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 f = clear ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : net_force[i];
+    float v[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (VIRIAL && !clear)
+        {
+#pragma unroll
+        for (int k = 0; k < 6; k++) v[k] = net_virial[k * net_virial_pitch + i];
+        }
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+        {
+        if (fl.f[a])
+            {
+            const float4 g = reinterpret_cast<const float4*>(fl.f[a])[i];
+            f.x = __fadd_rn(f.x, g.x);
+            f.y = __fadd_rn(f.y, g.y);
+            f.z = __fadd_rn(f.z, g.z);
+            f.w = __fadd_rn(f.w, g.w);
+            if (VIRIAL && fl.v[a])
+                {
+#pragma unroll
+                for (int k = 0; k < 6; k++) v[k] = __fadd_rn(v[k], fl.v[a][k * fl.vpitch[a] + i]);
+                }
+            }
+        }
+    net_force[i] = f;
+    if (VIRIAL)
+        {
+#pragma unroll
+        for (int k = 0; k < 6; k++) net_virial[k * net_virial_pitch + i] = v[k];
+        }
+    }
+
+__global__ void __launch_bounds__(256) k_nve_step_one(float4* __restrict__ pos, float4* __restrict__ vel,
+                                                      const float3s* __restrict__ accel, int3* __restrict__ image,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      Box box, float dt, bool limit, float limit_val, bool zero_force)
+    {
+    unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 p = pos[j];
+    float4 v = vel[j];
+    float3s a = accel[j];
+    if (zero_force) a.x = a.y = a.z = 0.0f;
+    int3 img = image[j];
+    nve_step_one_body(p, v, a, img, box, dt, limit, limit_val);
+    pos[j] = p;
+    vel[j] = v;
+    image[j] = img;
+    }
+
+__global__ void __launch_bounds__(256) k_nve_step_two(float4* __restrict__ vel, float3s* __restrict__ accel,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      const float4* __restrict__ net_force, float dt, bool limit,
+                                                      float limit_val, bool zero_force)
+    {
+    unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 v = vel[j];
+    float3s a = accel[j];
+    nve_step_two_body(v, a, net_force[j], dt, limit, limit_val, zero_force);
+    vel[j] = v;
+    accel[j] = a;
+    }
+
+__global__ void __launch_bounds__(256) k_langevin_step_two(const float4* __restrict__ pos, float4* __restrict__ vel,
+                                                           float3s* __restrict__ accel,
+                                                           const float* __restrict__ diameter,
+                                                           const unsigned int* __restrict__ tag,
+                                                           const unsigned int* __restrict__ group,
+                                                           unsigned int group_size,
+                                                           const float4* __restrict__ net_force,
+                                                           const float* __restrict__ gamma_tab, bool use_lambda,
+                                                           float lambda, float T, unsigned int timestep,
+                                                           unsigned int seed, float* __restrict__ sum_bdenergy,
+                                                           bool noiseless_t, bool tally, float dt, unsigned int D)
+    {
+    unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    float e = 0.0f;
+    if (g < group_size)
+        {
+        const unsigned int j = group ? group[g] : g;
+        float4 v = vel[j];
+        float3s a;
+        float gamma;
+        if (use_lambda) gamma = __fmul_rn(lambda, diameter[j]);
+        else gamma = gamma_tab[(unsigned int)__float_as_int(pos[j].w)];
+        e = langevin_step_two_body(v, a, net_force[j], tag[j], timestep, seed, gamma, T, dt, noiseless_t, D);
+        vel[j] = v;
+        accel[j] = a;
+        }
+    if (tally)
+        {
+        // warp shuffle reduce, one atomic per warp (the reference block-reduces then sums partials,
+        // hoomd/md/TwoStepLangevinGPU.cu:150-240; the tally is a diagnostic, not part of the trajectory)
+        for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(sum_bdenergy, e);
+        }
+    }
+
+__global__ void k_saru_draw(unsigned int* __restrict__ u32_out, float* __restrict__ f_out,
+                            const unsigned int* __restrict__ seeds3, unsigned int ntriples, unsigned int ndraws)
+    {
+    unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntriples) return;
+    if (u32_out)
+        {
+        Saru s(seeds3[3 * t], seeds3[3 * t + 1], seeds3[3 * t + 2]);
+        for (unsigned int d = 0; d < ndraws; d++) u32_out[(size_t)t * ndraws + d] = s.u32();
+        }
+    if (f_out)
+        {
+        Saru s(seeds3[3 * t], seeds3[3 * t + 1], seeds3[3 * t + 2]);
+        for (unsigned int d = 0; d < ndraws; d++) f_out[(size_t)t * ndraws + d] = s.s(-1.0f, 1.0f);
+        }
+    }
+} // namespace b200
+
+// ---- ComputeThermo (hoomd/ComputeThermo.cc:195-380): double-precision sums, fixed two-pass order ------------------------
+namespace b200
+{
+constexpr int TH_NQ = 9; // ke2 (= sum m v^2), pe, virial trace, then the 6 virial components
+
+__global__ void __launch_bounds__(256) k_thermo_partial(double* __restrict__ partial, const float4* __restrict__ vel,
+                                                        const float4* __restrict__ net_force,
+                                                        const float* __restrict__ net_virial,
+                                                        unsigned int virial_pitch,
+                                                        const unsigned int* __restrict__ group,
+                                                        unsigned int group_size)
+    {
+    double acc[TH_NQ];
+#pragma unroll
+    for (int q = 0; q < TH_NQ; q++) acc[q] = 0.0;
+    // contiguous chunk per block, fixed stride per thread: the summation order depends only on (grid, block)
+    for (unsigned int g = blockIdx.x * blockDim.x + threadIdx.x; g < group_size; g += gridDim.x * blockDim.x)
+        {
+        const unsigned int j = group ? group[g] : g;
+        const float4 v = vel[j];
+        acc[0] += (double)v.w * ((double)v.x * (double)v.x + (double)v.y * (double)v.y + (double)v.z * (double)v.z);
+        acc[1] += (double)net_force[j].w;
+        if (net_virial)
+            {
+#pragma unroll
+            for (int k = 0; k < 6; k++) acc[3 + k] += (double)net_virial[k * virial_pitch + j];
+            }
+        }
+    acc[2] = acc[3] + acc[6] + acc[8];
+    __shared__ double s[8][TH_NQ];
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int q = 0; q < TH_NQ; q++)
+        {
+        double x = acc[q];
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) s[warp][q] = x;
+        }
+    __syncthreads();
+    if (threadIdx.x < TH_NQ)
+        {
+        double x = 0.0;
+        for (int w = 0; w < 8; w++) x += s[w][threadIdx.x];
+        partial[(size_t)blockIdx.x * TH_NQ + threadIdx.x] = x;
+        }
+    }
+
+__global__ void k_thermo_final(double* __restrict__ out, const double* __restrict__ partial, unsigned int nblocks)
+    {
+    if (threadIdx.x < TH_NQ)
+        {
+        double x = 0.0;
+        for (unsigned int b = 0; b < nblocks; b++) x += partial[(size_t)b * TH_NQ + threadIdx.x];
+        if (threadIdx.x == 0) x *= 0.5; // KE = 1/2 sum m v^2
+        out[threadIdx.x] = x;
+        }
+    }
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_integrator_sum_net_force(float* d_net_force, float* d_net_virial, unsigned int net_virial_pitch,
+                                  const b200_force_list* fl, unsigned int n, int clear, int compute_virial,
+                                  b200_stream_t stream)
+    {
+    if (n == 0) return 0;
+    if (compute_virial)
+        k_sum_net_force<true><<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)d_net_force, d_net_virial,
+                                                                                 net_virial_pitch, *fl, n, clear);
+    else
+        k_sum_net_force<false><<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)d_net_force, d_net_virial,
+                                                                                  net_virial_pitch, *fl, n, clear);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nve_step_one(float* d_pos, float* d_vel, const float* d_accel, int* d_image,
+                      const unsigned int* d_group_members, unsigned int group_size, const b200_box* box, float deltaT,
+                      int limit, float limit_val, int zero_force, b200_stream_t stream)
+    {
+    if (!box_is_orthorhombic(*box)) return (int)cudaErrorNotSupported;
+    if (group_size == 0) return 0;
+    k_nve_step_one<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_pos, (float4*)d_vel, (const float3s*)d_accel, (int3*)d_image, d_group_members, group_size,
+        make_box(*box), deltaT, limit != 0, limit_val, zero_force != 0);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nve_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members, unsigned int group_size,
+                      const float* d_net_force, float deltaT, int limit, float limit_val, int zero_force,
+                      b200_stream_t stream)
+    {
+    if (group_size == 0) return 0;
+    k_nve_step_two<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_vel, (float3s*)d_accel, d_group_members, group_size, (const float4*)d_net_force, deltaT, limit != 0,
+        limit_val, zero_force != 0);
+    return (int)cudaGetLastError();
+    }
+
+unsigned int b200_langevin_hash_seed(unsigned int s)
+    {
+    s = s * 0x12345677u + 0x12345u;
+    s ^= (s >> 16);
+    s *= 0x45679u;
+    return s;
+    }
+
+int b200_langevin_step_two(const float* d_pos, float* d_vel, float* d_accel, const float* d_diameter,
+                           const unsigned int* d_tag, const unsigned int* d_group_members, unsigned int group_size,
+                           const float* d_net_force, const b200_langevin_args* a, float deltaT, unsigned int D,
+                           b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (group_size == 0) return 0;
+    if (a->use_lambda && !d_diameter) return (int)cudaErrorInvalidValue;
+    if (a->tally)
+        {
+        if (!a->d_sum_bdenergy) return (int)cudaErrorInvalidValue;
+        cudaMemsetAsync(a->d_sum_bdenergy, 0, sizeof(float), stream);
+        }
+    k_langevin_step_two<<<(group_size + 255) / 256, 256, 0, stream>>>(
+        (const float4*)d_pos, (float4*)d_vel, (float3s*)d_accel, d_diameter, d_tag, d_group_members, group_size,
+        (const float4*)d_net_force, a->d_gamma, a->use_lambda != 0, a->lambda, a->T, a->timestep, a->seed,
+        a->d_sum_bdenergy, a->noiseless_t != 0, a->tally != 0, deltaT, D);
+    return (int)cudaGetLastError();
+    }
+
+int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3, unsigned int ntriples,
+                   unsigned int ndraws, b200_stream_t stream)
+    {
+    if (ntriples == 0) return 0;
+    k_saru_draw<<<(ntriples + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_u32_out, d_f_out, d_seeds3, ntriples,
+                                                                         ndraws);
+    return (int)cudaGetLastError();
+    }
+
+int b200_compute_thermo(double* d_out, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                        const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                        const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n_partial_blocks == 0) return (int)cudaErrorInvalidValue;
+    k_thermo_partial<<<n_partial_blocks, 256, 0, stream>>>(d_partial, (const float4*)d_vel, (const float4*)d_net_force,
+                                                          d_net_virial, virial_pitch, d_group_members, group_size);
+    k_thermo_final<<<1, 32, 0, stream>>>(d_out, d_partial, n_partial_blocks);
+    return (int)cudaGetLastError();
+    }
+
+} // extern "C"

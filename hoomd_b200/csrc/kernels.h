@@ -1,0 +1,53 @@
+// Internal (C++) declarations shared between the kernel translation units and the engine.  Not part of the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/hoomd_b200.h"
+
+namespace b200
+{
+// Device-resident control block of the device-driven step loop (one per system).  Everything the reference keeps in
+// host members of NeighborList (m_last_updated_tstep, m_force_update, m_updates, ...; hoomd/md/NeighborList.cc:1080-1163)
+// lives here so that no step needs a host round trip.
+struct StepState
+    {
+    unsigned int timestep;        // System::m_cur_tstep
+    unsigned int ts_step_two;     // the `timestep` argument of integrateStepTwo of the step in flight
+    unsigned int moved;           // distance-check result of the step in flight (set by the step-one kernel)
+    unsigned int need_rebuild;    // consumed by the rebuild kernels (`enable` pointer) / the conditional graph node
+    unsigned int force_update;    // NeighborList::m_force_update
+    unsigned int last_updated;    // NeighborList::m_last_updated_tstep
+    unsigned int every;           // NeighborList::m_every (check_period)
+    unsigned int r_buff_tiny;     // r_buff < 1e-6: rebuild whenever allowed
+    unsigned int num_updates;     // NeighborList::m_updates
+    unsigned int num_forced;      // NeighborList::m_forced_updates
+    unsigned int overflow;        // sticky: some n_neigh exceeded Nmax during a device-driven rebuild
+    unsigned int ntypes;
+    };
+
+cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream);
+cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream);
+unsigned int pick_pair_tpp(unsigned int N);
+
+// fused_step.cu -- kernels of the device-driven step loop (group = all particles)
+struct FusedStepArgs
+    {
+    float4* pos; float4* vel; float* accel; int* image; const float4* net_force; const float4* last_pos;
+    const unsigned int* tag; const float* rcut_max; const float* gamma;
+    unsigned int N; b200_box box; float dt; float r_buff;
+    int method;                   // 1 = NVE, 2 = Langevin
+    int limit; float limit_val; int zero_force;
+    float kT; unsigned int seed; int noiseless_t;
+    };
+// step one (+ distance check into st->moved)
+cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);
+// rebuild decision for timestep+1 (NeighborList::needsUpdating); optionally sets a conditional graph node handle
+cudaError_t launch_decide(StepState* st, unsigned long long cond_handle, int use_cond, cudaStream_t stream);
+// after a device-driven rebuild: overflow detection, condition reset
+cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
+                                cudaStream_t stream);
+// step two (timestep taken from st->ts_step_two)
+cudaError_t launch_fused_step_two(const FusedStepArgs& a, const StepState* st, cudaStream_t stream);
+// a = F/m (Integrator::computeAccelerations, hoomd/Integrator.cc:222-256)
+cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,
+                                 cudaStream_t stream);
+} // namespace b200

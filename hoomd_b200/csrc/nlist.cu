@@ -43,8 +43,9 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
                                                       const unsigned int* __restrict__ cell_type, uint3 dim, Box box,
                                                       float3 ghost_width, const float* __restrict__ r_cut,
                                                       const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                      int half_storage)
+                                                      int half_storage, const unsigned int* __restrict__ enable)
     {
+    if (enable && !*enable) return;
     const unsigned int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned int lane = threadIdx.x & 31;
     if (i >= N) return;
@@ -277,12 +278,15 @@ int b200_nlist_build_head_list(unsigned int* d_head_list, unsigned int* d_req_si
     return (int)cudaGetLastError();
     }
 
-int b200_compute_nlist_binned(const b200_nlist_args* a, b200_stream_t stream_)
+} // extern "C" (reopened below)
+
+namespace b200
+{
+cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream)
     {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    if (!box_is_orthorhombic(a->box)) return (int)cudaErrorNotSupported;
-    if (a->N == 0) return 0;
-    if (a->ntypes > 1 && !a->d_cell_type) return (int)cudaErrorInvalidValue;
+    if (!box_is_orthorhombic(a->box)) return cudaErrorNotSupported;
+    if (a->N == 0) return cudaSuccess;
+    if (a->ntypes > 1 && !a->d_cell_type) return cudaErrorInvalidValue;
     Box box = make_box(a->box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
@@ -293,14 +297,23 @@ int b200_compute_nlist_binned(const b200_nlist_args* a, b200_stream_t stream_)
                                                        a->d_Nmax, a->d_head_list, (const float4*)a->d_pos, a->N,
                                                        a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type,
                                                        dim, box, gw, a->d_r_cut, a->d_r_listsq, a->ntypes,
-                                                       a->half_storage);
+                                                       a->half_storage, enable);
     else
         k_nlist_binned<false><<<grid, 128, 0, stream>>>(a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos,
                                                         a->d_conditions, a->d_Nmax, a->d_head_list,
                                                         (const float4*)a->d_pos, a->N, a->d_cell_start,
                                                         (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, gw,
-                                                        a->d_r_cut, a->d_r_listsq, a->ntypes, a->half_storage);
-    return (int)cudaGetLastError();
+                                                        a->d_r_cut, a->d_r_listsq, a->ntypes, a->half_storage,
+                                                        enable);
+    return cudaGetLastError();
+    }
+} // namespace b200
+
+extern "C" {
+
+int b200_compute_nlist_binned(const b200_nlist_args* a, b200_stream_t stream)
+    {
+    return (int)b200::launch_nlist_binned(a, nullptr, (cudaStream_t)stream);
     }
 
 int b200_nlist_needs_update_check(unsigned int* d_result, const float* d_last_pos, const float* d_pos, unsigned int N,
