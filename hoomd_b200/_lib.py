@@ -1,0 +1,170 @@
+"""ctypes binding of hoomd_b200/libhoomd_b200.so (the C ABI declared in include/hoomd_b200.h).
+
+There is no fallback: if the library is missing, importing any compute entry point raises.  Build it with
+``python -c "import __graft_entry__ as g; g.build()"`` or ``make -C hoomd_b200/csrc``.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhoomd_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "hoomd_b200.h")
+
+c_float_p = C.POINTER(C.c_float)
+c_uint_p = C.POINTER(C.c_uint)
+c_int_p = C.POINTER(C.c_int)
+c_double_p = C.POINTER(C.c_double)
+vp = C.c_void_p
+
+
+class Box(C.Structure):
+    """b200_box (BoxDim, hoomd/BoxDim.h:568-576)"""
+    _fields_ = [("lo", C.c_float * 3), ("hi", C.c_float * 3), ("L", C.c_float * 3), ("Linv", C.c_float * 3),
+                ("xy", C.c_float), ("xz", C.c_float), ("yz", C.c_float), ("periodic", C.c_ubyte * 3),
+                ("_pad", C.c_ubyte)]
+
+
+class Dim3(C.Structure):
+    _fields_ = [("x", C.c_uint), ("y", C.c_uint), ("z", C.c_uint)]
+
+
+class CellListArgs(C.Structure):
+    _fields_ = [("d_cell_start", vp), ("d_cell_xyzf", vp), ("d_cell_type", vp), ("d_cell_idx", vp),
+                ("d_conditions", vp), ("d_cell_count", vp), ("d_particle_cell", vp), ("d_particle_slot", vp),
+                ("d_scratch_idx", vp), ("d_pos", vp), ("d_charge", vp), ("N", C.c_uint), ("n_ghost", C.c_uint),
+                ("flag_charge", C.c_int), ("flag_type", C.c_int), ("box", Box), ("dim", Dim3),
+                ("ghost_width", C.c_float * 3)]
+
+
+class NlistArgs(C.Structure):
+    _fields_ = [("d_nlist", vp), ("d_n_neigh", vp), ("d_last_pos", vp), ("d_conditions", vp), ("d_Nmax", vp),
+                ("d_head_list", vp), ("d_pos", vp), ("N", C.c_uint), ("d_cell_start", vp), ("d_cell_xyzf", vp),
+                ("d_cell_type", vp), ("dim", Dim3), ("box", Box), ("ghost_width", C.c_float * 3), ("d_r_cut", vp),
+                ("d_r_listsq", vp), ("ntypes", C.c_uint), ("half_storage", C.c_int)]
+
+
+class PairArgs(C.Structure):
+    _fields_ = [("d_force", vp), ("d_virial", vp), ("virial_pitch", C.c_uint), ("N", C.c_uint), ("d_pos", vp),
+                ("box", Box), ("d_n_neigh", vp), ("d_nlist", vp), ("d_head_list", vp), ("d_rcutsq", vp),
+                ("d_ronsq", vp), ("ntypes", C.c_uint), ("shift_mode", C.c_uint), ("compute_virial", C.c_uint),
+                ("threads_per_particle", C.c_uint), ("block_size", C.c_uint)]
+
+
+class ForceList(C.Structure):
+    _fields_ = [("f", vp * 6), ("v", vp * 6), ("vpitch", C.c_uint * 6)]
+
+
+class LangevinArgs(C.Structure):
+    _fields_ = [("d_gamma", vp), ("n_types", C.c_uint), ("use_lambda", C.c_int), ("lambda_", C.c_float),
+                ("T", C.c_float), ("timestep", C.c_uint), ("seed", C.c_uint), ("d_sum_bdenergy", vp),
+                ("noiseless_t", C.c_int), ("tally", C.c_int)]
+
+
+class PDataArrays(C.Structure):
+    _fields_ = [("pos", vp), ("vel", vp), ("accel", vp), ("image", vp), ("tag", vp), ("net_force", vp),
+                ("charge", vp), ("diameter", vp), ("body", vp)]
+
+
+# every symbol include/hoomd_b200.h declares; tests/test_abi.py checks this list against the header and the .so
+SYMBOLS = [
+    "b200_box_init", "b200_box_init_lohi", "b200_compute_cell_list", "b200_cell_list_dimensions",
+    "b200_cell_list_export_padded", "b200_cell_list_build_adjacency", "b200_nlist_build_head_list",
+    "b200_compute_nlist_binned", "b200_nlist_needs_update_check", "b200_compute_lj_forces",
+    "b200_integrator_sum_net_force", "b200_nve_step_one", "b200_nve_step_two", "b200_langevin_hash_seed",
+    "b200_langevin_step_two", "b200_saru_draw", "b200_sfc_generate_sorted_order", "b200_sfc_apply_sorted_order",
+    "b200_compute_thermo", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
+    "b200_sys_set_accel", "b200_sys_get_particles", "b200_sys_setup_lj", "b200_sys_set_virial",
+    "b200_sys_setup_integrator", "b200_sys_add_nve", "b200_sys_add_langevin", "b200_sys_set_sorter",
+    "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
+    "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
+    "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
+    "b200_sys_get_thermo",
+]
+
+_lib = None
+
+
+def lib():
+    """Load the C-ABI library (once) and attach prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("hoomd_b200: %s is missing -- build the CUDA extension first (no CPU fallback exists)"
+                           % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    L.b200_box_init.argtypes = [C.POINTER(Box), C.c_float, C.c_float, C.c_float]
+    L.b200_box_init.restype = None
+    L.b200_box_init_lohi.argtypes = [C.POINTER(Box), C.c_float * 3, C.c_float * 3, C.c_ubyte * 3]
+    L.b200_box_init_lohi.restype = None
+    L.b200_cell_list_dimensions.argtypes = [C.POINTER(Box), C.c_float, C.c_uint, C.c_float, C.POINTER(Dim3),
+                                            C.c_float * 3]
+    L.b200_cell_list_dimensions.restype = None
+    L.b200_compute_cell_list.argtypes = [C.POINTER(CellListArgs), vp]
+    L.b200_cell_list_export_padded.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_uint, C.c_uint, vp]
+    L.b200_cell_list_build_adjacency.argtypes = [vp, Dim3, C.c_uint, C.c_uint, vp]
+    L.b200_nlist_build_head_list.argtypes = [vp, vp, vp, vp, C.c_uint, C.c_uint, vp]
+    L.b200_compute_nlist_binned.argtypes = [C.POINTER(NlistArgs), vp]
+    L.b200_nlist_needs_update_check.argtypes = [vp, vp, vp, C.c_uint, C.POINTER(Box), vp, C.c_float, C.c_uint,
+                                                C.c_float, C.c_float * 3, C.c_uint, vp]
+    L.b200_compute_lj_forces.argtypes = [C.POINTER(PairArgs), vp, vp]
+    L.b200_integrator_sum_net_force.argtypes = [vp, vp, C.c_uint, C.POINTER(ForceList), C.c_uint, C.c_int, C.c_int,
+                                                vp]
+    L.b200_nve_step_one.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.POINTER(Box), C.c_float, C.c_int, C.c_float,
+                                    C.c_int, vp]
+    L.b200_nve_step_two.argtypes = [vp, vp, vp, C.c_uint, vp, C.c_float, C.c_int, C.c_float, C.c_int, vp]
+    L.b200_langevin_hash_seed.argtypes = [C.c_uint]
+    L.b200_langevin_hash_seed.restype = C.c_uint
+    L.b200_langevin_step_two.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint, vp, C.POINTER(LangevinArgs), C.c_float,
+                                         C.c_uint, vp]
+    L.b200_saru_draw.argtypes = [vp, vp, vp, C.c_uint, C.c_uint, vp]
+    L.b200_sfc_generate_sorted_order.argtypes = [vp, vp, vp, vp, C.c_uint64, C.POINTER(C.c_uint64), vp, C.c_uint,
+                                                 C.POINTER(Box), C.c_uint, vp]
+    L.b200_sfc_apply_sorted_order.argtypes = [C.POINTER(PDataArrays), C.POINTER(PDataArrays), vp, vp, C.c_uint, vp]
+    L.b200_compute_thermo.argtypes = [vp, vp, C.c_uint, vp, vp, vp, C.c_uint, vp, C.c_uint, vp]
+    # engine
+    L.b200_sys_create.argtypes = [C.c_uint, C.POINTER(Box), C.c_uint, C.c_int]
+    L.b200_sys_create.restype = vp
+    L.b200_sys_destroy.argtypes = [vp]
+    L.b200_sys_destroy.restype = None
+    L.b200_sys_last_error.argtypes = [vp]
+    L.b200_sys_last_error.restype = C.c_char_p
+    L.b200_sys_set_particles.argtypes = [vp, vp, vp, vp]
+    L.b200_sys_set_accel.argtypes = [vp, vp]
+    L.b200_sys_get_particles.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    L.b200_sys_setup_lj.argtypes = [vp, C.c_float, C.c_uint, vp, vp, vp, vp, C.c_int]
+    L.b200_sys_set_virial.argtypes = [vp, C.c_int]
+    L.b200_sys_setup_integrator.argtypes = [vp, C.c_float]
+    L.b200_sys_add_nve.argtypes = [vp, C.c_int, C.c_float, C.c_int]
+    L.b200_sys_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
+    L.b200_sys_set_sorter.argtypes = [vp, C.c_uint]
+    L.b200_sys_sort_now.argtypes = [vp]
+    L.b200_sys_set_timestep.argtypes = [vp, C.c_uint]
+    L.b200_sys_set_timestep.restype = None
+    L.b200_sys_get_timestep.argtypes = [vp]
+    L.b200_sys_get_timestep.restype = C.c_uint
+    L.b200_sys_set_tuning.argtypes = [vp, C.c_uint, C.c_int]
+    L.b200_sys_compute_nlist.argtypes = [vp, C.c_uint]
+    L.b200_sys_compute_forces.argtypes = [vp, C.c_uint]
+    L.b200_sys_run.argtypes = [vp, C.c_uint, c_double_p, c_double_p]
+    L.b200_sys_step_one.argtypes = [vp, C.c_uint]
+    L.b200_sys_step_two.argtypes = [vp, C.c_uint, vp]
+    L.b200_sys_get_forces.argtypes = [vp, vp, vp]
+    L.b200_sys_get_nlist_size.argtypes = [vp]
+    L.b200_sys_get_nlist_size.restype = C.c_uint
+    L.b200_sys_get_nlist.argtypes = [vp, vp, vp, vp, C.c_uint]
+    L.b200_sys_get_stats.argtypes = [vp, C.POINTER(C.c_ulonglong)]
+    L.b200_sys_get_thermo.argtypes = [vp, c_double_p]
+    _lib = L
+    return L
+
+
+def make_box(Lx, Ly, Lz):
+    b = Box()
+    lib().b200_box_init(C.byref(b), Lx, Ly, Lz)
+    return b
+
+
+def check(rc, what="b200 call"):
+    if rc != 0:
+        raise RuntimeError("%s failed: CUDA error %d" % (what, rc))

@@ -1,0 +1,1113 @@
+// ENGINE: host side of the device-resident system behind the b200_sys_* C ABI.
+//
+// The C++ classes below mirror the reference's plugin objects one to one -- ParticleData (hoomd/ParticleData.h),
+// CellList (hoomd/CellList.h), NeighborListBinned (hoomd/md/NeighborList.h, NeighborListBinned.h), PotentialPairLJ
+// (hoomd/md/PotentialPair.h), TwoStepNVE / TwoStepLangevin (hoomd/md/TwoStepNVE.h, TwoStepLangevin.h),
+// IntegratorTwoStep (hoomd/md/IntegratorTwoStep.h), SFCPackUpdater (hoomd/SFCPackUpdater.h), ComputeThermo -- with the
+// same method names and control flow (compute(ts), needsUpdating, buildHeadList, checkConditions, integrateStepOne/Two,
+// prepRun, update).  Two execution modes produce the same trajectory:
+//   * host-driven   : the reference's control flow, one flag read-back per checked step (NeighborListGPU.cc:93-108)
+//   * device-driven : the whole step (step one + distance check, rebuild decision, conditional rebuild, pair force,
+//                     step two) is a CUDA graph replayed without any host round trip; Nmax overflow (needs a host
+//                     reallocation) sets a sticky flag and the chunk is replayed host-driven from a checkpoint.
+// There is NO CPU fallback: every compute path launches the sm_100a kernels of this directory.
+#include "common.cuh"
+#include "kernels.h"
+#include <string>
+#include <vector>
+#include <chrono>
+#include <stdexcept>
+#include <cmath>
+#include <cstring>
+#include <algorithm>
+
+namespace b200
+{
+#define CUDA_OK(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t _e = (cudaError_t)(expr);                                                           \
+        if (_e != cudaSuccess)                                                                          \
+            throw std::runtime_error(std::string(#expr) + ": " + cudaGetErrorString(_e));               \
+    } while (0)
+
+template<class T> struct DevBuf
+    {
+    T* p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void alloc(size_t count, bool zero = true)
+        {
+        release();
+        n = count;
+        CUDA_OK(cudaMalloc((void**)&p, sizeof(T) * std::max<size_t>(count, 1)));
+        // cudaMemset runs on the legacy stream, which the engine's non-blocking stream does not wait for: finish it here
+        if (zero)
+            {
+            CUDA_OK(cudaMemset(p, 0, sizeof(T) * std::max<size_t>(count, 1)));
+            CUDA_OK(cudaDeviceSynchronize());
+            }
+        }
+    // grow keeping contents (GPUArray::resize)
+    void resize(size_t count)
+        {
+        T* q = nullptr;
+        CUDA_OK(cudaMalloc((void**)&q, sizeof(T) * std::max<size_t>(count, 1)));
+        CUDA_OK(cudaMemset(q, 0, sizeof(T) * std::max<size_t>(count, 1)));
+        if (p) CUDA_OK(cudaMemcpy(q, p, sizeof(T) * std::min(n, count), cudaMemcpyDeviceToDevice));
+        CUDA_OK(cudaDeviceSynchronize());
+        if (p) cudaFree(p);
+        p = q;
+        n = count;
+        }
+    void upload(const T* h, size_t count, cudaStream_t s = 0)
+        {
+        CUDA_OK(cudaMemcpyAsync(p, h, sizeof(T) * count, cudaMemcpyHostToDevice, s));
+        }
+    void download(T* h, size_t count, cudaStream_t s = 0) const
+        {
+        CUDA_OK(cudaMemcpyAsync(h, p, sizeof(T) * count, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        }
+    };
+
+struct f3 { float x, y, z; };
+struct i3 { int x, y, z; };
+} // namespace b200
+
+using namespace b200;
+
+struct b200_system
+    {
+    int device = 0;
+    cudaStream_t stream = 0;
+    std::string error;
+
+    // ---- ParticleData -------------------------------------------------------------------------------------------
+    unsigned int N = 0, ntypes = 1;
+    b200_box box;
+    DevBuf<float4> pos, vel, net_force, pos_alt, vel_alt, net_force_alt;
+    DevBuf<f3> accel, accel_alt;
+    DevBuf<i3> image, image_alt;
+    DevBuf<unsigned int> tag, rtag, tag_alt;
+    DevBuf<float> net_virial; // 6 x pitch
+    unsigned int virial_pitch = 0;
+    bool accel_set = false;
+    bool compute_virial = false; // pdata flags pressure_tensor | isotropic_virial
+
+    // ---- CellList -----------------------------------------------------------------------------------------------
+    b200_dim3 dim = {1, 1, 1};
+    float ghost_width[3] = {0, 0, 0};
+    float nominal_width = 0.0f;
+    DevBuf<unsigned int> cell_count, cell_start, cell_type, particle_cell, particle_slot, scratch_idx, cl_conditions;
+    DevBuf<float4> cell_xyzf;
+    bool cl_first = true, cl_force = true;
+    unsigned int cl_last_computed = 0;
+
+    // ---- NeighborList -------------------------------------------------------------------------------------------
+    bool have_nlist = false;
+    float r_buff = 0.0f;
+    std::vector<float> h_r_cut, h_r_listsq, h_rcut_max;
+    float rcut_max_max = 0.0f;
+    DevBuf<float> d_r_cut, d_r_listsq, d_rcut_max;
+    std::vector<unsigned int> h_Nmax;
+    DevBuf<unsigned int> d_Nmax, nl_conditions, head_list, n_neigh, nlist, d_req_size;
+    DevBuf<float4> last_pos;
+    bool nl_first_compute = true;
+    unsigned int nl_last_computed = 0;
+    bool force_update = true;
+    unsigned int every = 0, last_updated_tstep = 0, last_checked_tstep = 0;
+    bool last_check_result = false;
+    unsigned long long num_updates = 0, num_forced = 0, num_overflows = 0;
+
+    // ---- PotentialPairLJ ----------------------------------------------------------------------------------------
+    DevBuf<float2> d_params;
+    DevBuf<float> d_rcutsq, d_ronsq;
+    int shift_mode = 0;
+    unsigned int pair_tpp = 0;
+
+    // ---- IntegratorTwoStep + method ---------------------------------------------------------------------------
+    bool have_integrator = false;
+    float dt = 0.005f;
+    int method = 0; // 0 none, 1 TwoStepNVE, 2 TwoStepLangevin
+    int limit = 0, zero_force = 0;
+    float limit_val = 0.0f;
+    float kT = 0.0f;
+    unsigned int seed_hashed = 0;
+    int noiseless_t = 0;
+    DevBuf<float> d_gamma;
+
+    // ---- SFCPackUpdater ---------------------------------------------------------------------------------------
+    unsigned int sorter_period = 0, sorter_next = 0, sorter_grid = 256;
+    DevBuf<unsigned int> sort_order, sort_keys, sort_scratch;
+    DevBuf<unsigned char> sort_temp;
+
+    // ---- System -------------------------------------------------------------------------------------------------
+    unsigned int timestep = 0;
+    int use_graph = 1;
+    unsigned int* h_flag = nullptr;      // pinned: distance-check result / small read-backs
+    DevBuf<unsigned int> d_flag;
+    DevBuf<StepState> d_state;
+    StepState* h_state = nullptr;        // pinned
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    bool graph_valid = false;
+    int graph_uses_cond = 0;
+    unsigned long long kernels_last_run = 0;
+    // checkpoint of the device-driven chunk
+    DevBuf<float4> ck_pos, ck_vel, ck_last_pos;
+    DevBuf<f3> ck_accel;
+    DevBuf<i3> ck_image;
+    // thermo
+    DevBuf<double> th_partial, th_out;
+    };
+
+namespace b200
+{
+static void invalidate_graph(b200_system* s)
+    {
+    if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+    if (s->graph) cudaGraphDestroy(s->graph);
+    s->graph_exec = nullptr;
+    s->graph = nullptr;
+    s->graph_valid = false;
+    }
+
+// ---- CellList::compute (hoomd/CellList.cc:133-199) ------------------------------------------------------------------
+static void cell_list_args(b200_system* s, b200_cell_list_args& a)
+    {
+    memset(&a, 0, sizeof(a));
+    a.d_cell_start = s->cell_start.p;
+    a.d_cell_xyzf = (float*)s->cell_xyzf.p;
+    a.d_cell_type = s->ntypes > 1 ? s->cell_type.p : nullptr;
+    a.d_cell_idx = nullptr;
+    a.d_conditions = s->cl_conditions.p;
+    a.d_cell_count = s->cell_count.p;
+    a.d_particle_cell = s->particle_cell.p;
+    a.d_particle_slot = s->particle_slot.p;
+    a.d_scratch_idx = s->scratch_idx.p;
+    a.d_pos = (const float*)s->pos.p;
+    a.N = s->N;
+    a.n_ghost = 0;
+    a.box = s->box;
+    a.dim = s->dim;
+    for (int d = 0; d < 3; d++) a.ghost_width[d] = s->ghost_width[d];
+    }
+
+static void nlist_args(b200_system* s, b200_nlist_args& a)
+    {
+    memset(&a, 0, sizeof(a));
+    a.d_nlist = s->nlist.p;
+    a.d_n_neigh = s->n_neigh.p;
+    a.d_last_pos = (float*)s->last_pos.p;
+    a.d_conditions = s->nl_conditions.p;
+    a.d_Nmax = s->d_Nmax.p;
+    a.d_head_list = s->head_list.p;
+    a.d_pos = (const float*)s->pos.p;
+    a.N = s->N;
+    a.d_cell_start = s->cell_start.p;
+    a.d_cell_xyzf = (const float*)s->cell_xyzf.p;
+    a.d_cell_type = s->ntypes > 1 ? s->cell_type.p : nullptr;
+    a.dim = s->dim;
+    a.box = s->box;
+    for (int d = 0; d < 3; d++) a.ghost_width[d] = s->ghost_width[d];
+    a.d_r_cut = s->d_r_cut.p;
+    a.d_r_listsq = s->d_r_listsq.p;
+    a.ntypes = s->ntypes;
+    a.half_storage = 0;
+    }
+
+static void pair_args(b200_system* s, b200_pair_args& a)
+    {
+    memset(&a, 0, sizeof(a));
+    a.d_force = (float*)s->net_force.p; // single ForceCompute: written straight into the net force (fused K8)
+    a.d_virial = s->net_virial.p;
+    a.virial_pitch = s->virial_pitch;
+    a.N = s->N;
+    a.d_pos = (const float*)s->pos.p;
+    a.box = s->box;
+    a.d_n_neigh = s->n_neigh.p;
+    a.d_nlist = s->nlist.p;
+    a.d_head_list = s->head_list.p;
+    a.d_rcutsq = s->d_rcutsq.p;
+    a.d_ronsq = s->d_ronsq.p;
+    a.ntypes = s->ntypes;
+    a.shift_mode = (unsigned int)s->shift_mode;
+    a.compute_virial = s->compute_virial ? 1u : 0u;
+    a.threads_per_particle = s->pair_tpp;
+    a.block_size = 0;
+    }
+
+static void fused_args(b200_system* s, FusedStepArgs& a)
+    {
+    memset(&a, 0, sizeof(a));
+    a.pos = s->pos.p; a.vel = s->vel.p; a.accel = (float*)s->accel.p; a.image = (int*)s->image.p;
+    a.net_force = s->net_force.p; a.last_pos = s->last_pos.p; a.tag = s->tag.p;
+    a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p;
+    a.N = s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
+    a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
+    a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
+    }
+} // namespace b200
+
+namespace b200
+{
+// ---- CellList ---------------------------------------------------------------------------------------------------------
+static void cell_list_check_conditions(b200_system* s)
+    {
+    unsigned int c[3];
+    s->cl_conditions.download(c, 3, s->stream);
+    if (c[1])
+        throw std::runtime_error("Error computing cell list: particle with index " + std::to_string(c[1] - 1)
+                                 + " has NaN for its position.");
+    if (c[2])
+        throw std::runtime_error("Error computing cell list: particle with index " + std::to_string(c[2] - 1)
+                                 + " is no longer in the simulation box.");
+    }
+
+static void cell_list_compute(b200_system* s, unsigned int ts)
+    {
+    // Compute::shouldCompute + m_force_compute (particle sort / box change)
+    bool should = s->cl_first || s->cl_force || s->cl_last_computed != ts;
+    if (!should) return;
+    s->cl_first = false;
+    s->cl_force = false;
+    s->cl_last_computed = ts;
+    b200_cell_list_args a;
+    cell_list_args(s, a);
+    CUDA_OK(launch_cell_list(&a, nullptr, s->stream));
+    s->kernels_last_run += 4;
+    cell_list_check_conditions(s);
+    }
+
+// ---- NeighborList -----------------------------------------------------------------------------------------------------
+// NeighborList::updateRList (hoomd/md/NeighborList.cc:354-400)
+static void nlist_update_rlist(b200_system* s)
+    {
+    const unsigned int nt = s->ntypes;
+    s->h_r_listsq.assign(nt * nt, 0.0f);
+    s->h_rcut_max.assign(nt, 0.0f);
+    float r_cut_max = 0.0f;
+    for (unsigned int i = 0; i < nt; i++)
+        {
+        float r_cut_max_i = 0.0f;
+        for (unsigned int j = 0; j < nt; j++)
+            {
+            const float r_cut_ij = s->h_r_cut[i * nt + j];
+            if (r_cut_ij > r_cut_max_i) r_cut_max_i = r_cut_ij;
+            float r_list = (r_cut_ij > 0.0f) ? r_cut_ij + s->r_buff : 0.0f;
+            s->h_r_listsq[i * nt + j] = r_list * r_list;
+            }
+        s->h_rcut_max[i] = r_cut_max_i;
+        if (r_cut_max_i > r_cut_max) r_cut_max = r_cut_max_i;
+        }
+    s->rcut_max_max = r_cut_max;
+    s->d_r_cut.upload(s->h_r_cut.data(), nt * nt, s->stream);
+    s->d_r_listsq.upload(s->h_r_listsq.data(), nt * nt, s->stream);
+    s->d_rcut_max.upload(s->h_rcut_max.data(), nt, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    }
+
+// NeighborList::buildHeadList + resizeNlist (hoomd/md/NeighborList.cc:1336-1380)
+static void nlist_build_head_list(b200_system* s)
+    {
+    CUDA_OK(b200_nlist_build_head_list(s->head_list.p, s->d_req_size.p, s->d_Nmax.p, (const float*)s->pos.p, s->N,
+                                       s->ntypes, s->stream));
+    s->kernels_last_run += (s->ntypes == 1) ? 1 : 3;
+    unsigned int size = 0;
+    s->d_req_size.download(&size, 1, s->stream);
+    if (size > s->nlist.n)
+        {
+        size_t alloc_size = s->nlist.n ? s->nlist.n : 1;
+        while (size > alloc_size) alloc_size = ((size_t)(((float)alloc_size) * 1.125f)) + 1;
+        s->nlist.alloc(alloc_size, false);
+        invalidate_graph(s);
+        }
+    }
+
+// NeighborList::checkConditions (hoomd/md/NeighborList.cc:1389-1405)
+static bool nlist_check_conditions(b200_system* s)
+    {
+    std::vector<unsigned int> c(s->ntypes);
+    s->nl_conditions.download(c.data(), s->ntypes, s->stream);
+    bool result = false;
+    for (unsigned int i = 0; i < s->ntypes; i++)
+        if (c[i] > s->h_Nmax[i])
+            {
+            s->h_Nmax[i] = (c[i] > 8) ? (c[i] + 7) & ~7u : 8;
+            result = true;
+            }
+    if (result)
+        {
+        s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        }
+    return result;
+    }
+
+// NeighborList::distanceCheck (hoomd/md/NeighborList.cc:964-1040): kernel + one mapped-flag style read-back
+static bool nlist_distance_check(b200_system* s, unsigned int ts)
+    {
+    CUDA_OK(cudaMemsetAsync(s->d_flag.p, 0, sizeof(unsigned int), s->stream));
+    const float lambda[3] = {1.0f, 1.0f, 1.0f};
+    CUDA_OK(b200_nlist_needs_update_check(s->d_flag.p, (const float*)s->last_pos.p, (const float*)s->pos.p, s->N,
+                                          &s->box, s->d_rcut_max.p, s->r_buff, s->ntypes, 1.0f, lambda, ts + 1,
+                                          s->stream));
+    s->kernels_last_run += 1;
+    CUDA_OK(cudaMemcpyAsync(s->h_flag, s->d_flag.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    return *s->h_flag == ts + 1;
+    }
+
+// NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163); dist_check is always on (md.nlist.cell default)
+static bool nlist_needs_updating(b200_system* s, unsigned int ts)
+    {
+    if (s->last_checked_tstep == ts)
+        {
+        if (s->force_update)
+            {
+            s->force_update = false;
+            return true;
+            }
+        return s->last_check_result;
+        }
+    s->last_checked_tstep = ts;
+    const bool should_check = !s->force_update && !(ts < s->last_updated_tstep + s->every);
+    if (!s->force_update && !should_check)
+        {
+        s->last_check_result = false;
+        return false;
+        }
+    bool result = false;
+    if (s->force_update)
+        {
+        result = true;
+        s->force_update = false;
+        s->num_forced += 1;
+        s->last_updated_tstep = ts;
+        }
+    else
+        {
+        if (s->r_buff < 1e-6f) result = true;
+        else result = nlist_distance_check(s, ts);
+        if (result)
+            {
+            s->last_updated_tstep = ts;
+            s->num_updates += 1;
+            }
+        }
+    s->last_check_result = result;
+    return result;
+    }
+
+// NeighborListBinned::buildNlist (hoomd/md/NeighborListBinned.cc:79-240)
+static void nlist_build(b200_system* s, unsigned int ts)
+    {
+    cell_list_compute(s, ts);
+    const float rmax = s->rcut_max_max + s->r_buff;
+    for (int d = 0; d < 3; d++)
+        if (s->box.periodic[d] && s->box.L[d] <= rmax * 2.0f)
+            throw std::runtime_error("nlist: Simulation box is too small! Particles would be interacting with themselves.");
+    b200_nlist_args a;
+    nlist_args(s, a);
+    CUDA_OK(launch_nlist_binned(&a, nullptr, s->stream));
+    s->kernels_last_run += 1;
+    }
+
+// NeighborList::compute (hoomd/md/NeighborList.cc:201-253)
+static void nlist_compute(b200_system* s, unsigned int ts)
+    {
+    if (!s->have_nlist) throw std::runtime_error("nlist: not set up (call b200_sys_setup_lj first)");
+    bool should = s->nl_first_compute || s->nl_last_computed != ts;
+    s->nl_first_compute = false;
+    s->nl_last_computed = ts;
+    if (!should && !s->force_update) return;
+    if (s->force_update) nlist_build_head_list(s);
+    if (nlist_needs_updating(s, ts))
+        {
+        bool overflowed = false;
+        do
+            {
+            nlist_build(s, ts);
+            overflowed = nlist_check_conditions(s);
+            if (overflowed)
+                {
+                s->num_overflows += 1;
+                nlist_build_head_list(s);
+                CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+                }
+            } while (overflowed);
+        // setLastUpdatedPos: done by the build kernel (like the reference GPU path, NeighborListGPUBinned.cu:280-285)
+        }
+    }
+
+// ---- PotentialPair::computeForces + Integrator::computeNetForce (single force => fused) -------------------------------
+static void compute_net_force(b200_system* s, unsigned int ts)
+    {
+    nlist_compute(s, ts);
+    b200_pair_args a;
+    pair_args(s, a);
+    CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
+    s->kernels_last_run += 1;
+    }
+
+static void integrate_step_one(b200_system* s, unsigned int ts)
+    {
+    (void)ts;
+    const bool nve = s->method == 1;
+    CUDA_OK(b200_nve_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p, nullptr,
+                              s->N, &s->box, s->dt, nve ? s->limit : 0, s->limit_val, nve ? s->zero_force : 0,
+                              s->stream));
+    s->kernels_last_run += 1;
+    }
+
+static void integrate_step_two(b200_system* s, unsigned int ts)
+    {
+    if (s->method == 2)
+        {
+        b200_langevin_args la;
+        memset(&la, 0, sizeof(la));
+        la.d_gamma = s->d_gamma.p;
+        la.n_types = s->ntypes;
+        la.T = s->kT;
+        la.timestep = ts;
+        la.seed = s->seed_hashed;
+        la.noiseless_t = s->noiseless_t;
+        CUDA_OK(b200_langevin_step_two((const float*)s->pos.p, (float*)s->vel.p, (float*)s->accel.p, nullptr, s->tag.p,
+                                       nullptr, s->N, (const float*)s->net_force.p, &la, s->dt, 3, s->stream));
+        }
+    else
+        CUDA_OK(b200_nve_step_two((float*)s->vel.p, (float*)s->accel.p, nullptr, s->N, (const float*)s->net_force.p,
+                                  s->dt, s->limit, s->limit_val, s->zero_force, s->stream));
+    s->kernels_last_run += 1;
+    }
+
+// IntegratorTwoStep::prepRun (hoomd/md/IntegratorTwoStep.cc:336-398)
+static void prep_run(b200_system* s, unsigned int ts)
+    {
+    if (!s->have_integrator || !s->method) throw std::runtime_error("integrate: no integration method set");
+    compute_net_force(s, ts);
+    if (!s->accel_set)
+        {
+        CUDA_OK(launch_compute_accel((float*)s->accel.p, s->net_force.p, s->vel.p, s->N, s->stream));
+        s->kernels_last_run += 1;
+        s->accel_set = true;
+        }
+    }
+
+// SFCPackUpdater::update (hoomd/SFCPackUpdater.cc:70-108)
+static void sorter_update(b200_system* s)
+    {
+    const unsigned int N = s->N;
+    if (s->sort_order.n < N)
+        {
+        s->sort_order.alloc(N);
+        s->sort_keys.alloc(N);
+        s->sort_scratch.alloc(2 * (size_t)N);
+        uint64_t need = 0;
+        CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, nullptr, 0, &need,
+                                               (const float*)s->pos.p, N, &s->box, s->sorter_grid, s->stream));
+        s->sort_temp.alloc(need + 16);
+        s->pos_alt.alloc(N); s->vel_alt.alloc(N); s->net_force_alt.alloc(N);
+        s->accel_alt.alloc(N); s->image_alt.alloc(N); s->tag_alt.alloc(N);
+        }
+    CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, s->sort_temp.p,
+                                           s->sort_temp.n, nullptr, (const float*)s->pos.p, N, &s->box, s->sorter_grid,
+                                           s->stream));
+    b200_pdata_arrays in, out;
+    memset(&in, 0, sizeof(in));
+    memset(&out, 0, sizeof(out));
+    in.pos = (float*)s->pos.p; in.vel = (float*)s->vel.p; in.accel = (float*)s->accel.p; in.image = (int*)s->image.p;
+    in.tag = s->tag.p; in.net_force = (float*)s->net_force.p;
+    out.pos = (float*)s->pos_alt.p; out.vel = (float*)s->vel_alt.p; out.accel = (float*)s->accel_alt.p;
+    out.image = (int*)s->image_alt.p; out.tag = s->tag_alt.p; out.net_force = (float*)s->net_force_alt.p;
+    CUDA_OK(b200_sfc_apply_sorted_order(&out, &in, s->rtag.p, s->sort_order.p, N, s->stream));
+    // copy back instead of swapping pointers: the captured step graph keeps its baked addresses
+    CUDA_OK(cudaMemcpyAsync(s->pos.p, s->pos_alt.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->vel.p, s->vel_alt.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->net_force.p, s->net_force_alt.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->accel.p, s->accel_alt.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->image.p, s->image_alt.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->tag.p, s->tag_alt.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
+    s->kernels_last_run += 4;
+    // notifyParticleSort(): nlist forceUpdate, cell list force compute
+    s->force_update = true;
+    s->cl_force = true;
+    }
+} // namespace b200
+
+namespace b200
+{
+// ---- device-driven stepping -----------------------------------------------------------------------------------------------
+// One graph = one IntegratorTwoStep::update(ts) (hoomd/md/IntegratorTwoStep.cc:96-161):
+//   k_fused_step_one -> k_decide -> [IF need_rebuild: cell list (4 kernels) -> nlist -> k_post_rebuild] -> pair -> step two
+// mode 2 puts the bracket into a conditional IF node (CUDA >= 12.4); mode 1 launches the rebuild kernels every step and
+// lets them return at once on !need_rebuild (the `enable` pointer).
+static void enqueue_rebuild(b200_system* s, const unsigned int* enable)
+    {
+    b200_cell_list_args ca;
+    cell_list_args(s, ca);
+    CUDA_OK(launch_cell_list(&ca, enable, s->stream));
+    b200_nlist_args na;
+    nlist_args(s, na);
+    CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
+    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    }
+
+static void enqueue_forces_and_step_two(b200_system* s, const FusedStepArgs& fa)
+    {
+    b200_pair_args pa;
+    pair_args(s, pa);
+    CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
+    CUDA_OK(launch_fused_step_two(fa, s->d_state.p, s->stream));
+    }
+
+static bool build_graph_conditional(b200_system* s)
+    {
+#if (CUDART_VERSION >= 12040)
+    FusedStepArgs fa;
+    fused_args(s, fa);
+    const unsigned int* enable = &s->d_state.p->need_rebuild;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool capturing = false;
+    try
+        {
+        CUDA_OK(cudaGraphCreate(&graph, 0));
+        cudaGraphConditionalHandle handle;
+        CUDA_OK(cudaGraphConditionalHandleCreate(&handle, graph, 0, cudaGraphCondAssignDefault));
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+        CUDA_OK(launch_decide(s->d_state.p, (unsigned long long)handle, 1, s->stream));
+        // splice the conditional node in after what has been captured so far
+        cudaStreamCaptureStatus status;
+        const cudaGraphNode_t* deps = nullptr;
+        size_t ndeps = 0;
+        cudaGraph_t cap_graph = nullptr;
+        CUDA_OK(cudaStreamGetCaptureInfo_v2(s->stream, &status, nullptr, &cap_graph, &deps, &ndeps));
+        cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+        np.type = cudaGraphNodeTypeConditional;
+        np.conditional.handle = handle;
+        np.conditional.type = cudaGraphCondTypeIf;
+        np.conditional.size = 1;
+        cudaGraphNode_t cond_node;
+        CUDA_OK(cudaGraphAddNode(&cond_node, graph, deps, ndeps, &np));
+        cudaGraph_t body = np.conditional.phGraph_out[0];
+        CUDA_OK(cudaStreamUpdateCaptureDependencies(s->stream, &cond_node, 1, cudaStreamSetCaptureDependencies));
+        enqueue_forces_and_step_two(s, fa);
+        cudaGraph_t out = nullptr;
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        // body of the IF node
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        enqueue_rebuild(s, enable);
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+        }
+    catch (const std::exception& e)
+        {
+        if (capturing)
+            {
+            cudaGraph_t junk = nullptr;
+            cudaStreamEndCapture(s->stream, &junk);
+            }
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        s->error = std::string("conditional graph unavailable, using early-exit kernels: ") + e.what();
+        return false;
+        }
+    s->graph = graph;
+    s->graph_exec = exec;
+    s->graph_uses_cond = 1;
+    s->graph_valid = true;
+    return true;
+#else
+    return false;
+#endif
+    }
+
+static void build_graph_plain(b200_system* s)
+    {
+    FusedStepArgs fa;
+    fused_args(s, fa);
+    const unsigned int* enable = &s->d_state.p->need_rebuild;
+    CUDA_OK(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+    try
+        {
+        CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+        CUDA_OK(launch_decide(s->d_state.p, 0ull, 0, s->stream));
+        enqueue_rebuild(s, enable);
+        enqueue_forces_and_step_two(s, fa);
+        }
+    catch (...)
+        {
+        cudaGraph_t junk = nullptr;
+        cudaStreamEndCapture(s->stream, &junk);
+        if (junk) cudaGraphDestroy(junk);
+        throw;
+        }
+    CUDA_OK(cudaStreamEndCapture(s->stream, &s->graph));
+    CUDA_OK(cudaGraphInstantiate(&s->graph_exec, s->graph, 0));
+    s->graph_uses_cond = 0;
+    s->graph_valid = true;
+    }
+
+static void ensure_graph(b200_system* s)
+    {
+    if (s->graph_valid) return;
+    invalidate_graph(s);
+    if (s->use_graph >= 2 && build_graph_conditional(s)) return;
+    build_graph_plain(s);
+    }
+
+static void host_step(b200_system* s)
+    {
+    integrate_step_one(s, s->timestep);
+    compute_net_force(s, s->timestep + 1);
+    integrate_step_two(s, s->timestep);
+    s->timestep++;
+    }
+
+static void run_chunk_device(b200_system* s, unsigned int chunk)
+    {
+    const unsigned int N = s->N;
+    if (s->force_update) nlist_build_head_list(s); // types may have been permuted by the sorter
+    ensure_graph(s);
+    if (s->ck_pos.n < N)
+        {
+        s->ck_pos.alloc(N); s->ck_vel.alloc(N); s->ck_last_pos.alloc(N); s->ck_accel.alloc(N); s->ck_image.alloc(N);
+        }
+    // checkpoint (device to device, ~72 B/particle per chunk)
+    CUDA_OK(cudaMemcpyAsync(s->ck_pos.p, s->pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->ck_vel.p, s->vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->ck_last_pos.p, s->last_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->ck_accel.p, s->accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->ck_image.p, s->image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+    const bool ck_force_update = s->force_update;
+
+    StepState& st = *s->h_state;
+    memset(&st, 0, sizeof(st));
+    st.timestep = s->timestep;
+    st.force_update = s->force_update ? 1u : 0u;
+    st.last_updated = s->last_updated_tstep;
+    st.every = s->every;
+    st.r_buff_tiny = (s->r_buff < 1e-6f) ? 1u : 0u;
+    st.ntypes = s->ntypes;
+    CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
+    for (unsigned int k = 0; k < chunk; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+    CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    if (!st.overflow) cell_list_check_conditions(s);
+
+    if (st.overflow)
+        {
+        CUDA_OK(cudaMemsetAsync(s->cl_conditions.p, 0, sizeof(unsigned int) * 3, s->stream));
+        // Nmax overflow needs a host reallocation: restore the checkpoint and replay the chunk with the reference's
+        // host protocol (NeighborList.cc:226-244).  The trajectory is deterministic, so the replay is exact.
+        s->num_overflows += 1;
+        CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+        s->force_update = ck_force_update;
+        if (!ck_force_update)
+            {
+            // re-create the list that was current at the checkpoint: it is a pure function of last_pos
+            CUDA_OK(launch_merge_xyz_w(s->pos.p, s->ck_last_pos.p, s->ck_pos.p, N, s->stream));
+            bool overflowed;
+            do
+                {
+                s->cl_force = true;
+                nlist_build(s, s->timestep);
+                overflowed = nlist_check_conditions(s);
+                if (overflowed)
+                    {
+                    nlist_build_head_list(s);
+                    CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+                    }
+                } while (overflowed);
+            }
+        CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        s->cl_force = true;
+        for (unsigned int k = 0; k < chunk; k++) host_step(s);
+        return;
+        }
+    const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
+    s->kernels_last_run += s->graph_uses_cond ? (4ull * chunk + 6ull * rebuilds) : 10ull * chunk;
+    s->timestep = st.timestep;
+    s->last_updated_tstep = st.last_updated;
+    s->num_updates += st.num_updates;
+    s->num_forced += st.num_forced;
+    s->force_update = st.force_update != 0;
+    s->last_checked_tstep = st.timestep;
+    s->last_check_result = st.need_rebuild != 0;
+    s->nl_last_computed = st.timestep;
+    s->nl_first_compute = false;
+    if (rebuilds)
+        {
+        s->cl_last_computed = st.last_updated;
+        s->cl_first = false;
+        s->cl_force = false;
+        }
+    }
+} // namespace b200
+
+// ---- C ABI --------------------------------------------------------------------------------------------------------------
+#define SYS_TRY(s) (s)->error.clear(); try { CUDA_OK(cudaSetDevice((s)->device));
+#define SYS_CATCH(s) } catch (const std::exception& e) { (s)->error = e.what(); cudaGetLastError(); return 1; } return 0;
+
+extern "C" {
+
+b200_system* b200_sys_create(unsigned int N, const b200_box* box, unsigned int ntypes, int device)
+    {
+    b200_system* s = new b200_system;
+    s->device = device;
+    try
+        {
+        int ndev = 0;
+        CUDA_OK(cudaGetDeviceCount(&ndev));
+        if (ndev == 0) throw std::runtime_error("no CUDA device: hoomd_b200 has no CPU fallback");
+        CUDA_OK(cudaSetDevice(device));
+        CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+        s->N = N;
+        s->ntypes = ntypes ? ntypes : 1;
+        s->box = *box;
+        s->pos.alloc(N); s->vel.alloc(N); s->net_force.alloc(N); s->accel.alloc(N); s->image.alloc(N);
+        s->tag.alloc(N); s->rtag.alloc(N); s->last_pos.alloc(N);
+        s->virial_pitch = N + (16 - (N & 15)); // GPUArray 2D pitch rule (hoomd/GPUArray.h:424-425)
+        s->net_virial.alloc(6 * (size_t)s->virial_pitch);
+        std::vector<unsigned int> ident(N);
+        for (unsigned int i = 0; i < N; i++) ident[i] = i;
+        s->tag.upload(ident.data(), N, s->stream);
+        s->rtag.upload(ident.data(), N, s->stream);
+        // default mass 1 (ParticleData ctor)
+        std::vector<float4> v(N, make_float4(0.0f, 0.0f, 0.0f, 1.0f));
+        s->vel.upload(v.data(), N, s->stream);
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        s->d_flag.alloc(4);
+        s->d_state.alloc(1);
+        s->d_req_size.alloc(1);
+        s->cl_conditions.alloc(3);
+        CUDA_OK(cudaHostAlloc((void**)&s->h_flag, 4 * sizeof(unsigned int), cudaHostAllocDefault));
+        CUDA_OK(cudaHostAlloc((void**)&s->h_state, sizeof(StepState), cudaHostAllocDefault));
+        s->th_partial.alloc(9 * 1024);
+        s->th_out.alloc(16);
+        }
+    catch (const std::exception& e)
+        {
+        s->error = e.what();
+        }
+    return s;
+    }
+
+void b200_sys_destroy(b200_system* s)
+    {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    invalidate_graph(s);
+    if (s->h_flag) cudaFreeHost(s->h_flag);
+    if (s->h_state) cudaFreeHost(s->h_state);
+    cudaStream_t st = s->stream;
+    delete s;
+    if (st) cudaStreamDestroy(st);
+    }
+
+const char* b200_sys_last_error(b200_system* s) { return s->error.c_str(); }
+
+int b200_sys_set_particles(b200_system* s, const float* pos4, const float* vel4, const int* image3)
+    {
+    SYS_TRY(s)
+    if (pos4) s->pos.upload((const float4*)pos4, s->N, s->stream);
+    if (vel4) s->vel.upload((const float4*)vel4, s->N, s->stream);
+    if (image3) s->image.upload((const i3*)image3, s->N, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    s->force_update = true;
+    s->cl_force = true;
+    SYS_CATCH(s)
+    }
+
+int b200_sys_set_accel(b200_system* s, const float* accel3)
+    {
+    SYS_TRY(s)
+    s->accel.upload((const f3*)accel3, s->N, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    s->accel_set = true;
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_particles(b200_system* s, float* pos4, float* vel4, float* accel3, int* image3, unsigned int* tag,
+                           unsigned int* rtag)
+    {
+    SYS_TRY(s)
+    if (pos4) s->pos.download((float4*)pos4, s->N, s->stream);
+    if (vel4) s->vel.download((float4*)vel4, s->N, s->stream);
+    if (accel3) s->accel.download((f3*)accel3, s->N, s->stream);
+    if (image3) s->image.download((i3*)image3, s->N, s->stream);
+    if (tag) s->tag.download(tag, s->N, s->stream);
+    if (rtag) s->rtag.download(rtag, s->N, s->stream);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut, const float* lj1,
+                      const float* lj2, const float* ron, int shift_mode)
+    {
+    SYS_TRY(s)
+    const unsigned int nt = s->ntypes;
+    if (r_buff < 0.0f) throw std::runtime_error("nlist: Requested buffer radius is less than zero");
+    if (shift_mode < 0 || shift_mode > 2) throw std::runtime_error("pair: invalid shift mode");
+    s->r_buff = r_buff;
+    s->every = check_period;
+    s->shift_mode = shift_mode;
+    s->h_r_cut.assign(rcut, rcut + nt * nt);
+    s->d_r_cut.alloc(nt * nt); s->d_r_listsq.alloc(nt * nt); s->d_rcut_max.alloc(nt);
+    nlist_update_rlist(s);
+    // pair tables: rcutsq = rcut*rcut, ronsq = ron*ron (PotentialPair::setRcut/setRon, hoomd/md/PotentialPair.h:237-269)
+    std::vector<float2> prm(nt * nt);
+    std::vector<float> rcsq(nt * nt), ronsq(nt * nt, 0.0f);
+    for (unsigned int k = 0; k < nt * nt; k++)
+        {
+        prm[k] = make_float2(lj1[k], lj2[k]);
+        rcsq[k] = rcut[k] * rcut[k];
+        if (ron) ronsq[k] = ron[k] * ron[k];
+        }
+    s->d_params.alloc(nt * nt); s->d_rcutsq.alloc(nt * nt); s->d_ronsq.alloc(nt * nt);
+    s->d_params.upload(prm.data(), nt * nt, s->stream);
+    s->d_rcutsq.upload(rcsq.data(), nt * nt, s->stream);
+    s->d_ronsq.upload(ronsq.data(), nt * nt, s->stream);
+    // NeighborList ctor: Nmax = 8 per type, nlist 8*N (hoomd/md/NeighborList.cc:80-98)
+    s->h_Nmax.assign(nt, 8u);
+    s->d_Nmax.alloc(nt);
+    s->d_Nmax.upload(s->h_Nmax.data(), nt, s->stream);
+    s->nl_conditions.alloc(nt);
+    s->head_list.alloc(s->N);
+    s->n_neigh.alloc(s->N);
+    s->nlist.alloc(8 * (size_t)s->N);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    // CellList: nominal width = max r_cut + r_buff (NeighborListBinned.cc:56-76), radius 1, no ghosts (single domain)
+    s->nominal_width = s->rcut_max_max + s->r_buff;
+    b200_cell_list_dimensions(&s->box, s->nominal_width, 1, 0.0f, &s->dim, s->ghost_width);
+    const size_t ncells = (size_t)s->dim.x * s->dim.y * s->dim.z;
+    s->cell_count.alloc(ncells); s->cell_start.alloc(ncells + 1);
+    s->cell_xyzf.alloc(s->N); s->cell_type.alloc(s->N);
+    s->particle_cell.alloc(s->N); s->particle_slot.alloc(s->N); s->scratch_idx.alloc(s->N);
+    s->have_nlist = true;
+    s->force_update = true;
+    s->cl_force = true;
+    s->nl_first_compute = true;
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_set_virial(b200_system* s, int on)
+    {
+    s->compute_virial = on != 0;
+    invalidate_graph(s);
+    return 0;
+    }
+
+int b200_sys_setup_integrator(b200_system* s, float dt)
+    {
+    s->dt = dt;
+    s->have_integrator = true;
+    invalidate_graph(s);
+    return 0;
+    }
+
+int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force)
+    {
+    s->method = 1;
+    s->limit = limit;
+    s->limit_val = limit_val;
+    s->zero_force = zero_force;
+    invalidate_graph(s);
+    return 0;
+    }
+
+int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t)
+    {
+    SYS_TRY(s)
+    s->method = 2;
+    s->limit = 0;
+    s->zero_force = 0;
+    s->kT = kT;
+    s->seed_hashed = b200_langevin_hash_seed(seed);
+    s->noiseless_t = noiseless_t;
+    std::vector<float> g(s->ntypes, 1.0f);
+    if (gamma) g.assign(gamma, gamma + s->ntypes);
+    s->d_gamma.alloc(s->ntypes);
+    s->d_gamma.upload(g.data(), s->ntypes, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_set_sorter(b200_system* s, unsigned int period)
+    {
+    s->sorter_period = period;
+    s->sorter_next = s->timestep;
+    return 0;
+    }
+
+int b200_sys_sort_now(b200_system* s)
+    {
+    SYS_TRY(s)
+    sorter_update(s);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+void b200_sys_set_timestep(b200_system* s, unsigned int ts) { s->timestep = ts; }
+unsigned int b200_sys_get_timestep(b200_system* s) { return s->timestep; }
+
+int b200_sys_set_tuning(b200_system* s, unsigned int pair_tpp, int use_graph)
+    {
+    s->pair_tpp = pair_tpp;
+    s->use_graph = use_graph;
+    invalidate_graph(s);
+    return 0;
+    }
+
+int b200_sys_compute_nlist(b200_system* s, unsigned int ts)
+    {
+    SYS_TRY(s)
+    nlist_compute(s, ts);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_compute_forces(b200_system* s, unsigned int ts)
+    {
+    SYS_TRY(s)
+    compute_net_force(s, ts);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double* gpu_ms)
+    {
+    SYS_TRY(s)
+    s->kernels_last_run = 0;
+    prep_run(s, s->timestep);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    cudaEvent_t e0, e1;
+    CUDA_OK(cudaEventCreate(&e0));
+    CUDA_OK(cudaEventCreate(&e1));
+    auto t0 = std::chrono::steady_clock::now();
+    CUDA_OK(cudaEventRecord(e0, s->stream));
+    unsigned int remaining = nsteps;
+    const unsigned int chunk_max = 500;
+    while (remaining)
+        {
+        if (s->sorter_period && s->timestep == s->sorter_next)
+            {
+            sorter_update(s);
+            s->sorter_next += s->sorter_period;
+            }
+        unsigned int chunk = std::min(remaining, chunk_max);
+        if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
+        if (s->use_graph)
+            run_chunk_device(s, chunk);
+        else
+            for (unsigned int k = 0; k < chunk; k++) host_step(s);
+        remaining -= chunk;
+        }
+    CUDA_OK(cudaEventRecord(e1, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    auto t1 = std::chrono::steady_clock::now();
+    float ms = 0.0f;
+    CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (elapsed_s) *elapsed_s = std::chrono::duration<double>(t1 - t0).count();
+    if (gpu_ms) *gpu_ms = ms;
+    SYS_CATCH(s)
+    }
+
+int b200_sys_step_one(b200_system* s, unsigned int ts)
+    {
+    SYS_TRY(s)
+    if (!s->method) throw std::runtime_error("integrate: no integration method set");
+    integrate_step_one(s, ts);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_step_two(b200_system* s, unsigned int ts, const float* net_force4)
+    {
+    SYS_TRY(s)
+    if (!s->method) throw std::runtime_error("integrate: no integration method set");
+    if (net_force4) s->net_force.upload((const float4*)net_force4, s->N, s->stream);
+    integrate_step_two(s, ts);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_forces(b200_system* s, float* force4, float* virial6)
+    {
+    SYS_TRY(s)
+    if (force4) s->net_force.download((float4*)force4, s->N, s->stream);
+    if (virial6)
+        {
+        for (unsigned int k = 0; k < 6; k++)
+            CUDA_OK(cudaMemcpyAsync(virial6 + (size_t)k * s->N, s->net_virial.p + (size_t)k * s->virial_pitch,
+                                    sizeof(float) * s->N, cudaMemcpyDeviceToHost, s->stream));
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        }
+    SYS_CATCH(s)
+    }
+
+unsigned int b200_sys_get_nlist_size(b200_system* s) { return (unsigned int)s->nlist.n; }
+
+int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist,
+                       unsigned int nlist_len)
+    {
+    SYS_TRY(s)
+    if (n_neigh) s->n_neigh.download(n_neigh, s->N, s->stream);
+    if (head) s->head_list.download(head, s->N, s->stream);
+    if (nlist) s->nlist.download(nlist, std::min<size_t>(nlist_len, s->nlist.n), s->stream);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_stats(b200_system* s, unsigned long long* out8)
+    {
+    out8[0] = s->num_updates;
+    out8[1] = s->num_forced;
+    out8[2] = s->num_overflows;
+    out8[3] = s->kernels_last_run;
+    out8[4] = s->dim.x;
+    out8[5] = s->dim.y;
+    out8[6] = s->dim.z;
+    out8[7] = s->h_Nmax.empty() ? 0 : s->h_Nmax[0];
+    return 0;
+    }
+
+int b200_sys_get_thermo(b200_system* s, double* out5)
+    {
+    SYS_TRY(s)
+    const unsigned int nblocks = std::max(1u, std::min(1024u, (s->N + 255u) / 256u));
+    CUDA_OK(b200_compute_thermo(s->th_out.p, s->th_partial.p, nblocks, (const float*)s->vel.p,
+                                (const float*)s->net_force.p, s->compute_virial ? s->net_virial.p : nullptr,
+                                s->virial_pitch, nullptr, s->N, s->stream));
+    double h[9];
+    s->th_out.download(h, 9, s->stream);
+    // IntegratorTwoStep::getNDOF: D*N - D (hoomd/md/IntegratorTwoStep.cc:270-283); ComputeThermo stores FP32 properties
+    const double ndof = 3.0 * s->N - 3.0;
+    const float ke = (float)h[0], pe = (float)h[1];
+    const double volume = (double)(s->box.L[0] * s->box.L[1] * s->box.L[2]);
+    const double W = (1.0f / 3.0f) * h[2];
+    out5[0] = ke;
+    out5[1] = pe;
+    out5[2] = (float)(2.0f / (float)ndof) * ke;
+    out5[3] = s->compute_virial ? (float)((2.0 * h[0] / 3.0 + W) / (float)volume) : 0.0;
+    out5[4] = ndof;
+    SYS_CATCH(s)
+    }
+
+} // extern "C"

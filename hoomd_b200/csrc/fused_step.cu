@@ -171,3 +171,23 @@ cudaError_t launch_compute_accel(float* accel, const float4* net_force, const fl
     return cudaGetLastError();
     }
 } // namespace b200
+
+// out[i] = (xyz of a[i], w of b[i]) -- rebuilds the positions a neighbor list was built from (last_pos carries no type)
+namespace b200
+{
+__global__ void __launch_bounds__(256) k_merge_xyz_w(float4* __restrict__ out, const float4* __restrict__ a,
+                                                     const float4* __restrict__ b, unsigned int N)
+    {
+    unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float4 x = a[i];
+    out[i] = make_float4(x.x, x.y, x.z, b[i].w);
+    }
+
+cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, unsigned int N, cudaStream_t stream)
+    {
+    if (N == 0) return cudaSuccess;
+    k_merge_xyz_w<<<(N + 255) / 256, 256, 0, stream>>>(out, a, b, N);
+    return cudaGetLastError();
+    }
+} // namespace b200

