@@ -273,3 +273,522 @@ static int cl_compute(orc_system* s, unsigned int ts) /* CellList::compute, Cell
         }
     return 0;
     }
+
+/* ---- NeighborList (hoomd/md/NeighborList.cc, NeighborListBinned.cc) ---------------------------------------------------- */
+static void nl_update_rlist(orc_system* s) /* NeighborList.cc:354-400 */
+    {
+    unsigned int nt = s->ntypes;
+    float r_cut_max = 0.0f;
+    for (unsigned int i = 0; i < nt; i++)
+        {
+        float r_cut_max_i = 0.0f;
+        for (unsigned int j = 0; j < nt; j++)
+            {
+            const float r_cut_ij = s->r_cut[i * nt + j];
+            if (r_cut_ij > r_cut_max_i) r_cut_max_i = r_cut_ij;
+            float r_list = (r_cut_ij > 0.0f) ? r_cut_ij + s->r_buff : 0.0f;
+            s->r_listsq[i * nt + j] = r_list * r_list;
+            }
+        s->rcut_max[i] = r_cut_max_i;
+        if (r_cut_max_i > r_cut_max) r_cut_max = r_cut_max_i;
+        }
+    s->rcut_max_max = r_cut_max;
+    }
+
+static void nl_build_head_list(orc_system* s) /* NeighborList.cc:1336-1380 */
+    {
+    unsigned int head = 0;
+    for (unsigned int i = 0; i < s->N; i++)
+        {
+        s->head[i] = head;
+        head += s->Nmax[as_uint(s->pos[i].w)];
+        }
+    if (head > s->nlist_alloc)
+        {
+        size_t alloc = s->nlist_alloc ? s->nlist_alloc : 1;
+        while (head > alloc) alloc = ((size_t)(((float)alloc) * 1.125f)) + 1;
+        s->nlist = (unsigned int*)realloc(s->nlist, alloc * sizeof(unsigned int));
+        s->nlist_alloc = alloc;
+        }
+    }
+
+static int nl_distance_check(orc_system* s) /* NeighborList.cc:964-1040, fixed box: lambda = 1 */
+    {
+    for (unsigned int i = 0; i < s->N; i++)
+        {
+        const float old_rmin = s->rcut_max[as_uint(s->pos[i].w)];
+        const float rmax = old_rmin + s->r_buff;
+        const float delta_max = (rmax * 1.0f - old_rmin) / 2.0f;
+        const float maxsq = (delta_max > 0) ? delta_max * delta_max : 0;
+        f3 dx = {s->pos[i].x - 1.0f * s->last_pos[i].x, s->pos[i].y - 1.0f * s->last_pos[i].y,
+                 s->pos[i].z - 1.0f * s->last_pos[i].z};
+        dx = box_min_image(&s->box, dx);
+        if (dot3(dx) >= maxsq) return 1;
+        }
+    return 0;
+    }
+
+static int nl_needs_updating(orc_system* s, unsigned int ts) /* NeighborList.cc:1080-1163 (dist_check on) */
+    {
+    int result = 0;
+    if (s->last_checked == ts)
+        {
+        if (s->force_update) { s->force_update = 0; return 1; }
+        return s->last_check_result;
+        }
+    s->last_checked = ts;
+    if (!s->force_update && (ts < s->last_updated + s->every)) { s->last_check_result = 0; return 0; }
+    if (s->force_update)
+        {
+        result = 1; s->force_update = 0; s->forced += 1; s->last_updated = ts;
+        }
+    else
+        {
+        if (s->r_buff < 1e-6f) result = 1;
+        else result = nl_distance_check(s);
+        if (result) { s->last_updated = ts; s->updates += 1; }
+        }
+    s->last_check_result = result;
+    return result;
+    }
+
+/* NeighborListBinned::buildNlist (NeighborListBinned.cc:79-240), full storage, no body filter, no diameter shift */
+static int nl_build(orc_system* s, unsigned int ts)
+    {
+    if (cl_compute(s, ts)) return 1;
+    {
+    const float rmax = s->rcut_max_max + s->r_buff;
+    if ((s->box.periodic[0] && s->box.L.x <= rmax * 2.0f) || (s->box.periodic[1] && s->box.L.y <= rmax * 2.0f)
+        || (s->box.periodic[2] && s->box.L.z <= rmax * 2.0f))
+        {
+        snprintf(s->error, sizeof(s->error), "nlist: Simulation box is too small!");
+        return 1;
+        }
+    }
+    const unsigned int nt = s->ntypes;
+#pragma omp parallel for schedule(static) num_threads(s->nthreads)
+    for (int i = 0; i < (int)s->N; i++)
+        {
+        unsigned int cur_n_neigh = 0;
+        const f3 my_pos = {s->pos[i].x, s->pos[i].y, s->pos[i].z};
+        const unsigned int type_i = as_uint(s->pos[i].w);
+        const unsigned int Nmax_i = s->Nmax[type_i];
+        const unsigned int head_i = s->head[i];
+        f3 f = box_make_fraction(&s->box, my_pos);
+        int ib = (unsigned int)(f.x * s->dim[0]), jb = (unsigned int)(f.y * s->dim[1]), kb = (unsigned int)(f.z * s->dim[2]);
+        if (ib == (int)s->dim[0] && s->box.periodic[0]) ib = 0;
+        if (jb == (int)s->dim[1] && s->box.periodic[1]) jb = 0;
+        if (kb == (int)s->dim[2] && s->box.periodic[2]) kb = 0;
+        const unsigned int my_cell = ((unsigned int)kb * s->dim[1] + jb) * s->dim[0] + ib;
+        for (unsigned int a = 0; a < s->n_adj; a++)
+            {
+            const unsigned int neigh_cell = s->cell_adj[(size_t)my_cell * s->n_adj + a];
+            const unsigned int size = s->cell_size[neigh_cell];
+            for (unsigned int o = 0; o < size; o++)
+                {
+                const f4 c = s->xyzf[(size_t)neigh_cell * s->cl_Nmax + o];
+                const unsigned int j = as_uint(c.w);
+                const unsigned int type_j = as_uint(s->pos[j].w);
+                const float r_cut = s->r_cut[type_i * nt + type_j];
+                if ((i == (int)j) || (r_cut <= 0.0f)) continue;
+                f3 dx = {my_pos.x - c.x, my_pos.y - c.y, my_pos.z - c.z};
+                dx = box_min_image(&s->box, dx);
+                const float dr_sq = dot3(dx);
+                if (dr_sq <= (s->r_listsq[type_i * nt + type_j] + 0.0f))
+                    {
+                    if (cur_n_neigh < Nmax_i) s->nlist[head_i + cur_n_neigh] = j;
+                    else
+                        {
+#pragma omp critical
+                        if (cur_n_neigh + 1 > s->conditions[type_i]) s->conditions[type_i] = cur_n_neigh + 1;
+                        }
+                    cur_n_neigh++;
+                    }
+                }
+            }
+        s->n_neigh[i] = cur_n_neigh;
+        }
+    return 0;
+    }
+
+static int nl_compute(orc_system* s, unsigned int ts) /* NeighborList::compute, NeighborList.cc:201-253 */
+    {
+    if (!s->have_nlist) { snprintf(s->error, sizeof(s->error), "nlist not set up"); return 1; }
+    int should = s->nl_first || s->nl_last != ts;
+    s->nl_first = 0; s->nl_last = ts;
+    if (!should && !s->force_update) return 0;
+    if (s->force_update) nl_build_head_list(s);
+    if (nl_needs_updating(s, ts))
+        {
+        int overflowed;
+        do
+            {
+            if (nl_build(s, ts)) return 1;
+            overflowed = 0;
+            for (unsigned int t = 0; t < s->ntypes; t++) /* checkConditions, NeighborList.cc:1389-1405 */
+                if (s->conditions[t] > s->Nmax[t])
+                    {
+                    s->Nmax[t] = (s->conditions[t] > 8) ? (s->conditions[t] + 7) & ~7u : 8;
+                    overflowed = 1;
+                    }
+            if (overflowed)
+                {
+                nl_build_head_list(s);
+                memset(s->conditions, 0, sizeof(unsigned int) * s->ntypes);
+                }
+            } while (overflowed);
+        for (unsigned int i = 0; i < s->N; i++) /* setLastUpdatedPos, NeighborList.cc:1044-1066 */
+            {
+            f4 lp = {s->pos[i].x, s->pos[i].y, s->pos[i].z, 0.0f};
+            s->last_pos[i] = lp;
+            }
+        }
+    return 0;
+    }
+
+/* ---- PotentialPair<EvaluatorPairLJ>::computeForces (PotentialPair.h:309-522, EvaluatorPairLJ.h:137-158), full list ------ */
+static int compute_forces(orc_system* s, unsigned int ts)
+    {
+    if (nl_compute(s, ts)) return 1;
+    const unsigned int nt = s->ntypes, N = s->N;
+    const int compute_virial = s->compute_virial;
+    memset(s->net_force, 0, sizeof(f4) * N);
+    memset(s->net_virial, 0, sizeof(float) * 6 * (size_t)N);
+#pragma omp parallel for schedule(static) num_threads(s->nthreads)
+    for (int i = 0; i < (int)N; i++)
+        {
+        const f3 pi = {s->pos[i].x, s->pos[i].y, s->pos[i].z};
+        const unsigned int typei = as_uint(s->pos[i].w);
+        f3 fi = {0, 0, 0};
+        float pei = 0.0f, vxx = 0, vxy = 0, vxz = 0, vyy = 0, vyz = 0, vzz = 0;
+        const unsigned int head = s->head[i], size = s->n_neigh[i];
+        for (unsigned int k = 0; k < size; k++)
+            {
+            const unsigned int j = s->nlist[head + k];
+            f3 dx = {pi.x - s->pos[j].x, pi.y - s->pos[j].y, pi.z - s->pos[j].z};
+            const unsigned int typej = as_uint(s->pos[j].w);
+            dx = box_min_image(&s->box, dx);
+            const float rsq = dot3(dx);
+            const unsigned int tp = typei * nt + typej;
+            const float lj1 = s->lj1[tp], lj2 = s->lj2[tp], rcutsq = s->rcutsq[tp];
+            float ronsq = 0.0f;
+            int energy_shift = 0;
+            if (s->shift_mode == 2) ronsq = s->ronsq[tp];
+            if (s->shift_mode == 1) energy_shift = 1;
+            else if (s->shift_mode == 2 && ronsq > rcutsq) energy_shift = 1;
+            float force_divr = 0.0f, pair_eng = 0.0f;
+            if (rsq < rcutsq && lj1 != 0)
+                {
+                float r2inv = 1.0f / rsq;
+                float r6inv = r2inv * r2inv * r2inv;
+                force_divr = r2inv * r6inv * (12.0f * lj1 * r6inv - 6.0f * lj2);
+                pair_eng = r6inv * (lj1 * r6inv - lj2);
+                if (energy_shift)
+                    {
+                    float rcut2inv = 1.0f / rcutsq;
+                    float rcut6inv = rcut2inv * rcut2inv * rcut2inv;
+                    pair_eng -= rcut6inv * (lj1 * rcut6inv - lj2);
+                    }
+                if (s->shift_mode == 2 && rsq >= ronsq && rsq < rcutsq)
+                    {
+                    float old_pair_eng = pair_eng, old_force_divr = force_divr;
+                    float xplor_denom_inv = 1.0f / ((rcutsq - ronsq) * (rcutsq - ronsq) * (rcutsq - ronsq));
+                    float rsq_minus_r_cut_sq = rsq - rcutsq;
+                    float sw = rsq_minus_r_cut_sq * rsq_minus_r_cut_sq * (rcutsq + 2.0f * rsq - 3.0f * ronsq) * xplor_denom_inv;
+                    float ds_dr_divr = 12.0f * (rsq - ronsq) * rsq_minus_r_cut_sq * xplor_denom_inv;
+                    pair_eng = old_pair_eng * sw;
+                    force_divr = sw * old_force_divr - ds_dr_divr * old_pair_eng;
+                    }
+                {
+                float force_div2r = force_divr * 0.5f;
+                fi.x += dx.x * force_divr; fi.y += dx.y * force_divr; fi.z += dx.z * force_divr;
+                pei += pair_eng * 0.5f;
+                if (compute_virial)
+                    {
+                    vxx += force_div2r * dx.x * dx.x; vxy += force_div2r * dx.x * dx.y; vxz += force_div2r * dx.x * dx.z;
+                    vyy += force_div2r * dx.y * dx.y; vyz += force_div2r * dx.y * dx.z; vzz += force_div2r * dx.z * dx.z;
+                    }
+                }
+                }
+            }
+        s->net_force[i].x += fi.x; s->net_force[i].y += fi.y; s->net_force[i].z += fi.z; s->net_force[i].w += pei;
+        if (compute_virial)
+            {
+            s->net_virial[0 * (size_t)N + i] += vxx; s->net_virial[1 * (size_t)N + i] += vxy;
+            s->net_virial[2 * (size_t)N + i] += vxz; s->net_virial[3 * (size_t)N + i] += vyy;
+            s->net_virial[4 * (size_t)N + i] += vyz; s->net_virial[5 * (size_t)N + i] += vzz;
+            }
+        }
+    return 0;
+    }
+
+/* ---- TwoStepNVE / TwoStepLangevin (hoomd/md/TwoStepNVE.cc:77-122,255-300; TwoStepLangevin.cc:86-125,240-330) ------------ */
+static void step_one(orc_system* s)
+    {
+    const float dt = s->dt;
+    const int nve = s->method == 1;
+    for (unsigned int j = 0; j < s->N; j++)
+        {
+        if (nve && s->zero_force) s->accel[j].x = s->accel[j].y = s->accel[j].z = 0.0f;
+        float dx = s->vel[j].x * dt + (1.0f / 2.0f) * s->accel[j].x * dt * dt;
+        float dy = s->vel[j].y * dt + (1.0f / 2.0f) * s->accel[j].y * dt * dt;
+        float dz = s->vel[j].z * dt + (1.0f / 2.0f) * s->accel[j].z * dt * dt;
+        if (nve && s->limit)
+            {
+            float len = sqrtf(dx * dx + dy * dy + dz * dz);
+            if (len > s->limit_val)
+                {
+                dx = dx / len * s->limit_val;
+                dy = dy / len * s->limit_val;
+                dz = dz / len * s->limit_val;
+                }
+            }
+        s->pos[j].x += dx; s->pos[j].y += dy; s->pos[j].z += dz;
+        s->vel[j].x += (1.0f / 2.0f) * s->accel[j].x * dt;
+        s->vel[j].y += (1.0f / 2.0f) * s->accel[j].y * dt;
+        s->vel[j].z += (1.0f / 2.0f) * s->accel[j].z * dt;
+        box_wrap(&s->box, &s->pos[j], &s->image[j]);
+        }
+    }
+
+static void step_two(orc_system* s, unsigned int timestep)
+    {
+    const float dt = s->dt;
+    for (unsigned int j = 0; j < s->N; j++)
+        {
+        if (s->method == 2)
+            {
+            saru_t saru = saru_init(s->tag[j], timestep, s->seed);
+            float rx = saru_s(&saru, -1, 1), ry = saru_s(&saru, -1, 1), rz = saru_s(&saru, -1, 1);
+            float gamma = s->gamma[as_uint(s->pos[j].w)];
+            float coeff = sqrtf(6.0f * gamma * s->kT / dt);
+            if (s->noiseless_t) coeff = 0.0f;
+            float bd_fx = rx * coeff - gamma * s->vel[j].x;
+            float bd_fy = ry * coeff - gamma * s->vel[j].y;
+            float bd_fz = rz * coeff - gamma * s->vel[j].z;
+            float minv = 1.0f / s->vel[j].w;
+            s->accel[j].x = (s->net_force[j].x + bd_fx) * minv;
+            s->accel[j].y = (s->net_force[j].y + bd_fy) * minv;
+            s->accel[j].z = (s->net_force[j].z + bd_fz) * minv;
+            s->vel[j].x += (1.0f / 2.0f) * s->accel[j].x * dt;
+            s->vel[j].y += (1.0f / 2.0f) * s->accel[j].y * dt;
+            s->vel[j].z += (1.0f / 2.0f) * s->accel[j].z * dt;
+            }
+        else
+            {
+            if (s->zero_force) s->accel[j].x = s->accel[j].y = s->accel[j].z = 0.0f;
+            else
+                {
+                float minv = 1.0f / s->vel[j].w;
+                s->accel[j].x = s->net_force[j].x * minv;
+                s->accel[j].y = s->net_force[j].y * minv;
+                s->accel[j].z = s->net_force[j].z * minv;
+                }
+            s->vel[j].x += (1.0f / 2.0f) * s->accel[j].x * dt;
+            s->vel[j].y += (1.0f / 2.0f) * s->accel[j].y * dt;
+            s->vel[j].z += (1.0f / 2.0f) * s->accel[j].z * dt;
+            if (s->limit)
+                {
+                float vel = sqrtf(s->vel[j].x * s->vel[j].x + s->vel[j].y * s->vel[j].y + s->vel[j].z * s->vel[j].z);
+                if ((vel * dt) > s->limit_val)
+                    {
+                    s->vel[j].x = s->vel[j].x / vel * s->limit_val / dt;
+                    s->vel[j].y = s->vel[j].y / vel * s->limit_val / dt;
+                    s->vel[j].z = s->vel[j].z / vel * s->limit_val / dt;
+                    }
+                }
+            }
+        }
+    }
+
+/* ---- public API ---------------------------------------------------------------------------------------------------------- */
+orc_system* orc_create(unsigned int N, float Lx, float Ly, float Lz, unsigned int ntypes)
+    {
+    orc_system* s = (orc_system*)calloc(1, sizeof(orc_system));
+    s->N = N; s->ntypes = ntypes ? ntypes : 1; s->nthreads = 1;
+    box_init(&s->box, Lx, Ly, Lz);
+    s->pos = (f4*)calloc(N, sizeof(f4)); s->vel = (f4*)calloc(N, sizeof(f4)); s->net_force = (f4*)calloc(N, sizeof(f4));
+    s->last_pos = (f4*)calloc(N, sizeof(f4)); s->accel = (f3*)calloc(N, sizeof(f3)); s->image = (i3*)calloc(N, sizeof(i3));
+    s->tag = (unsigned int*)calloc(N, sizeof(unsigned int)); s->net_virial = (float*)calloc(6 * (size_t)N, sizeof(float));
+    for (unsigned int i = 0; i < N; i++) { s->tag[i] = i; s->vel[i].w = 1.0f; }
+    s->cl_first = s->cl_force = 1; s->nl_first = 1; s->force_update = 1;
+    return s;
+    }
+
+void orc_destroy(orc_system* s)
+    {
+    if (!s) return;
+    free(s->pos); free(s->vel); free(s->net_force); free(s->last_pos); free(s->accel); free(s->image); free(s->tag);
+    free(s->net_virial); free(s->cell_size); free(s->xyzf); free(s->cell_adj); free(s->r_cut); free(s->r_listsq);
+    free(s->rcut_max); free(s->Nmax); free(s->conditions); free(s->head); free(s->n_neigh); free(s->nlist);
+    free(s->lj1); free(s->lj2); free(s->rcutsq); free(s->ronsq); free(s->gamma);
+    free(s);
+    }
+
+const char* orc_last_error(orc_system* s) { return s->error; }
+void orc_set_threads(orc_system* s, int n) { s->nthreads = n > 0 ? n : 1; }
+
+void orc_set_particles(orc_system* s, const float* pos4, const float* vel4, const int* image3)
+    {
+    if (pos4) memcpy(s->pos, pos4, sizeof(f4) * s->N);
+    if (vel4) memcpy(s->vel, vel4, sizeof(f4) * s->N);
+    if (image3) memcpy(s->image, image3, sizeof(i3) * s->N);
+    s->force_update = 1; s->cl_force = 1;
+    }
+
+void orc_set_accel(orc_system* s, const float* accel3) { memcpy(s->accel, accel3, sizeof(f3) * s->N); s->accel_set = 1; }
+
+void orc_get_particles(orc_system* s, float* pos4, float* vel4, float* accel3, int* image3, unsigned int* tag)
+    {
+    if (pos4) memcpy(pos4, s->pos, sizeof(f4) * s->N);
+    if (vel4) memcpy(vel4, s->vel, sizeof(f4) * s->N);
+    if (accel3) memcpy(accel3, s->accel, sizeof(f3) * s->N);
+    if (image3) memcpy(image3, s->image, sizeof(i3) * s->N);
+    if (tag) memcpy(tag, s->tag, sizeof(unsigned int) * s->N);
+    }
+
+int orc_setup_lj(orc_system* s, float r_buff, unsigned int check_period, const float* rcut, const float* lj1,
+                 const float* lj2, const float* ron, int shift_mode)
+    {
+    const unsigned int nt = s->ntypes, n2 = nt * nt;
+    s->r_buff = r_buff; s->every = check_period; s->shift_mode = shift_mode;
+    s->r_cut = (float*)calloc(n2, 4); s->r_listsq = (float*)calloc(n2, 4); s->rcut_max = (float*)calloc(nt, 4);
+    s->lj1 = (float*)calloc(n2, 4); s->lj2 = (float*)calloc(n2, 4); s->rcutsq = (float*)calloc(n2, 4);
+    s->ronsq = (float*)calloc(n2, 4);
+    for (unsigned int k = 0; k < n2; k++)
+        {
+        s->r_cut[k] = rcut[k]; s->lj1[k] = lj1[k]; s->lj2[k] = lj2[k];
+        s->rcutsq[k] = rcut[k] * rcut[k];                 /* PotentialPair::setRcut, PotentialPair.h:237-250 */
+        s->ronsq[k] = ron ? ron[k] * ron[k] : 0.0f;
+        }
+    nl_update_rlist(s);
+    s->Nmax = (unsigned int*)calloc(nt, 4); s->conditions = (unsigned int*)calloc(nt, 4);
+    for (unsigned int t = 0; t < nt; t++) s->Nmax[t] = 8;  /* NeighborList.cc:92-98 */
+    s->head = (unsigned int*)calloc(s->N, 4); s->n_neigh = (unsigned int*)calloc(s->N, 4);
+    s->nlist_alloc = 8 * (size_t)s->N; s->nlist = (unsigned int*)calloc(s->nlist_alloc ? s->nlist_alloc : 1, 4);
+    cl_dimensions(s, s->rcut_max_max + s->r_buff);          /* NeighborListBinned.cc:56-76 */
+    s->have_nlist = 1; s->force_update = 1; s->cl_force = 1; s->nl_first = 1;
+    return 0;
+    }
+
+void orc_set_virial(orc_system* s, int on) { s->compute_virial = on; }
+int orc_setup_integrator(orc_system* s, float dt) { s->dt = dt; return 0; }
+int orc_add_nve(orc_system* s, int limit, float limit_val, int zero_force)
+    {
+    s->method = 1; s->limit = limit; s->limit_val = limit_val; s->zero_force = zero_force;
+    return 0;
+    }
+int orc_add_langevin(orc_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t)
+    {
+    s->method = 2; s->limit = 0; s->zero_force = 0; s->kT = kT; s->noiseless_t = noiseless_t;
+    seed = seed * 0x12345677u + 0x12345u; seed ^= (seed >> 16); seed *= 0x45679u; /* TwoStepLangevinBase.cc:54 */
+    s->seed = seed;
+    free(s->gamma);
+    s->gamma = (float*)calloc(s->ntypes, 4);
+    for (unsigned int t = 0; t < s->ntypes; t++) s->gamma[t] = gamma ? gamma[t] : 1.0f;
+    return 0;
+    }
+void orc_set_timestep(orc_system* s, unsigned int ts) { s->timestep = ts; }
+unsigned int orc_get_timestep(orc_system* s) { return s->timestep; }
+int orc_compute_nlist(orc_system* s, unsigned int ts) { return nl_compute(s, ts); }
+int orc_compute_forces(orc_system* s, unsigned int ts) { return compute_forces(s, ts); }
+
+static double now_s(void)
+    {
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return t.tv_sec + 1e-9 * t.tv_nsec;
+    }
+
+int orc_run(orc_system* s, unsigned int nsteps, double* elapsed_s) /* System.cc:484-599, IntegratorTwoStep.cc:96-161,336-398 */
+    {
+    if (!s->method) { snprintf(s->error, sizeof(s->error), "no integration method"); return 1; }
+    if (compute_forces(s, s->timestep)) return 1;
+    if (!s->accel_set)
+        {
+        for (unsigned int j = 0; j < s->N; j++) /* Integrator::computeAccelerations, Integrator.cc:222-256 */
+            {
+            float minv = 1.0f / s->vel[j].w;
+            s->accel[j].x = s->net_force[j].x * minv; s->accel[j].y = s->net_force[j].y * minv;
+            s->accel[j].z = s->net_force[j].z * minv;
+            }
+        s->accel_set = 1;
+        }
+    double t0 = now_s();
+    for (unsigned int k = 0; k < nsteps; k++)
+        {
+        step_one(s);
+        if (compute_forces(s, s->timestep + 1)) return 1;
+        step_two(s, s->timestep);
+        s->timestep++;
+        }
+    if (elapsed_s) *elapsed_s = now_s() - t0;
+    return 0;
+    }
+
+int orc_step_one(orc_system* s, unsigned int ts) { (void)ts; step_one(s); return 0; }
+int orc_step_two(orc_system* s, unsigned int ts, const float* net_force4)
+    {
+    if (net_force4) memcpy(s->net_force, net_force4, sizeof(f4) * s->N);
+    step_two(s, ts);
+    return 0;
+    }
+
+void orc_get_forces(orc_system* s, float* force4, float* virial6)
+    {
+    if (force4) memcpy(force4, s->net_force, sizeof(f4) * s->N);
+    if (virial6) memcpy(virial6, s->net_virial, sizeof(float) * 6 * (size_t)s->N);
+    }
+
+unsigned int orc_get_nlist_size(orc_system* s) { return (unsigned int)s->nlist_alloc; }
+void orc_get_nlist(orc_system* s, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist, unsigned int len)
+    {
+    if (n_neigh) memcpy(n_neigh, s->n_neigh, 4 * (size_t)s->N);
+    if (head) memcpy(head, s->head, 4 * (size_t)s->N);
+    if (nlist) memcpy(nlist, s->nlist, 4 * (len < s->nlist_alloc ? len : s->nlist_alloc));
+    }
+void orc_get_stats(orc_system* s, unsigned long long* out4)
+    {
+    out4[0] = s->updates; out4[1] = s->forced; out4[2] = s->dim[0]; out4[3] = s->Nmax ? s->Nmax[0] : 0;
+    }
+void orc_get_cell_dims(orc_system* s, unsigned int* out5)
+    {
+    out5[0] = s->dim[0]; out5[1] = s->dim[1]; out5[2] = s->dim[2]; out5[3] = s->cl_Nmax; out5[4] = s->n_adj;
+    }
+void orc_get_cell_list(orc_system* s, unsigned int* cell_size, float* xyzf4)
+    {
+    if (cell_size) memcpy(cell_size, s->cell_size, 4 * (size_t)s->ncells);
+    if (xyzf4) memcpy(xyzf4, s->xyzf, sizeof(f4) * (size_t)s->ncells * s->cl_Nmax);
+    }
+
+void orc_get_thermo(orc_system* s, double* out5) /* ComputeThermo.cc:195-380, FP32 properties */
+    {
+    double ke = 0.0, pe = 0.0, W = 0.0;
+    for (unsigned int j = 0; j < s->N; j++)
+        {
+        ke += (double)s->vel[j].w * ((double)s->vel[j].x * (double)s->vel[j].x + (double)s->vel[j].y * (double)s->vel[j].y
+                                     + (double)s->vel[j].z * (double)s->vel[j].z);
+        pe += (double)s->net_force[j].w;
+        }
+    ke *= 0.5f;
+    if (s->compute_virial)
+        {
+        double vxx = 0, vyy = 0, vzz = 0;
+        for (unsigned int j = 0; j < s->N; j++)
+            {
+            vxx += (double)s->net_virial[0 * (size_t)s->N + j];
+            vyy += (double)s->net_virial[3 * (size_t)s->N + j];
+            vzz += (double)s->net_virial[5 * (size_t)s->N + j];
+            }
+        W = (float)(1. / 3.) * (vxx + vyy + vzz);
+        }
+    {
+    const double ndof = 3.0 * s->N - 3.0;
+    const float volume = s->box.L.x * s->box.L.y * s->box.L.z;
+    out5[0] = (float)ke;
+    out5[1] = (float)pe;
+    out5[2] = (float)(2.0f / (float)ndof) * (float)ke;
+    out5[3] = s->compute_virial ? (float)((2.0 * ke / 3.0f + W) / volume) : 0.0;
+    out5[4] = ndof;
+    }
+    }

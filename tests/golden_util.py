@@ -1,0 +1,122 @@
+"""Shared checks of an implementation (oracle restatement or CUDA engine) against tests/golden/*.npz, the vectors
+generated from the unmodified reference by tests/golden/make_golden.py."""
+import os
+
+import numpy as np
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return np.load(os.path.join(GOLD, name + ".npz"))
+
+
+def flat_nlist(s):
+    n, h, nl = s.nlist()
+    return n, h, [nl[h[i]:h[i] + n[i]] for i in range(len(n))]
+
+
+def check_nlist(make, exact_order=True):
+    """make(pos, box, ntypes) -> system with setup_lj/compute_nlist/nlist.  Sorted-set equality (north_star bar); with
+    exact_order also entry order (CPU reference order)."""
+    g = load("nlist_random")
+    L = float(g["L"])
+    s = make(g["pos"], (L, L, L), 1)
+    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    s.compute_nlist(0)
+    _cmp_nlist(s, g, exact_order)
+    g = load("nlist_two_types")
+    L = float(g["L"])
+    s = make(g["pos"], (L, L, L), 2)
+    s.setup_lj(r_cut=g["rcut"], epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]], r_buff=0.3)
+    s.compute_nlist(0)
+    _cmp_nlist(s, g, exact_order)
+
+
+def _cmp_nlist(s, g, exact_order):
+    n, h, segs = flat_nlist(s)
+    assert np.array_equal(n, g["n_neigh"])
+    assert np.array_equal(h, g["head"])
+    off = np.concatenate([[0], np.cumsum(g["n_neigh"].astype(np.int64))]).astype(np.int64)
+    for i, seg in enumerate(segs):
+        want = g["nlist"][off[i]:off[i + 1]]
+        if exact_order:
+            assert np.array_equal(seg, want), i
+        else:
+            assert np.array_equal(np.sort(seg), np.sort(want)), i
+
+
+def check_forces(make, rtol, bit_exact=False):
+    g = load("liquid_forces")
+    L = float(g["L"])
+    for mode, name in ((0, "none"), (1, "shift"), (2, "xplor")):
+        s = make(g["pos"], (L, L, L), 1)
+        s.setup_lj(r_cut=3.0, r_buff=0.4, shift_mode=mode, r_on=2.0 if mode == 2 else None)
+        s.set_virial(True)
+        s.compute_forces(0)
+        f, v = s.forces()
+        fr, vr = g["force_" + name], g["virial_" + name]
+        if bit_exact:
+            assert np.array_equal(f.view(np.uint32), fr.view(np.uint32)), name
+            assert np.array_equal(v.view(np.uint32), vr.view(np.uint32)), name
+            continue
+        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+        assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, name
+        escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
+        assert (np.abs(fr[:, 3] - f[:, 3]) / escale).max() < rtol, name
+        vscale = np.maximum(np.abs(vr), np.abs(vr).mean())
+        assert (np.abs(vr - v) / vscale).max() < rtol, name
+        # totals: 1e-5 relative (north_star)
+        for a, b in ((fr[:, 3], f[:, 3]), (vr[0] + vr[3] + vr[5], v[0] + v[3] + v[5])):
+            sa, sb = a.astype(np.float64).sum(), b.astype(np.float64).sum()
+            assert abs(sa - sb) < 1e-5 * abs(sa), name
+
+
+def check_half_steps(make):
+    g = load("half_steps")
+    L = float(g["L"])
+    eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+    for limit, tag in ((None, "nolimit"), (0.01, "limit")):
+        s = make(g["pos"], (L, L, L), 1, vel=g["vel"])
+        s.setup_lj(r_cut=2.0, r_buff=0.3)
+        s.setup_integrator(0.005)
+        s.add_nve(limit=limit)
+        s.set_accel(g["accel"])
+        s.step_one(0)
+        p = s.particles()
+        assert eq(p["pos"], g["s1_pos_" + tag]) and eq(p["vel"], g["s1_vel_" + tag])
+        assert np.array_equal(p["image"], g["s1_image_" + tag])
+        s.step_two(0, g["fnet"])
+        p = s.particles()
+        assert eq(p["vel"], g["s2_vel_" + tag]) and eq(p["accel"], g["s2_accel_" + tag])
+    s = make(g["pos"], (L, L, L), 1, vel=g["vel"])
+    s.setup_lj(r_cut=2.0, r_buff=0.3)
+    s.setup_integrator(0.005)
+    s.add_langevin(1.2, 4)
+    s.step_two(123456, g["fnet"])
+    p = s.particles()
+    assert eq(p["vel"], g["lang_vel"]) and eq(p["accel"], g["lang_accel"])
+
+
+def check_trajectories(make, bit_exact, pos_tol=2e-4, vel_tol=2e-3):
+    for method in ("nve", "langevin"):
+        g = load("traj_" + method)
+        L = float(g["L"])
+        s = make(g["pos0"], (L, L, L), 1, vel=g["vel0"], image=g["image0"])
+        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        s.set_virial(True)
+        s.setup_integrator(0.005)
+        s.add_nve() if method == "nve" else s.add_langevin(1.2, 4)
+        s.run(40)
+        p = s.particles()
+        if bit_exact:
+            for k in ("pos", "vel", "accel", "image"):
+                assert np.array_equal(p[k].view(np.uint32), g[k].view(np.uint32)), (method, k)
+        else:
+            assert np.abs(p["pos"][:, :3] - g["pos"][:, :3]).max() < pos_tol, method
+            assert np.abs(p["vel"][:, :3] - g["vel"][:, :3]).max() < vel_tol, method
+            assert np.array_equal(p["image"], g["image"]), method
+        th = s.thermo()
+        want = g["thermo"]
+        for k, w in zip(("ke", "pe", "T", "P", "ndof"), want):
+            assert abs(th[k] - w) <= 2e-4 * abs(w), (method, k, th[k], w)

@@ -1,0 +1,131 @@
+"""CPU tests of the oracle (test infrastructure): the plain-C restatement oracle/oracle.c is pinned
+(a) against golden vectors generated from the unmodified reference (tests/golden/, make_golden.py),
+(b) against the reference's own known-answer constants (hoomd/md/test/test_lj_force.cc), and
+(c) when oracle/_ref/libhoomd_ref.so is present, bit for bit against the reference CPU classes on fresh inputs."""
+import numpy as np
+import pytest
+
+import golden_util as G
+from hoomd_b200 import workloads
+from oracle import oracle_c, ref
+
+pytestmark = pytest.mark.skipif(not oracle_c.available(), reason="oracle/_ref/liboracle.so not built (run build())")
+
+
+def make(pos, box, ntypes, vel=None, image=None):
+    return oracle_c.OracleSystem(pos, box, ntypes=ntypes, vel4=vel, image=image)
+
+
+def test_saru_golden():
+    g = G.load("saru")
+    for t, u, f in zip(g["triples"], g["u32"], g["f"]):
+        uu, ff = oracle_c.saru(int(t[0]), int(t[1]), int(t[2]), 4)
+        assert np.array_equal(uu, u) and np.array_equal(ff.view(np.uint32), f.view(np.uint32))
+
+
+def test_nlist_golden():
+    G.check_nlist(make, exact_order=True)
+
+
+def test_forces_golden_bit_exact():
+    G.check_forces(make, rtol=0.0, bit_exact=True)
+
+
+def test_half_steps_golden_bit_exact():
+    G.check_half_steps(make)
+
+
+def test_trajectories_golden_bit_exact():
+    G.check_trajectories(make, bit_exact=True)
+
+
+def test_lj_known_answers():
+    """hoomd/md/test/test_lj_force.cc:41-149 (3 particles on the x axis, r_cut 1.3, buffer 3.0)"""
+    pos = np.zeros((3, 4), np.float32)
+    pos[1, 0] = 2.0 ** (1.0 / 6.0)
+    pos[2, 0] = 2.0 * 2.0 ** (1.0 / 6.0)
+    tol = 1e-4
+    s = make(pos, (1000.0,) * 3, 1)
+    s.setup_lj(r_cut=1.3, epsilon=1.15, sigma=1.0, alpha=1.0, r_buff=3.0)
+    s.set_virial(True)
+    s.compute_forces(0)
+    f, v = s.forces()
+    assert np.abs(f[:, :3]).max() < 1e-3
+    np.testing.assert_allclose(f[:, 3], [-0.575, -1.15, -0.575], rtol=tol)
+    s = make(pos, (1000.0,) * 3, 1)
+    s.setup_lj(r_cut=1.3, epsilon=1.15, sigma=1.2, alpha=0.45, r_buff=3.0)
+    s.set_virial(True)
+    s.compute_forces(0)
+    f, v = s.forces()
+    np.testing.assert_allclose(f[[0, 2], 0], [-93.09822608552962, 93.09822608552962], rtol=tol)
+    np.testing.assert_allclose(f[:, 3], [3.5815110377468, 7.1630220754935, 3.581511037746], rtol=tol)
+    np.testing.assert_allclose((v[0] + v[3] + v[5]) / 3.0, [17.416537590989, 34.833075181975, 17.416537590989], rtol=tol)
+
+
+def test_lj_periodic_known_answers():
+    """hoomd/md/test/test_lj_force.cc:180-288 (lj_force_periodic_test): 6 particles, 3 types, each pair interacts
+    through a different face of the box (20 x 40 x 60)."""
+    pos = np.zeros((6, 4), np.float32)
+    xyz = [(-9.6, 0, 0), (9.6, 0, 0), (0, -19.6, 0), (0, 19.6, 0), (0, 0, -29.6), (0, 0, 29.6)]
+    types = np.array([0, 1, 2, 0, 2, 1], np.int32)
+    pos[:, :3] = xyz
+    pos[:, 3] = types.view(np.float32)
+    s = make(pos, (20.0, 40.0, 60.0), 3)
+    eps = np.array([[1.0, 2.0, 3.0], [2.0, 4.0, 5.0], [3.0, 5.0, 6.0]])  # "just change epsilon for the different pairs"
+    s.setup_lj(r_cut=1.3, epsilon=eps, sigma=0.5, alpha=0.45, r_buff=3.0)
+    s.set_virial(True)
+    s.compute_forces(0)
+    f, v = s.forces()
+    tol = 1e-4
+    W = (v[0] + v[3] + v[5]) / 3.0
+    np.testing.assert_allclose([f[0, 0], f[1, 0]], [-1.18299976747949, 1.18299976747949], rtol=tol)
+    np.testing.assert_allclose([f[2, 1], f[3, 1]], [-1.77449965121923, 1.77449965121923], rtol=tol)
+    np.testing.assert_allclose([f[4, 2], f[5, 2]], [-2.95749941869871, 2.95749941869871], rtol=tol)
+    np.testing.assert_allclose(W, [-0.15773330233059] * 2 + [-0.23659995349591] * 2 + [-0.39433325582651] * 2, rtol=tol)
+    off_axis = f[:, :3].copy()
+    off_axis[[0, 1], 0] = off_axis[[2, 3], 1] = off_axis[[4, 5], 2] = 0.0
+    assert np.abs(off_axis).max() < 1e-3
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+@pytest.mark.parametrize("method,ntypes", [("nve", 1), ("langevin", 1), ("langevin", 2)])
+def test_restatement_matches_reference_bitwise(method, ntypes):
+    """fresh inputs, longer run, including Nmax overflow and many rebuilds"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.4) ** (1.0 / 3.0), kT=1.0, seed=77, ntypes=ntypes,
+                                       type_fractions=[0.8, 0.2][:ntypes] if ntypes > 1 else None)
+    lj = dict(r_cut=2.5, r_buff=0.4)
+    if ntypes == 2:
+        lj = dict(r_cut=[[2.5, 2.0], [2.0, 2.2]], epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]],
+                  r_buff=0.3, shift_mode=1)
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (L, L, L), ntypes=ntypes, vel4=vel)
+        s.setup_lj(full=True, **lj)
+        s.setup_integrator(0.005)
+        s.add_nve() if method == "nve" else s.add_langevin(1.0, 7, gamma=[1.0, 2.0][:ntypes])
+        s.run(150)
+        outs.append((s.particles(), s.nlist(), s.nlist_stats()["updates"]))
+    (pa, na, ua), (pb, nb, ub) = outs
+    for k in ("pos", "vel", "accel", "image"):
+        assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
+    assert ua == ub and ua > 3
+    assert np.array_equal(na[0], nb[0]) and np.array_equal(na[1], nb[1])
+    for i in range(len(na[0])):
+        assert np.array_equal(na[2][na[1][i]:na[1][i] + na[0][i]], nb[2][nb[1][i]:nb[1][i] + nb[0][i]])
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+def test_cell_list_matches_reference():
+    pos = workloads.random_system(2000, 15.0, seed=3)
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (15.0,) * 3)
+        s.setup_lj(r_cut=3.0, r_buff=0.4, full=True)
+        s.compute_nlist(0)
+        outs.append(s.cell_list())
+    a, b = outs
+    assert np.array_equal(a["dim"], b["dim"]) and a["Nmax"] == b["Nmax"]
+    assert np.array_equal(a["cell_size"], b["cell_size"])
+    for c in range(len(a["cell_size"])):
+        n = a["cell_size"][c]
+        assert np.array_equal(a["xyzf"][c, :n].view(np.uint32), b["xyzf"][c, :n].view(np.uint32))
