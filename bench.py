@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""Benchmark of the MD hot path (BASELINE.json metric: timesteps/sec for LJ liquid).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload lj64k|lj1m|ka256k|lj8m]
+
+One bench "step" = one System::run of --md-steps MD timesteps (NVE, LJ r_cut 3.0, r_buff 0.4, dt 0.005) of the synthetic
+LJ liquid (N = 64,000, rho = 0.2, lattice start, Langevin-equilibrated with this engine).
+`value` = MD timesteps / second with the state resident in HBM (CUDA events on the engine stream);
+`e2e` = the same through the public host-buffer API (hoomd_b200.System: set_particles H2D, run, particles()+thermo D2H).
+--impl reference times the reference's own CPU classes (oracle/_ref, HOOMD-blue 2.3.0 SINGLE_PRECISION, serial: the MD
+CPU path has no threading and there is no MPI on the box) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (n_side of the sc lattice, rho, kT, description)
+    "lj64k": (40, 0.2, 1.2, "LJ liquid 64,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
+    "lj1m": (100, 0.2, 1.2, "LJ liquid 1,000,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
+    "lj8m": (200, 0.2, 1.2, "LJ liquid 8,000,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
+}
+BYTES_PER_PARTICLE_STEP = 420.0   # SURVEY 8(d) planning figure (NVE, fused net force, amortised rebuild)
+FLOPS_PER_PARTICLE_STEP = 1800.0
+PAIR_BYTES_PER_PARTICLE = 172.0   # pair kernel: pos_i 16 + n_neigh 4 + head 4 + nlist 4*32.9 + force 16
+PAIR_FLOPS_PER_PARTICLE = 1316.0  # 40 flop x 32.9 neighbors
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._loop, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, smax, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                smax.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+EQUIL_STEPS = None  # --equil-steps override (profiling runs)
+USE_GRAPH = int(os.environ.get("HOOMD_B200_USE_GRAPH", "2"))  # 0 host-driven, 1 plain graph, 2 conditional graph
+
+
+def make_state(workload, rank=0):
+    """Lattice start + Langevin equilibration ON THE GPU ENGINE (not timed); returns host arrays + box length."""
+    import hoomd_b200
+    from hoomd_b200 import workloads
+    n_side, rho, kT, _ = WORKLOADS[workload]
+    pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42 + rank)
+    s = hoomd_b200.System(pos, (L, L, L), vel4=vel)
+    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    s.setup_integrator(0.005)
+    s.add_langevin(kT, 42)
+    s.set_sorter(300)
+    s.set_tuning(use_graph=USE_GRAPH)
+    s.run(EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 3000))
+    p = s.particles()
+    s.close()
+    return p, L
+
+
+def new_system(state, L, device=0):
+    import hoomd_b200
+    s = hoomd_b200.System(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], device=device)
+    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    s.setup_integrator(0.005)
+    s.add_nve()
+    s.set_sorter(300)  # hoomd.update.sort default period on the GPU (hoomd/update.py:258-263)
+    s.set_tuning(use_graph=USE_GRAPH)
+    return s
+
+
+def run_reference(args):
+    """reference arm: the reference's own CPU classes on the box's host cores, bounded sample per step."""
+    from oracle import ref, oracle_c
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    workload = args.workload
+    n_side, rho, kT, desc = WORKLOADS[workload]
+    from hoomd_b200 import workloads
+    md_steps = args.ref_md_steps
+    have_gpu = False
+    try:
+        import torch
+        have_gpu = torch.cuda.is_available()
+    except Exception:
+        pass
+    if have_gpu:
+        state, L = make_state(workload)  # same equilibrated liquid as the CUDA arm (equilibration is not timed)
+    else:
+        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
+        state = dict(pos=pos, vel=vel, image=np.zeros((len(pos), 3), np.int32))
+    if ref.available():
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"])
+        s.setup_lj(r_cut=3.0, r_buff=0.4, full=False)  # the CPU md.pair.lj default: half list + Newton's third law
+        kind, cores = "reference", 1
+        s.set_sorter(100)  # hoomd.update.sort default period on the CPU
+    else:
+        cores = os.cpu_count() or 1
+        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores)
+        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        kind = "port"
+    s.setup_integrator(0.005)
+    s.add_nve()
+    for _ in range(args.warmup):
+        s.run(md_steps)
+    t = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        s.run(md_steps)
+        t.append(time.perf_counter() - t0)
+    total = sum(t)
+    tps = md_steps * args.steps / total
+    N = len(state["pos"])
+    sample = "%d MD steps per bench step x %d steps of the %d-particle workload, %s" % (
+        md_steps, args.steps, N, "HOOMD-blue 2.3.0 CPU classes (oracle/_ref), half neighbor list, 1 core (no MPI on the box)"
+        if kind == "reference" else "C restatement (oracle/oracle.c) with OpenMP")
+    line = {"impl": "reference", "metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "md_steps_per_step": md_steps, "N": N},
+            "particle_steps_per_sec": tps * N,
+            "cpu_baseline": {"value": tps, "unit": "timesteps/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": tps, "unit": "timesteps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def cpu_baseline(state, L, budget_s=15.0):
+    """bounded sample of the same workload on the host cores with the reference's own CPU classes"""
+    from oracle import ref, oracle_c
+    N = len(state["pos"])
+    if ref.available():
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"])
+        s.setup_lj(r_cut=3.0, r_buff=0.4, full=False)
+        kind, cores = "reference", 1
+    elif oracle_c.available():
+        cores = os.cpu_count() or 1
+        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores)
+        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        kind = "port"
+    else:
+        return None
+    s.setup_integrator(0.005)
+    s.add_nve()
+    t0 = time.perf_counter()
+    s.run(5)
+    per = (time.perf_counter() - t0) / 5
+    n = max(5, min(2000, int(budget_s / max(per, 1e-6))))
+    t0 = time.perf_counter()
+    s.run(n)
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "timesteps/s", "cores": cores, "kind": kind,
+            "sample": "%d NVE steps of the same %d-particle state (%.1f s), %s" % (
+                n, N, dt, "HOOMD-blue 2.3.0 CPU classes built from /root/reference (oracle/_ref), half list, serial"
+                if kind == "reference" else "C restatement oracle/oracle.c, OpenMP")}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="lj64k", choices=sorted(WORKLOADS))
+    ap.add_argument("--md-steps", type=int, default=0, help="MD timesteps per bench step (0 = by workload)")
+    ap.add_argument("--ref-md-steps", type=int, default=20)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--equil-steps", type=int, default=None)
+    args = ap.parse_args()
+    global EQUIL_STEPS
+    EQUIL_STEPS = args.equil_steps
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- hoomd_b200 has no CPU fallback")
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    workload = args.workload
+    n_side, rho, kT, desc = WORKLOADS[workload]
+    N = n_side ** 3
+    md_steps = args.md_steps or (2000 if N <= 100000 else (400 if N <= 2000000 else 100))
+    hbm_peak, peak_src = peaks()
+
+    state, L = make_state(workload, rank)
+    s = new_system(state, L, device=local_rank)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ---------------------------------------------------------------------------------
+    for _ in range(args.warmup):
+        s.run(md_steps)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    gpu_ms, launches = [], 0
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.fill_(1)               # evict L2 between timed iterations (the 15 MB working set re-warms in < 1 MD step)
+        torch.cuda.synchronize()
+        _, ms = s.run(md_steps)
+        gpu_ms.append(ms)
+        launches += s.stats()["kernels_last_run"]
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    total_ms = sum(gpu_ms)
+    if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    tps_rank = md_steps * args.steps / (total_ms * 1e-3)
+    # N > 1 (until the domain-decomposed path lands): independent replicas, aggregate particle-steps
+    tps = tps_rank
+    stats = s.stats()
+
+    # ---- dominant kernel: pair force, CUDA events on the engine stream --------------------------------------------
+    pair_ms = s.time_kernel(0, 200)
+    nlist_ms = s.time_kernel(1, 20)
+    n_neigh = s.nlist()[0]
+    nbar = float(n_neigh.mean())
+    pair_bytes = (16 + 4 + 4 + 4 * nbar + 16) * N
+    achieved = pair_bytes / (pair_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_pair_forces<EvaluatorPairLJ>", "achieved": achieved, "peak": hbm_peak,
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "kernel_ms": pair_ms, "algorithmic_bytes_per_launch": pair_bytes, "mean_neighbors": nbar,
+                "fp32_tflops": 40.0 * nbar * N / (pair_ms * 1e-3) / 1e12,
+                "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12,
+                "nlist_rebuild_ms": nlist_ms,
+                "step_hbm_frac": BYTES_PER_PARTICLE_STEP * N * tps_rank / (hbm_peak * 1e9),
+                "note": "working set at 64k is L2-resident (15 MB < 126 MB L2): the step is launch/latency bound, "
+                        "the HBM fraction is low by construction (SURVEY 8d)"}
+
+    # ---- end to end through the host-buffer API ----------------------------------------------------------------------
+    host = s.particles()
+    e2e_t, h2d, d2h = [], 0, 0
+    for it in range(max(1, args.steps)):
+        t0 = time.perf_counter()
+        s.set_particles(host["pos"], host["vel"], host["image"])         # H2D of the step's inputs
+        s.run(md_steps)
+        host = s.particles()                                              # D2H of the step's result
+        th = s.thermo()
+        e2e_t.append(time.perf_counter() - t0)
+        h2d = host["pos"].nbytes + host["vel"].nbytes + host["image"].nbytes
+        d2h = sum(host[k].nbytes for k in host) + 5 * 8
+    e2e_tps = md_steps * len(e2e_t) / sum(e2e_t)
+    if world > 1:
+        t = torch.tensor([sum(e2e_t)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_tps = md_steps * len(e2e_t) / float(t.item())
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(state, L)
+
+    if rank == 0:
+        line = {"metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak" if world > 1 else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": desc, "N": N, "md_steps_per_step": md_steps,
+                           "parallelism": "1 GPU" if world == 1 else "%d independent replicas (one per GPU)" % world,
+                           "l2": "L2 flushed (256 MiB write) between timed iterations; within an iteration the 64k "
+                                 "working set is L2-resident, which is the workload",
+                           "sorter_period": 300, "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels", 2: "CUDA graph, conditional IF node"}[USE_GRAPH], "nlist": {"r_buff": 0.4, "check_period": 1,
+                                                           "rebuilds_total": stats["updates"] + stats["forced"],
+                                                           "Nmax": stats["Nmax0"]}},
+                "particle_steps_per_sec": tps * N * world,
+                "wall_tps": md_steps * args.steps / t_wall,
+                "gpu_launches": launches,
+                "clocks": clocks,
+                "roofline": roofline,
+                "e2e": {"value": e2e_tps, "unit": "timesteps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "thermo_T": th["T"]},
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+    s.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

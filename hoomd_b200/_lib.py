@@ -78,7 +78,7 @@ SYMBOLS = [
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
     "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
     "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
-    "b200_sys_get_thermo",
+    "b200_sys_get_thermo", "b200_sys_time_kernel",
 ]
 
 _lib = None
@@ -155,6 +155,7 @@ def lib():
     L.b200_sys_get_nlist.argtypes = [vp, vp, vp, vp, C.c_uint]
     L.b200_sys_get_stats.argtypes = [vp, C.POINTER(C.c_ulonglong)]
     L.b200_sys_get_thermo.argtypes = [vp, c_double_p]
+    L.b200_sys_time_kernel.argtypes = [vp, C.c_int, C.c_uint, c_double_p]
     _lib = L
     return L
 

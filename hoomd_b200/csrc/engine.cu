@@ -1088,6 +1088,42 @@ int b200_sys_get_stats(b200_system* s, unsigned long long* out8)
     return 0;
     }
 
+int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* avg_ms)
+    {
+    SYS_TRY(s)
+    if (!s->have_nlist) throw std::runtime_error("nlist: not set up");
+    if (iters == 0) iters = 1;
+    cudaEvent_t e0, e1;
+    CUDA_OK(cudaEventCreate(&e0));
+    CUDA_OK(cudaEventCreate(&e1));
+    b200_pair_args pa;
+    pair_args(s, pa);
+    b200_cell_list_args ca;
+    cell_list_args(s, ca);
+    b200_nlist_args na;
+    nlist_args(s, na);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    CUDA_OK(cudaEventRecord(e0, s->stream));
+    for (unsigned int k = 0; k < iters; k++)
+        {
+        if (which == 0)
+            CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
+        else
+            {
+            CUDA_OK(launch_cell_list(&ca, nullptr, s->stream));
+            CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
+            }
+        }
+    CUDA_OK(cudaEventRecord(e1, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    float ms = 0.0f;
+    CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *avg_ms = (double)ms / iters;
+    SYS_CATCH(s)
+    }
+
 int b200_sys_get_thermo(b200_system* s, double* out5)
     {
     SYS_TRY(s)

@@ -153,6 +153,12 @@ class System:
         return dict(updates=int(out[0]), forced=int(out[1]), overflows=int(out[2]), kernels_last_run=int(out[3]),
                     dim=(int(out[4]), int(out[5]), int(out[6])), Nmax0=int(out[7]))
 
+    def time_kernel(self, which, iters=20):
+        """average CUDA-event milliseconds per launch of the pair kernel (which=0) or the nlist rebuild (which=1)"""
+        ms = C.c_double(0)
+        self._check(_lib.lib().b200_sys_time_kernel(self.h, int(which), int(iters), C.byref(ms)))
+        return ms.value
+
     def thermo(self):
         out = np.zeros(5, np.float64)
         self._check(_lib.lib().b200_sys_get_thermo(self.h, out.ctypes.data_as(C.POINTER(C.c_double))))
