@@ -215,6 +215,7 @@ def main():
     ap.add_argument("--ref-md-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--equil-steps", type=int, default=None)
+    ap.add_argument("--no-flush", action="store_true", help="profiling only: skip the L2 flush between timed iterations")
     args = ap.parse_args()
     global EQUIL_STEPS
     EQUIL_STEPS = args.equil_steps
@@ -259,8 +260,9 @@ def main():
     gpu_ms, launches = [], 0
     t_wall0 = time.perf_counter()
     for _ in range(args.steps):
-        flush.fill_(1)               # evict L2 between timed iterations (the 15 MB working set re-warms in < 1 MD step)
-        torch.cuda.synchronize()
+        if not args.no_flush:
+            flush.fill_(1)           # evict L2 between timed iterations (the 15 MB working set re-warms in < 1 MD step)
+            torch.cuda.synchronize()
         _, ms = s.run(md_steps)
         gpu_ms.append(ms)
         launches += s.stats()["kernels_last_run"]
@@ -329,7 +331,7 @@ def main():
                                                            "Nmax": stats["Nmax0"]}},
                 "particle_steps_per_sec": tps * N * world,
                 "wall_tps": md_steps * args.steps / t_wall,
-                "gpu_launches": launches,
+                "gpu_launches": launches, "ms_runs": gpu_ms, "nlist_overflows": stats["overflows"],
                 "clocks": clocks,
                 "roofline": roofline,
                 "e2e": {"value": e2e_tps, "unit": "timesteps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

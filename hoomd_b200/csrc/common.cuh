@@ -70,9 +70,9 @@ __device__ __forceinline__ float3 min_image_exact(float3 w, const Box& box)
 // wider than 2*r_list, hoomd/md/NeighborListBinned.cc:109-115).
 __device__ __forceinline__ float3 min_image_fast(float3 w, const Box& box)
     {
-    if (box.periodic.z) w.z = __fmaf_rn(-box.L.z, rintf(w.z * box.Linv.z), w.z);
-    if (box.periodic.y) w.y = __fmaf_rn(-box.L.y, rintf(w.y * box.Linv.y), w.y);
-    if (box.periodic.x) w.x = __fmaf_rn(-box.L.x, rintf(w.x * box.Linv.x), w.x);
+    if (box.periodic.z) w.z = __fmaf_rn(-box.L.z, rintf(__fmul_rn(w.z, box.Linv.z)), w.z);
+    if (box.periodic.y) w.y = __fmaf_rn(-box.L.y, rintf(__fmul_rn(w.y, box.Linv.y)), w.y);
+    if (box.periodic.x) w.x = __fmaf_rn(-box.L.x, rintf(__fmul_rn(w.x, box.Linv.x)), w.x);
     return w;
     }
 

@@ -511,7 +511,7 @@ static void sorter_update(b200_system* s)
         CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, nullptr, 0, &need,
                                                (const float*)s->pos.p, N, &s->box, s->sorter_grid, s->stream));
         s->sort_temp.alloc(need + 16);
-        s->pos_alt.alloc(N); s->vel_alt.alloc(N); s->net_force_alt.alloc(N);
+        s->vel_alt.alloc(N); s->net_force_alt.alloc(N);
         s->accel_alt.alloc(N); s->image_alt.alloc(N); s->tag_alt.alloc(N);
         }
     CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, s->sort_temp.p,
@@ -542,28 +542,56 @@ static void sorter_update(b200_system* s)
 namespace b200
 {
 // ---- device-driven stepping -----------------------------------------------------------------------------------------------
-// One graph = one IntegratorTwoStep::update(ts) (hoomd/md/IntegratorTwoStep.cc:96-161):
-//   k_fused_step_one -> k_decide -> [IF need_rebuild: cell list (4 kernels) -> nlist -> k_post_rebuild] -> pair -> step two
-// mode 2 puts the bracket into a conditional IF node (CUDA >= 12.4); mode 1 launches the rebuild kernels every step and
+// A chunk of n IntegratorTwoStep::update() calls (hoomd/md/IntegratorTwoStep.cc:96-161) runs as
+//   prologue : k_fused_step_one(ts) + k_decide                                   (2 launches per chunk)
+//   graph    : [k_graph_pre] -> IF{rebuild from A} -> k_md_step(A->B) -> IF{rebuild from B} -> k_md_step(B->A)
+// replayed ceil(n/2) times.  k_md_step = force(ts+1) + step two(ts) + step one(ts+1) + distance check + rebuild decision
+// in ONE launch (see fused_step.cu); positions ping-pong between pos (A) and pos_alt (B) and always end in A.
+// mode 2 brackets the rebuild in conditional IF nodes (CUDA >= 12.4); mode 1 launches the rebuild kernels every step and
 // lets them return at once on !need_rebuild (the `enable` pointer).
-static void enqueue_rebuild(b200_system* s, const unsigned int* enable)
+static void enqueue_rebuild(b200_system* s, const unsigned int* enable, const float4* pos)
     {
     b200_cell_list_args ca;
     cell_list_args(s, ca);
+    ca.d_pos = (const float*)pos;
     CUDA_OK(launch_cell_list(&ca, enable, s->stream));
     b200_nlist_args na;
     nlist_args(s, na);
+    na.d_pos = (const float*)pos;
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
     CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
     }
 
-static void enqueue_forces_and_step_two(b200_system* s, const FusedStepArgs& fa)
+static void enqueue_md_step(b200_system* s, const FusedStepArgs& fa, int phase, unsigned long long handle, int use_cond)
     {
     b200_pair_args pa;
     pair_args(s, pa);
-    CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
-    CUDA_OK(launch_fused_step_two(fa, s->d_state.p, s->stream));
+    const float4* pin = phase == 0 ? s->pos.p : s->pos_alt.p;
+    float4* pout = phase == 0 ? s->pos_alt.p : s->pos.p;
+    CUDA_OK(launch_md_step_lj(pa, (const float*)s->d_params.p, fa, pin, pout, phase == 1, s->d_state.p, handle, use_cond,
+                              s->stream));
     }
+
+#if (CUDART_VERSION >= 12040)
+// splice a conditional IF node in after what has been captured so far on the stream; returns its body graph
+static cudaGraph_t add_if_node(b200_system* s, cudaGraph_t graph, cudaGraphConditionalHandle handle)
+    {
+    cudaStreamCaptureStatus status;
+    const cudaGraphNode_t* deps = nullptr;
+    size_t ndeps = 0;
+    cudaGraph_t cap_graph = nullptr;
+    CUDA_OK(cudaStreamGetCaptureInfo_v2(s->stream, &status, nullptr, &cap_graph, &deps, &ndeps));
+    cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+    np.type = cudaGraphNodeTypeConditional;
+    np.conditional.handle = handle;
+    np.conditional.type = cudaGraphCondTypeIf;
+    np.conditional.size = 1;
+    cudaGraphNode_t cond_node;
+    CUDA_OK(cudaGraphAddNode(&cond_node, graph, deps, ndeps, &np));
+    CUDA_OK(cudaStreamUpdateCaptureDependencies(s->stream, &cond_node, 1, cudaStreamSetCaptureDependencies));
+    return np.conditional.phGraph_out[0];
+    }
+#endif
 
 static bool build_graph_conditional(b200_system* s)
     {
@@ -577,35 +605,28 @@ static bool build_graph_conditional(b200_system* s)
     try
         {
         CUDA_OK(cudaGraphCreate(&graph, 0));
-        cudaGraphConditionalHandle handle;
-        CUDA_OK(cudaGraphConditionalHandleCreate(&handle, graph, 0, cudaGraphCondAssignDefault));
+        cudaGraphConditionalHandle h0, h1;
+        CUDA_OK(cudaGraphConditionalHandleCreate(&h0, graph, 0, cudaGraphCondAssignDefault));
+        CUDA_OK(cudaGraphConditionalHandleCreate(&h1, graph, 0, cudaGraphCondAssignDefault));
         CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
         capturing = true;
-        CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
-        CUDA_OK(launch_decide(s->d_state.p, (unsigned long long)handle, 1, s->stream));
-        // splice the conditional node in after what has been captured so far
-        cudaStreamCaptureStatus status;
-        const cudaGraphNode_t* deps = nullptr;
-        size_t ndeps = 0;
-        cudaGraph_t cap_graph = nullptr;
-        CUDA_OK(cudaStreamGetCaptureInfo_v2(s->stream, &status, nullptr, &cap_graph, &deps, &ndeps));
-        cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
-        np.type = cudaGraphNodeTypeConditional;
-        np.conditional.handle = handle;
-        np.conditional.type = cudaGraphCondTypeIf;
-        np.conditional.size = 1;
-        cudaGraphNode_t cond_node;
-        CUDA_OK(cudaGraphAddNode(&cond_node, graph, deps, ndeps, &np));
-        cudaGraph_t body = np.conditional.phGraph_out[0];
-        CUDA_OK(cudaStreamUpdateCaptureDependencies(s->stream, &cond_node, 1, cudaStreamSetCaptureDependencies));
-        enqueue_forces_and_step_two(s, fa);
+        CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h0, s->stream));
+        cudaGraph_t body0 = add_if_node(s, graph, h0);
+        enqueue_md_step(s, fa, 0, (unsigned long long)h1, 1);
+        cudaGraph_t body1 = add_if_node(s, graph, h1);
+        enqueue_md_step(s, fa, 1, 0ull, 0);
         cudaGraph_t out = nullptr;
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
-        // body of the IF node
-        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        // bodies of the IF nodes
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body0, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
         capturing = true;
-        enqueue_rebuild(s, enable);
+        enqueue_rebuild(s, enable, s->pos.p);
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body1, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        enqueue_rebuild(s, enable, s->pos_alt.p);
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
         CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
@@ -640,10 +661,10 @@ static void build_graph_plain(b200_system* s)
     CUDA_OK(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
     try
         {
-        CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
-        CUDA_OK(launch_decide(s->d_state.p, 0ull, 0, s->stream));
-        enqueue_rebuild(s, enable);
-        enqueue_forces_and_step_two(s, fa);
+        enqueue_rebuild(s, enable, s->pos.p);
+        enqueue_md_step(s, fa, 0, 0ull, 0);
+        enqueue_rebuild(s, enable, s->pos_alt.p);
+        enqueue_md_step(s, fa, 1, 0ull, 0);
         }
     catch (...)
         {
@@ -699,8 +720,14 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     st.every = s->every;
     st.r_buff_tiny = (s->r_buff < 1e-6f) ? 1u : 0u;
     st.ntypes = s->ntypes;
+    st.steps_left = chunk;
     CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
-    for (unsigned int k = 0; k < chunk; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+    FusedStepArgs fa;
+    fused_args(s, fa);
+    CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+    CUDA_OK(launch_decide(s->d_state.p, s->stream));
+    const unsigned int nreplay = (chunk + 1) / 2;
+    for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
     if (!st.overflow) cell_list_check_conditions(s);
@@ -739,7 +766,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         return;
         }
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    s->kernels_last_run += s->graph_uses_cond ? (4ull * chunk + 6ull * rebuilds) : 10ull * chunk;
+    s->kernels_last_run += 2ull + (s->graph_uses_cond ? (3ull * nreplay + 6ull * rebuilds) : 14ull * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
     s->num_updates += st.num_updates;
@@ -780,6 +807,7 @@ b200_system* b200_sys_create(unsigned int N, const b200_box* box, unsigned int n
         s->box = *box;
         s->pos.alloc(N); s->vel.alloc(N); s->net_force.alloc(N); s->accel.alloc(N); s->image.alloc(N);
         s->tag.alloc(N); s->rtag.alloc(N); s->last_pos.alloc(N);
+        s->pos_alt.alloc(N); // ping-pong partner of pos (device-driven stepping) and the sorter's gather target
         s->virial_pitch = N + (16 - (N & 15)); // GPUArray 2D pitch rule (hoomd/GPUArray.h:424-425)
         s->net_virial.alloc(6 * (size_t)s->virial_pitch);
         std::vector<unsigned int> ident(N);

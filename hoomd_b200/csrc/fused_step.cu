@@ -1,13 +1,14 @@
 // Kernels of the device-driven step loop (engine only; group = all particles).
 //   k_fused_step_one : IntegrationMethodTwoStep::integrateStepOne + NeighborList::distanceCheck in one pass over the
-//                      particles (the check re-uses the freshly written position: +16 B/particle instead of a second
-//                      32 B/particle kernel, hoomd/md/NeighborListGPU.cu:32-82)
+//                      particles -- the prologue of a chunk (the check re-uses the freshly written position: +16 B/particle
+//                      instead of a second 32 B/particle kernel, hoomd/md/NeighborListGPU.cu:32-82)
 //   k_decide         : NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163) on the device, 1 thread
+//   k_md_step        : the whole MD step in one launch (force + step two + next step one + check + decision)
 //   k_post_rebuild   : overflow detection after a rebuild (hoomd/md/NeighborList.cc:1389-1405 needs the host: sticky flag)
-//   k_fused_step_two : integrateStepTwo with the timestep read from the control block
-// Per-particle arithmetic is the shared body of integrate_body.cuh => bit-identical to the driver kernels.
+// Per-particle arithmetic is the shared body of integrate_body.cuh / pair_body.cuh => bit-identical to the driver kernels.
 #include "common.cuh"
 #include "integrate_body.cuh"
+#include "pair_body.cuh"
 #include "kernels.h"
 
 namespace b200
@@ -45,9 +46,9 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
     if (__any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) st->moved = 1u; // benign same-value race
     }
 
-__global__ void k_decide(StepState* st, cudaGraphConditionalHandle handle, int use_cond)
+// NeighborList::needsUpdating(ts+1) for the force evaluation that follows (update(ts) computes forces at ts+1)
+__device__ __forceinline__ void decide_body(StepState* st)
     {
-    // update(ts): forces are computed at ts+1 => needsUpdating(ts+1)
     const unsigned int ts1 = st->timestep + 1u;
     bool result;
     if (st->force_update)
@@ -61,7 +62,7 @@ __global__ void k_decide(StepState* st, cudaGraphConditionalHandle handle, int u
         result = false;
     else
         {
-        result = st->r_buff_tiny || st->moved;
+        result = st->r_buff_tiny || *((volatile unsigned int*)&st->moved);
         if (result)
             {
             st->last_updated = ts1;
@@ -72,8 +73,18 @@ __global__ void k_decide(StepState* st, cudaGraphConditionalHandle handle, int u
     st->need_rebuild = result ? 1u : 0u;
     st->ts_step_two = st->timestep;
     st->timestep = ts1;
+    }
+
+__global__ void k_decide(StepState* st)
+    {
+    decide_body(st);
+    }
+
+// first node of every replay of the step graph: hand the pending rebuild decision to the first conditional node
+__global__ void k_graph_pre(StepState* st, cudaGraphConditionalHandle handle)
+    {
 #if (CUDART_VERSION >= 12040)
-    if (use_cond) cudaGraphSetConditional(handle, result ? 1u : 0u);
+    cudaGraphSetConditional(handle, (st->steps_left && st->need_rebuild) ? 1u : 0u);
 #endif
     }
 
@@ -87,31 +98,134 @@ __global__ void k_post_rebuild(StepState* st, unsigned int* __restrict__ conditi
         }
     }
 
-__global__ void __launch_bounds__(256) k_fused_step_two(float4* __restrict__ vel, float3s* __restrict__ accel,
-                                                        const float4* __restrict__ pos,
-                                                        const float4* __restrict__ net_force,
-                                                        const unsigned int* __restrict__ tag,
-                                                        const float* __restrict__ gamma_tab, unsigned int N, float dt,
-                                                        int method, bool limit, float limit_val, bool zero_force,
-                                                        float kT, unsigned int seed, bool noiseless_t,
-                                                        const StepState* __restrict__ st)
+// ---- the single-kernel MD step -------------------------------------------------------------------------------------------
+// One launch = PotentialPair::computeForces(ts+1) + integrateStepTwo(ts) + integrateStepOne(ts+1) + distanceCheck +
+// NeighborList::needsUpdating(ts+2).  Velocity Verlet lets step two of one update() and step one of the next run back
+// to back per particle (nothing in between reads another particle), so the only grid-wide dependencies left in a
+// step are "all positions written before any force reads them" -- solved by ping-pong position buffers (pos_in is read
+// by every neighbor gather, pos_out is written by the owner) -- and the rebuild decision, taken by the last CTA to
+// finish (ticket counter).  Arithmetic per particle is the shared bodies => bit-identical to the separate kernels.
+template<class Evaluator> struct MdStepArgs
     {
-    unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= N) return;
-    float4 v = vel[j];
-    float3s a;
-    if (method == 2)
+    const float4* pos_in; float4* pos_out; float4* vel; float3s* accel; int3* image; float4* net_force;
+    float* virial; unsigned int virial_pitch;
+    const float4* last_pos; const unsigned int* tag;
+    const unsigned int* n_neigh; const unsigned int* nlist; const unsigned int* head_list;
+    const typename Evaluator::param_type* params; const float* rcutsq; const float* ronsq; unsigned int ntypes;
+    const float* rcut_max; const float* gamma;
+    unsigned int N; Box box; float dt; float r_buff;
+    int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
+    int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
+    StepState* st; cudaGraphConditionalHandle handle; int use_cond;
+    };
+
+template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE>
+__global__ void __launch_bounds__(256) k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
+    {
+    extern __shared__ unsigned char smem_raw[];
+    StepState* st = a.st;
+    const unsigned int steps_left = st->steps_left;
+    if (steps_left == 0) return; // padding launch of an odd-length chunk (uniform over the grid)
+    const bool last = steps_left == 1;
+    const unsigned int ts2 = st->ts_step_two;
+    const bool store_force = last || st->store_force;
+
+    PairTables<Evaluator> T;
+    pair_tables_load<Evaluator, SHIFT_MODE, MULTI_TYPE>(T, smem_raw, a.params, a.rcutsq, a.ronsq, a.ntypes);
+    const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int i = gtid / TPP;
+    const unsigned int sub = gtid % TPP;
+    const bool active = i < a.N;
+    const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const unsigned int size = active ? a.n_neigh[i] : 0u;
+    const unsigned int head = active ? a.head_list[i] : 0u;
+    const bool lead = (sub == 0) && active;
+    // operands of the integration half steps: issued before the neighbor walk so they are in registers when it ends
+    float4 v = make_float4(0.0f, 0.0f, 0.0f, 1.0f), lp = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    int3 img = make_int3(0, 0, 0);
+    unsigned int ptag = 0;
+    if (lead)
         {
-        const float gamma = gamma_tab[(unsigned int)__float_as_int(pos[j].w)];
-        langevin_step_two_body(v, a, net_force[j], tag[j], st->ts_step_two, seed, gamma, kT, dt, noiseless_t, 3u);
+        v = a.vel[i];
+        if (!last)
+            {
+            img = a.image[i];
+            lp = a.last_pos[i];
+            }
+        if (a.method == 2) ptag = a.tag[i];
         }
-    else
+    const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(pi4, size, head, sub, a.pos_in,
+                                                                                       a.box, a.nlist, T, a.ntypes);
+    bool moved = false;
+    if (lead)
         {
-        a = accel[j];
-        nve_step_two_body(v, a, net_force[j], dt, limit, limit_val, zero_force);
+        const float4 F = make_float4(r.fx, r.fy, r.fz, r.pe);
+        if (store_force)
+            {
+            a.net_force[i] = F;
+            if (VIRIAL)
+                {
+                a.virial[0 * a.virial_pitch + i] = r.vxx;
+                a.virial[1 * a.virial_pitch + i] = r.vxy;
+                a.virial[2 * a.virial_pitch + i] = r.vxz;
+                a.virial[3 * a.virial_pitch + i] = r.vyy;
+                a.virial[4 * a.virial_pitch + i] = r.vyz;
+                a.virial[5 * a.virial_pitch + i] = r.vzz;
+                }
+            }
+        const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
+        const bool nve = a.method == 1;
+        float3s acc;
+        // ---- integrateStepTwo(ts) ----
+        if (nve)
+            nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
+        else
+            langevin_step_two_body(v, acc, F, ptag, ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
+        a.accel[i] = acc;
+        if (!last)
+            {
+            // ---- integrateStepOne(ts+1): Langevin step one == NVE step one without limit (TwoStepLangevin.cc:86-125) ----
+            float4 p = pi4;
+            nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
+            a.pos_out[i] = p;
+            a.image[i] = img;
+            // ---- NeighborList::distanceCheck, fixed box (hoomd/md/NeighborList.cc:992-1016) ----
+            const float old_rmin = a.rcut_max[type_i];
+            const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(old_rmin, a.r_buff), 1.0f), old_rmin), 2.0f);
+            const float maxsq = (delta_max > 0.0f) ? __fmul_rn(delta_max, delta_max) : 0.0f;
+            float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
+                                    __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
+            dx = min_image_exact(dx, a.box);
+            moved = dot_exact(dx) >= maxsq;
+            }
+        else if (a.copy_pos_on_last)
+            a.pos_out[i] = pi4;
+        a.vel[i] = v;
         }
-    vel[j] = v;
-    accel[j] = a;
+    // ---- last CTA to finish takes the rebuild decision for the next launch ----
+    const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    if (threadIdx.x == 0)
+        {
+        if (any_moved) atomicOr(&st->moved, 1u);
+        __threadfence();
+        const unsigned int ticket = atomicAdd(&st->blocks_done, 1u);
+        if (ticket == gridDim.x - 1)
+            {
+            __threadfence();
+            st->blocks_done = 0u;
+            st->steps_left = steps_left - 1u;
+            if (!last)
+                decide_body(st);
+            else
+                {
+                st->need_rebuild = 0u;
+                st->moved = 0u;
+                }
+#if (CUDART_VERSION >= 12040)
+            if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
+#endif
+            }
+        }
     }
 
 __global__ void __launch_bounds__(256) k_compute_accel(float3s* __restrict__ accel,
@@ -141,9 +255,15 @@ cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStr
     return cudaGetLastError();
     }
 
-cudaError_t launch_decide(StepState* st, unsigned long long cond_handle, int use_cond, cudaStream_t stream)
+cudaError_t launch_decide(StepState* st, cudaStream_t stream)
     {
-    k_decide<<<1, 1, 0, stream>>>(st, (cudaGraphConditionalHandle)cond_handle, use_cond);
+    k_decide<<<1, 1, 0, stream>>>(st);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_graph_pre(StepState* st, unsigned long long cond_handle, cudaStream_t stream)
+    {
+    k_graph_pre<<<1, 1, 0, stream>>>(st, (cudaGraphConditionalHandle)cond_handle);
     return cudaGetLastError();
     }
 
@@ -154,13 +274,72 @@ cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, c
     return cudaGetLastError();
     }
 
-cudaError_t launch_fused_step_two(const FusedStepArgs& a, const StepState* st, cudaStream_t stream)
+template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>
+static cudaError_t md_step_mt(const MdStepArgs<Evaluator>& a, cudaStream_t stream)
     {
-    if (a.N == 0) return cudaSuccess;
-    k_fused_step_two<<<(a.N + 255) / 256, 256, 0, stream>>>(a.vel, (float3s*)a.accel, a.pos, a.net_force, a.tag, a.gamma,
-                                                            a.N, a.dt, a.method, a.limit != 0, a.limit_val,
-                                                            a.zero_force != 0, a.kT, a.seed, a.noiseless_t != 0, st);
+    const unsigned int bs = 128;
+    const unsigned int per_block = bs / TPP;
+    const unsigned int grid = (a.N + per_block - 1) / per_block;
+    if (a.ntypes > 1)
+        {
+        size_t smem = (size_t)a.ntypes * a.ntypes * (sizeof(typename Evaluator::param_type) + 2 * sizeof(float));
+        if (smem > 48 * 1024) return cudaErrorInvalidValue;
+        k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, true><<<grid, bs, smem, stream>>>(a);
+        }
+    else
+        k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false><<<grid, bs, 0, stream>>>(a);
     return cudaGetLastError();
+    }
+
+template<class Evaluator, int TPP>
+static cudaError_t md_step_tpp(const MdStepArgs<Evaluator>& a, unsigned int shift_mode, bool v, cudaStream_t stream)
+    {
+    switch (shift_mode)
+        {
+        case B200_SHIFT_NONE:
+            return v ? md_step_mt<Evaluator, TPP, B200_SHIFT_NONE, true>(a, stream)
+                     : md_step_mt<Evaluator, TPP, B200_SHIFT_NONE, false>(a, stream);
+        case B200_SHIFT_SHIFT:
+            return v ? md_step_mt<Evaluator, TPP, B200_SHIFT_SHIFT, true>(a, stream)
+                     : md_step_mt<Evaluator, TPP, B200_SHIFT_SHIFT, false>(a, stream);
+        case B200_SHIFT_XPLOR:
+            return v ? md_step_mt<Evaluator, TPP, B200_SHIFT_XPLOR, true>(a, stream)
+                     : md_step_mt<Evaluator, TPP, B200_SHIFT_XPLOR, false>(a, stream);
+        default:
+            return cudaErrorInvalidValue;
+        }
+    }
+
+cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, const FusedStepArgs& fa,
+                              const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
+                              unsigned long long cond_handle, int use_cond, cudaStream_t stream)
+    {
+    if (fa.N == 0) return cudaSuccess;
+    if (!box_is_orthorhombic(pa.box)) return cudaErrorNotSupported;
+    MdStepArgs<EvaluatorPairLJ> a;
+    a.pos_in = pos_in; a.pos_out = pos_out; a.vel = fa.vel; a.accel = (float3s*)fa.accel; a.image = (int3*)fa.image;
+    a.net_force = (float4*)pa.d_force; a.virial = pa.d_virial; a.virial_pitch = pa.virial_pitch;
+    a.last_pos = fa.last_pos; a.tag = fa.tag;
+    a.n_neigh = pa.d_n_neigh; a.nlist = pa.d_nlist; a.head_list = pa.d_head_list;
+    a.params = (const float2*)d_params; a.rcutsq = pa.d_rcutsq; a.ronsq = pa.d_ronsq; a.ntypes = pa.ntypes;
+    a.rcut_max = fa.rcut_max; a.gamma = fa.gamma;
+    a.N = fa.N; a.box = make_box(fa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
+    a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
+    a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
+    a.copy_pos_on_last = copy_pos_on_last;
+    a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
+    const bool v = pa.compute_virial != 0;
+    const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);
+    switch (tpp)
+        {
+        case 1: return md_step_tpp<EvaluatorPairLJ, 1>(a, pa.shift_mode, v, stream);
+        case 2: return md_step_tpp<EvaluatorPairLJ, 2>(a, pa.shift_mode, v, stream);
+        case 4: return md_step_tpp<EvaluatorPairLJ, 4>(a, pa.shift_mode, v, stream);
+        case 8: return md_step_tpp<EvaluatorPairLJ, 8>(a, pa.shift_mode, v, stream);
+        case 16: return md_step_tpp<EvaluatorPairLJ, 16>(a, pa.shift_mode, v, stream);
+        case 32: return md_step_tpp<EvaluatorPairLJ, 32>(a, pa.shift_mode, v, stream);
+        default: return cudaErrorInvalidValue;
+        }
     }
 
 cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,

@@ -22,6 +22,9 @@ struct StepState
     unsigned int num_forced;      // NeighborList::m_forced_updates
     unsigned int overflow;        // sticky: some n_neigh exceeded Nmax during a device-driven rebuild
     unsigned int ntypes;
+    unsigned int steps_left;      // MD steps still to run in this chunk (k_md_step counts it down; 0 = launches are no-ops)
+    unsigned int blocks_done;     // ticket counter of k_md_step (last CTA takes the rebuild decision)
+    unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
     };
 
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream);
@@ -40,13 +43,17 @@ struct FusedStepArgs
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);
-// rebuild decision for timestep+1 (NeighborList::needsUpdating); optionally sets a conditional graph node handle
-cudaError_t launch_decide(StepState* st, unsigned long long cond_handle, int use_cond, cudaStream_t stream);
+// rebuild decision for timestep+1 (NeighborList::needsUpdating)
+cudaError_t launch_decide(StepState* st, cudaStream_t stream);
+// first node of the step graph: arm the first conditional node from st->need_rebuild
+cudaError_t launch_graph_pre(StepState* st, unsigned long long cond_handle, cudaStream_t stream);
+// single-kernel MD step: pair force + step two + step one of the next step + distance check + rebuild decision
+cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, const FusedStepArgs& fa,
+                              const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
+                              unsigned long long cond_handle, int use_cond, cudaStream_t stream);
 // after a device-driven rebuild: overflow detection, condition reset
 cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
                                 cudaStream_t stream);
-// step two (timestep taken from st->ts_step_two)
-cudaError_t launch_fused_step_two(const FusedStepArgs& a, const StepState* st, cudaStream_t stream);
 // a = F/m (Integrator::computeAccelerations, hoomd/Integrator.cc:222-256)
 cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,
                                  cudaStream_t stream);
