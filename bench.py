@@ -326,7 +326,7 @@ def main():
                            "parallelism": "1 GPU" if world == 1 else "%d independent replicas (one per GPU)" % world,
                            "l2": "L2 flushed (256 MiB write) between timed iterations; within an iteration the 64k "
                                  "working set is L2-resident, which is the workload",
-                           "sorter_period": 300, "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels", 2: "CUDA graph, conditional IF node"}[USE_GRAPH], "nlist": {"r_buff": 0.4, "check_period": 1,
+                           "sorter_period": 300, "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels", 2: "CUDA graph, conditional IF node", 3: "stream launches of the graph kernels"}[USE_GRAPH], "nlist": {"r_buff": 0.4, "check_period": 1,
                                                            "rebuilds_total": stats["updates"] + stats["forced"],
                                                            "Nmax": stats["Nmax0"]}},
                 "particle_steps_per_sec": tps * N * world,

@@ -65,6 +65,29 @@ __device__ __forceinline__ float3 min_image_exact(float3 w, const Box& box)
     return w;
     }
 
+// Branch-free restatement of min_image_exact for candidates whose separation satisfies |w| < 1.5 L (both particles inside
+// the box): there `int i = (int)(|w|*Linv + 0.5f)` can only be 0 or 1, so `(float)i * L` is L when the rounded sum
+// reaches 1.0f and 0 otherwise; w -+ 0 leaves w unchanged (up to the sign of zero, which dot() erases).  Same bits out.
+__device__ __forceinline__ float min_image_1d_sel(float w, float lo, float hi, float L, float Linv, bool periodic_xy)
+    {
+    const bool up = w >= hi, dn = w < lo;
+    float s = L;
+    if (periodic_xy)
+        {
+        const float val = __fadd_rn(__fmul_rn(up ? w : -w, Linv), 0.5f);
+        s = (val >= 1.0f) ? L : 0.0f;
+        }
+    return __fadd_rn(w, up ? -s : (dn ? s : 0.0f));
+    }
+
+__device__ __forceinline__ float3 min_image_exact_sel(float3 w, const Box& box, bool wx, bool wy, bool wz)
+    {
+    if (wz) w.z = min_image_1d_sel(w.z, box.lo.z, box.hi.z, box.L.z, box.Linv.z, false);
+    if (wy) w.y = min_image_1d_sel(w.y, box.lo.y, box.hi.y, box.L.y, box.Linv.y, true);
+    if (wx) w.x = min_image_1d_sel(w.x, box.lo.x, box.hi.x, box.L.x, box.Linv.x, true);
+    return w;
+    }
+
 // Branch-free form for the force kernel: w -= L * rint(w / L), the reference's DEVICE minImage (hoomd/BoxDim.h:281-300).
 // Identical to the host form whenever |w| != L/2 exactly (a pair at L/2 is beyond any legal cutoff: the box must be
 // wider than 2*r_list, hoomd/md/NeighborListBinned.cc:109-115).

@@ -112,7 +112,7 @@ struct b200_system
     float r_buff = 0.0f;
     std::vector<float> h_r_cut, h_r_listsq, h_rcut_max;
     float rcut_max_max = 0.0f;
-    DevBuf<float> d_r_cut, d_r_listsq, d_rcut_max;
+    DevBuf<float> d_r_cut, d_r_listsq, d_rcut_max, d_maxsq;
     std::vector<unsigned int> h_Nmax;
     DevBuf<unsigned int> d_Nmax, nl_conditions, head_list, n_neigh, nlist, d_req_size;
     DevBuf<float4> last_pos;
@@ -246,7 +246,7 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     memset(&a, 0, sizeof(a));
     a.pos = s->pos.p; a.vel = s->vel.p; a.accel = (float*)s->accel.p; a.image = (int*)s->image.p;
     a.net_force = s->net_force.p; a.last_pos = s->last_pos.p; a.tag = s->tag.p;
-    a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p;
+    a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p; a.maxsq = s->d_maxsq.p;
     a.N = s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
@@ -308,6 +308,17 @@ static void nlist_update_rlist(b200_system* s)
     s->d_r_cut.upload(s->h_r_cut.data(), nt * nt, s->stream);
     s->d_r_listsq.upload(s->h_r_listsq.data(), nt * nt, s->stream);
     s->d_rcut_max.upload(s->h_rcut_max.data(), nt, s->stream);
+    // distance-check threshold per type for a fixed box (lambda = 1), hoomd/md/NeighborList.cc:1002-1006, in FP32
+    std::vector<float> maxsq(nt);
+    for (unsigned int i = 0; i < nt; i++)
+        {
+        const float old_rmin = s->h_rcut_max[i];
+        volatile float rmax = old_rmin + s->r_buff;
+        volatile float num = rmax * 1.0f - old_rmin;
+        const float delta_max = num / 2.0f;
+        maxsq[i] = (delta_max > 0.0f) ? delta_max * delta_max : 0.0f;
+        }
+    s->d_maxsq.upload(maxsq.data(), nt, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     }
 
@@ -699,7 +710,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     {
     const unsigned int N = s->N;
     if (s->force_update) nlist_build_head_list(s); // types may have been permuted by the sorter
-    ensure_graph(s);
+    if (s->use_graph != 3) ensure_graph(s);
     if (s->ck_pos.n < N)
         {
         s->ck_pos.alloc(N); s->ck_vel.alloc(N); s->ck_last_pos.alloc(N); s->ck_accel.alloc(N); s->ck_image.alloc(N);
@@ -727,7 +738,20 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
     CUDA_OK(launch_decide(s->d_state.p, s->stream));
     const unsigned int nreplay = (chunk + 1) / 2;
-    for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+    if (s->use_graph == 3)
+        {
+        // same kernel sequence as the plain graph, launched directly on the stream (profilers see every kernel)
+        const unsigned int* enable = &s->d_state.p->need_rebuild;
+        for (unsigned int k = 0; k < nreplay; k++)
+            {
+            enqueue_rebuild(s, enable, s->pos.p);
+            enqueue_md_step(s, fa, 0, 0ull, 0);
+            enqueue_rebuild(s, enable, s->pos_alt.p);
+            enqueue_md_step(s, fa, 1, 0ull, 0);
+            }
+        }
+    else
+        for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
     if (!st.overflow) cell_list_check_conditions(s);
@@ -766,7 +790,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         return;
         }
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    s->kernels_last_run += 2ull + (s->graph_uses_cond ? (3ull * nreplay + 6ull * rebuilds) : 14ull * nreplay);
+    s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + 6ull * rebuilds) : 14ull * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
     s->num_updates += st.num_updates;
@@ -894,7 +918,7 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     s->every = check_period;
     s->shift_mode = shift_mode;
     s->h_r_cut.assign(rcut, rcut + nt * nt);
-    s->d_r_cut.alloc(nt * nt); s->d_r_listsq.alloc(nt * nt); s->d_rcut_max.alloc(nt);
+    s->d_r_cut.alloc(nt * nt); s->d_r_listsq.alloc(nt * nt); s->d_rcut_max.alloc(nt); s->d_maxsq.alloc(nt);
     nlist_update_rlist(s);
     // pair tables: rcutsq = rcut*rcut, ronsq = ron*ron (PotentialPair::setRcut/setRon, hoomd/md/PotentialPair.h:237-269)
     std::vector<float2> prm(nt * nt);

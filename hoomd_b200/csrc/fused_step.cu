@@ -112,17 +112,22 @@ template<class Evaluator> struct MdStepArgs
     const float4* last_pos; const unsigned int* tag;
     const unsigned int* n_neigh; const unsigned int* nlist; const unsigned int* head_list;
     const typename Evaluator::param_type* params; const float* rcutsq; const float* ronsq; unsigned int ntypes;
-    const float* rcut_max; const float* gamma;
+    const float* maxsq; const float* gamma;
     unsigned int N; Box box; float dt; float r_buff;
     int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
     int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
     StepState* st; cudaGraphConditionalHandle handle; int use_cond;
     };
 
+constexpr int MD_BLOCK = 256;
+
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE>
-__global__ void __launch_bounds__(256) k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
+__global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     {
+    constexpr int PPB = MD_BLOCK / TPP; // particles per CTA
     extern __shared__ unsigned char smem_raw[];
+    __shared__ float4 s_force[PPB];
+    __shared__ float s_virial[VIRIAL ? 6 * PPB : 1];
     StepState* st = a.st;
     const unsigned int steps_left = st->steps_left;
     if (steps_left == 0) return; // padding launch of an odd-length chunk (uniform over the grid)
@@ -130,47 +135,50 @@ __global__ void __launch_bounds__(256) k_md_step(const __grid_constant__ MdStepA
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
 
+    // ---- phase 1: TPP lanes per particle walk its neighbor list (PotentialPair::computeForces) ----
     PairTables<Evaluator> T;
     pair_tables_load<Evaluator, SHIFT_MODE, MULTI_TYPE>(T, smem_raw, a.params, a.rcutsq, a.ronsq, a.ntypes);
-    const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-    const unsigned int i = gtid / TPP;
-    const unsigned int sub = gtid % TPP;
-    const bool active = i < a.N;
-    const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    const unsigned int size = active ? a.n_neigh[i] : 0u;
-    const unsigned int head = active ? a.head_list[i] : 0u;
-    const bool lead = (sub == 0) && active;
-    // operands of the integration half steps: issued before the neighbor walk so they are in registers when it ends
-    float4 v = make_float4(0.0f, 0.0f, 0.0f, 1.0f), lp = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    int3 img = make_int3(0, 0, 0);
-    unsigned int ptag = 0;
-    if (lead)
         {
-        v = a.vel[i];
-        if (!last)
+        const unsigned int slot = threadIdx.x / TPP;
+        const unsigned int i = blockIdx.x * PPB + slot;
+        const unsigned int sub = threadIdx.x % TPP;
+        const bool active = i < a.N;
+        const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const unsigned int size = active ? a.n_neigh[i] : 0u;
+        const unsigned int head = active ? a.head_list[i] : 0u;
+        const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(
+            pi4, size, head, sub, a.pos_in, a.box, a.nlist, T, a.ntypes);
+        if (sub == 0)
             {
-            img = a.image[i];
-            lp = a.last_pos[i];
+            s_force[slot] = make_float4(r.fx, r.fy, r.fz, r.pe);
+            if (VIRIAL)
+                {
+                s_virial[0 * PPB + slot] = r.vxx;
+                s_virial[1 * PPB + slot] = r.vxy;
+                s_virial[2 * PPB + slot] = r.vxz;
+                s_virial[3 * PPB + slot] = r.vyy;
+                s_virial[4 * PPB + slot] = r.vyz;
+                s_virial[5 * PPB + slot] = r.vzz;
+                }
             }
-        if (a.method == 2) ptag = a.tag[i];
         }
-    const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(pi4, size, head, sub, a.pos_in,
-                                                                                       a.box, a.nlist, T, a.ntypes);
+    __syncthreads();
+
+    // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
     bool moved = false;
-    if (lead)
+    const unsigned int i = blockIdx.x * PPB + threadIdx.x;
+    if (threadIdx.x < PPB && i < a.N)
         {
-        const float4 F = make_float4(r.fx, r.fy, r.fz, r.pe);
+        const float4 F = s_force[threadIdx.x];
+        const float4 pi4 = a.pos_in[i];
+        float4 v = a.vel[i];
         if (store_force)
             {
             a.net_force[i] = F;
             if (VIRIAL)
                 {
-                a.virial[0 * a.virial_pitch + i] = r.vxx;
-                a.virial[1 * a.virial_pitch + i] = r.vxy;
-                a.virial[2 * a.virial_pitch + i] = r.vxz;
-                a.virial[3 * a.virial_pitch + i] = r.vyy;
-                a.virial[4 * a.virial_pitch + i] = r.vyz;
-                a.virial[5 * a.virial_pitch + i] = r.vzz;
+#pragma unroll
+                for (int c = 0; c < 6; c++) a.virial[c * a.virial_pitch + i] = s_virial[c * PPB + threadIdx.x];
                 }
             }
         const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
@@ -180,22 +188,23 @@ __global__ void __launch_bounds__(256) k_md_step(const __grid_constant__ MdStepA
         if (nve)
             nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
         else
-            langevin_step_two_body(v, acc, F, ptag, ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
+            langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0,
+                                   3u);
         a.accel[i] = acc;
         if (!last)
             {
             // ---- integrateStepOne(ts+1): Langevin step one == NVE step one without limit (TwoStepLangevin.cc:86-125) ----
             float4 p = pi4;
+            int3 img = a.image[i];
+            const float4 lp = a.last_pos[i];
             nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
             a.pos_out[i] = p;
             a.image[i] = img;
             // ---- NeighborList::distanceCheck, fixed box (hoomd/md/NeighborList.cc:992-1016) ----
-            const float old_rmin = a.rcut_max[type_i];
-            const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(old_rmin, a.r_buff), 1.0f), old_rmin), 2.0f);
-            const float maxsq = (delta_max > 0.0f) ? __fmul_rn(delta_max, delta_max) : 0.0f;
+            const float maxsq = a.maxsq[type_i];
             float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
                                     __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
-            dx = min_image_exact(dx, a.box);
+            dx = min_image_exact_sel(dx, a.box, a.box.periodic.x, a.box.periodic.y, a.box.periodic.z);
             moved = dot_exact(dx) >= maxsq;
             }
         else if (a.copy_pos_on_last)
@@ -206,13 +215,13 @@ __global__ void __launch_bounds__(256) k_md_step(const __grid_constant__ MdStepA
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
     if (threadIdx.x == 0)
         {
-        if (any_moved) atomicOr(&st->moved, 1u);
-        __threadfence();
-        const unsigned int ticket = atomicAdd(&st->blocks_done, 1u);
-        if (ticket == gridDim.x - 1)
+        // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
+        const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
+        const unsigned long long old = atomicAdd(&st->ticket, inc);
+        if ((unsigned int)old == gridDim.x - 1)
             {
-            __threadfence();
-            st->blocks_done = 0u;
+            if ((old + inc) >> 32) st->moved = 1u;
+            st->ticket = 0ull;
             st->steps_left = steps_left - 1u;
             if (!last)
                 decide_body(st);
@@ -277,13 +286,13 @@ cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, c
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>
 static cudaError_t md_step_mt(const MdStepArgs<Evaluator>& a, cudaStream_t stream)
     {
-    const unsigned int bs = 128;
+    const unsigned int bs = MD_BLOCK;
     const unsigned int per_block = bs / TPP;
     const unsigned int grid = (a.N + per_block - 1) / per_block;
     if (a.ntypes > 1)
         {
         size_t smem = (size_t)a.ntypes * a.ntypes * (sizeof(typename Evaluator::param_type) + 2 * sizeof(float));
-        if (smem > 48 * 1024) return cudaErrorInvalidValue;
+        if (smem > 32 * 1024) return cudaErrorInvalidValue;
         k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, true><<<grid, bs, smem, stream>>>(a);
         }
     else
@@ -322,7 +331,7 @@ cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, c
     a.last_pos = fa.last_pos; a.tag = fa.tag;
     a.n_neigh = pa.d_n_neigh; a.nlist = pa.d_nlist; a.head_list = pa.d_head_list;
     a.params = (const float2*)d_params; a.rcutsq = pa.d_rcutsq; a.ronsq = pa.d_ronsq; a.ntypes = pa.ntypes;
-    a.rcut_max = fa.rcut_max; a.gamma = fa.gamma;
+    a.maxsq = fa.maxsq; a.gamma = fa.gamma;
     a.N = fa.N; a.box = make_box(fa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
     a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
     a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;

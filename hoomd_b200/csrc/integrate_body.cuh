@@ -43,7 +43,7 @@ __device__ __forceinline__ void nve_step_two_body(float4& v, float3s& a, float4 
         a.x = a.y = a.z = 0.0f;
     else
         {
-        const float minv = __fdiv_rn(1.0f, v.w);
+        const float minv = __frcp_rn(v.w); // == Scalar(1.0)/mass, correctly rounded
         a.x = __fmul_rn(f.x, minv);
         a.y = __fmul_rn(f.y, minv);
         a.z = __fmul_rn(f.z, minv);
@@ -79,7 +79,7 @@ __device__ __forceinline__ float langevin_step_two_body(float4& v, float3s& a, f
     const float bd_fy = __fsub_rn(__fmul_rn(ry, coeff), __fmul_rn(gamma, v.y));
     float bd_fz = __fsub_rn(__fmul_rn(rz, coeff), __fmul_rn(gamma, v.z));
     if (D < 3) bd_fz = 0.0f;
-    const float minv = __fdiv_rn(1.0f, v.w);
+    const float minv = __frcp_rn(v.w); // == Scalar(1.0)/mass, correctly rounded
     a.x = __fmul_rn(__fadd_rn(f.x, bd_fx), minv);
     a.y = __fmul_rn(__fadd_rn(f.y, bd_fy), minv);
     a.z = __fmul_rn(__fadd_rn(f.z, bd_fz), minv);

@@ -23,7 +23,8 @@ struct StepState
     unsigned int overflow;        // sticky: some n_neigh exceeded Nmax during a device-driven rebuild
     unsigned int ntypes;
     unsigned int steps_left;      // MD steps still to run in this chunk (k_md_step counts it down; 0 = launches are no-ops)
-    unsigned int blocks_done;     // ticket counter of k_md_step (last CTA takes the rebuild decision)
+    unsigned int _pad0;
+    unsigned long long ticket;    // k_md_step: low word = CTAs finished, high word = CTAs that saw a mover (one atomic)
     unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
     };
 
@@ -36,6 +37,7 @@ struct FusedStepArgs
     {
     float4* pos; float4* vel; float* accel; int* image; const float4* net_force; const float4* last_pos;
     const unsigned int* tag; const float* rcut_max; const float* gamma;
+    const float* maxsq;           // per type: distance-check threshold^2 (NeighborList.cc:1002-1006, fixed box)
     unsigned int N; b200_box box; float dt; float r_buff;
     int method;                   // 1 = NVE, 2 = Langevin
     int limit; float limit_val; int zero_force;

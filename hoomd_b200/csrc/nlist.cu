@@ -206,6 +206,16 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     const unsigned int lanemask_lt = (1u << lane) - 1u;
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
+    // A candidate of an interior cell is less than two cell widths away along every axis; with >= 5 cells per axis that is
+    // inside [lo, hi) and minImage is the identity: only cells on a periodic face pay for it (CTA-uniform).
+    bool wx, wy, wz;
+        {
+        const unsigned int bx = cell % dim.x, by = (cell / dim.x) % dim.y, bz = cell / (dim.x * dim.y);
+        wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
+        wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
+        wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+        }
+    const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NL_CAP)
         {
@@ -259,7 +269,7 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
                         }
                     const bool excluded = (j == i) || (rc <= 0.0f);
                     float3 dx = make_float3(__fsub_rn(pi4.x, cj.x), __fsub_rn(pi4.y, cj.y), __fsub_rn(pi4.z, cj.z));
-                    dx = min_image_exact(dx, box);
+                    if (wrap_any) dx = min_image_exact_sel(dx, box, wx, wy, wz);
                     const float drsq = dot_exact(dx);
                     hit = !excluded && (drsq <= rlsq) && (!half_storage || i < j);
                     }

@@ -8,7 +8,7 @@ wl = sys.argv[1] if len(sys.argv) > 1 else "lj64k"
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2000
 bench.EQUIL_STEPS = int(sys.argv[3]) if len(sys.argv) > 3 else None
 state, L = bench.make_state(wl)
-for ug in (2, 1, 0):
+for ug in (2,):
     for tpp in (2, 4, 8, 16, 32):
         bench.USE_GRAPH = ug
         s = bench.new_system(state, L)
