@@ -279,18 +279,25 @@ def main():
     tps = tps_rank
     stats = s.stats()
 
-    # ---- dominant kernel: pair force, CUDA events on the engine stream --------------------------------------------
+    # ---- dominant kernel: the single-kernel MD step (pair force + both half steps + distance check), timed live with
+    # CUDA events on the engine stream (b200_sys_time_kernel); algorithmic bytes per particle per launch:
+    # read pos 16 + n_neigh 4 + head 4 + nlist 4*nbar + vel 16 + image 12 + last_pos 16; write pos 16 + vel 16 + accel 12
+    # + image 12  = 124 + 4*nbar
+    step_ms = s.time_kernel(2, 20)
     pair_ms = s.time_kernel(0, 200)
     nlist_ms = s.time_kernel(1, 20)
     n_neigh = s.nlist()[0]
     nbar = float(n_neigh.mean())
-    pair_bytes = (16 + 4 + 4 + 4 * nbar + 16) * N
-    achieved = pair_bytes / (pair_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_pair_forces<EvaluatorPairLJ>", "achieved": achieved, "peak": hbm_peak,
-                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "kernel_ms": pair_ms, "algorithmic_bytes_per_launch": pair_bytes, "mean_neighbors": nbar,
-                "fp32_tflops": 40.0 * nbar * N / (pair_ms * 1e-3) / 1e12,
+    step_bytes = (124.0 + 4.0 * nbar) * N
+    step_flops = (40.0 * nbar + 55.0) * N
+    achieved = step_bytes / (step_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_md_step<EvaluatorPairLJ> (force + step two + step one + distance check)",
+                "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak_source": peak_src, "kernel_ms": step_ms, "algorithmic_bytes_per_launch": step_bytes,
+                "mean_neighbors": nbar,
+                "fp32_tflops": step_flops / (step_ms * 1e-3) / 1e12,
                 "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12,
+                "pair_kernel_ms": pair_ms, "pair_kernel_gbs": (40.0 + 4.0 * nbar) * N / (pair_ms * 1e-3) / 1e9,
                 "nlist_rebuild_ms": nlist_ms,
                 "step_hbm_frac": BYTES_PER_PARTICLE_STEP * N * tps_rank / (hbm_peak * 1e9),
                 "note": "working set at 64k is L2-resident (15 MB < 126 MB L2): the step is launch/latency bound, "

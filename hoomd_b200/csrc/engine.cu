@@ -1154,6 +1154,46 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
     cell_list_args(s, ca);
     b200_nlist_args na;
     nlist_args(s, na);
+    if (which == 2)
+        {
+        // the single-kernel MD step itself: `iters` back-to-back launches (alternating ping-pong phase, no rebuild in
+        // between, never the chunk's last step) on a scratch copy of the integrator state, which is restored afterwards
+        if (!s->method) throw std::runtime_error("integrate: no integration method set");
+        const unsigned int N = s->N;
+        if (s->ck_pos.n < N)
+            {
+            s->ck_pos.alloc(N); s->ck_vel.alloc(N); s->ck_last_pos.alloc(N); s->ck_accel.alloc(N); s->ck_image.alloc(N);
+            }
+        CUDA_OK(cudaMemcpyAsync(s->ck_pos.p, s->pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->ck_vel.p, s->vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->ck_accel.p, s->accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->ck_image.p, s->image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        StepState& st = *s->h_state;
+        memset(&st, 0, sizeof(st));
+        st.timestep = s->timestep;
+        st.last_updated = s->timestep;
+        st.every = 0x7fffffffu; // no rebuild decision can fire
+        st.ntypes = s->ntypes;
+        st.steps_left = iters + 1;
+        CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
+        FusedStepArgs fa;
+        fused_args(s, fa);
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        CUDA_OK(cudaEventRecord(e0, s->stream));
+        for (unsigned int k = 0; k < iters; k++) enqueue_md_step(s, fa, (int)(k & 1), 0ull, 0);
+        CUDA_OK(cudaEventRecord(e1, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        float ms2 = 0.0f;
+        CUDA_OK(cudaEventElapsedTime(&ms2, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        *avg_ms = (double)ms2 / iters;
+        return 0;
+        }
     CUDA_OK(cudaStreamSynchronize(s->stream));
     CUDA_OK(cudaEventRecord(e0, s->stream));
     for (unsigned int k = 0; k < iters; k++)

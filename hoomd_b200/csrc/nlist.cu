@@ -137,7 +137,57 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
 constexpr int NL_BLOCK = 128;
 constexpr int NL_CAP = 1024; // staged candidates per pass (16 kB + 4 kB types); denser neighborhoods take several passes
 
-template<bool MULTI_TYPE>
+// One warp tests every staged candidate against particle i: 2 x 32 candidates per trip, ballot + popc compaction in the
+// staged (= oracle) order.  The tile is padded to a multiple of 64 with far-away sentinels, so there is no bounds test.
+template<bool MULTI_TYPE, bool WRAP, bool HALF>
+__device__ __forceinline__ unsigned int nlist_scan_tile(unsigned int n, const float4 pi4, unsigned int i,
+                                                        unsigned int type_i, unsigned int Nmax_i,
+                                                        unsigned int* __restrict__ row, const float4* s_cand,
+                                                        const unsigned int* s_type, unsigned int cnt_padded,
+                                                        unsigned int lane, const Box& box, bool wx, bool wy, bool wz,
+                                                        float rcut_00, float rlsq_00, const float* __restrict__ r_cut,
+                                                        const float* __restrict__ r_listsq, unsigned int ntypes)
+    {
+    const unsigned int lanemask_lt = (1u << lane) - 1u;
+    for (unsigned int base = 0; base < cnt_padded; base += 64)
+        {
+        bool hit[2];
+        unsigned int jj[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+            {
+            const unsigned int t = base + 32 * u + lane;
+            const float4 cj = s_cand[t];
+            const unsigned int j = (unsigned int)__float_as_int(cj.w);
+            float rlsq = rlsq_00;
+            bool excluded = (j == i);
+            if (MULTI_TYPE)
+                {
+                const unsigned int tj = s_type[t];
+                excluded |= __ldg(&r_cut[type_i * ntypes + tj]) <= 0.0f;
+                rlsq = __ldg(&r_listsq[type_i * ntypes + tj]);
+                }
+            else
+                excluded |= rcut_00 <= 0.0f;
+            float3 dx = make_float3(__fsub_rn(pi4.x, cj.x), __fsub_rn(pi4.y, cj.y), __fsub_rn(pi4.z, cj.z));
+            if (WRAP) dx = min_image_exact_sel(dx, box, wx, wy, wz);
+            const float drsq = dot_exact(dx);
+            hit[u] = !excluded && (drsq <= rlsq) && (!HALF || i < j);
+            jj[u] = j;
+            }
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+            {
+            const unsigned int mask = __ballot_sync(0xffffffffu, hit[u]);
+            const unsigned int k = n + __popc(mask & lanemask_lt);
+            if (hit[u] && k < Nmax_i) row[k] = jj[u];
+            n += __popc(mask);
+            }
+        }
+    return n;
+    }
+
+template<bool MULTI_TYPE, bool HALF>
 __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restrict__ nlist,
                                                           unsigned int* __restrict__ n_neigh,
                                                           float4* __restrict__ last_pos,
@@ -149,7 +199,7 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
                                                           const unsigned int* __restrict__ cell_type, uint3 dim,
                                                           Box box, const float* __restrict__ r_cut,
                                                           const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                          int half_storage, const unsigned int* __restrict__ enable)
+                                                          const unsigned int* __restrict__ enable)
     {
     if (enable && !*enable) return;
     extern __shared__ float4 s_cand[];
@@ -157,14 +207,15 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     __shared__ unsigned int s_beg[28], s_off[28]; // per adjacent cell: first entry, exclusive prefix of the lengths
     __shared__ unsigned int s_nr;
 
-    const unsigned int cell = blockIdx.x;
+    // grid = (dim.x, dim.y, dim.z): the cell coordinates come for free
+    const unsigned int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z;
+    const unsigned int cell = (bz * dim.y + by) * dim.x + bx;
     const unsigned int own_beg = cell_start[cell], own_end = cell_start[cell + 1];
     if (own_beg == own_end) return; // uniform per CTA
     const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     if (warp == 0)
         {
-        const int bx = cell % dim.x, by = (cell / dim.x) % dim.y, bz = cell / (dim.x * dim.y);
         int xs[3], ys[3], zs[3];
         const int nx = axis_set(bx, dim.x, box.periodic.x, xs);
         const int ny = axis_set(by, dim.y, box.periodic.y, ys);
@@ -203,37 +254,42 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     __syncthreads();
     const unsigned int nr = s_nr;
     const unsigned int total = s_off[nr];
-    const unsigned int lanemask_lt = (1u << lane) - 1u;
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
     // A candidate of an interior cell is less than two cell widths away along every axis; with >= 5 cells per axis that is
     // inside [lo, hi) and minImage is the identity: only cells on a periodic face pay for it (CTA-uniform).
-    bool wx, wy, wz;
-        {
-        const unsigned int bx = cell % dim.x, by = (cell / dim.x) % dim.y, bz = cell / (dim.x * dim.y);
-        wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
-        wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
-        wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
-        }
+    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
+    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
+    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
     const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NL_CAP)
         {
         const unsigned int cnt = min((unsigned int)NL_CAP, total - pass);
+        const unsigned int cnt_padded = (cnt + 63u) & ~63u; // NL_CAP is a multiple of 64
         if (pass) __syncthreads(); // everyone is done with the previous tile
-        for (unsigned int t = threadIdx.x; t < cnt; t += NL_BLOCK)
+        for (unsigned int t = threadIdx.x; t < cnt_padded; t += NL_BLOCK)
             {
-            const unsigned int g = pass + t;
-            // adjacent cell holding staged entry g: last r with s_off[r] <= g (<= 27 ranges: 5-step bisection)
-            unsigned int lo = 0, hi = nr;
-            while (hi - lo > 1)
+            if (t < cnt)
                 {
-                const unsigned int mid = (lo + hi) >> 1;
-                if (s_off[mid] <= g) lo = mid; else hi = mid;
+                const unsigned int g = pass + t;
+                // adjacent cell holding staged entry g: last r with s_off[r] <= g (<= 27 ranges: 5-step bisection)
+                unsigned int lo = 0, hi = nr;
+                while (hi - lo > 1)
+                    {
+                    const unsigned int mid = (lo + hi) >> 1;
+                    if (s_off[mid] <= g) lo = mid; else hi = mid;
+                    }
+                const unsigned int e = s_beg[lo] + (g - s_off[lo]);
+                s_cand[t] = cell_xyzf[e];
+                if (MULTI_TYPE) s_type[t] = cell_type[e];
                 }
-            const unsigned int e = s_beg[lo] + (g - s_off[lo]);
-            s_cand[t] = cell_xyzf[e];
-            if (MULTI_TYPE) s_type[t] = cell_type[e];
+            else
+                {
+                // sentinel: dr^2 overflows to +inf, never <= r_list^2; index 0xffffffff is nobody
+                s_cand[t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
+                if (MULTI_TYPE) s_type[t] = 0u;
+                }
             }
         __syncthreads();
 
@@ -244,43 +300,16 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
             if (i >= N) continue; // ghosts are candidates only
             const unsigned int type_i = MULTI_TYPE ? cell_type[p] : 0u;
             const unsigned int Nmax_i = Nmax[type_i];
-            const unsigned int head_i = head_list[i];
+            unsigned int* row = nlist + head_list[i];
             unsigned int n = pass ? n_neigh[i] : 0u; // later passes continue the count this warp stored itself
-            for (unsigned int base = 0; base < cnt; base += 32)
-                {
-                const unsigned int t = base + lane;
-                bool hit = false;
-                unsigned int j = 0;
-                if (t < cnt)
-                    {
-                    const float4 cj = s_cand[t];
-                    j = (unsigned int)__float_as_int(cj.w);
-                    float rc, rlsq;
-                    if (MULTI_TYPE)
-                        {
-                        const unsigned int tj = s_type[t];
-                        rc = __ldg(&r_cut[type_i * ntypes + tj]);
-                        rlsq = __ldg(&r_listsq[type_i * ntypes + tj]);
-                        }
-                    else
-                        {
-                        rc = rcut_00;
-                        rlsq = rlsq_00;
-                        }
-                    const bool excluded = (j == i) || (rc <= 0.0f);
-                    float3 dx = make_float3(__fsub_rn(pi4.x, cj.x), __fsub_rn(pi4.y, cj.y), __fsub_rn(pi4.z, cj.z));
-                    if (wrap_any) dx = min_image_exact_sel(dx, box, wx, wy, wz);
-                    const float drsq = dot_exact(dx);
-                    hit = !excluded && (drsq <= rlsq) && (!half_storage || i < j);
-                    }
-                const unsigned int mask = __ballot_sync(0xffffffffu, hit);
-                if (hit)
-                    {
-                    const unsigned int k = n + __popc(mask & lanemask_lt);
-                    if (k < Nmax_i) nlist[head_i + k] = j;
-                    }
-                n += __popc(mask);
-                }
+            if (wrap_any)
+                n = nlist_scan_tile<MULTI_TYPE, true, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                                                            lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
+                                                            ntypes);
+            else
+                n = nlist_scan_tile<MULTI_TYPE, false, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                                                             lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
+                                                             ntypes);
             if (lane == 0)
                 {
                 if (pass + NL_CAP < total)
@@ -465,17 +494,23 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
     static const bool use_warp_kernel = getenv("HOOMD_B200_NLIST_WARP") != nullptr; // A/B switch for profiling
     if (!use_warp_kernel)
         {
-        const unsigned int ncells = a->dim.x * a->dim.y * a->dim.z;
+        if (a->dim.y > 65535u || a->dim.z > 65535u) return cudaErrorInvalidValue;
+        const dim3 grid(a->dim.x, a->dim.y, a->dim.z);
+        const size_t smem1 = NL_CAP * sizeof(float4), smemN = NL_CAP * (sizeof(float4) + sizeof(unsigned int));
+#define B200_NL_LAUNCH(MT, HALF, SMEM)                                                                               \
+    k_nlist_tiled<MT, HALF><<<grid, NL_BLOCK, SMEM, stream>>>(                                                     \
+        a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,         \
+        a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,        \
+        a->ntypes, enable)
         if (a->ntypes > 1)
-            k_nlist_tiled<true><<<ncells, NL_BLOCK, NL_CAP * (sizeof(float4) + sizeof(unsigned int)), stream>>>(
-                a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,
-                a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,
-                a->ntypes, a->half_storage, enable);
+            {
+            if (a->half_storage) B200_NL_LAUNCH(true, true, smemN); else B200_NL_LAUNCH(true, false, smemN);
+            }
         else
-            k_nlist_tiled<false><<<ncells, NL_BLOCK, NL_CAP * sizeof(float4), stream>>>(
-                a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,
-                a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,
-                a->ntypes, a->half_storage, enable);
+            {
+            if (a->half_storage) B200_NL_LAUNCH(false, true, smem1); else B200_NL_LAUNCH(false, false, smem1);
+            }
+#undef B200_NL_LAUNCH
         return cudaGetLastError();
         }
     const unsigned int warps_per_block = 4;

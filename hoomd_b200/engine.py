@@ -154,7 +154,8 @@ class System:
                     dim=(int(out[4]), int(out[5]), int(out[6])), Nmax0=int(out[7]))
 
     def time_kernel(self, which, iters=20):
-        """average CUDA-event milliseconds per launch of the pair kernel (which=0) or the nlist rebuild (which=1)"""
+        """average CUDA-event milliseconds per launch: which=0 pair kernel, 1 cell list + nlist rebuild, 2 the single-kernel
+        MD step (runs on a scratch copy of the integrator state; the system is not advanced)"""
         ms = C.c_double(0)
         self._check(_lib.lib().b200_sys_time_kernel(self.h, int(which), int(iters), C.byref(ms)))
         return ms.value

@@ -335,8 +335,9 @@ B200_API int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned 
  *       dim.x, dim.y, dim.z, Nmax[0]} */
 B200_API int b200_sys_get_stats(b200_system* s, unsigned long long* out8);
 /* Micro-benchmarks in the spirit of Compute::benchmark (hoomd/ForceCompute.cc:153-180, hoomd/md/NeighborList.cc:260-289):
- * launches kernel `which` (0 = pair force on the current list, 1 = cell list + neighbor list build) `iters` times on the
- * system's stream between two CUDA events and returns the average milliseconds per launch.  State is not advanced. */
+ * launches kernel `which` (0 = pair force on the current list, 1 = cell list + neighbor list build, 2 = the single-kernel
+ * MD step on a scratch copy of the integrator state) `iters` times on the system's stream between two CUDA events and
+ * returns the average milliseconds per launch.  State is not advanced. */
 B200_API int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* avg_ms);
 /* ComputeThermo at the current step: out = {KE, PE, temperature, pressure, ndof} */
 B200_API int b200_sys_get_thermo(b200_system* s, double* out5);
