@@ -5,3 +5,4 @@ from .engine import System  # noqa: F401
 from . import workloads  # noqa: F401
 
 __version__ = "0.1.0"
+from . import domain  # noqa: F401,E402

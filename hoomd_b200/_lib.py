@@ -65,6 +65,13 @@ class PDataArrays(C.Structure):
                 ("charge", vp), ("diameter", vp), ("body", vp)]
 
 
+class MgParams(C.Structure):
+    """b200_mg_params"""
+    _fields_ = [("world", C.c_uint), ("rank", C.c_uint), ("grid", C.c_uint * 3), ("global_box", Box),
+                ("N_global", C.c_uint), ("N_local", C.c_uint), ("Ncap", C.c_uint), ("r_ghost", C.c_float),
+                ("capacity_factor", C.c_float), ("ntypes", C.c_uint), ("device", C.c_int)]
+
+
 # every symbol include/hoomd_b200.h declares; tests/test_abi.py checks this list against the header and the .so
 SYMBOLS = [
     "b200_box_init", "b200_box_init_lohi", "b200_compute_cell_list", "b200_cell_list_dimensions",
@@ -79,6 +86,8 @@ SYMBOLS = [
     "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
     "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
     "b200_sys_get_thermo", "b200_sys_time_kernel",
+    "b200_sys_create_mg", "b200_sys_mg_export", "b200_sys_mg_connect", "b200_sys_get_n", "b200_sys_set_tags",
+    "b200_sys_mg_stats", "b200_sys_mg_get_ghosts",
 ]
 
 _lib = None
@@ -156,6 +165,15 @@ def lib():
     L.b200_sys_get_stats.argtypes = [vp, C.POINTER(C.c_ulonglong)]
     L.b200_sys_get_thermo.argtypes = [vp, c_double_p]
     L.b200_sys_time_kernel.argtypes = [vp, C.c_int, C.c_uint, c_double_p]
+    L.b200_sys_create_mg.argtypes = [C.POINTER(MgParams)]
+    L.b200_sys_create_mg.restype = vp
+    L.b200_sys_mg_export.argtypes = [vp, vp, C.POINTER(Box), c_uint_p]
+    L.b200_sys_mg_connect.argtypes = [vp, vp]
+    L.b200_sys_get_n.argtypes = [vp]
+    L.b200_sys_get_n.restype = C.c_uint
+    L.b200_sys_set_tags.argtypes = [vp, vp]
+    L.b200_sys_mg_stats.argtypes = [vp, C.POINTER(C.c_ulonglong)]
+    L.b200_sys_mg_get_ghosts.argtypes = [vp, vp, vp]
     _lib = L
     return L
 

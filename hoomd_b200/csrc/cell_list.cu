@@ -13,11 +13,22 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
                                                   unsigned int* __restrict__ conditions,
                                                   const float4* __restrict__ pos, unsigned int N, unsigned int n_ghost,
                                                   Box box, uint3 dim, float3 ghost_width,
-                                                  const unsigned int* __restrict__ enable)
+                                                  const unsigned int* __restrict__ enable,
+                                                  const unsigned int* __restrict__ d_N)
     {
     if (enable && !*enable) return; // device-driven stepping: the rebuild was not requested this step
     unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N + n_ghost) return;
+    if (d_N)
+        {
+        // multi-GPU layout: locals [0, *d_N), unused capacity [*d_N, N), ghosts [N, N + n_ghost)
+        const unsigned int Nloc = *d_N;
+        if (n >= Nloc && n < N)
+            {
+            particle_cell[n] = B200_NOT_BINNED;
+            return;
+            }
+        }
     float4 p = pos[n];
     unsigned int cell = B200_NOT_BINNED, slot = 0;
     if (isnan(p.x) || isnan(p.y) || isnan(p.z))
@@ -289,7 +300,8 @@ namespace b200
 {
 // enable == NULL: unconditional (driver entry point, zeroes cell_count itself).  enable != NULL: every kernel returns
 // at once unless *enable != 0, and cell_count must already be zero (k_cell_scan leaves it zeroed).
-cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream)
+cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
+                             const unsigned int* d_N)
     {
     if (!box_is_orthorhombic(a->box)) return cudaErrorNotSupported;
     const unsigned int ntot = a->N + a->n_ghost;
@@ -301,7 +313,7 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     if (ntot)
         k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
                                                             a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
-                                                            box, dim, gw, enable);
+                                                            box, dim, gw, enable, d_N);
     k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions, enable);
     if (ntot)
         {
@@ -320,7 +332,7 @@ extern "C" {
 
 int b200_compute_cell_list(const b200_cell_list_args* a, b200_stream_t stream)
     {
-    return (int)b200::launch_cell_list(a, nullptr, (cudaStream_t)stream);
+    return (int)b200::launch_cell_list(a, nullptr, (cudaStream_t)stream, nullptr);
     }
 
 int b200_cell_list_export_padded(unsigned int* d_cell_size, float* d_xyzf, float* d_tdb, unsigned int* d_conditions,

@@ -1,0 +1,36 @@
+// NeighborList::needsUpdating on the device, shared by the single-GPU step kernels and the multi-GPU step barrier.
+#pragma once
+#include "kernels.h"
+
+namespace b200
+{
+// NeighborList::needsUpdating(ts+1) for the force evaluation that follows (update(ts) computes forces at ts+1)
+__device__ __forceinline__ void decide_body(StepState* st)
+    {
+    const unsigned int ts1 = st->timestep + 1u;
+    bool result;
+    if (st->force_update)
+        {
+        result = true;
+        st->force_update = 0u;
+        st->num_forced += 1u;
+        st->last_updated = ts1;
+        }
+    else if (ts1 < st->last_updated + st->every) // !shouldCheckDistance
+        result = false;
+    else
+        {
+        result = st->r_buff_tiny || *((volatile unsigned int*)&st->moved);
+        if (result)
+            {
+            st->last_updated = ts1;
+            st->num_updates += 1u;
+            }
+        }
+    st->moved = 0u;
+    st->need_rebuild = result ? 1u : 0u;
+    st->ts_step_two = st->timestep;
+    st->timestep = ts1;
+    }
+
+} // namespace b200

@@ -13,6 +13,7 @@
 // There is NO CPU fallback: every compute path launches the sm_100a kernels of this directory.
 #include "common.cuh"
 #include "kernels.h"
+#include "comm.cuh"
 #include <string>
 #include <vector>
 #include <chrono>
@@ -34,11 +35,14 @@ template<class T> struct DevBuf
     {
     T* p = nullptr;
     size_t n = 0;
+    bool owned = true;
     DevBuf() {}
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() { release(); }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void release() { if (p && owned) cudaFree(p); p = nullptr; n = 0; owned = true; }
+    // non-owning view into a larger allocation (multi-GPU slab)
+    void view(T* q, size_t count) { release(); p = q; n = count; owned = false; }
     void alloc(size_t count, bool zero = true)
         {
         release();
@@ -88,7 +92,9 @@ struct b200_system
 
     // ---- ParticleData -------------------------------------------------------------------------------------------
     unsigned int N = 0, ntypes = 1;
-    b200_box box;
+    unsigned int Ncap = 0;   // allocated local capacity (== N on one GPU; > N under domain decomposition)
+    unsigned int Gcap = 0;   // ghost capacity: ghosts live at [Ncap, Ncap + Gcap) of pos / tag / cell arrays
+    b200_box box;            // local box (== global box on one GPU)
     DevBuf<float4> pos, vel, net_force, pos_alt, vel_alt, net_force_alt;
     DevBuf<f3> accel, accel_alt;
     DevBuf<i3> image, image_alt;
@@ -147,7 +153,7 @@ struct b200_system
 
     // ---- System -------------------------------------------------------------------------------------------------
     unsigned int timestep = 0;
-    int use_graph = 1;
+    int use_graph = 2;                   // 0 host-driven, 1 plain graph, 2 conditional graph (default), 3 stream launches
     unsigned int* h_flag = nullptr;      // pinned: distance-check result / small read-backs
     DevBuf<unsigned int> d_flag;
     DevBuf<StepState> d_state;
@@ -163,6 +169,22 @@ struct b200_system
     DevBuf<i3> ck_image;
     // thermo
     DevBuf<double> th_partial, th_out;
+
+    // ---- DomainDecomposition + Communicator (multi-GPU) -------------------------------------------------------
+    bool mg = false;
+    b200_box global_box;
+    unsigned int mg_grid[3] = {1, 1, 1}, mg_pos[3] = {0, 0, 0};
+    float r_ghost = 0.0f;
+    MgConst mgc;
+    MgLocal mgl;
+    void* slab = nullptr;            // IPC-exported: posA | posB | tag | migration mailboxes | counts | flags
+    size_t slab_bytes = 0, off_posA = 0, off_posB = 0, off_tag = 0, off_mig = 0, off_migcnt = 0, off_flags = 0;
+    void* peer_base[MG_MAX_RANKS] = {nullptr};
+    bool mg_connected = false;
+    DevBuf<MgState> d_ms;
+    MgState* h_ms = nullptr;         // pinned
+    DevBuf<unsigned int> holes, low_holes, hole_mark, plan_src;
+    DevBuf<unsigned char> slot_dir;
     };
 
 namespace b200
@@ -190,8 +212,8 @@ static void cell_list_args(b200_system* s, b200_cell_list_args& a)
     a.d_particle_slot = s->particle_slot.p;
     a.d_scratch_idx = s->scratch_idx.p;
     a.d_pos = (const float*)s->pos.p;
-    a.N = s->N;
-    a.n_ghost = 0;
+    a.N = s->mg ? s->Ncap : s->N; // multi-GPU: the ghost base; the live local count is read on the device
+    a.n_ghost = s->Gcap;
     a.box = s->box;
     a.dim = s->dim;
     for (int d = 0; d < 3; d++) a.ghost_width[d] = s->ghost_width[d];
@@ -207,7 +229,7 @@ static void nlist_args(b200_system* s, b200_nlist_args& a)
     a.d_Nmax = s->d_Nmax.p;
     a.d_head_list = s->head_list.p;
     a.d_pos = (const float*)s->pos.p;
-    a.N = s->N;
+    a.N = s->mg ? s->Ncap : s->N; // entries with an index >= N are ghosts
     a.d_cell_start = s->cell_start.p;
     a.d_cell_xyzf = (const float*)s->cell_xyzf.p;
     a.d_cell_type = s->ntypes > 1 ? s->cell_type.p : nullptr;
@@ -247,7 +269,8 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.pos = s->pos.p; a.vel = s->vel.p; a.accel = (float*)s->accel.p; a.image = (int*)s->image.p;
     a.net_force = s->net_force.p; a.last_pos = s->last_pos.p; a.tag = s->tag.p;
     a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p; a.maxsq = s->d_maxsq.p;
-    a.N = s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
+    a.N = s->mg ? s->Ncap : s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
+    a.d_N = s->mg ? &s->d_state.p->N : nullptr; a.mg = s->mg ? 1 : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
     }
@@ -325,7 +348,8 @@ static void nlist_update_rlist(b200_system* s)
 // NeighborList::buildHeadList + resizeNlist (hoomd/md/NeighborList.cc:1336-1380)
 static void nlist_build_head_list(b200_system* s)
     {
-    CUDA_OK(b200_nlist_build_head_list(s->head_list.p, s->d_req_size.p, s->d_Nmax.p, (const float*)s->pos.p, s->N,
+    CUDA_OK(b200_nlist_build_head_list(s->head_list.p, s->d_req_size.p, s->d_Nmax.p, (const float*)s->pos.p,
+                                       s->mg ? s->Ncap : s->N,
                                        s->ntypes, s->stream));
     s->kernels_last_run += (s->ntypes == 1) ? 1 : 3;
     unsigned int size = 0;
@@ -512,18 +536,18 @@ static void prep_run(b200_system* s, unsigned int ts)
 // SFCPackUpdater::update (hoomd/SFCPackUpdater.cc:70-108)
 static void sorter_update(b200_system* s)
     {
-    const unsigned int N = s->N;
-    if (s->sort_order.n < N)
+    const unsigned int N = s->N, C = s->Ncap;
+    if (s->sort_order.n < C)
         {
-        s->sort_order.alloc(N);
-        s->sort_keys.alloc(N);
-        s->sort_scratch.alloc(2 * (size_t)N);
+        s->sort_order.alloc(C);
+        s->sort_keys.alloc(C);
+        s->sort_scratch.alloc(2 * (size_t)C);
         uint64_t need = 0;
         CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, nullptr, 0, &need,
-                                               (const float*)s->pos.p, N, &s->box, s->sorter_grid, s->stream));
+                                               (const float*)s->pos.p, C, &s->box, s->sorter_grid, s->stream));
         s->sort_temp.alloc(need + 16);
-        s->vel_alt.alloc(N); s->net_force_alt.alloc(N);
-        s->accel_alt.alloc(N); s->image_alt.alloc(N); s->tag_alt.alloc(N);
+        s->vel_alt.alloc(C); s->net_force_alt.alloc(C);
+        s->accel_alt.alloc(C); s->image_alt.alloc(C); s->tag_alt.alloc(C);
         }
     CUDA_OK(b200_sfc_generate_sorted_order(s->sort_order.p, s->sort_keys.p, s->sort_scratch.p, s->sort_temp.p,
                                            s->sort_temp.n, nullptr, (const float*)s->pos.p, N, &s->box, s->sorter_grid,
@@ -535,7 +559,8 @@ static void sorter_update(b200_system* s)
     in.tag = s->tag.p; in.net_force = (float*)s->net_force.p;
     out.pos = (float*)s->pos_alt.p; out.vel = (float*)s->vel_alt.p; out.accel = (float*)s->accel_alt.p;
     out.image = (int*)s->image_alt.p; out.tag = s->tag_alt.p; out.net_force = (float*)s->net_force_alt.p;
-    CUDA_OK(b200_sfc_apply_sorted_order(&out, &in, s->rtag.p, s->sort_order.p, N, s->stream));
+    // global tags exceed the local capacity under domain decomposition: no reverse-lookup table there
+    CUDA_OK(b200_sfc_apply_sorted_order(&out, &in, s->mg ? nullptr : s->rtag.p, s->sort_order.p, N, s->stream));
     // copy back instead of swapping pointers: the captured step graph keeps its baked addresses
     CUDA_OK(cudaMemcpyAsync(s->pos.p, s->pos_alt.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->vel.p, s->vel_alt.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
@@ -809,6 +834,47 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     }
 } // namespace b200
 
+#include "engine_mg.inl"
+
+namespace b200
+{
+static void sys_open_device(b200_system* s)
+    {
+    int ndev = 0;
+    CUDA_OK(cudaGetDeviceCount(&ndev));
+    if (ndev == 0) throw std::runtime_error("no CUDA device: hoomd_b200 has no CPU fallback");
+    CUDA_OK(cudaSetDevice(s->device));
+    CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    }
+
+// per-particle arrays sized for the local capacity; pos / pos_alt / tag are allocated by the caller (they carry the
+// ghost region under domain decomposition)
+static void sys_alloc_common(b200_system* s)
+    {
+    const unsigned int N = s->N, C = s->Ncap;
+    s->vel.alloc(C); s->net_force.alloc(C); s->accel.alloc(C); s->image.alloc(C);
+    s->rtag.alloc(C); s->last_pos.alloc(C);
+    s->virial_pitch = C + (16 - (C & 15)); // GPUArray 2D pitch rule (hoomd/GPUArray.h:424-425)
+    s->net_virial.alloc(6 * (size_t)s->virial_pitch);
+    std::vector<unsigned int> ident(C);
+    for (unsigned int i = 0; i < C; i++) ident[i] = i;
+    s->tag.upload(ident.data(), N, s->stream);
+    s->rtag.upload(ident.data(), N, s->stream);
+    // default mass 1 (ParticleData ctor)
+    std::vector<float4> v(C, make_float4(0.0f, 0.0f, 0.0f, 1.0f));
+    s->vel.upload(v.data(), C, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    s->d_flag.alloc(4);
+    s->d_state.alloc(1);
+    s->d_req_size.alloc(1);
+    s->cl_conditions.alloc(3);
+    CUDA_OK(cudaHostAlloc((void**)&s->h_flag, 4 * sizeof(unsigned int), cudaHostAllocDefault));
+    CUDA_OK(cudaHostAlloc((void**)&s->h_state, sizeof(StepState), cudaHostAllocDefault));
+    s->th_partial.alloc(9 * 1024);
+    s->th_out.alloc(16);
+    }
+} // namespace b200
+
 // ---- C ABI --------------------------------------------------------------------------------------------------------------
 #define SYS_TRY(s) (s)->error.clear(); try { CUDA_OK(cudaSetDevice((s)->device));
 #define SYS_CATCH(s) } catch (const std::exception& e) { (s)->error = e.what(); cudaGetLastError(); return 1; } return 0;
@@ -821,35 +887,17 @@ b200_system* b200_sys_create(unsigned int N, const b200_box* box, unsigned int n
     s->device = device;
     try
         {
-        int ndev = 0;
-        CUDA_OK(cudaGetDeviceCount(&ndev));
-        if (ndev == 0) throw std::runtime_error("no CUDA device: hoomd_b200 has no CPU fallback");
-        CUDA_OK(cudaSetDevice(device));
-        CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+        sys_open_device(s);
         s->N = N;
+        s->Ncap = N;
+        s->Gcap = 0;
         s->ntypes = ntypes ? ntypes : 1;
         s->box = *box;
-        s->pos.alloc(N); s->vel.alloc(N); s->net_force.alloc(N); s->accel.alloc(N); s->image.alloc(N);
-        s->tag.alloc(N); s->rtag.alloc(N); s->last_pos.alloc(N);
+        s->global_box = *box;
+        s->pos.alloc(N);
         s->pos_alt.alloc(N); // ping-pong partner of pos (device-driven stepping) and the sorter's gather target
-        s->virial_pitch = N + (16 - (N & 15)); // GPUArray 2D pitch rule (hoomd/GPUArray.h:424-425)
-        s->net_virial.alloc(6 * (size_t)s->virial_pitch);
-        std::vector<unsigned int> ident(N);
-        for (unsigned int i = 0; i < N; i++) ident[i] = i;
-        s->tag.upload(ident.data(), N, s->stream);
-        s->rtag.upload(ident.data(), N, s->stream);
-        // default mass 1 (ParticleData ctor)
-        std::vector<float4> v(N, make_float4(0.0f, 0.0f, 0.0f, 1.0f));
-        s->vel.upload(v.data(), N, s->stream);
-        CUDA_OK(cudaStreamSynchronize(s->stream));
-        s->d_flag.alloc(4);
-        s->d_state.alloc(1);
-        s->d_req_size.alloc(1);
-        s->cl_conditions.alloc(3);
-        CUDA_OK(cudaHostAlloc((void**)&s->h_flag, 4 * sizeof(unsigned int), cudaHostAllocDefault));
-        CUDA_OK(cudaHostAlloc((void**)&s->h_state, sizeof(StepState), cudaHostAllocDefault));
-        s->th_partial.alloc(9 * 1024);
-        s->th_out.alloc(16);
+        s->tag.alloc(N);
+        sys_alloc_common(s);
         }
     catch (const std::exception& e)
         {
@@ -858,12 +906,106 @@ b200_system* b200_sys_create(unsigned int N, const b200_box* box, unsigned int n
     return s;
     }
 
+b200_system* b200_sys_create_mg(const b200_mg_params* p)
+    {
+    b200_system* s = new b200_system;
+    s->device = p->device;
+    try
+        {
+        sys_open_device(s);
+        s->ntypes = p->ntypes ? p->ntypes : 1;
+        mg_setup(s, *p);
+        sys_alloc_common(s);
+        mg_bind_local(s);
+        }
+    catch (const std::exception& e)
+        {
+        s->error = e.what();
+        }
+    return s;
+    }
+
+int b200_sys_mg_export(b200_system* s, unsigned char* handle64, b200_box* local_box, unsigned int* caps3)
+    {
+    SYS_TRY(s)
+    if (!s->mg) throw std::runtime_error("comm: not a domain-decomposed system");
+    cudaIpcMemHandle_t h;
+    CUDA_OK(cudaIpcGetMemHandle(&h, s->slab));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    memcpy(handle64, &h, 64);
+    if (local_box) *local_box = s->box;
+    if (caps3)
+        {
+        caps3[0] = s->Ncap;
+        caps3[1] = s->Gcap;
+        caps3[2] = s->mgc.mig_cap;
+        }
+    SYS_CATCH(s)
+    }
+
+int b200_sys_mg_connect(b200_system* s, const unsigned char* handles)
+    {
+    SYS_TRY(s)
+    if (!s->mg) throw std::runtime_error("comm: not a domain-decomposed system");
+    mg_connect(s, handles);
+    SYS_CATCH(s)
+    }
+
+unsigned int b200_sys_get_n(b200_system* s) { return s->N; }
+
+int b200_sys_set_tags(b200_system* s, const unsigned int* tags)
+    {
+    SYS_TRY(s)
+    s->tag.upload(tags, s->N, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_mg_stats(b200_system* s, unsigned long long* out8)
+    {
+    SYS_TRY(s)
+    if (!s->mg) throw std::runtime_error("comm: not a domain-decomposed system");
+    CUDA_OK(cudaMemcpyAsync(s->h_ms, s->d_ms.p, sizeof(MgState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    out8[0] = s->N;
+    out8[1] = s->Ncap;
+    out8[2] = s->Gcap;
+    out8[3] = s->h_ms->max_N;
+    out8[4] = s->h_ms->max_send;
+    out8[5] = s->h_ms->max_gsend;
+    unsigned long long g = 0;
+    for (int d = 0; d < MG_NDIR; d++) g += std::min(s->h_ms->gsend_cnt[d], s->mgc.seg_cap[d]);
+    out8[6] = g;
+    out8[7] = s->h_ms->epoch[0];
+    SYS_CATCH(s)
+    }
+
+/* ghost tags + positions as they currently sit in this rank's ghost region (validation) */
+int b200_sys_mg_get_ghosts(b200_system* s, float* pos4, unsigned int* tag)
+    {
+    SYS_TRY(s)
+    if (!s->mg) throw std::runtime_error("comm: not a domain-decomposed system");
+    if (pos4)
+        CUDA_OK(cudaMemcpyAsync(pos4, s->pos.p + s->Ncap, sizeof(float4) * s->Gcap, cudaMemcpyDeviceToHost, s->stream));
+    if (tag)
+        CUDA_OK(cudaMemcpyAsync(tag, s->tag.p + s->Ncap, sizeof(unsigned int) * s->Gcap, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
 void b200_sys_destroy(b200_system* s)
     {
     if (!s) return;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     invalidate_graph(s);
+    if (s->mg)
+        {
+        for (unsigned int q = 0; q < s->mgc.world; q++)
+            if (q != s->mgc.rank && s->peer_base[q]) cudaIpcCloseMemHandle(s->peer_base[q]);
+        if (s->slab) cudaFree(s->slab);
+        if (s->h_ms) cudaFreeHost(s->h_ms);
+        }
     if (s->h_flag) cudaFreeHost(s->h_flag);
     if (s->h_state) cudaFreeHost(s->h_state);
     cudaStream_t st = s->stream;
@@ -938,17 +1080,20 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     s->d_Nmax.alloc(nt);
     s->d_Nmax.upload(s->h_Nmax.data(), nt, s->stream);
     s->nl_conditions.alloc(nt);
-    s->head_list.alloc(s->N);
-    s->n_neigh.alloc(s->N);
-    s->nlist.alloc(8 * (size_t)s->N);
+    s->head_list.alloc(s->Ncap);
+    s->n_neigh.alloc(s->Ncap);
+    s->nlist.alloc(8 * (size_t)s->Ncap);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     // CellList: nominal width = max r_cut + r_buff (NeighborListBinned.cc:56-76), radius 1, no ghosts (single domain)
     s->nominal_width = s->rcut_max_max + s->r_buff;
-    b200_cell_list_dimensions(&s->box, s->nominal_width, 1, 0.0f, &s->dim, s->ghost_width);
+    if (s->mg && s->nominal_width > s->r_ghost * 1.000001f)
+        throw std::runtime_error("comm: r_cut + r_buff exceeds the ghost layer width the domain was created with");
+    b200_cell_list_dimensions(&s->box, s->nominal_width, 1, s->mg ? s->nominal_width : 0.0f, &s->dim, s->ghost_width);
     const size_t ncells = (size_t)s->dim.x * s->dim.y * s->dim.z;
     s->cell_count.alloc(ncells); s->cell_start.alloc(ncells + 1);
-    s->cell_xyzf.alloc(s->N); s->cell_type.alloc(s->N);
-    s->particle_cell.alloc(s->N); s->particle_slot.alloc(s->N); s->scratch_idx.alloc(s->N);
+    const size_t ntot = (size_t)s->Ncap + s->Gcap;
+    s->cell_xyzf.alloc(ntot); s->cell_type.alloc(ntot);
+    s->particle_cell.alloc(ntot); s->particle_slot.alloc(ntot); s->scratch_idx.alloc(ntot);
     s->have_nlist = true;
     s->force_update = true;
     s->cl_force = true;
@@ -1037,7 +1182,10 @@ int b200_sys_compute_nlist(b200_system* s, unsigned int ts)
 int b200_sys_compute_forces(b200_system* s, unsigned int ts)
     {
     SYS_TRY(s)
-    compute_net_force(s, ts);
+    if (s->mg)
+        mg_prep_run(s, ts);
+    else
+        compute_net_force(s, ts);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     SYS_CATCH(s)
     }
@@ -1046,7 +1194,14 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
     {
     SYS_TRY(s)
     s->kernels_last_run = 0;
-    prep_run(s, s->timestep);
+    if (s->mg)
+        {
+        if (!s->have_integrator || !s->method) throw std::runtime_error("integrate: no integration method set");
+        if (s->use_graph < 2) throw std::runtime_error("comm: domain decomposition needs device-driven stepping");
+        mg_prep_run(s, s->timestep);
+        }
+    else
+        prep_run(s, s->timestep);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     cudaEvent_t e0, e1;
     CUDA_OK(cudaEventCreate(&e0));
@@ -1064,7 +1219,9 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
             }
         unsigned int chunk = std::min(remaining, chunk_max);
         if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
-        if (s->use_graph)
+        if (s->mg)
+            mg_run_chunk(s, chunk);
+        else if (s->use_graph)
             run_chunk_device(s, chunk);
         else
             for (unsigned int k = 0; k < chunk; k++) host_step(s);

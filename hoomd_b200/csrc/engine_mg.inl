@@ -1,0 +1,397 @@
+// Multi-GPU half of the engine (included by engine.cu): DomainDecomposition + Communicator driven from the device.
+// Reference semantics: hoomd/DomainDecomposition.cc:323-372 (grid), :531-557 (local box: non-periodic along split axes),
+// hoomd/Communicator.cc:1300-1366 (communicate(): migrate + exchange ghosts on rebuild steps, update ghosts otherwise),
+// hoomd/md/NeighborListGPU.cc:117-122 (global vote on the distance check).
+namespace b200
+{
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static void mg_check_errors(b200_system* s)
+    {
+    CUDA_OK(cudaMemcpyAsync(s->h_ms, s->d_ms.p, sizeof(MgState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    const unsigned int e = s->h_ms->error;
+    if (!e) return;
+    std::string msg = "comm:";
+    if (e & 1u) msg += " migration mailbox overflow (too many particles left the domain in one rebuild);";
+    if (e & 2u) msg += " ghost segment overflow (raise capacity_factor);";
+    if (e & 4u) msg += " local particle capacity exceeded (raise Ncap);";
+    if (e & 8u) msg += " a peer rank did not reach the barrier within 4 s;";
+    throw std::runtime_error(msg);
+    }
+
+// geometry, capacities and the slab; peers are attached later by b200_sys_mg_connect
+static void mg_setup(b200_system* s, const b200_mg_params& p)
+    {
+    if (p.world < 1 || p.world > (unsigned int)MG_MAX_RANKS) throw std::runtime_error("comm: 1..8 ranks supported");
+    if (p.grid[0] * p.grid[1] * p.grid[2] != p.world) throw std::runtime_error("comm: grid does not match the world size");
+    if (!box_is_orthorhombic(p.global_box)) throw std::runtime_error("comm: orthorhombic boxes only");
+    s->mg = true;
+    s->global_box = p.global_box;
+    s->r_ghost = p.r_ghost;
+    MgConst& c = s->mgc;
+    memset(&c, 0, sizeof(c));
+    c.world = p.world;
+    c.rank = p.rank;
+    unsigned int r = p.rank;
+    for (int a = 0; a < 3; a++)
+        {
+        s->mg_grid[a] = p.grid[a];
+        s->mg_pos[a] = r % p.grid[a];
+        r /= p.grid[a];
+        }
+    // local box: uniform cut planes (DomainDecomposition ctor with uniform fractions), non-periodic along split axes
+    float lo[3], hi[3];
+    unsigned char per[3];
+    for (int a = 0; a < 3; a++)
+        {
+        const float L = p.global_box.L[a], glo = p.global_box.lo[a];
+        c.split[a] = p.grid[a] > 1;
+        c.Lg[a] = L;
+        c.glo[a] = glo;
+        c.ghi[a] = p.global_box.hi[a];
+        if (c.split[a])
+            {
+            lo[a] = glo + L * ((float)s->mg_pos[a] / (float)p.grid[a]);
+            hi[a] = (s->mg_pos[a] + 1 == p.grid[a]) ? p.global_box.hi[a]
+                                                    : glo + L * ((float)(s->mg_pos[a] + 1) / (float)p.grid[a]);
+            per[a] = 0;
+            if (hi[a] - lo[a] < 2.0f * p.r_ghost)
+                throw std::runtime_error("comm: domain narrower than two ghost layers");
+            }
+        else
+            {
+            lo[a] = glo;
+            hi[a] = p.global_box.hi[a];
+            per[a] = p.global_box.periodic[a];
+            }
+        c.lo[a] = lo[a];
+        c.hi[a] = hi[a];
+        }
+    b200_box_init_lohi(&s->box, lo, hi, per);
+    c.r_ghost = p.r_ghost;
+    // neighbors, periodic shifts, ghost segments (identical on every rank: uniform domains)
+    const double rho = (double)p.N_global
+                       / ((double)p.global_box.L[0] * p.global_box.L[1] * p.global_box.L[2]);
+    const double cf = p.capacity_factor > 0.0f ? p.capacity_factor : 1.5;
+    unsigned int off = 0;
+    for (int d = 0; d < MG_NDIR; d++)
+        {
+        const int dd[3] = {d % 3 - 1, (d / 3) % 3 - 1, d / 9 - 1};
+        bool used = d != MG_DIR_STAY;
+        int np[3];
+        double vol = 1.0;
+        for (int a = 0; a < 3; a++)
+            {
+            if (dd[a] != 0 && !c.split[a]) used = false;
+            int q = (int)s->mg_pos[a] + dd[a];
+            c.shift[d][a] = 0.0f;
+            if (q < 0) { q += (int)p.grid[a]; c.shift[d][a] = c.Lg[a]; }
+            if (q >= (int)p.grid[a]) { q -= (int)p.grid[a]; c.shift[d][a] = -c.Lg[a]; }
+            np[a] = q;
+            vol *= dd[a] != 0 ? (double)p.r_ghost : (double)(hi[a] - lo[a]);
+            }
+        c.dir_rank[d] = used ? (int)((np[2] * p.grid[1] + np[1]) * p.grid[0] + np[0]) : -1;
+        c.seg_off[d] = off;
+        c.seg_cap[d] = used ? (unsigned int)(cf * rho * vol) + 1024u : 0u;
+        off += c.seg_cap[d];
+        if (!used)
+            for (int a = 0; a < 3; a++) c.shift[d][a] = 0.0f;
+        }
+    s->Gcap = off;
+    c.Gcap = off;
+    const unsigned int expect = p.N_global / p.world + 1;
+    s->Ncap = p.Ncap ? p.Ncap : (unsigned int)(1.25 * expect) + 8192u;
+    if (p.N_local > s->Ncap) throw std::runtime_error("comm: more local particles than Ncap");
+    c.Ncap = s->Ncap;
+    c.mig_cap = std::max(4096u, s->Ncap / 32u);
+    s->N = p.N_local;
+    // slab
+    const size_t ntot = (size_t)s->Ncap + s->Gcap;
+    size_t o = 0;
+    s->off_posA = o; o = align_up(o + ntot * sizeof(float4), 256);
+    s->off_posB = o; o = align_up(o + ntot * sizeof(float4), 256);
+    s->off_tag = o; o = align_up(o + ntot * sizeof(unsigned int), 256);
+    s->off_mig = o; o = align_up(o + (size_t)MG_NDIR * c.mig_cap * sizeof(MigElem), 256);
+    s->off_migcnt = o; o = align_up(o + MG_NDIR * sizeof(unsigned int), 256);
+    s->off_flags = o; o = align_up(o + (size_t)MG_NBARRIER * 2 * MG_MAX_RANKS * sizeof(unsigned long long), 256);
+    s->slab_bytes = o;
+    CUDA_OK(cudaMalloc(&s->slab, s->slab_bytes));
+    CUDA_OK(cudaMemset(s->slab, 0, s->slab_bytes));
+    CUDA_OK(cudaDeviceSynchronize());
+    char* base = (char*)s->slab;
+    s->pos.view((float4*)(base + s->off_posA), ntot);
+    s->pos_alt.view((float4*)(base + s->off_posB), ntot);
+    s->tag.view((unsigned int*)(base + s->off_tag), ntot);
+    c.my_mig = (MigElem*)(base + s->off_mig);
+    c.my_mig_cnt = (unsigned int*)(base + s->off_migcnt);
+    // rank-local scratch
+    s->d_ms.alloc(1);
+    CUDA_OK(cudaHostAlloc((void**)&s->h_ms, sizeof(MgState), cudaHostAllocDefault));
+    s->holes.alloc(s->Ncap); s->low_holes.alloc(s->Ncap); s->hole_mark.alloc(s->Ncap);
+    s->plan_src.alloc(std::max(1u, s->Gcap));
+    s->slot_dir.alloc(std::max(1u, s->Gcap));
+    std::vector<unsigned char> sd(std::max(1u, s->Gcap), 0);
+    for (int d = 0; d < MG_NDIR; d++)
+        for (unsigned int k = 0; k < c.seg_cap[d]; k++) sd[c.seg_off[d] + k] = (unsigned char)d;
+    s->slot_dir.upload(sd.data(), sd.size(), s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    }
+
+static void mg_bind_local(b200_system* s)
+    {
+    MgLocal& l = s->mgl;
+    l.ms = s->d_ms.p;
+    l.st = s->d_state.p;
+    l.vel = s->vel.p;
+    l.accel = (float*)s->accel.p;
+    l.image = (int*)s->image.p;
+    l.tag = s->tag.p;
+    l.holes = s->holes.p;
+    l.low_holes = s->low_holes.p;
+    l.hole_mark = s->hole_mark.p;
+    l.plan_src = s->plan_src.p;
+    l.slot_dir = s->slot_dir.p;
+    }
+
+static void mg_connect(b200_system* s, const unsigned char* handles)
+    {
+    MgConst& c = s->mgc;
+    for (unsigned int q = 0; q < c.world; q++)
+        {
+        if (q == c.rank)
+            s->peer_base[q] = s->slab;
+        else
+            {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, handles + (size_t)q * sizeof(cudaIpcMemHandle_t), sizeof(h));
+            CUDA_OK(cudaIpcOpenMemHandle(&s->peer_base[q], h, cudaIpcMemLazyEnablePeerAccess));
+            }
+        c.flags[q] = (unsigned long long*)((char*)s->peer_base[q] + s->off_flags);
+        }
+    for (int d = 0; d < MG_NDIR; d++)
+        {
+        if (c.dir_rank[d] < 0) continue;
+        char* pb = (char*)s->peer_base[c.dir_rank[d]];
+        c.peer_posA[d] = (float4*)(pb + s->off_posA);
+        c.peer_posB[d] = (float4*)(pb + s->off_posB);
+        c.peer_tag[d] = (unsigned int*)(pb + s->off_tag);
+        c.peer_mig[d] = (MigElem*)(pb + s->off_mig) + (size_t)d * c.mig_cap;
+        c.peer_mig_cnt[d] = (unsigned int*)(pb + s->off_migcnt) + d;
+        }
+    mg_bind_local(s);
+    s->mg_connected = true;
+    invalidate_graph(s);
+    }
+
+// the rebuild bracket of one rank: migrate -> ghost plan + first ghost write -> cell list -> neighbor list
+static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float4* pos, int buffer)
+    {
+    CUDA_OK(launch_mg_migrate(s->mgc, s->mgl, pos, enable, s->stream));
+    CUDA_OK(launch_mg_ghost_plan(s->mgc, s->mgl, pos, buffer, enable, s->stream));
+    b200_cell_list_args ca;
+    cell_list_args(s, ca);
+    ca.d_pos = (const float*)pos;
+    CUDA_OK(launch_cell_list(&ca, enable, s->stream, &s->d_state.p->N));
+    b200_nlist_args na;
+    nlist_args(s, na);
+    na.d_pos = (const float*)pos;
+    CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
+    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    }
+constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 2;
+
+static void mg_upload_state(b200_system* s, unsigned int steps_left)
+    {
+    StepState& st = *s->h_state;
+    memset(&st, 0, sizeof(st));
+    st.timestep = s->timestep;
+    st.force_update = s->force_update ? 1u : 0u;
+    st.last_updated = s->last_updated_tstep;
+    st.every = s->every;
+    st.r_buff_tiny = (s->r_buff < 1e-6f) ? 1u : 0u;
+    st.ntypes = s->ntypes;
+    st.steps_left = steps_left;
+    st.N = s->N;
+    CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
+    }
+
+static void mg_download_state(b200_system* s)
+    {
+    CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    s->N = s->h_state->N;
+    }
+
+// prepRun under domain decomposition: a forced, stream-launched rebuild (every rank runs the same sequence, so the
+// barriers inside pair up), Nmax growth as in NeighborList::compute, then the pair force on the local particles
+static void mg_prep_run(b200_system* s, unsigned int ts)
+    {
+    if (!s->mg_connected) throw std::runtime_error("comm: peers not attached (b200_sys_mg_connect)");
+    if (s->ntypes != 1) throw std::runtime_error("comm: one particle type supported under domain decomposition");
+    if (s->force_update || s->nl_first_compute)
+        {
+        nlist_build_head_list(s);
+        mg_upload_state(s, 0);
+        CUDA_OK(launch_mg_migrate(s->mgc, s->mgl, s->pos.p, nullptr, s->stream));
+        CUDA_OK(launch_mg_ghost_plan(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        mg_download_state(s);
+        mg_check_errors(s);
+        bool overflowed;
+        do
+            {
+            b200_cell_list_args ca;
+            cell_list_args(s, ca);
+            CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, &s->d_state.p->N));
+            cell_list_check_conditions(s);
+            b200_nlist_args na;
+            nlist_args(s, na);
+            CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
+            overflowed = nlist_check_conditions(s);
+            if (overflowed)
+                {
+                // head room: a later overflow inside a device-driven chunk cannot be replayed across ranks
+                for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 5u / 4u) + 7u) & ~7u;
+                s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
+                CUDA_OK(cudaStreamSynchronize(s->stream));
+                s->num_overflows += 1;
+                nlist_build_head_list(s);
+                CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+                }
+            } while (overflowed);
+        s->force_update = false;
+        s->nl_first_compute = false;
+        s->cl_first = false;
+        s->cl_force = false;
+        s->num_forced += 1;
+        s->last_updated_tstep = ts;
+        s->kernels_last_run += MG_REBUILD_KERNELS;
+        }
+    s->nl_last_computed = ts;
+    s->last_checked_tstep = ts;
+    b200_pair_args a;
+    pair_args(s, a);
+    CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
+    s->kernels_last_run += 1;
+    if (!s->accel_set)
+        {
+        CUDA_OK(launch_compute_accel((float*)s->accel.p, s->net_force.p, s->vel.p, s->N, s->stream));
+        s->kernels_last_run += 1;
+        s->accel_set = true;
+        }
+    }
+
+// graph of two MD steps:  barrier -> IF{rebuild from A} -> k_md_step(A->B) -> ghosts(B)
+//                         barrier -> IF{rebuild from B} -> k_md_step(B->A) -> ghosts(A)
+static void mg_build_graph(b200_system* s)
+    {
+#if (CUDART_VERSION >= 12040)
+    FusedStepArgs fa;
+    fused_args(s, fa);
+    const unsigned int* enable = &s->d_state.p->need_rebuild;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool capturing = false;
+    try
+        {
+        CUDA_OK(cudaGraphCreate(&graph, 0));
+        cudaGraphConditionalHandle h0, h1;
+        CUDA_OK(cudaGraphConditionalHandleCreate(&h0, graph, 0, cudaGraphCondAssignDefault));
+        CUDA_OK(cudaGraphConditionalHandleCreate(&h1, graph, 0, cudaGraphCondAssignDefault));
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
+        cudaGraph_t body0 = add_if_node(s, graph, h0);
+        enqueue_md_step(s, fa, 0, 0ull, 0);
+        CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+        CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
+        cudaGraph_t body1 = add_if_node(s, graph, h1);
+        enqueue_md_step(s, fa, 1, 0ull, 0);
+        CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        cudaGraph_t out = nullptr;
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body0, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        mg_enqueue_rebuild(s, enable, s->pos.p, 0);
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body1, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
+        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+        capturing = false;
+        CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+        }
+    catch (...)
+        {
+        if (capturing)
+            {
+            cudaGraph_t junk = nullptr;
+            cudaStreamEndCapture(s->stream, &junk);
+            }
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        throw;
+        }
+    s->graph = graph;
+    s->graph_exec = exec;
+    s->graph_uses_cond = 1;
+    s->graph_valid = true;
+#else
+    throw std::runtime_error("comm: conditional graph nodes need CUDA >= 12.4");
+#endif
+    }
+
+static void mg_run_chunk(b200_system* s, unsigned int chunk)
+    {
+    if (s->force_update) nlist_build_head_list(s);
+    if (s->use_graph != 3 && !s->graph_valid)
+        {
+        invalidate_graph(s);
+        mg_build_graph(s);
+        }
+    mg_upload_state(s, chunk);
+    FusedStepArgs fa;
+    fused_args(s, fa);
+    // prologue: step one of the first update() + its ghost update; the first barrier of the graph takes the vote
+    CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+    CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+    const unsigned int nreplay = (chunk + 1) / 2;
+    if (s->use_graph == 3)
+        {
+        const unsigned int* enable = &s->d_state.p->need_rebuild;
+        for (unsigned int k = 0; k < nreplay; k++)
+            {
+            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+            mg_enqueue_rebuild(s, enable, s->pos.p, 0);
+            enqueue_md_step(s, fa, 0, 0ull, 0);
+            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+            mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
+            enqueue_md_step(s, fa, 1, 0ull, 0);
+            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+            }
+        }
+    else
+        for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+    mg_download_state(s);
+    const StepState& st = *s->h_state;
+    mg_check_errors(s);
+    cell_list_check_conditions(s);
+    if (st.overflow)
+        throw std::runtime_error("nlist: neighbor list overflow inside a multi-GPU chunk (not replayable across ranks); "
+                                 "the engine pre-sizes Nmax with 25% head room");
+    const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
+    s->kernels_last_run += 2ull + 6ull * nreplay + MG_REBUILD_KERNELS * rebuilds;
+    s->timestep = st.timestep;
+    s->last_updated_tstep = st.last_updated;
+    s->num_updates += st.num_updates;
+    s->num_forced += st.num_forced;
+    s->force_update = st.force_update != 0;
+    s->last_checked_tstep = st.timestep;
+    s->last_check_result = st.need_rebuild != 0;
+    s->nl_last_computed = st.timestep;
+    s->nl_first_compute = false;
+    }
+} // namespace b200

@@ -10,6 +10,7 @@
 #include "integrate_body.cuh"
 #include "pair_body.cuh"
 #include "kernels.h"
+#include "decide.cuh"
 
 namespace b200
 {
@@ -18,10 +19,12 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
                                                         const float4* __restrict__ last_pos,
                                                         const float* __restrict__ rcut_max, unsigned int N, Box box,
                                                         float dt, float r_buff, bool limit, float limit_val,
-                                                        bool zero_force, StepState* __restrict__ st)
+                                                        bool zero_force, StepState* __restrict__ st,
+                                                        const unsigned int* __restrict__ d_N)
     {
     unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
     bool moved = false;
+    if (d_N) N = *d_N;
     if (j < N)
         {
         float4 p = pos[j];
@@ -44,35 +47,6 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
         moved = dot_exact(dx) >= maxsq;
         }
     if (__any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) st->moved = 1u; // benign same-value race
-    }
-
-// NeighborList::needsUpdating(ts+1) for the force evaluation that follows (update(ts) computes forces at ts+1)
-__device__ __forceinline__ void decide_body(StepState* st)
-    {
-    const unsigned int ts1 = st->timestep + 1u;
-    bool result;
-    if (st->force_update)
-        {
-        result = true;
-        st->force_update = 0u;
-        st->num_forced += 1u;
-        st->last_updated = ts1;
-        }
-    else if (ts1 < st->last_updated + st->every) // !shouldCheckDistance
-        result = false;
-    else
-        {
-        result = st->r_buff_tiny || *((volatile unsigned int*)&st->moved);
-        if (result)
-            {
-            st->last_updated = ts1;
-            st->num_updates += 1u;
-            }
-        }
-    st->moved = 0u;
-    st->need_rebuild = result ? 1u : 0u;
-    st->ts_step_two = st->timestep;
-    st->timestep = ts1;
     }
 
 __global__ void k_decide(StepState* st)
@@ -116,6 +90,8 @@ template<class Evaluator> struct MdStepArgs
     unsigned int N; Box box; float dt; float r_buff;
     int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
     int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
+    const unsigned int* d_N;  // multi-GPU: live local particle count (N is the capacity the grid was sized for)
+    int mg;                   // multi-GPU: leave the rebuild decision to the all-ranks step barrier
     StepState* st; cudaGraphConditionalHandle handle; int use_cond;
     };
 
@@ -134,6 +110,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
     const bool last = steps_left == 1;
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
+    const unsigned int N = a.d_N ? *a.d_N : a.N;
 
     // ---- phase 1: TPP lanes per particle walk its neighbor list (PotentialPair::computeForces) ----
     PairTables<Evaluator> T;
@@ -142,7 +119,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
         const unsigned int slot = threadIdx.x / TPP;
         const unsigned int i = blockIdx.x * PPB + slot;
         const unsigned int sub = threadIdx.x % TPP;
-        const bool active = i < a.N;
+        const bool active = i < N;
         const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         const unsigned int size = active ? a.n_neigh[i] : 0u;
         const unsigned int head = active ? a.head_list[i] : 0u;
@@ -167,7 +144,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
     // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
     bool moved = false;
     const unsigned int i = blockIdx.x * PPB + threadIdx.x;
-    if (threadIdx.x < PPB && i < a.N)
+    if (threadIdx.x < PPB && i < N)
         {
         const float4 F = s_force[threadIdx.x];
         const float4 pi4 = a.pos_in[i];
@@ -223,7 +200,9 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
             st->steps_left = steps_left - 1u;
-            if (!last)
+            if (a.mg)
+                ; // the vote needs every rank: k_mg_step_barrier decides
+            else if (!last)
                 decide_body(st);
             else
                 {
@@ -260,7 +239,7 @@ cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStr
     k_fused_step_one<<<(a.N + 255) / 256, 256, 0, stream>>>(a.pos, a.vel, (const float3s*)a.accel, (int3*)a.image,
                                                             a.last_pos, a.rcut_max, a.N, make_box(a.box), a.dt,
                                                             a.r_buff, nve && a.limit, a.limit_val, nve && a.zero_force,
-                                                            st);
+                                                            st, a.d_N);
     return cudaGetLastError();
     }
 
@@ -336,6 +315,7 @@ cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, c
     a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
     a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
     a.copy_pos_on_last = copy_pos_on_last;
+    a.d_N = fa.d_N; a.mg = fa.mg;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     const bool v = pa.compute_virial != 0;
     const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);

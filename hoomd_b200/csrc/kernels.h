@@ -26,9 +26,12 @@ struct StepState
     unsigned int _pad0;
     unsigned long long ticket;    // k_md_step: low word = CTAs finished, high word = CTAs that saw a mover (one atomic)
     unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
+    unsigned int N;               // local particle count (multi-GPU: changes at every migration)
     };
 
-cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream);
+// d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
+cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
+                             const unsigned int* d_N = nullptr);
 cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream);
 unsigned int pick_pair_tpp(unsigned int N);
 
@@ -42,6 +45,8 @@ struct FusedStepArgs
     int method;                   // 1 = NVE, 2 = Langevin
     int limit; float limit_val; int zero_force;
     float kT; unsigned int seed; int noiseless_t;
+    const unsigned int* d_N;      // multi-GPU: live local particle count (N above is then the capacity); else NULL
+    int mg;                       // multi-GPU: the rebuild decision is taken by the all-ranks step barrier, not here
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);

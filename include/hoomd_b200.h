@@ -342,6 +342,44 @@ B200_API int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters,
 /* ComputeThermo at the current step: out = {KE, PE, temperature, pressure, ndof} */
 B200_API int b200_sys_get_thermo(b200_system* s, double* out5);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Multi-GPU: DomainDecomposition + Communicator(GPU) for one NVSwitch box, one process per GPU.
+ * Replaces hoomd/DomainDecomposition.cc (findDecomposition :323-372 is host arithmetic done by the caller,
+ * calculateLocalBox :531-557) and hoomd/CommunicatorGPU.cc (migrateParticles :1495, exchangeGhosts :1804,
+ * beginUpdateGhosts/finishUpdateGhosts :2500/:2870).  Every rank exports ONE device slab (positions, tags, migration
+ * mailboxes, flag words) as a CUDA IPC handle; the caller all-gathers the handles (torch.distributed / MPI / anything)
+ * and hands them back; from then on ghosts, migrants and barrier flags travel as plain stores over NVLink from inside
+ * the step kernels.  rank = (iz*grid[1] + iy)*grid[0] + ix.  One particle type in this round.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct b200_mg_params
+    {
+    unsigned int world, rank;
+    unsigned int grid[3];        /* ranks per axis (product == world) */
+    b200_box     global_box;
+    unsigned int N_global;       /* total particle count (capacity estimates) */
+    unsigned int N_local;        /* particles this rank starts with */
+    unsigned int Ncap;           /* local capacity, 0 = 1.25 * N_global/world + 8192 */
+    float        r_ghost;        /* ghost layer width = max r_cut + r_buff (NeighborList::getGhostLayerWidth) */
+    float        capacity_factor;/* ghost segment head room over the mean density, 0 = 1.5 */
+    unsigned int ntypes;
+    int          device;
+    } b200_mg_params;
+
+B200_API b200_system* b200_sys_create_mg(const b200_mg_params* p);
+/* handle64: cudaIpcMemHandle_t of this rank's slab; local_box: DomainDecomposition::calculateLocalBox;
+ * caps3 = {Ncap, Gcap, migrants per direction} */
+B200_API int b200_sys_mg_export(b200_system* s, unsigned char* handle64, b200_box* local_box, unsigned int* caps3);
+/* handles: world * 64 bytes in rank order (the own entry is ignored) */
+B200_API int b200_sys_mg_connect(b200_system* s, const unsigned char* handles);
+/* current local particle count (changes with migration); getters/setters move this many entries */
+B200_API unsigned int b200_sys_get_n(b200_system* s);
+/* global tags of the local particles (b200_sys_create numbers them 0..N-1) */
+B200_API int b200_sys_set_tags(b200_system* s, const unsigned int* tags);
+/* out: {N local, Ncap, Gcap, max N seen, max migrants/direction, max ghosts/direction, ghosts sent now, step barriers} */
+B200_API int b200_sys_mg_stats(b200_system* s, unsigned long long* out8);
+/* this rank's ghost region (Gcap entries; unused slots hold x = 1e30): positions and global tags */
+B200_API int b200_sys_mg_get_ghosts(b200_system* s, float* pos4, unsigned int* tag);
+
 #ifdef __cplusplus
 }
 #endif
