@@ -89,19 +89,24 @@ EQUIL_STEPS = None  # --equil-steps override (profiling runs)
 USE_GRAPH = int(os.environ.get("HOOMD_B200_USE_GRAPH", "2"))  # 0 host-driven, 1 plain graph, 2 conditional graph
 
 
+def _lj_snapshot(workload):
+    from hoomd_b200 import workloads
+    n_side, rho, kT, _ = WORKLOADS[workload]
+    return workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
+
+
 def make_state(workload, rank=0):
     """Lattice start + Langevin equilibration ON THE GPU ENGINE (not timed); returns host arrays + box length."""
     import hoomd_b200
-    from hoomd_b200 import workloads
-    n_side, rho, kT, _ = WORKLOADS[workload]
-    pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42 + rank)
+    _, _, kT, _ = WORKLOADS[workload]
+    pos, vel, L = _lj_snapshot(workload)
     s = hoomd_b200.System(pos, (L, L, L), vel4=vel)
     s.setup_lj(r_cut=3.0, r_buff=0.4)
     s.setup_integrator(0.005)
     s.add_langevin(kT, 42)
     s.set_sorter(300)
     s.set_tuning(use_graph=USE_GRAPH)
-    s.run(EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 3000))
+    s.run(EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 2000))
     p = s.particles()
     s.close()
     return p, L
@@ -118,13 +123,31 @@ def new_system(state, L, device=0):
     return s
 
 
+def new_domain_system(workload, local_rank):
+    """N > 1: the same lattice snapshot on every rank, each keeps its sub-domain; Langevin equilibration (untimed,
+    tag-keyed noise => independent of the decomposition), then the NVE integrator on the same device-resident state."""
+    from hoomd_b200 import domain
+    _, _, kT, _ = WORKLOADS[workload]
+    pos, vel, L = _lj_snapshot(workload)
+    s = domain.DomainSystem(pos, (L, L, L), r_ghost=3.4, vel4=vel, device=local_rank)
+    del pos, vel
+    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    s.setup_integrator(0.005)
+    s.add_langevin(kT, 42)
+    s.set_sorter(300)
+    s.set_tuning(use_graph=USE_GRAPH)
+    s.run(EQUIL_STEPS if EQUIL_STEPS is not None else 2000)
+    s.add_nve()
+    return s, L
+
+
 def run_reference(args):
     """reference arm: the reference's own CPU classes on the box's host cores, bounded sample per step."""
     from oracle import ref, oracle_c
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    workload = args.workload
+    workload = args.workload or "lj64k"
     n_side, rho, kT, desc = WORKLOADS[workload]
     from hoomd_b200 import workloads
     md_steps = args.ref_md_steps
@@ -210,7 +233,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default="lj64k", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: lj64k on 1 GPU (BASELINE configs[1]), lj8m domain-decomposed on N > 1 (configs[4])")
+    ap.add_argument("--no-scale-ref", action="store_true", help="skip the 1-GPU 8M-particle reference point")
     ap.add_argument("--md-steps", type=int, default=0, help="MD timesteps per bench step (0 = by workload)")
     ap.add_argument("--ref-md-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -235,14 +260,18 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    workload = args.workload
+    workload = args.workload or ("lj64k" if world == 1 else "lj8m")
     n_side, rho, kT, desc = WORKLOADS[workload]
     N = n_side ** 3
-    md_steps = args.md_steps or (2000 if N <= 100000 else (400 if N <= 2000000 else 100))
+    md_steps = args.md_steps or (2000 if N <= 100000 else (400 if N <= 2000000 else 200))
     hbm_peak, peak_src = peaks()
 
-    state, L = make_state(workload, rank)
-    s = new_system(state, L, device=local_rank)
+    if world == 1:
+        state, L = make_state(workload, rank)
+        s = new_system(state, L, device=local_rank)
+    else:
+        state = None
+        s, L = new_domain_system(workload, local_rank)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -275,9 +304,9 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     tps_rank = md_steps * args.steps / (total_ms * 1e-3)
-    # N > 1 (until the domain-decomposed path lands): independent replicas, aggregate particle-steps
-    tps = tps_rank
+    tps = tps_rank  # one domain-decomposed system: every rank advances the same timesteps
     stats = s.stats()
+    n_local = s.N
 
     # ---- dominant kernel: the single-kernel MD step (pair force + both half steps + distance check), timed live with
     # CUDA events on the engine stream (b200_sys_time_kernel); algorithmic bytes per particle per launch:
@@ -286,10 +315,10 @@ def main():
     step_ms = s.time_kernel(2, 20)
     pair_ms = s.time_kernel(0, 200)
     nlist_ms = s.time_kernel(1, 20)
-    n_neigh = s.nlist()[0]
+    n_neigh = s.nlist(counts_only=True)[0][:n_local]
     nbar = float(n_neigh.mean())
-    step_bytes = (124.0 + 4.0 * nbar) * N
-    step_flops = (40.0 * nbar + 55.0) * N
+    step_bytes = (124.0 + 4.0 * nbar) * n_local
+    step_flops = (40.0 * nbar + 55.0) * n_local
     achieved = step_bytes / (step_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "k_md_step<EvaluatorPairLJ> (force + step two + step one + distance check)",
                 "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
@@ -297,11 +326,12 @@ def main():
                 "mean_neighbors": nbar,
                 "fp32_tflops": step_flops / (step_ms * 1e-3) / 1e12,
                 "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12,
-                "pair_kernel_ms": pair_ms, "pair_kernel_gbs": (40.0 + 4.0 * nbar) * N / (pair_ms * 1e-3) / 1e9,
+                "pair_kernel_ms": pair_ms, "pair_kernel_gbs": (40.0 + 4.0 * nbar) * n_local / (pair_ms * 1e-3) / 1e9,
                 "nlist_rebuild_ms": nlist_ms,
-                "step_hbm_frac": BYTES_PER_PARTICLE_STEP * N * tps_rank / (hbm_peak * 1e9),
-                "note": "working set at 64k is L2-resident (15 MB < 126 MB L2): the step is launch/latency bound, "
-                        "the HBM fraction is low by construction (SURVEY 8d)"}
+                "step_hbm_frac": BYTES_PER_PARTICLE_STEP * n_local * tps_rank / (hbm_peak * 1e9),
+                "note": ("working set at 64k is L2-resident (15 MB < 126 MB L2): the step is launch/latency bound, "
+                         "the HBM fraction is low by construction (SURVEY 8d)") if N <= 100000 else
+                        "per-rank figures (local particles of rank 0)"}
 
     # ---- end to end through the host-buffer API ----------------------------------------------------------------------
     host = s.particles()
@@ -325,18 +355,43 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(state, L)
 
+    # 1-GPU reference point of the multi-GPU workload (BASELINE configs[4]: parallel efficiency = TPS_n / (n * TPS_1)
+    # with TPS_1 measured at 8M on one GPU), short run, reported beside the headline
+    scale_ref = None
+    mg_stats = None
+    if world == 1 and workload == "lj64k" and not args.no_scale_ref:
+        s.close()
+        s = None
+        st8, L8 = make_state("lj8m")
+        s8 = new_system(st8, L8, device=local_rank)
+        s8.run(200)
+        ms8 = min(s8.run(200)[1] for _ in range(2))
+        scale_ref = {"workload": WORKLOADS["lj8m"][3], "n_gpus": 1, "value": 200.0 / (ms8 * 1e-3), "unit": "timesteps/s",
+                     "particle_steps_per_sec": 200.0 / (ms8 * 1e-3) * 8e6, "md_steps": 200,
+                     "k_md_step_ms": s8.time_kernel(2, 10), "nlist_rebuild_ms": s8.time_kernel(1, 5)}
+        s8.close()
+    if world > 1:
+        mg_stats = s.mg_stats()
+        mg_stats["grid"] = list(s.grid)
+
     if rank == 0:
         line = {"metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-                "scaling": "weak" if world > 1 else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": desc, "N": N, "md_steps_per_step": md_steps,
-                           "parallelism": "1 GPU" if world == 1 else "%d independent replicas (one per GPU)" % world,
-                           "l2": "L2 flushed (256 MiB write) between timed iterations; within an iteration the 64k "
-                                 "working set is L2-resident, which is the workload",
-                           "sorter_period": 300, "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels", 2: "CUDA graph, conditional IF node", 3: "stream launches of the graph kernels"}[USE_GRAPH], "nlist": {"r_buff": 0.4, "check_period": 1,
-                                                           "rebuilds_total": stats["updates"] + stats["forced"],
-                                                           "Nmax": stats["Nmax0"]}},
-                "particle_steps_per_sec": tps * N * world,
+                           "parallelism": "1 GPU" if world == 1 else
+                           "spatial domain decomposition %s, ghosts + migration over NVLink peer memory" % (
+                               "x".join(str(g) for g in mg_stats["grid"])),
+                           "l2": "L2 flushed (256 MiB write) between timed iterations" + (
+                               "; within an iteration the 64k working set is L2-resident, which is the workload"
+                               if N <= 100000 else "; per-GPU working set exceeds L2"),
+                           "sorter_period": 300,
+                           "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels",
+                                        2: "CUDA graph, conditional IF node",
+                                        3: "stream launches of the graph kernels"}[USE_GRAPH],
+                           "nlist": {"r_buff": 0.4, "check_period": 1,
+                                     "rebuilds_total": stats["updates"] + stats["forced"], "Nmax": stats["Nmax0"]}},
+                "particle_steps_per_sec": tps * N,
                 "wall_tps": md_steps * args.steps / t_wall,
                 "gpu_launches": launches, "ms_runs": gpu_ms, "nlist_overflows": stats["overflows"],
                 "clocks": clocks,
@@ -344,8 +399,13 @@ def main():
                 "e2e": {"value": e2e_tps, "unit": "timesteps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "thermo_T": th["T"]},
                 "cpu_baseline": cpu}
+        if scale_ref:
+            line["scale_ref"] = scale_ref
+        if mg_stats:
+            line["domain"] = mg_stats
         print(json.dumps(line))
-    s.close()
+    if s is not None:
+        s.close()
     if world > 1:
         dist.destroy_process_group()
 

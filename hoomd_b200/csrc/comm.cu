@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(32) k_mg_step_barrier(const __grid_constant__ 
     if (threadIdx.x == 0)
         {
         st->moved = moved ? 1u : 0u;
-        if (st->steps_left)
+        if (st->steps_left && !st->abort)
             decide_body(st);
         else
             {
@@ -88,6 +88,17 @@ __global__ void __launch_bounds__(32) k_mg_barrier(const __grid_constant__ MgCon
     {
     if (enable && !*enable) return;
     warp_barrier(c, ms, kind, false);
+    }
+
+// last kernel of the rebuild bracket: did the neighbor list of ANY rank overflow Nmax?  Then no rank may step on (the
+// host grows Nmax and the chunk resumes from this very step): the reference's overflow loop
+// (hoomd/md/NeighborList.cc:226-244) made collective.
+__global__ void __launch_bounds__(32) k_mg_rebuild_vote(const __grid_constant__ MgConst c, MgState* ms, StepState* st,
+                                                        int buffer, const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    const bool any = warp_barrier(c, ms, 3, st->overflow != 0u);
+    if (threadIdx.x == 0 && any) st->abort = 1u + (unsigned int)buffer;
     }
 
 // ---- rebuild bracket, part 1: migration ---------------------------------------------------------------------------------
@@ -360,6 +371,13 @@ cudaError_t launch_mg_barrier(const MgConst& c, const MgLocal& l, int kind, cons
                               cudaStream_t stream)
     {
     k_mg_barrier<<<1, 32, 0, stream>>>(c, l.ms, kind, enable);
+    return cudaGetLastError();
+    }
+
+cudaError_t launch_mg_rebuild_vote(const MgConst& c, const MgLocal& l, int buffer, const unsigned int* enable,
+                                   cudaStream_t stream)
+    {
+    k_mg_rebuild_vote<<<1, 32, 0, stream>>>(c, l.ms, l.st, buffer, enable);
     return cudaGetLastError();
     }
 

@@ -93,6 +93,9 @@ cudaError_t launch_mg_step_barrier(const MgConst& c, const MgLocal& l, unsigned 
                                    cudaStream_t stream);
 cudaError_t launch_mg_barrier(const MgConst& c, const MgLocal& l, int kind, const unsigned int* enable,
                               cudaStream_t stream);
+// rebuild bracket, last: collective Nmax-overflow vote (sets st->abort on every rank)
+cudaError_t launch_mg_rebuild_vote(const MgConst& c, const MgLocal& l, int buffer, const unsigned int* enable,
+                                   cudaStream_t stream);
 // rebuild bracket, part 1: migration (mark + pack into the neighbor's mailbox) ... barrier ... unpack + hole filling
 cudaError_t launch_mg_migrate(const MgConst& c, const MgLocal& l, float4* pos, const unsigned int* enable,
                               cudaStream_t stream);

@@ -1332,6 +1332,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         st.every = 0x7fffffffu; // no rebuild decision can fire
         st.ntypes = s->ntypes;
         st.steps_left = iters + 1;
+        st.N = s->N;
         CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
         FusedStepArgs fa;
         fused_args(s, fa);
@@ -1359,7 +1360,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
             CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
         else
             {
-            CUDA_OK(launch_cell_list(&ca, nullptr, s->stream));
+            CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, s->mg ? &s->d_state.p->N : nullptr));
             CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
             }
         }

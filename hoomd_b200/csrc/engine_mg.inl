@@ -198,8 +198,9 @@ static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float
     na.d_pos = (const float*)pos;
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
     CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    CUDA_OK(launch_mg_rebuild_vote(s->mgc, s->mgl, buffer, enable, s->stream));
     }
-constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 2;
+constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 3;
 
 static void mg_upload_state(b200_system* s, unsigned int steps_left)
     {
@@ -250,8 +251,8 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
             overflowed = nlist_check_conditions(s);
             if (overflowed)
                 {
-                // head room: a later overflow inside a device-driven chunk cannot be replayed across ranks
-                for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 5u / 4u) + 7u) & ~7u;
+                // head room: a later overflow inside a device-driven chunk costs a collective abort + resume
+                for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 9u / 8u) + 7u) & ~7u;
                 s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
                 CUDA_OK(cudaStreamSynchronize(s->stream));
                 s->num_overflows += 1;
@@ -345,53 +346,77 @@ static void mg_build_graph(b200_system* s)
 
 static void mg_run_chunk(b200_system* s, unsigned int chunk)
     {
-    if (s->force_update) nlist_build_head_list(s);
-    if (s->use_graph != 3 && !s->graph_valid)
+    unsigned int remaining = chunk;
+    bool resume = false; // re-entering the step whose rebuild overflowed: its step one has already been taken
+    while (remaining)
         {
-        invalidate_graph(s);
-        mg_build_graph(s);
-        }
-    mg_upload_state(s, chunk);
-    FusedStepArgs fa;
-    fused_args(s, fa);
-    // prologue: step one of the first update() + its ghost update; the first barrier of the graph takes the vote
-    CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
-    CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
-    const unsigned int nreplay = (chunk + 1) / 2;
-    if (s->use_graph == 3)
-        {
-        const unsigned int* enable = &s->d_state.p->need_rebuild;
-        for (unsigned int k = 0; k < nreplay; k++)
+        if (s->force_update) nlist_build_head_list(s);
+        if (s->use_graph != 3 && !s->graph_valid)
             {
-            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
-            mg_enqueue_rebuild(s, enable, s->pos.p, 0);
-            enqueue_md_step(s, fa, 0, 0ull, 0);
-            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
-            mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
-            enqueue_md_step(s, fa, 1, 0ull, 0);
-            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+            invalidate_graph(s);
+            mg_build_graph(s);
             }
+        mg_upload_state(s, remaining);
+        FusedStepArgs fa;
+        fused_args(s, fa);
+        // prologue: step one of the first update() + its ghost update; the first barrier of the graph takes the vote
+        if (!resume) CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+        CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        const unsigned int nreplay = (remaining + 1) / 2;
+        if (s->use_graph == 3)
+            {
+            const unsigned int* enable = &s->d_state.p->need_rebuild;
+            for (unsigned int k = 0; k < nreplay; k++)
+                {
+                CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                mg_enqueue_rebuild(s, enable, s->pos.p, 0);
+                enqueue_md_step(s, fa, 0, 0ull, 0);
+                CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+                CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
+                enqueue_md_step(s, fa, 1, 0ull, 0);
+                CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+                }
+            }
+        else
+            for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+        mg_download_state(s);
+        const StepState st = *s->h_state;
+        mg_check_errors(s);
+        cell_list_check_conditions(s);
+        const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
+        s->kernels_last_run += 2ull + 6ull * nreplay + MG_REBUILD_KERNELS * rebuilds;
+        s->num_updates += st.num_updates;
+        s->num_forced += st.num_forced;
+        s->nl_first_compute = false;
+        if (st.abort)
+            {
+            // collective Nmax overflow: the aborted step has its step one and its migration behind it but no force yet.
+            // Grow Nmax where needed (NeighborList::checkConditions), then redo the step's rebuild as a forced update.
+            if (st.abort == 2u)
+                CUDA_OK(cudaMemcpyAsync(s->pos.p, s->pos_alt.p, sizeof(float4) * s->N, cudaMemcpyDeviceToDevice, s->stream));
+            if (nlist_check_conditions(s))
+                {
+                for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 9u / 8u) + 7u) & ~7u;
+                s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
+                CUDA_OK(cudaStreamSynchronize(s->stream));
+                }
+            CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+            s->num_overflows += 1;
+            s->timestep = st.timestep - 1u; // the decision of the aborted step is taken again
+            s->last_updated_tstep = st.last_updated;
+            s->force_update = true;
+            remaining = st.steps_left;
+            resume = true;
+            continue;
+            }
+        s->timestep = st.timestep;
+        s->last_updated_tstep = st.last_updated;
+        s->force_update = st.force_update != 0;
+        s->last_checked_tstep = st.timestep;
+        s->last_check_result = st.need_rebuild != 0;
+        s->nl_last_computed = st.timestep;
+        remaining = 0;
         }
-    else
-        for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
-    mg_download_state(s);
-    const StepState& st = *s->h_state;
-    mg_check_errors(s);
-    cell_list_check_conditions(s);
-    if (st.overflow)
-        throw std::runtime_error("nlist: neighbor list overflow inside a multi-GPU chunk (not replayable across ranks); "
-                                 "the engine pre-sizes Nmax with 25% head room");
-    const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    s->kernels_last_run += 2ull + 6ull * nreplay + MG_REBUILD_KERNELS * rebuilds;
-    s->timestep = st.timestep;
-    s->last_updated_tstep = st.last_updated;
-    s->num_updates += st.num_updates;
-    s->num_forced += st.num_forced;
-    s->force_update = st.force_update != 0;
-    s->last_checked_tstep = st.timestep;
-    s->last_check_result = st.need_rebuild != 0;
-    s->nl_last_computed = st.timestep;
-    s->nl_first_compute = false;
     }
 } // namespace b200

@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
     __shared__ float s_virial[VIRIAL ? 6 * PPB : 1];
     StepState* st = a.st;
     const unsigned int steps_left = st->steps_left;
-    if (steps_left == 0) return; // padding launch of an odd-length chunk (uniform over the grid)
+    if (steps_left == 0 || st->abort) return; // padding launch of an odd-length chunk / aborted chunk (grid-uniform)
     const bool last = steps_left == 1;
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;

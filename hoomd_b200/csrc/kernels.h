@@ -27,6 +27,7 @@ struct StepState
     unsigned long long ticket;    // k_md_step: low word = CTAs finished, high word = CTAs that saw a mover (one atomic)
     unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
     unsigned int N;               // local particle count (multi-GPU: changes at every migration)
+    unsigned int abort;           // multi-GPU: some rank's rebuild overflowed Nmax; every rank stops stepping (1 + buffer)
     };
 
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count

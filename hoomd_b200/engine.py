@@ -139,9 +139,12 @@ class System:
 
     net_force = lambda self: self.forces(False)[0]
 
-    def nlist(self):
+    def nlist(self, counts_only=False):
         n = np.empty(self.N, np.uint32)
         head = np.empty(self.N, np.uint32)
+        if counts_only:
+            self._check(_lib.lib().b200_sys_get_nlist(self.h, _p(n), _p(head), None, 0))
+            return n, head, None
         size = int(_lib.lib().b200_sys_get_nlist_size(self.h))
         nl = np.empty(size, np.uint32)
         self._check(_lib.lib().b200_sys_get_nlist(self.h, _p(n), _p(head), _p(nl), size))
