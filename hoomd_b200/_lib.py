@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhoomd_b200.so")
+LIB_PATH = os.environ.get("HOOMD_B200_LIB", os.path.join(_HERE, "libhoomd_b200.so"))  # override: A/B kernel variants
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "hoomd_b200.h")
 
 c_float_p = C.POINTER(C.c_float)
@@ -47,7 +47,7 @@ class PairArgs(C.Structure):
     _fields_ = [("d_force", vp), ("d_virial", vp), ("virial_pitch", C.c_uint), ("N", C.c_uint), ("d_pos", vp),
                 ("box", Box), ("d_n_neigh", vp), ("d_nlist", vp), ("d_head_list", vp), ("d_rcutsq", vp),
                 ("d_ronsq", vp), ("ntypes", C.c_uint), ("shift_mode", C.c_uint), ("compute_virial", C.c_uint),
-                ("threads_per_particle", C.c_uint), ("block_size", C.c_uint)]
+                ("threads_per_particle", C.c_uint), ("block_size", C.c_uint), ("wrap_skip_margin", C.c_float)]
 
 
 class ForceList(C.Structure):

@@ -99,6 +99,17 @@ __device__ __forceinline__ float3 min_image_fast(float3 w, const Box& box)
     return w;
     }
 
+// true when p is at least `margin` away from every periodic face of the box (margin <= 0: never)
+__device__ __forceinline__ bool box_interior(float4 p, const Box& box, float margin)
+    {
+    if (!(margin > 0.0f)) return false;
+    bool in = true;
+    if (box.periodic.x) in &= (p.x >= box.lo.x + margin) && (p.x < box.hi.x - margin);
+    if (box.periodic.y) in &= (p.y >= box.lo.y + margin) && (p.y < box.hi.y - margin);
+    if (box.periodic.z) in &= (p.z >= box.lo.z + margin) && (p.z < box.hi.z - margin);
+    return in;
+    }
+
 // dot(dx,dx) exactly as HOOMDMath.h:324-327 evaluates it on the host: (x*x + y*y) + z*z, three rounded products
 __device__ __forceinline__ float dot_exact(float3 a)
     {

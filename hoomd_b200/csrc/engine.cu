@@ -261,6 +261,9 @@ static void pair_args(b200_system* s, b200_pair_args& a)
     a.compute_virial = s->compute_virial ? 1u : 0u;
     a.threads_per_particle = s->pair_tpp;
     a.block_size = 0;
+    // listed pairs are at most r_list apart at build time and each partner drifts < r_buff/2 (+ one step) before the
+    // next rebuild: r_cut + 2 r_buff bounds every |r_i - r_j| the kernel will see
+    a.wrap_skip_margin = s->rcut_max_max + 2.0f * s->r_buff + 0.1f;
     }
 
 static void fused_args(b200_system* s, FusedStepArgs& a)

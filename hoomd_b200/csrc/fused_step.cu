@@ -87,7 +87,7 @@ template<class Evaluator> struct MdStepArgs
     const unsigned int* n_neigh; const unsigned int* nlist; const unsigned int* head_list;
     const typename Evaluator::param_type* params; const float* rcutsq; const float* ronsq; unsigned int ntypes;
     const float* maxsq; const float* gamma;
-    unsigned int N; Box box; float dt; float r_buff;
+    unsigned int N; Box box; float dt; float r_buff; float wrap_skip_margin;
     int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
     int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
     const unsigned int* d_N;  // multi-GPU: live local particle count (N is the capacity the grid was sized for)
@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
         const unsigned int size = active ? a.n_neigh[i] : 0u;
         const unsigned int head = active ? a.head_list[i] : 0u;
         const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(
-            pi4, size, head, sub, a.pos_in, a.box, a.nlist, T, a.ntypes);
+            pi4, size, head, sub, a.pos_in, a.box, a.nlist, T, a.ntypes,
+            !active || box_interior(pi4, a.box, a.wrap_skip_margin));
         if (sub == 0)
             {
             s_force[slot] = make_float4(r.fx, r.fy, r.fz, r.pe);
@@ -312,6 +313,7 @@ cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, c
     a.params = (const float2*)d_params; a.rcutsq = pa.d_rcutsq; a.ronsq = pa.d_ronsq; a.ntypes = pa.ntypes;
     a.maxsq = fa.maxsq; a.gamma = fa.gamma;
     a.N = fa.N; a.box = make_box(fa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
+    a.wrap_skip_margin = pa.wrap_skip_margin;
     a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
     a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
     a.copy_pos_on_last = copy_pos_on_last;

@@ -17,7 +17,8 @@ __global__ void __launch_bounds__(256) k_pair_forces(float4* __restrict__ force,
                                                      const unsigned int* __restrict__ head_list,
                                                      const typename Evaluator::param_type* __restrict__ params,
                                                      const float* __restrict__ rcutsq_tab,
-                                                     const float* __restrict__ ronsq_tab, unsigned int ntypes)
+                                                     const float* __restrict__ ronsq_tab, unsigned int ntypes,
+                                                     float wrap_skip_margin)
     {
     extern __shared__ unsigned char smem_raw[];
     PairTables<Evaluator> T;
@@ -30,8 +31,8 @@ __global__ void __launch_bounds__(256) k_pair_forces(float4* __restrict__ force,
     const float4 pi4 = active ? pos[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     const unsigned int size = active ? n_neigh[i] : 0u;
     const unsigned int head = active ? head_list[i] : 0u;
-    const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(pi4, size, head, sub, pos, box,
-                                                                                       nlist, T, ntypes);
+    const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(
+        pi4, size, head, sub, pos, box, nlist, T, ntypes, !active || box_interior(pi4, box, wrap_skip_margin));
     if (sub == 0 && active)
         {
         force[i] = make_float4(r.fx, r.fy, r.fz, r.pe);
@@ -61,12 +62,12 @@ static cudaError_t launch_mt(const b200_pair_args& a, const typename Evaluator::
         if (smem > 48 * 1024) return cudaErrorInvalidValue;
         k_pair_forces<Evaluator, TPP, SHIFT_MODE, VIRIAL, true><<<grid, bs, smem, stream>>>(
             (float4*)a.d_force, a.d_virial, a.virial_pitch, a.N, (const float4*)a.d_pos, box, a.d_n_neigh, a.d_nlist,
-            a.d_head_list, params, a.d_rcutsq, a.d_ronsq, a.ntypes);
+            a.d_head_list, params, a.d_rcutsq, a.d_ronsq, a.ntypes, a.wrap_skip_margin);
         }
     else
         k_pair_forces<Evaluator, TPP, SHIFT_MODE, VIRIAL, false><<<grid, bs, 0, stream>>>(
             (float4*)a.d_force, a.d_virial, a.virial_pitch, a.N, (const float4*)a.d_pos, box, a.d_n_neigh, a.d_nlist,
-            a.d_head_list, params, a.d_rcutsq, a.d_ronsq, a.ntypes);
+            a.d_head_list, params, a.d_rcutsq, a.d_ronsq, a.ntypes, a.wrap_skip_margin);
     return cudaGetLastError();
     }
 

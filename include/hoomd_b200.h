@@ -191,6 +191,9 @@ typedef struct b200_pair_args
     unsigned int  compute_virial;
     unsigned int  threads_per_particle; /* 0 = pick (1,2,4,8,16,32 accepted; the reference autotunes this) */
     unsigned int  block_size;           /* 0 = pick */
+    float         wrap_skip_margin;     /* > 0: particles farther than this from every periodic face skip minImage
+                                           (identity there).  Must be >= the largest |r_i - r_j| of any listed pair,
+                                           i.e. max r_cut + 2 r_buff; 0 = always apply minImage */
     } b200_pair_args;
 
 /* d_params: Scalar2[ntypes*ntypes] = (lj1, lj2) = (4 eps sigma^12, 4 alpha eps sigma^6) (hoomd/md/pair.py:602-609) */

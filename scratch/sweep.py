@@ -4,12 +4,13 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 import numpy as np
 
+TPPS = [int(x) for x in os.environ.get("TPPS", "1,2,4,8").split(",")]
 wl = sys.argv[1] if len(sys.argv) > 1 else "lj64k"
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2000
 bench.EQUIL_STEPS = int(sys.argv[3]) if len(sys.argv) > 3 else None
 state, L = bench.make_state(wl)
 for ug in (2,):
-    for tpp in (2, 4, 8, 16, 32):
+    for tpp in TPPS:
         bench.USE_GRAPH = ug
         s = bench.new_system(state, L)
         s.set_tuning(pair_tpp=tpp, use_graph=ug)
