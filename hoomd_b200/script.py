@@ -1,0 +1,568 @@
+"""The reference's Python job-script surface for the MD hot path, driving the B200 engine.
+
+An unmodified HOOMD-blue 2.3 job script of the shape in the reference README (README.md:56-72)
+
+    import hoomd
+    from hoomd import md
+    hoomd.context.initialize()
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name='A'), n=10)
+    nl = md.nlist.cell()
+    lj = md.pair.lj(r_cut=3.0, nlist=nl)
+    lj.pair_coeff.set('A', 'A', epsilon=1.0, sigma=1.0)
+    all = hoomd.group.all()
+    md.integrate.mode_standard(dt=0.005)
+    md.integrate.langevin(group=all, kT=1.2, seed=4)
+    hoomd.run(10e3)
+
+runs after ``import hoomd_b200.script as hoomd`` (or ``hoomd_b200.script.install()``, which registers the modules as
+``hoomd`` / ``hoomd.md``).  Same names, argument meaning and error behaviour as hoomd/md/nlist.py:555,
+hoomd/md/pair.py:358-445,579-609, hoomd/md/integrate.py:49,729,844, hoomd/__init__.py (run), hoomd/init.py:32-93,
+hoomd/data.py (make_snapshot / take_snapshot), hoomd/update.py:239-263 (sort).  Like the reference, commands only record
+parameters; the C++/CUDA objects are (re)configured when ``run()`` starts (hoomd/md/nlist.py:80-109 update_rcut,
+hoomd/md/pair.py:430-445 update_coeffs).  Only the path of SURVEY.md section 8 is covered: one pair force (lj), one
+integration method on group.all(), orthorhombic boxes.
+"""
+import sys
+import types
+
+import numpy as np
+
+
+class _Context:
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self.system = None          # _SystemData
+        self.neighbor_lists = []
+        self.forces = []
+        self.integrator = None
+        self.integration_methods = []
+        self.sorter = update.sort() if "update" in globals() else None
+        self.loggers = []
+        self.engine = None
+        self.engine_dirty = True
+        self.timestep = 0
+
+
+class _ContextModule(types.ModuleType):
+    """hoomd.context: initialize(), current"""
+
+    def __init__(self):
+        super().__init__("hoomd.context")
+        self.current = None
+        self.exec_conf = None
+
+    def initialize(self, args=None):
+        self.current = _Context()
+        self.current.sorter = update.sort()
+        return self.current
+
+
+# ---- hoomd.lattice / hoomd.init / hoomd.data -------------------------------------------------------------------------
+class _UnitCell:
+    def __init__(self, N, a1, a2, a3, position, type_name):
+        self.N, self.a1, self.a2, self.a3 = N, np.asarray(a1, float), np.asarray(a2, float), np.asarray(a3, float)
+        self.position, self.type_name = np.asarray(position, float), type_name
+
+
+lattice = types.ModuleType("hoomd.lattice")
+lattice.sc = lambda a, type_name="A": _UnitCell(1, [a, 0, 0], [0, a, 0], [0, 0, a], [[0, 0, 0]], [type_name])
+lattice.bcc = lambda a, type_name="A": _UnitCell(2, [a, 0, 0], [0, a, 0], [0, 0, a],
+                                                 [[0, 0, 0], [a / 2, a / 2, a / 2]], [type_name] * 2)
+lattice.fcc = lambda a, type_name="A": _UnitCell(4, [a, 0, 0], [0, a, 0], [0, 0, a],
+                                                 [[0, 0, 0], [0, a / 2, a / 2], [a / 2, 0, a / 2], [a / 2, a / 2, 0]],
+                                                 [type_name] * 4)
+
+
+class _BoxDim:
+    """hoomd.data.boxdim (orthorhombic)"""
+
+    def __init__(self, Lx=1.0, Ly=1.0, Lz=1.0, L=None, dimensions=3):
+        if L is not None:
+            Lx = Ly = Lz = L
+        self.Lx, self.Ly, self.Lz, self.xy, self.xz, self.yz, self.dimensions = Lx, Ly, Lz, 0.0, 0.0, 0.0, dimensions
+
+    def get_volume(self):
+        return self.Lx * self.Ly * self.Lz
+
+
+class _ParticleSnapshot:
+    def __init__(self, N, types):
+        self.N = N
+        self.types = list(types)
+        self.position = np.zeros((N, 3), np.float32)
+        self.velocity = np.zeros((N, 3), np.float32)
+        self.acceleration = np.zeros((N, 3), np.float32)
+        self.typeid = np.zeros(N, np.uint32)
+        self.mass = np.ones(N, np.float32)
+        self.image = np.zeros((N, 3), np.int32)
+
+
+class _Snapshot:
+    def __init__(self, N, box, particle_types):
+        self.box = box
+        self.particles = _ParticleSnapshot(N, particle_types)
+
+
+class _ParticleTypes:
+    def __init__(self, names):
+        self._names = list(names)
+
+    def __len__(self):
+        return len(self._names)
+
+    def __getitem__(self, i):
+        return self._names[i]
+
+    def __iter__(self):
+        return iter(self._names)
+
+
+class _Particles:
+    def __init__(self, sysdata):
+        self._s = sysdata
+        self.types = _ParticleTypes(sysdata.types)
+
+    def __len__(self):
+        return self._s.N
+
+
+class _SystemData:
+    """hoomd.data.system_data: the host-side snapshot the engine is seeded from / synchronised back into"""
+
+    def __init__(self, snapshot):
+        p = snapshot.particles
+        self.N = int(p.N)
+        self.types = list(p.types)
+        self.box = snapshot.box
+        self.pos4 = np.zeros((self.N, 4), np.float32)
+        self.pos4[:, :3] = p.position
+        self.pos4[:, 3] = np.asarray(p.typeid, np.int32).view(np.float32)
+        self.vel4 = np.zeros((self.N, 4), np.float32)
+        self.vel4[:, :3] = p.velocity
+        self.vel4[:, 3] = p.mass
+        self.image = np.array(p.image, np.int32)
+        self.particles = _Particles(self)
+
+    def take_snapshot(self, **kwargs):
+        """current state in TAG order (hoomd/data.py take_snapshot)"""
+        ctx = context.current
+        if ctx.engine is not None:
+            st = ctx.engine.particles()
+            order = np.argsort(st["tag"], kind="stable")
+            self.pos4, self.vel4, self.image = st["pos"][order], st["vel"][order], st["image"][order]
+            accel = st["accel"][order]
+        else:
+            accel = np.zeros((self.N, 3), np.float32)
+        snap = _Snapshot(self.N, self.box, self.types)
+        q = snap.particles
+        q.position[:] = self.pos4[:, :3]
+        q.velocity[:] = self.vel4[:, :3]
+        q.mass[:] = self.vel4[:, 3]
+        q.typeid[:] = self.pos4[:, 3].view(np.int32)
+        q.image[:] = self.image
+        q.acceleration[:] = accel
+        return snap
+
+    def restore_snapshot(self, snapshot):
+        self.__init__(snapshot)
+        context.current.engine_dirty = True
+
+
+data = types.ModuleType("hoomd.data")
+data.boxdim = _BoxDim
+data.make_snapshot = lambda N, box, particle_types=("A",), **kw: _Snapshot(N, box, particle_types)
+
+
+def _require_context():
+    if context.current is None:
+        raise RuntimeError("Cannot initialize without context.initialize() first")
+
+
+def _read_snapshot(snapshot):
+    _require_context()
+    if context.current.system is not None:
+        raise RuntimeError("Cannot initialize more than once")
+    context.current.system = _SystemData(snapshot)
+    return context.current.system
+
+
+def _create_lattice(unitcell, n):
+    """hoomd.init.create_lattice (hoomd/init.py:32-93): n unit cells per direction, box centred on the origin"""
+    n = (n, n, n) if np.isscalar(n) else tuple(n)
+    L = np.array([unitcell.a1[0] * n[0], unitcell.a2[1] * n[1], unitcell.a3[2] * n[2]])
+    types_ = sorted(set(unitcell.type_name), key=unitcell.type_name.index)
+    N = unitcell.N * n[0] * n[1] * n[2]
+    snap = _Snapshot(N, _BoxDim(*L), types_)
+    i, j, k = np.meshgrid(np.arange(n[0]), np.arange(n[1]), np.arange(n[2]), indexing="ij")
+    cells = np.stack([i.ravel() * unitcell.a1[0], j.ravel() * unitcell.a2[1], k.ravel() * unitcell.a3[2]], axis=1)
+    lo = -L / 2.0
+    # SnapshotParticleData::replicate order (hoomd/ParticleData.cc:2892-2930): unit-cell particle outermost, then x, y, z
+    half = np.array([unitcell.a1[0], unitcell.a2[1], unitcell.a3[2]]) / 2.0
+    pos = (unitcell.position[:, None, :] + cells[None, :, :] + lo + half).reshape(-1, 3)
+    snap.particles.position[:] = pos
+    snap.particles.typeid[:] = np.repeat([types_.index(t) for t in unitcell.type_name], n[0] * n[1] * n[2])
+    return _read_snapshot(snap)
+
+
+init = types.ModuleType("hoomd.init")
+init.read_snapshot = _read_snapshot
+init.create_lattice = _create_lattice
+
+# ---- hoomd.group ---------------------------------------------------------------------------------------------------------
+group = types.ModuleType("hoomd.group")
+
+
+class _Group:
+    def __init__(self, name):
+        self.name = name
+
+    def __len__(self):
+        return context.current.system.N
+
+
+group.all = lambda: _Group("all")
+
+# ---- hoomd.update ---------------------------------------------------------------------------------------------------------
+update = types.ModuleType("hoomd.update")
+
+
+class _Sort:
+    """hoomd.update.sort: period 300 on the GPU (hoomd/update.py:258-263)"""
+
+    def __init__(self):
+        self.period, self.enabled = 300, True
+
+    def set_params(self, grid=None):
+        pass
+
+    def set_period(self, period):
+        self.period = int(period)
+        if context.current is not None:
+            context.current.engine_dirty = True
+
+    def disable(self):
+        self.enabled = False
+        if context.current is not None:
+            context.current.engine_dirty = True
+
+    def enable(self):
+        self.enabled = True
+
+
+update.sort = _Sort
+
+# ---- hoomd.md -------------------------------------------------------------------------------------------------------------
+md = types.ModuleType("hoomd.md")
+md.nlist = types.ModuleType("hoomd.md.nlist")
+md.pair = types.ModuleType("hoomd.md.pair")
+md.integrate = types.ModuleType("hoomd.md.integrate")
+
+
+class _Cell:
+    """md.nlist.cell (hoomd/md/nlist.py:555)"""
+
+    def __init__(self, r_buff=0.4, check_period=1, d_max=None, dist_check=True, name=None, deterministic=False):
+        _require_context()
+        if context.current.system is None:
+            raise RuntimeError("Cannot create neighbor list before initialization")
+        self.r_buff, self.check_period, self.dist_check = float(r_buff), int(check_period), bool(dist_check)
+        self.subscribers = []
+        context.current.neighbor_lists.append(self)
+        context.current.engine_dirty = True
+
+    def set_params(self, r_buff=None, check_period=None, d_max=None, dist_check=None):
+        if r_buff is not None:
+            self.r_buff = float(r_buff)
+        if check_period is not None:
+            self.check_period = int(check_period)
+        if dist_check is not None:
+            self.dist_check = bool(dist_check)
+        context.current.engine_dirty = True
+
+    def query_update_period(self):
+        eng = context.current.engine
+        return None if eng is None else eng.stats()
+
+
+md.nlist.cell = _Cell
+
+
+class _Coeff:
+    """pair.coeff (hoomd/md/pair.py:60-255): symmetric type-pair table with per-potential defaults"""
+
+    def __init__(self):
+        self.values = {}
+        self.default_coeff = {}
+
+    def set_default_coeff(self, name, value):
+        self.default_coeff[name] = value
+
+    def set(self, a, b, **coeffs):
+        a = [a] if isinstance(a, str) else list(a)
+        b = [b] if isinstance(b, str) else list(b)
+        for ai in a:
+            for bi in b:
+                key = (ai, bi) if (ai, bi) in self.values or (bi, ai) not in self.values else (bi, ai)
+                self.values.setdefault(key, {}).update(coeffs)
+        if context.current is not None:
+            context.current.engine_dirty = True
+
+    def get(self, a, b, name):
+        v = self.values.get((a, b), self.values.get((b, a)))
+        if v is None:
+            return None
+        return v.get(name, self.default_coeff.get(name))
+
+    def verify(self, types_, required):
+        ok = True
+        for i, a in enumerate(types_):
+            for b in types_[i:]:
+                if (a, b) not in self.values and (b, a) not in self.values:
+                    sys.stderr.write("**ERROR**: Type pair (%s, %s) not found in pair coeff\n" % (a, b))
+                    ok = False
+                    continue
+                for r in required:
+                    if self.get(a, b, r) is None:
+                        sys.stderr.write("**ERROR**: Type pair (%s, %s) is missing required coefficient %s\n" % (a, b, r))
+                        ok = False
+        return ok
+
+
+class _LJ:
+    """md.pair.lj (hoomd/md/pair.py:579-609)"""
+
+    def __init__(self, r_cut, nlist, name=None):
+        _require_context()
+        if context.current.system is None:
+            raise RuntimeError("Cannot create force before initialization")
+        if any(isinstance(f, _LJ) for f in context.current.forces):
+            raise RuntimeError("hoomd_b200: one md.pair.lj per system in this round")
+        self.global_r_cut, self.nlist, self.shift_mode = float(r_cut), nlist, 0
+        self.pair_coeff = _Coeff()
+        self.pair_coeff.set_default_coeff("alpha", 1.0)
+        self.pair_coeff.set_default_coeff("r_cut", self.global_r_cut)
+        self.pair_coeff.set_default_coeff("r_on", self.global_r_cut)
+        self.required_coeffs = ["epsilon", "sigma", "alpha"]
+        self.enabled = True
+        nlist.subscribers.append(self)
+        context.current.forces.append(self)
+        context.current.engine_dirty = True
+
+    def set_params(self, mode=None):
+        if mode is not None:
+            if mode not in ("no_shift", "shift", "xplor"):
+                raise RuntimeError("Error changing parameters in pair force")  # hoomd/md/pair.py:402-403
+            self.shift_mode = {"no_shift": 0, "shift": 1, "xplor": 2}[mode]
+            context.current.engine_dirty = True
+
+    def tables(self, types_):
+        """ntypes x ntypes (r_cut, epsilon, sigma, alpha, r_on); raises like update_coeffs (hoomd/md/pair.py:430-445)"""
+        if not self.pair_coeff.verify(types_, self.required_coeffs):
+            raise RuntimeError("Error updating pair coefficients")
+        nt = len(types_)
+        out = {k: np.zeros((nt, nt)) for k in ("r_cut", "epsilon", "sigma", "alpha", "r_on")}
+        for i, a in enumerate(types_):
+            for j, b in enumerate(types_):
+                for k in out:
+                    v = self.pair_coeff.get(a, b, k)
+                    if v is False:  # r_cut = False disables the pair (hoomd/md/pair.py:330-345)
+                        v = -1.0
+                    out[k][i, j] = v
+        return out
+
+    def get_energy(self, group=None):
+        f, _ = context.current.engine.forces(False)
+        return float(f[:, 3].astype(np.float64).sum())
+
+
+md.pair.lj = _LJ
+
+
+class _ModeStandard:
+    """md.integrate.mode_standard (hoomd/md/integrate.py:49)"""
+
+    def __init__(self, dt, aniso=None):
+        _require_context()
+        self.dt = float(dt)
+        context.current.integrator = self
+        context.current.engine_dirty = True
+
+    def set_params(self, dt=None, aniso=None):
+        if dt is not None:
+            self.dt = float(dt)
+            context.current.engine_dirty = True
+
+
+class _Method:
+    def __init__(self, group_):
+        _require_context()
+        if group_ is None or group_.name != "all":
+            raise RuntimeError("hoomd_b200: integration methods act on group.all() in this round")
+        context.current.integration_methods.append(self)
+        context.current.engine_dirty = True
+        self.enabled = True
+
+    def disable(self):
+        self.enabled = False
+        context.current.engine_dirty = True
+
+    def enable(self):
+        self.enabled = True
+        context.current.engine_dirty = True
+
+
+class _NVE(_Method):
+    """md.integrate.nve (hoomd/md/integrate.py:729)"""
+
+    def __init__(self, group, limit=None, zero_force=False):
+        super().__init__(group)
+        self.limit, self.zero_force = limit, bool(zero_force)
+
+    def set_params(self, limit=None, zero_force=None):
+        if limit is not None:
+            self.limit = None if limit is False else limit
+        if zero_force is not None:
+            self.zero_force = bool(zero_force)
+        context.current.engine_dirty = True
+
+
+class _Langevin(_Method):
+    """md.integrate.langevin (hoomd/md/integrate.py:844)"""
+
+    def __init__(self, group, kT, seed, dscale=False, tally=False, noiseless_t=False, noiseless_r=False):
+        super().__init__(group)
+        if dscale:
+            raise RuntimeError("hoomd_b200: dscale (gamma = lambda * diameter) is out of scope")
+        self.kT, self.seed, self.noiseless_t = float(kT), int(seed), bool(noiseless_t)
+        self.gamma = {}
+
+    def set_params(self, kT=None, tally=None):
+        if kT is not None:
+            self.kT = float(kT)
+            context.current.engine_dirty = True
+
+    def set_gamma(self, a, gamma):
+        types_ = context.current.system.types
+        if isinstance(a, str):
+            if a not in types_:
+                raise RuntimeError("Trying to set gamma for a non existent type! " + str(a))
+            self.gamma[a] = float(gamma)
+        else:
+            self.gamma[types_[a]] = float(gamma)
+        context.current.engine_dirty = True
+
+
+md.integrate.mode_standard = _ModeStandard
+md.integrate.nve = _NVE
+md.integrate.langevin = _Langevin
+
+# ---- hoomd.analyze.log (in-memory subset: the thermodynamic quantities of ComputeThermo) ---------------------------------
+analyze = types.ModuleType("hoomd.analyze")
+
+
+class _Log:
+    QUANTITIES = {"temperature": "T", "kinetic_energy": "ke", "potential_energy": "pe", "pressure": "P"}
+
+    def __init__(self, filename=None, quantities=(), period=1, **kw):
+        _require_context()
+        for q in quantities:
+            if q not in self.QUANTITIES and q != "pair_lj_energy":
+                raise RuntimeError("Unknown log quantity " + q)
+        self.quantities, self.period, self.filename, self.rows = list(quantities), int(period), filename, []
+        context.current.loggers.append(self)
+        context.current.engine_dirty = True
+
+    def query(self, quantity):
+        th = context.current.engine.thermo()
+        th["pair_lj_energy"] = th["pe"]
+        return float(th[self.QUANTITIES.get(quantity, quantity)])
+
+
+analyze.log = _Log
+
+
+# ---- hoomd.run ------------------------------------------------------------------------------------------------------------
+def _configure_engine():
+    """(Re)build the device-resident system from the recorded commands: what System::run's prepRun / update_rcut /
+    update_coeffs do in the reference before the first step."""
+    from .engine import System
+    ctx = context.current
+    sysd = ctx.system
+    if ctx.integrator is None:
+        raise RuntimeError("Cannot run without an integrator")  # the reference warns and integrates nothing
+    methods = [m for m in ctx.integration_methods if m.enabled]
+    if len(methods) != 1:
+        raise RuntimeError("hoomd_b200: exactly one enabled integration method is supported, got %d" % len(methods))
+    ljs = [f for f in ctx.forces if isinstance(f, _LJ) and f.enabled]
+    if len(ljs) != 1:
+        raise RuntimeError("hoomd_b200: exactly one md.pair.lj force is supported, got %d" % len(ljs))
+    lj = ljs[0]
+    if ctx.engine is not None:  # carry the state over
+        sysd.take_snapshot()
+        ctx.engine.close()
+    eng = System(sysd.pos4, (sysd.box.Lx, sysd.box.Ly, sysd.box.Lz), ntypes=len(sysd.types), vel4=sysd.vel4,
+                 image=sysd.image)
+    t = lj.tables(sysd.types)
+    need_virial = any("pressure" in lg.quantities for lg in ctx.loggers)
+    eng.setup_lj(r_cut=t["r_cut"], epsilon=t["epsilon"], sigma=t["sigma"], alpha=t["alpha"], r_buff=lj.nlist.r_buff,
+                 check_period=lj.nlist.check_period, shift_mode=lj.shift_mode,
+                 r_on=t["r_on"] if lj.shift_mode == 2 else None)
+    eng.set_virial(need_virial)
+    eng.setup_integrator(ctx.integrator.dt)
+    m = methods[0]
+    if isinstance(m, _NVE):
+        eng.add_nve(limit=m.limit, zero_force=m.zero_force)
+    else:
+        gamma = [m.gamma.get(tn, 1.0) for tn in sysd.types]
+        eng.add_langevin(m.kT, m.seed, gamma=gamma, noiseless_t=m.noiseless_t)
+    eng.set_sorter(ctx.sorter.period if ctx.sorter.enabled else 0)
+    eng.set_timestep(ctx.timestep)
+    ctx.engine, ctx.engine_dirty = eng, False
+
+
+def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_period=0, callback=None, quiet=False):
+    """hoomd.run: advance tsteps steps; logged quantities are sampled every `period` steps (hoomd/__init__.py run)"""
+    _require_context()
+    ctx = context.current
+    if ctx.system is None:
+        raise RuntimeError("Cannot run before initialization")
+    if ctx.engine is None or ctx.engine_dirty:
+        _configure_engine()
+    eng = ctx.engine
+    tsteps = int(tsteps)
+    periods = [lg.period for lg in ctx.loggers] + ([int(callback_period)] if callback and callback_period else [])
+    done = 0
+    while done < tsteps:
+        ts = eng.timestep
+        nxt = tsteps - done
+        for p in periods:
+            nxt = min(nxt, p - ts % p)
+        for lg in ctx.loggers:
+            if ts % lg.period == 0:
+                lg.rows.append([ts] + [lg.query(q) for q in lg.quantities])
+        if callback and callback_period and ts % callback_period == 0:
+            callback(ts)
+        eng.run(nxt)
+        done += nxt
+    ctx.timestep = eng.timestep
+
+
+def get_step():
+    return context.current.timestep if context.current else 0
+
+
+context = _ContextModule()
+
+
+def install():
+    """register this module as `hoomd` (+ submodules) so that unmodified job scripts import it"""
+    me = sys.modules[__name__]
+    sys.modules["hoomd"] = me
+    for name, mod in (("context", context), ("init", init), ("lattice", lattice), ("data", data), ("group", group),
+                      ("update", update), ("md", md), ("analyze", analyze)):
+        sys.modules["hoomd." + name] = mod
+    for name, mod in (("nlist", md.nlist), ("pair", md.pair), ("integrate", md.integrate)):
+        sys.modules["hoomd.md." + name] = mod
+    return me

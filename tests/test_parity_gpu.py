@@ -330,3 +330,47 @@ def test_thermo(ref, hb):
     assert abs(tr["T"] - tg["T"]) < 1e-4 * abs(tr["T"])
     assert abs(tr["P"] - tg["P"]) < 2e-4 * abs(tr["P"])
     assert tr["ndof"] == tg["ndof"]
+
+
+def test_nve_energy_drift_matches_reference(ref, hb):
+    """BASELINE north_star: NVE energy drift over 1e5 steps must match the reference's.  1000-particle LJ liquid
+    (rho 0.2, r_cut 3.0 unshifted, r_buff 0.4, dt 0.005), equilibrated by the reference, then 1e5 NVE steps on both;
+    total energy per particle sampled every 2000 steps.  Trajectories decorrelate (chaos), so the comparison is between
+    the drift statistics: end-to-end drift and RMS fluctuation of E/N agree, and both stay small."""
+    import os
+    nsteps = int(os.environ.get("HOOMD_B200_DRIFT_STEPS", "100000"))
+    pos, vel, L = _liquid(hb, n_side=10)
+    lj = dict(r_cut=3.0, r_buff=0.4)
+    r0 = ref.RefSystem(pos, (L, L, L), vel4=vel)
+    r0.setup_lj(full=True, **lj)
+    r0.setup_integrator(0.005)
+    r0.add_langevin(1.2, 3)
+    r0.run(3000)
+    st = r0.particles()
+    order = np.argsort(st["tag"])
+    p0, v0, i0 = st["pos"][order], st["vel"][order], st["image"][order]
+
+    def trace(s):
+        s.setup_lj(**lj) if not isinstance(s, ref.RefSystem) else s.setup_lj(full=False, **lj)
+        s.setup_integrator(0.005)
+        s.add_nve()
+        s.set_sorter(300)
+        e = []
+        for _ in range(nsteps // 2000):
+            s.run(2000)
+            th = s.thermo()
+            e.append((th["ke"] + th["pe"]) / len(p0))
+        return np.array(e)
+
+    eg = trace(hb.System(p0, (L, L, L), vel4=v0, image=i0))
+    er = trace(ref.RefSystem(p0, (L, L, L), vel4=v0, image=i0))
+    scale = abs(er.mean())
+    drift_g, drift_r = (eg[-1] - eg[0]) / scale, (er[-1] - er[0]) / scale
+    slope_g = np.polyfit(np.arange(len(eg)), eg, 1)[0] * len(eg) / scale
+    slope_r = np.polyfit(np.arange(len(er)), er, 1)[0] * len(er) / scale
+    print("E/N ref %.5f gpu %.5f | drift ref %.2e gpu %.2e | fitted ref %.2e gpu %.2e | rms ref %.2e gpu %.2e" % (
+        er.mean(), eg.mean(), drift_r, drift_g, slope_r, slope_g, er.std() / scale, eg.std() / scale))
+    assert abs(eg[0] - er[0]) < 2e-4 * scale          # same start
+    assert abs(slope_g) < 5e-3 and abs(slope_r) < 5e-3  # both conserve energy to FP32 + cutoff-jump level
+    assert abs(slope_g - slope_r) < 5e-3
+    assert abs(eg.std() - er.std()) < 3e-3 * scale

@@ -1,0 +1,115 @@
+"""The reference's job-script surface (hoomd_b200/script.py): README lj.py runs unmodified; names, argument meaning and
+error behaviour follow hoomd/md/nlist.py, pair.py, integrate.py."""
+import numpy as np
+import pytest
+
+README_LJ = """
+import hoomd
+from hoomd import md
+hoomd.context.initialize()
+
+# create a 10x10x10 square lattice of particles with name A
+hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name='A'), n=10)
+# specify Lennard-Jones interactions between particle pairs
+nl = md.nlist.cell()
+lj = md.pair.lj(r_cut=3.0, nlist=nl)
+lj.pair_coeff.set('A', 'A', epsilon=1.0, sigma=1.0)
+# integrate at constant temperature
+all = hoomd.group.all();
+md.integrate.mode_standard(dt=0.005)
+hoomd.md.integrate.langevin(group=all, kT=1.2, seed=4)
+# run 10,000 time steps
+hoomd.run(NSTEPS)
+"""
+
+
+def _fresh():
+    from hoomd_b200 import script
+    script.install()
+    script.context.initialize()
+    return script
+
+
+def test_surface_and_errors_without_gpu():
+    hoomd = _fresh()
+    with pytest.raises(RuntimeError):
+        hoomd.md.nlist.cell()  # before initialization, like the reference
+    sysd = hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=10)
+    assert len(sysd.particles) == 1000 and list(sysd.particles.types) == ["A"]
+    snap = sysd.take_snapshot()
+    # 10x10x10 sc lattice centred in L = 20: first particle at -9, z fastest (SnapshotParticleData::replicate order)
+    assert snap.box.Lx == 20.0
+    np.testing.assert_allclose(snap.particles.position[0], [-9, -9, -9])
+    np.testing.assert_allclose(snap.particles.position[1], [-9, -9, -7])
+    np.testing.assert_allclose(snap.particles.position[-1], [9, 9, 9])
+    with pytest.raises(RuntimeError):
+        hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0), n=2)  # Cannot initialize more than once
+    nl = hoomd.md.nlist.cell(r_buff=0.3, check_period=2)
+    lj = hoomd.md.pair.lj(r_cut=2.5, nlist=nl)
+    assert nl.r_buff == 0.3 and nl.check_period == 2 and lj in nl.subscribers
+    with pytest.raises(RuntimeError):
+        lj.set_params(mode="bogus")
+    lj.set_params(mode="shift")
+    assert lj.shift_mode == 1
+    # missing coefficients are an error at run time (update_coeffs), not at construction
+    with pytest.raises(RuntimeError):
+        lj.tables(["A"])
+    lj.pair_coeff.set("A", "A", epsilon=1.5, sigma=0.9)
+    t = lj.tables(["A"])
+    assert t["epsilon"][0, 0] == 1.5 and t["alpha"][0, 0] == 1.0 and t["r_cut"][0, 0] == 2.5
+    lj.pair_coeff.set("A", "A", r_cut=2.0)
+    assert lj.tables(["A"])["r_cut"][0, 0] == 2.0
+    hoomd.md.integrate.mode_standard(dt=0.005)
+    lv = hoomd.md.integrate.langevin(group=hoomd.group.all(), kT=1.2, seed=4)
+    lv.set_gamma("A", 2.0)
+    with pytest.raises(RuntimeError):
+        lv.set_gamma("B", 1.0)
+
+
+def test_two_type_coefficient_table():
+    hoomd = _fresh()
+    snap = hoomd.data.make_snapshot(N=4, box=hoomd.data.boxdim(L=10), particle_types=["A", "B"])
+    snap.particles.typeid[:] = [0, 1, 0, 1]
+    hoomd.init.read_snapshot(snap)
+    nl = hoomd.md.nlist.cell()
+    lj = hoomd.md.pair.lj(r_cut=2.5, nlist=nl)
+    lj.pair_coeff.set("A", "A", epsilon=1.0, sigma=1.0)
+    lj.pair_coeff.set("A", "B", epsilon=1.5, sigma=0.8, r_cut=2.0)
+    with pytest.raises(RuntimeError):
+        lj.tables(["A", "B"])  # (B, B) missing
+    lj.pair_coeff.set("B", "B", epsilon=0.5, sigma=0.88, r_cut=2.2)
+    t = lj.tables(["A", "B"])
+    assert t["epsilon"][0, 1] == t["epsilon"][1, 0] == 1.5
+    assert t["r_cut"][1, 1] == 2.2 and t["r_cut"][0, 1] == 2.0 and t["r_cut"][0, 0] == 2.5
+
+
+@pytest.mark.gpu
+def test_readme_lj_runs_unmodified_and_matches_reference():
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    hoomd = _fresh()
+    nsteps = 60
+    ns = {}
+    exec(README_LJ.replace("NSTEPS", str(nsteps)), ns)
+    snap = hoomd.context.current.system.take_snapshot()
+    assert hoomd.get_step() == nsteps
+    # the same script on the reference's CPU classes
+    from hoomd_b200 import workloads
+    pos, vel, L = workloads.sc_lattice(10, 2.0)
+    assert L == 20.0
+    r = R.RefSystem(pos, (L, L, L), vel4=vel)
+    r.setup_lj(r_cut=3.0, r_buff=0.4, full=True)
+    r.setup_integrator(0.005)
+    r.add_langevin(1.2, 4)
+    r.set_sorter(300)
+    r.run(nsteps)
+    a = r.particles()
+    order = np.argsort(a["tag"])
+    # identical lattice order => tags coincide
+    assert np.abs(a["pos"][order][:, :3] - snap.particles.position).max() < 2e-4
+    assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
+    # logging surface
+    log = hoomd.analyze.log(filename=None, quantities=["temperature", "potential_energy"], period=10)
+    hoomd.run(20)
+    assert len(log.rows) == 2 and 0.0 < log.rows[0][1] < 5.0
