@@ -374,3 +374,92 @@ def test_nve_energy_drift_matches_reference(ref, hb):
     assert abs(slope_g) < 5e-3 and abs(slope_r) < 5e-3  # both conserve energy to FP32 + cutoff-jump level
     assert abs(slope_g - slope_r) < 5e-3
     assert abs(eg.std() - er.std()) < 3e-3 * scale
+
+
+def _ka_system(hb, n_side, seed=42):
+    """Kob-Andersen 80:20 (BASELINE config 3): rho 1.2, types by permutation, per-pair eps/sigma/r_cut, shifted LJ"""
+    rho = 1.2
+    pos, vel, L = hb.workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=1.0, seed=seed, ntypes=2,
+                                          type_fractions=[0.8, 0.2])
+    return pos, vel, L
+
+
+def test_kob_andersen_small_vs_reference(ref, hb):
+    """two-type parameter table, per-pair r_cut, mode=shift, per-type gamma Langevin: nlist exact, forces 1e-5,
+    60-step trajectory with the same rebuild count (BASELINE config 3 at N = 1728)"""
+    pos, vel, L = _ka_system(hb, 12)
+    pos[:, :3] += np.random.default_rng(1).normal(0, 0.05, (len(pos), 3)).astype(np.float32)
+    lj = dict(shift_mode=1, r_buff=0.3, **hb.workloads.KA_PARAMS)
+    r, g = _pair(ref, hb, pos, L, ntypes=2, vel=vel, **lj)
+    for s in (r, g):
+        s.set_virial(True)
+        s.compute_forces(0)
+    _assert_nlist_equal(r, g)
+    fr, vr = r.forces()
+    fg, vg = g.forces()
+    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+    assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < FORCE_RTOL * 10
+    escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
+    assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < FORCE_RTOL * 10
+    assert abs(fr[:, 3].astype(np.float64).sum() - fg[:, 3].astype(np.float64).sum()) \
+        < FORCE_RTOL * abs(fr[:, 3].astype(np.float64).sum())
+    for s in (r, g):
+        s.setup_integrator(0.002)
+        s.add_langevin(1.0, 7, gamma=[1.0, 1.5])
+        s.run(60)
+    a, b = r.particles(), g.particles()
+    assert np.array_equal(a["tag"], b["tag"])
+    assert np.abs(a["pos"][:, :3] - b["pos"][:, :3]).max() < 5e-4
+    assert r.nlist_stats()["updates"] == g.stats()["updates"]
+
+
+def _full_size_properties(g, N, ntypes):
+    """size-independent properties of a full list + its forces: the list is symmetric (j in N(i) <=> i in N(j)),
+    entries are in range and unique per row, and Newton's third law makes the net force vanish"""
+    g.compute_forces(0)
+    n, head, nl = g.nlist()
+    assert n.sum() % 2 == 0
+    rows = np.repeat(np.arange(N, dtype=np.int64), n)
+    idx = (head.astype(np.int64)[:, None] + np.arange(n.max(), dtype=np.int64)[None, :])
+    mask = np.arange(n.max())[None, :] < n[:, None]
+    cols = nl[idx[mask]].astype(np.int64)
+    assert cols.min() >= 0 and cols.max() < N and (cols != rows).all()
+    fwd = np.sort(rows * N + cols)
+    bwd = np.sort(cols * N + rows)
+    assert np.array_equal(fwd, bwd), "neighbor list is not symmetric"
+    assert len(np.unique(fwd)) == len(fwd), "duplicate neighbor entries"
+    f = g.forces(False)[0].astype(np.float64)
+    fsum = np.abs(f[:, :3].sum(axis=0)).max()
+    assert fsum < 1e-3 * np.abs(f[:, :3]).sum() / N * np.sqrt(N), fsum
+
+
+def test_full_size_lj64k_properties(hb):
+    """BASELINE config 2 at full size (N = 64,000)"""
+    pos, vel, L = hb.workloads.lj_liquid(64000)
+    pos[:, :3] += np.random.default_rng(2).normal(0, 0.2, (len(pos), 3)).astype(np.float32)
+    g = hb.System(pos, (L, L, L), vel4=vel)
+    g.setup_lj(r_cut=3.0, r_buff=0.4)
+    _full_size_properties(g, len(pos), 1)
+    g.setup_integrator(0.005)
+    g.add_nve()
+    g.set_sorter(300)
+    p0 = (g.particles()["vel"][:, :3].astype(np.float64)).sum(axis=0)
+    g.run(400)
+    p1 = (g.particles()["vel"][:, :3].astype(np.float64)).sum(axis=0)
+    assert np.abs(p1 - p0).max() < 0.05, (p0, p1)  # total momentum conserved (mass 1)
+
+
+def test_full_size_ka256k_properties(hb):
+    """BASELINE config 3 at full size (N = 262,144 = 64^3, closest cube to 256k), Langevin kT = 1.0"""
+    pos, vel, L = _ka_system(hb, 64)
+    pos[:, :3] += np.random.default_rng(3).normal(0, 0.03, (len(pos), 3)).astype(np.float32)
+    g = hb.System(pos, (L, L, L), ntypes=2, vel4=vel)
+    g.setup_lj(shift_mode=1, r_buff=0.3, **hb.workloads.KA_PARAMS)
+    _full_size_properties(g, len(pos), 2)
+    g.setup_integrator(0.002)
+    g.add_langevin(1.0, 7)
+    g.set_sorter(300)
+    g.run(300)
+    th = g.thermo()
+    assert 0.5 < th["T"] < 1.5 and np.isfinite(th["pe"])
+    assert g.stats()["updates"] > 0
