@@ -397,7 +397,7 @@ def main():
                 "clocks": clocks,
                 "roofline": roofline,
                 "e2e": {"value": e2e_tps, "unit": "timesteps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "thermo_T": th["T"]},
+                        "thermo_T": th["T"], "ms_runs": [1e3 * x for x in e2e_t]},
                 "cpu_baseline": cpu}
         if scale_ref:
             line["scale_ref"] = scale_ref

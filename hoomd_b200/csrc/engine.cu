@@ -360,7 +360,9 @@ static void nlist_build_head_list(b200_system* s)
     if (size > s->nlist.n)
         {
         size_t alloc_size = s->nlist.n ? s->nlist.n : 1;
-        while (size > alloc_size) alloc_size = ((size_t)(((float)alloc_size) * 1.125f)) + 1;
+        // amortised growth (the reference uses x1.125, hoomd/md/NeighborList.cc:1365-1380; a larger factor keeps the
+        // captured step graph, which bakes the list's address, alive across more Nmax increases)
+        while (size > alloc_size) alloc_size = ((size_t)(((float)alloc_size) * 1.25f)) + 1;
         s->nlist.alloc(alloc_size, false);
         invalidate_graph(s);
         }

@@ -91,12 +91,13 @@ static cudaError_t launch_tpp(const b200_pair_args& a, const typename Evaluator:
         }
     }
 
-// default threads-per-particle: enough groups to fill 148 SMs x 2048 threads at small N, 1-2 lanes at large N where
-// the kernel is bound by the nlist stream rather than by latency
+// default threads-per-particle (measured on B200, LJ liquid rho 0.2: 64k particles 29.4k / 27.3k / 25.2k steps/s at
+// TPP 2 / 4 / 8; 1M particles 3.7k / 3.2k at TPP 2 / 4): 2 lanes once N fills the 148 SMs, more lanes for small systems
 unsigned int pick_pair_tpp(unsigned int N)
     {
-    if (N <= 100000u) return 8;
-    if (N <= 400000u) return 4;
+    if (N <= 12000u) return 16;
+    if (N <= 24000u) return 8;
+    if (N <= 48000u) return 4;
     return 2;
     }
 
