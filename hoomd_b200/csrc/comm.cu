@@ -298,40 +298,45 @@ __global__ void __launch_bounds__(256) k_mg_ghost_plan(const __grid_constant__ M
     {
     if (enable && !*enable) return;
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= l.st->N) return;
-    const float4 p = pos[i];
+    const unsigned int lane = threadIdx.x & 31;
+    const bool active = i < l.st->N;
+    const float4 p = active ? pos[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     const float x[3] = {p.x, p.y, p.z};
     bool nlo[3], nhi[3];
     bool any = false;
 #pragma unroll
     for (int a = 0; a < 3; a++)
         {
-        nlo[a] = c.split[a] && (x[a] < c.lo[a] + c.r_ghost);
-        nhi[a] = c.split[a] && (x[a] >= c.hi[a] - c.r_ghost);
+        nlo[a] = active && c.split[a] && (x[a] < c.lo[a] + c.r_ghost);
+        nhi[a] = active && c.split[a] && (x[a] >= c.hi[a] - c.r_ghost);
         any |= nlo[a] | nhi[a];
         }
-    if (!any) return;
-    const unsigned int ptag = l.tag[i];
-    for (int dz = -1; dz <= 1; dz++)
+    if (!__any_sync(0xffffffffu, any)) return; // interior warp
+    const unsigned int ptag = active ? l.tag[i] : 0u;
+    // Slots are handed out per warp (one atomic per warp and direction, lanes ranked by ballot): the particles of a
+    // warp are neighbors along the space-filling curve, so their ghost copies land next to each other on the receiver
+    // and its position gathers keep their locality.
+    for (int d = 0; d < MG_NDIR; d++)
         {
-        if ((dz < 0 && !nlo[2]) || (dz > 0 && !nhi[2])) continue;
-        for (int dy = -1; dy <= 1; dy++)
+        if (c.seg_cap[d] == 0u) continue; // unused direction (uniform)
+        const int dx = d % 3 - 1, dy = (d / 3) % 3 - 1, dz = d / 9 - 1;
+        const bool send = !((dx < 0 && !nlo[0]) || (dx > 0 && !nhi[0]) || (dy < 0 && !nlo[1]) || (dy > 0 && !nhi[1])
+                            || (dz < 0 && !nlo[2]) || (dz > 0 && !nhi[2]));
+        const unsigned int mask = __ballot_sync(0xffffffffu, send);
+        if (!mask) continue;
+        unsigned int base = 0;
+        if (lane == (unsigned int)(__ffs(mask) - 1)) base = atomicAdd(&l.ms->gsend_cnt[d], (unsigned int)__popc(mask));
+        base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+        if (send)
             {
-            if ((dy < 0 && !nlo[1]) || (dy > 0 && !nhi[1])) continue;
-            for (int dx = -1; dx <= 1; dx++)
+            const unsigned int slot = base + __popc(mask & ((1u << lane) - 1u));
+            if (slot < c.seg_cap[d])
                 {
-                if ((dx < 0 && !nlo[0]) || (dx > 0 && !nhi[0])) continue;
-                const int d = (dz + 1) * 9 + (dy + 1) * 3 + (dx + 1);
-                if (d == MG_DIR_STAY) continue;
-                const unsigned int slot = atomicAdd(&l.ms->gsend_cnt[d], 1u);
-                if (slot < c.seg_cap[d])
-                    {
-                    l.plan_src[c.seg_off[d] + slot] = i;
-                    c.peer_tag[d][c.Ncap + c.seg_off[d] + slot] = ptag;
-                    }
-                else
-                    atomicOr(&l.ms->error, 2u);
+                l.plan_src[c.seg_off[d] + slot] = i;
+                c.peer_tag[d][c.Ncap + c.seg_off[d] + slot] = ptag;
                 }
+            else
+                atomicOr(&l.ms->error, 2u);
             }
         }
     }

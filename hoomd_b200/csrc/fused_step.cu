@@ -11,6 +11,7 @@
 #include "pair_body.cuh"
 #include "kernels.h"
 #include "decide.cuh"
+#include <cstdlib>
 
 namespace b200
 {
@@ -266,6 +267,17 @@ cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, c
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>
 static cudaError_t md_step_mt(const MdStepArgs<Evaluator>& a, cudaStream_t stream)
     {
+    // L1 / shared split: the kernel needs <= 10 kB of shared memory; the neighbor-position gathers live off L1
+    static const int carveout = getenv("HOOMD_B200_CARVEOUT") ? atoi(getenv("HOOMD_B200_CARVEOUT")) : -1;
+    static bool configured = false;
+    if (!configured && carveout >= 0)
+        {
+        cudaFuncSetAttribute(k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, true>,
+                             cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        cudaFuncSetAttribute(k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false>,
+                             cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        configured = true;
+        }
     const unsigned int bs = MD_BLOCK;
     const unsigned int per_block = bs / TPP;
     const unsigned int grid = (a.N + per_block - 1) / per_block;
