@@ -83,6 +83,7 @@ SYMBOLS = [
     "b200_sys_set_accel", "b200_sys_get_particles", "b200_sys_setup_lj", "b200_sys_set_virial",
     "b200_sys_setup_integrator", "b200_sys_add_nve", "b200_sys_add_langevin", "b200_sys_set_sorter",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
+    "b200_sys_set_pair_mode", "b200_sys_get_pair_mode",
     "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
     "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
     "b200_sys_get_thermo", "b200_sys_time_kernel",
@@ -153,6 +154,8 @@ def lib():
     L.b200_sys_get_timestep.argtypes = [vp]
     L.b200_sys_get_timestep.restype = C.c_uint
     L.b200_sys_set_tuning.argtypes = [vp, C.c_uint, C.c_int]
+    L.b200_sys_set_pair_mode.argtypes = [vp, C.c_int, C.c_uint, C.c_uint, C.c_uint, C.c_uint]
+    L.b200_sys_get_pair_mode.argtypes = [vp, C.POINTER(C.c_uint)]
     L.b200_sys_compute_nlist.argtypes = [vp, C.c_uint]
     L.b200_sys_compute_forces.argtypes = [vp, C.c_uint]
     L.b200_sys_run.argtypes = [vp, C.c_uint, c_double_p, c_double_p]

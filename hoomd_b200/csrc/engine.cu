@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "comm.cuh"
+#include "tile.h"
 #include <string>
 #include <vector>
 #include <chrono>
@@ -21,6 +22,8 @@
 #include <cmath>
 #include <cstring>
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 namespace b200
 {
@@ -185,6 +188,15 @@ struct b200_system
     MgState* h_ms = nullptr;         // pinned
     DevBuf<unsigned int> holes, low_holes, hole_mark, plan_src;
     DevBuf<unsigned char> slot_dir;
+
+    // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
+    int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
+    bool tile_on = false;
+    unsigned int tile_req[3] = {0, 0, 0}; // requested cells per tile (0 = auto)
+    TileGeom tile_geom = {};
+    unsigned int tile_tpp = 0, tile_Nmax = 0, tile_pitch = 0;
+    DevBuf<uint4> tile_ell;
+    DevBuf<unsigned int> tile_nn, tile_perm, tile_cond, ck_tag;
     };
 
 namespace b200
@@ -205,7 +217,8 @@ static void cell_list_args(b200_system* s, b200_cell_list_args& a)
     a.d_cell_start = s->cell_start.p;
     a.d_cell_xyzf = (float*)s->cell_xyzf.p;
     a.d_cell_type = s->ntypes > 1 ? s->cell_type.p : nullptr;
-    a.d_cell_idx = nullptr;
+    a.d_cell_idx = s->tile_on ? s->tile_perm.p : nullptr;
+    a.flag_type = s->tile_on ? 1 : 0; // tile path: cell_xyzf is the cell-sorted copy of pos (type in w)
     a.d_conditions = s->cl_conditions.p;
     a.d_cell_count = s->cell_count.p;
     a.d_particle_cell = s->particle_cell.p;
@@ -281,6 +294,11 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
 
 namespace b200
 {
+static void tile_nlist_build(b200_system* s);
+static bool tile_check_conditions(b200_system* s);
+static void tile_step_args(b200_system* s, TileStepArgs& a, int force_only);
+static void tile_enqueue_rebuild(b200_system* s, const unsigned int* enable, float4* pos);
+
 // ---- CellList ---------------------------------------------------------------------------------------------------------
 static void cell_list_check_conditions(b200_system* s)
     {
@@ -351,6 +369,7 @@ static void nlist_update_rlist(b200_system* s)
 // NeighborList::buildHeadList + resizeNlist (hoomd/md/NeighborList.cc:1336-1380)
 static void nlist_build_head_list(b200_system* s)
     {
+    if (s->tile_on) return; // ELL rows: no head list
     CUDA_OK(b200_nlist_build_head_list(s->head_list.p, s->d_req_size.p, s->d_Nmax.p, (const float*)s->pos.p,
                                        s->mg ? s->Ncap : s->N,
                                        s->ntypes, s->stream));
@@ -468,6 +487,11 @@ static void nlist_compute(b200_system* s, unsigned int ts)
     if (s->force_update) nlist_build_head_list(s);
     if (nlist_needs_updating(s, ts))
         {
+        if (s->tile_on)
+            {
+            tile_nlist_build(s);
+            return;
+            }
         bool overflowed = false;
         do
             {
@@ -490,7 +514,17 @@ static void compute_net_force(b200_system* s, unsigned int ts)
     nlist_compute(s, ts);
     b200_pair_args a;
     pair_args(s, a);
-    CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
+    if (s->tile_on)
+        {
+        FusedStepArgs fa;
+        fused_args(s, fa);
+        TileStepArgs ta;
+        tile_step_args(s, ta, 1);
+        CUDA_OK(launch_md_step_tile_lj(a, (const float*)s->d_params.p, fa, ta, s->pos.p, nullptr, 0, s->d_state.p, 0ull, 0,
+                                       s->stream));
+        }
+    else
+        CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
     s->kernels_last_run += 1;
     }
 
@@ -539,8 +573,16 @@ static void prep_run(b200_system* s, unsigned int ts)
     }
 
 // SFCPackUpdater::update (hoomd/SFCPackUpdater.cc:70-108)
-static void sorter_update(b200_system* s)
+static void sorter_update(b200_system* s, bool periodic = true)
     {
+    if (s->tile_on && periodic)
+        {
+        // the particles are re-ordered by cell at every rebuild already; keep the reference's schedule of forced list
+        // rebuilds (notifyParticleSort -> NeighborList::forceUpdate) so the update counters stay comparable
+        s->force_update = true;
+        s->cl_force = true;
+        return;
+        }
     const unsigned int N = s->N, C = s->Ncap;
     if (s->sort_order.n < C)
         {
@@ -592,6 +634,12 @@ namespace b200
 // lets them return at once on !need_rebuild (the `enable` pointer).
 static void enqueue_rebuild(b200_system* s, const unsigned int* enable, const float4* pos)
     {
+    if (s->tile_on)
+        {
+        tile_enqueue_rebuild(s, enable, const_cast<float4*>(pos));
+        CUDA_OK(launch_tile_post(s->d_state.p, s->tile_cond.p, s->tile_Nmax, s->stream));
+        return;
+        }
     b200_cell_list_args ca;
     cell_list_args(s, ca);
     ca.d_pos = (const float*)pos;
@@ -609,6 +657,14 @@ static void enqueue_md_step(b200_system* s, const FusedStepArgs& fa, int phase, 
     pair_args(s, pa);
     const float4* pin = phase == 0 ? s->pos.p : s->pos_alt.p;
     float4* pout = phase == 0 ? s->pos_alt.p : s->pos.p;
+    if (s->tile_on)
+        {
+        TileStepArgs ta;
+        tile_step_args(s, ta, 0);
+        CUDA_OK(launch_md_step_tile_lj(pa, (const float*)s->d_params.p, fa, ta, pin, pout, phase == 1, s->d_state.p, handle,
+                                       use_cond, s->stream));
+        return;
+        }
     CUDA_OK(launch_md_step_lj(pa, (const float*)s->d_params.p, fa, pin, pout, phase == 1, s->d_state.p, handle, use_cond,
                               s->stream));
     }
@@ -745,6 +801,12 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         {
         s->ck_pos.alloc(N); s->ck_vel.alloc(N); s->ck_last_pos.alloc(N); s->ck_accel.alloc(N); s->ck_image.alloc(N);
         }
+    if (s->tile_on)
+        {
+        // rebuilds re-order the particles: the checkpoint carries the tags too
+        if (s->ck_tag.n < N) s->ck_tag.alloc(N);
+        CUDA_OK(cudaMemcpyAsync(s->ck_tag.p, s->tag.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
+        }
     // checkpoint (device to device, ~72 B/particle per chunk)
     CUDA_OK(cudaMemcpyAsync(s->ck_pos.p, s->pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->ck_vel.p, s->vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
@@ -797,7 +859,19 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
         s->force_update = ck_force_update;
-        if (!ck_force_update)
+        if (s->tile_on)
+            {
+            CUDA_OK(cudaMemcpyAsync(s->tag.p, s->ck_tag.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
+            // grow the capacity that overflowed (the device rebuild left its high-water marks in tile_cond)
+            tile_check_conditions(s);
+            if (!ck_force_update)
+                {
+                // the checkpointed order IS the cell order of last_pos: this rebuild is the identity permutation
+                CUDA_OK(launch_merge_xyz_w(s->pos.p, s->ck_last_pos.p, s->ck_pos.p, N, s->stream));
+                tile_nlist_build(s);
+                }
+            }
+        else if (!ck_force_update)
             {
             // re-create the list that was current at the checkpoint: it is a pure function of last_pos
             CUDA_OK(launch_merge_xyz_w(s->pos.p, s->ck_last_pos.p, s->ck_pos.p, N, s->stream));
@@ -820,7 +894,9 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         return;
         }
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + 6ull * rebuilds) : 14ull * nreplay);
+    const unsigned long long rk = s->tile_on ? 8ull : 6ull; // kernels per rebuild
+    s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + rk * rebuilds)
+                                                                             : (2ull + 2ull * rk) * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
     s->num_updates += st.num_updates;
@@ -840,6 +916,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
 } // namespace b200
 
 #include "engine_mg.inl"
+#include "engine_tile.inl"
 
 namespace b200
 {
@@ -850,6 +927,15 @@ static void sys_open_device(b200_system* s)
     if (ndev == 0) throw std::runtime_error("no CUDA device: hoomd_b200 has no CPU fallback");
     CUDA_OK(cudaSetDevice(s->device));
     CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    // developer overrides of the pair path: HOOMD_B200_PAIR_MODE = -1 | 0 | 1, HOOMD_B200_TILE = "bx,by,bz,tpp"
+    if (const char* m = getenv("HOOMD_B200_PAIR_MODE")) s->pair_mode = atoi(m);
+    if (const char* t = getenv("HOOMD_B200_TILE"))
+        {
+        unsigned int v[4] = {0, 0, 0, 0};
+        sscanf(t, "%u,%u,%u,%u", &v[0], &v[1], &v[2], &v[3]);
+        s->tile_req[0] = v[0]; s->tile_req[1] = v[1]; s->tile_req[2] = v[2];
+        s->tile_tpp = v[3];
+        }
     }
 
 // per-particle arrays sized for the local capacity; pos / pos_alt / tag are allocated by the caller (they carry the
@@ -1104,6 +1190,7 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     s->cl_force = true;
     s->nl_first_compute = true;
     invalidate_graph(s);
+    tile_configure(s);
     SYS_CATCH(s)
     }
 
@@ -1160,7 +1247,7 @@ int b200_sys_set_sorter(b200_system* s, unsigned int period)
 int b200_sys_sort_now(b200_system* s)
     {
     SYS_TRY(s)
-    sorter_update(s);
+    sorter_update(s, false);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     SYS_CATCH(s)
     }
@@ -1173,6 +1260,34 @@ int b200_sys_set_tuning(b200_system* s, unsigned int pair_tpp, int use_graph)
     s->pair_tpp = pair_tpp;
     s->use_graph = use_graph;
     invalidate_graph(s);
+    return 0;
+    }
+
+int b200_sys_set_pair_mode(b200_system* s, int mode, unsigned int bx, unsigned int by, unsigned int bz, unsigned int tpp)
+    {
+    SYS_TRY(s)
+    if (mode < -1 || mode > 1) throw std::runtime_error("pair_mode must be -1 (auto), 0 (CSR walk) or 1 (cell tiles)");
+    if (tpp != 0 && tpp != 1 && tpp != 2 && tpp != 4) throw std::runtime_error("tile: tpp must be 0 (auto), 1, 2 or 4");
+    s->pair_mode = mode;
+    s->tile_req[0] = bx; s->tile_req[1] = by; s->tile_req[2] = bz;
+    if (bx == 0 || by == 0 || bz == 0) s->tile_req[0] = s->tile_req[1] = s->tile_req[2] = 0;
+    s->tile_tpp = tpp;
+    const bool was = s->tile_on;
+    tile_configure(s);
+    if (was != s->tile_on || s->tile_on)
+        {
+        s->force_update = true;
+        s->cl_force = true;
+        }
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_pair_mode(b200_system* s, unsigned int* out8)
+    {
+    out8[0] = s->tile_on ? 1u : 0u;
+    out8[1] = s->tile_geom.b.x; out8[2] = s->tile_geom.b.y; out8[3] = s->tile_geom.b.z;
+    out8[4] = s->tile_geom.cap; out8[5] = s->tile_tpp; out8[6] = s->tile_Nmax;
+    out8[7] = s->tile_geom.tdim.x * s->tile_geom.tdim.y * s->tile_geom.tdim.z;
     return 0;
     }
 
@@ -1277,12 +1392,29 @@ int b200_sys_get_forces(b200_system* s, float* force4, float* virial6)
     SYS_CATCH(s)
     }
 
-unsigned int b200_sys_get_nlist_size(b200_system* s) { return (unsigned int)s->nlist.n; }
+unsigned int b200_sys_get_nlist_size(b200_system* s)
+    {
+    return s->tile_on ? s->N * s->tile_Nmax : (unsigned int)s->nlist.n;
+    }
 
 int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist,
                        unsigned int nlist_len)
     {
     SYS_TRY(s)
+    if (s->tile_on)
+        {
+        // tile slots -> particle indices (current storage order), rows of tile_Nmax entries
+        DevBuf<unsigned int> on, oh, ol;
+        on.alloc(s->N); oh.alloc(s->N); ol.alloc((size_t)s->N * s->tile_Nmax);
+        TileBuildArgs ba;
+        tile_build_args(s, ba, nullptr, s->pos.p);
+        CUDA_OK(launch_tile_to_csr(ba, on.p, oh.p, ol.p, s->stream));
+        if (n_neigh) on.download(n_neigh, s->N, s->stream);
+        if (head) oh.download(head, s->N, s->stream);
+        if (nlist) ol.download(nlist, std::min<size_t>(nlist_len, ol.n), s->stream);
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        return 0;
+        }
     if (n_neigh) s->n_neigh.download(n_neigh, s->N, s->stream);
     if (head) s->head_list.download(head, s->N, s->stream);
     if (nlist) s->nlist.download(nlist, std::min<size_t>(nlist_len, s->nlist.n), s->stream);
@@ -1298,7 +1430,7 @@ int b200_sys_get_stats(b200_system* s, unsigned long long* out8)
     out8[4] = s->dim.x;
     out8[5] = s->dim.y;
     out8[6] = s->dim.z;
-    out8[7] = s->h_Nmax.empty() ? 0 : s->h_Nmax[0];
+    out8[7] = s->tile_on ? s->tile_Nmax : (s->h_Nmax.empty() ? 0 : s->h_Nmax[0]);
     return 0;
     }
 
@@ -1361,7 +1493,18 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
     CUDA_OK(cudaEventRecord(e0, s->stream));
     for (unsigned int k = 0; k < iters; k++)
         {
-        if (which == 0)
+        if (s->tile_on && which == 0)
+            {
+            FusedStepArgs fa;
+            fused_args(s, fa);
+            TileStepArgs ta;
+            tile_step_args(s, ta, 1);
+            CUDA_OK(launch_md_step_tile_lj(pa, (const float*)s->d_params.p, fa, ta, s->pos.p, nullptr, 0, s->d_state.p, 0ull, 0,
+                                           s->stream));
+            }
+        else if (s->tile_on)
+            tile_enqueue_rebuild(s, nullptr, s->pos.p); // identity permutation: the particles are in cell order
+        else if (which == 0)
             CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
         else
             {

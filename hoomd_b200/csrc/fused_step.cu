@@ -7,10 +7,7 @@
 //   k_post_rebuild   : overflow detection after a rebuild (hoomd/md/NeighborList.cc:1389-1405 needs the host: sticky flag)
 // Per-particle arithmetic is the shared body of integrate_body.cuh / pair_body.cuh => bit-identical to the driver kernels.
 #include "common.cuh"
-#include "integrate_body.cuh"
-#include "pair_body.cuh"
-#include "kernels.h"
-#include "decide.cuh"
+#include "md_step_body.cuh"
 #include <cstdlib>
 
 namespace b200
@@ -73,30 +70,6 @@ __global__ void k_post_rebuild(StepState* st, unsigned int* __restrict__ conditi
         }
     }
 
-// ---- the single-kernel MD step -------------------------------------------------------------------------------------------
-// One launch = PotentialPair::computeForces(ts+1) + integrateStepTwo(ts) + integrateStepOne(ts+1) + distanceCheck +
-// NeighborList::needsUpdating(ts+2).  Velocity Verlet lets step two of one update() and step one of the next run back
-// to back per particle (nothing in between reads another particle), so the only grid-wide dependencies left in a
-// step are "all positions written before any force reads them" -- solved by ping-pong position buffers (pos_in is read
-// by every neighbor gather, pos_out is written by the owner) -- and the rebuild decision, taken by the last CTA to
-// finish (ticket counter).  Arithmetic per particle is the shared bodies => bit-identical to the separate kernels.
-template<class Evaluator> struct MdStepArgs
-    {
-    const float4* pos_in; float4* pos_out; float4* vel; float3s* accel; int3* image; float4* net_force;
-    float* virial; unsigned int virial_pitch;
-    const float4* last_pos; const unsigned int* tag;
-    const unsigned int* n_neigh; const unsigned int* nlist; const unsigned int* head_list;
-    const typename Evaluator::param_type* params; const float* rcutsq; const float* ronsq; unsigned int ntypes;
-    const float* maxsq; const float* gamma;
-    unsigned int N; Box box; float dt; float r_buff; float wrap_skip_margin;
-    int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
-    int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
-    const unsigned int* d_N;  // multi-GPU: live local particle count (N is the capacity the grid was sized for)
-    int mg;                   // multi-GPU: leave the rebuild decision to the all-ranks step barrier
-    StepState* st; cudaGraphConditionalHandle handle; int use_cond;
-    };
-
-constexpr int MD_BLOCK = 256;
 
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE>
 __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
@@ -148,74 +121,15 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
     const unsigned int i = blockIdx.x * PPB + threadIdx.x;
     if (threadIdx.x < PPB && i < N)
         {
-        const float4 F = s_force[threadIdx.x];
-        const float4 pi4 = a.pos_in[i];
-        float4 v = a.vel[i];
-        if (store_force)
+        float vir[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+        if (VIRIAL)
             {
-            a.net_force[i] = F;
-            if (VIRIAL)
-                {
 #pragma unroll
-                for (int c = 0; c < 6; c++) a.virial[c * a.virial_pitch + i] = s_virial[c * PPB + threadIdx.x];
-                }
+            for (int c = 0; c < 6; c++) vir[c] = s_virial[c * PPB + threadIdx.x];
             }
-        const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
-        const bool nve = a.method == 1;
-        float3s acc;
-        // ---- integrateStepTwo(ts) ----
-        if (nve)
-            nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
-        else
-            langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0,
-                                   3u);
-        a.accel[i] = acc;
-        if (!last)
-            {
-            // ---- integrateStepOne(ts+1): Langevin step one == NVE step one without limit (TwoStepLangevin.cc:86-125) ----
-            float4 p = pi4;
-            int3 img = a.image[i];
-            const float4 lp = a.last_pos[i];
-            nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
-            a.pos_out[i] = p;
-            a.image[i] = img;
-            // ---- NeighborList::distanceCheck, fixed box (hoomd/md/NeighborList.cc:992-1016) ----
-            const float maxsq = a.maxsq[type_i];
-            float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
-                                    __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
-            dx = min_image_exact_sel(dx, a.box, a.box.periodic.x, a.box.periodic.y, a.box.periodic.z);
-            moved = dot_exact(dx) >= maxsq;
-            }
-        else if (a.copy_pos_on_last)
-            a.pos_out[i] = pi4;
-        a.vel[i] = v;
+        moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force);
         }
-    // ---- last CTA to finish takes the rebuild decision for the next launch ----
-    const int any_moved = __syncthreads_or(moved ? 1 : 0);
-    if (threadIdx.x == 0)
-        {
-        // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
-        const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
-        const unsigned long long old = atomicAdd(&st->ticket, inc);
-        if ((unsigned int)old == gridDim.x - 1)
-            {
-            if ((old + inc) >> 32) st->moved = 1u;
-            st->ticket = 0ull;
-            st->steps_left = steps_left - 1u;
-            if (a.mg)
-                ; // the vote needs every rank: k_mg_step_barrier decides
-            else if (!last)
-                decide_body(st);
-            else
-                {
-                st->need_rebuild = 0u;
-                st->moved = 0u;
-                }
-#if (CUDART_VERSION >= 12040)
-            if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
-#endif
-            }
-        }
+    md_step_finish(a, st, moved, steps_left, last);
     }
 
 __global__ void __launch_bounds__(256) k_compute_accel(float3s* __restrict__ accel,
@@ -318,19 +232,7 @@ cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, c
     if (fa.N == 0) return cudaSuccess;
     if (!box_is_orthorhombic(pa.box)) return cudaErrorNotSupported;
     MdStepArgs<EvaluatorPairLJ> a;
-    a.pos_in = pos_in; a.pos_out = pos_out; a.vel = fa.vel; a.accel = (float3s*)fa.accel; a.image = (int3*)fa.image;
-    a.net_force = (float4*)pa.d_force; a.virial = pa.d_virial; a.virial_pitch = pa.virial_pitch;
-    a.last_pos = fa.last_pos; a.tag = fa.tag;
-    a.n_neigh = pa.d_n_neigh; a.nlist = pa.d_nlist; a.head_list = pa.d_head_list;
-    a.params = (const float2*)d_params; a.rcutsq = pa.d_rcutsq; a.ronsq = pa.d_ronsq; a.ntypes = pa.ntypes;
-    a.maxsq = fa.maxsq; a.gamma = fa.gamma;
-    a.N = fa.N; a.box = make_box(fa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
-    a.wrap_skip_margin = pa.wrap_skip_margin;
-    a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
-    a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
-    a.copy_pos_on_last = copy_pos_on_last;
-    a.d_N = fa.d_N; a.mg = fa.mg;
-    a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
+    fill_md_step_args(a, pa, d_params, fa, pos_in, pos_out, copy_pos_on_last, st, cond_handle, use_cond);
     const bool v = pa.compute_virial != 0;
     const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);
     switch (tpp)

@@ -104,6 +104,18 @@ class System:
     def set_tuning(self, pair_tpp=0, use_graph=2):
         self._check(_lib.lib().b200_sys_set_tuning(self.h, int(pair_tpp), int(use_graph)))
 
+    def set_pair_mode(self, mode=-1, tile=(0, 0, 0), tpp=0):
+        """Pair-force path of the step loop: 0 = walk the reference-layout neighbor list, 1 = shared-memory cell tiles
+        (particles kept in cell order), -1 = tiles when supported.  tile = cells per CTA, tpp = lanes per particle."""
+        self._check(_lib.lib().b200_sys_set_pair_mode(self.h, int(mode), int(tile[0]), int(tile[1]), int(tile[2]),
+                                                      int(tpp)))
+
+    def pair_mode(self):
+        out = (C.c_uint * 8)()
+        _lib.lib().b200_sys_get_pair_mode(self.h, out)
+        return dict(tile=bool(out[0]), cells_per_tile=(int(out[1]), int(out[2]), int(out[3])), cap=int(out[4]),
+                    tpp=int(out[5]), row_capacity=int(out[6]), tiles=int(out[7]))
+
     def set_timestep(self, ts):
         _lib.lib().b200_sys_set_timestep(self.h, int(ts))
 

@@ -319,6 +319,17 @@ B200_API void b200_sys_set_timestep(b200_system* s, unsigned int ts);
 B200_API unsigned int b200_sys_get_timestep(b200_system* s);
 /* Launch tuning: threads per particle of the pair kernel (0 = auto), fused device-driven stepping on/off */
 B200_API int b200_sys_set_tuning(b200_system* s, unsigned int pair_tpp, int use_graph);
+/* Pair-force path of the step loop.  mode 0: walk the reference-layout neighbor list (head list + global indices,
+ * hoomd/md/PotentialPairGPU.cuh:100-330).  mode 1: cell tiles -- the particles are kept in CellList order (re-ordered at
+ * every list rebuild), each CTA stages its cells + one halo layer in shared memory and the list stores 16-bit tile slots
+ * (DESIGN.md section 4b); needs one GPU, a periodic orthorhombic box and >= 3 cells per axis, else an error.  mode -1
+ * (default): the engine's choice -- currently always mode 0 (the tile step kernel wins at >= 1M particles, its list build
+ * does not yet).  bx,by,bz = cells per tile (0 = auto), tpp = lanes per particle (0 = auto, 1, 2, 4).
+ * Same pairs, same rebuild decisions; forces differ by FP32 summation order only. */
+B200_API int b200_sys_set_pair_mode(b200_system* s, int mode, unsigned int bx, unsigned int by, unsigned int bz,
+                                    unsigned int tpp);
+/* out8 = {tile path active, bx, by, bz, staged positions per CTA, tpp, row capacity, number of tiles} */
+B200_API int b200_sys_get_pair_mode(b200_system* s, unsigned int* out8);
 
 /* NeighborList::compute(ts) / ForceCompute::compute(ts) in isolation (kernel-level parity) */
 B200_API int b200_sys_compute_nlist(b200_system* s, unsigned int ts);

@@ -1,4 +1,3 @@
-CMD="python bench.py --steps 1 --warmup 1 --md-steps 60 --equil-steps 300 --no-cpu-baseline --no-scale-ref"
-HOOMD_B200_USE_GRAPH=0 $CMD > gpurun_out/plain.log 2>&1 && \
-HOOMD_B200_USE_GRAPH=0 ncu --set full --clock-control none --import-source on -k regex:k_nlist_tiled -s 20 -c 1 -o gpurun_out/prof_nlist_r1g $CMD > gpurun_out/ncu2.log 2>&1
+CMD="python scratch/prof_tile.py ${WL:-lj64k}"
+HOOMD_B200_PAIR_MODE=1 HOOMD_B200_TILE=4,2,2,2 ncu --set full --clock-control none --import-source on -k regex:"k_tile_build" -s 1 -c 1 -o gpurun_out/prof_tilebuild_${WL:-lj64k} $CMD > gpurun_out/ncu2.log 2>&1
 tail -2 gpurun_out/ncu2.log

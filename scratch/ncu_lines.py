@@ -12,7 +12,8 @@ for r in rows:
     if r[0] == "Line No": hdr = r; continue
     if hdr and r[0].isdigit():
         d = dict(zip(hdr[4:], r[4:]))
-        rec.append((fname, int(r[0]), int(d.get("Instructions Executed", 0) or 0), int(d.get("# Samples", 0) or 0), r[1].strip()[:100]))
+        I = lambda v: int(v) if str(v).lstrip("-").isdigit() else 0
+        rec.append((fname, int(r[0]), I(d.get("Instructions Executed", 0)), I(d.get("# Samples", 0)), r[1].strip()[:100]))
 ti = sum(x[2] for x in rec); ts = sum(x[3] for x in rec)
 print("total warp-instructions %d, samples %d" % (ti, ts))
 for x in sorted(rec, key=lambda x: -x[2])[:top]:

@@ -60,6 +60,7 @@ def main():
 
     # ---- single-GPU reference on every rank's own GPU (cheap at this size) ----
     ref = hoomd_b200.System(pos, box, vel4=vel, device=local_rank)
+    ref.set_pair_mode(0)
     ref.setup_lj(r_cut=r_cut, r_buff=r_buff)
     ref.compute_forces(0)
     f_ref = ref.forces(False)[0]

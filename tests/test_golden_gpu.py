@@ -20,6 +20,7 @@ def hb():
 def _make(hb, use_graph=2, tpp=0):
     def make(pos, box, ntypes, vel=None, image=None):
         s = hb.System(pos, box, ntypes=ntypes, vel4=vel, image=image)
+        s.set_pair_mode(0)  # golden vectors are index by index in the reference's particle order
         s.set_tuning(pair_tpp=tpp, use_graph=use_graph)
         return s
     return make

@@ -36,10 +36,13 @@ def hb():
     return hoomd_b200
 
 
-def _pair(ref, hb, pos, L, ntypes=1, vel=None, **lj):
+def _pair(ref, hb, pos, L, ntypes=1, vel=None, pair_mode=0, **lj):
+    """pair_mode 0 = the reference-layout path (same particle order, head list and neighbor order as the reference, so
+    the comparisons below are index by index); the cell-tile path is compared by tag in test_tile_gpu.py"""
     box = (L, L, L) if np.isscalar(L) else L
     r = ref.RefSystem(pos, box, ntypes=ntypes, vel4=vel)
     g = hb.System(pos, box, ntypes=ntypes, vel4=vel)
+    g.set_pair_mode(pair_mode)
     r.setup_lj(full=True, **lj)
     g.setup_lj(**lj)
     return r, g
@@ -285,15 +288,18 @@ def test_short_trajectory_vs_reference(ref, hb, method, use_graph):
     assert r.nlist_stats()["updates"] == g.stats()["updates"]
 
 
+@pytest.mark.parametrize("pair_mode", [0, 1])
 @pytest.mark.parametrize("method", ["nve", "langevin"])
-def test_graph_modes_bit_identical_to_host_driven(ref, hb, method):
+def test_graph_modes_bit_identical_to_host_driven(ref, hb, method, pair_mode):
     """device-driven (plain graph, conditional graph) == host-driven control flow, bit for bit, over rebuilds,
     Nmax overflows (the lattice start overflows Nmax=8 at once) and sorter events."""
     outs = []
     for ug in (0, 1, 2):
         pos, vel, L = _liquid(hb, n_side=12)
         g = hb.System(pos, (L, L, L), vel4=vel)
+        g.set_pair_mode(pair_mode)
         g.setup_lj(r_cut=3.0, r_buff=0.4)
+        assert g.pair_mode()["tile"] == bool(pair_mode)
         g.setup_integrator(0.005)
         g.add_nve() if method == "nve" else g.add_langevin(1.2, 7)
         g.set_sorter(100)
