@@ -40,7 +40,7 @@ class NlistArgs(C.Structure):
     _fields_ = [("d_nlist", vp), ("d_n_neigh", vp), ("d_last_pos", vp), ("d_conditions", vp), ("d_Nmax", vp),
                 ("d_head_list", vp), ("d_pos", vp), ("N", C.c_uint), ("d_cell_start", vp), ("d_cell_xyzf", vp),
                 ("d_cell_type", vp), ("dim", Dim3), ("box", Box), ("ghost_width", C.c_float * 3), ("d_r_cut", vp),
-                ("d_r_listsq", vp), ("ntypes", C.c_uint), ("half_storage", C.c_int)]
+                ("d_r_listsq", vp), ("ntypes", C.c_uint), ("half_storage", C.c_int), ("cand_hint", C.c_uint)]
 
 
 class PairArgs(C.Structure):

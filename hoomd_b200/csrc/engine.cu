@@ -253,6 +253,9 @@ static void nlist_args(b200_system* s, b200_nlist_args& a)
     a.d_r_listsq = s->d_r_listsq.p;
     a.ntypes = s->ntypes;
     a.half_storage = 0;
+    // staging capacity of a build pass: the mean 27-cell population with head room for density fluctuations
+    const double per_cell = (double)(s->N + (s->mg ? s->Gcap / 2 : 0)) / ((double)s->dim.x * s->dim.y * s->dim.z);
+    a.cand_hint = (unsigned int)std::min(1024.0, 27.0 * per_cell * 1.5 + 48.0);
     }
 
 static void pair_args(b200_system* s, b200_pair_args& a)

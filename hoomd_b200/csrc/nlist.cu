@@ -3,6 +3,7 @@
 // compaction into the CSR list.  Membership arithmetic and entry order are those of the CPU oracle
 // hoomd/md/NeighborListBinned.cc:144-236 (see include/hoomd_b200.h).
 #include "common.cuh"
+#include "bulk_copy.cuh"
 #include <cstdlib>
 
 namespace b200
@@ -326,6 +327,270 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
         }
     }
 
+// ---- cell-scan build: one CTA per cell, EIGHT lanes per particle, each scanning a contiguous eighth of the staged
+// candidates -------------------------------------------------------------------------------------------------------------
+// The tiled kernel above spends one warp per particle with lanes = candidates: every 32 tests cost a ballot, two popc and
+// a scattered store decision, ~1.9 warp-instructions per test, and the build is issue-bound (~100 % issue utilisation at
+// 1M particles).  Here a warp holds 4 particles x 8 lanes; the candidate list is the same for every particle of the cell,
+// so the scan loop is warp-uniform (no divergence, 8 distinct shared-memory addresses per load, the rest broadcast) and a
+// test costs its arithmetic plus one bit of a register mask.  Lane q of a particle scans candidates [q*Q, (q+1)*Q); the
+// eight sub-lists are concatenated (a width-8 prefix of the popcounts) into the row, which keeps the oracle's order
+// (ascending staged index = neighbor cells by id, occupants by index).  The candidates are staged with one bulk copy
+// (cp.async.bulk) per adjacent cell.  Membership arithmetic as above (bit-exact vs the oracle).
+constexpr int NC_BLOCK = 128; // 4 warps = 16 particles per round
+constexpr int NC_G = 8;       // lanes per particle
+constexpr int NC_WORDS = 4;   // 32-candidate mask words per lane: Q <= 128, i.e. <= 1024 candidates per pass
+
+template<bool MULTI_TYPE, bool WRAP, bool HALF>
+__device__ __forceinline__ unsigned int nlist_scan_word(const float4 pi4, unsigned int i, unsigned int type_i,
+                                                        const float4* s_cand, const unsigned int* s_type,
+                                                        unsigned int t0, unsigned int nq, const Box& box, bool wx, bool wy,
+                                                        bool wz, float rcut_00, float rlsq_00,
+                                                        const float* __restrict__ r_cut,
+                                                        const float* __restrict__ r_listsq, unsigned int ntypes)
+    {
+    unsigned int mask = 0, bit = 1;
+#pragma unroll 2
+    for (unsigned int q = 0; q < nq; q++)
+        {
+        const float4 cj = s_cand[t0 + q];
+        const unsigned int j = (unsigned int)__float_as_int(cj.w);
+        float rlsq = rlsq_00;
+        bool excluded = (j == i);
+        if (MULTI_TYPE)
+            {
+            const unsigned int tj = s_type[t0 + q];
+            excluded |= __ldg(&r_cut[type_i * ntypes + tj]) <= 0.0f;
+            rlsq = __ldg(&r_listsq[type_i * ntypes + tj]);
+            }
+        else
+            excluded |= rcut_00 <= 0.0f;
+        float3 dx = make_float3(__fsub_rn(pi4.x, cj.x), __fsub_rn(pi4.y, cj.y), __fsub_rn(pi4.z, cj.z));
+        if (WRAP) dx = min_image_exact_sel(dx, box, wx, wy, wz);
+        const bool hit = !excluded && (dot_exact(dx) <= rlsq) && (!HALF || i < j);
+        if (hit) mask |= bit;
+        bit += bit;
+        }
+    return mask;
+    }
+
+template<bool MULTI_TYPE, bool HALF, bool BULK>
+__global__ void __launch_bounds__(NC_BLOCK) k_nlist_cellscan(unsigned int* __restrict__ nlist,
+                                                             unsigned int* __restrict__ n_neigh,
+                                                             float4* __restrict__ last_pos,
+                                                             unsigned int* __restrict__ conditions,
+                                                             const unsigned int* __restrict__ Nmax,
+                                                             const unsigned int* __restrict__ head_list, unsigned int N,
+                                                             const unsigned int* __restrict__ cell_start,
+                                                             const float4* __restrict__ cell_xyzf,
+                                                             const unsigned int* __restrict__ cell_type, uint3 dim,
+                                                             Box box, const float* __restrict__ r_cut,
+                                                             const float* __restrict__ r_listsq, unsigned int ntypes,
+                                                             unsigned int cap, const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    // dynamic shared memory: [cap + 16] candidates, then [cap + 16] types
+    extern __shared__ float4 s_cand[];
+    unsigned int* s_type = reinterpret_cast<unsigned int*>(s_cand + cap + 16);
+    __shared__ unsigned int s_beg[28], s_off[28];
+    __shared__ unsigned int s_nr, s_heads;
+    __shared__ __align__(8) unsigned long long s_bar;
+
+    const unsigned int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z;
+    const unsigned int cell = (bz * dim.y + by) * dim.x + bx;
+    const unsigned int own_beg = cell_start[cell], own_end = cell_start[cell + 1];
+    if (own_beg == own_end) return; // uniform per CTA
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (warp == 0)
+        {
+        if (lane == 0 && BULK) mbar_init(&s_bar, 1);
+        int xs[3], ys[3], zs[3];
+        const int nx = axis_set(bx, dim.x, box.periodic.x, xs);
+        const int ny = axis_set(by, dim.y, box.periodic.y, ys);
+        const int nz = axis_set(bz, dim.z, box.periodic.z, zs);
+        const int nr = nx * ny * nz;
+        unsigned int beg = 0, len = 0, nc = 0xffffffffu;
+        if ((int)lane < nr)
+            {
+            const int r = lane % nx, q = (lane / nx) % ny, c = lane / (nx * ny);
+            const int x = (r == 0) ? xs[0] : (r == 1) ? xs[1] : xs[2];
+            const int y = (q == 0) ? ys[0] : (q == 1) ? ys[1] : ys[2];
+            const int z = (c == 0) ? zs[0] : (c == 1) ? zs[1] : zs[2];
+            nc = ((unsigned int)z * dim.y + (unsigned int)y) * dim.x + (unsigned int)x;
+            beg = cell_start[nc];
+            len = cell_start[nc + 1] - beg;
+            }
+        unsigned int incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int)lane >= o) incl += t;
+            }
+        // cells with consecutive ids are consecutive in memory AND in the staged order: one bulk copy per run
+        const unsigned int prev_nc = __shfl_up_sync(0xffffffffu, nc, 1);
+        const bool head = (int)lane < nr && (lane == 0 || nc != prev_nc + 1u);
+        const unsigned int heads = __ballot_sync(0xffffffffu, head);
+        if (lane < 28)
+            {
+            s_beg[lane] = beg;
+            s_off[lane] = incl - len;
+            }
+        if ((int)lane == nr - 1)
+            {
+            s_off[nr] = incl;
+            s_nr = nr;
+            s_heads = heads;
+            }
+        }
+    __syncthreads();
+    const unsigned int nr = s_nr;
+    const unsigned int total = s_off[nr];
+    const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
+    const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
+    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
+    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
+    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+    const bool wrap_any = wx || wy || wz;
+    const unsigned int slot = threadIdx.x / NC_G, sub = threadIdx.x % NC_G;
+    unsigned int parity = 0;
+
+    for (unsigned int pass = 0; pass < total; pass += cap)
+        {
+        const unsigned int cnt = min(cap, total - pass);
+        const unsigned int Q = (((cnt + NC_G - 1) / NC_G) + 1u) & ~1u; // per-lane share, even (the scan is unrolled by 2)
+        const unsigned int cnt_padded = Q * NC_G;                      // <= cap + 15
+        if (pass) __syncthreads(); // everyone is done with the previous window
+        if (BULK)
+            {
+            // one bulk copy per run of adjacent cells (clipped to this pass's window), issued by the lanes of warp 0
+            if (warp == 0)
+                {
+                if (pass) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                if (lane == 0) mbar_arrive_expect_tx(&s_bar, cnt * (unsigned int)sizeof(float4));
+                __syncwarp();
+                const unsigned int heads = s_heads;
+                if ((heads >> lane) & 1u)
+                    {
+                    const unsigned int later = (lane < 31) ? (heads >> (lane + 1)) : 0u;
+                    const unsigned int next = later ? lane + (unsigned int)__ffs(later) : nr; // next run's first cell
+                    const unsigned int lo = max(s_off[lane], pass), hi = min(s_off[next], pass + cnt);
+                    if (hi > lo)
+                        bulk_g2s(s_cand + (lo - pass), cell_xyzf + s_beg[lane] + (lo - s_off[lane]),
+                                 (hi - lo) * (unsigned int)sizeof(float4), &s_bar);
+                    }
+                }
+            // sentinels: dr^2 overflows to +inf, never <= r_list^2; index 0xffffffff is nobody
+            for (unsigned int t = cnt + threadIdx.x; t < cnt_padded; t += NC_BLOCK)
+                s_cand[t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
+            __syncthreads();
+            mbar_wait(&s_bar, parity);
+            parity ^= 1u;
+            }
+        else
+            {
+            for (unsigned int t = threadIdx.x; t < cnt_padded; t += NC_BLOCK)
+                {
+                if (t < cnt)
+                    {
+                    const unsigned int g = pass + t;
+                    unsigned int lo = 0, hi = nr; // adjacent cell holding staged entry g: last r with s_off[r] <= g
+                    while (hi - lo > 1)
+                        {
+                        const unsigned int mid = (lo + hi) >> 1;
+                        if (s_off[mid] <= g) lo = mid; else hi = mid;
+                        }
+                    const unsigned int e = s_beg[lo] + (g - s_off[lo]);
+                    s_cand[t] = cell_xyzf[e];
+                    if (MULTI_TYPE) s_type[t] = cell_type[e];
+                    }
+                else
+                    {
+                    s_cand[t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
+                    if (MULTI_TYPE) s_type[t] = 0u;
+                    }
+                }
+            __syncthreads();
+            }
+
+        for (unsigned int p0 = own_beg; p0 < own_end; p0 += NC_BLOCK / NC_G)
+            {
+            // a warp whose 4 particle slots are all past the end has nothing to do (warp-uniform)
+            if (p0 + warp * (32 / NC_G) >= own_end) continue;
+            const unsigned int p = p0 + slot;
+            const bool in_cell = p < own_end;
+            const float4 pi4 = in_cell ? cell_xyzf[p] : make_float4(0.0f, 0.0f, 0.0f, __int_as_float(-2));
+            const unsigned int i = (unsigned int)__float_as_int(pi4.w);
+            const bool active = in_cell && i < N; // ghosts are candidates only
+            const unsigned int type_i = (MULTI_TYPE && active) ? cell_type[p] : 0u;
+            const unsigned int t0 = sub * Q;
+            unsigned int masks[NC_WORDS];
+            unsigned int c = 0;
+#pragma unroll
+            for (int w = 0; w < NC_WORDS; w++)
+                {
+                masks[w] = 0u;
+                if (w * 32u < Q)
+                    {
+                    const unsigned int nq = min(32u, Q - w * 32u);
+                    if (wrap_any)
+                        masks[w] = nlist_scan_word<MULTI_TYPE, true, HALF>(pi4, i, type_i, s_cand, s_type, t0 + w * 32u, nq,
+                                                                           box, wx, wy, wz, rcut_00, rlsq_00, r_cut,
+                                                                           r_listsq, ntypes);
+                    else
+                        masks[w] = nlist_scan_word<MULTI_TYPE, false, HALF>(pi4, i, type_i, s_cand, s_type, t0 + w * 32u, nq,
+                                                                            box, wx, wy, wz, rcut_00, rlsq_00, r_cut,
+                                                                            r_listsq, ntypes);
+                    if (!active) masks[w] = 0u;
+                    c += __popc(masks[w]);
+                    }
+                }
+            // concatenate the eight sub-lists of a particle: exclusive prefix over its lanes
+            unsigned int incl = c;
+#pragma unroll
+            for (int o = 1; o < NC_G; o <<= 1)
+                {
+                const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o, NC_G);
+                if (sub >= (unsigned int)o) incl += v;
+                }
+            const unsigned int found = __shfl_sync(0xffffffffu, incl, NC_G - 1, NC_G);
+            const unsigned int Nmax_i = active ? Nmax[type_i] : 0u;
+            const unsigned int n0 = (pass && active) ? n_neigh[i] : 0u; // running (unclamped) count of earlier passes
+            if (active)
+                {
+                unsigned int* row = nlist + head_list[i];
+                unsigned int k = n0 + incl - c;
+#pragma unroll
+                for (int w = 0; w < NC_WORDS; w++)
+                    {
+                    unsigned int m = masks[w];
+                    while (m)
+                        {
+                        const unsigned int q = __ffs(m) - 1u;
+                        m &= m - 1u;
+                        if (k < Nmax_i) row[k] = (unsigned int)__float_as_int(s_cand[t0 + w * 32u + q].w);
+                        k++;
+                        }
+                    }
+                }
+            __syncwarp();
+            if (active && sub == 0)
+                {
+                const unsigned int n = n0 + found;
+                if (pass + cap < total)
+                    n_neigh[i] = n;
+                else
+                    {
+                    n_neigh[i] = min(n, Nmax_i);
+                    if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+                    if (last_pos) last_pos[i] = make_float4(pi4.x, pi4.y, pi4.z, 0.0f);
+                    }
+                }
+            }
+        }
+    }
+
 // ---- distance check (NeighborList::distanceCheck) -----------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_nlist_dist_check(unsigned int* __restrict__ result,
                                                           const float4* __restrict__ last_pos,
@@ -491,7 +756,41 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
     Box box = make_box(a->box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
-    static const bool use_warp_kernel = getenv("HOOMD_B200_NLIST_WARP") != nullptr; // A/B switch for profiling
+    static const bool use_warp_kernel = getenv("HOOMD_B200_NLIST_WARP") != nullptr; // A/B switches for profiling
+    // the cell-scan kernel executes ~2.5x fewer instructions than the tiled one but is latency-bound per CTA and measured
+    // slower on B200 (rebuild 85 vs 71 us at 64k particles, 782 vs 637 us at 1M): opt-in until that is fixed
+    static const bool use_cellscan_kernel = getenv("HOOMD_B200_NLIST_CELLSCAN") != nullptr;
+    if (!use_warp_kernel && use_cellscan_kernel)
+        {
+        if (a->dim.y > 65535u || a->dim.z > 65535u) return cudaErrorInvalidValue;
+        const dim3 grid(a->dim.x, a->dim.y, a->dim.z);
+        // candidates staged per pass: the caller's estimate of a cell neighborhood's population (cand_hint), else 512
+        unsigned int cap = a->cand_hint ? a->cand_hint : 512u;
+        cap = ((cap < 64u ? 64u : cap > 1024u ? 1024u : cap) + 7u) & ~7u;
+        size_t smem = (cap + 16) * sizeof(float4);
+        if (a->ntypes > 1) smem += (cap + 16) * sizeof(unsigned int);
+        static const bool manual_staging = getenv("HOOMD_B200_NC_MANUAL") != nullptr;
+#define B200_NC_LAUNCH(MT, HALF) do { if (!MT && !manual_staging) B200_NC_LAUNCH2(MT, HALF, !MT); else B200_NC_LAUNCH2(MT, HALF, false); } while (0)
+#define B200_NC_LAUNCH2(MT, HALF, BULK)                                                                              \
+    do {                                                                                                             \
+        cudaFuncSetAttribute(k_nlist_cellscan<MT, HALF, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_nlist_cellscan<MT, HALF, BULK><<<grid, NC_BLOCK, smem, stream>>>(                                          \
+            a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,      \
+            a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,     \
+            a->ntypes, cap, enable);                                                                                 \
+    } while (0)
+        if (a->ntypes > 1)
+            {
+            if (a->half_storage) B200_NC_LAUNCH(true, true); else B200_NC_LAUNCH(true, false);
+            }
+        else
+            {
+            if (a->half_storage) B200_NC_LAUNCH(false, true); else B200_NC_LAUNCH(false, false);
+            }
+#undef B200_NC_LAUNCH
+#undef B200_NC_LAUNCH2
+        return cudaGetLastError();
+        }
     if (!use_warp_kernel)
         {
         if (a->dim.y > 65535u || a->dim.z > 65535u) return cudaErrorInvalidValue;

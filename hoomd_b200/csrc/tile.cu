@@ -19,6 +19,7 @@
 // on the same distance-check decisions, so forces differ from the CSR path only by the order of the FP32 sum.
 #include "md_step_body.cuh"
 #include "tile.h"
+#include "bulk_copy.cuh"
 
 namespace b200
 {
@@ -34,42 +35,6 @@ struct TileCtx
     unsigned int own_off[TILE_MAX_RUNS + 1]; //           exclusive prefix of the owned counts
     unsigned int hxn, hyn, hzn, ownx, owny, ownz, n_own, total, wrap;
     };
-
-// ---- bulk-copy (TMA) staging helpers: cp.async.bulk global -> shared, completion on an mbarrier -----------------------------
-__device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned int count)
-    {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-
-__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned int bytes)
-    {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-    }
-
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned int bytes, unsigned long long* bar)
-    {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-    }
-
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned int parity)
-    {
-    asm volatile("{\n"
-                 ".reg .pred P1;\n"
-                 "WAIT_LOOP:\n"
-                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-                 "@P1 bra WAIT_DONE;\n"
-                 "bra WAIT_LOOP;\n"
-                 "WAIT_DONE:\n"
-                 "}" ::"r"(smem_u32(bar)),
-                 "r"(parity)
-                 : "memory");
-    }
 
 // Tile coordinates = blockIdx (3-D grid).  Halo cell h = (hz*hyn + hy)*hxn + hx covers cell (x0-1+hx, y0-1+hy, z0-1+hz),
 // wrapped on periodic axes, empty outside the grid otherwise.  Computed by warp 0; ends with a CTA barrier.

@@ -155,6 +155,8 @@ typedef struct b200_nlist_args
     const float*  d_r_listsq;        /* [ntypes*ntypes] (r_cut+r_buff)^2 computed like NeighborList::updateRList (NeighborList.cc:354-400) */
     unsigned int  ntypes;
     int           half_storage;      /* 1: keep only i<j (NeighborList::half); GPU classes always use 0 */
+    unsigned int  cand_hint;         /* tuning only: expected particles in a cell's <=27-cell neighborhood (sizes the
+                                        shared-memory staging of a pass; 0 = 512).  Larger neighborhoods take more passes. */
     } b200_nlist_args;
 
 B200_API int b200_compute_nlist_binned(const b200_nlist_args* args, b200_stream_t stream);
