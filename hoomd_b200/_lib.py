@@ -65,6 +65,13 @@ class PDataArrays(C.Structure):
                 ("charge", vp), ("diameter", vp), ("body", vp)]
 
 
+class BondArgs(C.Structure):
+    """b200_bond_args (bond_args_t, hoomd/md/PotentialBondGPU.cuh:26-98)"""
+    _fields_ = [("d_force", vp), ("d_virial", vp), ("virial_pitch", C.c_uint), ("N", C.c_uint), ("d_pos", vp),
+                ("d_diameter", vp), ("box", Box), ("d_bond_list", vp), ("pitch", C.c_uint), ("d_n_bonds", vp),
+                ("n_bond_types", C.c_uint), ("compute_virial", C.c_uint), ("d_tag", vp), ("d_rtag", vp)]
+
+
 class MgParams(C.Structure):
     """b200_mg_params"""
     _fields_ = [("world", C.c_uint), ("rank", C.c_uint), ("grid", C.c_uint * 3), ("global_box", Box),
@@ -77,6 +84,9 @@ SYMBOLS = [
     "b200_box_init", "b200_box_init_lohi", "b200_compute_cell_list", "b200_cell_list_dimensions",
     "b200_cell_list_export_padded", "b200_cell_list_build_adjacency", "b200_nlist_build_head_list",
     "b200_compute_nlist_binned", "b200_nlist_needs_update_check", "b200_compute_lj_forces",
+    "b200_nlist_filter", "b200_compute_fene_bond_forces", "b200_compute_harmonic_bond_forces",
+    "b200_sys_set_bonds", "b200_sys_setup_bond_force", "b200_sys_nlist_exclusions_from_bonds",
+    "b200_sys_get_force_component",
     "b200_integrator_sum_net_force", "b200_nve_step_one", "b200_nve_step_two", "b200_langevin_hash_seed",
     "b200_langevin_step_two", "b200_saru_draw", "b200_sfc_generate_sorted_order", "b200_sfc_apply_sorted_order",
     "b200_compute_thermo", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
@@ -118,6 +128,13 @@ def lib():
     L.b200_nlist_needs_update_check.argtypes = [vp, vp, vp, C.c_uint, C.POINTER(Box), vp, C.c_float, C.c_uint,
                                                 C.c_float, C.c_float * 3, C.c_uint, vp]
     L.b200_compute_lj_forces.argtypes = [C.POINTER(PairArgs), vp, vp]
+    L.b200_nlist_filter.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.c_uint, vp, vp, C.c_uint, vp]
+    L.b200_compute_fene_bond_forces.argtypes = [C.POINTER(BondArgs), vp, vp, vp]
+    L.b200_compute_harmonic_bond_forces.argtypes = [C.POINTER(BondArgs), vp, vp, vp]
+    L.b200_sys_set_bonds.argtypes = [vp, C.c_uint, vp, vp, C.c_uint]
+    L.b200_sys_setup_bond_force.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    L.b200_sys_nlist_exclusions_from_bonds.argtypes = [vp, C.c_int]
+    L.b200_sys_get_force_component.argtypes = [vp, C.c_int, vp, vp]
     L.b200_integrator_sum_net_force.argtypes = [vp, vp, C.c_uint, C.POINTER(ForceList), C.c_uint, C.c_int, C.c_int,
                                                 vp]
     L.b200_nve_step_one.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.POINTER(Box), C.c_float, C.c_int, C.c_float,

@@ -138,6 +138,22 @@ struct b200_system
     int shift_mode = 0;
     unsigned int pair_tpp = 0;
 
+    // ---- BondData + PotentialBond + nlist exclusions (row f1) --------------------------------------------------
+    // per-particle tables keyed by TAG with partner TAGS (resolved through rtag): never rebuilt on a particle sort
+    unsigned int n_bond_types = 0, bond_pitch = 0, bond_max = 0;
+    std::vector<unsigned int> h_bond_tags, h_bond_types; // the bond set as given (2 tags per bond)
+    DevBuf<unsigned int> bond_n;          // [N] bonds per tag
+    DevBuf<uint2> bond_list;              // [bond_max * pitch] (partner tag, bond type) at [k*pitch + tag]
+    int bond_kind = -1;                   // -1 none, 0 FENE, 1 harmonic
+    DevBuf<float4> bond_params4;
+    DevBuf<float2> bond_params2;
+    DevBuf<float4> bond_force, pair_force_copy;
+    DevBuf<float> bond_virial, pair_virial_copy;
+    DevBuf<unsigned int> bond_flags;
+    bool exclusions_set = false;
+    unsigned int ex_max = 0, ex_pitch = 0;
+    DevBuf<unsigned int> ex_n, ex_list;   // [N], [ex_max * pitch]: partner tag at [k*pitch + tag]
+
     // ---- IntegratorTwoStep + method ---------------------------------------------------------------------------
     bool have_integrator = false;
     float dt = 0.005f;
@@ -292,6 +308,49 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.d_N = s->mg ? &s->d_state.p->N : nullptr; a.mg = s->mg ? 1 : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
+    if (s->bond_kind >= 0)
+        {
+        a.extra_force = s->bond_force.p; a.extra_virial = s->bond_virial.p; a.extra_virial_pitch = s->virial_pitch;
+        }
+    }
+
+// PotentialBond<evaluator>::computeForces at `pos` into bond_force / bond_virial (hoomd/md/PotentialBond.h:155-300)
+static void enqueue_bond_forces(b200_system* s, const float4* pos)
+    {
+    if (s->bond_kind < 0) return;
+    b200_bond_args a;
+    memset(&a, 0, sizeof(a));
+    a.d_force = (float*)s->bond_force.p; a.d_virial = s->bond_virial.p; a.virial_pitch = s->virial_pitch;
+    a.N = s->N; a.d_pos = (const float*)pos; a.d_diameter = nullptr; a.box = s->box;
+    a.d_bond_list = (const unsigned int*)s->bond_list.p; a.pitch = s->bond_pitch; a.d_n_bonds = s->bond_n.p;
+    a.n_bond_types = s->n_bond_types; a.compute_virial = s->compute_virial ? 1u : 0u;
+    a.d_tag = s->tag.p; a.d_rtag = s->rtag.p;
+    if (s->bond_kind == 0)
+        CUDA_OK(b200_compute_fene_bond_forces(&a, (const float*)s->bond_params4.p, s->bond_flags.p, s->stream));
+    else
+        CUDA_OK(b200_compute_harmonic_bond_forces(&a, (const float*)s->bond_params2.p, s->bond_flags.p, s->stream));
+    }
+
+// "bond.fene: bond out of bounds" (hoomd/md/PotentialBond.h:288-292): raised at the next host synchronisation point
+static void check_bond_flags(b200_system* s)
+    {
+    if (s->bond_kind < 0) return;
+    unsigned int f = 0;
+    s->bond_flags.download(&f, 1, s->stream);
+    if (f)
+        {
+        CUDA_OK(cudaMemsetAsync(s->bond_flags.p, 0, sizeof(unsigned int), s->stream));
+        throw std::runtime_error(std::string("bond.") + (s->bond_kind == 0 ? "fene" : "harmonic")
+                                 + ": bond out of bounds. Error in bond calculation");
+        }
+    }
+
+// NeighborList::filterNlist (hoomd/md/NeighborList.cc:246-247,1275-1328)
+static void enqueue_nlist_filter(b200_system* s, const unsigned int* enable)
+    {
+    if (!s->exclusions_set || s->ex_max == 0) return;
+    CUDA_OK(launch_nlist_filter(s->n_neigh.p, s->nlist.p, s->head_list.p, s->ex_n.p, s->ex_list.p, s->ex_pitch, s->ex_max,
+                                s->tag.p, s->rtag.p, s->N, enable, s->stream));
     }
 } // namespace b200
 
@@ -507,6 +566,11 @@ static void nlist_compute(b200_system* s, unsigned int ts)
                 CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
                 }
             } while (overflowed);
+        if (s->exclusions_set)
+            {
+            enqueue_nlist_filter(s, nullptr);
+            s->kernels_last_run += 1;
+            }
         // setLastUpdatedPos: done by the build kernel (like the reference GPU path, NeighborListGPUBinned.cu:280-285)
         }
     }
@@ -529,6 +593,21 @@ static void compute_net_force(b200_system* s, unsigned int ts)
     else
         CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
     s->kernels_last_run += 1;
+    if (s->bond_kind >= 0)
+        {
+        // second ForceCompute + Integrator::computeNetForce: net = pair + bond.  The pair force alone is kept for
+        // b200_sys_get_force_component.
+        const unsigned int N = s->N;
+        CUDA_OK(cudaMemcpyAsync(s->pair_force_copy.p, s->net_force.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+        if (s->compute_virial)
+            CUDA_OK(cudaMemcpyAsync(s->pair_virial_copy.p, s->net_virial.p, sizeof(float) * 6 * (size_t)s->virial_pitch,
+                                    cudaMemcpyDeviceToDevice, s->stream));
+        enqueue_bond_forces(s, s->pos.p);
+        CUDA_OK(launch_add_force(s->net_force.p, s->net_virial.p, s->virial_pitch, s->bond_force.p, s->bond_virial.p,
+                                 s->virial_pitch, N, s->compute_virial, s->stream));
+        s->kernels_last_run += 2;
+        check_bond_flags(s);
+        }
     }
 
 static void integrate_step_one(b200_system* s, unsigned int ts)
@@ -652,6 +731,8 @@ static void enqueue_rebuild(b200_system* s, const unsigned int* enable, const fl
     na.d_pos = (const float*)pos;
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
     CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    // filterNlist runs on the complete rows; after an overflow the rows are discarded anyway (checkpoint replay)
+    enqueue_nlist_filter(s, enable);
     }
 
 static void enqueue_md_step(b200_system* s, const FusedStepArgs& fa, int phase, unsigned long long handle, int use_cond)
@@ -660,6 +741,7 @@ static void enqueue_md_step(b200_system* s, const FusedStepArgs& fa, int phase, 
     pair_args(s, pa);
     const float4* pin = phase == 0 ? s->pos.p : s->pos_alt.p;
     float4* pout = phase == 0 ? s->pos_alt.p : s->pos.p;
+    enqueue_bond_forces(s, pin); // second ForceCompute at the positions this step reads; k_md_step adds it (fa.extra_force)
     if (s->tile_on)
         {
         TileStepArgs ta;
@@ -890,14 +972,17 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
                     CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
                     }
                 } while (overflowed);
+            enqueue_nlist_filter(s, nullptr);
             }
         CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         s->cl_force = true;
         for (unsigned int k = 0; k < chunk; k++) host_step(s);
         return;
         }
+    check_bond_flags(s);
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    const unsigned long long rk = s->tile_on ? 8ull : 6ull; // kernels per rebuild
+    const unsigned long long rk = (s->tile_on ? 8ull : 6ull) + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // per rebuild
+    if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
     s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + rk * rebuilds)
                                                                              : (2ull + 2ull * rk) * nreplay);
     s->timestep = st.timestep;
@@ -1194,6 +1279,152 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     s->nl_first_compute = true;
     invalidate_graph(s);
     tile_configure(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* tags2, const unsigned int* types,
+                       unsigned int n_bond_types)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("bond: bonded forces under domain decomposition are not supported in this round");
+    const unsigned int N = s->N;
+    if (nbonds && n_bond_types == 0) throw std::runtime_error("bond: no bond types defined");
+    if (n_bond_types > 256) throw std::runtime_error("bond: more than 256 bond types");
+    std::vector<unsigned int> cnt(N, 0u);
+    for (unsigned int b = 0; b < nbonds; b++)
+        {
+        const unsigned int ta = tags2[2 * b], tb = tags2[2 * b + 1];
+        if (ta >= N || tb >= N) throw std::runtime_error("bond: particle tag out of bounds when attempting to add a bond");
+        if (ta == tb) throw std::runtime_error("bond: particle cannot be bonded to itself");
+        if (types[b] >= n_bond_types) throw std::runtime_error("bond: invalid bond type");
+        cnt[ta]++; cnt[tb]++;
+        }
+    unsigned int mx = 0;
+    for (unsigned int i = 0; i < N; i++) mx = std::max(mx, cnt[i]);
+    s->h_bond_tags.assign(tags2, tags2 + 2 * (size_t)nbonds);
+    s->h_bond_types.assign(types, types + nbonds);
+    s->n_bond_types = n_bond_types;
+    s->bond_max = mx;
+    s->bond_pitch = N;
+    // per-particle rows in bond order, like BondedGroupData::rebuildGPUTable fills its table (hoomd/BondedGroupData.cc)
+    std::vector<uint2> table((size_t)std::max(mx, 1u) * N, make_uint2(0u, 0u));
+    std::fill(cnt.begin(), cnt.end(), 0u);
+    for (unsigned int b = 0; b < nbonds; b++)
+        {
+        const unsigned int ta = tags2[2 * b], tb = tags2[2 * b + 1];
+        table[(size_t)cnt[ta]++ * N + ta] = make_uint2(tb, types[b]);
+        table[(size_t)cnt[tb]++ * N + tb] = make_uint2(ta, types[b]);
+        }
+    s->bond_n.alloc(N);
+    s->bond_list.alloc(table.size());
+    s->bond_n.upload(cnt.data(), N, s->stream);
+    s->bond_list.upload(table.data(), table.size(), s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_setup_bond_force(b200_system* s, int kind, const float* K, const float* r0, const float* lj1,
+                              const float* lj2)
+    {
+    SYS_TRY(s)
+    if (kind != 0 && kind != 1) throw std::runtime_error("bond: unknown bond potential");
+    if (s->n_bond_types == 0 || s->h_bond_types.empty()) throw std::runtime_error("bond: No bonds are defined.");
+    if (s->tile_on) throw std::runtime_error("bond: the cell-tile pair path does not carry bonded forces (use pair mode 0)");
+    const unsigned int nb = s->n_bond_types;
+    if (kind == 0)
+        {
+        std::vector<float4> p(nb);
+        for (unsigned int t = 0; t < nb; t++) p[t] = make_float4(K[t], r0[t], lj1[t], lj2[t]);
+        s->bond_params4.alloc(nb);
+        s->bond_params4.upload(p.data(), nb, s->stream);
+        }
+    else
+        {
+        std::vector<float2> p(nb);
+        for (unsigned int t = 0; t < nb; t++) p[t] = make_float2(K[t], r0[t]);
+        s->bond_params2.alloc(nb);
+        s->bond_params2.upload(p.data(), nb, s->stream);
+        }
+    s->bond_force.alloc(s->Ncap);
+    s->pair_force_copy.alloc(s->Ncap);
+    s->bond_virial.alloc(6 * (size_t)s->virial_pitch);
+    s->pair_virial_copy.alloc(6 * (size_t)s->virial_pitch);
+    s->bond_flags.alloc(1);
+    CUDA_OK(cudaMemsetAsync(s->bond_flags.p, 0, sizeof(unsigned int), s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    s->bond_kind = kind;
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_nlist_exclusions_from_bonds(b200_system* s, int on)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("nlist: exclusions under domain decomposition are not supported in this round");
+    if (s->tile_on) throw std::runtime_error("nlist: the cell-tile pair path does not filter exclusions (use pair mode 0)");
+    invalidate_graph(s);
+    s->force_update = true;
+    if (!on)
+        {
+        s->exclusions_set = false; // NeighborList::clearExclusions (hoomd/md/NeighborList.cc:505-520)
+        s->ex_max = 0;
+        }
+    else
+        {
+        const unsigned int N = s->N;
+        const size_t nbonds = s->h_bond_types.size();
+        // NeighborList::addExclusion per bond, duplicates skipped (hoomd/md/NeighborList.cc:431-470)
+        std::vector<std::vector<unsigned int>> ex(N);
+        for (size_t b = 0; b < nbonds; b++)
+            {
+            const unsigned int ta = s->h_bond_tags[2 * b], tb = s->h_bond_tags[2 * b + 1];
+            if (std::find(ex[ta].begin(), ex[ta].end(), tb) != ex[ta].end()) continue;
+            ex[ta].push_back(tb);
+            ex[tb].push_back(ta);
+            }
+        unsigned int mx = 0;
+        std::vector<unsigned int> cnt(N);
+        for (unsigned int i = 0; i < N; i++)
+            {
+            cnt[i] = (unsigned int)ex[i].size();
+            mx = std::max(mx, cnt[i]);
+            }
+        std::vector<unsigned int> table((size_t)std::max(mx, 1u) * N, 0u);
+        for (unsigned int i = 0; i < N; i++)
+            for (unsigned int k = 0; k < cnt[i]; k++) table[(size_t)k * N + i] = ex[i][k];
+        s->ex_n.alloc(N);
+        s->ex_list.alloc(table.size());
+        s->ex_n.upload(cnt.data(), N, s->stream);
+        s->ex_list.upload(table.data(), table.size(), s->stream);
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        s->ex_max = mx;
+        s->ex_pitch = N;
+        s->exclusions_set = true; // addExclusion sets it even when the bond list is empty
+        }
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_force_component(b200_system* s, int which, float* force4, float* virial6)
+    {
+    SYS_TRY(s)
+    const unsigned int N = s->N;
+    const float4* f = nullptr;
+    const float* v = nullptr;
+    if (s->bond_kind < 0)
+        {
+        if (which != 0) throw std::runtime_error("force: no bond force set up");
+        f = s->net_force.p; v = s->net_virial.p;
+        }
+    else if (which == 0) { f = s->pair_force_copy.p; v = s->pair_virial_copy.p; }
+    else if (which == 1) { f = s->bond_force.p; v = s->bond_virial.p; }
+    else throw std::runtime_error("force: unknown component");
+    if (force4) CUDA_OK(cudaMemcpyAsync(force4, f, sizeof(float4) * N, cudaMemcpyDeviceToHost, s->stream));
+    if (virial6)
+        for (int c = 0; c < 6; c++)
+            CUDA_OK(cudaMemcpyAsync(virial6 + (size_t)c * N, v + (size_t)c * s->virial_pitch, sizeof(float) * N,
+                                    cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
     SYS_CATCH(s)
     }
 
@@ -1513,6 +1744,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
             {
             CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, s->mg ? &s->d_state.p->N : nullptr));
             CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
+            enqueue_nlist_filter(s, nullptr);
             }
         }
     CUDA_OK(cudaEventRecord(e1, s->stream));

@@ -66,6 +66,8 @@ static void tile_configure(b200_system* s)
     // particles (137 vs 270 us, profiles/r1h_*), but its list build is slower than the binned CSR build and at 64k
     // particles both are latency-bound -- see DESIGN.md section 4b for the measurements and what is left to do
     if (!s->have_nlist || s->pair_mode != 1) return;
+    if (s->bond_kind >= 0 || s->exclusions_set)
+        throw std::runtime_error("tile: the cell-tile path carries neither bonded forces nor nlist exclusions");
     if (!tile_pick_geometry(s))
         {
         if (s->pair_mode == 1) throw std::runtime_error("tile: cell-tile path needs one GPU, a periodic orthorhombic box with "

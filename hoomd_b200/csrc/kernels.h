@@ -48,6 +48,9 @@ struct FusedStepArgs
     float kT; unsigned int seed; int noiseless_t;
     const unsigned int* d_N;      // multi-GPU: live local particle count (N above is then the capacity); else NULL
     int mg;                       // multi-GPU: the rebuild decision is taken by the all-ranks step barrier, not here
+    // second ForceCompute (bond force), already evaluated at the positions this step reads: added to the pair force
+    // before step two (Integrator::computeNetForce).  NULL = the pair force is the only force.
+    const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch;
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);
@@ -69,5 +72,12 @@ cudaError_t launch_compute_accel(float* accel, const float4* net_force, const fl
 
 namespace b200
 {
+// bond.cu
+cudaError_t launch_nlist_filter(unsigned int* n_neigh, unsigned int* nlist, const unsigned int* head_list,
+                                const unsigned int* n_ex, const unsigned int* ex_list, unsigned int ex_pitch,
+                                unsigned int max_ex, const unsigned int* tag, const unsigned int* rtag, unsigned int N,
+                                const unsigned int* enable, cudaStream_t stream);
+cudaError_t launch_add_force(float4* net, float* net_virial, unsigned int net_pitch, const float4* f, const float* v,
+                             unsigned int v_pitch, unsigned int N, bool virial, cudaStream_t stream);
 cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, unsigned int N, cudaStream_t stream);
 }

@@ -36,6 +36,7 @@ template<class Evaluator> struct MdStepArgs
     // cell-tile path (tile.cu)
     TileGeom tile; const unsigned int* cell_start; const uint4* ell4; unsigned int ell_pitch, ell_nmax;
     int force_only;           // compute and store the net force only (prepRun / stand-alone force evaluation)
+    const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch; // second ForceCompute (bonds)
     };
 
 constexpr int MD_BLOCK = 256;
@@ -43,12 +44,23 @@ constexpr int MD_BLOCK = 256;
 // phase 2 of the step for particle i: net force F -> step two(ts2) -> step one(ts2+1) -> distance check.  Returns the
 // particle's distance-check result.
 template<class Evaluator, bool VIRIAL>
-__device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, const float4 F,
-                                                  const float4 pi4, const float (&vir)[6], unsigned int ts2, bool last,
+__device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, float4 F,
+                                                  const float4 pi4, float (&vir)[6], unsigned int ts2, bool last,
                                                   bool store_force)
     {
     bool moved = false;
     float4 v = a.vel[i];
+    if (a.extra_force)
+        {
+        // Integrator::computeNetForce: net = pair + bond, in the order the forces were added (hoomd/Integrator.cc:308-420)
+        const float4 e = a.extra_force[i];
+        F.x = __fadd_rn(F.x, e.x); F.y = __fadd_rn(F.y, e.y); F.z = __fadd_rn(F.z, e.z); F.w = __fadd_rn(F.w, e.w);
+        if (VIRIAL)
+            {
+#pragma unroll
+            for (int c = 0; c < 6; c++) vir[c] = __fadd_rn(vir[c], a.extra_virial[(size_t)c * a.extra_virial_pitch + i]);
+            }
+        }
     if (store_force)
         {
         a.net_force[i] = F;
@@ -140,6 +152,7 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
     a.copy_pos_on_last = copy_pos_on_last;
     a.d_N = fa.d_N; a.mg = fa.mg;
+    a.extra_force = fa.extra_force; a.extra_virial = fa.extra_virial; a.extra_virial_pitch = fa.extra_virial_pitch;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

@@ -17,8 +17,9 @@ def _p(a):
 class System:
     """SystemDefinition + nlist.cell + pair.lj + integrate.mode_standard + nve/langevin on one B200."""
 
-    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, device=0):
+    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, device=0, n_bond_types=0):
         L = _lib.lib()
+        self.n_bond_types = int(n_bond_types)
         pos4 = np.ascontiguousarray(pos4, np.float32)
         self.N = int(pos4.shape[0])
         self.ntypes = int(ntypes)
@@ -79,6 +80,44 @@ class System:
         self._check(_lib.lib().b200_sys_setup_lj(self.h, C.c_float(r_buff), int(check_period), _p(rc), _p(lj1),
                                                  _p(lj2), _p(ron), int(shift_mode)))
         self.lj1, self.lj2, self.rcut = lj1, lj2, rc
+
+    # ---- BondData + md.bond.* + nlist exclusions -------------------------------------------------------------
+    def set_bonds(self, bonds, types=None, n_bond_types=None):
+        """bonds: (nbonds, 2) particle TAGS; types: bond type per bond (default 0)"""
+        b = np.ascontiguousarray(bonds, np.uint32).reshape(-1, 2)
+        t = np.zeros(len(b), np.uint32) if types is None else np.ascontiguousarray(types, np.uint32)
+        self.n_bond_types = int(n_bond_types or self.n_bond_types or 1)
+        self._check(_lib.lib().b200_sys_set_bonds(self.h, len(b), _p(b), _p(t), self.n_bond_types))
+
+    def setup_fene(self, k=30.0, r0=1.5, epsilon=1.0, sigma=1.0):
+        """md.bond.fene + bond_coeff.set: lj1 = 4 eps sigma^12, lj2 = 4 eps sigma^6 (hoomd/md/bond.py:367-372)"""
+        nb = self.n_bond_types
+        bc = lambda x: np.broadcast_to(np.asarray(x, np.float64), (nb,))
+        K = np.ascontiguousarray(bc(k), np.float32)
+        R = np.ascontiguousarray(bc(r0), np.float32)
+        lj1 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 12, np.float32)
+        lj2 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 6, np.float32)
+        self._check(_lib.lib().b200_sys_setup_bond_force(self.h, 0, _p(K), _p(R), _p(lj1), _p(lj2)))
+        self.bond_params = (K, R, lj1, lj2)
+
+    def setup_harmonic(self, k, r0):
+        """md.bond.harmonic + bond_coeff.set (hoomd/md/bond.py:290-296)"""
+        nb = self.n_bond_types
+        K = np.ascontiguousarray(np.broadcast_to(np.asarray(k, np.float64), (nb,)), np.float32)
+        R = np.ascontiguousarray(np.broadcast_to(np.asarray(r0, np.float64), (nb,)), np.float32)
+        self._check(_lib.lib().b200_sys_setup_bond_force(self.h, 1, _p(K), _p(R), None, None))
+        self.bond_params = (K, R)
+
+    def exclusions_from_bonds(self, on=True):
+        """nlist.reset_exclusions(['bond']) / reset_exclusions([])"""
+        self._check(_lib.lib().b200_sys_nlist_exclusions_from_bonds(self.h, int(on)))
+
+    def force_component(self, which, virial=False):
+        """per-ForceCompute arrays after compute_forces: 0 = pair, 1 = bond"""
+        f = np.empty((self.N, 4), np.float32)
+        v = np.empty((6, self.N), np.float32) if virial else None
+        self._check(_lib.lib().b200_sys_get_force_component(self.h, int(which), _p(f), _p(v)))
+        return f, v
 
     def set_virial(self, on=True):
         self._check(_lib.lib().b200_sys_set_virial(self.h, int(on)))

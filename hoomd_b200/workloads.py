@@ -56,3 +56,33 @@ def random_system(N, L, seed=0, ntypes=1, min_dist=0.0):
 
 KA_PARAMS = dict(  # Kob-Andersen 80:20 (BASELINE config 3)
     epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]], r_cut=[[2.5, 2.0], [2.0, 2.2]])
+
+
+KG_PARAMS = dict(  # Kremer-Grest bead-spring melt (BASELINE config 4)
+    rho=0.85, r_cut=2.0 ** (1.0 / 6.0), fene_k=30.0, fene_r0=1.5, epsilon=1.0, sigma=1.0, kT=1.0)
+
+
+def polymer_lattice(n_side, chain_len, rho=0.85, kT=1.0, seed=42):
+    """n_side^3 beads on a simple-cubic lattice (a = rho^(-1/3)), threaded into linear chains of chain_len beads.
+
+    The lattice sites are visited along a boustrophedon (snake) path so that consecutive sites are always lattice
+    neighbors (bond length a = 1.056 at rho = 0.85 < FENE r0 = 1.5); the path is cut every chain_len sites.  With
+    n_side = 100 and chain_len = 100 every chain is one straight row (10,000 chains x 100 beads = 1M beads).
+    Returns (pos4, vel4, L, bonds[nbonds, 2] of particle tags).
+    """
+    N = n_side ** 3
+    assert N % chain_len == 0, "chain_len must divide n_side^3"
+    a = (1.0 / rho) ** (1.0 / 3.0)
+    pos, vel, L = sc_lattice(n_side, a, kT=kT, seed=seed)
+    # site index along the snake path: z slowest, y snakes within z, x snakes within y
+    z, y, x = np.meshgrid(np.arange(n_side), np.arange(n_side), np.arange(n_side), indexing="ij")
+    y = np.where(z % 2 == 1, n_side - 1 - y, y)
+    row = z * n_side + np.where(z % 2 == 1, n_side - 1 - y, y)  # rows in visiting order
+    x = np.where(row % 2 == 1, n_side - 1 - x, x)
+    # sc_lattice numbers sites as (ix * n + iy) * n + iz (meshgrid 'ij'): take the snake's sites in path order
+    site = ((x * n_side + y) * n_side + z).ravel()
+    pos = np.ascontiguousarray(pos[site])
+    p = np.arange(N, dtype=np.uint32)
+    keep = (p % chain_len) != (chain_len - 1)
+    bonds = np.stack([p[keep], p[keep] + 1], axis=1).astype(np.uint32)
+    return pos, vel, L, bonds

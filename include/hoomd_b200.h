@@ -202,6 +202,53 @@ typedef struct b200_pair_args
 B200_API int b200_compute_lj_forces(const b200_pair_args* args, const float* d_params, b200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * NeighborList exclusions  -- replaces gpu_nlist_filter (hoomd/md/NeighborListGPU.cu:140-240); semantics of
+ * NeighborList::filterNlist (hoomd/md/NeighborList.cc:1275-1328): every row is rewritten in place without its excluded
+ * partners, order of the survivors kept, n_neigh updated.  Exclusion table: d_ex_list[k * ex_pitch + row], k < d_n_ex[row]
+ * (Index2D exli(row, k), hoomd/Index1D.h).  d_tag == d_rtag == NULL: rows and entries are particle INDICES (the
+ * reference's m_ex_list_idx, rebuilt by updateExListIdx after every sort).  Both non-NULL: rows are keyed by tag[i] and
+ * entries are TAGS resolved through rtag on the fly (the reference's m_ex_list_tag used directly: no table rebuild).
+ * ------------------------------------------------------------------------------------------------------------- */
+B200_API int b200_nlist_filter(unsigned int* d_n_neigh, unsigned int* d_nlist, const unsigned int* d_head_list,
+                               const unsigned int* d_n_ex, const unsigned int* d_ex_list, unsigned int ex_pitch,
+                               unsigned int ex_height /* Index2D::getH(): longest exclusion row */,
+                               const unsigned int* d_tag, const unsigned int* d_rtag, unsigned int N,
+                               b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * PotentialBond<EvaluatorBondFENE | EvaluatorBondHarmonic>  -- replaces gpu_compute_fene_forces /
+ * gpu_compute_harmonic_forces(const bond_args_t&, params, d_flags) (hoomd/md/AllDriverPotentialBondGPU.cuh:17-24,
+ * hoomd/md/PotentialBondGPU.cuh:26-98,112-330); arithmetic of hoomd/md/PotentialBond.h:155-300 +
+ * hoomd/md/EvaluatorBondFENE.h:95-133 / EvaluatorBondHarmonic.h:75-92.  One thread per particle walks its bond rows:
+ * force_i = sum dx * force_divr, pe_i = sum bond_eng/2, virial_i = sum dx dx force_divr/2, dx = minImage(pos_i - pos_j).
+ * *d_flags is set to 1 when a bond cannot be evaluated (FENE: r >= r_0, "bond out of bounds").
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct b200_bond_args
+    {
+    float*        d_force;        /* Scalar4[N] */
+    float*        d_virial;       /* [6*virial_pitch]; may be NULL if !compute_virial */
+    unsigned int  virial_pitch;
+    unsigned int  N;
+    const float*  d_pos;          /* Scalar4 */
+    const float*  d_diameter;     /* [n] or NULL = every diameter 1.0 (ParticleData default) */
+    b200_box      box;
+    const unsigned int* d_bond_list; /* uint2 (partner, bond type) at [k * pitch + row] (group_storage<2>, gpu_table_indexer) */
+    unsigned int  pitch;
+    const unsigned int* d_n_bonds;   /* [rows] */
+    unsigned int  n_bond_types;
+    unsigned int  compute_virial;
+    const unsigned int* d_tag;    /* NULL: rows/partners are particle indices (BondedGroupData GPU table);           */
+    const unsigned int* d_rtag;   /* both set: rows keyed by tag[i], partners are tags looked up in rtag             */
+    } b200_bond_args;
+
+/* d_params: Scalar4[n_bond_types] = (K, r_0, lj1, lj2), lj1 = 4 eps sigma^12, lj2 = 4 eps sigma^6 (hoomd/md/bond.py:367-372) */
+B200_API int b200_compute_fene_bond_forces(const b200_bond_args* args, const float* d_params, unsigned int* d_flags,
+                                           b200_stream_t stream);
+/* d_params: Scalar2[n_bond_types] = (K, r_0) (hoomd/md/bond.py:290-296) */
+B200_API int b200_compute_harmonic_bond_forces(const b200_bond_args* args, const float* d_params,
+                                               unsigned int* d_flags, b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * Integrator  -- replaces gpu_integrator_sum_net_force (hoomd/Integrator.cu:115-153), gpu_nve_step_one/two
  * (hoomd/md/TwoStepNVEGPU.cu:120-150,392-430), gpu_langevin_step_two (hoomd/md/TwoStepLangevinGPU.cu:444-500).
  * Arithmetic follows the CPU oracle (hoomd/md/TwoStepNVE.cc:77-122,255-300, hoomd/md/TwoStepLangevin.cc:86-125,
@@ -306,6 +353,20 @@ B200_API int b200_sys_get_particles(b200_system* s, float* pos4, float* vel4, fl
  * rcut/lj1/lj2/ron: ntypes x ntypes row-major (ron may be NULL). */
 B200_API int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut,
                                const float* lj1, const float* lj2, const float* ron, int shift_mode);
+/* BondData of the snapshot (hoomd/BondedGroupData.h): nbonds bonds between particle TAGS tags2[2b], tags2[2b+1] of bond
+ * type types[b] < n_bond_types (HOST pointers).  Replaces any previous bond set. */
+B200_API int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* tags2,
+                                const unsigned int* types, unsigned int n_bond_types);
+/* md.bond.fene() + bond_coeff.set per bond type (K, r0, lj1, lj2 arrays of n_bond_types; hoomd/md/bond.py:308-372), or
+ * md.bond.harmonic() (K, r0; lj1 = lj2 = NULL, kind = 1).  kind 0 = FENE.  The bond force is a second ForceCompute of
+ * the integrator, summed after the pair force (Integrator::computeNetForce, hoomd/Integrator.cc:308-420). */
+B200_API int b200_sys_setup_bond_force(b200_system* s, int kind, const float* K, const float* r0, const float* lj1,
+                                       const float* lj2);
+/* nlist.reset_exclusions(exclusions=['bond']) (NeighborList::addExclusionsFromBonds, hoomd/md/NeighborList.cc:603-630);
+ * on = 0: clearExclusions.  The md.nlist default is ['bond','body'] (hoomd/md/nlist.py:104-110). */
+B200_API int b200_sys_nlist_exclusions_from_bonds(b200_system* s, int on);
+/* per-ForceCompute arrays after b200_sys_compute_forces: which = 0 pair force, 1 bond force (index order; virial6 [6*N]) */
+B200_API int b200_sys_get_force_component(b200_system* s, int which, float* force4, float* virial6);
 /* pdata flags pressure_tensor | isotropic_virial (hoomd/md/PotentialPair.h:342-343) */
 B200_API int b200_sys_set_virial(b200_system* s, int on);
 /* md.integrate.mode_standard(dt) */

@@ -54,6 +54,15 @@ struct orc_system
     /* Integrator */
     float dt; int method, limit, zero_force, noiseless_t; float limit_val, kT; unsigned int seed; float* gamma;
     unsigned int timestep;
+    /* BondData + PotentialBond + exclusions (tag == index in this restatement: no sorter) */
+    unsigned int nbonds, n_bond_types;
+    unsigned int *bond_a, *bond_b, *bond_type;
+    int bond_kind; /* -1 none, 0 FENE, 1 harmonic */
+    float *bond_K, *bond_r0, *bond_lj1, *bond_lj2;
+    f4 *pair_force, *bond_force;
+    float *pair_virial, *bond_virial;
+    int exclusions_set; unsigned int ex_max; unsigned int *ex_n, *ex_list; /* ex_list[i*ex_max + k] */
+    int bond_error;
     char error[256];
     };
 
@@ -411,6 +420,24 @@ static int nl_build(orc_system* s, unsigned int ts)
     return 0;
     }
 
+static void nl_filter(orc_system* s) /* NeighborList::filterNlist, NeighborList.cc:1275-1328 */
+    {
+    for (unsigned int idx = 0; idx < s->N; idx++)
+        {
+        const unsigned int head = s->head[idx], n = s->n_neigh[idx], n_ex = s->ex_n[idx];
+        unsigned int out = 0;
+        for (unsigned int k = 0; k < n; k++)
+            {
+            const unsigned int cur = s->nlist[head + k];
+            int excluded = 0;
+            for (unsigned int e = 0; e < n_ex; e++)
+                if (s->ex_list[(size_t)idx * s->ex_max + e] == cur) { excluded = 1; break; }
+            if (!excluded) s->nlist[head + out++] = cur;
+            }
+        s->n_neigh[idx] = out;
+        }
+    }
+
 static int nl_compute(orc_system* s, unsigned int ts) /* NeighborList::compute, NeighborList.cc:201-253 */
     {
     if (!s->have_nlist) { snprintf(s->error, sizeof(s->error), "nlist not set up"); return 1; }
@@ -437,12 +464,102 @@ static int nl_compute(orc_system* s, unsigned int ts) /* NeighborList::compute, 
                 memset(s->conditions, 0, sizeof(unsigned int) * s->ntypes);
                 }
             } while (overflowed);
+        if (s->exclusions_set) nl_filter(s);
         for (unsigned int i = 0; i < s->N; i++) /* setLastUpdatedPos, NeighborList.cc:1044-1066 */
             {
             f4 lp = {s->pos[i].x, s->pos[i].y, s->pos[i].z, 0.0f};
             s->last_pos[i] = lp;
             }
         }
+    return 0;
+    }
+
+/* ---- PotentialBond<evaluator>::computeForces (PotentialBond.h:155-300) + EvaluatorBondFENE.h:95-133 /
+ * EvaluatorBondHarmonic.h:75-92, then Integrator::computeNetForce (Integrator.cc:308-420): net = pair + bond ------------- */
+static int compute_bond_forces(orc_system* s)
+    {
+    const unsigned int N = s->N;
+    const int compute_virial = s->compute_virial;
+    memcpy(s->pair_force, s->net_force, sizeof(f4) * N);
+    memcpy(s->pair_virial, s->net_virial, sizeof(float) * 6 * (size_t)N);
+    memset(s->bond_force, 0, sizeof(f4) * N);
+    memset(s->bond_virial, 0, sizeof(float) * 6 * (size_t)N);
+    for (unsigned int b = 0; b < s->nbonds; b++)
+        {
+        const unsigned int ia = s->bond_a[b], ib = s->bond_b[b], t = s->bond_type[b]; /* rtag == identity */
+        f3 dx = {s->pos[ib].x - s->pos[ia].x, s->pos[ib].y - s->pos[ia].y, s->pos[ib].z - s->pos[ia].z};
+        dx = box_min_image(&s->box, dx);
+        float rsq = dot3(dx);
+        float force_divr = 0.0f, bond_eng = 0.0f;
+        const float K = s->bond_K[t], r_0 = s->bond_r0[t];
+        if (s->bond_kind == 0)
+            {
+            const float lj1 = s->bond_lj1[t], lj2 = s->bond_lj2[t];
+            const float diameter_a = 1.0f, diameter_b = 1.0f; /* ParticleData default diameter */
+            float rmdoverr = 1.0f;
+            float rtemp = sqrtf(rsq) - diameter_a / 2 - diameter_b / 2 + 1.0f;
+            rmdoverr = rtemp / sqrtf(rsq);
+            rsq = rtemp * rtemp;
+            {
+            float r2inv = 1.0f / rsq;
+            float r6inv = r2inv * r2inv * r2inv;
+            float WCAforcemag_divr = 0.0f, pair_eng = 0.0f;
+            float sigma6inv = lj2 / lj1;
+            float epsilon = lj2 * lj2 / 4.0f / lj1;
+            if (r6inv > sigma6inv / 2.0f)
+                {
+                WCAforcemag_divr = r2inv * r6inv * (12.0f * lj1 * r6inv - 6.0f * lj2);
+                pair_eng = (r6inv * (lj1 * r6inv - lj2) + epsilon);
+                }
+            force_divr = WCAforcemag_divr * rmdoverr;
+            bond_eng = pair_eng;
+            if (K != 0.0f)
+                {
+                if (rsq >= r_0 * r_0)
+                    {
+                    snprintf(s->error, sizeof(s->error), "bond.fene: bond out of bounds");
+                    return 1;
+                    }
+                force_divr += -K / (1.0f - rsq / (r_0 * r_0)) * rmdoverr;
+                bond_eng += -0.5f * K * (r_0 * r_0) * logf(1.0f - rsq / (r_0 * r_0));
+                }
+            }
+            }
+        else
+            {
+            float r = sqrtf(rsq);
+            force_divr = K * (r_0 / r - 1.0f);
+            if (!isfinite(force_divr)) force_divr = 0.0f;
+            bond_eng = 0.5f * K * (r_0 - r) * (r_0 - r);
+            }
+        bond_eng *= 0.5f;
+        {
+        float bv[6] = {0, 0, 0, 0, 0, 0};
+        if (compute_virial)
+            {
+            float force_div2r = (float)(1.0 / 2.0) * force_divr;
+            bv[0] = dx.x * dx.x * force_div2r; bv[1] = dx.x * dx.y * force_div2r; bv[2] = dx.x * dx.z * force_div2r;
+            bv[3] = dx.y * dx.y * force_div2r; bv[4] = dx.y * dx.z * force_div2r; bv[5] = dx.z * dx.z * force_div2r;
+            }
+        s->bond_force[ib].x += force_divr * dx.x; s->bond_force[ib].y += force_divr * dx.y;
+        s->bond_force[ib].z += force_divr * dx.z; s->bond_force[ib].w += bond_eng;
+        s->bond_force[ia].x -= force_divr * dx.x; s->bond_force[ia].y -= force_divr * dx.y;
+        s->bond_force[ia].z -= force_divr * dx.z; s->bond_force[ia].w += bond_eng;
+        if (compute_virial)
+            for (int c = 0; c < 6; c++)
+                {
+                s->bond_virial[c * (size_t)N + ib] += bv[c];
+                s->bond_virial[c * (size_t)N + ia] += bv[c];
+                }
+        }
+        }
+    for (unsigned int i = 0; i < N; i++)
+        {
+        s->net_force[i].x += s->bond_force[i].x; s->net_force[i].y += s->bond_force[i].y;
+        s->net_force[i].z += s->bond_force[i].z; s->net_force[i].w += s->bond_force[i].w;
+        }
+    if (compute_virial)
+        for (size_t k = 0; k < 6 * (size_t)N; k++) s->net_virial[k] += s->bond_virial[k];
     return 0;
     }
 
@@ -519,6 +636,7 @@ static int compute_forces(orc_system* s, unsigned int ts)
             s->net_virial[4 * (size_t)N + i] += vyz; s->net_virial[5 * (size_t)N + i] += vzz;
             }
         }
+    if (s->bond_kind >= 0) return compute_bond_forces(s);
     return 0;
     }
 
@@ -612,7 +730,90 @@ orc_system* orc_create(unsigned int N, float Lx, float Ly, float Lz, unsigned in
     s->tag = (unsigned int*)calloc(N, sizeof(unsigned int)); s->net_virial = (float*)calloc(6 * (size_t)N, sizeof(float));
     for (unsigned int i = 0; i < N; i++) { s->tag[i] = i; s->vel[i].w = 1.0f; }
     s->cl_first = s->cl_force = 1; s->nl_first = 1; s->force_update = 1;
+    s->bond_kind = -1;
     return s;
+    }
+
+/* BondData: bonds between particle tags (tag == index here) */
+int orc_set_bonds(orc_system* s, unsigned int nbonds, const unsigned int* tags2, const unsigned int* types,
+                  unsigned int n_bond_types)
+    {
+    free(s->bond_a); free(s->bond_b); free(s->bond_type);
+    s->nbonds = nbonds; s->n_bond_types = n_bond_types;
+    s->bond_a = (unsigned int*)calloc(nbonds ? nbonds : 1, sizeof(unsigned int));
+    s->bond_b = (unsigned int*)calloc(nbonds ? nbonds : 1, sizeof(unsigned int));
+    s->bond_type = (unsigned int*)calloc(nbonds ? nbonds : 1, sizeof(unsigned int));
+    for (unsigned int b = 0; b < nbonds; b++)
+        {
+        if (tags2[2 * b] >= s->N || tags2[2 * b + 1] >= s->N || types[b] >= n_bond_types)
+            {
+            snprintf(s->error, sizeof(s->error), "bond: tag or type out of bounds");
+            return 1;
+            }
+        s->bond_a[b] = tags2[2 * b]; s->bond_b[b] = tags2[2 * b + 1]; s->bond_type[b] = types[b];
+        }
+    return 0;
+    }
+
+/* md.bond.fene (kind 0) / md.bond.harmonic (kind 1) */
+int orc_setup_bond(orc_system* s, int kind, const float* K, const float* r0, const float* lj1, const float* lj2)
+    {
+    const unsigned int nb = s->n_bond_types, N = s->N;
+    if (!nb) { snprintf(s->error, sizeof(s->error), "bond: No bonds are defined."); return 1; }
+    free(s->bond_K); free(s->bond_r0); free(s->bond_lj1); free(s->bond_lj2);
+    s->bond_K = (float*)calloc(nb, sizeof(float)); s->bond_r0 = (float*)calloc(nb, sizeof(float));
+    s->bond_lj1 = (float*)calloc(nb, sizeof(float)); s->bond_lj2 = (float*)calloc(nb, sizeof(float));
+    for (unsigned int t = 0; t < nb; t++)
+        {
+        s->bond_K[t] = K[t]; s->bond_r0[t] = r0[t];
+        if (kind == 0) { s->bond_lj1[t] = lj1[t]; s->bond_lj2[t] = lj2[t]; }
+        }
+    if (!s->bond_force)
+        {
+        s->pair_force = (f4*)calloc(N, sizeof(f4)); s->bond_force = (f4*)calloc(N, sizeof(f4));
+        s->pair_virial = (float*)calloc(6 * (size_t)N, sizeof(float));
+        s->bond_virial = (float*)calloc(6 * (size_t)N, sizeof(float));
+        }
+    s->bond_kind = kind;
+    return 0;
+    }
+
+/* NeighborList::addExclusionsFromBonds (NeighborList.cc:603-630) / clearExclusions; duplicates skipped (:431-470) */
+int orc_exclusions_from_bonds(orc_system* s, int on)
+    {
+    const unsigned int N = s->N;
+    free(s->ex_n); free(s->ex_list);
+    s->ex_n = NULL; s->ex_list = NULL; s->ex_max = 0; s->exclusions_set = 0;
+    s->force_update = 1;
+    if (!on) return 0;
+    s->ex_n = (unsigned int*)calloc(N, sizeof(unsigned int));
+    unsigned int* cnt = (unsigned int*)calloc(N, sizeof(unsigned int));
+    for (unsigned int b = 0; b < s->nbonds; b++) { cnt[s->bond_a[b]]++; cnt[s->bond_b[b]]++; }
+    unsigned int mx = 1;
+    for (unsigned int i = 0; i < N; i++) if (cnt[i] > mx) mx = cnt[i];
+    free(cnt);
+    s->ex_max = mx;
+    s->ex_list = (unsigned int*)calloc((size_t)N * mx, sizeof(unsigned int));
+    for (unsigned int b = 0; b < s->nbonds; b++)
+        {
+        const unsigned int ta = s->bond_a[b], tb = s->bond_b[b];
+        int dup = 0;
+        for (unsigned int e = 0; e < s->ex_n[ta]; e++) if (s->ex_list[(size_t)ta * mx + e] == tb) dup = 1;
+        if (dup) continue;
+        s->ex_list[(size_t)ta * mx + s->ex_n[ta]++] = tb;
+        s->ex_list[(size_t)tb * mx + s->ex_n[tb]++] = ta;
+        }
+    s->exclusions_set = 1;
+    return 0;
+    }
+
+/* which = 0 pair force, 1 bond force (after orc_compute_forces) */
+void orc_get_force_component(orc_system* s, int which, float* force4, float* virial6)
+    {
+    const f4* f = s->bond_kind < 0 ? s->net_force : (which ? s->bond_force : s->pair_force);
+    const float* v = s->bond_kind < 0 ? s->net_virial : (which ? s->bond_virial : s->pair_virial);
+    if (force4) memcpy(force4, f, sizeof(f4) * s->N);
+    if (virial6) memcpy(virial6, v, sizeof(float) * 6 * (size_t)s->N);
     }
 
 void orc_destroy(orc_system* s)
@@ -622,6 +823,9 @@ void orc_destroy(orc_system* s)
     free(s->net_virial); free(s->cell_size); free(s->xyzf); free(s->cell_adj); free(s->r_cut); free(s->r_listsq);
     free(s->rcut_max); free(s->Nmax); free(s->conditions); free(s->head); free(s->n_neigh); free(s->nlist);
     free(s->lj1); free(s->lj2); free(s->rcutsq); free(s->ronsq); free(s->gamma);
+    free(s->bond_a); free(s->bond_b); free(s->bond_type); free(s->bond_K); free(s->bond_r0); free(s->bond_lj1);
+    free(s->bond_lj2); free(s->pair_force); free(s->bond_force); free(s->pair_virial); free(s->bond_virial);
+    free(s->ex_n); free(s->ex_list);
     free(s);
     }
 

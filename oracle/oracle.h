@@ -26,6 +26,14 @@ void orc_get_particles(orc_system* s, float* pos4, float* vel4, float* accel3, i
 /* md.nlist.cell + md.pair.lj; matrices ntypes x ntypes row-major; full storage mode */
 int orc_setup_lj(orc_system* s, float r_buff, unsigned int check_period, const float* rcut, const float* lj1,
                  const float* lj2, const float* ron, int shift_mode);
+/* BondData + md.bond.fene (kind 0: K, r0, lj1, lj2) / md.bond.harmonic (kind 1: K, r0) + nlist bond exclusions:
+ * hoomd/md/PotentialBond.h:155-300, EvaluatorBondFENE.h:95-133, EvaluatorBondHarmonic.h:75-92, NeighborList.cc:603-630,
+ * 1275-1328 */
+int orc_set_bonds(orc_system* s, unsigned int nbonds, const unsigned int* tags2, const unsigned int* types,
+                  unsigned int n_bond_types);
+int orc_setup_bond(orc_system* s, int kind, const float* K, const float* r0, const float* lj1, const float* lj2);
+int orc_exclusions_from_bonds(orc_system* s, int on);
+void orc_get_force_component(orc_system* s, int which, float* force4, float* virial6);
 void orc_set_virial(orc_system* s, int on);
 int orc_setup_integrator(orc_system* s, float dt);
 int orc_add_nve(orc_system* s, int limit, float limit_val, int zero_force);

@@ -52,6 +52,10 @@ def lib():
         L.orc_get_cell_dims.argtypes = [vp, vp]
         L.orc_get_cell_list.argtypes = [vp, vp, vp]
         L.orc_get_thermo.argtypes = [vp, vp]
+        L.orc_set_bonds.argtypes = [vp, C.c_uint, vp, vp, C.c_uint]
+        L.orc_setup_bond.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+        L.orc_exclusions_from_bonds.argtypes = [vp, C.c_int]
+        L.orc_get_force_component.argtypes = [vp, C.c_int, vp, vp]
         L.orc_saru.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp]
         _lib = L
     return _lib
@@ -62,8 +66,9 @@ def _ptr(a):
 
 
 class OracleSystem:
-    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, threads=1):
+    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, threads=1, n_bond_types=0):
         L = lib()
+        self.n_bond_types = int(n_bond_types)
         pos4 = np.ascontiguousarray(pos4, np.float32)
         self.N = pos4.shape[0]
         self.ntypes = ntypes
@@ -102,6 +107,37 @@ class OracleSystem:
         ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
         self._check(lib().orc_setup_lj(self.h, C.c_float(r_buff), int(check_period), _ptr(rc), _ptr(lj1), _ptr(lj2),
                                        _ptr(ron), int(shift_mode)))
+
+    # ---- BondData + md.bond.* + nlist exclusions (same surface as hoomd_b200.System / oracle.ref.RefSystem) ----
+    def set_bonds(self, bonds, types=None, n_bond_types=None):
+        b = np.ascontiguousarray(bonds, np.uint32).reshape(-1, 2)
+        t = np.zeros(len(b), np.uint32) if types is None else np.ascontiguousarray(types, np.uint32)
+        self.n_bond_types = int(n_bond_types or self.n_bond_types or 1)
+        self._check(lib().orc_set_bonds(self.h, len(b), _ptr(b), _ptr(t), self.n_bond_types))
+
+    def setup_fene(self, k=30.0, r0=1.5, epsilon=1.0, sigma=1.0):
+        nb = self.n_bond_types
+        bc = lambda x: np.broadcast_to(np.asarray(x, np.float64), (nb,))
+        K = np.ascontiguousarray(bc(k), np.float32)
+        R = np.ascontiguousarray(bc(r0), np.float32)
+        lj1 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 12, np.float32)
+        lj2 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 6, np.float32)
+        self._check(lib().orc_setup_bond(self.h, 0, _ptr(K), _ptr(R), _ptr(lj1), _ptr(lj2)))
+
+    def setup_harmonic(self, k, r0):
+        nb = self.n_bond_types
+        K = np.ascontiguousarray(np.broadcast_to(np.asarray(k, np.float64), (nb,)), np.float32)
+        R = np.ascontiguousarray(np.broadcast_to(np.asarray(r0, np.float64), (nb,)), np.float32)
+        self._check(lib().orc_setup_bond(self.h, 1, _ptr(K), _ptr(R), None, None))
+
+    def exclusions_from_bonds(self, on=True):
+        self._check(lib().orc_exclusions_from_bonds(self.h, int(on)))
+
+    def force_component(self, which, virial=False):
+        f = np.empty((self.N, 4), np.float32)
+        v = np.empty((6, self.N), np.float32) if virial else None
+        lib().orc_get_force_component(self.h, int(which), _ptr(f), _ptr(v))
+        return f, v
 
     def set_virial(self, on=True):
         lib().orc_set_virial(self.h, int(on))

@@ -28,6 +28,12 @@ def lib():
         _lib = C.CDLL(_PATH, mode=C.RTLD_GLOBAL)
         _lib.ref_create.restype = C.c_void_p
         _lib.ref_create.argtypes = [C.c_uint, C.c_float, C.c_float, C.c_float, C.c_uint]
+        _lib.ref_create_bonded.restype = C.c_void_p
+        _lib.ref_create_bonded.argtypes = [C.c_uint, C.c_float, C.c_float, C.c_float, C.c_uint, C.c_uint]
+        _lib.ref_add_bonds.argtypes = [C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p]
+        _lib.ref_setup_bond.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.ref_nlist_exclusions_from_bonds.argtypes = [C.c_void_p, C.c_int]
+        _lib.ref_get_bond_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
         for name in ("ref_destroy", "ref_last_error", "ref_get_N", "ref_get_timestep", "ref_get_virial_pitch",
@@ -43,12 +49,17 @@ def _ptr(a):
 class RefSystem:
     """One reference simulation: ParticleData + nlist.cell + pair.lj + integrate.mode_standard + nve/langevin."""
 
-    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None):
+    def __init__(self, pos4, box, ntypes=1, vel4=None, image=None, n_bond_types=0):
         L = lib()
         pos4 = np.ascontiguousarray(pos4, np.float32)
         self.N = pos4.shape[0]
         self.ntypes = ntypes
-        self.h = C.c_void_p(L.ref_create(self.N, C.c_float(box[0]), C.c_float(box[1]), C.c_float(box[2]), ntypes))
+        self.n_bond_types = int(n_bond_types)
+        if n_bond_types:
+            self.h = C.c_void_p(L.ref_create_bonded(self.N, C.c_float(box[0]), C.c_float(box[1]), C.c_float(box[2]),
+                                                    ntypes, int(n_bond_types)))
+        else:
+            self.h = C.c_void_p(L.ref_create(self.N, C.c_float(box[0]), C.c_float(box[1]), C.c_float(box[2]), ntypes))
         self._check(0)
         self.set_particles(pos4, vel4, image)
 
@@ -89,6 +100,38 @@ class RefSystem:
                                    _ptr(lj2), _ptr(ron), int(shift_mode))
         self._check(rcode)
         self.lj1, self.lj2, self.rcut = lj1, lj2, rc
+
+    # ---- BondData + md.bond.* + nlist exclusions (same surface as hoomd_b200.System) ----
+    def set_bonds(self, bonds, types=None, n_bond_types=None):
+        b = np.ascontiguousarray(bonds, np.uint32).reshape(-1, 2)
+        t = np.zeros(len(b), np.uint32) if types is None else np.ascontiguousarray(types, np.uint32)
+        self._check(lib().ref_add_bonds(self.h, len(b), _ptr(b), _ptr(t)))
+
+    def setup_fene(self, k=30.0, r0=1.5, epsilon=1.0, sigma=1.0):
+        nb = self.n_bond_types
+        bc = lambda x: np.broadcast_to(np.asarray(x, np.float64), (nb,))
+        K = np.ascontiguousarray(bc(k), np.float32)
+        R = np.ascontiguousarray(bc(r0), np.float32)
+        lj1 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 12, np.float32)
+        lj2 = np.ascontiguousarray(4.0 * bc(epsilon) * bc(sigma) ** 6, np.float32)
+        self._check(lib().ref_setup_bond(self.h, 0, _ptr(K), _ptr(R), _ptr(lj1), _ptr(lj2)))
+
+    def setup_harmonic(self, k, r0):
+        nb = self.n_bond_types
+        K = np.ascontiguousarray(np.broadcast_to(np.asarray(k, np.float64), (nb,)), np.float32)
+        R = np.ascontiguousarray(np.broadcast_to(np.asarray(r0, np.float64), (nb,)), np.float32)
+        self._check(lib().ref_setup_bond(self.h, 1, _ptr(K), _ptr(R), None, None))
+
+    def exclusions_from_bonds(self, on=True):
+        self._check(lib().ref_nlist_exclusions_from_bonds(self.h, int(on)))
+
+    def force_component(self, which, virial=False):
+        if which == 0:
+            return self.forces(virial)
+        f = np.empty((self.N, 4), np.float32)
+        v = np.empty((6, self.N), np.float32) if virial else None
+        lib().ref_get_bond_forces(self.h, _ptr(f), _ptr(v))
+        return f, v
 
     def set_virial(self, on=True):
         lib().ref_set_virial(self.h, int(on))

@@ -21,6 +21,7 @@
 #include "hoomd/Saru.h"
 #include "hoomd/md/NeighborListBinned.h"
 #include "hoomd/md/AllPairPotentials.h"
+#include "hoomd/md/AllBondPotentials.h"
 #include "hoomd/md/IntegratorTwoStep.h"
 #include "hoomd/md/TwoStepNVE.h"
 #include "hoomd/md/TwoStepLangevin.h"
@@ -41,6 +42,7 @@ struct RefSystem
     std::shared_ptr<CellList> cl;
     std::shared_ptr<NeighborListBinned> nlist;
     std::shared_ptr<PotentialPairLJ> lj;
+    std::shared_ptr<ForceCompute> bond;   // PotentialBondFENE or PotentialBondHarmonic (md.bond.fene / md.bond.harmonic)
     std::shared_ptr<IntegratorTwoStep> integrator;
     std::shared_ptr<TwoStepNVE> nve;
     std::shared_ptr<TwoStepLangevin> langevin;
@@ -94,6 +96,78 @@ void* ref_create(unsigned int N, float Lx, float Ly, float Lz, unsigned int ntyp
         s->error = e.what();
         }
     return s;
+    }
+
+//! Same with \a n_bond_types bond types (BondData is sized at SystemDefinition construction)
+void* ref_create_bonded(unsigned int N, float Lx, float Ly, float Lz, unsigned int ntypes, unsigned int n_bond_types)
+    {
+    RefSystem* s = new RefSystem;
+    try
+        {
+        std::shared_ptr<Messenger> msg(new Messenger());
+        msg->setNoticeLevel(0);
+        s->exec_conf = std::shared_ptr<ExecutionConfiguration>(
+            new ExecutionConfiguration(ExecutionConfiguration::CPU, -1, false, false, msg));
+        BoxDim box(Lx, Ly, Lz);
+        s->sysdef = std::shared_ptr<SystemDefinition>(
+            new SystemDefinition(N, box, ntypes, n_bond_types, 0, 0, 0, s->exec_conf));
+        s->pdata = s->sysdef->getParticleData();
+        std::shared_ptr<ParticleSelector> sel(new ParticleSelectorTag(s->sysdef, 0, N - 1));
+        s->group_all = std::shared_ptr<ParticleGroup>(new ParticleGroup(s->sysdef, sel));
+        apply_flags(s);
+        }
+    catch (const std::exception& e)
+        {
+        s->error = e.what();
+        }
+    return s;
+    }
+
+//! BondData::addBondedGroup for every bond (tags2 = pairs of particle tags)
+int ref_add_bonds(void* h, unsigned int nbonds, const unsigned int* tags2, const unsigned int* types)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<BondData> bd = s->sysdef->getBondData();
+    for (unsigned int b = 0; b < nbonds; b++)
+        bd->addBondedGroup(Bond(types[b], tags2[2 * b], tags2[2 * b + 1]));
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! md.bond.fene (kind 0: params (K, r0, lj1, lj2)) or md.bond.harmonic (kind 1: params (K, r0)) per bond type
+int ref_setup_bond(void* h, int kind, const float* K, const float* r0, const float* lj1, const float* lj2)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    unsigned int nb = s->sysdef->getBondData()->getNTypes();
+    if (kind == 0)
+        {
+        std::shared_ptr<PotentialBondFENE> f(new PotentialBondFENE(s->sysdef, ""));
+        for (unsigned int t = 0; t < nb; t++) f->setParams(t, make_scalar4(K[t], r0[t], lj1[t], lj2[t]));
+        s->bond = f;
+        }
+    else
+        {
+        std::shared_ptr<PotentialBondHarmonic> f(new PotentialBondHarmonic(s->sysdef, ""));
+        for (unsigned int t = 0; t < nb; t++) f->setParams(t, make_scalar2(K[t], r0[t]));
+        s->bond = f;
+        }
+    if (s->integrator) s->integrator->addForceCompute(s->bond);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! nlist.reset_exclusions(['bond']) (on) / reset_exclusions([]) (off)
+int ref_nlist_exclusions_from_bonds(void* h, int on)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->nlist->clearExclusions();
+    if (on) s->nlist->addExclusionsFromBonds();
+    s->nlist->forceUpdate();
+    REF_CATCH(s, 1)
+    return 0;
     }
 
 void ref_destroy(void* h)
@@ -178,6 +252,7 @@ int ref_setup_integrator(void* h, float dt)
     REF_TRY(s)
     s->integrator = std::shared_ptr<IntegratorTwoStep>(new IntegratorTwoStep(s->sysdef, dt));
     if (s->lj) s->integrator->addForceCompute(s->lj);
+    if (s->bond) s->integrator->addForceCompute(s->bond);
     s->thermo = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, s->group_all, ""));
     REF_CATCH(s, 1)
     return 0;
@@ -248,8 +323,25 @@ int ref_compute_forces(void* h, unsigned int ts)
     RefSystem* s = static_cast<RefSystem*>(h);
     REF_TRY(s)
     s->lj->compute(ts);
+    if (s->bond) s->bond->compute(ts);
     REF_CATCH(s, 1)
     return 0;
+    }
+
+//! force / virial arrays of the bond ForceCompute after ref_compute_forces
+void ref_get_bond_forces(void* h, float* force4, float* virial6)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    unsigned int N = s->pdata->getN();
+    ArrayHandle<Scalar4> f(s->bond->getForceArray(), access_location::host, access_mode::read);
+    memcpy(force4, f.data, sizeof(Scalar4) * N);
+    if (virial6)
+        {
+        unsigned int pitch = s->bond->getVirialArray().getPitch();
+        ArrayHandle<Scalar> v(s->bond->getVirialArray(), access_location::host, access_mode::read);
+        for (unsigned int k = 0; k < 6; k++)
+            memcpy(virial6 + k * N, v.data + k * pitch, sizeof(Scalar) * N);
+        }
     }
 
 //! System::run(nsteps): prepRun at the current step, then updaters + integrator->update per step

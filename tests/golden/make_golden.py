@@ -18,7 +18,53 @@ def csr(s):
     return n, h, np.concatenate([nl[h[i]:h[i] + n[i]] for i in range(len(n))]) if len(n) else nl[:0]
 
 
+def kremer_grest():
+    """(8) Kremer-Grest bead-spring chains (WCA pair + FENE bonds, bond exclusions): 216 beads in chains of 8, melted with
+    the reference; filtered neighbor list, per-ForceCompute forces / virials, 40-step NVE and Langevin trajectories"""
+    kg = workloads.KG_PARAMS
+    pos, vel, L, bonds = workloads.polymer_lattice(6, 8, rho=kg["rho"], kT=kg["kT"], seed=3)
+
+    def make(p, v, img=None):
+        q = ref.RefSystem(p, (L, L, L), vel4=v, image=img, n_bond_types=1)
+        q.set_bonds(bonds)
+        q.setup_lj(r_cut=kg["r_cut"], r_buff=0.4, full=True, shift_mode=1)
+        q.setup_fene(k=kg["fene_k"], r0=kg["fene_r0"])
+        q.exclusions_from_bonds(True)
+        return q
+
+    s = make(pos, vel)
+    s.setup_integrator(0.005)
+    s.add_langevin(kg["kT"], 11)
+    s.run(400)
+    st = s.particles()
+    q = make(st["pos"], st["vel"])
+    q.set_virial(True)
+    q.compute_forces(0)
+    n, h, flat = csr(q)
+    fp, vp = q.force_component(0, True)
+    fb, vb = q.force_component(1, True)
+    res = dict(pos=st["pos"], vel=st["vel"], image=st["image"], L=L, bonds=bonds, n_neigh=n, head=h, nlist=flat,
+               force_pair=fp, virial_pair=vp, force_bond=fb, virial_bond=vb)
+    for method in ("nve", "langevin"):
+        q = make(st["pos"], st["vel"], st["image"])
+        q.set_virial(True)
+        q.setup_integrator(0.005)
+        q.add_nve() if method == "nve" else q.add_langevin(kg["kT"], 4)
+        q.run(40)
+        p = q.particles()
+        th = q.thermo()
+        for k in ("pos", "vel", "accel", "image"):
+            res["%s_%s" % (method, k)] = p[k]
+        res[method + "_updates"] = q.nlist_stats()["updates"]
+        res[method + "_thermo"] = np.array([th[k] for k in ("ke", "pe", "T", "P", "ndof")])
+    np.savez_compressed(os.path.join(HERE, "kremer_grest.npz"), **res)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "kg":
+        kremer_grest()
+        return
+    kremer_grest()
     out = {}
     # (1) Saru stream: (tag, timestep, seed) triples
     rng = np.random.default_rng(0)

@@ -120,3 +120,65 @@ def check_trajectories(make, bit_exact, pos_tol=2e-4, vel_tol=2e-3):
         want = g["thermo"]
         for k, w in zip(("ke", "pe", "T", "P", "ndof"), want):
             assert abs(th[k] - w) <= 2e-4 * abs(w), (method, k, th[k], w)
+
+
+def make_kg(make, g, vel=True, image=False):
+    """Kremer-Grest system of the kremer_grest fixture on implementation `make` (WCA + FENE + bond exclusions)."""
+    L = float(g["L"])
+    rc = 2.0 ** (1.0 / 6.0)
+    s = make(g["pos"], (L, L, L), 1, vel=g["vel"] if vel else None, image=g["image"] if image else None, n_bond_types=1)
+    s.set_bonds(g["bonds"])
+    s.setup_lj(r_cut=rc, r_buff=0.4, shift_mode=1)
+    s.setup_fene(k=30.0, r0=1.5)
+    s.exclusions_from_bonds(True)
+    return s
+
+
+def _rel(a, b):
+    scale = np.maximum(np.abs(b), np.abs(b).mean())
+    return (np.abs(a - b) / scale).max()
+
+
+def check_kremer_grest(make, rtol, bit_exact=False, traj_bit_exact=False, pos_tol=2e-4, vel_tol=2e-3):
+    """filtered neighbor list (exact, incl. order), per-ForceCompute forces / virials, net force, 40-step trajectories"""
+    g = load("kremer_grest")
+    s = make_kg(make, g)
+    s.set_virial(True)
+    s.compute_forces(0)
+    _cmp_nlist(s, g, True)
+    eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+    fnet, vnet = s.forces()
+    for which, name in ((0, "pair"), (1, "bond")):
+        f, v = s.force_component(which, True)
+        fr, vr = g["force_" + name], g["virial_" + name]
+        if bit_exact:
+            assert eq(f[:, :3], fr[:, :3]) and eq(v, vr), name
+            # the energy goes through logf: allow the last bit
+            assert np.abs(f[:, 3] - fr[:, 3]).max() <= 4e-6 * np.abs(fr[:, 3]).max(), name
+            continue
+        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+        assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, name
+        assert _rel(f[:, 3], fr[:, 3]) < rtol, name
+        assert _rel(v, vr) < rtol, name
+    want = g["force_pair"] + g["force_bond"]
+    fscale = np.maximum(np.linalg.norm(want[:, :3], axis=1, keepdims=True), np.abs(want[:, :3]).mean())
+    assert (np.abs(want[:, :3] - fnet[:, :3]) / fscale).max() < max(rtol, 1e-6)
+    assert _rel(vnet, g["virial_pair"] + g["virial_bond"]) < max(rtol, 1e-6)
+    for method in ("nve", "langevin"):
+        s = make_kg(make, g, image=True)
+        s.set_virial(True)
+        s.setup_integrator(0.005)
+        s.add_nve() if method == "nve" else s.add_langevin(1.0, 4)
+        s.run(40)
+        p = s.particles()
+        order = np.argsort(p["tag"]) if "tag" in p else slice(None)
+        if traj_bit_exact:
+            for k in ("pos", "vel", "accel", "image"):
+                assert eq(p[k][order], g["%s_%s" % (method, k)]), (method, k)
+        else:
+            assert np.abs(p["pos"][order][:, :3] - g[method + "_pos"][:, :3]).max() < pos_tol, method
+            assert np.abs(p["vel"][order][:, :3] - g[method + "_vel"][:, :3]).max() < vel_tol, method
+            assert np.array_equal(p["image"][order], g[method + "_image"]), method
+        th = s.thermo()
+        for k, w in zip(("ke", "pe", "T", "P", "ndof"), g[method + "_thermo"]):
+            assert abs(th[k] - w) <= 2e-4 * abs(w), (method, k, th[k], w)

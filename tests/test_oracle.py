@@ -12,8 +12,8 @@ from oracle import oracle_c, ref
 pytestmark = pytest.mark.skipif(not oracle_c.available(), reason="oracle/_ref/liboracle.so not built (run build())")
 
 
-def make(pos, box, ntypes, vel=None, image=None):
-    return oracle_c.OracleSystem(pos, box, ntypes=ntypes, vel4=vel, image=image)
+def make(pos, box, ntypes, vel=None, image=None, n_bond_types=0):
+    return oracle_c.OracleSystem(pos, box, ntypes=ntypes, vel4=vel, image=image, n_bond_types=n_bond_types)
 
 
 def test_saru_golden():
@@ -129,3 +129,52 @@ def test_cell_list_matches_reference():
     for c in range(len(a["cell_size"])):
         n = a["cell_size"][c]
         assert np.array_equal(a["xyzf"][c, :n].view(np.uint32), b["xyzf"][c, :n].view(np.uint32))
+
+
+def test_kremer_grest_golden_bit_exact():
+    """WCA + FENE + bond exclusions: filtered list, per-ForceCompute forces, trajectories"""
+    G.check_kremer_grest(make, 0.0, bit_exact=True, traj_bit_exact=True)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+@pytest.mark.parametrize("kind,excl", [("fene", True), ("harmonic", True), ("harmonic", False)])
+def test_bonded_restatement_matches_reference_bitwise(kind, excl):
+    """fresh inputs: two bond types, branched bonds (up to 3 per bead), exclusions on / off, 120 Langevin steps"""
+    pos, vel, L, bonds = workloads.polymer_lattice(8, 16, rho=0.85, kT=1.0, seed=9)
+    rng = np.random.default_rng(5)
+    types = rng.integers(0, 2, len(bonds)).astype(np.uint32)
+    # a few cross links between lattice neighbors of different chains (third bond on some beads)
+    extra = np.array([[i, i + 31] for i in range(0, 400, 40)], np.uint32)
+    d = pos[extra[:, 1], :3] - pos[extra[:, 0], :3]
+    d -= L * np.round(d / L)
+    extra = extra[np.linalg.norm(d, axis=1) < 1.2]
+    assert len(extra) > 0
+    bonds2 = np.concatenate([bonds, extra])
+    types2 = np.concatenate([types, np.ones(len(extra), np.uint32)])
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (L, L, L), vel4=vel, n_bond_types=2)
+        s.set_bonds(bonds2, types2)
+        s.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, full=True, shift_mode=1)
+        if kind == "fene":
+            s.setup_fene(k=[30.0, 25.0], r0=[1.5, 1.6])
+        else:
+            s.setup_harmonic(k=[300.0, 200.0], r0=[1.0, 1.05])
+        s.exclusions_from_bonds(excl)
+        s.set_virial(True)
+        s.setup_integrator(0.004)
+        s.add_langevin(1.0, 3)
+        s.run(120)
+        s.compute_forces(s.timestep)
+        outs.append((s.particles(), s.nlist(), s.nlist_stats()["updates"], s.force_component(1, True),
+                     s.force_component(0, True)))
+    (pa, na, ua, ba, fa), (pb, nb, ub, bb, fb) = outs
+    for k in ("pos", "vel", "accel", "image"):
+        assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
+    assert ua == ub and ua > 2
+    assert np.array_equal(na[0], nb[0]) and np.array_equal(na[1], nb[1])
+    for i in range(len(na[0])):
+        assert np.array_equal(na[2][na[1][i]:na[1][i] + na[0][i]], nb[2][nb[1][i]:nb[1][i] + nb[0][i]])
+    assert np.array_equal(ba[0][:, :3].view(np.uint32), bb[0][:, :3].view(np.uint32))
+    assert np.array_equal(ba[1].view(np.uint32), bb[1].view(np.uint32))
+    assert np.array_equal(fa[0][:, :3].view(np.uint32), fb[0][:, :3].view(np.uint32))
