@@ -29,7 +29,11 @@ WORKLOADS = {
     "lj64k": (40, 0.2, 1.2, "LJ liquid 64,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
     "lj1m": (100, 0.2, 1.2, "LJ liquid 1,000,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
     "lj8m": (200, 0.2, 1.2, "LJ liquid 8,000,000 particles, rho 0.2, r_cut 3.0, r_buff 0.4, NVE dt 0.005"),
+    # BASELINE configs[3]: 10,000 chains x 100 beads, WCA (LJ r_cut 2^(1/6), shift) + FENE (K 30, r0 1.5), bond exclusions
+    "kg1m": (100, 0.85, 1.0, "Kremer-Grest polymer melt 1,000,000 beads (10,000 x 100), rho 0.85, WCA + FENE, r_buff 0.4, "
+                             "NVE dt 0.005"),
 }
+KG_CHAIN = 100
 BYTES_PER_PARTICLE_STEP = 420.0   # SURVEY 8(d) planning figure (NVE, fused net force, amortised rebuild)
 FLOPS_PER_PARTICLE_STEP = 1800.0
 PAIR_BYTES_PER_PARTICLE = 172.0   # pair kernel: pos_i 16 + n_neigh 4 + head 4 + nlist 4*32.9 + force 16
@@ -95,13 +99,33 @@ def _lj_snapshot(workload):
     return workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
 
 
+def _snapshot(workload):
+    """(pos4, vel4, L, bonds or None)"""
+    from hoomd_b200 import workloads
+    n_side, rho, kT, _ = WORKLOADS[workload]
+    if workload.startswith("kg"):
+        return workloads.polymer_lattice(n_side, KG_CHAIN, rho=rho, kT=kT, seed=42)
+    return _lj_snapshot(workload) + (None,)
+
+
+def setup_forces(s, workload, bonds, **kw):
+    """md.nlist.cell + the workload's force field on any implementation (hoomd_b200.System, RefSystem, OracleSystem)"""
+    if workload.startswith("kg"):
+        s.set_bonds(bonds)
+        s.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, shift_mode=1, **kw)
+        s.setup_fene(k=30.0, r0=1.5)
+        s.exclusions_from_bonds(True)
+    else:
+        s.setup_lj(r_cut=3.0, r_buff=0.4, **kw)
+
+
 def make_state(workload, rank=0):
     """Lattice start + Langevin equilibration ON THE GPU ENGINE (not timed); returns host arrays + box length."""
     import hoomd_b200
     _, _, kT, _ = WORKLOADS[workload]
-    pos, vel, L = _lj_snapshot(workload)
+    pos, vel, L, bonds = _snapshot(workload)
     s = hoomd_b200.System(pos, (L, L, L), vel4=vel)
-    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    setup_forces(s, workload, bonds)
     s.setup_integrator(0.005)
     s.add_langevin(kT, 42)
     s.set_sorter(300)
@@ -109,13 +133,17 @@ def make_state(workload, rank=0):
     s.run(EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 2000))
     p = s.particles()
     s.close()
+    # back to TAG order: the bond table names particles by tag (= index of a freshly created system)
+    order = np.argsort(p["tag"], kind="stable")
+    p = {k: np.ascontiguousarray(v[order]) for k, v in p.items()}
+    p["bonds"] = bonds
     return p, L
 
 
-def new_system(state, L, device=0):
+def new_system(state, L, device=0, workload="lj64k"):
     import hoomd_b200
     s = hoomd_b200.System(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], device=device)
-    s.setup_lj(r_cut=3.0, r_buff=0.4)
+    setup_forces(s, workload, state.get("bonds"))
     s.setup_integrator(0.005)
     s.add_nve()
     s.set_sorter(300)  # hoomd.update.sort default period on the GPU (hoomd/update.py:258-263)
@@ -160,17 +188,19 @@ def run_reference(args):
     if have_gpu:
         state, L = make_state(workload)  # same equilibrated liquid as the CUDA arm (equilibration is not timed)
     else:
-        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
-        state = dict(pos=pos, vel=vel, image=np.zeros((len(pos), 3), np.int32))
+        pos, vel, L, bonds = _snapshot(workload)
+        state = dict(pos=pos, vel=vel, image=np.zeros((len(pos), 3), np.int32), bonds=bonds)
+    nbt = 1 if state.get("bonds") is not None else 0
     if ref.available():
-        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"])
-        s.setup_lj(r_cut=3.0, r_buff=0.4, full=False)  # the CPU md.pair.lj default: half list + Newton's third law
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt)
+        setup_forces(s, workload, state.get("bonds"), full=False)  # CPU md.pair.lj default: half list + Newton's 3rd law
         kind, cores = "reference", 1
         s.set_sorter(100)  # hoomd.update.sort default period on the CPU
     else:
         cores = os.cpu_count() or 1
-        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores)
-        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores,
+                                  n_bond_types=nbt)
+        setup_forces(s, workload, state.get("bonds"))
         kind = "port"
     s.setup_integrator(0.005)
     s.add_nve()
@@ -197,18 +227,20 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def cpu_baseline(state, L, budget_s=15.0):
+def cpu_baseline(state, L, budget_s=15.0, workload="lj64k"):
     """bounded sample of the same workload on the host cores with the reference's own CPU classes"""
     from oracle import ref, oracle_c
     N = len(state["pos"])
+    nbt = 1 if state.get("bonds") is not None else 0
     if ref.available():
-        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"])
-        s.setup_lj(r_cut=3.0, r_buff=0.4, full=False)
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt)
+        setup_forces(s, workload, state.get("bonds"), full=False)
         kind, cores = "reference", 1
     elif oracle_c.available():
         cores = os.cpu_count() or 1
-        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores)
-        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores,
+                                  n_bond_types=nbt)
+        setup_forces(s, workload, state.get("bonds"))
         kind = "port"
     else:
         return None
@@ -268,7 +300,7 @@ def main():
 
     if world == 1:
         state, L = make_state(workload, rank)
-        s = new_system(state, L, device=local_rank)
+        s = new_system(state, L, device=local_rank, workload=workload)
     else:
         state = None
         s, L = new_domain_system(workload, local_rank)
@@ -318,9 +350,14 @@ def main():
     n_neigh = s.nlist(counts_only=True)[0][:n_local]
     nbar = float(n_neigh.mean())
     step_bytes = (124.0 + 4.0 * nbar) * n_local
+    if workload.startswith("kg"):
+        # + k_bond_forces (pos 16 + tag 4 + n_bonds 4 + 2 bonds x (entry 8 + rtag 4) + force 16 = 64) and the 16 B read of
+        # that force by k_md_step; time_kernel(2) launches both per step
+        step_bytes += 80.0 * n_local
     step_flops = (40.0 * nbar + 55.0) * n_local
     achieved = step_bytes / (step_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_md_step<EvaluatorPairLJ> (force + step two + step one + distance check)",
+    roofline = {"bound": "hbm", "kernel": "k_md_step<EvaluatorPairLJ> (force + step two + step one + distance check)"
+                + (" + k_bond_forces<EvaluatorBondFENE>" if workload.startswith("kg") else ""),
                 "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "peak_source": peak_src, "kernel_ms": step_ms, "algorithmic_bytes_per_launch": step_bytes,
                 "mean_neighbors": nbar,
@@ -353,7 +390,7 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(state, L)
+        cpu = cpu_baseline(state, L, workload=workload)
 
     # 1-GPU reference point of the multi-GPU workload (BASELINE configs[4]: parallel efficiency = TPS_n / (n * TPS_1)
     # with TPS_1 measured at 8M on one GPU), short run, reported beside the headline

@@ -17,7 +17,8 @@ An unmodified HOOMD-blue 2.3 job script of the shape in the reference README (RE
 runs after ``import hoomd_b200.script as hoomd`` (or ``hoomd_b200.script.install()``, which registers the modules as
 ``hoomd`` / ``hoomd.md``).  Same names, argument meaning and error behaviour as hoomd/md/nlist.py:555,
 hoomd/md/pair.py:358-445,579-609, hoomd/md/integrate.py:49,729,844, hoomd/__init__.py (run), hoomd/init.py:32-93,
-hoomd/data.py (make_snapshot / take_snapshot), hoomd/update.py:239-263 (sort).  Like the reference, commands only record
+hoomd/data.py (make_snapshot / take_snapshot, snapshot.bonds, system.bonds.add), hoomd/md/bond.py:236-372 (bond.fene,
+bond.harmonic), hoomd/md/nlist.py:213-285 (reset_exclusions), hoomd/update.py:239-263 (sort).  Like the reference, commands only record
 parameters; the C++/CUDA objects are (re)configured when ``run()`` starts (hoomd/md/nlist.py:80-109 update_rcut,
 hoomd/md/pair.py:430-445 update_coeffs).  Only the path of SURVEY.md section 8 is covered: one pair force (lj), one
 integration method on group.all(), orthorhombic boxes.
@@ -99,10 +100,27 @@ class _ParticleSnapshot:
         self.image = np.zeros((N, 3), np.int32)
 
 
+class _BondSnapshot:
+    """snapshot.bonds (hoomd/data.py: N, types, typeid, group, resize)"""
+
+    def __init__(self, types=()):
+        self.types = list(types)
+        self.resize(0)
+
+    def resize(self, n):
+        old_t, old_g = getattr(self, "typeid", np.zeros(0, np.uint32)), getattr(self, "group", np.zeros((0, 2), np.uint32))
+        self.N = int(n)
+        self.typeid = np.zeros(self.N, np.uint32)
+        self.group = np.zeros((self.N, 2), np.uint32)
+        k = min(len(old_t), self.N)
+        self.typeid[:k], self.group[:k] = old_t[:k], old_g[:k]
+
+
 class _Snapshot:
-    def __init__(self, N, box, particle_types):
+    def __init__(self, N, box, particle_types, bond_types=()):
         self.box = box
         self.particles = _ParticleSnapshot(N, particle_types)
+        self.bonds = _BondSnapshot(bond_types)
 
 
 class _ParticleTypes:
@@ -117,6 +135,27 @@ class _ParticleTypes:
 
     def __iter__(self):
         return iter(self._names)
+
+
+class _Bonds:
+    """system.bonds (hoomd/data.py bond_data): len(), add(type, a, b)"""
+
+    def __init__(self, sysdata):
+        self._s = sysdata
+
+    def __len__(self):
+        return len(self._s.bond_group)
+
+    def add(self, type, a, b):
+        s = self._s
+        if type not in s.bond_types:
+            raise RuntimeError("Error adding bond: unknown bond type " + str(type))
+        if max(int(a), int(b)) >= s.N:
+            raise RuntimeError("Particle tag out of bounds when attempting to add bond")
+        s.bond_group = np.concatenate([s.bond_group, np.array([[a, b]], np.uint32)])
+        s.bond_typeid = np.concatenate([s.bond_typeid, np.array([s.bond_types.index(type)], np.uint32)])
+        context.current.engine_dirty = True
+        return len(s.bond_group) - 1
 
 
 class _Particles:
@@ -144,6 +183,11 @@ class _SystemData:
         self.vel4[:, 3] = p.mass
         self.image = np.array(p.image, np.int32)
         self.particles = _Particles(self)
+        b = getattr(snapshot, "bonds", None) or _BondSnapshot()
+        self.bond_types = list(b.types)
+        self.bond_group = np.array(b.group, np.uint32).reshape(-1, 2)
+        self.bond_typeid = np.array(b.typeid, np.uint32)
+        self.bonds = _Bonds(self)
 
     def take_snapshot(self, **kwargs):
         """current state in TAG order (hoomd/data.py take_snapshot)"""
@@ -155,7 +199,10 @@ class _SystemData:
             accel = st["accel"][order]
         else:
             accel = np.zeros((self.N, 3), np.float32)
-        snap = _Snapshot(self.N, self.box, self.types)
+        snap = _Snapshot(self.N, self.box, self.types, self.bond_types)
+        snap.bonds.resize(len(self.bond_group))
+        snap.bonds.group[:] = self.bond_group
+        snap.bonds.typeid[:] = self.bond_typeid
         q = snap.particles
         q.position[:] = self.pos4[:, :3]
         q.velocity[:] = self.vel4[:, :3]
@@ -172,7 +219,8 @@ class _SystemData:
 
 data = types.ModuleType("hoomd.data")
 data.boxdim = _BoxDim
-data.make_snapshot = lambda N, box, particle_types=("A",), **kw: _Snapshot(N, box, particle_types)
+data.make_snapshot = lambda N, box, particle_types=("A",), bond_types=(), **kw: _Snapshot(N, box, particle_types,
+                                                                                          bond_types)
 
 
 def _require_context():
@@ -268,6 +316,7 @@ class _Cell:
         if context.current.system is None:
             raise RuntimeError("Cannot create neighbor list before initialization")
         self.r_buff, self.check_period, self.dist_check = float(r_buff), int(check_period), bool(dist_check)
+        self.exclusions = ["bond", "body"]  # the md.nlist default (hoomd/md/nlist.py:104-110)
         self.subscribers = []
         context.current.neighbor_lists.append(self)
         context.current.engine_dirty = True
@@ -279,6 +328,16 @@ class _Cell:
             self.check_period = int(check_period)
         if dist_check is not None:
             self.dist_check = bool(dist_check)
+        context.current.engine_dirty = True
+
+    def reset_exclusions(self, exclusions=None):
+        """nlist.reset_exclusions (hoomd/md/nlist.py:213-285): 'bond' and 'body' are honoured here; the angle / dihedral /
+        1-3 / 1-4 kinds belong to force fields outside this path"""
+        exclusions = list(exclusions or [])
+        for e in exclusions:
+            if e not in ("bond", "body", "constraint", "pair"):
+                raise RuntimeError("hoomd_b200: exclusion type '%s' is not supported on this path" % e)
+        self.exclusions = exclusions
         context.current.engine_dirty = True
 
     def query_update_period(self):
@@ -378,6 +437,69 @@ class _LJ:
 
 
 md.pair.lj = _LJ
+
+
+class _BondCoeff:
+    """bond.coeff (hoomd/md/bond.py:22-164): per-bond-type table"""
+
+    def __init__(self):
+        self.values = {}
+
+    def set(self, type, **coeffs):
+        for t in ([type] if isinstance(type, str) else list(type)):
+            self.values.setdefault(t, {}).update(coeffs)
+        if context.current is not None:
+            context.current.engine_dirty = True
+
+    def table(self, bond_types, required):
+        out = {k: [] for k in required}
+        for t in bond_types:
+            if t not in self.values:
+                sys.stderr.write("**ERROR**: Bond type %s not found in bond coeff\n" % t)
+                raise RuntimeError("Error updating bond coefficients")
+            for k in required:
+                if k not in self.values[t]:
+                    sys.stderr.write("**ERROR**: Bond type %s is missing required coefficient %s\n" % (t, k))
+                    raise RuntimeError("Error updating bond coefficients")
+                out[k].append(float(self.values[t][k]))
+        return out
+
+
+class _Bond:
+    kind, required_coeffs = None, []
+
+    def __init__(self, name=None):
+        _require_context()
+        if context.current.system is None:
+            raise RuntimeError("Cannot create force before initialization")
+        if len(context.current.system.bonds) == 0:
+            sys.stderr.write("**ERROR**: No bonds are defined.\n")
+            raise RuntimeError("Error creating bond forces")  # hoomd/md/bond.py:348-351
+        if any(isinstance(f, _Bond) for f in context.current.forces):
+            raise RuntimeError("hoomd_b200: one bond force per system in this round")
+        self.bond_coeff = _BondCoeff()
+        self.enabled = True
+        context.current.forces.append(self)
+        context.current.engine_dirty = True
+
+    def get_energy(self, group=None):
+        f, _ = context.current.engine.force_component(1)
+        return float(f[:, 3].astype(np.float64).sum())
+
+
+class _FENE(_Bond):
+    """md.bond.fene (hoomd/md/bond.py:308-372)"""
+    kind, required_coeffs = "fene", ["k", "r0", "epsilon", "sigma"]
+
+
+class _Harmonic(_Bond):
+    """md.bond.harmonic (hoomd/md/bond.py:236-296)"""
+    kind, required_coeffs = "harmonic", ["k", "r0"]
+
+
+md.bond = types.ModuleType("hoomd.md.bond")
+md.bond.fene = _FENE
+md.bond.harmonic = _Harmonic
 
 
 class _ModeStandard:
@@ -509,6 +631,16 @@ def _configure_engine():
     eng.setup_lj(r_cut=t["r_cut"], epsilon=t["epsilon"], sigma=t["sigma"], alpha=t["alpha"], r_buff=lj.nlist.r_buff,
                  check_period=lj.nlist.check_period, shift_mode=lj.shift_mode,
                  r_on=t["r_on"] if lj.shift_mode == 2 else None)
+    bonds = [f for f in ctx.forces if isinstance(f, _Bond) and f.enabled]
+    if len(sysd.bond_group):
+        eng.set_bonds(sysd.bond_group, sysd.bond_typeid, n_bond_types=len(sysd.bond_types))
+        if bonds:
+            t = bonds[0].bond_coeff.table(sysd.bond_types, bonds[0].required_coeffs)
+            if bonds[0].kind == "fene":
+                eng.setup_fene(k=t["k"], r0=t["r0"], epsilon=t["epsilon"], sigma=t["sigma"])
+            else:
+                eng.setup_harmonic(k=t["k"], r0=t["r0"])
+        eng.exclusions_from_bonds("bond" in lj.nlist.exclusions)
     eng.set_virial(need_virial)
     eng.setup_integrator(ctx.integrator.dt)
     m = methods[0]
@@ -563,6 +695,6 @@ def install():
     for name, mod in (("context", context), ("init", init), ("lattice", lattice), ("data", data), ("group", group),
                       ("update", update), ("md", md), ("analyze", analyze)):
         sys.modules["hoomd." + name] = mod
-    for name, mod in (("nlist", md.nlist), ("pair", md.pair), ("integrate", md.integrate)):
+    for name, mod in (("nlist", md.nlist), ("pair", md.pair), ("integrate", md.integrate), ("bond", md.bond)):
         sys.modules["hoomd.md." + name] = mod
     return me

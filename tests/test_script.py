@@ -113,3 +113,80 @@ def test_readme_lj_runs_unmodified_and_matches_reference():
     log = hoomd.analyze.log(filename=None, quantities=["temperature", "potential_energy"], period=10)
     hoomd.run(20)
     assert len(log.rows) == 2 and 0.0 < log.rows[0][1] < 5.0
+
+
+KG_SCRIPT = """
+import hoomd
+from hoomd import md
+hoomd.context.initialize()
+snap = hoomd.data.make_snapshot(N=N, box=hoomd.data.boxdim(L=L), particle_types=['A'], bond_types=['polymer'])
+snap.particles.position[:] = POS
+snap.particles.velocity[:] = VEL
+snap.bonds.resize(len(BONDS))
+snap.bonds.group[:] = BONDS
+system = hoomd.init.read_snapshot(snap)
+nl = md.nlist.cell()
+wca = md.pair.lj(r_cut=2**(1.0/6.0), nlist=nl)
+wca.pair_coeff.set('A', 'A', epsilon=1.0, sigma=1.0)
+wca.set_params(mode='shift')
+fene = md.bond.fene()
+fene.bond_coeff.set('polymer', k=30.0, r0=1.5, sigma=1.0, epsilon=1.0)
+md.integrate.mode_standard(dt=0.005)
+md.integrate.nve(group=hoomd.group.all())
+hoomd.run(NSTEPS)
+"""
+
+
+def test_bond_surface_without_gpu():
+    hoomd = _fresh()
+    snap = hoomd.data.make_snapshot(N=4, box=hoomd.data.boxdim(L=10), particle_types=["A"], bond_types=["polymer"])
+    hoomd.init.read_snapshot(snap)
+    with pytest.raises(RuntimeError):
+        hoomd.md.bond.fene()  # "No bonds are defined." (hoomd/md/bond.py:348-351)
+    sysd = hoomd.context.current.system
+    assert sysd.bonds.add("polymer", 0, 1) == 0 and len(sysd.bonds) == 1
+    with pytest.raises(RuntimeError):
+        sysd.bonds.add("bogus", 1, 2)
+    fene = hoomd.md.bond.fene()
+    with pytest.raises(RuntimeError):
+        fene.bond_coeff.table(["polymer"], fene.required_coeffs)  # coefficients not set
+    fene.bond_coeff.set("polymer", k=30.0, r0=1.5, sigma=1.0, epsilon=1.0)
+    assert fene.bond_coeff.table(["polymer"], fene.required_coeffs)["k"] == [30.0]
+    nl = hoomd.md.nlist.cell()
+    assert nl.exclusions == ["bond", "body"]
+    nl.reset_exclusions([])
+    assert nl.exclusions == []
+    with pytest.raises(RuntimeError):
+        nl.reset_exclusions(["1-4"])
+    s2 = sysd.take_snapshot()
+    assert s2.bonds.N == 1 and list(s2.bonds.group[0]) == [0, 1] and s2.bonds.types == ["polymer"]
+
+
+@pytest.mark.gpu
+def test_kremer_grest_script_matches_reference():
+    """a Kremer-Grest job script (snapshot with bonds, WCA via pair.lj shift, bond.fene, default bond exclusions, NVE)"""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    from hoomd_b200 import workloads
+    hoomd = _fresh()
+    pos, vel, L, bonds = workloads.polymer_lattice(8, 16, rho=0.85, kT=1.0, seed=21)
+    nsteps = 80
+    ns = dict(N=len(pos), L=L, POS=pos[:, :3], VEL=vel[:, :3], BONDS=bonds, NSTEPS=nsteps)
+    exec(KG_SCRIPT, ns)
+    snap = hoomd.context.current.system.take_snapshot()
+    r = R.RefSystem(pos, (L, L, L), vel4=vel, n_bond_types=1)
+    r.set_bonds(bonds)
+    r.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, full=True, shift_mode=1)
+    r.setup_fene(k=30.0, r0=1.5)
+    r.exclusions_from_bonds(True)
+    r.setup_integrator(0.005)
+    r.add_nve()
+    r.set_sorter(300)
+    r.run(nsteps)
+    a = r.particles()
+    order = np.argsort(a["tag"])
+    assert np.abs(a["pos"][order][:, :3] - snap.particles.position).max() < 2e-4
+    assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
+    assert snap.bonds.N == len(bonds)
+    assert abs(ns["fene"].get_energy() - 20.0 * len(bonds)) < 5.0 * len(bonds)
