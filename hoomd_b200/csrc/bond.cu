@@ -160,7 +160,9 @@ static cudaError_t bond_forces(const b200_bond_args* a, const float* d_params, u
 // ---- NeighborList::filterNlist ------------------------------------------------------------------------------------------
 constexpr int FILTER_MAX_EX = 8; // exclusions held in registers per pass (the reference's FILTER_BATCH_SIZE is 4)
 
-template<bool TAGKEYED>
+// G lanes per row (G = 8: four rows per warp for short rows such as the ~12-entry rows of a bead-spring melt; G = 32: one
+// row per warp).  Every lane of the warp takes part in every ballot; a row's lanes look at their own G-bit segment.
+template<bool TAGKEYED, int G>
 __global__ void __launch_bounds__(256) k_nlist_filter(unsigned int* __restrict__ n_neigh, unsigned int* __restrict__ nlist,
                                                       const unsigned int* __restrict__ head_list,
                                                       const unsigned int* __restrict__ n_ex,
@@ -171,28 +173,39 @@ __global__ void __launch_bounds__(256) k_nlist_filter(unsigned int* __restrict__
     {
     if (enable && !*enable) return;
     const unsigned int lane = threadIdx.x & 31u;
-    const unsigned int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (i >= N) return;
-    const unsigned int row = TAGKEYED ? tag[i] : i;
-    const unsigned int nex = n_ex[row];
-    if (ex_start >= nex) return;
+    const unsigned int sub = lane % G, seg = lane / G;
+    const unsigned int i = (blockIdx.x * blockDim.x + threadIdx.x) / G;
+    const bool live = i < N;
+    unsigned int row = 0, nex = 0;
+    if (live)
+        {
+        row = TAGKEYED ? tag[i] : i;
+        nex = n_ex[row];
+        }
+    const bool work = live && ex_start < nex;
+    if (!__any_sync(0xffffffffu, work)) return;
     unsigned int ex[FILTER_MAX_EX];
 #pragma unroll
     for (int k = 0; k < FILTER_MAX_EX; k++)
         {
         ex[k] = 0xffffffffu;
-        if (ex_start + k < nex)
+        if (work && ex_start + k < nex)
             {
             const unsigned int e = ex_list[(size_t)(ex_start + k) * ex_pitch + row];
             ex[k] = TAGKEYED ? rtag[e] : e;
             }
         }
-    const unsigned int head = head_list[i];
-    const unsigned int n = n_neigh[i];
+    const unsigned int head = work ? head_list[i] : 0u;
+    const unsigned int n = work ? n_neigh[i] : 0u;
+    unsigned int nmax = n;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, o));
+    const unsigned int segmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (seg * G));
+    const unsigned int below = segmask & ((1u << lane) - 1u);
     unsigned int out = 0;
-    for (unsigned int base = 0; base < n; base += 32)
+    for (unsigned int base = 0; base < nmax; base += G)
         {
-        const unsigned int k = base + lane;
+        const unsigned int k = base + sub;
         unsigned int j = 0xffffffffu;
         bool keep = false;
         if (k < n)
@@ -207,30 +220,93 @@ __global__ void __launch_bounds__(256) k_nlist_filter(unsigned int* __restrict__
         // at positions <= the chunk's own entries, which are not read again
         if (keep)
             {
-            const unsigned int dst = out + __popc(mask & ((1u << lane) - 1u));
+            const unsigned int dst = out + __popc(mask & below);
             if (dst != k) nlist[head + dst] = j;
             }
-        out += __popc(mask);
+        out += __popc(mask & segmask);
         }
-    if (lane == 0 && out != n) n_neigh[i] = out;
+    if (work && sub == 0 && out != n) n_neigh[i] = out;
     }
 
+template<int G>
+static void filter_launch(unsigned int* n_neigh, unsigned int* nlist, const unsigned int* head_list,
+                          const unsigned int* n_ex, const unsigned int* ex_list, unsigned int ex_pitch, unsigned int start,
+                          const unsigned int* tag, const unsigned int* rtag, unsigned int N, const unsigned int* enable,
+                          cudaStream_t stream)
+    {
+    const unsigned int grid = (unsigned int)(((size_t)N * G + 255) / 256);
+    if (tag)
+        k_nlist_filter<true, G><<<grid, 256, 0, stream>>>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, tag, rtag, N,
+                                                          start, enable);
+    else
+        k_nlist_filter<false, G><<<grid, 256, 0, stream>>>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, nullptr,
+                                                           nullptr, N, start, enable);
+    }
+
+// row_hint: typical row length (Nmax); rows up to ~32 entries take 8 lanes each
 cudaError_t launch_nlist_filter(unsigned int* n_neigh, unsigned int* nlist, const unsigned int* head_list,
                                 const unsigned int* n_ex, const unsigned int* ex_list, unsigned int ex_pitch,
                                 unsigned int max_ex, const unsigned int* tag, const unsigned int* rtag, unsigned int N,
-                                const unsigned int* enable, cudaStream_t stream)
+                                const unsigned int* enable, cudaStream_t stream, unsigned int row_hint)
     {
     if (N == 0) return cudaSuccess;
-    const unsigned int grid = (unsigned int)(((size_t)N * 32 + 255) / 256);
     for (unsigned int start = 0; start < max_ex; start += FILTER_MAX_EX)
         {
-        if (tag)
-            k_nlist_filter<true><<<grid, 256, 0, stream>>>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, tag, rtag, N,
-                                                           start, enable);
+        if (row_hint && row_hint <= 32)
+            filter_launch<8>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, start, tag, rtag, N, enable, stream);
         else
-            k_nlist_filter<false><<<grid, 256, 0, stream>>>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, nullptr,
-                                                            nullptr, N, start, enable);
+            filter_launch<32>(n_neigh, nlist, head_list, n_ex, ex_list, ex_pitch, start, tag, rtag, N, enable, stream);
         }
+    return cudaGetLastError();
+    }
+
+// ---- index-keyed copies of the tag-keyed tables ----------------------------------------------------------------------------
+// What BondedGroupData::rebuildGPUTable / NeighborList::updateExListIdx do after a particle sort: row of particle i =
+// row of tag[i] with every partner tag translated through rtag.  One launch per sort (every 300 steps) buys the per-step
+// bond kernel and the per-rebuild filter a two-level load chain (row -> partner position) instead of four
+// (tag -> row -> rtag -> position): k_bond_forces 36 -> see profiles/ at 1M beads.
+__global__ void __launch_bounds__(256) k_rekey_tables(unsigned int* __restrict__ bond_n_idx, uint2* __restrict__ bond_list_idx,
+                                                      const unsigned int* __restrict__ bond_n,
+                                                      const uint2* __restrict__ bond_list, unsigned int bond_max,
+                                                      unsigned int* __restrict__ ex_n_idx,
+                                                      unsigned int* __restrict__ ex_list_idx,
+                                                      const unsigned int* __restrict__ ex_n,
+                                                      const unsigned int* __restrict__ ex_list, unsigned int ex_max,
+                                                      unsigned int pitch, const unsigned int* __restrict__ tag,
+                                                      const unsigned int* __restrict__ rtag, unsigned int N)
+    {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const unsigned int t = tag[i];
+    if (bond_n)
+        {
+        const unsigned int nb = bond_n[t];
+        bond_n_idx[i] = nb;
+        for (unsigned int k = 0; k < nb && k < bond_max; k++)
+            {
+            const uint2 e = bond_list[(size_t)k * pitch + t];
+            bond_list_idx[(size_t)k * pitch + i] = make_uint2(rtag[e.x], e.y);
+            }
+        }
+    if (ex_n)
+        {
+        const unsigned int ne = ex_n[t];
+        ex_n_idx[i] = ne;
+        for (unsigned int k = 0; k < ne && k < ex_max; k++)
+            ex_list_idx[(size_t)k * pitch + i] = rtag[ex_list[(size_t)k * pitch + t]];
+        }
+    }
+
+cudaError_t launch_rekey_tables(unsigned int* bond_n_idx, unsigned int* bond_list_idx, const unsigned int* bond_n,
+                                const unsigned int* bond_list, unsigned int bond_max, unsigned int* ex_n_idx,
+                                unsigned int* ex_list_idx, const unsigned int* ex_n, const unsigned int* ex_list,
+                                unsigned int ex_max, unsigned int pitch, const unsigned int* tag, const unsigned int* rtag,
+                                unsigned int N, cudaStream_t stream)
+    {
+    if (N == 0) return cudaSuccess;
+    k_rekey_tables<<<(N + 255) / 256, 256, 0, stream>>>(bond_n_idx, (uint2*)bond_list_idx, bond_n, (const uint2*)bond_list,
+                                                        bond_max, ex_n_idx, ex_list_idx, ex_n, ex_list, ex_max, pitch, tag,
+                                                        rtag, N);
     return cudaGetLastError();
     }
 

@@ -115,6 +115,103 @@ __global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ c
     if (lane == 0 && max_occ) atomicMax(&conditions[0], max_occ);
     }
 
+// ---- K2 for large grids: the same scan over many CTAs in two launches ------------------------------------------------------
+// The single CTA above walks ncells/4096 tiles one after the other: 66 us at 125k cells (LJ 1M) and 171 us at 328k cells
+// (Kremer-Grest 1M, r_list 1.52) -- 10-14 % of a list rebuild (profiles/r1h_launches_host_*.md).  Here every CTA scans one
+// 4096-cell tile (local exclusive scan + tile total), then a second launch adds the sum of the preceding tile totals
+// (<= a few hundred values, re-summed by every CTA: cheaper than a third launch or a look-back chain).
+constexpr unsigned int SCAN_TILE = 4096;
+
+__device__ __forceinline__ unsigned int block_scan_1024(unsigned int tsum, unsigned int* warp_sums, unsigned int& total)
+    {
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+        }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0)
+        {
+        unsigned int w = warp_sums[lane];
+        unsigned int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            unsigned int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+            }
+        warp_sums[lane] = wi - w; // exclusive
+        if (lane == 31) warp_sums[32] = wi;
+        }
+    __syncthreads();
+    total = warp_sums[32];
+    return warp_sums[warp] + incl - tsum; // exclusive prefix of this thread
+    }
+
+__global__ void __launch_bounds__(1024) k_cell_scan_tiles(unsigned int* __restrict__ cell_start,
+                                                          unsigned int* __restrict__ cell_count, unsigned int ncells,
+                                                          unsigned int* __restrict__ tile_sums,
+                                                          unsigned int* __restrict__ conditions,
+                                                          const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    __shared__ unsigned int warp_sums[33];
+    const unsigned int i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    unsigned int c[4];
+    if (i0 + 3 < ncells)
+        {
+        const uint4 v = *reinterpret_cast<const uint4*>(cell_count + i0); // cudaMalloc base + multiple of 16 B
+        c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w;
+        *reinterpret_cast<uint4*>(cell_count + i0) = make_uint4(0u, 0u, 0u, 0u); // self-cleaning, as above
+        }
+    else
+        {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            {
+            c[k] = (i0 + k < ncells) ? cell_count[i0 + k] : 0u;
+            if (i0 + k < ncells) cell_count[i0 + k] = 0u;
+            }
+        }
+    unsigned int max_occ = max(max(c[0], c[1]), max(c[2], c[3]));
+    unsigned int total;
+    unsigned int excl = block_scan_1024(c[0] + c[1] + c[2] + c[3], warp_sums, total);
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        {
+        if (i0 + k < ncells) cell_start[i0 + k] = excl;
+        excl += c[k];
+        }
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+    for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
+    if ((threadIdx.x & 31) == 0 && max_occ) atomicMax(&conditions[0], max_occ);
+    }
+
+__global__ void __launch_bounds__(1024) k_cell_scan_fix(unsigned int* __restrict__ cell_start, unsigned int ncells,
+                                                        const unsigned int* __restrict__ tile_sums,
+                                                        const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    __shared__ unsigned int warp_sums[33];
+    // offset of this tile = sum of the totals of the tiles before it
+    unsigned int part = 0;
+    for (unsigned int t = threadIdx.x; t < blockIdx.x; t += 1024) part += tile_sums[t];
+    unsigned int offset;
+    block_scan_1024(part, warp_sums, offset);
+    const unsigned int i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    if (blockIdx.x)
+        {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (i0 + k < ncells) cell_start[i0 + k] += offset;
+        }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) cell_start[ncells] = offset + tile_sums[blockIdx.x];
+    }
+
 // ---- K3: scatter particle indices to their (arbitrary) slot inside the cell range ----------------------------------
 __global__ void __launch_bounds__(256) k_cell_scatter(unsigned int* __restrict__ scratch_idx,
                                                       const unsigned int* __restrict__ cell_start,
@@ -298,6 +395,13 @@ void b200_cell_list_dimensions(const b200_box* box, float nominal_width, unsigne
 
 namespace b200
 {
+// launches per cell-list build: the multi-CTA scan (one launch more) pays off beyond a few tiles
+unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot)
+    {
+    const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
+    return (ntiles > 4 && ntiles <= ntot) ? 5u : 4u;
+    }
+
 // enable == NULL: unconditional (driver entry point, zeroes cell_count itself).  enable != NULL: every kernel returns
 // at once unless *enable != 0, and cell_count must already be zero (k_cell_scan leaves it zeroed).
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
@@ -314,7 +418,16 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
         k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
                                                             a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
                                                             box, dim, gw, enable, d_N);
-    k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions, enable);
+    const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
+    if (cell_list_kernels(ncells, ntot) == 5)
+        {
+        // tile totals live in d_scratch_idx, which is not needed before k_cell_scatter
+        k_cell_scan_tiles<<<ntiles, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_scratch_idx,
+                                                       a->d_conditions, enable);
+        k_cell_scan_fix<<<ntiles, 1024, 0, stream>>>(a->d_cell_start, ncells, a->d_scratch_idx, enable);
+        }
+    else
+        k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions, enable);
     if (ntot)
         {
         k_cell_scatter<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,

@@ -153,6 +153,10 @@ struct b200_system
     bool exclusions_set = false;
     unsigned int ex_max = 0, ex_pitch = 0;
     DevBuf<unsigned int> ex_n, ex_list;   // [N], [ex_max * pitch]: partner tag at [k*pitch + tag]
+    // index-keyed working copies (rows by particle index, partners as indices), refreshed after every particle sort
+    bool idx_tables = true, idx_tables_dirty = true;
+    DevBuf<unsigned int> bond_n_idx, ex_n_idx, ex_list_idx;
+    DevBuf<uint2> bond_list_idx;
 
     // ---- IntegratorTwoStep + method ---------------------------------------------------------------------------
     bool have_integrator = false;
@@ -314,6 +318,23 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         }
     }
 
+// BondedGroupData::rebuildGPUTable + NeighborList::updateExListIdx: refresh the index-keyed tables when the particle order
+// or the bond / exclusion sets changed (never inside a captured graph: callers run this before launching steps)
+static void ensure_idx_tables(b200_system* s)
+    {
+    if (!s->idx_tables || !s->idx_tables_dirty) return;
+    const bool have_b = s->bond_n.n != 0, have_e = s->exclusions_set && s->ex_max;
+    if (have_b || have_e)
+        {
+        CUDA_OK(launch_rekey_tables(have_b ? s->bond_n_idx.p : nullptr, (unsigned int*)s->bond_list_idx.p,
+                                    have_b ? s->bond_n.p : nullptr, (const unsigned int*)s->bond_list.p, s->bond_max,
+                                    have_e ? s->ex_n_idx.p : nullptr, s->ex_list_idx.p, have_e ? s->ex_n.p : nullptr,
+                                    s->ex_list.p, s->ex_max, s->N, s->tag.p, s->rtag.p, s->N, s->stream));
+        s->kernels_last_run += 1;
+        }
+    s->idx_tables_dirty = false;
+    }
+
 // PotentialBond<evaluator>::computeForces at `pos` into bond_force / bond_virial (hoomd/md/PotentialBond.h:155-300)
 static void enqueue_bond_forces(b200_system* s, const float4* pos)
     {
@@ -325,6 +346,11 @@ static void enqueue_bond_forces(b200_system* s, const float4* pos)
     a.d_bond_list = (const unsigned int*)s->bond_list.p; a.pitch = s->bond_pitch; a.d_n_bonds = s->bond_n.p;
     a.n_bond_types = s->n_bond_types; a.compute_virial = s->compute_virial ? 1u : 0u;
     a.d_tag = s->tag.p; a.d_rtag = s->rtag.p;
+    if (s->idx_tables)
+        {
+        a.d_bond_list = (const unsigned int*)s->bond_list_idx.p; a.d_n_bonds = s->bond_n_idx.p;
+        a.d_tag = nullptr; a.d_rtag = nullptr;
+        }
     if (s->bond_kind == 0)
         CUDA_OK(b200_compute_fene_bond_forces(&a, (const float*)s->bond_params4.p, s->bond_flags.p, s->stream));
     else
@@ -349,8 +375,12 @@ static void check_bond_flags(b200_system* s)
 static void enqueue_nlist_filter(b200_system* s, const unsigned int* enable)
     {
     if (!s->exclusions_set || s->ex_max == 0) return;
-    CUDA_OK(launch_nlist_filter(s->n_neigh.p, s->nlist.p, s->head_list.p, s->ex_n.p, s->ex_list.p, s->ex_pitch, s->ex_max,
-                                s->tag.p, s->rtag.p, s->N, enable, s->stream));
+    if (s->idx_tables)
+        CUDA_OK(launch_nlist_filter(s->n_neigh.p, s->nlist.p, s->head_list.p, s->ex_n_idx.p, s->ex_list_idx.p, s->ex_pitch,
+                                    s->ex_max, nullptr, nullptr, s->N, enable, s->stream, s->h_Nmax[0]));
+    else
+        CUDA_OK(launch_nlist_filter(s->n_neigh.p, s->nlist.p, s->head_list.p, s->ex_n.p, s->ex_list.p, s->ex_pitch,
+                                    s->ex_max, s->tag.p, s->rtag.p, s->N, enable, s->stream, s->h_Nmax[0]));
     }
 } // namespace b200
 
@@ -385,7 +415,7 @@ static void cell_list_compute(b200_system* s, unsigned int ts)
     b200_cell_list_args a;
     cell_list_args(s, a);
     CUDA_OK(launch_cell_list(&a, nullptr, s->stream));
-    s->kernels_last_run += 4;
+    s->kernels_last_run += cell_list_kernels(a.dim.x * a.dim.y * a.dim.z, a.N + a.n_ghost);
     cell_list_check_conditions(s);
     }
 
@@ -547,6 +577,7 @@ static void nlist_compute(b200_system* s, unsigned int ts)
     s->nl_last_computed = ts;
     if (!should && !s->force_update) return;
     if (s->force_update) nlist_build_head_list(s);
+    ensure_idx_tables(s);
     if (nlist_needs_updating(s, ts))
         {
         if (s->tile_on)
@@ -598,6 +629,7 @@ static void compute_net_force(b200_system* s, unsigned int ts)
         // second ForceCompute + Integrator::computeNetForce: net = pair + bond.  The pair force alone is kept for
         // b200_sys_get_force_component.
         const unsigned int N = s->N;
+        ensure_idx_tables(s);
         CUDA_OK(cudaMemcpyAsync(s->pair_force_copy.p, s->net_force.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         if (s->compute_virial)
             CUDA_OK(cudaMemcpyAsync(s->pair_virial_copy.p, s->net_virial.p, sizeof(float) * 6 * (size_t)s->virial_pitch,
@@ -698,9 +730,10 @@ static void sorter_update(b200_system* s, bool periodic = true)
     CUDA_OK(cudaMemcpyAsync(s->image.p, s->image_alt.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->tag.p, s->tag_alt.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
     s->kernels_last_run += 4;
-    // notifyParticleSort(): nlist forceUpdate, cell list force compute
+    // notifyParticleSort(): nlist forceUpdate, cell list force compute, bonded tables / exclusion indices rebuilt
     s->force_update = true;
     s->cl_force = true;
+    s->idx_tables_dirty = true;
     }
 } // namespace b200
 
@@ -881,6 +914,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     {
     const unsigned int N = s->N;
     if (s->force_update) nlist_build_head_list(s); // types may have been permuted by the sorter
+    ensure_idx_tables(s);
     if (s->use_graph != 3) ensure_graph(s);
     if (s->ck_pos.n < N)
         {
@@ -981,7 +1015,9 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         }
     check_bond_flags(s);
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-    const unsigned long long rk = (s->tile_on ? 8ull : 6ull) + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // per rebuild
+    const unsigned long long cl_extra = cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->N) - 4u;
+    const unsigned long long rk = (s->tile_on ? 8ull : 6ull) + cl_extra
+                                  + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
     s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + rk * rebuilds)
                                                                              : (2ull + 2ull * rk) * nreplay);
@@ -1017,6 +1053,7 @@ static void sys_open_device(b200_system* s)
     CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     // developer overrides of the pair path: HOOMD_B200_PAIR_MODE = -1 | 0 | 1, HOOMD_B200_TILE = "bx,by,bz,tpp"
     if (const char* m = getenv("HOOMD_B200_PAIR_MODE")) s->pair_mode = atoi(m);
+    if (const char* m = getenv("HOOMD_B200_TAG_TABLES")) s->idx_tables = atoi(m) == 0; // A/B: tag-keyed bond / exclusion rows
     if (const char* t = getenv("HOOMD_B200_TILE"))
         {
         unsigned int v[4] = {0, 0, 0, 0};
@@ -1319,6 +1356,9 @@ int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* 
     s->bond_list.alloc(table.size());
     s->bond_n.upload(cnt.data(), N, s->stream);
     s->bond_list.upload(table.data(), table.size(), s->stream);
+    s->bond_n_idx.alloc(N);
+    s->bond_list_idx.alloc(table.size());
+    s->idx_tables_dirty = true;
     CUDA_OK(cudaStreamSynchronize(s->stream));
     invalidate_graph(s);
     SYS_CATCH(s)
@@ -1397,6 +1437,9 @@ int b200_sys_nlist_exclusions_from_bonds(b200_system* s, int on)
         s->ex_list.alloc(table.size());
         s->ex_n.upload(cnt.data(), N, s->stream);
         s->ex_list.upload(table.data(), table.size(), s->stream);
+        s->ex_n_idx.alloc(N);
+        s->ex_list_idx.alloc(table.size());
+        s->idx_tables_dirty = true;
         CUDA_OK(cudaStreamSynchronize(s->stream));
         s->ex_max = mx;
         s->ex_pitch = N;
@@ -1673,6 +1716,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
     SYS_TRY(s)
     if (!s->have_nlist) throw std::runtime_error("nlist: not set up");
     if (iters == 0) iters = 1;
+    ensure_idx_tables(s);
     cudaEvent_t e0, e1;
     CUDA_OK(cudaEventCreate(&e0));
     CUDA_OK(cudaEventCreate(&e1));

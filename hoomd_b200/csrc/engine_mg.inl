@@ -266,7 +266,7 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
         s->cl_force = false;
         s->num_forced += 1;
         s->last_updated_tstep = ts;
-        s->kernels_last_run += MG_REBUILD_KERNELS;
+        s->kernels_last_run += MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u;
         }
     s->nl_last_computed = ts;
     s->last_checked_tstep = ts;
@@ -385,7 +385,8 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_check_errors(s);
         cell_list_check_conditions(s);
         const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-        s->kernels_last_run += 2ull + 6ull * nreplay + MG_REBUILD_KERNELS * rebuilds;
+        s->kernels_last_run += 2ull + 6ull * nreplay
+                               + (MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u) * rebuilds;
         s->num_updates += st.num_updates;
         s->num_forced += st.num_forced;
         s->nl_first_compute = false;

@@ -33,6 +33,7 @@ struct StepState
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
                              const unsigned int* d_N = nullptr);
+unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot); // launches of one launch_cell_list
 cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream);
 unsigned int pick_pair_tpp(unsigned int N);
 
@@ -76,7 +77,12 @@ namespace b200
 cudaError_t launch_nlist_filter(unsigned int* n_neigh, unsigned int* nlist, const unsigned int* head_list,
                                 const unsigned int* n_ex, const unsigned int* ex_list, unsigned int ex_pitch,
                                 unsigned int max_ex, const unsigned int* tag, const unsigned int* rtag, unsigned int N,
-                                const unsigned int* enable, cudaStream_t stream);
+                                const unsigned int* enable, cudaStream_t stream, unsigned int row_hint = 0);
+cudaError_t launch_rekey_tables(unsigned int* bond_n_idx, unsigned int* bond_list_idx, const unsigned int* bond_n,
+                                const unsigned int* bond_list, unsigned int bond_max, unsigned int* ex_n_idx,
+                                unsigned int* ex_list_idx, const unsigned int* ex_n, const unsigned int* ex_list,
+                                unsigned int ex_max, unsigned int pitch, const unsigned int* tag, const unsigned int* rtag,
+                                unsigned int N, cudaStream_t stream);
 cudaError_t launch_add_force(float4* net, float* net_virial, unsigned int net_pitch, const float4* f, const float* v,
                              unsigned int v_pitch, unsigned int N, bool virial, cudaStream_t stream);
 cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, unsigned int N, cudaStream_t stream);
