@@ -84,6 +84,7 @@ SYMBOLS = [
     "b200_box_init", "b200_box_init_lohi", "b200_compute_cell_list", "b200_cell_list_dimensions",
     "b200_cell_list_export_padded", "b200_cell_list_build_adjacency", "b200_nlist_build_head_list",
     "b200_compute_nlist_binned", "b200_nlist_needs_update_check", "b200_compute_lj_forces",
+    "b200_compute_pair_forces", "b200_sys_setup_pair",
     "b200_nlist_filter", "b200_compute_fene_bond_forces", "b200_compute_harmonic_bond_forces",
     "b200_sys_set_bonds", "b200_sys_setup_bond_force", "b200_sys_nlist_exclusions_from_bonds",
     "b200_sys_get_force_component",
@@ -100,6 +101,36 @@ SYMBOLS = [
     "b200_sys_create_mg", "b200_sys_mg_export", "b200_sys_mg_connect", "b200_sys_get_n", "b200_sys_set_tags",
     "b200_sys_mg_stats", "b200_sys_mg_get_ghosts",
 ]
+
+# enum B200_PAIR_* (hoomd/md/AllPairPotentials.h)
+PAIR_KINDS = {"lj": 0, "gauss": 1, "yukawa": 2, "mie": 3, "force_shifted_lj": 4, "morse": 5}
+
+
+def pair_params(kind, nt, **c):
+    """ntypes x ntypes x 4 float32 parameter table of evaluator `kind` from user coefficients, processed like
+    hoomd/md/pair.py process_coeff (lj :602-609, gauss :674-678, yukawa :865-869, morse :1276-1281,
+    force_shifted_lj :1764-1772, mie :2083-2093) in double precision, then cast."""
+    import numpy as np
+    bc = lambda x: np.broadcast_to(np.asarray(x, np.float64), (nt, nt))
+    p = np.zeros((nt, nt, 4), np.float64)
+    if kind in ("lj", "force_shifted_lj"):
+        eps, sig, alp = bc(c.get("epsilon", 1.0)), bc(c.get("sigma", 1.0)), bc(c.get("alpha", 1.0))
+        p[..., 0] = 4.0 * eps * sig ** 12
+        p[..., 1] = alp * 4.0 * eps * sig ** 6
+    elif kind == "gauss":
+        p[..., 0], p[..., 1] = bc(c["epsilon"]), bc(c["sigma"])
+    elif kind == "yukawa":
+        p[..., 0], p[..., 1] = bc(c["epsilon"]), bc(c["kappa"])
+    elif kind == "mie":
+        eps, sig, n, m = bc(c["epsilon"]), bc(c["sigma"]), bc(c["n"]), bc(c["m"])
+        pref = (n / (n - m)) * (n / m) ** (m / (n - m))
+        p[..., 0], p[..., 1], p[..., 2], p[..., 3] = eps * sig ** n * pref, eps * sig ** m * pref, n, m
+    elif kind == "morse":
+        p[..., 0], p[..., 1], p[..., 2] = bc(c["D0"]), bc(c["alpha"]), bc(c["r0"])
+    else:
+        raise ValueError("unknown pair potential " + str(kind))
+    return np.ascontiguousarray(p.astype(np.float32))
+
 
 _lib = None
 
@@ -128,6 +159,8 @@ def lib():
     L.b200_nlist_needs_update_check.argtypes = [vp, vp, vp, C.c_uint, C.POINTER(Box), vp, C.c_float, C.c_uint,
                                                 C.c_float, C.c_float * 3, C.c_uint, vp]
     L.b200_compute_lj_forces.argtypes = [C.POINTER(PairArgs), vp, vp]
+    L.b200_compute_pair_forces.argtypes = [C.c_int, C.POINTER(PairArgs), vp, vp]
+    L.b200_sys_setup_pair.argtypes = [vp, C.c_int, C.c_float, C.c_uint, vp, vp, vp, C.c_int]
     L.b200_nlist_filter.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.c_uint, vp, vp, C.c_uint, vp]
     L.b200_compute_fene_bond_forces.argtypes = [C.POINTER(BondArgs), vp, vp, vp]
     L.b200_compute_harmonic_bond_forces.argtypes = [C.POINTER(BondArgs), vp, vp, vp]

@@ -133,7 +133,9 @@ struct b200_system
     unsigned long long num_updates = 0, num_forced = 0, num_overflows = 0;
 
     // ---- PotentialPairLJ ----------------------------------------------------------------------------------------
-    DevBuf<float2> d_params;
+    int pair_kind = 0;           // B200_PAIR_*: which EvaluatorPair* the pair force instantiates
+    DevBuf<float2> d_params;     // Scalar2 evaluators (LJ, Gauss, Yukawa, force-shifted LJ)
+    DevBuf<float4> d_params4;    // Scalar4 evaluators (Mie, Morse)
     DevBuf<float> d_rcutsq, d_ronsq;
     int shift_mode = 0;
     unsigned int pair_tpp = 0;
@@ -300,6 +302,12 @@ static void pair_args(b200_system* s, b200_pair_args& a)
     // listed pairs are at most r_list apart at build time and each partner drifts < r_buff/2 (+ one step) before the
     // next rebuild: r_cut + 2 r_buff bounds every |r_i - r_j| the kernel will see
     a.wrap_skip_margin = s->rcut_max_max + 2.0f * s->r_buff + 0.1f;
+    }
+
+static const void* pair_params_ptr(b200_system* s)
+    {
+    return (s->pair_kind == B200_PAIR_MIE || s->pair_kind == B200_PAIR_MORSE) ? (const void*)s->d_params4.p
+                                                                              : (const void*)s->d_params.p;
     }
 
 static void fused_args(b200_system* s, FusedStepArgs& a)
@@ -622,7 +630,7 @@ static void compute_net_force(b200_system* s, unsigned int ts)
                                        s->stream));
         }
     else
-        CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
+        CUDA_OK(b200_compute_pair_forces(s->pair_kind, &a, pair_params_ptr(s), s->stream));
     s->kernels_last_run += 1;
     if (s->bond_kind >= 0)
         {
@@ -783,8 +791,8 @@ static void enqueue_md_step(b200_system* s, const FusedStepArgs& fa, int phase, 
                                        use_cond, s->stream));
         return;
         }
-    CUDA_OK(launch_md_step_lj(pa, (const float*)s->d_params.p, fa, pin, pout, phase == 1, s->d_state.p, handle, use_cond,
-                              s->stream));
+    CUDA_OK(launch_md_step_kind(s->pair_kind, pa, pair_params_ptr(s), fa, pin, pout, phase == 1, s->d_state.p, handle,
+                                use_cond, s->stream));
     }
 
 #if (CUDART_VERSION >= 12040)
@@ -1265,11 +1273,15 @@ int b200_sys_get_particles(b200_system* s, float* pos4, float* vel4, float* acce
     SYS_CATCH(s)
     }
 
-int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut, const float* lj1,
-                      const float* lj2, const float* ron, int shift_mode)
+int b200_sys_setup_pair(b200_system* s, int evaluator, float r_buff, unsigned int check_period, const float* rcut,
+                        const float* params4, const float* ron, int shift_mode)
     {
     SYS_TRY(s)
     const unsigned int nt = s->ntypes;
+    if (evaluator < B200_PAIR_LJ || evaluator > B200_PAIR_MORSE) throw std::runtime_error("pair: unknown evaluator");
+    if (evaluator != B200_PAIR_LJ && s->pair_mode == 1)
+        throw std::runtime_error("pair: the cell-tile pair mode is instantiated for md.pair.lj only");
+    s->pair_kind = evaluator;
     if (r_buff < 0.0f) throw std::runtime_error("nlist: Requested buffer radius is less than zero");
     if (shift_mode < 0 || shift_mode > 2) throw std::runtime_error("pair: invalid shift mode");
     s->r_buff = r_buff;
@@ -1280,15 +1292,19 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     nlist_update_rlist(s);
     // pair tables: rcutsq = rcut*rcut, ronsq = ron*ron (PotentialPair::setRcut/setRon, hoomd/md/PotentialPair.h:237-269)
     std::vector<float2> prm(nt * nt);
+    std::vector<float4> prm4(nt * nt);
     std::vector<float> rcsq(nt * nt), ronsq(nt * nt, 0.0f);
     for (unsigned int k = 0; k < nt * nt; k++)
         {
-        prm[k] = make_float2(lj1[k], lj2[k]);
+        prm[k] = make_float2(params4[4 * k], params4[4 * k + 1]);
+        prm4[k] = make_float4(params4[4 * k], params4[4 * k + 1], params4[4 * k + 2], params4[4 * k + 3]);
         rcsq[k] = rcut[k] * rcut[k];
         if (ron) ronsq[k] = ron[k] * ron[k];
         }
     s->d_params.alloc(nt * nt); s->d_rcutsq.alloc(nt * nt); s->d_ronsq.alloc(nt * nt);
     s->d_params.upload(prm.data(), nt * nt, s->stream);
+    s->d_params4.alloc(nt * nt);
+    s->d_params4.upload(prm4.data(), nt * nt, s->stream);
     s->d_rcutsq.upload(rcsq.data(), nt * nt, s->stream);
     s->d_ronsq.upload(ronsq.data(), nt * nt, s->stream);
     // NeighborList ctor: Nmax = 8 per type, nlist 8*N (hoomd/md/NeighborList.cc:80-98)
@@ -1317,6 +1333,19 @@ int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, c
     invalidate_graph(s);
     tile_configure(s);
     SYS_CATCH(s)
+    }
+
+int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut, const float* lj1,
+                      const float* lj2, const float* ron, int shift_mode)
+    {
+    const unsigned int nt = s->ntypes;
+    std::vector<float> p4(4 * (size_t)nt * nt, 0.0f);
+    for (unsigned int k = 0; k < nt * nt; k++)
+        {
+        p4[4 * k] = lj1[k];
+        p4[4 * k + 1] = lj2[k];
+        }
+    return b200_sys_setup_pair(s, B200_PAIR_LJ, r_buff, check_period, rcut, p4.data(), ron, shift_mode);
     }
 
 int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* tags2, const unsigned int* types,
@@ -1783,7 +1812,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         else if (s->tile_on)
             tile_enqueue_rebuild(s, nullptr, s->pos.p); // identity permutation: the particles are in cell order
         else if (which == 0)
-            CUDA_OK(b200_compute_lj_forces(&pa, (const float*)s->d_params.p, s->stream));
+            CUDA_OK(b200_compute_pair_forces(s->pair_kind, &pa, pair_params_ptr(s), s->stream));
         else
             {
             CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, s->mg ? &s->d_state.p->N : nullptr));

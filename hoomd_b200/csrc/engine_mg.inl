@@ -272,7 +272,7 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
     s->last_checked_tstep = ts;
     b200_pair_args a;
     pair_args(s, a);
-    CUDA_OK(b200_compute_lj_forces(&a, (const float*)s->d_params.p, s->stream));
+    CUDA_OK(b200_compute_pair_forces(s->pair_kind, &a, pair_params_ptr(s), s->stream));
     s->kernels_last_run += 1;
     if (!s->accel_set)
         {

@@ -68,6 +68,7 @@ static void tile_configure(b200_system* s)
     if (!s->have_nlist || s->pair_mode != 1) return;
     if (s->bond_kind >= 0 || s->exclusions_set)
         throw std::runtime_error("tile: the cell-tile path carries neither bonded forces nor nlist exclusions");
+    if (s->pair_kind != B200_PAIR_LJ) throw std::runtime_error("tile: the cell-tile path is instantiated for md.pair.lj only");
     if (!tile_pick_geometry(s))
         {
         if (s->pair_mode == 1) throw std::runtime_error("tile: cell-tile path needs one GPU, a periodic orthorhombic box with "

@@ -63,6 +63,21 @@ cudaError_t launch_graph_pre(StepState* st, unsigned long long cond_handle, cuda
 cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, const FusedStepArgs& fa,
                               const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
                               unsigned long long cond_handle, int use_cond, cudaStream_t stream);
+// pair_ev.cu: the evaluators beyond LJ (enum B200_PAIR_* of include/hoomd_b200.h)
+#define B200_DECL_EV(NAME)                                                                                              \
+    cudaError_t launch_pair_##NAME(const b200_pair_args& a, const void* d_params, cudaStream_t stream);               \
+    cudaError_t launch_md_step_##NAME(const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,          \
+                                      const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,      \
+                                      unsigned long long cond_handle, int use_cond, cudaStream_t stream);
+B200_DECL_EV(gauss)
+B200_DECL_EV(yukawa)
+B200_DECL_EV(mie)
+B200_DECL_EV(fslj)
+B200_DECL_EV(morse)
+#undef B200_DECL_EV
+cudaError_t launch_md_step_kind(int evaluator, const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,
+                                const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
+                                unsigned long long cond_handle, int use_cond, cudaStream_t stream);
 // after a device-driven rebuild: overflow detection, condition reset
 cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
                                 cudaStream_t stream);

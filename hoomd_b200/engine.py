@@ -81,6 +81,18 @@ class System:
                                                  _p(lj2), _p(ron), int(shift_mode)))
         self.lj1, self.lj2, self.rcut = lj1, lj2, rc
 
+    def setup_pair(self, kind, r_cut, r_buff=0.4, check_period=1, shift_mode=0, r_on=None, **coeffs):
+        """md.pair.<kind> in place of md.pair.lj: kind in gauss | yukawa | mie | force_shifted_lj | morse | lj, coefficients
+        by their job-script names (epsilon, sigma, kappa, n, m, D0, alpha, r0), scalars or ntypes x ntypes arrays"""
+        nt = self.ntypes
+        bc = lambda x: np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), (nt, nt)))
+        prm = _lib.pair_params(kind, nt, **coeffs)
+        rc = np.ascontiguousarray(bc(r_cut).astype(np.float32))
+        ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
+        self._check(_lib.lib().b200_sys_setup_pair(self.h, _lib.PAIR_KINDS[kind], C.c_float(r_buff), int(check_period),
+                                                   _p(rc), _p(prm), _p(ron), int(shift_mode)))
+        self.pair_params, self.rcut = prm, rc
+
     # ---- BondData + md.bond.* + nlist exclusions -------------------------------------------------------------
     def set_bonds(self, bonds, types=None, n_bond_types=None):
         """bonds: (nbonds, 2) particle TAGS; types: bond type per bond (default 0)"""

@@ -389,21 +389,23 @@ class _Coeff:
         return ok
 
 
-class _LJ:
-    """md.pair.lj (hoomd/md/pair.py:579-609)"""
+class _Pair:
+    """md.pair.pair (hoomd/md/pair.py:258-445): one PotentialPair<evaluator> on a neighbor list"""
+    kind, required_coeffs, defaults = None, [], {}
 
     def __init__(self, r_cut, nlist, name=None):
         _require_context()
         if context.current.system is None:
             raise RuntimeError("Cannot create force before initialization")
-        if any(isinstance(f, _LJ) for f in context.current.forces):
-            raise RuntimeError("hoomd_b200: one md.pair.lj per system in this round")
+        if any(isinstance(f, _Pair) for f in context.current.forces):
+            raise RuntimeError("hoomd_b200: one pair force per system in this round")
         self.global_r_cut, self.nlist, self.shift_mode = float(r_cut), nlist, 0
         self.pair_coeff = _Coeff()
-        self.pair_coeff.set_default_coeff("alpha", 1.0)
+        for k, v in self.defaults.items():
+            self.pair_coeff.set_default_coeff(k, v)
         self.pair_coeff.set_default_coeff("r_cut", self.global_r_cut)
         self.pair_coeff.set_default_coeff("r_on", self.global_r_cut)
-        self.required_coeffs = ["epsilon", "sigma", "alpha"]
+        self.required_coeffs = list(type(self).required_coeffs)
         self.enabled = True
         nlist.subscribers.append(self)
         context.current.forces.append(self)
@@ -421,7 +423,7 @@ class _LJ:
         if not self.pair_coeff.verify(types_, self.required_coeffs):
             raise RuntimeError("Error updating pair coefficients")
         nt = len(types_)
-        out = {k: np.zeros((nt, nt)) for k in ("r_cut", "epsilon", "sigma", "alpha", "r_on")}
+        out = {k: np.zeros((nt, nt)) for k in ["r_cut", "r_on"] + self.required_coeffs}
         for i, a in enumerate(types_):
             for j, b in enumerate(types_):
                 for k in out:
@@ -436,7 +438,42 @@ class _LJ:
         return float(f[:, 3].astype(np.float64).sum())
 
 
+class _LJ(_Pair):
+    """md.pair.lj (hoomd/md/pair.py:579-609)"""
+    kind, required_coeffs, defaults = "lj", ["epsilon", "sigma", "alpha"], {"alpha": 1.0}
+
+
+class _Gauss(_Pair):
+    """md.pair.gauss (hoomd/md/pair.py:611-678)"""
+    kind, required_coeffs = "gauss", ["epsilon", "sigma"]
+
+
+class _Yukawa(_Pair):
+    """md.pair.yukawa (hoomd/md/pair.py:806-869)"""
+    kind, required_coeffs = "yukawa", ["epsilon", "kappa"]
+
+
+class _Mie(_Pair):
+    """md.pair.mie (hoomd/md/pair.py:2017-2093)"""
+    kind, required_coeffs = "mie", ["epsilon", "sigma", "n", "m"]
+
+
+class _ForceShiftedLJ(_Pair):
+    """md.pair.force_shifted_lj (hoomd/md/pair.py:1692-1772)"""
+    kind, required_coeffs, defaults = "force_shifted_lj", ["epsilon", "sigma", "alpha"], {"alpha": 1.0}
+
+
+class _Morse(_Pair):
+    """md.pair.morse (hoomd/md/pair.py:1213-1281)"""
+    kind, required_coeffs = "morse", ["D0", "alpha", "r0"]
+
+
 md.pair.lj = _LJ
+md.pair.gauss = _Gauss
+md.pair.yukawa = _Yukawa
+md.pair.mie = _Mie
+md.pair.force_shifted_lj = _ForceShiftedLJ
+md.pair.morse = _Morse
 
 
 class _BondCoeff:
@@ -617,9 +654,9 @@ def _configure_engine():
     methods = [m for m in ctx.integration_methods if m.enabled]
     if len(methods) != 1:
         raise RuntimeError("hoomd_b200: exactly one enabled integration method is supported, got %d" % len(methods))
-    ljs = [f for f in ctx.forces if isinstance(f, _LJ) and f.enabled]
+    ljs = [f for f in ctx.forces if isinstance(f, _Pair) and f.enabled]
     if len(ljs) != 1:
-        raise RuntimeError("hoomd_b200: exactly one md.pair.lj force is supported, got %d" % len(ljs))
+        raise RuntimeError("hoomd_b200: exactly one md.pair force is supported, got %d" % len(ljs))
     lj = ljs[0]
     if ctx.engine is not None:  # carry the state over
         sysd.take_snapshot()
@@ -628,9 +665,14 @@ def _configure_engine():
                  image=sysd.image)
     t = lj.tables(sysd.types)
     need_virial = any("pressure" in lg.quantities for lg in ctx.loggers)
-    eng.setup_lj(r_cut=t["r_cut"], epsilon=t["epsilon"], sigma=t["sigma"], alpha=t["alpha"], r_buff=lj.nlist.r_buff,
-                 check_period=lj.nlist.check_period, shift_mode=lj.shift_mode,
-                 r_on=t["r_on"] if lj.shift_mode == 2 else None)
+    if lj.kind == "lj":
+        eng.setup_lj(r_cut=t["r_cut"], epsilon=t["epsilon"], sigma=t["sigma"], alpha=t["alpha"], r_buff=lj.nlist.r_buff,
+                     check_period=lj.nlist.check_period, shift_mode=lj.shift_mode,
+                     r_on=t["r_on"] if lj.shift_mode == 2 else None)
+    else:
+        eng.setup_pair(lj.kind, r_cut=t["r_cut"], r_buff=lj.nlist.r_buff, check_period=lj.nlist.check_period,
+                       shift_mode=lj.shift_mode, r_on=t["r_on"] if lj.shift_mode == 2 else None,
+                       **{k: t[k] for k in lj.required_coeffs})
     bonds = [f for f in ctx.forces if isinstance(f, _Bond) and f.enabled]
     if len(sysd.bond_group):
         eng.set_bonds(sysd.bond_group, sysd.bond_typeid, n_bond_types=len(sysd.bond_types))

@@ -201,6 +201,18 @@ typedef struct b200_pair_args
 /* d_params: Scalar2[ntypes*ntypes] = (lj1, lj2) = (4 eps sigma^12, 4 alpha eps sigma^6) (hoomd/md/pair.py:602-609) */
 B200_API int b200_compute_lj_forces(const b200_pair_args* args, const float* d_params, b200_stream_t stream);
 
+/* The other PotentialPair<evaluator> instantiations of hoomd/md/AllPairPotentials.h:45-79 through the same kernel
+ * (replaces gpu_compute_gauss_forces / _yukawa_ / _mie_ / _force_shifted_lj_ / _morse_forces,
+ * hoomd/md/AllDriverPotentialPairGPU.cuh).  d_params is the reference's param_type array [ntypes*ntypes]:
+ *   LJ (lj1, lj2) Scalar2 | GAUSS (epsilon, sigma) Scalar2 | YUKAWA (epsilon, kappa) Scalar2 |
+ *   MIE (mie1, mie2, n, m) Scalar4 | FORCE_SHIFTED_LJ (lj1, lj2) Scalar2 | MORSE (D0, alpha, r0, -) Scalar4
+ * (coefficient processing: hoomd/md/pair.py gauss :611-690, yukawa :835-900, mie :2188-2265, force_shifted_lj :1781-1850,
+ * morse :1193-1260).  Energy shift modes as for LJ. */
+enum { B200_PAIR_LJ = 0, B200_PAIR_GAUSS = 1, B200_PAIR_YUKAWA = 2, B200_PAIR_MIE = 3, B200_PAIR_FORCE_SHIFTED_LJ = 4,
+       B200_PAIR_MORSE = 5 };
+B200_API int b200_compute_pair_forces(int evaluator, const b200_pair_args* args, const void* d_params,
+                                      b200_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * NeighborList exclusions  -- replaces gpu_nlist_filter (hoomd/md/NeighborListGPU.cu:140-240); semantics of
  * NeighborList::filterNlist (hoomd/md/NeighborList.cc:1275-1328): every row is rewritten in place without its excluded
@@ -353,6 +365,10 @@ B200_API int b200_sys_get_particles(b200_system* s, float* pos4, float* vel4, fl
  * rcut/lj1/lj2/ron: ntypes x ntypes row-major (ron may be NULL). */
 B200_API int b200_sys_setup_lj(b200_system* s, float r_buff, unsigned int check_period, const float* rcut,
                                const float* lj1, const float* lj2, const float* ron, int shift_mode);
+/* md.pair.<evaluator> in place of md.pair.lj: params4 = ntypes x ntypes x 4 floats (the evaluator's param_type padded to
+ * four components, meaning as listed at b200_compute_pair_forces); the cell-tile pair mode is LJ only */
+B200_API int b200_sys_setup_pair(b200_system* s, int evaluator, float r_buff, unsigned int check_period,
+                                 const float* rcut, const float* params4, const float* ron, int shift_mode);
 /* BondData of the snapshot (hoomd/BondedGroupData.h): nbonds bonds between particle TAGS tags2[2b], tags2[2b+1] of bond
  * type types[b] < n_bond_types (HOST pointers).  Replaces any previous bond set. */
 B200_API int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* tags2,

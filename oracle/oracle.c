@@ -49,8 +49,9 @@ struct orc_system
     unsigned int nl_last, every, last_updated, last_checked;
     unsigned long long updates, forced;
     /* PotentialPairLJ */
-    float *lj1, *lj2, *rcutsq, *ronsq;
-    int shift_mode;
+    float *lj1, *lj2, *rcutsq, *ronsq; /* lj1/lj2 = the first two components of the evaluator's param_type */
+    float *p3, *p4;                    /* third / fourth component (Mie, Morse) */
+    int shift_mode, pair_kind;
     /* Integrator */
     float dt; int method, limit, zero_force, noiseless_t; float limit_val, kT; unsigned int seed; float* gamma;
     unsigned int timestep;
@@ -563,6 +564,119 @@ static int compute_bond_forces(orc_system* s)
     return 0;
     }
 
+/* ---- EvaluatorPair*::evalForceAndEnergy: LJ (EvaluatorPairLJ.h:137-158), Gauss (EvaluatorPairGauss.h:100-122), Yukawa
+ * (EvaluatorPairYukawa.h:98-126), Mie (EvaluatorPairMie.h:104-128), force-shifted LJ (EvaluatorPairForceShiftedLJ.h:97-127),
+ * Morse (EvaluatorPairMorse.h:96-120); fast::exp / rsqrt / sqrt are libm calls in the CPU build (HOOMDMath.h) ------------- */
+static int pair_eval(int kind, float rsq, float rcutsq, float p1, float p2, float p3, float p4, int energy_shift,
+                     float* force_divr_out, float* pair_eng_out)
+    {
+    float force_divr = 0.0f, pair_eng = 0.0f;
+    switch (kind)
+        {
+        case 0: /* LJ: (lj1, lj2) */
+            {
+            const float lj1 = p1, lj2 = p2;
+            if (!(rsq < rcutsq && lj1 != 0)) return 0;
+            float r2inv = 1.0f / rsq;
+            float r6inv = r2inv * r2inv * r2inv;
+            force_divr = r2inv * r6inv * (12.0f * lj1 * r6inv - 6.0f * lj2);
+            pair_eng = r6inv * (lj1 * r6inv - lj2);
+            if (energy_shift)
+                {
+                float rcut2inv = 1.0f / rcutsq;
+                float rcut6inv = rcut2inv * rcut2inv * rcut2inv;
+                pair_eng -= rcut6inv * (lj1 * rcut6inv - lj2);
+                }
+            break;
+            }
+        case 1: /* Gauss: (epsilon, sigma) */
+            {
+            const float epsilon = p1, sigma = p2;
+            if (!(rsq < rcutsq)) return 0;
+            float sigma_sq = sigma * sigma;
+            float r_over_sigma_sq = rsq / sigma_sq;
+            float exp_val = expf(-1.0f / 2.0f * r_over_sigma_sq);
+            force_divr = epsilon / sigma_sq * exp_val;
+            pair_eng = epsilon * exp_val;
+            if (energy_shift) pair_eng -= epsilon * expf(-1.0f / 2.0f * rcutsq / sigma_sq);
+            break;
+            }
+        case 2: /* Yukawa: (epsilon, kappa) */
+            {
+            const float epsilon = p1, kappa = p2;
+            if (!(rsq < rcutsq && epsilon != 0)) return 0;
+            float rinv = 1.0f / sqrtf(rsq);
+            float r = 1.0f / rinv;
+            float r2inv = 1.0f / rsq;
+            float exp_val = expf(-kappa * r);
+            force_divr = epsilon * exp_val * r2inv * (rinv + kappa);
+            pair_eng = epsilon * exp_val * rinv;
+            if (energy_shift)
+                {
+                float rcutinv = 1.0f / sqrtf(rcutsq);
+                float rcut = 1.0f / rcutinv;
+                pair_eng -= epsilon * expf(-kappa * rcut) * rcutinv;
+                }
+            break;
+            }
+        case 3: /* Mie: (mie1, mie2, n, m) */
+            {
+            const float mie1 = p1, mie2 = p2, mie3 = p3, mie4 = p4;
+            if (!(rsq < rcutsq && mie1 != 0)) return 0;
+            float r2inv = 1.0f / rsq;
+            float rninv = powf(r2inv, mie3 / 2.0f);
+            float rminv = powf(r2inv, mie4 / 2.0f);
+            force_divr = r2inv * (mie3 * mie1 * rninv - mie4 * mie2 * rminv);
+            pair_eng = mie1 * rninv - mie2 * rminv;
+            if (energy_shift)
+                {
+                float rcutninv = 1.0f / powf(rcutsq, mie3 / 2.0f);
+                float rcutminv = 1.0f / powf(rcutsq, mie4 / 2.0f);
+                pair_eng -= mie1 * rcutninv - mie2 * rcutminv;
+                }
+            break;
+            }
+        case 4: /* force-shifted LJ: (lj1, lj2) */
+            {
+            const float lj1 = p1, lj2 = p2;
+            if (!(rsq < rcutsq && lj1 != 0)) return 0;
+            float r2inv = 1.0f / rsq;
+            float r6inv = r2inv * r2inv * r2inv;
+            force_divr = r2inv * r6inv * (12.0f * lj1 * r6inv - 6.0f * lj2);
+            pair_eng = r6inv * (lj1 * r6inv - lj2);
+            float rcut2inv = 1.0f / rcutsq;
+            float rcut6inv = rcut2inv * rcut2inv * rcut2inv;
+            if (energy_shift) pair_eng -= rcut6inv * (lj1 * rcut6inv - lj2);
+            float rcut_r_inv = 1.0f / sqrtf(rsq * rcutsq);
+            float force_rcut_at_rcut = rcut6inv * (12.0f * lj1 * rcut6inv - 6.0f * lj2);
+            force_divr -= rcut_r_inv * force_rcut_at_rcut;
+            pair_eng += (rsq * rcut_r_inv - 1.0f) * force_rcut_at_rcut;
+            break;
+            }
+        case 5: /* Morse: (D0, alpha, r0) */
+            {
+            const float D0 = p1, alpha = p2, r0 = p3;
+            if (!(rsq < rcutsq)) return 0;
+            float r = sqrtf(rsq);
+            float Exp_factor = expf(-alpha * (r - r0));
+            pair_eng = D0 * Exp_factor * (Exp_factor - 2.0f);
+            force_divr = 2.0f * D0 * alpha * Exp_factor * (Exp_factor - 1.0f) / r;
+            if (energy_shift)
+                {
+                float rcut = sqrtf(rcutsq);
+                float Exp_factor_cut = expf(-alpha * (rcut - r0));
+                pair_eng -= D0 * Exp_factor_cut * (Exp_factor_cut - 2.0f);
+                }
+            break;
+            }
+        default:
+            return 0;
+        }
+    *force_divr_out = force_divr;
+    *pair_eng_out = pair_eng;
+    return 1;
+    }
+
 /* ---- PotentialPair<EvaluatorPairLJ>::computeForces (PotentialPair.h:309-522, EvaluatorPairLJ.h:137-158), full list ------ */
 static int compute_forces(orc_system* s, unsigned int ts)
     {
@@ -587,25 +701,16 @@ static int compute_forces(orc_system* s, unsigned int ts)
             dx = box_min_image(&s->box, dx);
             const float rsq = dot3(dx);
             const unsigned int tp = typei * nt + typej;
-            const float lj1 = s->lj1[tp], lj2 = s->lj2[tp], rcutsq = s->rcutsq[tp];
+            const float rcutsq = s->rcutsq[tp];
             float ronsq = 0.0f;
             int energy_shift = 0;
             if (s->shift_mode == 2) ronsq = s->ronsq[tp];
             if (s->shift_mode == 1) energy_shift = 1;
             else if (s->shift_mode == 2 && ronsq > rcutsq) energy_shift = 1;
             float force_divr = 0.0f, pair_eng = 0.0f;
-            if (rsq < rcutsq && lj1 != 0)
+            if (pair_eval(s->pair_kind, rsq, rcutsq, s->lj1[tp], s->lj2[tp], s->p3 ? s->p3[tp] : 0.0f,
+                          s->p4 ? s->p4[tp] : 0.0f, energy_shift, &force_divr, &pair_eng))
                 {
-                float r2inv = 1.0f / rsq;
-                float r6inv = r2inv * r2inv * r2inv;
-                force_divr = r2inv * r6inv * (12.0f * lj1 * r6inv - 6.0f * lj2);
-                pair_eng = r6inv * (lj1 * r6inv - lj2);
-                if (energy_shift)
-                    {
-                    float rcut2inv = 1.0f / rcutsq;
-                    float rcut6inv = rcut2inv * rcut2inv * rcut2inv;
-                    pair_eng -= rcut6inv * (lj1 * rcut6inv - lj2);
-                    }
                 if (s->shift_mode == 2 && rsq >= ronsq && rsq < rcutsq)
                     {
                     float old_pair_eng = pair_eng, old_force_divr = force_divr;
@@ -825,7 +930,7 @@ void orc_destroy(orc_system* s)
     free(s->lj1); free(s->lj2); free(s->rcutsq); free(s->ronsq); free(s->gamma);
     free(s->bond_a); free(s->bond_b); free(s->bond_type); free(s->bond_K); free(s->bond_r0); free(s->bond_lj1);
     free(s->bond_lj2); free(s->pair_force); free(s->bond_force); free(s->pair_virial); free(s->bond_virial);
-    free(s->ex_n); free(s->ex_list);
+    free(s->ex_n); free(s->ex_list); free(s->p3); free(s->p4);
     free(s);
     }
 
@@ -872,7 +977,28 @@ int orc_setup_lj(orc_system* s, float r_buff, unsigned int check_period, const f
     s->nlist_alloc = 8 * (size_t)s->N; s->nlist = (unsigned int*)calloc(s->nlist_alloc ? s->nlist_alloc : 1, 4);
     cl_dimensions(s, s->rcut_max_max + s->r_buff);          /* NeighborListBinned.cc:56-76 */
     s->have_nlist = 1; s->force_update = 1; s->cl_force = 1; s->nl_first = 1;
+    s->pair_kind = 0;
     return 0;
+    }
+
+/* md.pair.<evaluator>: 0 lj, 1 gauss, 2 yukawa, 3 mie, 4 force_shifted_lj, 5 morse; params4 = ntypes x ntypes x 4 */
+int orc_setup_pair(orc_system* s, int evaluator, float r_buff, unsigned int check_period, const float* rcut,
+                   const float* params4, const float* ron, int shift_mode)
+    {
+    const unsigned int n2 = s->ntypes * s->ntypes;
+    float* a = (float*)calloc(n2, 4);
+    float* b = (float*)calloc(n2, 4);
+    free(s->p3); free(s->p4);
+    s->p3 = (float*)calloc(n2, 4); s->p4 = (float*)calloc(n2, 4);
+    for (unsigned int k = 0; k < n2; k++)
+        {
+        a[k] = params4[4 * k]; b[k] = params4[4 * k + 1]; s->p3[k] = params4[4 * k + 2]; s->p4[k] = params4[4 * k + 3];
+        }
+    int rc = orc_setup_lj(s, r_buff, check_period, rcut, a, b, ron, shift_mode);
+    free(a); free(b);
+    if (evaluator < 0 || evaluator > 5) { snprintf(s->error, sizeof(s->error), "unknown pair evaluator"); return 1; }
+    s->pair_kind = evaluator;
+    return rc;
     }
 
 void orc_set_virial(orc_system* s, int on) { s->compute_virial = on; }

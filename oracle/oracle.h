@@ -34,6 +34,9 @@ int orc_set_bonds(orc_system* s, unsigned int nbonds, const unsigned int* tags2,
 int orc_setup_bond(orc_system* s, int kind, const float* K, const float* r0, const float* lj1, const float* lj2);
 int orc_exclusions_from_bonds(orc_system* s, int on);
 void orc_get_force_component(orc_system* s, int which, float* force4, float* virial6);
+/* md.pair.<evaluator> (0 lj, 1 gauss, 2 yukawa, 3 mie, 4 force_shifted_lj, 5 morse), params4 = ntypes x ntypes x 4 floats */
+int orc_setup_pair(orc_system* s, int evaluator, float r_buff, unsigned int check_period, const float* rcut,
+                   const float* params4, const float* ron, int shift_mode);
 void orc_set_virial(orc_system* s, int on);
 int orc_setup_integrator(orc_system* s, float dt);
 int orc_add_nve(orc_system* s, int limit, float limit_val, int zero_force);

@@ -52,6 +52,7 @@ def lib():
         L.orc_get_cell_dims.argtypes = [vp, vp]
         L.orc_get_cell_list.argtypes = [vp, vp, vp]
         L.orc_get_thermo.argtypes = [vp, vp]
+        L.orc_setup_pair.argtypes = [vp, C.c_int, C.c_float, C.c_uint, vp, vp, vp, C.c_int]
         L.orc_set_bonds.argtypes = [vp, C.c_uint, vp, vp, C.c_uint]
         L.orc_setup_bond.argtypes = [vp, C.c_int, vp, vp, vp, vp]
         L.orc_exclusions_from_bonds.argtypes = [vp, C.c_int]
@@ -107,6 +108,17 @@ class OracleSystem:
         ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
         self._check(lib().orc_setup_lj(self.h, C.c_float(r_buff), int(check_period), _ptr(rc), _ptr(lj1), _ptr(lj2),
                                        _ptr(ron), int(shift_mode)))
+
+    def setup_pair(self, kind, r_cut, r_buff=0.4, check_period=1, full=True, shift_mode=0, r_on=None, **coeffs):
+        from hoomd_b200 import _lib as B  # coefficient processing only (pure numpy)
+        assert full
+        nt = self.ntypes
+        bc = lambda x: np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), (nt, nt)))
+        prm = B.pair_params(kind, nt, **coeffs)
+        rc = np.ascontiguousarray(bc(r_cut).astype(np.float32))
+        ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
+        self._check(lib().orc_setup_pair(self.h, B.PAIR_KINDS[kind], C.c_float(r_buff), int(check_period), _ptr(rc),
+                                         _ptr(prm), _ptr(ron), int(shift_mode)))
 
     # ---- BondData + md.bond.* + nlist exclusions (same surface as hoomd_b200.System / oracle.ref.RefSystem) ----
     def set_bonds(self, bonds, types=None, n_bond_types=None):

@@ -34,6 +34,8 @@ def lib():
         _lib.ref_setup_bond.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.ref_nlist_exclusions_from_bonds.argtypes = [C.c_void_p, C.c_int]
         _lib.ref_get_bond_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.ref_setup_pair.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_int]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
         for name in ("ref_destroy", "ref_last_error", "ref_get_N", "ref_get_timestep", "ref_get_virial_pitch",
@@ -132,6 +134,17 @@ class RefSystem:
         v = np.empty((6, self.N), np.float32) if virial else None
         lib().ref_get_bond_forces(self.h, _ptr(f), _ptr(v))
         return f, v
+
+    def setup_pair(self, kind, r_cut, r_buff=0.4, check_period=1, full=True, shift_mode=0, r_on=None, **coeffs):
+        """md.pair.<kind> (gauss | yukawa | mie | force_shifted_lj | morse | lj) on the reference's PotentialPair<evaluator>"""
+        from hoomd_b200 import _lib as B  # coefficient processing only (pure numpy, hoomd/md/pair.py process_coeff)
+        nt = self.ntypes
+        bc = lambda x: np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), (nt, nt)))
+        prm = B.pair_params(kind, nt, **coeffs)
+        rc = np.ascontiguousarray(bc(r_cut).astype(np.float32))
+        ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
+        self._check(lib().ref_setup_pair(self.h, B.PAIR_KINDS[kind], C.c_float(r_buff), int(check_period), int(full),
+                                         _ptr(rc), _ptr(prm), _ptr(ron), int(shift_mode)))
 
     def set_virial(self, on=True):
         lib().ref_set_virial(self.h, int(on))

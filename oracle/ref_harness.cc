@@ -41,7 +41,7 @@ struct RefSystem
     std::shared_ptr<ParticleGroup> group_all;
     std::shared_ptr<CellList> cl;
     std::shared_ptr<NeighborListBinned> nlist;
-    std::shared_ptr<PotentialPairLJ> lj;
+    std::shared_ptr<ForceCompute> lj;     // the pair force: PotentialPairLJ or another PotentialPair<evaluator>
     std::shared_ptr<ForceCompute> bond;   // PotentialBondFENE or PotentialBondHarmonic (md.bond.fene / md.bond.harmonic)
     std::shared_ptr<IntegratorTwoStep> integrator;
     std::shared_ptr<TwoStepNVE> nve;
@@ -65,6 +65,32 @@ void apply_flags(RefSystem* s)
         flags[pdata_flag::isotropic_virial] = 1;
         }
     s->pdata->setFlags(flags);
+    }
+} // namespace
+
+namespace
+{
+inline void make_param(Scalar2& p, const float* q) { p = make_scalar2(q[0], q[1]); }
+inline void make_param(Scalar4& p, const float* q) { p = make_scalar4(q[0], q[1], q[2], q[3]); }
+
+template<class P>
+std::shared_ptr<ForceCompute> make_pair(RefSystem* s, const float* rcut, const float* params4, const float* ron,
+                                        int shift_mode)
+    {
+    unsigned int nt = s->pdata->getNTypes();
+    std::shared_ptr<P> f(new P(s->sysdef, s->nlist));
+    for (unsigned int i = 0; i < nt; i++)
+        for (unsigned int j = i; j < nt; j++)
+            {
+            typename P::param_type prm;
+            make_param(prm, params4 + 4 * (i * nt + j));
+            f->setParams(i, j, prm);
+            f->setRcut(i, j, rcut[i * nt + j]);
+            if (ron) f->setRon(i, j, ron[i * nt + j]);
+            s->nlist->setRCutPair(i, j, rcut[i * nt + j]);
+            }
+    f->setShiftMode((typename P::energyShiftMode)shift_mode);
+    return f;
     }
 } // namespace
 
@@ -225,16 +251,43 @@ int ref_setup_lj(void* h, float r_buff, int check_period, int full_storage, cons
     s->nlist = std::shared_ptr<NeighborListBinned>(new NeighborListBinned(s->sysdef, Scalar(0.0), r_buff, s->cl));
     s->nlist->setEvery(check_period, true);
     s->nlist->setStorageMode(full_storage ? NeighborList::full : NeighborList::half);
-    s->lj = std::shared_ptr<PotentialPairLJ>(new PotentialPairLJ(s->sysdef, s->nlist));
+    std::shared_ptr<PotentialPairLJ> lj(new PotentialPairLJ(s->sysdef, s->nlist));
     for (unsigned int i = 0; i < nt; i++)
         for (unsigned int j = i; j < nt; j++)
             {
-            s->lj->setParams(i, j, make_scalar2(lj1[i * nt + j], lj2[i * nt + j]));
-            s->lj->setRcut(i, j, rcut[i * nt + j]);
-            if (ron) s->lj->setRon(i, j, ron[i * nt + j]);
+            lj->setParams(i, j, make_scalar2(lj1[i * nt + j], lj2[i * nt + j]));
+            lj->setRcut(i, j, rcut[i * nt + j]);
+            if (ron) lj->setRon(i, j, ron[i * nt + j]);
             s->nlist->setRCutPair(i, j, rcut[i * nt + j]);
             }
-    s->lj->setShiftMode((PotentialPairLJ::energyShiftMode)shift_mode);
+    lj->setShiftMode((PotentialPairLJ::energyShiftMode)shift_mode);
+    s->lj = lj;
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+
+//! md.nlist.cell + md.pair.<evaluator>: 0 lj, 1 gauss, 2 yukawa, 3 mie, 4 force_shifted_lj, 5 morse
+/*! \param params4 ntypes x ntypes x 4 floats: the evaluator's param_type padded to four components */
+int ref_setup_pair(void* h, int evaluator, float r_buff, int check_period, int full_storage, const float* rcut,
+                   const float* params4, const float* ron, int shift_mode)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->cl = std::shared_ptr<CellList>(new CellList(s->sysdef));
+    s->nlist = std::shared_ptr<NeighborListBinned>(new NeighborListBinned(s->sysdef, Scalar(0.0), r_buff, s->cl));
+    s->nlist->setEvery(check_period, true);
+    s->nlist->setStorageMode(full_storage ? NeighborList::full : NeighborList::half);
+    switch (evaluator)
+        {
+        case 0: s->lj = make_pair<PotentialPairLJ>(s, rcut, params4, ron, shift_mode); break;
+        case 1: s->lj = make_pair<PotentialPairGauss>(s, rcut, params4, ron, shift_mode); break;
+        case 2: s->lj = make_pair<PotentialPairYukawa>(s, rcut, params4, ron, shift_mode); break;
+        case 3: s->lj = make_pair<PotentialPairMie>(s, rcut, params4, ron, shift_mode); break;
+        case 4: s->lj = make_pair<PotentialPairForceShiftedLJ>(s, rcut, params4, ron, shift_mode); break;
+        case 5: s->lj = make_pair<PotentialPairMorse>(s, rcut, params4, ron, shift_mode); break;
+        default: throw std::runtime_error("unknown pair evaluator");
+        }
     REF_CATCH(s, 1)
     return 0;
     }

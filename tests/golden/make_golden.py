@@ -60,11 +60,53 @@ def kremer_grest():
     np.savez_compressed(os.path.join(HERE, "kremer_grest.npz"), **res)
 
 
+PAIR_CASES = {  # evaluator: (coefficients, r_cut, r_on for xplor)
+    "gauss": (dict(epsilon=2.0, sigma=0.9), 2.5, 1.8),
+    "yukawa": (dict(epsilon=1.5, kappa=1.2), 2.5, 1.8),
+    "mie": (dict(epsilon=1.0, sigma=1.0, n=13.0, m=7.0), 2.5, 1.8),
+    "force_shifted_lj": (dict(epsilon=1.0, sigma=1.0, alpha=1.0), 2.5, 1.8),
+    "morse": (dict(D0=1.2, alpha=3.0, r0=1.1), 2.5, 1.8),
+}
+
+
+def pair_evaluators():
+    """(9) the other PotentialPair<evaluator> instantiations on a melted 216-particle liquid: force / energy / virial for
+    every evaluator x energy-shift mode, and a 30-step Langevin trajectory per evaluator"""
+    pos, vel, L = workloads.sc_lattice(6, (1.0 / 0.5) ** (1.0 / 3.0), kT=1.0, seed=8)
+    s = ref.RefSystem(pos, (L, L, L), vel4=vel)
+    s.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+    s.setup_integrator(0.005)
+    s.add_langevin(1.0, 3)
+    s.run(300)
+    st = s.particles()
+    res = dict(pos=st["pos"], vel=st["vel"], image=st["image"], L=L)
+    for kind, (co, rc, ron) in PAIR_CASES.items():
+        for mode, name in ((0, "none"), (1, "shift"), (2, "xplor")):
+            q = ref.RefSystem(st["pos"], (L, L, L), vel4=st["vel"])
+            q.setup_pair(kind, r_cut=rc, r_buff=0.4, full=True, shift_mode=mode, r_on=ron if mode == 2 else None, **co)
+            q.set_virial(True)
+            q.compute_forces(0)
+            f, v = q.forces()
+            res["%s_%s_force" % (kind, name)], res["%s_%s_virial" % (kind, name)] = f, v
+        q = ref.RefSystem(st["pos"], (L, L, L), vel4=st["vel"], image=st["image"])
+        q.setup_pair(kind, r_cut=rc, r_buff=0.4, full=True, shift_mode=1, **co)
+        q.setup_integrator(0.005)
+        q.add_langevin(1.0, 5)
+        q.run(30)
+        p = q.particles()
+        res[kind + "_traj_pos"], res[kind + "_traj_vel"] = p["pos"], p["vel"]
+    np.savez_compressed(os.path.join(HERE, "pair_evaluators.npz"), **res)
+
+
 def main():
     if len(sys.argv) > 1 and sys.argv[1] == "kg":
         kremer_grest()
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "pairs":
+        pair_evaluators()
+        return
     kremer_grest()
+    pair_evaluators()
     out = {}
     # (1) Saru stream: (tag, timestep, seed) triples
     rng = np.random.default_rng(0)

@@ -182,3 +182,48 @@ def check_kremer_grest(make, rtol, bit_exact=False, traj_bit_exact=False, pos_to
         th = s.thermo()
         for k, w in zip(("ke", "pe", "T", "P", "ndof"), g[method + "_thermo"]):
             assert abs(th[k] - w) <= 2e-4 * abs(w), (method, k, th[k], w)
+
+
+PAIR_CASES = {  # as tests/golden/make_golden.py
+    "gauss": (dict(epsilon=2.0, sigma=0.9), 2.5, 1.8),
+    "yukawa": (dict(epsilon=1.5, kappa=1.2), 2.5, 1.8),
+    "mie": (dict(epsilon=1.0, sigma=1.0, n=13.0, m=7.0), 2.5, 1.8),
+    "force_shifted_lj": (dict(epsilon=1.0, sigma=1.0, alpha=1.0), 2.5, 1.8),
+    "morse": (dict(D0=1.2, alpha=3.0, r0=1.1), 2.5, 1.8),
+}
+
+
+def check_pair_evaluators(make, rtol, bit_exact=False, kinds=None, pos_tol=2e-4, vel_tol=2e-3):
+    """md.pair.gauss / yukawa / mie / force_shifted_lj / morse: forces, energies, virials in the three energy-shift modes
+    and a 30-step Langevin trajectory against the reference (fixture pair_evaluators)"""
+    g = load("pair_evaluators")
+    L = float(g["L"])
+    eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+    for kind, (co, rc, ron) in PAIR_CASES.items():
+        if kinds and kind not in kinds:
+            continue
+        for mode, name in ((0, "none"), (1, "shift"), (2, "xplor")):
+            s = make(g["pos"], (L, L, L), 1, vel=g["vel"])
+            s.setup_pair(kind, r_cut=rc, r_buff=0.4, shift_mode=mode, r_on=ron if mode == 2 else None, **co)
+            s.set_virial(True)
+            s.compute_forces(0)
+            f, v = s.forces()
+            fr, vr = g["%s_%s_force" % (kind, name)], g["%s_%s_virial" % (kind, name)]
+            if bit_exact:
+                assert eq(f, fr) and eq(v, vr), (kind, name)
+                continue
+            fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
+            assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, (kind, name)
+            assert _rel(f[:, 3], fr[:, 3]) < rtol, (kind, name)
+            assert _rel(v, vr) < rtol, (kind, name)
+        s = make(g["pos"], (L, L, L), 1, vel=g["vel"], image=g["image"])
+        s.setup_pair(kind, r_cut=rc, r_buff=0.4, shift_mode=1, **co)
+        s.setup_integrator(0.005)
+        s.add_langevin(1.0, 5)
+        s.run(30)
+        p = s.particles()
+        if bit_exact:
+            assert eq(p["pos"], g[kind + "_traj_pos"]) and eq(p["vel"], g[kind + "_traj_vel"]), kind
+        else:
+            assert np.abs(p["pos"][:, :3] - g[kind + "_traj_pos"][:, :3]).max() < pos_tol, kind
+            assert np.abs(p["vel"][:, :3] - g[kind + "_traj_vel"][:, :3]).max() < vel_tol, kind

@@ -178,3 +178,8 @@ def test_bonded_restatement_matches_reference_bitwise(kind, excl):
     assert np.array_equal(ba[0][:, :3].view(np.uint32), bb[0][:, :3].view(np.uint32))
     assert np.array_equal(ba[1].view(np.uint32), bb[1].view(np.uint32))
     assert np.array_equal(fa[0][:, :3].view(np.uint32), fb[0][:, :3].view(np.uint32))
+
+
+def test_pair_evaluators_golden_bit_exact():
+    """Gauss, Yukawa, Mie, force-shifted LJ, Morse in all energy-shift modes + trajectories"""
+    G.check_pair_evaluators(make, 0.0, bit_exact=True)
