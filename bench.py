@@ -32,8 +32,23 @@ WORKLOADS = {
     # BASELINE configs[3]: 10,000 chains x 100 beads, WCA (LJ r_cut 2^(1/6), shift) + FENE (K 30, r0 1.5), bond exclusions
     "kg1m": (100, 0.85, 1.0, "Kremer-Grest polymer melt 1,000,000 beads (10,000 x 100), rho 0.85, WCA + FENE, r_buff 0.4, "
                              "NVE dt 0.005"),
+    # BASELINE configs[2]: 80:20 binary mixture (64^3 = 262,144 particles, the closest cube to 256k), per-pair r_cut, Langevin
+    "ka256k": (64, 1.2, 1.0, "Kob-Andersen 80:20 binary LJ 262,144 particles, rho 1.2, r_cut 2.5 sigma_ab (shifted), r_buff 0.4, "
+                             "Langevin kT 1.0 dt 0.005"),
 }
 KG_CHAIN = 100
+
+
+def n_types(workload):
+    return 2 if workload.startswith("ka") else 1
+
+
+def add_method(s, workload, kT):
+    """the integration method the BASELINE config names: Langevin for Kob-Andersen, NVE otherwise"""
+    if workload.startswith("ka"):
+        s.add_langevin(kT, 7)
+    else:
+        s.add_nve()
 BYTES_PER_PARTICLE_STEP = 420.0   # SURVEY 8(d) planning figure (NVE, fused net force, amortised rebuild)
 FLOPS_PER_PARTICLE_STEP = 1800.0
 PAIR_BYTES_PER_PARTICLE = 172.0   # pair kernel: pos_i 16 + n_neigh 4 + head 4 + nlist 4*32.9 + force 16 (SURVEY 8d)
@@ -105,6 +120,11 @@ def _snapshot(workload):
     n_side, rho, kT, _ = WORKLOADS[workload]
     if workload.startswith("kg"):
         return workloads.polymer_lattice(n_side, KG_CHAIN, rho=rho, kT=kT, seed=42)
+    if workload.startswith("ka"):
+        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42, ntypes=2,
+                                           type_fractions=[0.8, 0.2])
+        pos[:, :3] += np.random.default_rng(3).normal(0, 0.03, (len(pos), 3)).astype(np.float32)
+        return pos, vel, L, None
     return _lj_snapshot(workload) + (None,)
 
 
@@ -115,6 +135,9 @@ def setup_forces(s, workload, bonds, **kw):
         s.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, shift_mode=1, **kw)
         s.setup_fene(k=30.0, r0=1.5)
         s.exclusions_from_bonds(True)
+    elif workload.startswith("ka"):
+        from hoomd_b200 import workloads
+        s.setup_lj(shift_mode=1, r_buff=0.4, **workloads.KA_PARAMS, **kw)
     else:
         s.setup_lj(r_cut=3.0, r_buff=0.4, **kw)
 
@@ -124,13 +147,19 @@ def make_state(workload, rank=0):
     import hoomd_b200
     _, _, kT, _ = WORKLOADS[workload]
     pos, vel, L, bonds = _snapshot(workload)
-    s = hoomd_b200.System(pos, (L, L, L), vel4=vel)
+    s = hoomd_b200.System(pos, (L, L, L), vel4=vel, ntypes=n_types(workload))
     setup_forces(s, workload, bonds)
-    s.setup_integrator(0.005)
-    s.add_langevin(kT, 42)
+    nequil = EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 2000)
     s.set_sorter(300)
     s.set_tuning(use_graph=USE_GRAPH)
-    s.run(EQUIL_STEPS if EQUIL_STEPS is not None else (10000 if len(pos) <= 100000 else 2000))
+    if workload.startswith("ka"):
+        # the compressed sc start (rho 1.2) relaxes with a short time step first
+        s.setup_integrator(0.002)
+        s.add_langevin(kT, 42)
+        s.run(nequil)
+    s.setup_integrator(0.005)
+    s.add_langevin(kT, 42)
+    s.run(nequil)
     p = s.particles()
     s.close()
     # back to TAG order: the bond table names particles by tag (= index of a freshly created system)
@@ -142,10 +171,11 @@ def make_state(workload, rank=0):
 
 def new_system(state, L, device=0, workload="lj64k"):
     import hoomd_b200
-    s = hoomd_b200.System(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], device=device)
+    s = hoomd_b200.System(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], device=device,
+                          ntypes=n_types(workload))
     setup_forces(s, workload, state.get("bonds"))
     s.setup_integrator(0.005)
-    s.add_nve()
+    add_method(s, workload, WORKLOADS[workload][2])
     s.set_sorter(300)  # hoomd.update.sort default period on the GPU (hoomd/update.py:258-263)
     s.set_tuning(use_graph=USE_GRAPH)
     return s
@@ -192,18 +222,19 @@ def run_reference(args):
         state = dict(pos=pos, vel=vel, image=np.zeros((len(pos), 3), np.int32), bonds=bonds)
     nbt = 1 if state.get("bonds") is not None else 0
     if ref.available():
-        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt)
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt,
+                          ntypes=n_types(workload))
         setup_forces(s, workload, state.get("bonds"), full=False)  # CPU md.pair.lj default: half list + Newton's 3rd law
         kind, cores = "reference", 1
         s.set_sorter(100)  # hoomd.update.sort default period on the CPU
     else:
         cores = os.cpu_count() or 1
         s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores,
-                                  n_bond_types=nbt)
+                                  n_bond_types=nbt, ntypes=n_types(workload))
         setup_forces(s, workload, state.get("bonds"))
         kind = "port"
     s.setup_integrator(0.005)
-    s.add_nve()
+    add_method(s, workload, WORKLOADS[workload][2])
     for _ in range(args.warmup):
         s.run(md_steps)
     t = []
@@ -233,19 +264,20 @@ def cpu_baseline(state, L, budget_s=15.0, workload="lj64k"):
     N = len(state["pos"])
     nbt = 1 if state.get("bonds") is not None else 0
     if ref.available():
-        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt)
+        s = ref.RefSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], n_bond_types=nbt,
+                          ntypes=n_types(workload))
         setup_forces(s, workload, state.get("bonds"), full=False)
         kind, cores = "reference", 1
     elif oracle_c.available():
         cores = os.cpu_count() or 1
         s = oracle_c.OracleSystem(state["pos"], (L, L, L), vel4=state["vel"], image=state["image"], threads=cores,
-                                  n_bond_types=nbt)
+                                  n_bond_types=nbt, ntypes=n_types(workload))
         setup_forces(s, workload, state.get("bonds"))
         kind = "port"
     else:
         return None
     s.setup_integrator(0.005)
-    s.add_nve()
+    add_method(s, workload, WORKLOADS[workload][2])
     t0 = time.perf_counter()
     s.run(5)
     per = (time.perf_counter() - t0) / 5
@@ -254,7 +286,7 @@ def cpu_baseline(state, L, budget_s=15.0, workload="lj64k"):
     s.run(n)
     dt = time.perf_counter() - t0
     return {"value": n / dt, "unit": "timesteps/s", "cores": cores, "kind": kind,
-            "sample": "%d NVE steps of the same %d-particle state (%.1f s), %s" % (
+            "sample": "%d MD steps of the same %d-particle state (%.1f s), %s" % (
                 n, N, dt, "HOOMD-blue 2.3.0 CPU classes built from /root/reference (oracle/_ref), half list, serial"
                 if kind == "reference" else "C restatement oracle/oracle.c, OpenMP")}
 
