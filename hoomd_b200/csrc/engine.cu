@@ -771,7 +771,7 @@ static void enqueue_rebuild(b200_system* s, const unsigned int* enable, const fl
     nlist_args(s, na);
     na.d_pos = (const float*)pos;
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
-    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream, 1));
     // filterNlist runs on the complete rows; after an overflow the rows are discarded anyway (checkpoint replay)
     enqueue_nlist_filter(s, enable);
     }
@@ -978,9 +978,12 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     if (st.overflow)
         {
         CUDA_OK(cudaMemsetAsync(s->cl_conditions.p, 0, sizeof(unsigned int) * 3, s->stream));
-        // Nmax overflow needs a host reallocation: restore the checkpoint and replay the chunk with the reference's
-        // host protocol (NeighborList.cc:226-244).  The trajectory is deterministic, so the replay is exact.
+        // Nmax overflow needs a host reallocation (NeighborList.cc:226-244): grow Nmax from the counts the overflowing
+        // rebuild recorded -- the very values checkConditions would have seen --, restore the checkpoint and run the chunk
+        // again.  The trajectory is deterministic, so the replay is exact.
         s->num_overflows += 1;
+        const bool grew = !s->tile_on && nlist_check_conditions(s);
+        if (grew) nlist_build_head_list(s);
         CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
@@ -1018,7 +1021,10 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
             }
         CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         s->cl_force = true;
-        for (unsigned int k = 0; k < chunk; k++) host_step(s);
+        if (grew)
+            run_chunk_device(s, chunk); // device-driven again with the larger rows (recurses on a further overflow)
+        else
+            for (unsigned int k = 0; k < chunk; k++) host_step(s); // the reference's host protocol, step by step
         return;
         }
     check_bond_flags(s);

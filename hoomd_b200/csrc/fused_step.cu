@@ -60,13 +60,17 @@ __global__ void k_graph_pre(StepState* st, cudaGraphConditionalHandle handle)
     }
 
 __global__ void k_post_rebuild(StepState* st, unsigned int* __restrict__ conditions,
-                               const unsigned int* __restrict__ Nmax)
+                               const unsigned int* __restrict__ Nmax, int stop_on_overflow)
     {
     if (!st->need_rebuild) return;
     for (unsigned int t = 0; t < st->ntypes; t++)
         {
         if (conditions[t] > Nmax[t]) st->overflow = 1u;
         }
+    // single GPU: the rest of the chunk would run on truncated lists and is discarded anyway -- turn the remaining
+    // launches into no-ops, so that `conditions` keeps exactly the counts of the overflowing rebuild (what the reference's
+    // checkConditions sees, hoomd/md/NeighborList.cc:1389-1405) for the host to grow Nmax from
+    if (stop_on_overflow && st->overflow) st->steps_left = 0u;
     }
 
 
@@ -110,9 +114,9 @@ cudaError_t launch_graph_pre(StepState* st, unsigned long long cond_handle, cuda
     }
 
 cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
-                                cudaStream_t stream)
+                                cudaStream_t stream, int stop_on_overflow)
     {
-    k_post_rebuild<<<1, 1, 0, stream>>>(st, nlist_conditions, Nmax);
+    k_post_rebuild<<<1, 1, 0, stream>>>(st, nlist_conditions, Nmax, stop_on_overflow);
     return cudaGetLastError();
     }
 
