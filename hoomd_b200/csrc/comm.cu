@@ -311,8 +311,13 @@ __global__ void __launch_bounds__(256) k_mg_ghost_plan(const __grid_constant__ M
         nhi[a] = active && c.split[a] && (x[a] >= c.hi[a] - c.r_ghost);
         any |= nlo[a] | nhi[a];
         }
-    if (!__any_sync(0xffffffffu, any)) return; // interior warp
+    if (!__any_sync(0xffffffffu, any))
+        {
+        if (active) l.pplan_n[i] = 0; // interior warp
+        return;
+        }
     const unsigned int ptag = active ? l.tag[i] : 0u;
+    unsigned int nplan = 0;
     // Slots are handed out per warp (one atomic per warp and direction, lanes ranked by ballot): the particles of a
     // warp are neighbors along the space-filling curve, so their ghost copies land next to each other on the receiver
     // and its position gathers keep their locality.
@@ -334,11 +339,14 @@ __global__ void __launch_bounds__(256) k_mg_ghost_plan(const __grid_constant__ M
                 {
                 l.plan_src[c.seg_off[d] + slot] = i;
                 c.peer_tag[d][c.Ncap + c.seg_off[d] + slot] = ptag;
+                l.pplan[(size_t)nplan * c.Ncap + i] = ((unsigned int)d << 27) | (c.seg_off[d] + slot); // <= 7 destinations
+                nplan++;
                 }
             else
                 atomicOr(&l.ms->error, 2u);
             }
         }
+    if (active) l.pplan_n[i] = (unsigned char)nplan;
     }
 
 // every MD step: one store per (boundary particle, destination) into the neighbor's position buffer

@@ -86,6 +86,8 @@ struct MgLocal // plain device arrays of the owner used by the rebuild kernels
     unsigned int* hole_mark;   // [Ncap] == rebuild_id where the slot was vacated in this rebuild
     unsigned int* plan_src;    // [sum seg_cap] local index of the particle feeding each remote ghost slot
     const unsigned char* slot_dir; // [sum seg_cap] direction code of each ghost slot (constant)
+    unsigned int* pplan;       // [7 * Ncap] reverse plan: ghost slots fed by particle i (k_md_step's fused ghost update)
+    unsigned char* pplan_n;    // [Ncap]
     };
 
 // all-ranks barrier of kind k; kind 0 also carries the distance-check vote and takes the rebuild decision

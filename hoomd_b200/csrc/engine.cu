@@ -209,7 +209,10 @@ struct b200_system
     DevBuf<MgState> d_ms;
     MgState* h_ms = nullptr;         // pinned
     DevBuf<unsigned int> holes, low_holes, hole_mark, plan_src;
-    DevBuf<unsigned char> slot_dir;
+    DevBuf<unsigned char> slot_dir, pplan_n;
+    DevBuf<unsigned int> pplan;
+    DevBuf<GhostSendTable> gs_table;
+    bool fused_ghosts = true;        // ghost update inside k_md_step (HOOMD_B200_FUSED_GHOSTS=0: stand-alone kernel)
 
     // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
     int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
@@ -320,6 +323,11 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.d_N = s->mg ? &s->d_state.p->N : nullptr; a.mg = s->mg ? 1 : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
+    if (s->mg && s->fused_ghosts && s->mg_connected)
+        {
+        a.gs.tab = s->gs_table.p; a.gs.pplan = s->pplan.p; a.gs.pplan_n = s->pplan_n.p; a.gs.slot_dir = s->slot_dir.p;
+        a.gs.pitch = s->Ncap;
+        }
     if (s->bond_kind >= 0)
         {
         a.extra_force = s->bond_force.p; a.extra_virial = s->bond_virial.p; a.extra_virial_pitch = s->virial_pitch;
@@ -1067,6 +1075,7 @@ static void sys_open_device(b200_system* s)
     CUDA_OK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     // developer overrides of the pair path: HOOMD_B200_PAIR_MODE = -1 | 0 | 1, HOOMD_B200_TILE = "bx,by,bz,tpp"
     if (const char* m = getenv("HOOMD_B200_PAIR_MODE")) s->pair_mode = atoi(m);
+    if (const char* m = getenv("HOOMD_B200_FUSED_GHOSTS")) s->fused_ghosts = atoi(m) != 0;
     if (const char* m = getenv("HOOMD_B200_TAG_TABLES")) s->idx_tables = atoi(m) == 0; // A/B: tag-keyed bond / exclusion rows
     if (const char* t = getenv("HOOMD_B200_TILE"))
         {
@@ -1786,6 +1795,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
         FusedStepArgs fa;
         fused_args(s, fa);
+        fa.gs.tab = nullptr; // scratch steps must not write into the neighbors' ghost regions
         CUDA_OK(cudaStreamSynchronize(s->stream));
         CUDA_OK(cudaEventRecord(e0, s->stream));
         for (unsigned int k = 0; k < iters; k++) enqueue_md_step(s, fa, (int)(k & 1), 0ull, 0);

@@ -135,6 +135,9 @@ static void mg_setup(b200_system* s, const b200_mg_params& p)
     for (int d = 0; d < MG_NDIR; d++)
         for (unsigned int k = 0; k < c.seg_cap[d]; k++) sd[c.seg_off[d] + k] = (unsigned char)d;
     s->slot_dir.upload(sd.data(), sd.size(), s->stream);
+    s->pplan.alloc(7 * (size_t)s->Ncap);
+    s->pplan_n.alloc(s->Ncap);
+    s->gs_table.alloc(1);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     }
 
@@ -152,6 +155,8 @@ static void mg_bind_local(b200_system* s)
     l.hole_mark = s->hole_mark.p;
     l.plan_src = s->plan_src.p;
     l.slot_dir = s->slot_dir.p;
+    l.pplan = s->pplan.p;
+    l.pplan_n = s->pplan_n.p;
     }
 
 static void mg_connect(b200_system* s, const unsigned char* handles)
@@ -179,6 +184,17 @@ static void mg_connect(b200_system* s, const unsigned char* handles)
         c.peer_mig[d] = (MigElem*)(pb + s->off_mig) + (size_t)d * c.mig_cap;
         c.peer_mig_cnt[d] = (unsigned int*)(pb + s->off_migcnt) + d;
         }
+    // device copy of what the fused ghost update needs per direction
+    GhostSendTable t;
+    memset(&t, 0, sizeof(t));
+    for (int d = 0; d < MG_NDIR; d++)
+        {
+        for (int k = 0; k < 3; k++) t.shift[d][k] = c.shift[d][k];
+        t.peer_posA[d] = c.peer_posA[d];
+        t.peer_posB[d] = c.peer_posB[d];
+        }
+    s->gs_table.upload(&t, 1, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
     mg_bind_local(s);
     s->mg_connected = true;
     invalidate_graph(s);
@@ -304,11 +320,11 @@ static void mg_build_graph(b200_system* s)
         CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
         cudaGraph_t body0 = add_if_node(s, graph, h0);
         enqueue_md_step(s, fa, 0, 0ull, 0);
-        CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+        if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
         CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
         cudaGraph_t body1 = add_if_node(s, graph, h1);
         enqueue_md_step(s, fa, 1, 0ull, 0);
-        CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
         cudaGraph_t out = nullptr;
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
@@ -371,11 +387,11 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
                 CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
                 mg_enqueue_rebuild(s, enable, s->pos.p, 0);
                 enqueue_md_step(s, fa, 0, 0ull, 0);
-                CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+                if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
                 CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
                 mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
                 enqueue_md_step(s, fa, 1, 0ull, 0);
-                CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+                if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
                 }
             }
         else
@@ -385,7 +401,7 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_check_errors(s);
         cell_list_check_conditions(s);
         const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-        s->kernels_last_run += 2ull + 6ull * nreplay
+        s->kernels_last_run += 2ull + (fa.gs.tab ? 4ull : 6ull) * nreplay
                                + (MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u) * rebuilds;
         s->num_updates += st.num_updates;
         s->num_forced += st.num_forced;

@@ -37,6 +37,25 @@ unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot); // launc
 cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream);
 unsigned int pick_pair_tpp(unsigned int N);
 
+// Multi-GPU: ghost update fused into the MD step.  The owner of a boundary particle writes its new position (+ the
+// periodic shift of the direction) straight into the neighbor ranks' position buffers over NVLink, from the same lane
+// that has just integrated it -- the stores of the first CTAs overlap the force work of the CTAs still running.
+// (hoomd/CommunicatorGPU.cc:2500-2870 beginUpdateGhosts / finishUpdateGhosts: pack, MPI send/recv, unpack.)
+struct GhostSendTable            // device-resident, constant between reconnects
+    {
+    float shift[27][3];
+    float4* peer_posA[27];
+    float4* peer_posB[27];
+    };
+struct GhostSendArgs
+    {
+    const GhostSendTable* tab;   // NULL = single GPU / ghost update by the stand-alone kernel
+    const unsigned int* pplan;   // [7 * pitch]: (direction << 27 | ghost slot) fed by particle i at [k * pitch + i], k < pplan_n[i]
+    const unsigned char* pplan_n;
+    const unsigned char* slot_dir;
+    unsigned int pitch;          // local capacity Ncap == ghost base of every rank's position buffer
+    };
+
 // fused_step.cu -- kernels of the device-driven step loop (group = all particles)
 struct FusedStepArgs
     {
@@ -52,6 +71,7 @@ struct FusedStepArgs
     // second ForceCompute (bond force), already evaluated at the positions this step reads: added to the pair force
     // before step two (Integrator::computeNetForce).  NULL = the pair force is the only force.
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch;
+    GhostSendArgs gs;             // multi-GPU: ghost update fused into k_md_step
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);

@@ -37,7 +37,26 @@ template<class Evaluator> struct MdStepArgs
     TileGeom tile; const unsigned int* cell_start; const uint4* ell4; unsigned int ell_pitch, ell_nmax;
     int force_only;           // compute and store the net force only (prepRun / stand-alone force evaluation)
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch; // second ForceCompute (bonds)
+    GhostSendArgs gs; int gs_buffer; // multi-GPU: fused ghost update into the peers' buffer gs_buffer (0 = A, 1 = B)
     };
+
+// write particle i's position into every ghost slot it feeds on the neighbor ranks (plain stores over NVLink)
+template<class Evaluator>
+__device__ __forceinline__ void md_step_send_ghosts(const MdStepArgs<Evaluator>& a, unsigned int i, const float4 p)
+    {
+    const unsigned int n = a.gs.pplan_n[i];
+    for (unsigned int k = 0; k < n; k++)
+        {
+        const unsigned int e = a.gs.pplan[(size_t)k * a.gs.pitch + i]; // direction in the top 5 bits, slot below
+        const unsigned int t = e & 0x07ffffffu, d = e >> 27;
+        float4 q = p;
+        q.x = __fadd_rn(q.x, a.gs.tab->shift[d][0]);
+        q.y = __fadd_rn(q.y, a.gs.tab->shift[d][1]);
+        q.z = __fadd_rn(q.z, a.gs.tab->shift[d][2]);
+        float4* dst = a.gs_buffer ? a.gs.tab->peer_posB[d] : a.gs.tab->peer_posA[d];
+        dst[a.gs.pitch + t] = q;
+        }
+    }
 
 constexpr int MD_BLOCK = 256;
 
@@ -87,6 +106,7 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         const float4 lp = a.last_pos[i];
         nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
         a.pos_out[i] = p;
+        if (a.gs.tab) md_step_send_ghosts(a, i, p);
         a.image[i] = img;
         // ---- NeighborList::distanceCheck, fixed box (hoomd/md/NeighborList.cc:992-1016) ----
         const float maxsq = a.maxsq[type_i];
@@ -96,7 +116,10 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         moved = dot_exact(dx) >= maxsq;
         }
     else if (a.copy_pos_on_last)
+        {
         a.pos_out[i] = pi4;
+        if (a.gs.tab) md_step_send_ghosts(a, i, pi4);
+        }
     a.vel[i] = v;
     return moved;
     }
@@ -153,6 +176,7 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.copy_pos_on_last = copy_pos_on_last;
     a.d_N = fa.d_N; a.mg = fa.mg;
     a.extra_force = fa.extra_force; a.extra_virial = fa.extra_virial; a.extra_virial_pitch = fa.extra_virial_pitch;
+    a.gs = fa.gs; a.gs_buffer = copy_pos_on_last ? 0 : 1; // phase 0 writes B, phase 1 writes A
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

@@ -327,6 +327,145 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
         }
     }
 
+// ---- warp-per-cell build for sparse cells --------------------------------------------------------------------------------
+// With ~3 particles per cell (bead-spring melt: rho 0.85, cell width 1.52) a 128-thread CTA per cell stages 81 candidates,
+// keeps one warp idle and pays two CTA barriers and a warp-0 prefix for ~250 distance tests: 0.75 of the 0.82 ms rebuild at
+// 1M beads went there (profiles/r1h_launches_host_kg1m.md).  Here every WARP owns a cell: its own staging slice, its own
+// prefix over the <=27 adjacent cells, __syncwarp instead of __syncthreads, particles of the cell one after the other
+// through the same nlist_scan_tile (same candidate order, same arithmetic => same list).  4 cells per CTA.
+constexpr int NW_WARPS = 4;
+constexpr int NW_CAP = 256; // staged candidates per warp and pass (multiple of 64)
+
+template<bool MULTI_TYPE, bool HALF>
+__global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* __restrict__ nlist,
+                                                                  unsigned int* __restrict__ n_neigh,
+                                                                  float4* __restrict__ last_pos,
+                                                                  unsigned int* __restrict__ conditions,
+                                                                  const unsigned int* __restrict__ Nmax,
+                                                                  const unsigned int* __restrict__ head_list,
+                                                                  unsigned int N,
+                                                                  const unsigned int* __restrict__ cell_start,
+                                                                  const float4* __restrict__ cell_xyzf,
+                                                                  const unsigned int* __restrict__ cell_type, uint3 dim,
+                                                                  Box box, const float* __restrict__ r_cut,
+                                                                  const float* __restrict__ r_listsq, unsigned int ntypes,
+                                                                  const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    extern __shared__ float4 s_all[];
+    __shared__ unsigned int s_beg_all[NW_WARPS][28], s_off_all[NW_WARPS][28];
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4* s_cand = s_all + warp * NW_CAP;
+    unsigned int* s_type = reinterpret_cast<unsigned int*>(s_all + NW_WARPS * NW_CAP) + warp * NW_CAP;
+    unsigned int* s_beg = s_beg_all[warp];
+    unsigned int* s_off = s_off_all[warp];
+
+    const unsigned int ncells = dim.x * dim.y * dim.z;
+    const unsigned int cell = blockIdx.x * NW_WARPS + warp;
+    if (cell >= ncells) return; // no CTA-wide barrier below: a warp may leave on its own
+    const unsigned int own_beg = cell_start[cell], own_end = cell_start[cell + 1];
+    if (own_beg == own_end) return;
+    const unsigned int bx = cell % dim.x, by = (cell / dim.x) % dim.y, bz = cell / (dim.x * dim.y);
+
+    int xs[3], ys[3], zs[3];
+    const int nx = axis_set(bx, dim.x, box.periodic.x, xs);
+    const int ny = axis_set(by, dim.y, box.periodic.y, ys);
+    const int nz = axis_set(bz, dim.z, box.periodic.z, zs);
+    const unsigned int nr = (unsigned int)(nx * ny * nz);
+    unsigned int beg = 0, len = 0;
+    if (lane < nr)
+        {
+        // (c, q, r) in lexicographic order == ascending cell id (id = (z*dimy + y)*dimx + x)
+        const int r = lane % nx, q = (lane / nx) % ny, c = lane / (nx * ny);
+        const int x = (r == 0) ? xs[0] : (r == 1) ? xs[1] : xs[2];
+        const int y = (q == 0) ? ys[0] : (q == 1) ? ys[1] : ys[2];
+        const int z = (c == 0) ? zs[0] : (c == 1) ? zs[1] : zs[2];
+        const unsigned int nc = ((unsigned int)z * dim.y + (unsigned int)y) * dim.x + (unsigned int)x;
+        beg = cell_start[nc];
+        len = cell_start[nc + 1] - beg;
+        }
+    unsigned int incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += t;
+        }
+    if (lane < 28)
+        {
+        s_beg[lane] = beg;
+        s_off[lane] = incl - len;
+        }
+    const unsigned int total = __shfl_sync(0xffffffffu, incl, nr - 1);
+    __syncwarp();
+    const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
+    const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
+    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
+    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
+    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+    const bool wrap_any = wx || wy || wz;
+
+    for (unsigned int pass = 0; pass < total; pass += NW_CAP)
+        {
+        const unsigned int cnt = min((unsigned int)NW_CAP, total - pass);
+        const unsigned int cnt_padded = (cnt + 63u) & ~63u;
+        if (pass) __syncwarp(); // the warp is done with the previous tile
+        for (unsigned int t = lane; t < cnt_padded; t += 32)
+            {
+            if (t < cnt)
+                {
+                const unsigned int g = pass + t;
+                unsigned int lo = 0, hi = nr;
+                while (hi - lo > 1)
+                    {
+                    const unsigned int mid = (lo + hi) >> 1;
+                    if (s_off[mid] <= g) lo = mid; else hi = mid;
+                    }
+                const unsigned int e = s_beg[lo] + (g - s_off[lo]);
+                s_cand[t] = cell_xyzf[e];
+                if (MULTI_TYPE) s_type[t] = cell_type[e];
+                }
+            else
+                {
+                s_cand[t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
+                if (MULTI_TYPE) s_type[t] = 0u;
+                }
+            }
+        __syncwarp();
+
+        for (unsigned int p = own_beg; p < own_end; p++)
+            {
+            const float4 pi4 = cell_xyzf[p];
+            const unsigned int i = (unsigned int)__float_as_int(pi4.w);
+            if (i >= N) continue; // ghosts are candidates only
+            const unsigned int type_i = MULTI_TYPE ? cell_type[p] : 0u;
+            const unsigned int Nmax_i = Nmax[type_i];
+            unsigned int* row = nlist + head_list[i];
+            unsigned int n = pass ? n_neigh[i] : 0u;
+            if (wrap_any)
+                n = nlist_scan_tile<MULTI_TYPE, true, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                                                            lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
+                                                            ntypes);
+            else
+                n = nlist_scan_tile<MULTI_TYPE, false, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                                                             lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
+                                                             ntypes);
+            if (lane == 0)
+                {
+                if (pass + NW_CAP < total)
+                    n_neigh[i] = n;
+                else
+                    {
+                    n_neigh[i] = min(n, Nmax_i);
+                    if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+                    if (last_pos) last_pos[i] = make_float4(pi4.x, pi4.y, pi4.z, 0.0f);
+                    }
+                }
+            __syncwarp();
+            }
+        }
+    }
+
 // ---- cell-scan build: one CTA per cell, EIGHT lanes per particle, each scanning a contiguous eighth of the staged
 // candidates -------------------------------------------------------------------------------------------------------------
 // The tiled kernel above spends one warp per particle with lanes = candidates: every 32 tests cost a ballot, two popc and
@@ -789,6 +928,30 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
             }
 #undef B200_NC_LAUNCH
 #undef B200_NC_LAUNCH2
+        return cudaGetLastError();
+        }
+    // sparse cells (<= ~5 particles per cell): one warp per cell instead of one CTA (see k_nlist_warpcell)
+    static const char* warpcell_env = getenv("HOOMD_B200_NLIST_WARPCELL");
+    const bool sparse = a->cand_hint && a->cand_hint <= 250u;
+    if (!use_warp_kernel && !use_cellscan_kernel && (warpcell_env ? atoi(warpcell_env) != 0 : sparse))
+        {
+        const unsigned int ncells = a->dim.x * a->dim.y * a->dim.z;
+        const unsigned int grid = (ncells + NW_WARPS - 1) / NW_WARPS;
+        const size_t smem = (size_t)NW_WARPS * NW_CAP * (sizeof(float4) + (a->ntypes > 1 ? sizeof(unsigned int) : 0));
+#define B200_NW_LAUNCH(MT, HALF)                                                                                     \
+    k_nlist_warpcell<MT, HALF><<<grid, NW_WARPS * 32, smem, stream>>>(                                              \
+        a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,         \
+        a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,        \
+        a->ntypes, enable)
+        if (a->ntypes > 1)
+            {
+            if (a->half_storage) B200_NW_LAUNCH(true, true); else B200_NW_LAUNCH(true, false);
+            }
+        else
+            {
+            if (a->half_storage) B200_NW_LAUNCH(false, true); else B200_NW_LAUNCH(false, false);
+            }
+#undef B200_NW_LAUNCH
         return cudaGetLastError();
         }
     if (!use_warp_kernel)
