@@ -212,7 +212,9 @@ struct b200_system
     DevBuf<unsigned char> slot_dir, pplan_n;
     DevBuf<unsigned int> pplan;
     DevBuf<GhostSendTable> gs_table;
-    bool fused_ghosts = true;        // ghost update inside k_md_step (HOOMD_B200_FUSED_GHOSTS=0: stand-alone kernel)
+    // ghost update inside k_md_step (HOOMD_B200_FUSED_GHOSTS=1).  Off by default: measured 1-3 % slower than the
+    // stand-alone k_mg_ghost_send (LJ 8M on 8 B200: 3735 vs 3860 TPS; LJ 1M on 2: 6946 vs 7031) -- see DESIGN.md section 6
+    bool fused_ghosts = false;
 
     // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
     int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
