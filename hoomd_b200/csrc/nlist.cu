@@ -140,7 +140,7 @@ constexpr int NL_CAP = 1024; // staged candidates per pass (16 kB + 4 kB types);
 
 // One warp tests every staged candidate against particle i: 2 x 32 candidates per trip, ballot + popc compaction in the
 // staged (= oracle) order.  The tile is padded to a multiple of 64 with far-away sentinels, so there is no bounds test.
-template<bool MULTI_TYPE, bool WRAP, bool HALF>
+template<bool MULTI_TYPE, bool WRAP, bool HALF, int U = 2>
 __device__ __forceinline__ unsigned int nlist_scan_tile(unsigned int n, const float4 pi4, unsigned int i,
                                                         unsigned int type_i, unsigned int Nmax_i,
                                                         unsigned int* __restrict__ row, const float4* s_cand,
@@ -150,12 +150,12 @@ __device__ __forceinline__ unsigned int nlist_scan_tile(unsigned int n, const fl
                                                         const float* __restrict__ r_listsq, unsigned int ntypes)
     {
     const unsigned int lanemask_lt = (1u << lane) - 1u;
-    for (unsigned int base = 0; base < cnt_padded; base += 64)
+    for (unsigned int base = 0; base < cnt_padded; base += 32 * U)
         {
-        bool hit[2];
-        unsigned int jj[2];
+        bool hit[U];
+        unsigned int jj[U];
 #pragma unroll
-        for (int u = 0; u < 2; u++)
+        for (int u = 0; u < U; u++)
             {
             const unsigned int t = base + 32 * u + lane;
             const float4 cj = s_cand[t];
@@ -177,7 +177,7 @@ __device__ __forceinline__ unsigned int nlist_scan_tile(unsigned int n, const fl
             jj[u] = j;
             }
 #pragma unroll
-        for (int u = 0; u < 2; u++)
+        for (int u = 0; u < U; u++)
             {
             const unsigned int mask = __ballot_sync(0xffffffffu, hit[u]);
             const unsigned int k = n + __popc(mask & lanemask_lt);
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
 // prefix over the <=27 adjacent cells, __syncwarp instead of __syncthreads, particles of the cell one after the other
 // through the same nlist_scan_tile (same candidate order, same arithmetic => same list).  4 cells per CTA.
 constexpr int NW_WARPS = 4;
-constexpr int NW_CAP = 256; // staged candidates per warp and pass (multiple of 64)
+constexpr int NW_CAP = 256; // staged candidates per warp and pass (multiple of 32)
 
 template<bool MULTI_TYPE, bool HALF>
 __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* __restrict__ nlist,
@@ -408,28 +408,25 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
     for (unsigned int pass = 0; pass < total; pass += NW_CAP)
         {
         const unsigned int cnt = min((unsigned int)NW_CAP, total - pass);
-        const unsigned int cnt_padded = (cnt + 63u) & ~63u;
+        const unsigned int cnt_padded = (cnt + 31u) & ~31u; // one candidate per lane and trip (U = 1): pad to 32 only
         if (pass) __syncwarp(); // the warp is done with the previous tile
-        for (unsigned int t = lane; t < cnt_padded; t += 32)
+        // lane r copies "its" adjacent cell (a handful of entries) into the staged order: no per-entry range search
+        if (lane < nr)
             {
-            if (t < cnt)
+            const unsigned int off = incl - len; // == s_off[lane]
+            const unsigned int k0 = pass > off ? pass - off : 0u;
+            const unsigned int k1 = min(len, pass + NW_CAP > off ? pass + NW_CAP - off : 0u);
+            for (unsigned int k = k0; k < k1; k++)
                 {
-                const unsigned int g = pass + t;
-                unsigned int lo = 0, hi = nr;
-                while (hi - lo > 1)
-                    {
-                    const unsigned int mid = (lo + hi) >> 1;
-                    if (s_off[mid] <= g) lo = mid; else hi = mid;
-                    }
-                const unsigned int e = s_beg[lo] + (g - s_off[lo]);
-                s_cand[t] = cell_xyzf[e];
-                if (MULTI_TYPE) s_type[t] = cell_type[e];
+                s_cand[off + k - pass] = cell_xyzf[beg + k];
+                if (MULTI_TYPE) s_type[off + k - pass] = cell_type[beg + k];
                 }
-            else
-                {
-                s_cand[t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
-                if (MULTI_TYPE) s_type[t] = 0u;
-                }
+            }
+        if (cnt + lane < cnt_padded)
+            {
+            // sentinel: dr^2 overflows to +inf, never <= r_list^2; index 0xffffffff is nobody
+            s_cand[cnt + lane] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, __int_as_float(-1));
+            if (MULTI_TYPE) s_type[cnt + lane] = 0u;
             }
         __syncwarp();
 
@@ -443,11 +440,11 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
             unsigned int* row = nlist + head_list[i];
             unsigned int n = pass ? n_neigh[i] : 0u;
             if (wrap_any)
-                n = nlist_scan_tile<MULTI_TYPE, true, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                n = nlist_scan_tile<MULTI_TYPE, true, HALF, 1>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
                                                             lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
                                                             ntypes);
             else
-                n = nlist_scan_tile<MULTI_TYPE, false, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
+                n = nlist_scan_tile<MULTI_TYPE, false, HALF, 1>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
                                                              lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
                                                              ntypes);
             if (lane == 0)
