@@ -1,9 +1,12 @@
 // CellList for sm_100a: count -> scan -> scatter -> in-cell rank.  Replaces hoomd/CellListGPU.cu:40-219 (atomicInc into a
 // padded Ncells x Nmax array) with contiguous, index-ordered cell ranges.  See include/hoomd_b200.h for the layout.
 #include "common.cuh"
+#include <cooperative_groups.h>
+#include <cstdlib>
 
 namespace b200
 {
+namespace cg = cooperative_groups;
 // ---- K1: bin every particle, count cell occupancies ---------------------------------------------------------------
 // 1 thread / particle, coalesced float4 load.  atomicAdd on cell_count returns an arbitrary slot; the final in-cell
 // order is fixed later by rank (k_cell_rank), so the result is deterministic.
@@ -16,6 +19,7 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
                                                   const unsigned int* __restrict__ enable,
                                                   const unsigned int* __restrict__ d_N)
     {
+    pdl_trigger(); // first kernel of the rebuild chain: let the scan's CTAs be scheduled behind this grid
     if (enable && !*enable) return; // device-driven stepping: the rebuild was not requested this step
     unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N + n_ghost) return;
@@ -55,6 +59,8 @@ __global__ void __launch_bounds__(1024) k_cell_scan(unsigned int* __restrict__ c
                                                     unsigned int* __restrict__ conditions,
                                                     const unsigned int* __restrict__ enable)
     {
+    pdl_wait();
+    pdl_trigger();
     if (enable && !*enable) return;
     __shared__ unsigned int warp_sums[32];
     __shared__ unsigned int carry_s;
@@ -158,6 +164,8 @@ __global__ void __launch_bounds__(1024) k_cell_scan_tiles(unsigned int* __restri
                                                           unsigned int* __restrict__ conditions,
                                                           const unsigned int* __restrict__ enable)
     {
+    pdl_wait();
+    pdl_trigger();
     if (enable && !*enable) return;
     __shared__ unsigned int warp_sums[33];
     const unsigned int i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
@@ -195,6 +203,8 @@ __global__ void __launch_bounds__(1024) k_cell_scan_fix(unsigned int* __restrict
                                                         const unsigned int* __restrict__ tile_sums,
                                                         const unsigned int* __restrict__ enable)
     {
+    pdl_wait();
+    pdl_trigger();
     if (enable && !*enable) return;
     __shared__ unsigned int warp_sums[33];
     // offset of this tile = sum of the totals of the tiles before it
@@ -219,6 +229,8 @@ __global__ void __launch_bounds__(256) k_cell_scatter(unsigned int* __restrict__
                                                       const unsigned int* __restrict__ particle_slot, unsigned int ntot,
                                                       const unsigned int* __restrict__ enable)
     {
+    pdl_wait();
+    pdl_trigger();
     if (enable && !*enable) return;
     unsigned int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= ntot) return;
@@ -239,6 +251,8 @@ __global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyz
                                                    unsigned int ncells, int flag_charge, int flag_type,
                                                    const unsigned int* __restrict__ enable)
     {
+    pdl_wait();
+    pdl_trigger();
     if (enable && !*enable) return;
     unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int nbinned = cell_start[ncells];
@@ -256,6 +270,144 @@ __global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyz
     cell_xyzf[s + rank] = make_float4(p.x, p.y, p.z, flag);
     if (cell_type) cell_type[s + rank] = (unsigned int)__float_as_int(p.w);
     if (cell_idx) cell_idx[s + rank] = n;
+    }
+
+// ---- small systems: the four phases in ONE cooperative launch ----------------------------------------------------------
+// At 64k particles each of the four kernels above runs 3 us while the dependent-launch gap inside the conditional rebuild
+// body is 5-8 us (profiles/r1n_*): the build is launch-bound.  One cooperative grid (<= one CTA of 512 threads per 512
+// particles, all co-resident) does bin -> grid.sync -> scan (CTA 0) -> grid.sync -> scatter -> grid.sync -> rank with the
+// same arithmetic and the same final order (the in-cell rank fixes it), so the result is bit-identical to the 4-kernel path.
+constexpr unsigned int CF_BLOCK = 512;
+constexpr unsigned int CF_MAX_CELLS = 4 * SCAN_TILE;
+
+__global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
+    unsigned int* __restrict__ cell_count, unsigned int* __restrict__ cell_start, unsigned int* __restrict__ particle_cell,
+    unsigned int* __restrict__ particle_slot, unsigned int* __restrict__ scratch_idx, float4* __restrict__ cell_xyzf,
+    unsigned int* __restrict__ cell_type, unsigned int* __restrict__ cell_idx, unsigned int* __restrict__ conditions,
+    const float4* __restrict__ pos, const float* __restrict__ charge, unsigned int N, unsigned int n_ghost, Box box,
+    uint3 dim, float3 ghost_width, int flag_charge, int flag_type, const unsigned int* __restrict__ enable,
+    const unsigned int* __restrict__ d_N)
+    {
+    if (enable && !*enable) return; // uniform over the grid: nobody reaches a grid.sync
+    cg::grid_group grid = cg::this_grid();
+    const unsigned int ntot = N + n_ghost;
+    const unsigned int ncells = dim.x * dim.y * dim.z;
+    const unsigned int stride = gridDim.x * blockDim.x;
+    const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    // phase 1: bin (k_cell_bin)
+    const unsigned int Nloc = d_N ? *d_N : N;
+    for (unsigned int n = tid; n < ntot; n += stride)
+        {
+        if (n >= Nloc && n < N) // multi-GPU: unused local capacity
+            {
+            particle_cell[n] = B200_NOT_BINNED;
+            continue;
+            }
+        const float4 p = pos[n];
+        unsigned int cell = B200_NOT_BINNED, slot = 0;
+        if (isnan(p.x) || isnan(p.y) || isnan(p.z))
+            atomicMax(&conditions[1], n + 1);
+        else
+            {
+            int3 b;
+            if (particle_bin(make_float3(p.x, p.y, p.z), box, ghost_width, dim, b))
+                {
+                cell = ((unsigned int)b.z * dim.y + (unsigned int)b.y) * dim.x + (unsigned int)b.x;
+                slot = atomicAdd(&cell_count[cell], 1u);
+                }
+            else if (n < N)
+                atomicMax(&conditions[2], n + 1);
+            }
+        particle_cell[n] = cell;
+        particle_slot[n] = slot;
+        }
+    grid.sync();
+    // phase 2: exclusive scan of the occupancies by CTA 0 (k_cell_scan; 8 cells per thread and tile), self-cleaning counts
+    if (blockIdx.x == 0)
+        {
+        __shared__ unsigned int warp_sums[CF_BLOCK / 32];
+        __shared__ unsigned int carry_s;
+        const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (threadIdx.x == 0) carry_s = 0;
+        unsigned int max_occ = 0;
+        __syncthreads();
+        for (unsigned int base = 0; base < ncells; base += CF_BLOCK * 8)
+            {
+            const unsigned int i0 = base + threadIdx.x * 8;
+            const unsigned int carry = carry_s;
+            unsigned int c[8];
+            unsigned int tsum = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                {
+                c[k] = (i0 + k < ncells) ? cell_count[i0 + k] : 0u;
+                if (i0 + k < ncells) cell_count[i0 + k] = 0u;
+                max_occ = max(max_occ, c[k]);
+                tsum += c[k];
+                }
+            unsigned int incl = tsum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+                {
+                const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+                }
+            if (lane == 31) warp_sums[warp] = incl;
+            __syncthreads();
+            if (warp == 0)
+                {
+                const unsigned int w = lane < CF_BLOCK / 32 ? warp_sums[lane] : 0u;
+                unsigned int wi = w;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1)
+                    {
+                    const unsigned int v = __shfl_up_sync(0xffffffffu, wi, o);
+                    if (lane >= o) wi += v;
+                    }
+                if (lane < CF_BLOCK / 32) warp_sums[lane] = wi - w;
+                if (lane == 31) carry_s = carry + wi;
+                }
+            __syncthreads();
+            unsigned int excl = carry + warp_sums[warp] + incl - tsum;
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                {
+                if (i0 + k < ncells) cell_start[i0 + k] = excl;
+                excl += c[k];
+                }
+            __syncthreads();
+            }
+        if (threadIdx.x == 0) cell_start[ncells] = carry_s;
+        for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
+        if (lane == 0 && max_occ) atomicMax(&conditions[0], max_occ);
+        }
+    grid.sync();
+    // phase 3: scatter (k_cell_scatter).  cell_start was written by another CTA in this launch: no read-only path
+    for (unsigned int n = tid; n < ntot; n += stride)
+        {
+        const unsigned int cell = particle_cell[n];
+        if (cell == B200_NOT_BINNED) continue;
+        scratch_idx[__ldcg(cell_start + cell) + particle_slot[n]] = n;
+        }
+    grid.sync();
+    // phase 4: in-cell rank by particle index, final arrays (k_cell_rank)
+    const unsigned int nbinned = __ldcg(cell_start + ncells);
+    for (unsigned int e = tid; e < nbinned; e += stride)
+        {
+        const unsigned int n = __ldcg(scratch_idx + e);
+        const unsigned int cell = __ldcg(particle_cell + n);
+        const unsigned int s = __ldcg(cell_start + cell), t = __ldcg(cell_start + cell + 1);
+        unsigned int rank = 0;
+        for (unsigned int k = s; k < t; k++) rank += (__ldcg(scratch_idx + k) < n) ? 1u : 0u;
+        const float4 p = pos[n];
+        float flag;
+        if (flag_charge) flag = charge[n];
+        else if (flag_type) flag = p.w;
+        else flag = __int_as_float((int)n);
+        cell_xyzf[s + rank] = make_float4(p.x, p.y, p.z, flag);
+        if (cell_type) cell_type[s + rank] = (unsigned int)__float_as_int(p.w);
+        if (cell_idx) cell_idx[s + rank] = n;
+        }
     }
 
 // ---- export to the reference's padded layout ------------------------------------------------------------------------
@@ -395,9 +547,44 @@ void b200_cell_list_dimensions(const b200_box* box, float nominal_width, unsigne
 
 namespace b200
 {
+bool pdl_enabled()
+    {
+    static const char* env = getenv("HOOMD_B200_PDL");
+    static const bool on = env ? atoi(env) != 0 : false;
+    return on;
+    }
+
+// co-resident CTAs of the cooperative build on the current device (0: cooperative launch unavailable or switched off)
+static unsigned int cell_fused_max_ctas()
+    {
+    static int cached = -1;
+    if (cached < 0)
+        {
+        cached = 0;
+        // measured SLOWER than the 4-kernel build inside the conditional graph body (LJ 64k: 31.5k vs 32.9k timesteps/s,
+        // Kob-Andersen 262k: 5.83k vs 6.19k; profiles/r1p_*): the cooperative launch and three grid-wide barriers cost more
+        // than the three launch gaps they remove.  Kept behind HOOMD_B200_CELL_FUSED=1 for A/B runs.
+        const char* env = getenv("HOOMD_B200_CELL_FUSED");
+        int dev = 0, coop = 0, sms = 0, per_sm = 0;
+        if (env && atoi(env) != 0 && cudaGetDevice(&dev) == cudaSuccess
+            && cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop
+            && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess
+            && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_cell_list_fused, (int)CF_BLOCK, 0) == cudaSuccess)
+            cached = sms * per_sm;
+        }
+    return (unsigned int)cached;
+    }
+
+static bool cell_use_fused(unsigned int ncells, unsigned int ntot)
+    {
+    // launch-bound sizes only: beyond a few hundred thousand particles the kernels dwarf the launch gaps
+    return ntot > 0 && ncells <= CF_MAX_CELLS && ntot <= 262144u && cell_fused_max_ctas() > 0;
+    }
+
 // launches per cell-list build: the multi-CTA scan (one launch more) pays off beyond a few tiles
 unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot)
     {
+    if (cell_use_fused(ncells, ntot)) return 1u;
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     return (ntiles > 4 && ntiles <= ntot) ? 5u : 4u;
     }
@@ -414,28 +601,45 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
     if (!enable) cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
+    if (cell_use_fused(ncells, ntot))
+        {
+        unsigned int grid = (ntot + CF_BLOCK - 1) / CF_BLOCK;
+        if (grid > cell_fused_max_ctas()) grid = cell_fused_max_ctas();
+        unsigned int N = a->N, n_ghost = a->n_ghost;
+        const float4* pos = (const float4*)a->d_pos;
+        float4* xyzf = (float4*)a->d_cell_xyzf;
+        int flag_charge = a->flag_charge, flag_type = a->flag_type;
+        void* args[] = {(void*)&a->d_cell_count, (void*)&a->d_cell_start, (void*)&a->d_particle_cell,
+                        (void*)&a->d_particle_slot, (void*)&a->d_scratch_idx, &xyzf, (void*)&a->d_cell_type,
+                        (void*)&a->d_cell_idx, (void*)&a->d_conditions, &pos, (void*)&a->d_charge, &N, &n_ghost, &box,
+                        &dim, &gw, &flag_charge, &flag_type, &enable, &d_N};
+        return cudaLaunchCooperativeKernel((const void*)k_cell_list_fused, dim3(grid), dim3(CF_BLOCK), args, 0, stream);
+        }
     if (ntot)
         k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
                                                             a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
                                                             box, dim, gw, enable, d_N);
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
+    // device-driven rebuild: the dependent kernels are scheduled behind their predecessor (see launch_chain)
+    const bool pdl = enable && pdl_enabled();
     if (cell_list_kernels(ncells, ntot) == 5)
         {
         // tile totals live in d_scratch_idx, which is not needed before k_cell_scatter
-        k_cell_scan_tiles<<<ntiles, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_scratch_idx,
-                                                       a->d_conditions, enable);
-        k_cell_scan_fix<<<ntiles, 1024, 0, stream>>>(a->d_cell_start, ncells, a->d_scratch_idx, enable);
+        launch_chain(k_cell_scan_tiles, dim3(ntiles), dim3(1024), 0, stream, pdl, a->d_cell_start, a->d_cell_count, ncells,
+                     a->d_scratch_idx, a->d_conditions, enable);
+        launch_chain(k_cell_scan_fix, dim3(ntiles), dim3(1024), 0, stream, pdl, a->d_cell_start, ncells, a->d_scratch_idx,
+                     enable);
         }
     else
-        k_cell_scan<<<1, 1024, 0, stream>>>(a->d_cell_start, a->d_cell_count, ncells, a->d_conditions, enable);
+        launch_chain(k_cell_scan, dim3(1), dim3(1024), 0, stream, pdl, a->d_cell_start, a->d_cell_count, ncells,
+                     a->d_conditions, enable);
     if (ntot)
         {
-        k_cell_scatter<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
-                                                                a->d_particle_slot, ntot, enable);
-        k_cell_rank<<<(ntot + 255) / 256, 256, 0, stream>>>((float4*)a->d_cell_xyzf, a->d_cell_type, a->d_cell_idx,
-                                                             a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
-                                                             (const float4*)a->d_pos, a->d_charge, ncells,
-                                                             a->flag_charge, a->flag_type, enable);
+        launch_chain(k_cell_scatter, dim3((ntot + 255) / 256), dim3(256), 0, stream, pdl, a->d_scratch_idx,
+                     a->d_cell_start, a->d_particle_cell, a->d_particle_slot, ntot, enable);
+        launch_chain(k_cell_rank, dim3((ntot + 255) / 256), dim3(256), 0, stream, pdl, (float4*)a->d_cell_xyzf,
+                     a->d_cell_type, a->d_cell_idx, a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
+                     (const float4*)a->d_pos, a->d_charge, ncells, a->flag_charge, a->flag_type, enable);
         }
     return cudaGetLastError();
     }

@@ -10,6 +10,34 @@
 
 namespace b200
 {
+// ---- programmatic dependent launch (sm_90+) -------------------------------------------------------------------------------
+// The rebuild bracket is a chain of small dependent kernels; with the attribute below a kernel's CTAs are scheduled while
+// its predecessor is still running and block in pdl_wait() until that grid has completed and flushed its writes.  Every
+// kernel of such a chain calls pdl_wait() before its first global access (completion is then transitive along the chain)
+// and pdl_trigger() right after it.  Both instructions are no-ops in an ordinary launch.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template<class... KArgs, class... Args>
+inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                bool pdl, Args&&... args)
+    {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+    }
+#endif
+bool pdl_enabled(); // HOOMD_B200_PDL (cell_list.cu)
+
 struct Box
     {
     float3 lo, hi, L, Linv;

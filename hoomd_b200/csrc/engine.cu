@@ -163,13 +163,18 @@ struct b200_system
     // ---- IntegratorTwoStep + method ---------------------------------------------------------------------------
     bool have_integrator = false;
     float dt = 0.005f;
-    int method = 0; // 0 none, 1 TwoStepNVE, 2 TwoStepLangevin
+    int method = 0; // 0 none, 1 TwoStepNVE, 2 TwoStepLangevin, 3 TwoStepNVTMTK
     int limit = 0, zero_force = 0;
     float limit_val = 0.0f;
     float kT = 0.0f;
     unsigned int seed_hashed = 0;
     int noiseless_t = 0;
     DevBuf<float> d_gamma;
+    // TwoStepNVTMTK: {xi, eta, exp_fac, -} lives on the device (d_nvt), checkpointed per chunk; partial sums of m v^2
+    float nvt_tau = 0.0f;
+    DevBuf<float> d_nvt, ck_nvt;
+    DevBuf<double> nvt_partial;
+    static constexpr unsigned int NVT_BLOCKS = 592; // CTAs of the stand-alone kinetic-energy pass (4 per SM)
 
     // ---- SFCPackUpdater ---------------------------------------------------------------------------------------
     unsigned int sorter_period = 0, sorter_next = 0, sorter_grid = 256;
@@ -315,6 +320,17 @@ static const void* pair_params_ptr(b200_system* s)
                                                                               : (const void*)s->d_params.p;
     }
 
+// IntegratorTwoStep::getNDOF for one method on all particles (hoomd/md/IntegratorTwoStep.cc:270-283): D N - D
+static unsigned int nvt_ndof(const b200_system* s) { return 3u * s->N - 3u; }
+
+// ComputeThermo (kinetic energy of the half-step velocities) + TwoStepNVTMTK::advanceThermostat, on the device
+static void nvt_advance(b200_system* s)
+    {
+    CUDA_OK(b200_nvt_mtk_advance(s->d_nvt.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p, nullptr,
+                                 s->N, nvt_ndof(s), s->kT, s->nvt_tau, s->dt, s->stream));
+    s->kernels_last_run += 2;
+    }
+
 static void fused_args(b200_system* s, FusedStepArgs& a)
     {
     memset(&a, 0, sizeof(a));
@@ -333,6 +349,10 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     if (s->bond_kind >= 0)
         {
         a.extra_force = s->bond_force.p; a.extra_virial = s->bond_virial.p; a.extra_virial_pitch = s->virial_pitch;
+        }
+    if (s->method == 3)
+        {
+        a.nvt_state = s->d_nvt.p; a.nvt_partial = s->nvt_partial.p; a.nvt_ndof = nvt_ndof(s); a.nvt_tau = s->nvt_tau;
         }
     }
 
@@ -663,6 +683,14 @@ static void compute_net_force(b200_system* s, unsigned int ts)
 static void integrate_step_one(b200_system* s, unsigned int ts)
     {
     (void)ts;
+    if (s->method == 3)
+        {
+        CUDA_OK(b200_nvt_mtk_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p,
+                                      nullptr, s->N, &s->box, s->d_nvt.p, s->dt, s->stream));
+        s->kernels_last_run += 1;
+        nvt_advance(s);
+        return;
+        }
     const bool nve = s->method == 1;
     CUDA_OK(b200_nve_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p, nullptr,
                               s->N, &s->box, s->dt, nve ? s->limit : 0, s->limit_val, nve ? s->zero_force : 0,
@@ -685,6 +713,9 @@ static void integrate_step_two(b200_system* s, unsigned int ts)
         CUDA_OK(b200_langevin_step_two((const float*)s->pos.p, (float*)s->vel.p, (float*)s->accel.p, nullptr, s->tag.p,
                                        nullptr, s->N, (const float*)s->net_force.p, &la, s->dt, 3, s->stream));
         }
+    else if (s->method == 3)
+        CUDA_OK(b200_nvt_mtk_step_two((float*)s->vel.p, (float*)s->accel.p, nullptr, s->N, (const float*)s->net_force.p,
+                                      s->d_nvt.p, s->dt, s->stream));
     else
         CUDA_OK(b200_nve_step_two((float*)s->vel.p, (float*)s->accel.p, nullptr, s->N, (const float*)s->net_force.p,
                                   s->dt, s->limit, s->limit_val, s->zero_force, s->stream));
@@ -780,8 +811,11 @@ static void enqueue_rebuild(b200_system* s, const unsigned int* enable, const fl
     b200_nlist_args na;
     nlist_args(s, na);
     na.d_pos = (const float*)pos;
-    CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
-    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream, 1));
+    // the build kernel raises StepState::overflow itself and stops the chunk (OverflowHook): no separate check kernel
+    OverflowHook hook;
+    hook.overflow = &s->d_state.p->overflow;
+    hook.steps_left = &s->d_state.p->steps_left;
+    CUDA_OK(launch_nlist_binned(&na, enable, s->stream, hook));
     // filterNlist runs on the complete rows; after an overflow the rows are discarded anyway (checkpoint replay)
     enqueue_nlist_filter(s, enable);
     }
@@ -951,6 +985,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     CUDA_OK(cudaMemcpyAsync(s->ck_accel.p, s->accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->ck_image.p, s->image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
     const bool ck_force_update = s->force_update;
+    if (s->method == 3)
+        CUDA_OK(cudaMemcpyAsync(s->ck_nvt.p, s->d_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
 
     StepState& st = *s->h_state;
     memset(&st, 0, sizeof(st));
@@ -965,6 +1001,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     FusedStepArgs fa;
     fused_args(s, fa);
     CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+    if (s->method == 3) nvt_advance(s); // thermostat of the prologue's step one; the later ones run inside k_md_step
     CUDA_OK(launch_decide(s->d_state.p, s->stream));
     const unsigned int nreplay = (chunk + 1) / 2;
     if (s->use_graph == 3)
@@ -997,6 +1034,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+        if (s->method == 3)
+            CUDA_OK(cudaMemcpyAsync(s->d_nvt.p, s->ck_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
         s->force_update = ck_force_update;
         if (s->tile_on)
@@ -1040,7 +1079,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     check_bond_flags(s);
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
     const unsigned long long cl_extra = cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->N) - 4u;
-    const unsigned long long rk = (s->tile_on ? 8ull : 6ull) + cl_extra
+    const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
     s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + rk * rebuilds)
@@ -1557,6 +1596,56 @@ int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const flo
     s->d_gamma.upload(g.data(), s->ntypes, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+int b200_sys_add_nvt(b200_system* s, float kT, float tau)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("integrate.nvt: not available under domain decomposition yet");
+    if (s->tile_on) throw std::runtime_error("integrate.nvt: not available on the cell-tile path");
+    if (!(kT > 0.0f)) throw std::runtime_error("integrate.nvt: kT must be positive");
+    if (tau <= 0.0f) fprintf(stderr, "*Warning*: integrate.nvt: tau set less than 0.0\n"); // TwoStepNVTMTK.cc:46-47
+    s->method = 3;
+    s->limit = 0;
+    s->zero_force = 0;
+    s->kT = kT;
+    s->nvt_tau = tau;
+    // initializeIntegratorVariables: xi = eta = 0, m_exp_thermo_fac = 1 (TwoStepNVTMTK.cc:39,50-54)
+    const float init[4] = {0.0f, 0.0f, 1.0f, 0.0f};
+    s->d_nvt.alloc(4);
+    s->ck_nvt.alloc(4);
+    s->d_nvt.upload(init, 4, s->stream);
+    // one slot per CTA of the widest k_md_step grid (>= 4 particles per CTA: 128 threads, <= 32 lanes per particle) or of the
+    // stand-alone pass
+    s->nvt_partial.alloc(std::max<size_t>(b200_system::NVT_BLOCKS, s->N / 4 + 2));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+// restart / re-configuration: IntegratorVariables of a previous run (TwoStepNVTMTK.cc:50-58, restartInfoTestValid)
+int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta)
+    {
+    SYS_TRY(s)
+    if (s->method != 3) throw std::runtime_error("integrate.nvt: no NVT method set");
+    // m_exp_thermo_fac is NOT part of the restart record: the reference starts from 1.0 and recomputes it at the first
+    // advanceThermostat (TwoStepNVTMTK.cc:39)
+    const float h[4] = {xi_eta[0], xi_eta[1], 1.0f, 0.0f};
+    s->d_nvt.upload(h, 4, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+int b200_sys_get_nvt_state(b200_system* s, float* xi_eta)
+    {
+    SYS_TRY(s)
+    if (s->method != 3) throw std::runtime_error("integrate.nvt: no NVT method set");
+    float h[4];
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    CUDA_OK(cudaMemcpy(h, s->d_nvt.p, sizeof(h), cudaMemcpyDeviceToHost));
+    xi_eta[0] = h[0];
+    xi_eta[1] = h[1];
     SYS_CATCH(s)
     }
 

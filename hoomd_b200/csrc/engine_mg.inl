@@ -212,11 +212,12 @@ static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float
     b200_nlist_args na;
     nlist_args(s, na);
     na.d_pos = (const float*)pos;
-    CUDA_OK(launch_nlist_binned(&na, enable, s->stream));
-    CUDA_OK(launch_post_rebuild(s->d_state.p, s->nl_conditions.p, s->d_Nmax.p, s->stream));
+    OverflowHook hook; // every rank must keep stepping to the barrier: raise the flag only
+    hook.overflow = &s->d_state.p->overflow;
+    CUDA_OK(launch_nlist_binned(&na, enable, s->stream, hook));
     CUDA_OK(launch_mg_rebuild_vote(s->mgc, s->mgl, buffer, enable, s->stream));
     }
-constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 3;
+constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 2; // migrate, ghost plan, cell list, nlist + vote
 
 static void mg_upload_state(b200_system* s, unsigned int steps_left)
     {

@@ -17,7 +17,8 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
                                                         const float* __restrict__ rcut_max, unsigned int N, Box box,
                                                         float dt, float r_buff, bool limit, float limit_val,
                                                         bool zero_force, StepState* __restrict__ st,
-                                                        const unsigned int* __restrict__ d_N)
+                                                        const unsigned int* __restrict__ d_N,
+                                                        const NvtState* __restrict__ nvt)
     {
     unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
     bool moved = false;
@@ -29,7 +30,10 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
         float3s a = accel[j];
         if (zero_force) a.x = a.y = a.z = 0.0f;
         int3 img = image[j];
-        nve_step_one_body(p, v, a, img, box, dt, limit, limit_val);
+        if (nvt) // TwoStepNVTMTK::integrateStepOne; the caller advances the thermostat afterwards
+            nvt_step_one_body(p, v, a, img, box, dt, nvt->exp_fac);
+        else
+            nve_step_one_body(p, v, a, img, box, dt, limit, limit_val);
         pos[j] = p;
         vel[j] = v;
         image[j] = img;
@@ -97,7 +101,8 @@ cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStr
     k_fused_step_one<<<(a.N + 255) / 256, 256, 0, stream>>>(a.pos, a.vel, (const float3s*)a.accel, (int3*)a.image,
                                                             a.last_pos, a.rcut_max, a.N, make_box(a.box), a.dt,
                                                             a.r_buff, nve && a.limit, a.limit_val, nve && a.zero_force,
-                                                            st, a.d_N);
+                                                            st, a.d_N,
+                                                            a.method == 3 ? (const NvtState*)a.nvt_state : nullptr);
     return cudaGetLastError();
     }
 

@@ -195,6 +195,71 @@ __global__ void k_thermo_final(double* __restrict__ out, const double* __restric
     }
 } // namespace b200
 
+// ---- TwoStepNVTMTK (hoomd/md/TwoStepNVTMTKGPU.cu:30-212): exp_fac comes from device memory, so the whole update
+// (step one -> kinetic energy -> advanceThermostat -> ... -> step two) is enqueued without a host round trip ------------------
+namespace b200
+{
+__global__ void __launch_bounds__(256) k_nvt_step_one(float4* __restrict__ pos, float4* __restrict__ vel,
+                                                      const float3s* __restrict__ accel, int3* __restrict__ image,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      Box box, const NvtState* __restrict__ state, float dt)
+    {
+    const unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 p = pos[j], v = vel[j];
+    int3 img = image[j];
+    nvt_step_one_body(p, v, accel[j], img, box, dt, state->exp_fac);
+    pos[j] = p;
+    vel[j] = v;
+    image[j] = img;
+    }
+
+__global__ void __launch_bounds__(256) k_nvt_step_two(float4* __restrict__ vel, float3s* __restrict__ accel,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      const float4* __restrict__ net_force,
+                                                      const NvtState* __restrict__ state, float dt)
+    {
+    const unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 v = vel[j];
+    float3s a;
+    nvt_step_two_body(v, a, net_force[j], dt, state->exp_fac);
+    vel[j] = v;
+    accel[j] = a;
+    }
+
+// sum(m v^2) over the group: per-CTA partial sums in a fixed order (pass 1 of the thermostat's ComputeThermo)
+__global__ void __launch_bounds__(256) k_nvt_ke_partial(double* __restrict__ partial, const float4* __restrict__ vel,
+                                                        const unsigned int* __restrict__ group, unsigned int group_size)
+    {
+    double acc = 0.0;
+    for (unsigned int g = blockIdx.x * blockDim.x + threadIdx.x; g < group_size; g += gridDim.x * blockDim.x)
+        acc += nvt_mv2(vel[group ? group[g] : g]);
+    __shared__ double s[8];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+        double x = 0.0;
+        for (int w = 0; w < 8; w++) x += s[w];
+        partial[blockIdx.x] = x;
+        }
+    }
+
+// pass 2 + TwoStepNVTMTK::advanceThermostat, one warp
+__global__ void k_nvt_advance(NvtState* __restrict__ state, const double* __restrict__ partial, unsigned int nblocks,
+                              unsigned int ndof, float T, float tau, float dt)
+    {
+    double x = 0.0;
+    for (unsigned int b = threadIdx.x; b < nblocks; b += 32) x += partial[b];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (threadIdx.x == 0) nvt_advance_body(state, x, ndof, T, tau, dt);
+    }
+} // namespace b200
+
 using namespace b200;
 
 extern "C" {
@@ -261,6 +326,40 @@ int b200_langevin_step_two(const float* d_pos, float* d_vel, float* d_accel, con
         (const float4*)d_pos, (float4*)d_vel, (float3s*)d_accel, d_diameter, d_tag, d_group_members, group_size,
         (const float4*)d_net_force, a->d_gamma, a->use_lambda != 0, a->lambda, a->T, a->timestep, a->seed,
         a->d_sum_bdenergy, a->noiseless_t != 0, a->tally != 0, deltaT, D);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nvt_mtk_step_one(float* d_pos, float* d_vel, const float* d_accel, int* d_image,
+                          const unsigned int* d_group_members, unsigned int group_size, const b200_box* box,
+                          const float* d_nvt_state, float deltaT, b200_stream_t stream)
+    {
+    if (group_size == 0) return 0;
+    if (!box_is_orthorhombic(*box)) return (int)cudaErrorNotSupported;
+    k_nvt_step_one<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_pos, (float4*)d_vel, (const float3s*)d_accel, (int3*)d_image, d_group_members, group_size,
+        make_box(*box), (const NvtState*)d_nvt_state, deltaT);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nvt_mtk_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members, unsigned int group_size,
+                          const float* d_net_force, const float* d_nvt_state, float deltaT, b200_stream_t stream)
+    {
+    if (group_size == 0) return 0;
+    k_nvt_step_two<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_vel, (float3s*)d_accel, d_group_members, group_size, (const float4*)d_net_force,
+        (const NvtState*)d_nvt_state, deltaT);
+    return (int)cudaGetLastError();
+    }
+
+int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                         const unsigned int* d_group_members, unsigned int group_size, unsigned int ndof, float T,
+                         float tau, float deltaT, b200_stream_t stream)
+    {
+    if (n_partial_blocks == 0 || !d_partial || !d_nvt_state) return (int)cudaErrorInvalidValue;
+    k_nvt_ke_partial<<<n_partial_blocks, 256, 0, (cudaStream_t)stream>>>(d_partial, (const float4*)d_vel,
+                                                                         d_group_members, group_size);
+    k_nvt_advance<<<1, 32, 0, (cudaStream_t)stream>>>((NvtState*)d_nvt_state, d_partial, n_partial_blocks, ndof, T, tau,
+                                                      deltaT);
     return (int)cudaGetLastError();
     }
 

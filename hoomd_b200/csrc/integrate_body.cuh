@@ -90,4 +90,59 @@ __device__ __forceinline__ float langevin_step_two_body(float4& v, float3s& a, f
     return __fadd_rn(__fadd_rn(__fmul_rn(bd_fx, v.x), __fmul_rn(bd_fy, v.y)), __fmul_rn(bd_fz, v.z));
     }
 
+// ---- TwoStepNVTMTK, point particles (hoomd/md/TwoStepNVTMTK.cc:107-160,297-340,387-404) ------------------------------------
+// Thermostat state on the device: IntegratorVariables xi, eta and the loop-invariant m_exp_thermo_fac.  Layout of the
+// `float d_nvt_state[4]` of the C ABI.
+struct NvtState { float xi, eta, exp_fac, _pad; };
+
+__device__ __forceinline__ void nvt_step_one_body(float4& p, float4& v, float3s a, int3& img, const Box& box, float dt,
+                                                  float exp_fac)
+    {
+    // v = (v + (1/2)*accel*dt) * exp_fac ; pos += dt*v ; wrap
+    v.x = __fmul_rn(__fadd_rn(v.x, __fmul_rn(__fmul_rn(0.5f, a.x), dt)), exp_fac);
+    v.y = __fmul_rn(__fadd_rn(v.y, __fmul_rn(__fmul_rn(0.5f, a.y), dt)), exp_fac);
+    v.z = __fmul_rn(__fadd_rn(v.z, __fmul_rn(__fmul_rn(0.5f, a.z), dt)), exp_fac);
+    p.x = __fadd_rn(p.x, __fmul_rn(dt, v.x));
+    p.y = __fadd_rn(p.y, __fmul_rn(dt, v.y));
+    p.z = __fadd_rn(p.z, __fmul_rn(dt, v.z));
+    box_wrap(p.x, p.y, p.z, img, box);
+    }
+
+__device__ __forceinline__ void nvt_step_two_body(float4& v, float3s& a, float4 f, float dt, float exp_fac)
+    {
+    const float minv = __frcp_rn(v.w);
+    a.x = __fmul_rn(f.x, minv);
+    a.y = __fmul_rn(f.y, minv);
+    a.z = __fmul_rn(f.z, minv);
+    // v = v*exp_fac + (1/2)*dt*accel, the scalar product first
+    const float hdt = __fmul_rn(0.5f, dt);
+    v.x = __fadd_rn(__fmul_rn(v.x, exp_fac), __fmul_rn(hdt, a.x));
+    v.y = __fadd_rn(__fmul_rn(v.y, exp_fac), __fmul_rn(hdt, a.y));
+    v.z = __fadd_rn(__fmul_rn(v.z, exp_fac), __fmul_rn(hdt, a.z));
+    }
+
+// m v^2 of one particle in double, the summand of ComputeThermo's kinetic energy (hoomd/ComputeThermo.cc:241-252)
+__device__ __forceinline__ double nvt_mv2(const float4 v)
+    {
+    return (double)v.w * ((double)v.x * (double)v.x + (double)v.y * (double)v.y + (double)v.z * (double)v.z);
+    }
+
+// TwoStepNVTMTK::advanceThermostat from sum(m v^2) of the half-step velocities.  m_T->getValue() is a double in the
+// reference, so the bracket and the two sums are evaluated in double and stored as Scalar; no FMA contraction.
+__device__ __forceinline__ void nvt_advance_body(NvtState* st, double mv2_sum, unsigned int ndof, float T, float tau,
+                                                 float dt)
+    {
+    const float ke = (float)__dmul_rn(mv2_sum, 0.5);
+    const float curr_T = __fmul_rn(__fdiv_rn(2.0f, (float)ndof), ke); // ComputeThermo::getTranslationalTemperature
+    const double dev = __dsub_rn(__ddiv_rn((double)curr_T, (double)T), 1.0);
+    const float c = __fdiv_rn(__fdiv_rn(__fmul_rn(0.5f, dt), tau), tau);
+    const double step = __dmul_rn((double)c, dev);
+    const float xi_prime = (float)__dadd_rn((double)st->xi, step);
+    const float xi = (float)__dadd_rn((double)xi_prime, step);
+    st->xi = xi;
+    st->eta = __fadd_rn(st->eta, __fmul_rn(xi_prime, dt));
+    // exp(-(1/2)*xi*dt) as the host libm's expf gives it: round the double result (correctly rounded but for ties)
+    st->exp_fac = (float)exp((double)__fmul_rn(__fmul_rn(-0.5f, xi), dt));
+    }
+
 } // namespace b200

@@ -34,7 +34,16 @@ struct StepState
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
                              const unsigned int* d_N = nullptr);
 unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot); // launches of one launch_cell_list
-cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream);
+// Device-driven stepping: the build kernel itself raises StepState::overflow when a row exceeds Nmax (what the host's
+// checkConditions does after the fact, hoomd/md/NeighborList.cc:1389-1405) and, on a single GPU, zeroes steps_left so the
+// rest of the chunk turns into no-ops and `conditions` keeps exactly the counts of the overflowing rebuild.
+struct OverflowHook
+    {
+    unsigned int* overflow = nullptr;   // set to 1 on overflow
+    unsigned int* steps_left = nullptr; // set to 0 on overflow (single GPU)
+    };
+cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream,
+                                OverflowHook hook = OverflowHook());
 unsigned int pick_pair_tpp(unsigned int N);
 
 // Multi-GPU: ghost update fused into the MD step.  The owner of a boundary particle writes its new position (+ the
@@ -63,7 +72,7 @@ struct FusedStepArgs
     const unsigned int* tag; const float* rcut_max; const float* gamma;
     const float* maxsq;           // per type: distance-check threshold^2 (NeighborList.cc:1002-1006, fixed box)
     unsigned int N; b200_box box; float dt; float r_buff;
-    int method;                   // 1 = NVE, 2 = Langevin
+    int method;                   // 1 = NVE, 2 = Langevin, 3 = NVT (MTK)
     int limit; float limit_val; int zero_force;
     float kT; unsigned int seed; int noiseless_t;
     const unsigned int* d_N;      // multi-GPU: live local particle count (N above is then the capacity); else NULL
@@ -72,6 +81,9 @@ struct FusedStepArgs
     // before step two (Integrator::computeNetForce).  NULL = the pair force is the only force.
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch;
     GhostSendArgs gs;             // multi-GPU: ghost update fused into k_md_step
+    // TwoStepNVTMTK: thermostat state {xi, eta, exp_fac, -} on the device, per-CTA partial sums of m v^2 (one slot per CTA of
+    // the widest k_md_step grid), NDOF of the group, coupling period tau; kT above is the set point
+    float* nvt_state; double* nvt_partial; unsigned int nvt_ndof; float nvt_tau;
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);

@@ -38,6 +38,7 @@ template<class Evaluator> struct MdStepArgs
     int force_only;           // compute and store the net force only (prepRun / stand-alone force evaluation)
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch; // second ForceCompute (bonds)
     GhostSendArgs gs; int gs_buffer; // multi-GPU: fused ghost update into the peers' buffer gs_buffer (0 = A, 1 = B)
+    NvtState* nvt; double* nvt_partial; unsigned int nvt_ndof; float nvt_tau; // TwoStepNVTMTK (method 3)
     };
 
 // write particle i's position into every ghost slot it feeds on the neighbor ranks (plain stores over NVLink)
@@ -68,7 +69,7 @@ constexpr int MD_BLOCK = B200_MD_BLOCK; // threads per CTA of k_md_step (B200 sw
 template<class Evaluator, bool VIRIAL>
 __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, float4 F,
                                                   const float4 pi4, float (&vir)[6], unsigned int ts2, bool last,
-                                                  bool store_force)
+                                                  bool store_force, double& mv2)
     {
     bool moved = false;
     float4 v = a.vel[i];
@@ -93,11 +94,16 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
             }
         }
     const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
-    const bool nve = a.method == 1;
+    const bool nve = a.method == 1, nvt = a.method == 3;
+    // one thermostat factor serves step two(ts) and step one(ts+1): advanceThermostat runs between step one and step two of
+    // the same update() (hoomd/md/TwoStepNVTMTK.cc:296), i.e. between two launches of this kernel
+    const float exp_fac = nvt ? a.nvt->exp_fac : 1.0f;
     float3s acc;
     // ---- integrateStepTwo(ts) ----
     if (nve)
         nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
+    else if (nvt)
+        nvt_step_two_body(v, acc, F, a.dt, exp_fac);
     else
         langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
     a.accel[i] = acc;
@@ -107,7 +113,13 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         float4 p = pi4;
         int3 img = a.image[i];
         const float4 lp = a.last_pos[i];
-        nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
+        if (nvt)
+            {
+            nvt_step_one_body(p, v, acc, img, a.box, a.dt, exp_fac);
+            mv2 = nvt_mv2(v); // summand of the kinetic energy advanceThermostat needs (md_step_finish reduces it)
+            }
+        else
+            nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
         a.pos_out[i] = p;
         if (a.gs.tab) md_step_send_ghosts(a, i, p);
         a.image[i] = img;
@@ -127,18 +139,39 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     return moved;
     }
 
-// last CTA to finish takes the rebuild decision for the next launch (every thread of the CTA must call this)
+// last CTA to finish takes the rebuild decision for the next launch (every thread of the CTA must call this).
+// NVT: the CTAs leave their partial sum of m v^2 behind and the last one reduces them in a fixed order and advances the
+// thermostat (ComputeThermo + TwoStepNVTMTK::advanceThermostat without leaving the kernel).
 template<class Evaluator>
 __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, StepState* st, bool moved,
-                                               unsigned int steps_left, bool last)
+                                               unsigned int steps_left, bool last, double mv2 = 0.0)
     {
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    const bool nvt = a.method == 3 && !last;
+    const unsigned int nblocks = gridDim.x * gridDim.y * gridDim.z;
+    __shared__ double s_mv2[MD_BLOCK / 32];
+    __shared__ unsigned int s_is_last;
+    if (nvt)
+        {
+        for (int o = 16; o > 0; o >>= 1) mv2 += __shfl_xor_sync(0xffffffffu, mv2, o);
+        if ((threadIdx.x & 31) == 0) s_mv2[threadIdx.x >> 5] = mv2;
+        __syncthreads();
+        if (threadIdx.x == 0)
+            {
+            double x = 0.0;
+            for (int w = 0; w < MD_BLOCK / 32; w++) x += s_mv2[w];
+            a.nvt_partial[blockIdx.x] = x;
+            __threadfence(); // the partial must be visible before this CTA's ticket
+            }
+        }
     if (threadIdx.x == 0)
         {
         // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
         const unsigned long long old = atomicAdd(&st->ticket, inc);
-        if ((unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1)
+        const bool is_last = (unsigned int)old == nblocks - 1;
+        if (nvt) s_is_last = is_last ? 1u : 0u;
+        if (is_last)
             {
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
@@ -155,6 +188,26 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
 #if (CUDART_VERSION >= 12040)
             if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
 #endif
+            if (nvt) __threadfence();
+            }
+        }
+    if (nvt)
+        {
+        __syncthreads();
+        if (s_is_last)
+            {
+            double x = 0.0;
+            for (unsigned int b = threadIdx.x; b < nblocks; b += MD_BLOCK) x += __ldcg(a.nvt_partial + b);
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+            __syncthreads(); // s_mv2 was read by thread 0 above
+            if ((threadIdx.x & 31) == 0) s_mv2[threadIdx.x >> 5] = x;
+            __syncthreads();
+            if (threadIdx.x == 0)
+                {
+                double t = 0.0;
+                for (int w = 0; w < MD_BLOCK / 32; w++) t += s_mv2[w];
+                nvt_advance_body(a.nvt, t, a.nvt_ndof, a.kT, a.nvt_tau, a.dt);
+                }
             }
         }
     }
@@ -180,6 +233,7 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.d_N = fa.d_N; a.mg = fa.mg;
     a.extra_force = fa.extra_force; a.extra_virial = fa.extra_virial; a.extra_virial_pitch = fa.extra_virial_pitch;
     a.gs = fa.gs; a.gs_buffer = copy_pos_on_last ? 0 : 1; // phase 0 writes B, phase 1 writes A
+    a.nvt = (NvtState*)fa.nvt_state; a.nvt_partial = fa.nvt_partial; a.nvt_ndof = fa.nvt_ndof; a.nvt_tau = fa.nvt_tau;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

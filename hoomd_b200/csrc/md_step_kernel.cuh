@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
 
     // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
     bool moved = false;
+    double mv2 = 0.0;
     const unsigned int i = blockIdx.x * PPB + threadIdx.x;
     if (threadIdx.x < PPB && i < N)
         {
@@ -63,9 +64,10 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
 #pragma unroll
             for (int c = 0; c < 6; c++) vir[c] = s_virial[c * PPB + threadIdx.x];
             }
-        moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force);
+        moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force,
+                                                     mv2);
         }
-    md_step_finish(a, st, moved, steps_left, last);
+    md_step_finish(a, st, moved, steps_left, last, mv2);
     }
 
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>

@@ -3,6 +3,7 @@
 // compaction into the CSR list.  Membership arithmetic and entry order are those of the CPU oracle
 // hoomd/md/NeighborListBinned.cc:144-236 (see include/hoomd_b200.h).
 #include "common.cuh"
+#include "kernels.h"
 #include "bulk_copy.cuh"
 #include <cstdlib>
 
@@ -32,6 +33,15 @@ __device__ __forceinline__ int axis_set(int c, int m, bool periodic, int out[3])
     return n;
     }
 
+// on overflow the true count goes to `conditions` (the host grows Nmax and rebuilds, NeighborList.cc:226-244)
+__device__ __forceinline__ void nlist_report_overflow(unsigned int* conditions, unsigned int type_i, unsigned int n,
+                                                      const OverflowHook& hook)
+    {
+    atomicMax(&conditions[type_i], n);
+    if (hook.overflow) *hook.overflow = 1u;
+    if (hook.steps_left) *hook.steps_left = 0u;
+    }
+
 template<bool MULTI_TYPE>
 __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__ nlist,
                                                       unsigned int* __restrict__ n_neigh,
@@ -45,8 +55,10 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
                                                       const unsigned int* __restrict__ cell_type, uint3 dim, Box box,
                                                       float3 ghost_width, const float* __restrict__ r_cut,
                                                       const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                      int half_storage, const unsigned int* __restrict__ enable)
+                                                      int half_storage, const unsigned int* __restrict__ enable,
+                                                      OverflowHook hook)
     {
+    pdl_wait();
     if (enable && !*enable) return;
     const unsigned int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned int lane = threadIdx.x & 31;
@@ -124,7 +136,7 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
         // on overflow the true count goes to `conditions` (the host grows Nmax and rebuilds, NeighborList.cc:226-244);
         // the stored count is clamped so that a consumer running before the retry never reads past this segment
         n_neigh[i] = min(n, Nmax_i);
-        if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+        if (n > Nmax_i) nlist_report_overflow(conditions, type_i, n, hook);
         if (last_pos) last_pos[i] = make_float4(pi.x, pi.y, pi.z, 0.0f);
         }
     }
@@ -200,8 +212,9 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
                                                           const unsigned int* __restrict__ cell_type, uint3 dim,
                                                           Box box, const float* __restrict__ r_cut,
                                                           const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                          const unsigned int* __restrict__ enable)
+                                                          const unsigned int* __restrict__ enable, OverflowHook hook)
     {
+    pdl_wait();
     if (enable && !*enable) return;
     extern __shared__ float4 s_cand[];
     unsigned int* s_type = reinterpret_cast<unsigned int*>(s_cand + NL_CAP);
@@ -318,7 +331,7 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
                 else
                     {
                     n_neigh[i] = min(n, Nmax_i);
-                    if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+                    if (n > Nmax_i) nlist_report_overflow(conditions, type_i, n, hook);
                     if (last_pos) last_pos[i] = make_float4(pi4.x, pi4.y, pi4.z, 0.0f);
                     }
                 }
@@ -349,8 +362,9 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
                                                                   const unsigned int* __restrict__ cell_type, uint3 dim,
                                                                   Box box, const float* __restrict__ r_cut,
                                                                   const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                                  const unsigned int* __restrict__ enable)
+                                                                  const unsigned int* __restrict__ enable, OverflowHook hook)
     {
+    pdl_wait();
     if (enable && !*enable) return;
     extern __shared__ float4 s_all[];
     __shared__ unsigned int s_beg_all[NW_WARPS][28], s_off_all[NW_WARPS][28];
@@ -454,7 +468,7 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
                 else
                     {
                     n_neigh[i] = min(n, Nmax_i);
-                    if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+                    if (n > Nmax_i) nlist_report_overflow(conditions, type_i, n, hook);
                     if (last_pos) last_pos[i] = make_float4(pi4.x, pi4.y, pi4.z, 0.0f);
                     }
                 }
@@ -522,8 +536,9 @@ __global__ void __launch_bounds__(NC_BLOCK) k_nlist_cellscan(unsigned int* __res
                                                              const unsigned int* __restrict__ cell_type, uint3 dim,
                                                              Box box, const float* __restrict__ r_cut,
                                                              const float* __restrict__ r_listsq, unsigned int ntypes,
-                                                             unsigned int cap, const unsigned int* __restrict__ enable)
+                                                             unsigned int cap, const unsigned int* __restrict__ enable, OverflowHook hook)
     {
+    pdl_wait();
     if (enable && !*enable) return;
     // dynamic shared memory: [cap + 16] candidates, then [cap + 16] types
     extern __shared__ float4 s_cand[];
@@ -719,7 +734,7 @@ __global__ void __launch_bounds__(NC_BLOCK) k_nlist_cellscan(unsigned int* __res
                 else
                     {
                     n_neigh[i] = min(n, Nmax_i);
-                    if (n > Nmax_i) atomicMax(&conditions[type_i], n);
+                    if (n > Nmax_i) nlist_report_overflow(conditions, type_i, n, hook);
                     if (last_pos) last_pos[i] = make_float4(pi4.x, pi4.y, pi4.z, 0.0f);
                     }
                 }
@@ -884,7 +899,8 @@ int b200_nlist_build_head_list(unsigned int* d_head_list, unsigned int* d_req_si
 
 namespace b200
 {
-cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream)
+cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream,
+                                OverflowHook hook)
     {
     if (!box_is_orthorhombic(a->box)) return cudaErrorNotSupported;
     if (a->N == 0) return cudaSuccess;
@@ -892,6 +908,7 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
     Box box = make_box(a->box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
+    const bool pdl = enable && pdl_enabled(); // chained behind k_cell_rank (launch_chain, common.cuh)
     static const bool use_warp_kernel = getenv("HOOMD_B200_NLIST_WARP") != nullptr; // A/B switches for profiling
     // the cell-scan kernel executes ~2.5x fewer instructions than the tiled one but is latency-bound per CTA and measured
     // slower on B200 (rebuild 85 vs 71 us at 64k particles, 782 vs 637 us at 1M): opt-in until that is fixed
@@ -913,7 +930,7 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
         k_nlist_cellscan<MT, HALF, BULK><<<grid, NC_BLOCK, smem, stream>>>(                                          \
             a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,      \
             a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,     \
-            a->ntypes, cap, enable);                                                                                 \
+            a->ntypes, cap, enable, hook);                                                                               \
     } while (0)
         if (a->ntypes > 1)
             {
@@ -936,10 +953,10 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
         const unsigned int grid = (ncells + NW_WARPS - 1) / NW_WARPS;
         const size_t smem = (size_t)NW_WARPS * NW_CAP * (sizeof(float4) + (a->ntypes > 1 ? sizeof(unsigned int) : 0));
 #define B200_NW_LAUNCH(MT, HALF)                                                                                     \
-    k_nlist_warpcell<MT, HALF><<<grid, NW_WARPS * 32, smem, stream>>>(                                              \
+    launch_chain(k_nlist_warpcell<MT, HALF>, dim3(grid), dim3(NW_WARPS * 32), smem, stream, pdl,                  \
         a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,         \
         a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,        \
-        a->ntypes, enable)
+        a->ntypes, enable, hook)
         if (a->ntypes > 1)
             {
             if (a->half_storage) B200_NW_LAUNCH(true, true); else B200_NW_LAUNCH(true, false);
@@ -957,10 +974,10 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
         const dim3 grid(a->dim.x, a->dim.y, a->dim.z);
         const size_t smem1 = NL_CAP * sizeof(float4), smemN = NL_CAP * (sizeof(float4) + sizeof(unsigned int));
 #define B200_NL_LAUNCH(MT, HALF, SMEM)                                                                               \
-    k_nlist_tiled<MT, HALF><<<grid, NL_BLOCK, SMEM, stream>>>(                                                     \
+    launch_chain(k_nlist_tiled<MT, HALF>, grid, dim3(NL_BLOCK), SMEM, stream, pdl,                                 \
         a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos, a->d_conditions, a->d_Nmax, a->d_head_list, a->N,         \
         a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, a->d_r_cut, a->d_r_listsq,        \
-        a->ntypes, enable)
+        a->ntypes, enable, hook)
         if (a->ntypes > 1)
             {
             if (a->half_storage) B200_NL_LAUNCH(true, true, smemN); else B200_NL_LAUNCH(true, false, smemN);
@@ -979,14 +996,14 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
                                                        a->d_Nmax, a->d_head_list, (const float4*)a->d_pos, a->N,
                                                        a->d_cell_start, (const float4*)a->d_cell_xyzf, a->d_cell_type,
                                                        dim, box, gw, a->d_r_cut, a->d_r_listsq, a->ntypes,
-                                                       a->half_storage, enable);
+                                                       a->half_storage, enable, hook);
     else
         k_nlist_binned<false><<<grid, 128, 0, stream>>>(a->d_nlist, a->d_n_neigh, (float4*)a->d_last_pos,
                                                         a->d_conditions, a->d_Nmax, a->d_head_list,
                                                         (const float4*)a->d_pos, a->N, a->d_cell_start,
                                                         (const float4*)a->d_cell_xyzf, a->d_cell_type, dim, box, gw,
                                                         a->d_r_cut, a->d_r_listsq, a->ntypes, a->half_storage,
-                                                        enable);
+                                                        enable, hook);
     return cudaGetLastError();
     }
 } // namespace b200

@@ -503,7 +503,10 @@ __global__ void __launch_bounds__(TILE_BLOCK* TPP) k_md_step_tile(const __grid_c
                         }
                     }
                 else
-                    moved |= md_step_integrate<Evaluator, VIRIAL>(a, gp, F, pi4, vir, ts2, last, store_force);
+                    {
+                    double mv2_unused = 0.0; // the NVT thermostat runs on the CSR path only (engine: add_nvt)
+                    moved |= md_step_integrate<Evaluator, VIRIAL>(a, gp, F, pi4, vir, ts2, last, store_force, mv2_unused);
+                    }
                 }
             }
         if (n_own == 0) mbar_wait(&s_bar, 0); // do not exit with the bulk copies in flight

@@ -146,6 +146,21 @@ class System:
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(_lib.lib().b200_sys_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _p(g), int(noiseless_t)))
 
+    def add_nvt(self, kT, tau):
+        """md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK (hoomd/md/integrate.py:163-260)"""
+        self._check(_lib.lib().b200_sys_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))
+
+    def set_nvt_state(self, xi, eta):
+        """restore the thermostat variables of an earlier run (restart / engine re-configuration)"""
+        st = np.array([xi, eta], np.float32)
+        self._check(_lib.lib().b200_sys_set_nvt_state(self.h, _p(st)))
+
+    def nvt_state(self):
+        """(xi, eta) of the Nose-Hoover thermostat"""
+        out = np.zeros(2, np.float32)
+        self._check(_lib.lib().b200_sys_get_nvt_state(self.h, _p(out)))
+        return out
+
     def set_sorter(self, period):
         self._check(_lib.lib().b200_sys_set_sorter(self.h, int(period)))
 

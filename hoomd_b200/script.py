@@ -613,7 +613,23 @@ class _Langevin(_Method):
         context.current.engine_dirty = True
 
 
+class _NVT(_Method):
+    """md.integrate.nvt (hoomd/md/integrate.py:163-260): Nose-Hoover thermostat, MTK equations"""
+
+    def __init__(self, group, kT, tau):
+        super().__init__(group)
+        self.kT, self.tau = float(kT), float(tau)
+
+    def set_params(self, kT=None, tau=None):
+        if kT is not None:
+            self.kT = float(kT)
+        if tau is not None:
+            self.tau = float(tau)
+        context.current.engine_dirty = True
+
+
 md.integrate.mode_standard = _ModeStandard
+md.integrate.nvt = _NVT
 md.integrate.nve = _NVE
 md.integrate.langevin = _Langevin
 
@@ -660,6 +676,9 @@ def _configure_engine():
     lj = ljs[0]
     if ctx.engine is not None:  # carry the state over
         sysd.take_snapshot()
+        for m in methods:  # IntegratorVariables live in the SystemDefinition, not in the method (hoomd/IntegratorData.h)
+            if isinstance(m, _NVT) and getattr(ctx.engine, "_has_nvt", False):
+                m._state = tuple(ctx.engine.nvt_state())
         ctx.engine.close()
     eng = System(sysd.pos4, (sysd.box.Lx, sysd.box.Ly, sysd.box.Lz), ntypes=len(sysd.types), vel4=sysd.vel4,
                  image=sysd.image)
@@ -688,6 +707,11 @@ def _configure_engine():
     m = methods[0]
     if isinstance(m, _NVE):
         eng.add_nve(limit=m.limit, zero_force=m.zero_force)
+    elif isinstance(m, _NVT):
+        eng.add_nvt(m.kT, m.tau)
+        eng._has_nvt = True
+        if getattr(m, "_state", None) is not None:
+            eng.set_nvt_state(*m._state)
     else:
         gamma = [m.gamma.get(tn, 1.0) for tn in sysd.types]
         eng.add_langevin(m.kT, m.seed, gamma=gamma, noiseless_t=m.noiseless_t)

@@ -308,6 +308,27 @@ B200_API int b200_langevin_step_two(const float* d_pos, float* d_vel, float* d_a
                                     const b200_langevin_args* args, float deltaT, unsigned int D,
                                     b200_stream_t stream);
 
+/* -----------------------------------------------------------------------------------------------------------------------
+ * TwoStepNVTMTK (Nose-Hoover / MTK thermostat, point particles) -- replaces gpu_nvt_mtk_step_one / gpu_nvt_mtk_step_two
+ * (hoomd/md/TwoStepNVTMTKGPU.cuh:17-38, .cu:30-212) and the host-side advanceThermostat (hoomd/md/TwoStepNVTMTK.cc:387-404).
+ * The reference passes m_exp_thermo_fac by value after reading the temperature back on the host; here the thermostat
+ * state lives in device memory, d_nvt_state = float[4] {xi, eta, exp_thermo_fac, unused} (initial state {0, 0, 1, 0}), so
+ * step one -> kinetic energy -> advanceThermostat -> force -> step two is one asynchronous chain.
+ *   step one : v = (v + (1/2) a dt) * exp_fac ; pos += dt v ; wrap           (TwoStepNVTMTK.cc:120-160)
+ *   advance  : T = 2 KE / ndof of the half-step velocities (double sum, fixed two-pass order over n_partial_blocks CTAs),
+ *              xi' = xi + (dt/2)/tau^2 (T/T0 - 1), xi = xi' + the same, eta += xi' dt, exp_fac = exp(-xi dt/2)
+ *   step two : a = F/m ; v = v * exp_fac + (1/2) dt a                        (TwoStepNVTMTK.cc:297-340)
+ * ndof = IntegratorTwoStep::getNDOF(group) (D N - D for one method on all particles, IntegratorTwoStep.cc:270-283). */
+B200_API int b200_nvt_mtk_step_one(float* d_pos, float* d_vel, const float* d_accel, int* d_image,
+                                   const unsigned int* d_group_members, unsigned int group_size, const b200_box* box,
+                                   const float* d_nvt_state, float deltaT, b200_stream_t stream);
+B200_API int b200_nvt_mtk_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members,
+                                   unsigned int group_size, const float* d_net_force, const float* d_nvt_state,
+                                   float deltaT, b200_stream_t stream);
+B200_API int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                                  const unsigned int* d_group_members, unsigned int group_size, unsigned int ndof,
+                                  float T, float tau, float deltaT, b200_stream_t stream);
+
 /* n draws of Saru(seed1,seed2,seed3).u32() and .s<float>(-1,1) per triple, evaluated on the device
  * (hoomd/Saru.h:324-340,417-441,603-640) -- used by the RNG parity tests. */
 B200_API int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3,
@@ -391,6 +412,11 @@ B200_API int b200_sys_setup_integrator(b200_system* s, float dt);
 B200_API int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force);
 /* md.integrate.langevin(group=all, kT, seed) + set_gamma per type (gamma NULL = 1.0) */
 B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
+/* md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK with its own ComputeThermo; the thermostat state stays on the device
+ * and advances inside the single-kernel MD step.  get_nvt_state: {xi, eta} (the method's IntegratorVariables). */
+B200_API int b200_sys_add_nvt(b200_system* s, float kT, float tau);
+B200_API int b200_sys_get_nvt_state(b200_system* s, float* xi_eta);
+B200_API int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta);
 /* hoomd.update.sort period (0 = disabled) */
 B200_API int b200_sys_set_sorter(b200_system* s, unsigned int period);
 B200_API int b200_sys_sort_now(b200_system* s);

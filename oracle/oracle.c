@@ -54,6 +54,7 @@ struct orc_system
     int shift_mode, pair_kind;
     /* Integrator */
     float dt; int method, limit, zero_force, noiseless_t; float limit_val, kT; unsigned int seed; float* gamma;
+    float nvt_tau, nvt_xi, nvt_eta, nvt_exp_fac; /* TwoStepNVTMTK: IntegratorVariables xi, eta and m_exp_thermo_fac */
     unsigned int timestep;
     /* BondData + PotentialBond + exclusions (tag == index in this restatement: no sorter) */
     unsigned int nbonds, n_bond_types;
@@ -746,10 +747,82 @@ static int compute_forces(orc_system* s, unsigned int ts)
     }
 
 /* ---- TwoStepNVE / TwoStepLangevin (hoomd/md/TwoStepNVE.cc:77-122,255-300; TwoStepLangevin.cc:86-125,240-330) ------------ */
+/* TwoStepNVTMTK::advanceThermostat (hoomd/md/TwoStepNVTMTK.cc:387-404), translational part: the temperature of the
+   half-step velocities from ComputeThermo (double sum of m v^2, FP32 property, ComputeThermo.cc:241-252 / .h:109-116) */
+static void nvt_advance(orc_system* s)
+    {
+    double ke = 0.0;
+    if (s->compute_virial) /* pdata_flag::pressure_tensor: KE = half the trace of the kinetic pressure tensor (:222-238) */
+        {
+        double xx = 0.0, yy = 0.0, zz = 0.0;
+        for (unsigned int j = 0; j < s->N; j++)
+            {
+            const double mass = s->vel[j].w;
+            xx += mass * ((double)s->vel[j].x * (double)s->vel[j].x);
+            yy += mass * ((double)s->vel[j].y * (double)s->vel[j].y);
+            zz += mass * ((double)s->vel[j].z * (double)s->vel[j].z);
+            }
+        ke = 0.5f * (xx + yy + zz);
+        }
+    else
+        {
+        for (unsigned int j = 0; j < s->N; j++)
+            ke += (double)s->vel[j].w * ((double)s->vel[j].x * (double)s->vel[j].x
+                                         + (double)s->vel[j].y * (double)s->vel[j].y
+                                         + (double)s->vel[j].z * (double)s->vel[j].z);
+        ke *= 0.5f;
+        }
+    const unsigned int ndof = 3u * s->N - 3u; /* IntegratorTwoStep::getNDOF, IntegratorTwoStep.cc:270-283 */
+    const float curr_T = 2.0f / (float)ndof * (float)ke;
+    /* m_T->getValue() is a double (hoomd/Variant.h): the bracket and the sum are evaluated in double, then stored as Scalar */
+    const float dt = s->dt, tau = s->nvt_tau;
+    const double dev = (double)curr_T / (double)s->kT - (double)1.0f;
+    const float c = (1.0f / 2.0f) * dt / tau / tau;
+    const float xi_prime = (float)((double)s->nvt_xi + (double)c * dev);
+    s->nvt_xi = (float)((double)xi_prime + (double)c * dev);
+    s->nvt_eta += xi_prime * dt;
+    s->nvt_exp_fac = expf(-(1.0f / 2.0f) * s->nvt_xi * dt);
+    }
+
+/* TwoStepNVTMTK::integrateStepOne, point particles (hoomd/md/TwoStepNVTMTK.cc:107-160) */
+static void nvt_step_one(orc_system* s)
+    {
+    const float dt = s->dt, fac = s->nvt_exp_fac;
+    for (unsigned int j = 0; j < s->N; j++)
+        {
+        float vx = s->vel[j].x + (1.0f / 2.0f) * s->accel[j].x * dt;
+        float vy = s->vel[j].y + (1.0f / 2.0f) * s->accel[j].y * dt;
+        float vz = s->vel[j].z + (1.0f / 2.0f) * s->accel[j].z * dt;
+        vx *= fac; vy *= fac; vz *= fac;
+        s->pos[j].x += dt * vx; s->pos[j].y += dt * vy; s->pos[j].z += dt * vz;
+        s->vel[j].x = vx; s->vel[j].y = vy; s->vel[j].z = vz;
+        }
+    for (unsigned int j = 0; j < s->N; j++) box_wrap(&s->box, &s->pos[j], &s->image[j]);
+    nvt_advance(s);
+    }
+
+/* TwoStepNVTMTK::integrateStepTwo (hoomd/md/TwoStepNVTMTK.cc:297-340) */
+static void nvt_step_two(orc_system* s)
+    {
+    const float dt = s->dt, fac = s->nvt_exp_fac;
+    for (unsigned int j = 0; j < s->N; j++)
+        {
+        const float minv = 1.0f / s->vel[j].w;
+        s->accel[j].x = s->net_force[j].x * minv; s->accel[j].y = s->net_force[j].y * minv;
+        s->accel[j].z = s->net_force[j].z * minv;
+        float vx = s->vel[j].x * fac, vy = s->vel[j].y * fac, vz = s->vel[j].z * fac;
+        vx += (1.0f / 2.0f) * dt * s->accel[j].x;
+        vy += (1.0f / 2.0f) * dt * s->accel[j].y;
+        vz += (1.0f / 2.0f) * dt * s->accel[j].z;
+        s->vel[j].x = vx; s->vel[j].y = vy; s->vel[j].z = vz;
+        }
+    }
+
 static void step_one(orc_system* s)
     {
     const float dt = s->dt;
     const int nve = s->method == 1;
+    if (s->method == 3) { nvt_step_one(s); return; }
     for (unsigned int j = 0; j < s->N; j++)
         {
         if (nve && s->zero_force) s->accel[j].x = s->accel[j].y = s->accel[j].z = 0.0f;
@@ -777,6 +850,7 @@ static void step_one(orc_system* s)
 static void step_two(orc_system* s, unsigned int timestep)
     {
     const float dt = s->dt;
+    if (s->method == 3) { nvt_step_two(s); return; }
     for (unsigned int j = 0; j < s->N; j++)
         {
         if (s->method == 2)
@@ -1018,6 +1092,13 @@ int orc_add_langevin(orc_system* s, float kT, unsigned int seed, const float* ga
     for (unsigned int t = 0; t < s->ntypes; t++) s->gamma[t] = gamma ? gamma[t] : 1.0f;
     return 0;
     }
+int orc_add_nvt(orc_system* s, float kT, float tau) /* TwoStepNVTMTK ctor + initializeIntegratorVariables: xi = eta = 0 */
+    {
+    s->method = 3; s->limit = 0; s->zero_force = 0; s->kT = kT; s->nvt_tau = tau;
+    s->nvt_xi = s->nvt_eta = 0.0f; s->nvt_exp_fac = 1.0f;
+    return 0;
+    }
+void orc_get_nvt_state(orc_system* s, float* xi_eta) { xi_eta[0] = s->nvt_xi; xi_eta[1] = s->nvt_eta; }
 void orc_set_timestep(orc_system* s, unsigned int ts) { s->timestep = ts; }
 unsigned int orc_get_timestep(orc_system* s) { return s->timestep; }
 int orc_compute_nlist(orc_system* s, unsigned int ts) { return nl_compute(s, ts); }

@@ -38,6 +38,8 @@ def lib():
         L.orc_setup_integrator.argtypes = [vp, C.c_float]
         L.orc_add_nve.argtypes = [vp, C.c_int, C.c_float, C.c_int]
         L.orc_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
+        L.orc_add_nvt.argtypes = [vp, C.c_float, C.c_float]
+        L.orc_get_nvt_state.argtypes = [vp, vp]
         L.orc_set_timestep.argtypes = [vp, C.c_uint]
         L.orc_get_timestep.argtypes = [vp]
         L.orc_compute_nlist.argtypes = [vp, C.c_uint]
@@ -163,6 +165,14 @@ class OracleSystem:
     def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         lib().orc_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), int(noiseless_t))
+
+    def add_nvt(self, kT, tau):
+        lib().orc_add_nvt(self.h, C.c_float(kT), C.c_float(tau))
+
+    def nvt_state(self):
+        out = np.zeros(2, np.float32)
+        lib().orc_get_nvt_state(self.h, _ptr(out))
+        return out
 
     def set_timestep(self, ts):
         lib().orc_set_timestep(self.h, int(ts))

@@ -36,6 +36,8 @@ def lib():
         _lib.ref_get_bond_forces.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.ref_setup_pair.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_int]
+        _lib.ref_add_nvt.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        _lib.ref_get_nvt_state.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
         for name in ("ref_destroy", "ref_last_error", "ref_get_N", "ref_get_timestep", "ref_get_virial_pitch",
@@ -158,6 +160,15 @@ class RefSystem:
     def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(lib().ref_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), int(noiseless_t)))
+
+    def add_nvt(self, kT, tau):
+        self._check(lib().ref_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))
+
+    def nvt_state(self):
+        """Thermostat variables (xi, eta) of the NVT method."""
+        out = np.zeros(2, np.float32)
+        self._check(lib().ref_get_nvt_state(self.h, _ptr(out)))
+        return out
 
     def set_sorter(self, period):
         lib().ref_set_sorter(self.h, C.c_uint(period))

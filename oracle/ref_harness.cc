@@ -18,6 +18,7 @@
 #include "hoomd/Variant.h"
 #include "hoomd/SFCPackUpdater.h"
 #include "hoomd/ComputeThermo.h"
+#include "hoomd/md/TwoStepNVTMTK.h"
 #include "hoomd/Saru.h"
 #include "hoomd/md/NeighborListBinned.h"
 #include "hoomd/md/AllPairPotentials.h"
@@ -48,6 +49,8 @@ struct RefSystem
     std::shared_ptr<TwoStepLangevin> langevin;
     std::shared_ptr<SFCPackUpdater> sorter;
     std::shared_ptr<ComputeThermo> thermo;
+    std::shared_ptr<ComputeThermo> thermo_nvt; // the method's own compute (hoomd/md/integrate.py:370-372)
+    std::shared_ptr<TwoStepNVTMTK> nvt;
     unsigned int sorter_period = 0;
     unsigned int sorter_next = 0;
     unsigned int timestep = 0;
@@ -336,6 +339,43 @@ int ref_add_langevin(void* h, float kT, unsigned int seed, const float* gamma, i
             s->langevin->setGamma(t, gamma[t]);
     s->integrator->removeAllIntegrationMethods();
     s->integrator->addIntegrationMethod(s->langevin);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! md.integrate.nvt(group=all, kT, tau) (hoomd/md/integrate.py:349-383): the method gets its own ComputeThermo whose NDOF
+//! the integrator sets before the run (hoomd/md/integrate.py:152-160)
+int ref_add_nvt(void* h, float kT, float tau)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<Variant> T(new VariantConst(kT));
+    s->thermo_nvt = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, s->group_all, "nvt"));
+    s->nvt = std::shared_ptr<TwoStepNVTMTK>(new TwoStepNVTMTK(s->sysdef, s->group_all, s->thermo_nvt, tau, T, ""));
+    s->integrator->removeAllIntegrationMethods();
+    s->integrator->addIntegrationMethod(s->nvt);
+    s->thermo_nvt->setNDOF(s->integrator->getNDOF(s->group_all));
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! thermostat state {xi, eta} (IntegratorVariables of the method, hoomd/md/TwoStepNVTMTK.cc:387-404)
+int ref_get_nvt_state(void* h, float* xi_eta)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    // the method's accessor is protected: find its record in the IntegratorData (the last "nvt_mtk" registered)
+    std::shared_ptr<IntegratorData> idata = s->sysdef->getIntegratorData();
+    xi_eta[0] = xi_eta[1] = 0.0f;
+    for (unsigned int i = 0; i < idata->getNumIntegrators(); i++)
+        {
+        const IntegratorVariables& v = idata->getIntegratorVariables(i);
+        if (v.type == "nvt_mtk" && v.variable.size() >= 2)
+            {
+            xi_eta[0] = v.variable[0];
+            xi_eta[1] = v.variable[1];
+            }
+        }
     REF_CATCH(s, 1)
     return 0;
     }

@@ -1,5 +1,7 @@
-for WL in lj64k lj1m; do for V in 1 0; do
-HOOMD_B200_NLIST_WARPCELL=$V python bench.py --workload $WL --no-scale-ref --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ab_$WL$V.json 2> gpurun_out/err.log; tail -2 gpurun_out/err.log
-python -c "
-import json; d=json.load(open('gpurun_out/ab_$WL$V.json')); print('$WL warpcell=$V', round(d['value']), d['roofline']['nlist_rebuild_ms'], round(d['e2e']['value']))"
-done; done
+set -x
+HOOMD_B200_PDL=1 timeout 400 python -m pytest tests -m gpu -q -x -k "cell or nlist or engine or overflow or step" 2>&1 | tail -5
+B="--no-cpu-baseline --no-scale-ref"
+for w in lj64k ka256k lj1m; do
+HOOMD_B200_PDL=1 timeout 300 python bench.py $B --workload $w > gpurun_out/r1p_${w}_pdl.json 2> gpurun_out/err.log; tail -3 gpurun_out/err.log; cut -c1-120 gpurun_out/r1p_${w}_pdl.json
+timeout 300 python bench.py $B --workload $w > gpurun_out/r1p_${w}_nopdl.json 2> gpurun_out/err.log; tail -3 gpurun_out/err.log; cut -c1-120 gpurun_out/r1p_${w}_nopdl.json
+done

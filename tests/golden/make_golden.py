@@ -98,7 +98,32 @@ def pair_evaluators():
     np.savez_compressed(os.path.join(HERE, "pair_evaluators.npz"), **res)
 
 
+def nvt():
+    """(10) Nose-Hoover (MTK) thermostat: an LJ liquid started at kT 1.5 and coupled to kT 1.0 with tau 0.5 -- state and
+    thermostat variables after 60 and 400 steps (Nmax growth and several rebuilds on the way), virial flag off and on
+    (the flag switches ComputeThermo to the pressure-tensor form of the kinetic energy)"""
+    pos, vel, L = workloads.sc_lattice(8, (1.0 / 0.4) ** (1.0 / 3.0), kT=1.5, seed=21)
+    res = dict(pos0=pos, vel0=vel, L=L)
+    for virial in (0, 1):
+        q = ref.RefSystem(pos, (L, L, L), vel4=vel)
+        q.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+        q.set_virial(bool(virial))
+        q.setup_integrator(0.005)
+        q.add_nvt(1.0, 0.5)
+        for nsteps, label in ((60, "a"), (340, "b")):
+            q.run(nsteps)
+            p, th = q.particles(), q.thermo()
+            k = "v%d%s_" % (virial, label)
+            res[k + "pos"], res[k + "vel"], res[k + "accel"], res[k + "image"] = p["pos"], p["vel"], p["accel"], p["image"]
+            res[k + "state"] = q.nvt_state()
+            res[k + "thermo"] = np.array([th[x] for x in ("ke", "pe", "T", "P", "ndof")])
+    np.savez_compressed(os.path.join(HERE, "nvt.npz"), **res)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "nvt":
+        nvt()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "kg":
         kremer_grest()
         return
@@ -107,6 +132,7 @@ def main():
         return
     kremer_grest()
     pair_evaluators()
+    nvt()
     out = {}
     # (1) Saru stream: (tag, timestep, seed) triples
     rng = np.random.default_rng(0)

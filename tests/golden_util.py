@@ -227,3 +227,39 @@ def check_pair_evaluators(make, rtol, bit_exact=False, kinds=None, pos_tol=2e-4,
         else:
             assert np.abs(p["pos"][:, :3] - g[kind + "_traj_pos"][:, :3]).max() < pos_tol, kind
             assert np.abs(p["vel"][:, :3] - g[kind + "_traj_vel"][:, :3]).max() < vel_tol, kind
+
+
+def check_nvt(make, bit_exact, pos_tol=2e-4, vel_tol=2e-3, state_rtol=2e-5, long_run=True):
+    """md.integrate.nvt against the reference's TwoStepNVTMTK + ComputeThermo (tests/golden/nvt.npz).  bit_exact: every
+    array and the thermostat variables bit for bit (the C restatement sums the kinetic energy in the reference's order);
+    otherwise tolerances: a device reduction adds the same doubles in another order, which can move the FP32 temperature
+    by one ulp."""
+    g = load("nvt")
+    L = float(g["L"])
+    for virial in (0, 1):
+        s = make(g["pos0"], (L, L, L), 1, vel=g["vel0"])
+        s.setup_lj(r_cut=2.5, r_buff=0.4)
+        s.set_virial(bool(virial))
+        s.setup_integrator(0.005)
+        s.add_nvt(1.0, 0.5)
+        for nsteps, label in ((60, "a"), (340, "b")):
+            if label == "b" and not long_run:
+                break
+            s.run(nsteps)
+            k = "v%d%s_" % (virial, label)
+            p, st = s.particles(), s.nvt_state()
+            if bit_exact:
+                for a in ("pos", "vel", "accel", "image"):
+                    assert np.array_equal(p[a].view(np.uint32), g[k + a].view(np.uint32)), (k, a)
+                assert np.array_equal(st.view(np.uint32), g[k + "state"].view(np.uint32)), (k, st, g[k + "state"])
+            else:
+                # 400 steps are ~2 Lyapunov times: a last-bit difference has grown, the global thermostat variables less so
+                rt = state_rtol if label == "a" else 100 * state_rtol
+                assert np.allclose(st, g[k + "state"], rtol=rt, atol=1e-6), (k, st, g[k + "state"])
+                if label == "a":  # before chaos amplifies a last-bit difference
+                    assert np.abs(p["pos"][:, :3] - g[k + "pos"][:, :3]).max() < pos_tol, k
+                    assert np.abs(p["vel"][:, :3] - g[k + "vel"][:, :3]).max() < vel_tol, k
+                    assert np.array_equal(p["image"], g[k + "image"]), k
+            th = s.thermo()
+            for name, w in zip(("ke", "pe", "T", "ndof"), g[k + "thermo"][[0, 1, 2, 4]]):
+                assert abs(th[name] - w) <= (1e-6 if bit_exact else 5e-4) * abs(w), (k, name, th[name], w)

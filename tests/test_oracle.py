@@ -183,3 +183,28 @@ def test_bonded_restatement_matches_reference_bitwise(kind, excl):
 def test_pair_evaluators_golden_bit_exact():
     """Gauss, Yukawa, Mie, force-shifted LJ, Morse in all energy-shift modes + trajectories"""
     G.check_pair_evaluators(make, 0.0, bit_exact=True)
+
+
+def test_nvt_golden_bit_exact():
+    """TwoStepNVTMTK + ComputeThermo restated: trajectory AND thermostat variables bit for bit (tests/golden/nvt.npz)"""
+    G.check_nvt(make, bit_exact=True)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+def test_nvt_restatement_matches_reference_bitwise():
+    """fresh two-type input, another tau / set point, 250 steps incl. Nmax growth"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.6) ** (1.0 / 3.0), kT=2.0, seed=41, ntypes=2, type_fractions=[0.8, 0.2])
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (L, L, L), ntypes=2, vel4=vel)
+        s.setup_lj(full=True, r_cut=[[2.5, 2.0], [2.0, 2.2]], epsilon=[[1.0, 1.5], [1.5, 0.5]],
+                   sigma=[[1.0, 0.8], [0.8, 0.88]], r_buff=0.3, shift_mode=1)
+        s.setup_integrator(0.004)
+        s.add_nvt(0.8, 0.25)
+        s.run(250)
+        outs.append((s.particles(), s.nvt_state()))
+    (pa, xa), (pb, xb) = outs
+    for k in ("pos", "vel", "accel", "image"):
+        assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
+    assert np.array_equal(xa.view(np.uint32), xb.view(np.uint32)), (xa, xb)
+    assert abs(xa[0]) > 1e-3
