@@ -39,13 +39,18 @@ WORKLOADS = {
 KG_CHAIN = 100
 
 
+METHOD_OVERRIDE = os.environ.get("HOOMD_B200_BENCH_METHOD", "")
+
+
 def n_types(workload):
     return 2 if workload.startswith("ka") else 1
 
 
 def add_method(s, workload, kT):
     """the integration method the BASELINE config names: Langevin for Kob-Andersen, NVE otherwise"""
-    if workload.startswith("ka"):
+    if METHOD_OVERRIDE == "nvt":  # A/B measurement of the thermostat's cost, never the default line
+        s.add_nvt(kT, 0.5)
+    elif workload.startswith("ka"):
         s.add_langevin(kT, 7)
     else:
         s.add_nve()
@@ -447,7 +452,8 @@ def main():
         line = {"metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": desc, "N": N, "md_steps_per_step": md_steps,
+                "config": {"workload": desc + (" [integration method overridden: %s]" % METHOD_OVERRIDE
+                                               if METHOD_OVERRIDE else ""), "N": N, "md_steps_per_step": md_steps,
                            "parallelism": "1 GPU" if world == 1 else
                            "spatial domain decomposition %s, ghosts + migration over NVLink peer memory" % (
                                "x".join(str(g) for g in mg_stats["grid"])),

@@ -170,10 +170,13 @@ struct b200_system
     unsigned int seed_hashed = 0;
     int noiseless_t = 0;
     DevBuf<float> d_gamma;
-    // TwoStepNVTMTK: {xi, eta, exp_fac, -} lives on the device (d_nvt), checkpointed per chunk; partial sums of m v^2
+    // TwoStepNVTMTK: {xi, eta, exp_fac, gen} lives on the device (d_nvt), checkpointed per chunk; fixed-point accumulators
+    // of sum(m v^2) for the step kernel (nvt_acc, scale nvt_scale), partial sums for the stand-alone pass
     float nvt_tau = 0.0f;
     DevBuf<float> d_nvt, ck_nvt;
     DevBuf<double> nvt_partial;
+    DevBuf<unsigned long long> nvt_acc;
+    double nvt_scale = 1.0;
     static constexpr unsigned int NVT_BLOCKS = 592; // CTAs of the stand-alone kinetic-energy pass (4 per SM)
 
     // ---- SFCPackUpdater ---------------------------------------------------------------------------------------
@@ -326,8 +329,9 @@ static unsigned int nvt_ndof(const b200_system* s) { return 3u * s->N - 3u; }
 // ComputeThermo (kinetic energy of the half-step velocities) + TwoStepNVTMTK::advanceThermostat, on the device
 static void nvt_advance(b200_system* s)
     {
-    CUDA_OK(b200_nvt_mtk_advance(s->d_nvt.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p, nullptr,
-                                 s->N, nvt_ndof(s), s->kT, s->nvt_tau, s->dt, s->stream));
+    // tagged with the timestep: the step kernel that runs step two of this update finds its factor ready
+    CUDA_OK(launch_nvt_advance(s->d_nvt.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p, nullptr,
+                               s->N, nvt_ndof(s), s->kT, s->nvt_tau, s->dt, s->timestep, s->stream));
     s->kernels_last_run += 2;
     }
 
@@ -352,7 +356,8 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         }
     if (s->method == 3)
         {
-        a.nvt_state = s->d_nvt.p; a.nvt_partial = s->nvt_partial.p; a.nvt_ndof = nvt_ndof(s); a.nvt_tau = s->nvt_tau;
+        a.nvt_state = s->d_nvt.p; a.nvt_acc = s->nvt_acc.p; a.nvt_scale = s->nvt_scale; a.nvt_ndof = nvt_ndof(s);
+        a.nvt_tau = s->nvt_tau;
         }
     }
 
@@ -986,7 +991,10 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     CUDA_OK(cudaMemcpyAsync(s->ck_image.p, s->image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
     const bool ck_force_update = s->force_update;
     if (s->method == 3)
+        {
         CUDA_OK(cudaMemcpyAsync(s->ck_nvt.p, s->d_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
+        }
 
     StepState& st = *s->h_state;
     memset(&st, 0, sizeof(st));
@@ -1020,6 +1028,10 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
+    if (st.nvt_error)
+        throw std::runtime_error(st.nvt_error == 1u
+                                     ? "integrate.nvt: kinetic energy is more than 2^20 times the set point (diverged?)"
+                                     : "integrate.nvt: thermostat hand-off inside the step kernel timed out");
     if (!st.overflow) cell_list_check_conditions(s);
 
     if (st.overflow)
@@ -1611,27 +1623,34 @@ int b200_sys_add_nvt(b200_system* s, float kT, float tau)
     s->zero_force = 0;
     s->kT = kT;
     s->nvt_tau = tau;
-    // initializeIntegratorVariables: xi = eta = 0, m_exp_thermo_fac = 1 (TwoStepNVTMTK.cc:39,50-54)
-    const float init[4] = {0.0f, 0.0f, 1.0f, 0.0f};
+    // initializeIntegratorVariables: xi = eta = 0, m_exp_thermo_fac = 1 (TwoStepNVTMTK.cc:39,50-54); gen = "no advance yet"
+    float init[4] = {0.0f, 0.0f, 1.0f, 0.0f};
+    const unsigned int no_gen = 0xfffffffeu;
+    memcpy(&init[3], &no_gen, 4);
     s->d_nvt.alloc(4);
     s->ck_nvt.alloc(4);
     s->d_nvt.upload(init, 4, s->stream);
-    // one slot per CTA of the widest k_md_step grid (>= 4 particles per CTA: 128 threads, <= 32 lanes per particle) or of the
-    // stand-alone pass
-    s->nvt_partial.alloc(std::max<size_t>(b200_system::NVT_BLOCKS, s->N / 4 + 2));
+    s->nvt_partial.alloc(b200_system::NVT_BLOCKS);
+    // fixed-point accumulators of sum(m v^2): 2^62 units span 2^20 x the set point's ndof kT (a power-of-two scale, so the
+    // conversion only rounds to an integer: 2^-42 of the expected sum per contribution)
+    s->nvt_acc.alloc(2 * NVT_SLOTS * NVT_SLOT_STRIDE);
+    CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
+    s->nvt_scale = std::exp2(std::floor(42.0 - std::log2((double)nvt_ndof(s) * (double)kT)));
     CUDA_OK(cudaStreamSynchronize(s->stream));
     invalidate_graph(s);
     SYS_CATCH(s)
     }
 
-// restart / re-configuration: IntegratorVariables of a previous run (TwoStepNVTMTK.cc:50-58, restartInfoTestValid)
+// Re-configuration within one job: the IntegratorVariables of the engine this one replaces.  m_exp_thermo_fac is a pure
+// function of xi (TwoStepNVTMTK.cc:402), so a continuing run keeps the factor the last advanceThermostat left behind.
 int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta)
     {
     SYS_TRY(s)
     if (s->method != 3) throw std::runtime_error("integrate.nvt: no NVT method set");
-    // m_exp_thermo_fac is NOT part of the restart record: the reference starts from 1.0 and recomputes it at the first
-    // advanceThermostat (TwoStepNVTMTK.cc:39)
-    const float h[4] = {xi_eta[0], xi_eta[1], 1.0f, 0.0f};
+    const float arg = -0.5f * xi_eta[0] * s->dt;
+    float h[4] = {xi_eta[0], xi_eta[1], (float)std::exp((double)arg), 0.0f};
+    const unsigned int no_gen = 0xfffffffeu;
+    memcpy(&h[3], &no_gen, 4);
     s->d_nvt.upload(h, 4, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     SYS_CATCH(s)
@@ -1883,6 +1902,15 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         st.ntypes = s->ntypes;
         st.steps_left = iters + 1;
         st.N = s->N;
+        float nvt_saved[4] = {0.0f, 0.0f, 1.0f, 0.0f};
+        if (s->method == 3)
+            {
+            // the thermostat takes part in the scratch steps: start from "factor ready for the first launch", restore after
+            CUDA_OK(cudaStreamSynchronize(s->stream));
+            CUDA_OK(cudaMemcpy(nvt_saved, s->d_nvt.p, sizeof(nvt_saved), cudaMemcpyDeviceToHost));
+            memcpy(&st.ts_step_two, &nvt_saved[3], 4);
+            CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
+            }
         CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
         FusedStepArgs fa;
         fused_args(s, fa);
@@ -1896,6 +1924,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaStreamSynchronize(s->stream));
+        if (s->method == 3) CUDA_OK(cudaMemcpy(s->d_nvt.p, nvt_saved, sizeof(nvt_saved), cudaMemcpyHostToDevice));
         float ms2 = 0.0f;
         CUDA_OK(cudaEventElapsedTime(&ms2, e0, e1));
         cudaEventDestroy(e0);

@@ -5,6 +5,7 @@
 // nothing is contracted into FMAs: one half step is bit-identical to the reference.
 #include "common.cuh"
 #include "integrate_body.cuh"
+#include "kernels.h"
 
 namespace b200
 {
@@ -251,12 +252,26 @@ __global__ void __launch_bounds__(256) k_nvt_ke_partial(double* __restrict__ par
 
 // pass 2 + TwoStepNVTMTK::advanceThermostat, one warp
 __global__ void k_nvt_advance(NvtState* __restrict__ state, const double* __restrict__ partial, unsigned int nblocks,
-                              unsigned int ndof, float T, float tau, float dt)
+                              unsigned int ndof, float T, float tau, float dt, unsigned int gen)
     {
     double x = 0.0;
     for (unsigned int b = threadIdx.x; b < nblocks; b += 32) x += partial[b];
     for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (threadIdx.x == 0) nvt_advance_body(state, x, ndof, T, tau, dt);
+    if (threadIdx.x == 0)
+        {
+        nvt_advance_body(state, x, ndof, T, tau, dt);
+        if (gen != 0xffffffffu) state->gen = gen; // engine: tag for the hand-off to the step kernel
+        }
+    }
+
+cudaError_t launch_nvt_advance(float* d_nvt_state, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                               const unsigned int* d_group, unsigned int group_size, unsigned int ndof, float T, float tau,
+                               float dt, unsigned int gen, cudaStream_t stream)
+    {
+    if (n_partial_blocks == 0 || !d_partial || !d_nvt_state) return cudaErrorInvalidValue;
+    k_nvt_ke_partial<<<n_partial_blocks, 256, 0, stream>>>(d_partial, (const float4*)d_vel, d_group, group_size);
+    k_nvt_advance<<<1, 32, 0, stream>>>((NvtState*)d_nvt_state, d_partial, n_partial_blocks, ndof, T, tau, dt, gen);
+    return cudaGetLastError();
     }
 } // namespace b200
 
@@ -355,12 +370,8 @@ int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigned int n_p
                          const unsigned int* d_group_members, unsigned int group_size, unsigned int ndof, float T,
                          float tau, float deltaT, b200_stream_t stream)
     {
-    if (n_partial_blocks == 0 || !d_partial || !d_nvt_state) return (int)cudaErrorInvalidValue;
-    k_nvt_ke_partial<<<n_partial_blocks, 256, 0, (cudaStream_t)stream>>>(d_partial, (const float4*)d_vel,
-                                                                         d_group_members, group_size);
-    k_nvt_advance<<<1, 32, 0, (cudaStream_t)stream>>>((NvtState*)d_nvt_state, d_partial, n_partial_blocks, ndof, T, tau,
-                                                      deltaT);
-    return (int)cudaGetLastError();
+    return (int)launch_nvt_advance(d_nvt_state, d_partial, n_partial_blocks, d_vel, d_group_members, group_size, ndof, T,
+                                   tau, deltaT, 0xffffffffu, (cudaStream_t)stream);
     }
 
 int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3, unsigned int ntriples,

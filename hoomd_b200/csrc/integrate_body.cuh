@@ -93,7 +93,7 @@ __device__ __forceinline__ float langevin_step_two_body(float4& v, float3s& a, f
 // ---- TwoStepNVTMTK, point particles (hoomd/md/TwoStepNVTMTK.cc:107-160,297-340,387-404) ------------------------------------
 // Thermostat state on the device: IntegratorVariables xi, eta and the loop-invariant m_exp_thermo_fac.  Layout of the
 // `float d_nvt_state[4]` of the C ABI.
-struct NvtState { float xi, eta, exp_fac, _pad; };
+struct NvtState { float xi, eta, exp_fac; unsigned int gen; }; // gen: engine's hand-off tag (ts of the last advance)
 
 __device__ __forceinline__ void nvt_step_one_body(float4& p, float4& v, float3s a, int3& img, const Box& box, float dt,
                                                   float exp_fac)

@@ -28,6 +28,7 @@ struct StepState
     unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
     unsigned int N;               // local particle count (multi-GPU: changes at every migration)
     unsigned int abort;           // multi-GPU: some rank's rebuild overflowed Nmax; every rank stops stepping (1 + buffer)
+    unsigned int nvt_error;       // NVT: 1 = kinetic energy outside the accumulator range, 2 = thermostat hand-off timed out
     };
 
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
@@ -37,6 +38,12 @@ unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot); // launc
 // Device-driven stepping: the build kernel itself raises StepState::overflow when a row exceeds Nmax (what the host's
 // checkConditions does after the fact, hoomd/md/NeighborList.cc:1389-1405) and, on a single GPU, zeroes steps_left so the
 // rest of the chunk turns into no-ops and `conditions` keeps exactly the counts of the overflowing rebuild.
+constexpr unsigned int NVT_SLOTS = 16, NVT_SLOT_STRIDE = 4; // 16 accumulators per parity, one 32 B sector each
+// ComputeThermo (KE of the group = all particles) + TwoStepNVTMTK::advanceThermostat; gen != 0xffffffff tags the state
+cudaError_t launch_nvt_advance(float* d_nvt_state, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                               const unsigned int* d_group, unsigned int group_size, unsigned int ndof, float T, float tau,
+                               float dt, unsigned int gen, cudaStream_t stream);
+
 struct OverflowHook
     {
     unsigned int* overflow = nullptr;   // set to 1 on overflow
@@ -81,9 +88,10 @@ struct FusedStepArgs
     // before step two (Integrator::computeNetForce).  NULL = the pair force is the only force.
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch;
     GhostSendArgs gs;             // multi-GPU: ghost update fused into k_md_step
-    // TwoStepNVTMTK: thermostat state {xi, eta, exp_fac, -} on the device, per-CTA partial sums of m v^2 (one slot per CTA of
-    // the widest k_md_step grid), NDOF of the group, coupling period tau; kT above is the set point
-    float* nvt_state; double* nvt_partial; unsigned int nvt_ndof; float nvt_tau;
+    // TwoStepNVTMTK: thermostat state {xi, eta, exp_fac, gen} on the device; fixed-point accumulators of sum(m v^2)
+    // (2 parities x NVT_SLOTS slots, NVT_SLOT_STRIDE words apart) and their scale (a power of two); NDOF of the group,
+    // coupling period tau; kT above is the set point
+    float* nvt_state; unsigned long long* nvt_acc; double nvt_scale; unsigned int nvt_ndof; float nvt_tau;
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);

@@ -38,7 +38,7 @@ template<class Evaluator> struct MdStepArgs
     int force_only;           // compute and store the net force only (prepRun / stand-alone force evaluation)
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch; // second ForceCompute (bonds)
     GhostSendArgs gs; int gs_buffer; // multi-GPU: fused ghost update into the peers' buffer gs_buffer (0 = A, 1 = B)
-    NvtState* nvt; double* nvt_partial; unsigned int nvt_ndof; float nvt_tau; // TwoStepNVTMTK (method 3)
+    NvtState* nvt; unsigned long long* nvt_acc; double nvt_scale; unsigned int nvt_ndof; float nvt_tau; // TwoStepNVTMTK
     };
 
 // write particle i's position into every ghost slot it feeds on the neighbor ranks (plain stores over NVLink)
@@ -69,7 +69,7 @@ constexpr int MD_BLOCK = B200_MD_BLOCK; // threads per CTA of k_md_step (B200 sw
 template<class Evaluator, bool VIRIAL>
 __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, float4 F,
                                                   const float4 pi4, float (&vir)[6], unsigned int ts2, bool last,
-                                                  bool store_force, double& mv2)
+                                                  bool store_force, double& mv2, float exp_fac = 1.0f)
     {
     bool moved = false;
     float4 v = a.vel[i];
@@ -95,9 +95,8 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         }
     const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
     const bool nve = a.method == 1, nvt = a.method == 3;
-    // one thermostat factor serves step two(ts) and step one(ts+1): advanceThermostat runs between step one and step two of
-    // the same update() (hoomd/md/TwoStepNVTMTK.cc:296), i.e. between two launches of this kernel
-    const float exp_fac = nvt ? a.nvt->exp_fac : 1.0f;
+    // exp_fac: ONE thermostat factor serves step two(ts) and step one(ts+1) -- advanceThermostat runs between step one and
+    // step two of the same update() (hoomd/md/TwoStepNVTMTK.cc:296), i.e. between two launches (md_step_nvt_begin)
     float3s acc;
     // ---- integrateStepTwo(ts) ----
     if (nve)
@@ -139,29 +138,81 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     return moved;
     }
 
+// ---- TwoStepNVTMTK inside the step kernel ---------------------------------------------------------------------------------
+// The thermostat needs sum(m v^2) of the velocities step one left behind.  Every CTA adds its share, converted to fixed
+// point (a power-of-two scale: exact conversion of the double up to its rounding to an integer), into one of NVT_SLOTS
+// 64-bit accumulators with a fire-and-forget atomic: integer addition is associative, so the total is the same bits
+// whatever the order -- deterministic without partial-sum arrays, fences or a serial tail.  The NEXT launch's first thread
+// (block 0; the kernel boundary orders it after all the adds) turns the total into xi / eta / exp_fac and publishes them with
+// the launch's timestep as tag; the other CTAs meet the tag only after their force phase, microseconds later (bounded spin).
+template<class Evaluator>
+__device__ __forceinline__ void md_step_nvt_begin(const MdStepArgs<Evaluator>& a, StepState* st, unsigned int ts2)
+    {
+    if (a.method != 3 || blockIdx.x != 0 || threadIdx.x >= 32) return; // warp 0 of block 0, one accumulator per lane
+    if (((volatile NvtState*)a.nvt)->gen == ts2) return; // the chunk prologue advanced the thermostat for this step
+    unsigned long long* acc = a.nvt_acc + (size_t)(ts2 & 1u) * NVT_SLOTS * NVT_SLOT_STRIDE;
+    unsigned long long v = 0ull;
+    if (threadIdx.x < NVT_SLOTS)
+        {
+        v = __ldcg(acc + threadIdx.x * NVT_SLOT_STRIDE);
+        acc[threadIdx.x * NVT_SLOT_STRIDE] = 0ull; // ready for the launch after the next one
+        }
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0)
+        {
+        nvt_advance_body(a.nvt, (double)(long long)v / a.nvt_scale, a.nvt_ndof, a.kT, a.nvt_tau, a.dt);
+        __threadfence();
+        ((volatile NvtState*)a.nvt)->gen = ts2;
+        }
+    (void)st;
+    }
+
+// thread 0 of every CTA, before the barrier between the force phase and the integration phase: wait for this launch's
+// thermostat factor and hand it to the CTA through shared memory
+template<class Evaluator>
+__device__ __forceinline__ void md_step_nvt_wait(const MdStepArgs<Evaluator>& a, StepState* st, unsigned int ts2,
+                                                 float* s_exp_fac)
+    {
+    if (a.method != 3 || threadIdx.x != 0) return;
+    volatile NvtState* nvt = (volatile NvtState*)a.nvt;
+    unsigned int spins = 0;
+    while (nvt->gen != ts2)
+        {
+        __nanosleep(64);
+        if (++spins > (1u << 21)) // ~0.1 s: block 0 never ran ahead of this CTA; fail loudly instead of hanging
+            {
+            st->nvt_error = 2u;
+            break;
+            }
+        }
+    __threadfence();
+    *s_exp_fac = nvt->exp_fac;
+    }
+
 // last CTA to finish takes the rebuild decision for the next launch (every thread of the CTA must call this).
-// NVT: the CTAs leave their partial sum of m v^2 behind and the last one reduces them in a fixed order and advances the
-// thermostat (ComputeThermo + TwoStepNVTMTK::advanceThermostat without leaving the kernel).
 template<class Evaluator>
 __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, StepState* st, bool moved,
-                                               unsigned int steps_left, bool last, double mv2 = 0.0)
+                                               unsigned int steps_left, bool last, double mv2 = 0.0,
+                                               unsigned int ts2 = 0)
     {
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
-    const bool nvt = a.method == 3 && !last;
-    const unsigned int nblocks = gridDim.x * gridDim.y * gridDim.z;
-    __shared__ double s_mv2[MD_BLOCK / 32];
-    __shared__ unsigned int s_is_last;
-    if (nvt)
+    if (a.method == 3 && !last)
         {
+        // this CTA's share of sum(m v^2): warp shuffles, then one fixed-point atomic per warp that integrated particles
         for (int o = 16; o > 0; o >>= 1) mv2 += __shfl_xor_sync(0xffffffffu, mv2, o);
-        if ((threadIdx.x & 31) == 0) s_mv2[threadIdx.x >> 5] = mv2;
-        __syncthreads();
-        if (threadIdx.x == 0)
+        if ((threadIdx.x & 31) == 0 && mv2 != 0.0)
             {
-            double x = 0.0;
-            for (int w = 0; w < MD_BLOCK / 32; w++) x += s_mv2[w];
-            a.nvt_partial[blockIdx.x] = x;
-            __threadfence(); // the partial must be visible before this CTA's ticket
+            const double scaled = mv2 * a.nvt_scale;
+            // 2^62 spread over every warp of the grid: no sum of admissible shares can wrap the accumulator
+            const double limit = 4611686018427387904.0 / ((double)gridDim.x * (MD_BLOCK / 32));
+            if (!(scaled < limit))
+                st->nvt_error = 1u;
+            else
+                {
+                const unsigned int slot = (blockIdx.x * (MD_BLOCK / 32) + (threadIdx.x >> 5)) % NVT_SLOTS;
+                atomicAdd(a.nvt_acc + ((size_t)((ts2 + 1u) & 1u) * NVT_SLOTS + slot) * NVT_SLOT_STRIDE,
+                          (unsigned long long)__double2ll_rn(scaled));
+                }
             }
         }
     if (threadIdx.x == 0)
@@ -169,9 +220,7 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
         // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
         const unsigned long long old = atomicAdd(&st->ticket, inc);
-        const bool is_last = (unsigned int)old == nblocks - 1;
-        if (nvt) s_is_last = is_last ? 1u : 0u;
-        if (is_last)
+        if ((unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1)
             {
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
@@ -188,26 +237,6 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
 #if (CUDART_VERSION >= 12040)
             if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
 #endif
-            if (nvt) __threadfence();
-            }
-        }
-    if (nvt)
-        {
-        __syncthreads();
-        if (s_is_last)
-            {
-            double x = 0.0;
-            for (unsigned int b = threadIdx.x; b < nblocks; b += MD_BLOCK) x += __ldcg(a.nvt_partial + b);
-            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-            __syncthreads(); // s_mv2 was read by thread 0 above
-            if ((threadIdx.x & 31) == 0) s_mv2[threadIdx.x >> 5] = x;
-            __syncthreads();
-            if (threadIdx.x == 0)
-                {
-                double t = 0.0;
-                for (int w = 0; w < MD_BLOCK / 32; w++) t += s_mv2[w];
-                nvt_advance_body(a.nvt, t, a.nvt_ndof, a.kT, a.nvt_tau, a.dt);
-                }
             }
         }
     }
@@ -233,7 +262,8 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.d_N = fa.d_N; a.mg = fa.mg;
     a.extra_force = fa.extra_force; a.extra_virial = fa.extra_virial; a.extra_virial_pitch = fa.extra_virial_pitch;
     a.gs = fa.gs; a.gs_buffer = copy_pos_on_last ? 0 : 1; // phase 0 writes B, phase 1 writes A
-    a.nvt = (NvtState*)fa.nvt_state; a.nvt_partial = fa.nvt_partial; a.nvt_ndof = fa.nvt_ndof; a.nvt_tau = fa.nvt_tau;
+    a.nvt = (NvtState*)fa.nvt_state; a.nvt_acc = fa.nvt_acc; a.nvt_scale = fa.nvt_scale; a.nvt_ndof = fa.nvt_ndof;
+    a.nvt_tau = fa.nvt_tau;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

@@ -5,10 +5,16 @@
 #include "md_step_body.cuh"
 #include <cstdlib>
 
+#include <type_traits>
+
 namespace b200
 {
+// register bound: 10 CTAs of 128 threads per SM (48 registers) for the plain variants, which fit without spilling; the
+// multi-type / virial / xplor variants and the exp/pow evaluators keep their 56-62 registers
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE>
-__global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
+__global__ void __launch_bounds__(MD_BLOCK, (MULTI_TYPE || VIRIAL || SHIFT_MODE == 2
+                                             || !std::is_same<Evaluator, EvaluatorPairLJ>::value) ? 1 : 1280 / MD_BLOCK)
+k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     {
     constexpr int PPB = MD_BLOCK / TPP; // particles per CTA
     extern __shared__ unsigned char smem_raw[];
@@ -21,6 +27,8 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
     const unsigned int N = a.d_N ? *a.d_N : a.N;
+    __shared__ float s_exp_fac;
+    md_step_nvt_begin(a, st, ts2); // NVT: thread 0 of block 0 advances the thermostat for this launch (no-op otherwise)
 
     // ---- phase 1: TPP lanes per particle walk its neighbor list (PotentialPair::computeForces) ----
     PairTables<Evaluator> T;
@@ -50,6 +58,7 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
                 }
             }
         }
+    md_step_nvt_wait(a, st, ts2, &s_exp_fac);
     __syncthreads();
 
     // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
@@ -65,9 +74,9 @@ __global__ void __launch_bounds__(MD_BLOCK) k_md_step(const __grid_constant__ Md
             for (int c = 0; c < 6; c++) vir[c] = s_virial[c * PPB + threadIdx.x];
             }
         moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force,
-                                                     mv2);
+                                                     mv2, a.method == 3 ? s_exp_fac : 1.0f);
         }
-    md_step_finish(a, st, moved, steps_left, last, mv2);
+    md_step_finish(a, st, moved, steps_left, last, mv2, ts2);
     }
 
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>

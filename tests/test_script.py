@@ -190,3 +190,62 @@ def test_kremer_grest_script_matches_reference():
     assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
     assert snap.bonds.N == len(bonds)
     assert abs(ns["fene"].get_energy() - 20.0 * len(bonds)) < 5.0 * len(bonds)
+
+
+NVT_SCRIPT = """
+import hoomd
+from hoomd import md
+hoomd.context.initialize()
+hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=1.6, type_name='A'), n=9)
+nl = md.nlist.cell()
+lj = md.pair.lj(r_cut=2.5, nlist=nl)
+lj.pair_coeff.set('A', 'A', epsilon=1.0, sigma=1.0)
+md.integrate.mode_standard(dt=0.005)
+nvt = md.integrate.nvt(group=hoomd.group.all(), kT=1.0, tau=0.5)
+hoomd.run(NSTEPS)
+"""
+
+
+def test_nvt_surface_without_gpu():
+    hoomd = _fresh()
+    from hoomd import md
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    m = md.integrate.nvt(group=hoomd.group.all(), kT=1.2, tau=0.5)
+    m.set_params(kT=1.5)
+    m.set_params(tau=1.0)
+    assert (m.kT, m.tau) == (1.5, 1.0)
+    with pytest.raises(TypeError):
+        md.integrate.nvt(group=hoomd.group.all(), kT=1.0)  # tau is required (hoomd/md/integrate.py:201)
+
+
+@pytest.mark.gpu
+def test_nvt_script_matches_reference():
+    """md.integrate.nvt from a job script: 80 steps against TwoStepNVTMTK on the reference's CPU classes; a second
+    hoomd.run continues with the thermostat state, also across an engine re-configuration (set_params)"""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    hoomd = _fresh()
+    ns = {}
+    exec(NVT_SCRIPT.replace("NSTEPS", "80"), ns)
+    snap = hoomd.context.current.system.take_snapshot()
+    from hoomd_b200 import workloads
+    pos, vel, L = workloads.sc_lattice(9, 1.6)
+    r = R.RefSystem(pos, (L, L, L), vel4=vel)
+    r.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+    r.setup_integrator(0.005)
+    r.add_nvt(1.0, 0.5)
+    r.set_sorter(300)
+    r.run(80)
+    a = r.particles()
+    order = np.argsort(a["tag"])
+    assert np.abs(a["pos"][order][:, :3] - snap.particles.position).max() < 2e-4
+    assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
+    eng = hoomd.context.current.engine
+    assert np.allclose(eng.nvt_state(), r.nvt_state(), rtol=2e-5, atol=1e-7)
+    # continue; the re-configured engine must pick the thermostat variables up again
+    ns["nvt"].set_params(tau=0.5)
+    hoomd.run(20)
+    r.run(20)
+    eng = hoomd.context.current.engine
+    assert np.allclose(eng.nvt_state(), r.nvt_state(), rtol=1e-4, atol=1e-6), (eng.nvt_state(), r.nvt_state())
