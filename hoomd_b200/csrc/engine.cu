@@ -122,6 +122,7 @@ struct b200_system
     std::vector<float> h_r_cut, h_r_listsq, h_rcut_max;
     float rcut_max_max = 0.0f;
     DevBuf<float> d_r_cut, d_r_listsq, d_rcut_max, d_maxsq;
+    float last_L[3] = {0.0f, 0.0f, 0.0f}; // NeighborList::m_last_L: box lengths at the last build (distance-check lambda)
     std::vector<unsigned int> h_Nmax;
     DevBuf<unsigned int> d_Nmax, nl_conditions, head_list, n_neigh, nlist, d_req_size;
     DevBuf<float4> last_pos;
@@ -546,9 +547,11 @@ static bool nlist_check_conditions(b200_system* s)
 static bool nlist_distance_check(b200_system* s, unsigned int ts)
     {
     CUDA_OK(cudaMemsetAsync(s->d_flag.p, 0, sizeof(unsigned int), s->stream));
-    const float lambda[3] = {1.0f, 1.0f, 1.0f};
+    // direction of maximum box contraction since the last build (hoomd/md/NeighborList.cc:981-986); 1 for a fixed box
+    const float lambda[3] = {s->box.L[0] / s->last_L[0], s->box.L[1] / s->last_L[1], s->box.L[2] / s->last_L[2]};
+    const float lambda_min = std::min(std::min(lambda[0], lambda[1]), lambda[2]);
     CUDA_OK(b200_nlist_needs_update_check(s->d_flag.p, (const float*)s->last_pos.p, (const float*)s->pos.p, s->N,
-                                          &s->box, s->d_rcut_max.p, s->r_buff, s->ntypes, 1.0f, lambda, ts + 1,
+                                          &s->box, s->d_rcut_max.p, s->r_buff, s->ntypes, lambda_min, lambda, ts + 1,
                                           s->stream));
     s->kernels_last_run += 1;
     CUDA_OK(cudaMemcpyAsync(s->h_flag, s->d_flag.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s->stream));
@@ -646,6 +649,7 @@ static void nlist_compute(b200_system* s, unsigned int ts)
             s->kernels_last_run += 1;
             }
         // setLastUpdatedPos: done by the build kernel (like the reference GPU path, NeighborListGPUBinned.cu:280-285)
+        for (int d = 0; d < 3; d++) s->last_L[d] = s->box.L[d]; // m_last_L (NeighborList.cc:1062)
         }
     }
 
@@ -959,6 +963,11 @@ static void ensure_graph(b200_system* s)
     build_graph_plain(s);
     }
 
+static bool box_scaled_since_build(const b200_system* s)
+    {
+    return s->have_nlist && (s->box.L[0] != s->last_L[0] || s->box.L[1] != s->last_L[1] || s->box.L[2] != s->last_L[2]);
+    }
+
 static void host_step(b200_system* s)
     {
     integrate_step_one(s, s->timestep);
@@ -1090,6 +1099,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         }
     check_bond_flags(s);
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
+    if (rebuilds)
+        for (int d = 0; d < 3; d++) s->last_L[d] = s->box.L[d]; // setLastUpdatedPos of the device-side builds
     const unsigned long long cl_extra = cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->N) - 4u;
     const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
@@ -1398,6 +1409,7 @@ int b200_sys_setup_pair(b200_system* s, int evaluator, float r_buff, unsigned in
     s->force_update = true;
     s->cl_force = true;
     s->nl_first_compute = true;
+    for (int d = 0; d < 3; d++) s->last_L[d] = s->box.L[d]; // NeighborList ctor (NeighborList.cc:58)
     invalidate_graph(s);
     tile_configure(s);
     SYS_CATCH(s)
@@ -1611,6 +1623,53 @@ int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const flo
     SYS_CATCH(s)
     }
 
+// hoomd.update.box_resize: BoxResizeUpdater::update (hoomd/BoxResizeUpdater.cc:60-136) for one target box.  The
+// reference's `no_change` test divides the (zero) tilt difference by the zero tilt: NaN < 1e-7 is false, so an orthorhombic
+// box is ALWAYS re-set, even to the same lengths -- reproduced here (the cell list is forced, positions are re-scaled).
+int b200_sys_set_box(b200_system* s, float Lx, float Ly, float Lz, int scale_particles)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("update.box_resize: not available under domain decomposition yet");
+    if (s->tile_on) throw std::runtime_error("update.box_resize: not available on the cell-tile path");
+    if (!(Lx > 0.0f && Ly > 0.0f && Lz > 0.0f)) throw std::runtime_error("update.box_resize: box lengths must be positive");
+    // updaters run in the order they were added: the sorter (created with the system) before box_resize
+    if (s->sorter_period && s->timestep == s->sorter_next)
+        {
+        sorter_update(s);
+        s->sorter_next += s->sorter_period;
+        }
+    b200_box nb;
+    b200_box_init(&nb, Lx, Ly, Lz);
+    for (int d = 0; d < 3; d++) nb.periodic[d] = s->box.periodic[d];
+    CUDA_OK(b200_box_resize_particles((float*)s->pos.p, (int*)s->image.p, s->N, &s->box, &nb, scale_particles, s->stream));
+    s->kernels_last_run += 1;
+    s->box = nb;
+    s->global_box = nb;
+    if (s->have_nlist)
+        {
+        // CellList::compute on m_box_changed (CellList.cc:151-171): same bin counts => only the width changes
+        b200_dim3 nd;
+        b200_cell_list_dimensions(&s->box, s->nominal_width, 1, 0.0f, &nd, s->ghost_width);
+        if (nd.x != s->dim.x || nd.y != s->dim.y || nd.z != s->dim.z)
+            {
+            CUDA_OK(cudaStreamSynchronize(s->stream));
+            s->dim = nd;
+            const size_t ncells = (size_t)nd.x * nd.y * nd.z;
+            s->cell_count.alloc(ncells);
+            s->cell_start.alloc(ncells + 1);
+            }
+        s->cl_force = true;
+        }
+    invalidate_graph(s); // the box is a by-value argument of the captured kernels
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    SYS_CATCH(s)
+    }
+
+void b200_sys_get_box(b200_system* s, float* L3)
+    {
+    for (int d = 0; d < 3; d++) L3[d] = s->box.L[d];
+    }
+
 int b200_sys_add_nvt(b200_system* s, float kT, float tau)
     {
     SYS_TRY(s)
@@ -1772,6 +1831,13 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
         if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
         if (s->mg)
             mg_run_chunk(s, chunk);
+        else if (s->use_graph && box_scaled_since_build(s))
+            {
+            // the box changed since the last neighbor-list build: the distance check needs lambda = L / L_last
+            // (NeighborList.cc:981-1007).  Step with the host protocol until the next build makes lambda 1 again.
+            host_step(s);
+            chunk = 1;
+            }
         else if (s->use_graph)
             run_chunk_device(s, chunk);
         else

@@ -275,6 +275,33 @@ cudaError_t launch_nvt_advance(float* d_nvt_state, double* d_partial, unsigned i
     }
 } // namespace b200
 
+// ---- BoxResizeUpdater::update, particle part (hoomd/BoxResizeUpdater.cc:98-131) --------------------------------------------
+namespace b200
+{
+__global__ void __launch_bounds__(256) k_box_resize(float4* __restrict__ pos, int3* __restrict__ image, unsigned int N,
+                                                    Box old_box, Box new_box, int scale_particles)
+    {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    float4 p = pos[i];
+    if (scale_particles)
+        {
+        // fractional coordinates in the old box, Cartesian coordinates in the new one (BoxDim.h:238-245,257-263)
+        const float3 f = make_fraction_exact(make_float3(p.x, p.y, p.z), old_box, make_float3(0.0f, 0.0f, 0.0f));
+        p.x = __fadd_rn(new_box.lo.x, __fmul_rn(f.x, new_box.L.x));
+        p.y = __fadd_rn(new_box.lo.y, __fmul_rn(f.y, new_box.L.y));
+        p.z = __fadd_rn(new_box.lo.z, __fmul_rn(f.z, new_box.L.z));
+        }
+    else
+        {
+        int3 img = image[i];
+        box_wrap(p.x, p.y, p.z, img, new_box);
+        image[i] = img;
+        }
+    pos[i] = p;
+    }
+} // namespace b200
+
 using namespace b200;
 
 extern "C" {
@@ -372,6 +399,16 @@ int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigned int n_p
     {
     return (int)launch_nvt_advance(d_nvt_state, d_partial, n_partial_blocks, d_vel, d_group_members, group_size, ndof, T,
                                    tau, deltaT, 0xffffffffu, (cudaStream_t)stream);
+    }
+
+int b200_box_resize_particles(float* d_pos, int* d_image, unsigned int N, const b200_box* old_box, const b200_box* new_box,
+                              int scale_particles, b200_stream_t stream)
+    {
+    if (N == 0) return 0;
+    if (!box_is_orthorhombic(*old_box) || !box_is_orthorhombic(*new_box)) return (int)cudaErrorNotSupported;
+    k_box_resize<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)d_pos, (int3*)d_image, N, make_box(*old_box),
+                                                                     make_box(*new_box), scale_particles);
+    return (int)cudaGetLastError();
     }
 
 int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3, unsigned int ntriples,

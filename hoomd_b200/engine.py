@@ -146,6 +146,16 @@ class System:
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(_lib.lib().b200_sys_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _p(g), int(noiseless_t)))
 
+    def set_box(self, Lx, Ly, Lz, scale_particles=True):
+        """hoomd.update.box_resize at a period boundary: one BoxResizeUpdater::update towards the box (Lx, Ly, Lz)"""
+        self._check(_lib.lib().b200_sys_set_box(self.h, C.c_float(Lx), C.c_float(Ly), C.c_float(Lz), int(scale_particles)))
+        self.box = _lib.make_box(float(Lx), float(Ly), float(Lz))
+
+    def box_lengths(self):
+        out = np.zeros(3, np.float32)
+        _lib.lib().b200_sys_get_box(self.h, _p(out))
+        return out
+
     def add_nvt(self, kT, tau):
         """md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK (hoomd/md/integrate.py:163-260)"""
         self._check(_lib.lib().b200_sys_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))

@@ -41,6 +41,7 @@ class _Context:
         self.integration_methods = []
         self.sorter = update.sort() if "update" in globals() else None
         self.loggers = []
+        self.box_resizers = []
         self.engine = None
         self.engine_dirty = True
         self.timestep = 0
@@ -300,6 +301,130 @@ class _Sort:
 
 
 update.sort = _Sort
+
+# ---- hoomd.variant (hoomd/variant.py, hoomd/Variant.cc) --------------------------------------------------------------------
+variant = types.ModuleType("hoomd.variant")
+
+
+class _VariantConst:
+    def __init__(self, value):
+        self.value = float(value)
+
+    def getValue(self, timestep):
+        return self.value
+
+
+class _LinearInterp:
+    """hoomd.variant.linear_interp: piecewise linear in the time step, constant outside the points (Variant.cc:38-91)"""
+
+    def __init__(self, points, zero="now"):
+        _require_context()
+        if len(points) == 0:
+            raise RuntimeError("Error creating variant: cannot create a linear_interp variant with 0 points")
+        now = context.current.timestep
+        if zero == "now":
+            self.offset = now
+        else:
+            if zero < 0:
+                raise RuntimeError("Error creating variant: cannot create a linear_interp variant with a negative zero")
+            if zero > now:
+                raise RuntimeError("Error creating variant: cannot create a linear_interp variant with a zero in the future")
+            self.offset = int(zero)
+        self.points = {}
+        for t, v in points:
+            if t < 0:
+                raise RuntimeError("Error creating variant: negative timestep in a variant is not allowed")
+            self.points[int(t)] = float(v)
+        self.keys = sorted(self.points)
+
+    def getValue(self, timestep):
+        t = 0 if timestep < self.offset else timestep - self.offset
+        k = self.keys
+        if len(k) == 1 or t < k[0]:
+            return self.points[k[0]]
+        if t >= k[-1]:
+            return self.points[k[-1]]
+        import bisect
+        b = bisect.bisect_right(k, t)
+        ta, tb = k[b - 1], k[b]
+        f = float(t - ta) / float(tb - ta)
+        return (1.0 - f) * self.points[ta] + f * self.points[tb]
+
+
+def _setup_variant_input(v):
+    return v if hasattr(v, "getValue") else _VariantConst(v)
+
+
+variant.linear_interp = _LinearInterp
+variant._setup_variant_input = _setup_variant_input
+
+
+class _BoxResize:
+    """hoomd.update.box_resize (hoomd/update.py:281-390, hoomd/BoxResizeUpdater.cc): every `period` steps the box is set to
+    the variants' values and the particles are scaled with it (or wrapped into it).  Orthorhombic boxes only."""
+
+    def __init__(self, Lx=None, Ly=None, Lz=None, xy=None, xz=None, yz=None, period=1, L=None, phase=0,
+                 scale_particles=True):
+        _require_context()
+        ctx = context.current
+        if ctx.system is None:
+            raise RuntimeError("Cannot create box_resize before initialization")
+        if L is not None:
+            Lx = Ly = Lz = L
+        if Lx is None and Ly is None and Lz is None and xy is None and xz is None and yz is None:
+            raise RuntimeError("update.box_resize: one of Lx, Ly, Lz, xy, xz, yz must be set")
+        for t in (xy, xz, yz):
+            if t is not None and (hasattr(t, "getValue") or float(t) != 0.0):
+                raise RuntimeError("hoomd_b200: triclinic boxes are out of scope (tilt factors must stay 0)")
+        box = ctx.system.box
+        self.Lx = _setup_variant_input(box.Lx if Lx is None else Lx)
+        self.Ly = _setup_variant_input(box.Ly if Ly is None else Ly)
+        self.Lz = _setup_variant_input(box.Lz if Lz is None else Lz)
+        self.scale_particles = bool(scale_particles)
+        self.enabled = True
+        self.period = None if period is None else int(period)
+        self.phase = int(phase)
+        self.created = ctx.timestep
+        if period is None:
+            self._apply(ctx.timestep)  # applied immediately, no periodic updates (hoomd/update.py:386-387)
+        else:
+            if self.period < 1:
+                raise RuntimeError("update.box_resize: period must be a positive integer")
+            ctx.box_resizers.append(self)
+
+    def _due(self, ts):
+        if not self.enabled or self.period is None:
+            return False
+        if self.phase < 0:
+            return (ts - self.created) % self.period == 0
+        return (ts + self.phase) % self.period == 0
+
+    def _next(self, ts):
+        """steps until this updater is due again, counted from ts (0 < n <= period)"""
+        for n in range(1, self.period + 1):
+            if self._due(ts + n):
+                return n
+        return self.period
+
+    def _apply(self, ts):
+        ctx = context.current
+        L3 = [np.float32(v.getValue(ts)) for v in (self.Lx, self.Ly, self.Lz)]  # Scalar Lx = m_Lx->getValue(timestep)
+        if ctx.engine is None or ctx.engine_dirty:
+            _configure_engine()
+        ctx.engine.set_box(L3[0], L3[1], L3[2], self.scale_particles)
+        ctx.system.box = _BoxDim(float(L3[0]), float(L3[1]), float(L3[2]))
+
+    def disable(self):
+        self.enabled = False
+
+    def enable(self):
+        self.enabled = True
+
+    def set_period(self, period):
+        self.period = int(period)
+
+
+update.box_resize = _BoxResize
 
 # ---- hoomd.md -------------------------------------------------------------------------------------------------------------
 md = types.ModuleType("hoomd.md")
@@ -737,11 +862,19 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
         nxt = tsteps - done
         for p in periods:
             nxt = min(nxt, p - ts % p)
+        for br in ctx.box_resizers:
+            if br.enabled:
+                nxt = min(nxt, br._next(ts))
+        # System::run order within a step: analyzers, updaters, integrator (hoomd/System.cc:484-599)
         for lg in ctx.loggers:
             if ts % lg.period == 0:
                 lg.rows.append([ts] + [lg.query(q) for q in lg.quantities])
         if callback and callback_period and ts % callback_period == 0:
             callback(ts)
+        for br in ctx.box_resizers:
+            if br._due(ts):
+                br._apply(ts)
+                eng = ctx.engine
         eng.run(nxt)
         done += nxt
     ctx.timestep = eng.timestep
@@ -759,7 +892,7 @@ def install():
     me = sys.modules[__name__]
     sys.modules["hoomd"] = me
     for name, mod in (("context", context), ("init", init), ("lattice", lattice), ("data", data), ("group", group),
-                      ("update", update), ("md", md), ("analyze", analyze)):
+                      ("update", update), ("variant", variant), ("md", md), ("analyze", analyze)):
         sys.modules["hoomd." + name] = mod
     for name, mod in (("nlist", md.nlist), ("pair", md.pair), ("integrate", md.integrate), ("bond", md.bond)):
         sys.modules["hoomd.md." + name] = mod

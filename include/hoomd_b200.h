@@ -329,6 +329,15 @@ B200_API int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigne
                                   const unsigned int* d_group_members, unsigned int group_size, unsigned int ndof,
                                   float T, float tau, float deltaT, b200_stream_t stream);
 
+/* -----------------------------------------------------------------------------------------------------------------------
+ * BoxResizeUpdater::update, particle part (hoomd/BoxResizeUpdater.cc:98-131; the reference does this on the host):
+ * scale_particles != 0: pos = new_box.makeCoordinates(old_box.makeFraction(pos)); else wrap pos into new_box and update
+ * the image flags.  The caller sets the new global box afterwards (ParticleData::setGlobalBox) -- the cell list then
+ * re-dimensions itself (CellList.cc:151-171) and the neighbor list's distance check sees lambda = L_new / L_last_build
+ * (b200_nlist_needs_update_check's lambda arguments, NeighborList.cc:981-1007). */
+B200_API int b200_box_resize_particles(float* d_pos, int* d_image, unsigned int N, const b200_box* old_box,
+                                       const b200_box* new_box, int scale_particles, b200_stream_t stream);
+
 /* n draws of Saru(seed1,seed2,seed3).u32() and .s<float>(-1,1) per triple, evaluated on the device
  * (hoomd/Saru.h:324-340,417-441,603-640) -- used by the RNG parity tests. */
 B200_API int b200_saru_draw(unsigned int* d_u32_out, float* d_f_out, const unsigned int* d_seeds3,
@@ -417,6 +426,11 @@ B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, 
 B200_API int b200_sys_add_nvt(b200_system* s, float kT, float tau);
 B200_API int b200_sys_get_nvt_state(b200_system* s, float* xi_eta);
 B200_API int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta);
+/* hoomd.update.box_resize at a period boundary: one BoxResizeUpdater::update towards the orthorhombic box (Lx, Ly, Lz).
+ * Steps run host-driven until the next neighbor-list build (the reference's lambda-scaled distance check decides it), then
+ * device-driven again in the new box. */
+B200_API int b200_sys_set_box(b200_system* s, float Lx, float Ly, float Lz, int scale_particles);
+B200_API void b200_sys_get_box(b200_system* s, float* L3);
 /* hoomd.update.sort period (0 = disabled) */
 B200_API int b200_sys_set_sorter(b200_system* s, unsigned int period);
 B200_API int b200_sys_sort_now(b200_system* s);

@@ -39,6 +39,7 @@ struct orc_system
     f4* xyzf;
     unsigned int* cell_adj; unsigned int n_adj;
     int cl_first, cl_force; unsigned int cl_last;
+    int cl_box_changed; f3 last_L; /* CellList::m_box_changed; NeighborList::m_last_L (nearest plane distances at the last build) */
     /* NeighborList */
     int have_nlist;
     float r_buff, rcut_max_max;
@@ -270,6 +271,14 @@ static long cl_compute_once(orc_system* s)
 
 static int cl_compute(orc_system* s, unsigned int ts) /* CellList::compute, CellList.cc:133-199 */
     {
+    if (s->cl_box_changed) /* CellList.cc:151-171: same bin counts => only the width changes, else re-initialise */
+        {
+        const unsigned int od[3] = {s->dim[0], s->dim[1], s->dim[2]};
+        cl_dimensions(s, s->rcut_max_max + s->r_buff);
+        if ((od[0] != s->dim[0] || od[1] != s->dim[1] || od[2] != s->dim[2]) && s->cell_size) cl_init_memory(s);
+        s->cl_box_changed = 0;
+        s->cl_force = 1;
+        }
     int should = s->cl_first || s->cl_force || s->cl_last != ts;
     if (!should) return 0;
     s->cl_first = 0; s->cl_force = 0; s->cl_last = ts;
@@ -323,16 +332,19 @@ static void nl_build_head_list(orc_system* s) /* NeighborList.cc:1336-1380 */
         }
     }
 
-static int nl_distance_check(orc_system* s) /* NeighborList.cc:964-1040, fixed box: lambda = 1 */
+static int nl_distance_check(orc_system* s) /* NeighborList.cc:964-1040; lambda = L_now / L_at_last_build per axis */
     {
+    const f3 lambda = {s->box.L.x / s->last_L.x, s->box.L.y / s->last_L.y, s->box.L.z / s->last_L.z};
+    float lambda_min = (lambda.x < lambda.y) ? lambda.x : lambda.y;
+    lambda_min = (lambda_min < lambda.z) ? lambda_min : lambda.z;
     for (unsigned int i = 0; i < s->N; i++)
         {
         const float old_rmin = s->rcut_max[as_uint(s->pos[i].w)];
         const float rmax = old_rmin + s->r_buff;
-        const float delta_max = (rmax * 1.0f - old_rmin) / 2.0f;
+        const float delta_max = (rmax * lambda_min - old_rmin) / 2.0f;
         const float maxsq = (delta_max > 0) ? delta_max * delta_max : 0;
-        f3 dx = {s->pos[i].x - 1.0f * s->last_pos[i].x, s->pos[i].y - 1.0f * s->last_pos[i].y,
-                 s->pos[i].z - 1.0f * s->last_pos[i].z};
+        f3 dx = {s->pos[i].x - lambda.x * s->last_pos[i].x, s->pos[i].y - lambda.y * s->last_pos[i].y,
+                 s->pos[i].z - lambda.z * s->last_pos[i].z};
         dx = box_min_image(&s->box, dx);
         if (dot3(dx) >= maxsq) return 1;
         }
@@ -472,6 +484,7 @@ static int nl_compute(orc_system* s, unsigned int ts) /* NeighborList::compute, 
             f4 lp = {s->pos[i].x, s->pos[i].y, s->pos[i].z, 0.0f};
             s->last_pos[i] = lp;
             }
+        s->last_L = s->box.L; /* NeighborList.cc:1062 (orthorhombic: nearest plane distance = L) */
         }
     return 0;
     }
@@ -1050,6 +1063,7 @@ int orc_setup_lj(orc_system* s, float r_buff, unsigned int check_period, const f
     s->head = (unsigned int*)calloc(s->N, 4); s->n_neigh = (unsigned int*)calloc(s->N, 4);
     s->nlist_alloc = 8 * (size_t)s->N; s->nlist = (unsigned int*)calloc(s->nlist_alloc ? s->nlist_alloc : 1, 4);
     cl_dimensions(s, s->rcut_max_max + s->r_buff);          /* NeighborListBinned.cc:56-76 */
+    s->last_L = s->box.L;                                   /* NeighborList.cc:58 */
     s->have_nlist = 1; s->force_update = 1; s->cl_force = 1; s->nl_first = 1;
     s->pair_kind = 0;
     return 0;
@@ -1099,6 +1113,32 @@ int orc_add_nvt(orc_system* s, float kT, float tau) /* TwoStepNVTMTK ctor + init
     return 0;
     }
 void orc_get_nvt_state(orc_system* s, float* xi_eta) { xi_eta[0] = s->nvt_xi; xi_eta[1] = s->nvt_eta; }
+/* BoxResizeUpdater::update for one target box (hoomd/BoxResizeUpdater.cc:60-136), orthorhombic */
+int orc_set_box(orc_system* s, float Lx, float Ly, float Lz, int scale_particles)
+    {
+    const box_t cur = s->box;
+    /* the tilt terms of no_change are 0/0 = NaN in the reference => `no_change` is false for every orthorhombic box */
+    box_t nb = cur;
+    nb.L.x = Lx; nb.L.y = Ly; nb.L.z = Lz;               /* BoxDim::setL, BoxDim.h:165-171 */
+    nb.hi.x = Lx / 2.0f; nb.hi.y = Ly / 2.0f; nb.hi.z = Lz / 2.0f;
+    nb.lo.x = -nb.hi.x; nb.lo.y = -nb.hi.y; nb.lo.z = -nb.hi.z;
+    nb.Linv.x = 1.0f / Lx; nb.Linv.y = 1.0f / Ly; nb.Linv.z = 1.0f / Lz;
+    s->box = nb;
+    s->cl_box_changed = 1;
+    if (scale_particles)
+        for (unsigned int i = 0; i < s->N; i++)
+            {
+            f3 p = {s->pos[i].x, s->pos[i].y, s->pos[i].z};
+            f3 f = box_make_fraction(&cur, p);
+            s->pos[i].x = nb.lo.x + f.x * nb.L.x;          /* BoxDim::makeCoordinates, BoxDim.h:257-263 */
+            s->pos[i].y = nb.lo.y + f.y * nb.L.y;
+            s->pos[i].z = nb.lo.z + f.z * nb.L.z;
+            }
+    else
+        for (unsigned int i = 0; i < s->N; i++) box_wrap(&s->box, &s->pos[i], &s->image[i]);
+    return 0;
+    }
+void orc_get_box(orc_system* s, float* L3) { L3[0] = s->box.L.x; L3[1] = s->box.L.y; L3[2] = s->box.L.z; }
 void orc_set_timestep(orc_system* s, unsigned int ts) { s->timestep = ts; }
 unsigned int orc_get_timestep(orc_system* s) { return s->timestep; }
 int orc_compute_nlist(orc_system* s, unsigned int ts) { return nl_compute(s, ts); }

@@ -39,6 +39,8 @@ def lib():
         L.orc_add_nve.argtypes = [vp, C.c_int, C.c_float, C.c_int]
         L.orc_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
         L.orc_add_nvt.argtypes = [vp, C.c_float, C.c_float]
+        L.orc_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
+        L.orc_get_box.argtypes = [vp, vp]
         L.orc_get_nvt_state.argtypes = [vp, vp]
         L.orc_set_timestep.argtypes = [vp, C.c_uint]
         L.orc_get_timestep.argtypes = [vp]
@@ -165,6 +167,15 @@ class OracleSystem:
     def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         lib().orc_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), int(noiseless_t))
+
+    def set_box(self, Lx, Ly, Lz, scale_particles=True):
+        """one BoxResizeUpdater::update towards the orthorhombic box (Lx, Ly, Lz)"""
+        lib().orc_set_box(self.h, C.c_float(Lx), C.c_float(Ly), C.c_float(Lz), int(scale_particles))
+
+    def box_lengths(self):
+        out = np.zeros(3, np.float32)
+        lib().orc_get_box(self.h, _ptr(out))
+        return out
 
     def add_nvt(self, kT, tau):
         lib().orc_add_nvt(self.h, C.c_float(kT), C.c_float(tau))

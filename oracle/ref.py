@@ -37,6 +37,8 @@ def lib():
         _lib.ref_setup_pair.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_int]
         _lib.ref_add_nvt.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
+        _lib.ref_get_box.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_get_nvt_state.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
@@ -160,6 +162,15 @@ class RefSystem:
     def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(lib().ref_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), int(noiseless_t)))
+
+    def set_box(self, Lx, Ly, Lz, scale_particles=True):
+        """one BoxResizeUpdater::update towards the orthorhombic box (Lx, Ly, Lz)"""
+        self._check(lib().ref_set_box(self.h, C.c_float(Lx), C.c_float(Ly), C.c_float(Lz), int(scale_particles)))
+
+    def box_lengths(self):
+        out = np.zeros(3, np.float32)
+        lib().ref_get_box(self.h, _ptr(out))
+        return out
 
     def add_nvt(self, kT, tau):
         self._check(lib().ref_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))

@@ -19,6 +19,7 @@
 #include "hoomd/SFCPackUpdater.h"
 #include "hoomd/ComputeThermo.h"
 #include "hoomd/md/TwoStepNVTMTK.h"
+#include "hoomd/BoxResizeUpdater.h"
 #include "hoomd/Saru.h"
 #include "hoomd/md/NeighborListBinned.h"
 #include "hoomd/md/AllPairPotentials.h"
@@ -378,6 +379,36 @@ int ref_get_nvt_state(void* h, float* xi_eta)
         }
     REF_CATCH(s, 1)
     return 0;
+    }
+
+//! One BoxResizeUpdater::update (hoomd/BoxResizeUpdater.cc:60-136) towards the box (Lx, Ly, Lz), tilts unchanged: what
+//! hoomd.update.box_resize does at a period boundary (the variants evaluated by the caller)
+int ref_set_box(void* h, float Lx, float Ly, float Lz, int scale_particles)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    // updaters run in the order they were added (System::run): the sorter comes first
+    if (s->sorter && s->sorter_period && s->timestep == s->sorter_next)
+        {
+        s->sorter->update(s->timestep);
+        s->sorter_next += s->sorter_period;
+        }
+    BoxDim cur = s->pdata->getGlobalBox();
+    std::shared_ptr<Variant> vx(new VariantConst(Lx)), vy(new VariantConst(Ly)), vz(new VariantConst(Lz));
+    std::shared_ptr<Variant> xy(new VariantConst(cur.getTiltFactorXY())), xz(new VariantConst(cur.getTiltFactorXZ())),
+        yz(new VariantConst(cur.getTiltFactorYZ()));
+    BoxResizeUpdater up(s->sysdef, vx, vy, vz, xy, xz, yz);
+    up.setParams(scale_particles != 0);
+    up.update(s->timestep);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+void ref_get_box(void* h, float* L3)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    Scalar3 L = s->pdata->getGlobalBox().getL();
+    L3[0] = L.x; L3[1] = L.y; L3[2] = L.z;
     }
 
 //! hoomd.update.sort (period 0 disables); the first sort happens at the first step run, like System::run

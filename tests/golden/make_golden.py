@@ -120,7 +120,47 @@ def nvt():
     np.savez_compressed(os.path.join(HERE, "nvt.npz"), **res)
 
 
+BOX_RESIZE_CASES = {  # name: (scale_particles, per-segment factor, segments, steps per segment)
+    "compress": (True, 0.996, 40, 5),
+    "expand_wrap": (False, 1.004, 30, 5),
+}
+
+
+def box_resize_schedule(L, factor, segments):
+    """the box lengths of segment k (FP32, slightly anisotropic so that the three lambdas differ)"""
+    out, Lc = [], np.float64(L)
+    for _ in range(segments):
+        Lc = Lc * factor
+        out.append((np.float32(Lc), np.float32(Lc * 1.001), np.float32(Lc * 0.999)))
+    return out
+
+
+def box_resize():
+    """(11) hoomd.update.box_resize: BoxResizeUpdater between run segments -- particle scaling / wrapping, the lambda-scaled
+    distance check (NeighborList.cc:981-1007) and the cell list re-dimensioning (4 -> 3 cells per axis on the way down)"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.3) ** (1.0 / 3.0), kT=1.2, seed=7)
+    res = dict(pos0=pos, vel0=vel, L=L)
+    for name, (scale, factor, segments, nsteps) in BOX_RESIZE_CASES.items():
+        q = ref.RefSystem(pos, (L, L, L), vel4=vel)
+        q.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+        q.setup_integrator(0.005)
+        q.add_langevin(1.0, 3)
+        for (lx, ly, lz) in box_resize_schedule(L, factor, segments):
+            q.set_box(lx, ly, lz, scale)
+            q.run(nsteps)
+        p = q.particles()
+        order = np.argsort(p["tag"])
+        for k in ("pos", "vel", "accel", "image"):
+            res[name + "_" + k] = p[k][order]
+        res[name + "_box"] = q.box_lengths()
+        res[name + "_updates"] = q.nlist_stats()["updates"]
+    np.savez_compressed(os.path.join(HERE, "box_resize.npz"), **res)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "box":
+        box_resize()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "nvt":
         nvt()
         return
@@ -133,6 +173,7 @@ def main():
     kremer_grest()
     pair_evaluators()
     nvt()
+    box_resize()
     out = {}
     # (1) Saru stream: (tag, timestep, seed) triples
     rng = np.random.default_rng(0)

@@ -263,3 +263,43 @@ def check_nvt(make, bit_exact, pos_tol=2e-4, vel_tol=2e-3, state_rtol=2e-5, long
             th = s.thermo()
             for name, w in zip(("ke", "pe", "T", "ndof"), g[k + "thermo"][[0, 1, 2, 4]]):
                 assert abs(th[name] - w) <= (1e-6 if bit_exact else 5e-4) * abs(w), (k, name, th[name], w)
+
+
+BOX_RESIZE_CASES = {"compress": (True, 0.996, 40, 5), "expand_wrap": (False, 1.004, 30, 5)}
+
+
+def box_resize_schedule(L, factor, segments):
+    out, Lc = [], np.float64(L)
+    for _ in range(segments):
+        Lc = Lc * factor
+        out.append((np.float32(Lc), np.float32(Lc * 1.001), np.float32(Lc * 0.999)))
+    return out
+
+
+def check_box_resize(make, bit_exact, pos_tol=3e-4, vel_tol=3e-3, updates=None):
+    """hoomd.update.box_resize between run segments against the reference's BoxResizeUpdater + lambda-scaled distance check
+    + cell-list re-dimensioning (tests/golden/box_resize.npz).  `updates(s)`: the system's neighbor-list build count."""
+    g = load("box_resize")
+    L = float(g["L"])
+    for name, (scale, factor, segments, nsteps) in BOX_RESIZE_CASES.items():
+        s = make(g["pos0"], (L, L, L), 1, vel=g["vel0"])
+        s.setup_lj(r_cut=2.5, r_buff=0.4)
+        s.setup_integrator(0.005)
+        s.add_langevin(1.0, 3)
+        for (lx, ly, lz) in box_resize_schedule(L, factor, segments):
+            s.set_box(lx, ly, lz, scale)
+            s.run(nsteps)
+        p = s.particles()
+        order = np.argsort(p["tag"]) if "tag" in p else np.arange(len(p["pos"]))
+        assert np.array_equal(np.asarray(s.box_lengths(), np.float32).view(np.uint32), g[name + "_box"].view(np.uint32)), name
+        if bit_exact:
+            for k in ("pos", "vel", "accel", "image"):
+                assert np.array_equal(p[k][order].view(np.uint32), g[name + "_" + k].view(np.uint32)), (name, k)
+        else:
+            Lf = g[name + "_box"]
+            d = p["pos"][order][:, :3] - g[name + "_pos"][:, :3]
+            d -= Lf * np.round(d / Lf)  # a particle within rounding of a face may sit in the neighboring image
+            assert np.abs(d).max() < pos_tol, (name, np.abs(d).max())
+            assert np.abs(p["vel"][order][:, :3] - g[name + "_vel"][:, :3]).max() < vel_tol, name
+        if updates is not None:
+            assert updates(s) == int(g[name + "_updates"]), (name, updates(s), int(g[name + "_updates"]))

@@ -208,3 +208,8 @@ def test_nvt_restatement_matches_reference_bitwise():
         assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
     assert np.array_equal(xa.view(np.uint32), xb.view(np.uint32)), (xa, xb)
     assert abs(xa[0]) > 1e-3
+
+
+def test_box_resize_golden_bit_exact():
+    """BoxResizeUpdater + lambda-scaled distance check + cell-list re-dimensioning restated (tests/golden/box_resize.npz)"""
+    G.check_box_resize(make, bit_exact=True, updates=lambda s: s.nlist_stats()["updates"])

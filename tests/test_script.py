@@ -249,3 +249,70 @@ def test_nvt_script_matches_reference():
     r.run(20)
     eng = hoomd.context.current.engine
     assert np.allclose(eng.nvt_state(), r.nvt_state(), rtol=1e-4, atol=1e-6), (eng.nvt_state(), r.nvt_state())
+
+
+BOX_SCRIPT = """
+import hoomd
+from hoomd import md
+hoomd.context.initialize()
+hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=1.8, type_name='A'), n=9)
+nl = md.nlist.cell()
+lj = md.pair.lj(r_cut=2.5, nlist=nl)
+lj.pair_coeff.set('A', 'A', epsilon=1.0, sigma=1.0)
+md.integrate.mode_standard(dt=0.005)
+md.integrate.langevin(group=hoomd.group.all(), kT=1.0, seed=5)
+resize = hoomd.update.box_resize(L=hoomd.variant.linear_interp([(0, L0), (100, L1)]), period=10)
+hoomd.run(120)
+"""
+
+
+def test_variant_and_box_resize_surface_without_gpu():
+    hoomd = _fresh()
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    v = hoomd.variant.linear_interp([(0, 10.0), (100, 20.0)])
+    assert v.getValue(0) == 10.0 and v.getValue(50) == 15.0 and v.getValue(100) == 20.0 and v.getValue(10 ** 6) == 20.0
+    assert hoomd.variant.linear_interp([(10, 1.0), (20, 3.0)]).getValue(5) == 1.0
+    with pytest.raises(RuntimeError):
+        hoomd.variant.linear_interp([])
+    with pytest.raises(RuntimeError):
+        hoomd.variant.linear_interp([(0, 1.0)], zero=5)  # zero in the future
+    with pytest.raises(RuntimeError):
+        hoomd.update.box_resize()  # nothing to resize (hoomd/update.py:344-346)
+    with pytest.raises(RuntimeError):
+        hoomd.update.box_resize(xy=0.5)  # triclinic: out of scope
+    br = hoomd.update.box_resize(L=hoomd.variant.linear_interp([(0, 8.0), (100, 6.0)]), period=10)
+    assert br._due(0) and not br._due(5) and br._due(20) and br._next(3) == 7 and br._next(10) == 10
+
+
+@pytest.mark.gpu
+def test_box_resize_script_matches_reference():
+    """update.box_resize(L=variant.linear_interp(...), period=10) from a job script against BoxResizeUpdater driven the
+    same way on the reference's CPU classes (sorter period 300 on both)"""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    from hoomd_b200 import workloads
+    pos, vel, L = workloads.sc_lattice(9, 1.8)
+    L1 = 0.9 * L
+    hoomd = _fresh()
+    ns = {}
+    exec(BOX_SCRIPT.replace("L0", repr(float(L))).replace("L1", repr(float(L1))), ns)
+    snap = hoomd.context.current.system.take_snapshot()
+    r = R.RefSystem(pos, (L, L, L), vel4=vel)
+    r.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+    r.setup_integrator(0.005)
+    r.add_langevin(1.0, 5)
+    r.set_sorter(300)
+    for ts in range(0, 120, 10):
+        f = min(ts, 100) / 100.0
+        Lt = np.float32((1.0 - f) * float(L) + f * float(L1)) if ts < 100 else np.float32(L1)
+        r.set_box(Lt, Lt, Lt, True)
+        r.run(10)
+    assert abs(hoomd.context.current.system.box.Lx - float(np.float32(L1))) < 1e-6
+    assert np.array_equal(r.box_lengths(), hoomd.context.current.engine.box_lengths())
+    a = r.particles()
+    order = np.argsort(a["tag"])
+    d = a["pos"][order][:, :3] - snap.particles.position
+    d -= np.float32(L1) * np.round(d / np.float32(L1))
+    assert np.abs(d).max() < 3e-4
+    assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 3e-3
