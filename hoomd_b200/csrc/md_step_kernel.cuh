@@ -9,11 +9,19 @@
 
 namespace b200
 {
-// register bound: 10 CTAs of 128 threads per SM (48 registers) for the plain variants, which fit without spilling; the
-// multi-type / virial / xplor variants and the exp/pow evaluators keep their 56-62 registers
-template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE>
-__global__ void __launch_bounds__(MD_BLOCK, (MULTI_TYPE || VIRIAL || SHIFT_MODE == 2
-                                             || !std::is_same<Evaluator, EvaluatorPairLJ>::value) ? 1 : 1280 / MD_BLOCK)
+// register bound for the plain variants (single type, no virial, no xplor, LJ): 10 CTAs of 128 threads per SM (48 registers,
+// no spills), or OCC = 1: 12 CTAs (40 registers, 36 B of spills outside the neighbor loop).  Measured (profiles/r1r_*.json):
+// at 1M particles the extra warps hide more gather latency (4257 -> 4388 TPS), at 64k the spills cost (31.4k -> 31.0k), so the
+// launcher picks OCC by system size.  The multi-type / virial / xplor variants and the exp/pow evaluators keep their 56-62
+// registers.
+template<class Evaluator, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE> struct MdStepPlain
+    {
+    static constexpr bool value = !MULTI_TYPE && !VIRIAL && SHIFT_MODE != 2 && std::is_same<Evaluator, EvaluatorPairLJ>::value;
+    };
+
+template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE, int OCC = 0>
+__global__ void __launch_bounds__(MD_BLOCK, !MdStepPlain<Evaluator, SHIFT_MODE, VIRIAL, MULTI_TYPE>::value
+                                                ? 1 : (OCC ? 1536 / MD_BLOCK : 1280 / MD_BLOCK))
 k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     {
     constexpr int PPB = MD_BLOCK / TPP; // particles per CTA
@@ -103,7 +111,20 @@ static cudaError_t md_step_mt(const MdStepArgs<Evaluator>& a, cudaStream_t strea
         k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, true><<<grid, bs, smem, stream>>>(a);
         }
     else
+        {
+        if constexpr (MdStepPlain<Evaluator, SHIFT_MODE, VIRIAL, false>::value)
+            {
+            // large systems are latency bound on the neighbor gathers: trade 8 registers for 2 more CTAs per SM
+            static const char* occ_env = getenv("HOOMD_B200_MD_OCC");
+            const bool high_occ = occ_env ? atoi(occ_env) != 0 : a.N >= 200000u;
+            if (high_occ)
+                {
+                k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false, 1><<<grid, bs, 0, stream>>>(a);
+                return cudaGetLastError();
+                }
+            }
         k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false><<<grid, bs, 0, stream>>>(a);
+        }
     return cudaGetLastError();
     }
 
