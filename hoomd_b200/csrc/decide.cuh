@@ -28,6 +28,7 @@ __device__ __forceinline__ void decide_body(StepState* st)
             }
         }
     st->moved = 0u;
+    if (result) st->box_scaled = 0u; // the build that follows resets m_last_L: lambda is 1 from the next check on
     st->need_rebuild = result ? 1u : 0u;
     st->ts_step_two = st->timestep;
     st->timestep = ts1;

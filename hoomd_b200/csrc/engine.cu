@@ -123,6 +123,8 @@ struct b200_system
     float rcut_max_max = 0.0f;
     DevBuf<float> d_r_cut, d_r_listsq, d_rcut_max, d_maxsq;
     float last_L[3] = {0.0f, 0.0f, 0.0f}; // NeighborList::m_last_L: box lengths at the last build (distance-check lambda)
+    std::vector<float> h_check_table[2];  // host copies of the two rows of d_maxsq (kept alive for the async upload)
+    DevBuf<unsigned int> ck_n_neigh, ck_nlist; // list checkpoint of a chunk that starts in a scaled box
     std::vector<unsigned int> h_Nmax;
     DevBuf<unsigned int> d_Nmax, nl_conditions, head_list, n_neigh, nlist, d_req_size;
     DevBuf<float4> last_pos;
@@ -346,6 +348,8 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.d_N = s->mg ? &s->d_state.p->N : nullptr; a.mg = s->mg ? 1 : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
+    for (int d = 0; d < 3; d++) a.lambda[d] = (s->mg || !s->have_nlist) ? 1.0f : s->box.L[d] / s->last_L[d];
+    a.lambda_min = std::min(std::min(a.lambda[0], a.lambda[1]), a.lambda[2]);
     if (s->mg && s->fused_ghosts && s->mg_connected)
         {
         a.gs.tab = s->gs_table.p; a.gs.pplan = s->pplan.p; a.gs.pplan_n = s->pplan_n.p; a.gs.slot_dir = s->slot_dir.p;
@@ -464,6 +468,30 @@ static void cell_list_compute(b200_system* s, unsigned int ts)
     }
 
 // ---- NeighborList -----------------------------------------------------------------------------------------------------
+// Row `row` of the device distance-check table (hoomd/md/NeighborList.cc:981-1006, FP32 like the reference): per type the
+// squared threshold ((r_cut_max + r_buff) lambda_min - r_cut_max) / 2, then lambda x/y/z.  Row 0: lambda = 1.
+static void upload_check_table(b200_system* s, int row)
+    {
+    const unsigned int nt = s->ntypes;
+    float lambda[3] = {1.0f, 1.0f, 1.0f};
+    if (row)
+        for (int d = 0; d < 3; d++) lambda[d] = s->box.L[d] / s->last_L[d];
+    const float lambda_min = std::min(std::min(lambda[0], lambda[1]), lambda[2]);
+    std::vector<float>& t = s->h_check_table[row];
+    t.assign(nt + 3, 0.0f);
+    for (unsigned int i = 0; i < nt; i++)
+        {
+        const float old_rmin = s->h_rcut_max[i];
+        volatile float rmax = old_rmin + s->r_buff;
+        volatile float num = rmax * lambda_min - old_rmin;
+        const float delta_max = num / 2.0f;
+        t[i] = (delta_max > 0.0f) ? delta_max * delta_max : 0.0f;
+        }
+    for (int d = 0; d < 3; d++) t[nt + d] = lambda[d];
+    CUDA_OK(cudaMemcpyAsync(s->d_maxsq.p + (size_t)row * (nt + 3), t.data(), sizeof(float) * (nt + 3),
+                            cudaMemcpyHostToDevice, s->stream));
+    }
+
 // NeighborList::updateRList (hoomd/md/NeighborList.cc:354-400)
 static void nlist_update_rlist(b200_system* s)
     {
@@ -488,17 +516,8 @@ static void nlist_update_rlist(b200_system* s)
     s->d_r_cut.upload(s->h_r_cut.data(), nt * nt, s->stream);
     s->d_r_listsq.upload(s->h_r_listsq.data(), nt * nt, s->stream);
     s->d_rcut_max.upload(s->h_rcut_max.data(), nt, s->stream);
-    // distance-check threshold per type for a fixed box (lambda = 1), hoomd/md/NeighborList.cc:1002-1006, in FP32
-    std::vector<float> maxsq(nt);
-    for (unsigned int i = 0; i < nt; i++)
-        {
-        const float old_rmin = s->h_rcut_max[i];
-        volatile float rmax = old_rmin + s->r_buff;
-        volatile float num = rmax * 1.0f - old_rmin;
-        const float delta_max = num / 2.0f;
-        maxsq[i] = (delta_max > 0.0f) ? delta_max * delta_max : 0.0f;
-        }
-    s->d_maxsq.upload(maxsq.data(), nt, s->stream);
+    // distance-check table for the device-driven steps: row 0 = fixed box (lambda = 1), row 1 = box scaled since the build
+    upload_check_table(s, 0);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     }
 
@@ -981,7 +1000,10 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     const unsigned int N = s->N;
     if (s->force_update) nlist_build_head_list(s); // types may have been permuted by the sorter
     ensure_idx_tables(s);
-    if (s->use_graph != 3) ensure_graph(s);
+    // a short chunk behind an invalidated graph (update.box_resize with a small period re-sets the by-value box argument
+    // every few steps): launching its dozen kernels directly is cheaper than capturing and instantiating a graph for it
+    const bool direct = s->use_graph == 3 || (!s->graph_valid && chunk <= 16);
+    if (!direct) ensure_graph(s);
     if (s->ck_pos.n < N)
         {
         s->ck_pos.alloc(N); s->ck_vel.alloc(N); s->ck_last_pos.alloc(N); s->ck_accel.alloc(N); s->ck_image.alloc(N);
@@ -1005,6 +1027,20 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
         }
 
+    // The box changed since the last list build (update.box_resize): the distance checks of this chunk use the lambda-scaled
+    // row of the table until the first rebuild decision clears StepState::box_scaled.  The list in force was built in the OLD
+    // box, so it cannot be re-created from last_pos after an Nmax overflow: checkpoint the list itself for that case.
+    const bool ck_scaled = box_scaled_since_build(s);
+    if (ck_scaled)
+        {
+        upload_check_table(s, 1);
+        if (s->ck_n_neigh.n < N) s->ck_n_neigh.alloc(N, false);
+        if (s->ck_nlist.n < s->nlist.n) s->ck_nlist.alloc(s->nlist.n, false);
+        CUDA_OK(cudaMemcpyAsync(s->ck_n_neigh.p, s->n_neigh.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->ck_nlist.p, s->nlist.p, sizeof(unsigned int) * s->nlist.n, cudaMemcpyDeviceToDevice,
+                                s->stream));
+        }
+
     StepState& st = *s->h_state;
     memset(&st, 0, sizeof(st));
     st.timestep = s->timestep;
@@ -1014,6 +1050,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     st.r_buff_tiny = (s->r_buff < 1e-6f) ? 1u : 0u;
     st.ntypes = s->ntypes;
     st.steps_left = chunk;
+    st.box_scaled = ck_scaled ? 1u : 0u;
     CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
     FusedStepArgs fa;
     fused_args(s, fa);
@@ -1021,7 +1058,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     if (s->method == 3) nvt_advance(s); // thermostat of the prologue's step one; the later ones run inside k_md_step
     CUDA_OK(launch_decide(s->d_state.p, s->stream));
     const unsigned int nreplay = (chunk + 1) / 2;
-    if (s->use_graph == 3)
+    if (direct)
         {
         // same kernel sequence as the plain graph, launched directly on the stream (profilers see every kernel)
         const unsigned int* enable = &s->d_state.p->need_rebuild;
@@ -1050,6 +1087,26 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         // rebuild recorded -- the very values checkConditions would have seen --, restore the checkpoint and run the chunk
         // again.  The trajectory is deterministic, so the replay is exact.
         s->num_overflows += 1;
+        if (ck_scaled)
+            {
+            // put the checkpoint back, list included (row layout and Nmax untouched), and run the chunk with the reference's
+            // host protocol, which grows Nmax at the overflowing build itself
+            CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->last_pos.p, s->ck_last_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->accel.p, s->ck_accel.p, sizeof(f3) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->n_neigh.p, s->ck_n_neigh.p, sizeof(unsigned int) * N, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemcpyAsync(s->nlist.p, s->ck_nlist.p, sizeof(unsigned int) * s->nlist.n, cudaMemcpyDeviceToDevice,
+                                    s->stream));
+            if (s->method == 3)
+                CUDA_OK(cudaMemcpyAsync(s->d_nvt.p, s->ck_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
+            CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
+            s->force_update = ck_force_update;
+            s->cl_force = true;
+            for (unsigned int k = 0; k < chunk; k++) host_step(s);
+            return;
+            }
         const bool grew = !s->tile_on && nlist_check_conditions(s);
         if (grew) nlist_build_head_list(s);
         CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
@@ -1105,7 +1162,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
-    s->kernels_last_run += 2ull + ((s->graph_uses_cond && s->use_graph != 3) ? (3ull * nreplay + rk * rebuilds)
+    s->kernels_last_run += 2ull + ((s->graph_uses_cond && !direct) ? (3ull * nreplay + rk * rebuilds)
                                                                              : (2ull + 2ull * rk) * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
@@ -1367,7 +1424,7 @@ int b200_sys_setup_pair(b200_system* s, int evaluator, float r_buff, unsigned in
     s->every = check_period;
     s->shift_mode = shift_mode;
     s->h_r_cut.assign(rcut, rcut + nt * nt);
-    s->d_r_cut.alloc(nt * nt); s->d_r_listsq.alloc(nt * nt); s->d_rcut_max.alloc(nt); s->d_maxsq.alloc(nt);
+    s->d_r_cut.alloc(nt * nt); s->d_r_listsq.alloc(nt * nt); s->d_rcut_max.alloc(nt); s->d_maxsq.alloc(2 * (nt + 3));
     nlist_update_rlist(s);
     // pair tables: rcutsq = rcut*rcut, ronsq = ron*ron (PotentialPair::setRcut/setRon, hoomd/md/PotentialPair.h:237-269)
     std::vector<float2> prm(nt * nt);
@@ -1831,13 +1888,6 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
         if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
         if (s->mg)
             mg_run_chunk(s, chunk);
-        else if (s->use_graph && box_scaled_since_build(s))
-            {
-            // the box changed since the last neighbor-list build: the distance check needs lambda = L / L_last
-            // (NeighborList.cc:981-1007).  Step with the host protocol until the next build makes lambda 1 again.
-            host_step(s);
-            chunk = 1;
-            }
         else if (s->use_graph)
             run_chunk_device(s, chunk);
         else

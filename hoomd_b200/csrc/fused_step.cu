@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
                                                         float dt, float r_buff, bool limit, float limit_val,
                                                         bool zero_force, StepState* __restrict__ st,
                                                         const unsigned int* __restrict__ d_N,
-                                                        const NvtState* __restrict__ nvt)
+                                                        const NvtState* __restrict__ nvt, float3 lambda, float lambda_min)
     {
     unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
     bool moved = false;
@@ -37,13 +37,13 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
         pos[j] = p;
         vel[j] = v;
         image[j] = img;
-        // NeighborList::distanceCheck with a fixed box (lambda = 1): hoomd/md/NeighborList.cc:992-1016
+        // NeighborList::distanceCheck, lambda = L / L_at_last_build (1 for a fixed box): hoomd/md/NeighborList.cc:981-1016
         const float4 lp = last_pos[j];
         const float old_rmin = rcut_max[(unsigned int)__float_as_int(p.w)];
-        const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(old_rmin, r_buff), 1.0f), old_rmin), 2.0f);
+        const float delta_max = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(old_rmin, r_buff), lambda_min), old_rmin), 2.0f);
         const float maxsq = (delta_max > 0.0f) ? __fmul_rn(delta_max, delta_max) : 0.0f;
-        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
-                                __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
+        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(lambda.x, lp.x)), __fsub_rn(p.y, __fmul_rn(lambda.y, lp.y)),
+                                __fsub_rn(p.z, __fmul_rn(lambda.z, lp.z)));
         dx = min_image_exact(dx, box);
         moved = dot_exact(dx) >= maxsq;
         }
@@ -102,7 +102,8 @@ cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStr
                                                             a.last_pos, a.rcut_max, a.N, make_box(a.box), a.dt,
                                                             a.r_buff, nve && a.limit, a.limit_val, nve && a.zero_force,
                                                             st, a.d_N,
-                                                            a.method == 3 ? (const NvtState*)a.nvt_state : nullptr);
+                                                            a.method == 3 ? (const NvtState*)a.nvt_state : nullptr,
+                                                            make_float3(a.lambda[0], a.lambda[1], a.lambda[2]), a.lambda_min);
     return cudaGetLastError();
     }
 

@@ -29,6 +29,8 @@ struct StepState
     unsigned int N;               // local particle count (multi-GPU: changes at every migration)
     unsigned int abort;           // multi-GPU: some rank's rebuild overflowed Nmax; every rank stops stepping (1 + buffer)
     unsigned int nvt_error;       // NVT: 1 = kinetic energy outside the accumulator range, 2 = thermostat hand-off timed out
+    unsigned int box_scaled;      // the box changed since the last list build: the distance check uses row 1 of the
+                                  // threshold table (lambda-scaled, NeighborList.cc:981-1007); cleared by the rebuild decision
     };
 
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
@@ -77,7 +79,9 @@ struct FusedStepArgs
     {
     float4* pos; float4* vel; float* accel; int* image; const float4* net_force; const float4* last_pos;
     const unsigned int* tag; const float* rcut_max; const float* gamma;
-    const float* maxsq;           // per type: distance-check threshold^2 (NeighborList.cc:1002-1006, fixed box)
+    const float* maxsq;           // distance-check table, 2 rows of ntypes + 3 floats: threshold^2 per type, then lambda x/y/z
+                                  // (NeighborList.cc:981-1006); row 0 = fixed box (lambda 1), row 1 = box scaled since the build
+    float lambda[3]; float lambda_min; // the same for the chunk prologue's step one (by value)
     unsigned int N; b200_box box; float dt; float r_buff;
     int method;                   // 1 = NVE, 2 = Langevin, 3 = NVT (MTK)
     int limit; float limit_val; int zero_force;

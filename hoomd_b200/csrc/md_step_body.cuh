@@ -122,10 +122,13 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         a.pos_out[i] = p;
         if (a.gs.tab) md_step_send_ghosts(a, i, p);
         a.image[i] = img;
-        // ---- NeighborList::distanceCheck, fixed box (hoomd/md/NeighborList.cc:992-1016) ----
-        const float maxsq = a.maxsq[type_i];
-        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(1.0f, lp.x)), __fsub_rn(p.y, __fmul_rn(1.0f, lp.y)),
-                                __fsub_rn(p.z, __fmul_rn(1.0f, lp.z)));
+        // ---- NeighborList::distanceCheck (hoomd/md/NeighborList.cc:981-1016): row 0 of the table for a fixed box
+        // (lambda = 1), row 1 while the box differs from the one the list was built in ----
+        const float* tab = a.maxsq + (a.st->box_scaled ? a.ntypes + 3u : 0u);
+        const float maxsq = tab[type_i];
+        float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(tab[a.ntypes], lp.x)),
+                                __fsub_rn(p.y, __fmul_rn(tab[a.ntypes + 1u], lp.y)),
+                                __fsub_rn(p.z, __fmul_rn(tab[a.ntypes + 2u], lp.z)));
         dx = min_image_exact_sel(dx, a.box, a.box.periodic.x, a.box.periodic.y, a.box.periodic.z);
         moved = dot_exact(dx) >= maxsq;
         }
