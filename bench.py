@@ -393,9 +393,19 @@ def main():
         step_bytes += 80.0 * n_local
     step_flops = (40.0 * nbar + 55.0) * n_local
     achieved = step_bytes / (step_ms * 1e-3) / 1e9
+    # DRAM bytes per launch from the committed ncu --set full capture of this workload (single GPU only), else null
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            ent = json.load(f).get(workload) if world == 1 else None
+        if ent:
+            traffic, traffic_src = ent["bytes"], ent["source"]
+    except (OSError, ValueError):
+        pass
     roofline = {"bound": "hbm", "kernel": "k_md_step<EvaluatorPairLJ> (force + step two + step one + distance check)"
                 + (" + k_bond_forces<EvaluatorBondFENE>" if workload.startswith("kg") else ""),
-                "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                "traffic_source": traffic_src,
                 "peak_source": peak_src, "kernel_ms": step_ms, "algorithmic_bytes_per_launch": step_bytes,
                 "mean_neighbors": nbar,
                 "fp32_tflops": step_flops / (step_ms * 1e-3) / 1e12,
