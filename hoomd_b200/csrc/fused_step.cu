@@ -4,7 +4,7 @@
 //                      instead of a second 32 B/particle kernel, hoomd/md/NeighborListGPU.cu:32-82)
 //   k_decide         : NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163) on the device, 1 thread
 //   k_md_step        : the whole MD step in one launch (force + step two + next step one + check + decision)
-//   k_post_rebuild   : overflow detection after a rebuild (hoomd/md/NeighborList.cc:1389-1405 needs the host: sticky flag)
+//   (Nmax overflow after a device-side rebuild is flagged by the build kernel itself: OverflowHook, kernels.h)
 // Per-particle arithmetic is the shared body of integrate_body.cuh / pair_body.cuh => bit-identical to the driver kernels.
 #include "common.cuh"
 #include "md_step_kernel.cuh"
@@ -63,21 +63,6 @@ __global__ void k_graph_pre(StepState* st, cudaGraphConditionalHandle handle)
 #endif
     }
 
-__global__ void k_post_rebuild(StepState* st, unsigned int* __restrict__ conditions,
-                               const unsigned int* __restrict__ Nmax, int stop_on_overflow)
-    {
-    if (!st->need_rebuild) return;
-    for (unsigned int t = 0; t < st->ntypes; t++)
-        {
-        if (conditions[t] > Nmax[t]) st->overflow = 1u;
-        }
-    // single GPU: the rest of the chunk would run on truncated lists and is discarded anyway -- turn the remaining
-    // launches into no-ops, so that `conditions` keeps exactly the counts of the overflowing rebuild (what the reference's
-    // checkConditions sees, hoomd/md/NeighborList.cc:1389-1405) for the host to grow Nmax from
-    if (stop_on_overflow && st->overflow) st->steps_left = 0u;
-    }
-
-
 __global__ void __launch_bounds__(256) k_compute_accel(float3s* __restrict__ accel,
                                                        const float4* __restrict__ net_force,
                                                        const float4* __restrict__ vel, unsigned int N)
@@ -116,13 +101,6 @@ cudaError_t launch_decide(StepState* st, cudaStream_t stream)
 cudaError_t launch_graph_pre(StepState* st, unsigned long long cond_handle, cudaStream_t stream)
     {
     k_graph_pre<<<1, 1, 0, stream>>>(st, (cudaGraphConditionalHandle)cond_handle);
-    return cudaGetLastError();
-    }
-
-cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
-                                cudaStream_t stream, int stop_on_overflow)
-    {
-    k_post_rebuild<<<1, 1, 0, stream>>>(st, nlist_conditions, Nmax, stop_on_overflow);
     return cudaGetLastError();
     }
 

@@ -122,9 +122,6 @@ B200_DECL_EV(morse)
 cudaError_t launch_md_step_kind(int evaluator, const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,
                                 const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
                                 unsigned long long cond_handle, int use_cond, cudaStream_t stream);
-// after a device-driven rebuild: overflow detection, condition reset
-cudaError_t launch_post_rebuild(StepState* st, unsigned int* nlist_conditions, const unsigned int* Nmax,
-                                cudaStream_t stream, int stop_on_overflow = 0);
 // a = F/m (Integrator::computeAccelerations, hoomd/Integrator.cc:222-256)
 cudaError_t launch_compute_accel(float* accel, const float4* net_force, const float4* vel, unsigned int N,
                                  cudaStream_t stream);
