@@ -105,7 +105,7 @@ SYMBOLS = [
 ]
 
 # enum B200_PAIR_* (hoomd/md/AllPairPotentials.h)
-PAIR_KINDS = {"lj": 0, "gauss": 1, "yukawa": 2, "mie": 3, "force_shifted_lj": 4, "morse": 5}
+PAIR_KINDS = {"lj": 0, "gauss": 1, "yukawa": 2, "mie": 3, "force_shifted_lj": 4, "morse": 5, "dpd_conservative": 6}
 
 
 def pair_params(kind, nt, **c):
@@ -129,6 +129,8 @@ def pair_params(kind, nt, **c):
         p[..., 0], p[..., 1], p[..., 2], p[..., 3] = eps * sig ** n * pref, eps * sig ** m * pref, n, m
     elif kind == "morse":
         p[..., 0], p[..., 1], p[..., 2] = bc(c["D0"]), bc(c["alpha"]), bc(c["r0"])
+    elif kind == "dpd_conservative":  # (A, gamma = 0), hoomd/md/pair.py:1513-1516
+        p[..., 0] = bc(c["A"])
     else:
         raise ValueError("unknown pair potential " + str(kind))
     return np.ascontiguousarray(p.astype(np.float32))

@@ -1414,7 +1414,7 @@ int b200_sys_setup_pair(b200_system* s, int evaluator, float r_buff, unsigned in
     {
     SYS_TRY(s)
     const unsigned int nt = s->ntypes;
-    if (evaluator < B200_PAIR_LJ || evaluator > B200_PAIR_MORSE) throw std::runtime_error("pair: unknown evaluator");
+    if (evaluator < B200_PAIR_LJ || evaluator > B200_PAIR_DPD) throw std::runtime_error("pair: unknown evaluator");
     if (evaluator != B200_PAIR_LJ && s->pair_mode == 1)
         throw std::runtime_error("pair: the cell-tile pair mode is instantiated for md.pair.lj only");
     s->pair_kind = evaluator;

@@ -132,6 +132,8 @@ cudaError_t launch_md_step_kind(int evaluator, const b200_pair_args& pa, const v
             return launch_md_step_fslj(pa, d_params, fa, pos_in, pos_out, copy_pos_on_last, st, cond_handle, use_cond, stream);
         case B200_PAIR_MORSE:
             return launch_md_step_morse(pa, d_params, fa, pos_in, pos_out, copy_pos_on_last, st, cond_handle, use_cond, stream);
+        case B200_PAIR_DPD:
+            return launch_md_step_dpd(pa, d_params, fa, pos_in, pos_out, copy_pos_on_last, st, cond_handle, use_cond, stream);
         default:
             return cudaErrorInvalidValue;
         }

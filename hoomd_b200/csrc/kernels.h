@@ -118,6 +118,7 @@ B200_DECL_EV(yukawa)
 B200_DECL_EV(mie)
 B200_DECL_EV(fslj)
 B200_DECL_EV(morse)
+B200_DECL_EV(dpd)
 #undef B200_DECL_EV
 cudaError_t launch_md_step_kind(int evaluator, const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,
                                 const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,

@@ -19,8 +19,11 @@
 #elif B200_EV == 5
 #define EV EvaluatorPairMorse
 #define NAME morse
+#elif B200_EV == 6
+#define EV EvaluatorPairDPD
+#define NAME dpd
 #else
-#error "B200_EV must be 1..5"
+#error "B200_EV must be 1..6"
 #endif
 #define CAT2(a, b) a##b
 #define CAT(a, b) CAT2(a, b)

@@ -38,6 +38,7 @@ extern "C" int b200_compute_pair_forces(int evaluator, const b200_pair_args* arg
         case B200_PAIR_MIE: return (int)launch_pair_mie(*args, d_params, (cudaStream_t)stream);
         case B200_PAIR_FORCE_SHIFTED_LJ: return (int)launch_pair_fslj(*args, d_params, (cudaStream_t)stream);
         case B200_PAIR_MORSE: return (int)launch_pair_morse(*args, d_params, (cudaStream_t)stream);
+        case B200_PAIR_DPD: return (int)launch_pair_dpd(*args, d_params, (cudaStream_t)stream);
         default: return (int)cudaErrorInvalidValue;
         }
     }

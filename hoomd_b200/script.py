@@ -601,6 +601,20 @@ md.pair.force_shifted_lj = _ForceShiftedLJ
 md.pair.morse = _Morse
 
 
+class _DPDConservative(_Pair):
+    """md.pair.dpd_conservative (hoomd/md/pair.py:1440-1517): the conservative part of the DPD force"""
+    kind, required_coeffs = "dpd_conservative", ["A"]
+
+    def set_params(self, coeff=None, mode=None):
+        if mode is not None:  # hoomd/md/pair.py:1502-1511: the potential is continuous at r_cut by construction
+            raise RuntimeError("Error setting DPD params: not possible to set energy shift mode for this potential")
+        if coeff is not None:
+            super().set_params(coeff=coeff)
+
+
+md.pair.dpd_conservative = _DPDConservative
+
+
 class _BondCoeff:
     """bond.coeff (hoomd/md/bond.py:22-164): per-bond-type table"""
 

@@ -206,10 +206,11 @@ B200_API int b200_compute_lj_forces(const b200_pair_args* args, const float* d_p
  * hoomd/md/AllDriverPotentialPairGPU.cuh).  d_params is the reference's param_type array [ntypes*ntypes]:
  *   LJ (lj1, lj2) Scalar2 | GAUSS (epsilon, sigma) Scalar2 | YUKAWA (epsilon, kappa) Scalar2 |
  *   MIE (mie1, mie2, n, m) Scalar4 | FORCE_SHIFTED_LJ (lj1, lj2) Scalar2 | MORSE (D0, alpha, r0, -) Scalar4
+ *   DPD (A, gamma) Scalar2: the conservative force of md.pair.dpd_conservative (EvaluatorPairDPDThermo.h:139-160)
  * (coefficient processing: hoomd/md/pair.py gauss :611-690, yukawa :835-900, mie :2188-2265, force_shifted_lj :1781-1850,
  * morse :1193-1260).  Energy shift modes as for LJ. */
 enum { B200_PAIR_LJ = 0, B200_PAIR_GAUSS = 1, B200_PAIR_YUKAWA = 2, B200_PAIR_MIE = 3, B200_PAIR_FORCE_SHIFTED_LJ = 4,
-       B200_PAIR_MORSE = 5 };
+       B200_PAIR_MORSE = 5, B200_PAIR_DPD = 6 };
 B200_API int b200_compute_pair_forces(int evaluator, const b200_pair_args* args, const void* d_params,
                                       b200_stream_t stream);
 

@@ -683,6 +683,18 @@ static int pair_eval(int kind, float rsq, float rcutsq, float p1, float p2, floa
                 }
             break;
             }
+        case 6: /* DPD conservative: (A, gamma), EvaluatorPairDPDThermo.h:139-160; no energy shift */
+            {
+            const float a = p1;
+            if (!(rsq < rcutsq)) return 0;
+            float rinv = 1.0f / sqrtf(rsq);
+            float r = 1.0f / rinv;
+            float rcutinv = 1.0f / sqrtf(rcutsq);
+            float rcut = 1.0f / rcutinv;
+            force_divr = a * (rinv - rcutinv);
+            pair_eng = a * (rcut - r) - (1.0f / 2.0f) * a * rcutinv * (rcutsq - rsq);
+            break;
+            }
         default:
             return 0;
         }
@@ -1069,7 +1081,7 @@ int orc_setup_lj(orc_system* s, float r_buff, unsigned int check_period, const f
     return 0;
     }
 
-/* md.pair.<evaluator>: 0 lj, 1 gauss, 2 yukawa, 3 mie, 4 force_shifted_lj, 5 morse; params4 = ntypes x ntypes x 4 */
+/* md.pair.<evaluator>: 0 lj, 1 gauss, 2 yukawa, 3 mie, 4 force_shifted_lj, 5 morse, 6 dpd_conservative; params4 = ntypes x ntypes x 4 */
 int orc_setup_pair(orc_system* s, int evaluator, float r_buff, unsigned int check_period, const float* rcut,
                    const float* params4, const float* ron, int shift_mode)
     {
@@ -1084,7 +1096,7 @@ int orc_setup_pair(orc_system* s, int evaluator, float r_buff, unsigned int chec
         }
     int rc = orc_setup_lj(s, r_buff, check_period, rcut, a, b, ron, shift_mode);
     free(a); free(b);
-    if (evaluator < 0 || evaluator > 5) { snprintf(s->error, sizeof(s->error), "unknown pair evaluator"); return 1; }
+    if (evaluator < 0 || evaluator > 6) { snprintf(s->error, sizeof(s->error), "unknown pair evaluator"); return 1; }
     s->pair_kind = evaluator;
     return rc;
     }

@@ -290,6 +290,7 @@ int ref_setup_pair(void* h, int evaluator, float r_buff, int check_period, int f
         case 3: s->lj = make_pair<PotentialPairMie>(s, rcut, params4, ron, shift_mode); break;
         case 4: s->lj = make_pair<PotentialPairForceShiftedLJ>(s, rcut, params4, ron, shift_mode); break;
         case 5: s->lj = make_pair<PotentialPairMorse>(s, rcut, params4, ron, shift_mode); break;
+        case 6: s->lj = make_pair<PotentialPairDPD>(s, rcut, params4, ron, shift_mode); break;
         default: throw std::runtime_error("unknown pair evaluator");
         }
     REF_CATCH(s, 1)

@@ -190,6 +190,7 @@ PAIR_CASES = {  # as tests/golden/make_golden.py
     "mie": (dict(epsilon=1.0, sigma=1.0, n=13.0, m=7.0), 2.5, 1.8),
     "force_shifted_lj": (dict(epsilon=1.0, sigma=1.0, alpha=1.0), 2.5, 1.8),
     "morse": (dict(D0=1.2, alpha=3.0, r0=1.1), 2.5, 1.8),
+    "dpd_conservative": (dict(A=25.0), 1.6, 1.2),
 }
 
 

@@ -47,6 +47,7 @@ TWO_TYPE = {  # per type pair (AA, AB, BB) coefficients
                 m=[[7.0, 6.0], [6.0, 7.0]]),
     "force_shifted_lj": dict(epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]]),
     "morse": dict(D0=[[1.2, 1.0], [1.0, 0.7]], alpha=[[3.0, 2.5], [2.5, 2.0]], r0=[[1.1, 1.0], [1.0, 1.2]]),
+    "dpd_conservative": dict(A=[[25.0, 40.0], [40.0, 15.0]]),
 }
 
 

@@ -316,3 +316,19 @@ def test_box_resize_script_matches_reference():
     d -= np.float32(L1) * np.round(d / np.float32(L1))
     assert np.abs(d).max() < 3e-4
     assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 3e-3
+
+
+def test_dpd_conservative_surface_without_gpu():
+    hoomd = _fresh()
+    from hoomd import md
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=1.0, type_name="A"), n=4)
+    nl = md.nlist.cell()
+    dpdc = md.pair.dpd_conservative(r_cut=1.0, nlist=nl)
+    dpdc.pair_coeff.set("A", "A", A=25.0)
+    t = dpdc.tables(["A"])
+    assert t["A"][0][0] == 25.0 and t["r_cut"][0][0] == 1.0
+    with pytest.raises(RuntimeError):
+        dpdc.set_params(mode="shift")  # hoomd/md/pair.py:1502-1511
+    from hoomd_b200 import _lib
+    p = _lib.pair_params("dpd_conservative", 1, A=25.0)
+    assert p.shape == (1, 1, 4) and p[0, 0, 0] == 25.0 and p[0, 0, 1] == 0.0  # (A, gamma = 0)
