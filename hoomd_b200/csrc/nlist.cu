@@ -280,7 +280,8 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     for (unsigned int pass = 0; pass < total; pass += NL_CAP)
         {
         const unsigned int cnt = min((unsigned int)NL_CAP, total - pass);
-        const unsigned int cnt_padded = (cnt + 63u) & ~63u; // NL_CAP is a multiple of 64
+        const unsigned int cnt_padded = (cnt + 31u) & ~31u; // NL_CAP is a multiple of 64
+        const unsigned int cnt64 = cnt_padded & ~63u;
         if (pass) __syncthreads(); // everyone is done with the previous tile
         for (unsigned int t = threadIdx.x; t < cnt_padded; t += NL_BLOCK)
             {
@@ -316,14 +317,26 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
             const unsigned int Nmax_i = Nmax[type_i];
             unsigned int* row = nlist + head_list[i];
             unsigned int n = pass ? n_neigh[i] : 0u; // later passes continue the count this warp stored itself
+            // 64 candidates per trip, then at most one 32-wide trip: the tile is padded to 32, not to 64 (a neighborhood
+            // holds 216 +- 15 candidates: 6 % fewer distance tests)
             if (wrap_any)
-                n = nlist_scan_tile<MULTI_TYPE, true, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
-                                                            lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
-                                                            ntypes);
+                {
+                n = nlist_scan_tile<MULTI_TYPE, true, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt64, lane, box,
+                                                            wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq, ntypes);
+                if (cnt_padded != cnt64)
+                    n = nlist_scan_tile<MULTI_TYPE, true, HALF, 1>(n, pi4, i, type_i, Nmax_i, row, s_cand + cnt64,
+                                                                   s_type + cnt64, 32u, lane, box, wx, wy, wz, rcut_00,
+                                                                   rlsq_00, r_cut, r_listsq, ntypes);
+                }
             else
-                n = nlist_scan_tile<MULTI_TYPE, false, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt_padded,
-                                                             lane, box, wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq,
-                                                             ntypes);
+                {
+                n = nlist_scan_tile<MULTI_TYPE, false, HALF>(n, pi4, i, type_i, Nmax_i, row, s_cand, s_type, cnt64, lane, box,
+                                                             wx, wy, wz, rcut_00, rlsq_00, r_cut, r_listsq, ntypes);
+                if (cnt_padded != cnt64)
+                    n = nlist_scan_tile<MULTI_TYPE, false, HALF, 1>(n, pi4, i, type_i, Nmax_i, row, s_cand + cnt64,
+                                                                    s_type + cnt64, 32u, lane, box, wx, wy, wz, rcut_00,
+                                                                    rlsq_00, r_cut, r_listsq, ntypes);
+                }
             if (lane == 0)
                 {
                 if (pass + NL_CAP < total)

@@ -159,6 +159,16 @@ class System:
     def add_nvt(self, kT, tau):
         """md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK (hoomd/md/integrate.py:163-260)"""
         self._check(_lib.lib().b200_sys_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))
+        self._nvt = (np.float32(kT), np.float32(tau))
+
+    def nvt_reservoir_energy(self):
+        """log quantity nvt_mtk_reservoir_energy: g kT (xi^2 tau^2 / 2 + eta), evaluated like TwoStepNVTMTK::getLogValue
+        (hoomd/md/TwoStepNVTMTK.cc:82-107: FP32 bracket, product with the double set point)"""
+        xi, eta = self.nvt_state()
+        kT, tau = self._nvt
+        g = np.float32(3 * self.N - 3)
+        inner = np.float32(np.float32(np.float32(np.float32(xi * xi) * tau) * tau) / np.float32(2.0)) + eta
+        return float(np.float32(np.float64(g) * np.float64(kT) * np.float64(np.float32(inner))))
 
     def set_nvt_state(self, xi, eta):
         """restore the thermostat variables of an earlier run (restart / engine re-configuration)"""

@@ -782,13 +782,15 @@ class _Log:
     def __init__(self, filename=None, quantities=(), period=1, **kw):
         _require_context()
         for q in quantities:
-            if q not in self.QUANTITIES and q != "pair_lj_energy":
+            if q not in self.QUANTITIES and q not in ("pair_lj_energy", "nvt_mtk_reservoir_energy_all"):
                 raise RuntimeError("Unknown log quantity " + q)
         self.quantities, self.period, self.filename, self.rows = list(quantities), int(period), filename, []
         context.current.loggers.append(self)
         context.current.engine_dirty = True
 
     def query(self, quantity):
+        if quantity == "nvt_mtk_reservoir_energy_all":  # provided by md.integrate.nvt (log name + "_" + group name)
+            return context.current.engine.nvt_reservoir_energy()
         th = context.current.engine.thermo()
         th["pair_lj_energy"] = th["pe"]
         return float(th[self.QUANTITIES.get(quantity, quantity)])

@@ -1125,6 +1125,12 @@ int orc_add_nvt(orc_system* s, float kT, float tau) /* TwoStepNVTMTK ctor + init
     return 0;
     }
 void orc_get_nvt_state(orc_system* s, float* xi_eta) { xi_eta[0] = s->nvt_xi; xi_eta[1] = s->nvt_eta; }
+float orc_get_nvt_reservoir_energy(orc_system* s) /* TwoStepNVTMTK::getLogValue, TwoStepNVTMTK.cc:82-107 */
+    {
+    const float g = (float)(3u * s->N - 3u);
+    const float xi = s->nvt_xi, eta = s->nvt_eta, tau = s->nvt_tau;
+    return (float)((double)g * (double)s->kT * (double)(xi * xi * tau * tau / 2.0f + eta));
+    }
 /* BoxResizeUpdater::update for one target box (hoomd/BoxResizeUpdater.cc:60-136), orthorhombic */
 int orc_set_box(orc_system* s, float Lx, float Ly, float Lz, int scale_particles)
     {

@@ -45,6 +45,7 @@ int orc_add_nvt(orc_system* s, float kT, float tau);
 int orc_set_box(orc_system* s, float Lx, float Ly, float Lz, int scale_particles);
 void orc_get_box(orc_system* s, float* L3);
 void orc_get_nvt_state(orc_system* s, float* xi_eta);
+float orc_get_nvt_reservoir_energy(orc_system* s);
 void orc_set_timestep(orc_system* s, unsigned int ts);
 unsigned int orc_get_timestep(orc_system* s);
 int orc_compute_nlist(orc_system* s, unsigned int ts);

@@ -42,6 +42,8 @@ def lib():
         L.orc_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
         L.orc_get_box.argtypes = [vp, vp]
         L.orc_get_nvt_state.argtypes = [vp, vp]
+        L.orc_get_nvt_reservoir_energy.argtypes = [vp]
+        L.orc_get_nvt_reservoir_energy.restype = C.c_float
         L.orc_set_timestep.argtypes = [vp, C.c_uint]
         L.orc_get_timestep.argtypes = [vp]
         L.orc_compute_nlist.argtypes = [vp, C.c_uint]
@@ -184,6 +186,9 @@ class OracleSystem:
         out = np.zeros(2, np.float32)
         lib().orc_get_nvt_state(self.h, _ptr(out))
         return out
+
+    def nvt_reservoir_energy(self):
+        return float(lib().orc_get_nvt_reservoir_energy(self.h))
 
     def set_timestep(self, ts):
         lib().orc_set_timestep(self.h, int(ts))

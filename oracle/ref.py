@@ -40,6 +40,7 @@ def lib():
         _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
         _lib.ref_get_box.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_get_nvt_state.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.ref_get_nvt_reservoir_energy.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
         for name in ("ref_destroy", "ref_last_error", "ref_get_N", "ref_get_timestep", "ref_get_virial_pitch",
@@ -180,6 +181,11 @@ class RefSystem:
         out = np.zeros(2, np.float32)
         self._check(lib().ref_get_nvt_state(self.h, _ptr(out)))
         return out
+
+    def nvt_reservoir_energy(self):
+        out = np.zeros(1, np.float32)
+        self._check(lib().ref_get_nvt_reservoir_energy(self.h, _ptr(out)))
+        return float(out[0])
 
     def set_sorter(self, period):
         lib().ref_set_sorter(self.h, C.c_uint(period))

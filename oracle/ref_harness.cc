@@ -412,6 +412,18 @@ void ref_get_box(void* h, float* L3)
     L3[0] = L.x; L3[1] = L.y; L3[2] = L.z;
     }
 
+//! the method's log quantity nvt_mtk_reservoir_energy (hoomd/md/TwoStepNVTMTK.cc:82-107)
+int ref_get_nvt_reservoir_energy(void* h, float* out)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    bool mine = false;
+    *out = s->nvt->getLogValue("nvt_mtk_reservoir_energy", s->timestep, mine);
+    if (!mine) throw std::runtime_error("nvt_mtk_reservoir_energy is not provided by the method");
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
 //! hoomd.update.sort (period 0 disables); the first sort happens at the first step run, like System::run
 void ref_set_sorter(void* h, unsigned int period)
     {

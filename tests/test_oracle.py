@@ -202,12 +202,13 @@ def test_nvt_restatement_matches_reference_bitwise():
         s.setup_integrator(0.004)
         s.add_nvt(0.8, 0.25)
         s.run(250)
-        outs.append((s.particles(), s.nvt_state()))
-    (pa, xa), (pb, xb) = outs
+        outs.append((s.particles(), s.nvt_state(), s.nvt_reservoir_energy()))
+    (pa, xa, _), (pb, xb, _) = outs
     for k in ("pos", "vel", "accel", "image"):
         assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
     assert np.array_equal(xa.view(np.uint32), xb.view(np.uint32)), (xa, xb)
     assert abs(xa[0]) > 1e-3
+    assert outs[0][2] == outs[1][2] and outs[0][2] != 0.0  # log quantity nvt_mtk_reservoir_energy
 
 
 def test_box_resize_golden_bit_exact():

@@ -243,6 +243,10 @@ def test_nvt_script_matches_reference():
     assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
     eng = hoomd.context.current.engine
     assert np.allclose(eng.nvt_state(), r.nvt_state(), rtol=2e-5, atol=1e-7)
+    log = hoomd.analyze.log(filename=None, quantities=["nvt_mtk_reservoir_energy_all", "temperature"], period=10)
+    assert abs(log.query("nvt_mtk_reservoir_energy_all") - r.nvt_reservoir_energy()) <= 1e-4 * abs(r.nvt_reservoir_energy())
+    hoomd.context.current.loggers.remove(log)
+    hoomd.context.current.engine_dirty = False
     # continue; the re-configured engine must pick the thermostat variables up again
     ns["nvt"].set_params(tau=0.5)
     hoomd.run(20)
