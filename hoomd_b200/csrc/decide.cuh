@@ -20,7 +20,9 @@ __device__ __forceinline__ void decide_body(StepState* st)
         result = false;
     else
         {
-        result = st->r_buff_tiny || *((volatile unsigned int*)&st->moved);
+        // distance checks off: the check period decides (every == 0: always); otherwise the distance check of the step
+        const bool period_hit = st->no_dist_check && (st->every == 0u || (st->every > 1u && ts1 == st->last_updated + st->every));
+        result = st->r_buff_tiny || period_hit || *((volatile unsigned int*)&st->moved);
         if (result)
             {
             st->last_updated = ts1;

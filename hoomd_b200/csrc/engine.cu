@@ -132,6 +132,7 @@ struct b200_system
     unsigned int nl_last_computed = 0;
     bool force_update = true;
     unsigned int every = 0, last_updated_tstep = 0, last_checked_tstep = 0;
+    bool dist_check = true;              // NeighborList::m_dist_check (md.nlist.cell(dist_check=...))
     bool last_check_result = false;
     unsigned long long num_updates = 0, num_forced = 0, num_overflows = 0;
 
@@ -578,7 +579,7 @@ static bool nlist_distance_check(b200_system* s, unsigned int ts)
     return *s->h_flag == ts + 1;
     }
 
-// NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163); dist_check is always on (md.nlist.cell default)
+// NeighborList::needsUpdating (hoomd/md/NeighborList.cc:1080-1163)
 static bool nlist_needs_updating(b200_system* s, unsigned int ts)
     {
     if (s->last_checked_tstep == ts)
@@ -607,7 +608,9 @@ static bool nlist_needs_updating(b200_system* s, unsigned int ts)
         }
     else
         {
-        if (s->r_buff < 1e-6f) result = true;
+        if (s->r_buff < 1e-6f
+            || (!s->dist_check && (s->every == 0 || (s->every > 1 && ts == s->last_updated_tstep + s->every))))
+            result = true; // distance checks off: the check period decides (NeighborList.cc:1126-1135)
         else result = nlist_distance_check(s, ts);
         if (result)
             {
@@ -1051,6 +1054,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     st.ntypes = s->ntypes;
     st.steps_left = chunk;
     st.box_scaled = ck_scaled ? 1u : 0u;
+    st.no_dist_check = s->dist_check ? 0u : 1u;
     CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
     FusedStepArgs fa;
     fused_args(s, fa);
@@ -1725,6 +1729,16 @@ int b200_sys_set_box(b200_system* s, float Lx, float Ly, float Lz, int scale_par
 void b200_sys_get_box(b200_system* s, float* L3)
     {
     for (int d = 0; d < 3; d++) L3[d] = s->box.L[d];
+    }
+
+// md.nlist.cell(dist_check=...) / nlist.set_params(dist_check=...): NeighborList::setEvery(every, dist_check)
+int b200_sys_set_dist_check(b200_system* s, int on)
+    {
+    SYS_TRY(s)
+    if (s->mg && !on) throw std::runtime_error("nlist: dist_check=False is not available under domain decomposition yet");
+    s->dist_check = on != 0;
+    s->force_update = true; // NeighborList::setEvery ends in forceUpdate() (hoomd/md/NeighborList.h:148-153)
+    SYS_CATCH(s)
     }
 
 int b200_sys_add_nvt(b200_system* s, float kT, float tau)

@@ -29,6 +29,7 @@ struct StepState
     unsigned int N;               // local particle count (multi-GPU: changes at every migration)
     unsigned int abort;           // multi-GPU: some rank's rebuild overflowed Nmax; every rank stops stepping (1 + buffer)
     unsigned int nvt_error;       // NVT: 1 = kinetic energy outside the accumulator range, 2 = thermostat hand-off timed out
+    unsigned int no_dist_check;   // NeighborList::m_dist_check off: rebuild when the check period is hit (NeighborList.cc:1126-1135)
     unsigned int box_scaled;      // the box changed since the last list build: the distance check uses row 1 of the
                                   // threshold table (lambda-scaled, NeighborList.cc:981-1007); cleared by the rebuild decision
     };

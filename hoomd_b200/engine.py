@@ -156,6 +156,10 @@ class System:
         _lib.lib().b200_sys_get_box(self.h, _p(out))
         return out
 
+    def set_dist_check(self, on=True):
+        """md.nlist.cell(dist_check=...): off = rebuild whenever the check period is hit"""
+        self._check(_lib.lib().b200_sys_set_dist_check(self.h, int(on)))
+
     def add_nvt(self, kT, tau):
         """md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK (hoomd/md/integrate.py:163-260)"""
         self._check(_lib.lib().b200_sys_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))

@@ -843,6 +843,7 @@ def _configure_engine():
             else:
                 eng.setup_harmonic(k=t["k"], r0=t["r0"])
         eng.exclusions_from_bonds("bond" in lj.nlist.exclusions)
+    eng.set_dist_check(lj.nlist.dist_check)
     eng.set_virial(need_virial)
     eng.setup_integrator(ctx.integrator.dt)
     m = methods[0]

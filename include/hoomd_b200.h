@@ -422,6 +422,9 @@ B200_API int b200_sys_setup_integrator(b200_system* s, float dt);
 B200_API int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force);
 /* md.integrate.langevin(group=all, kT, seed) + set_gamma per type (gamma NULL = 1.0) */
 B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
+/* md.nlist.cell(dist_check=False): rebuild when the check period is hit instead of when a particle moved r_buff/2
+ * (NeighborList::setEvery(every, dist_check), hoomd/md/NeighborList.cc:1126-1135); default on */
+B200_API int b200_sys_set_dist_check(b200_system* s, int on);
 /* md.integrate.nvt(group=all, kT, tau): TwoStepNVTMTK with its own ComputeThermo; the thermostat state stays on the device
  * and advances inside the single-kernel MD step.  get_nvt_state: {xi, eta} (the method's IntegratorVariables). */
 B200_API int b200_sys_add_nvt(b200_system* s, float kT, float tau);

@@ -39,6 +39,7 @@ struct orc_system
     f4* xyzf;
     unsigned int* cell_adj; unsigned int n_adj;
     int cl_first, cl_force; unsigned int cl_last;
+    int no_dist_check;       /* NeighborList::m_dist_check == false (md.nlist.cell(dist_check=False)) */
     int cl_box_changed; f3 last_L; /* CellList::m_box_changed; NeighborList::m_last_L (nearest plane distances at the last build) */
     /* NeighborList */
     int have_nlist;
@@ -351,7 +352,7 @@ static int nl_distance_check(orc_system* s) /* NeighborList.cc:964-1040; lambda 
     return 0;
     }
 
-static int nl_needs_updating(orc_system* s, unsigned int ts) /* NeighborList.cc:1080-1163 (dist_check on) */
+static int nl_needs_updating(orc_system* s, unsigned int ts) /* NeighborList.cc:1080-1163 */
     {
     int result = 0;
     if (s->last_checked == ts)
@@ -367,7 +368,10 @@ static int nl_needs_updating(orc_system* s, unsigned int ts) /* NeighborList.cc:
         }
     else
         {
-        if (s->r_buff < 1e-6f) result = 1;
+        /* distance checks off: rebuild when the check period is hit (or every step for period 0), NeighborList.cc:1126-1135 */
+        if (s->r_buff < 1e-6f
+            || (s->no_dist_check && (s->every == 0 || (s->every > 1 && ts == s->last_updated + s->every))))
+            result = 1;
         else result = nl_distance_check(s);
         if (result) { s->last_updated = ts; s->updates += 1; }
         }
@@ -1123,6 +1127,11 @@ int orc_add_nvt(orc_system* s, float kT, float tau) /* TwoStepNVTMTK ctor + init
     s->method = 3; s->limit = 0; s->zero_force = 0; s->kT = kT; s->nvt_tau = tau;
     s->nvt_xi = s->nvt_eta = 0.0f; s->nvt_exp_fac = 1.0f;
     return 0;
+    }
+void orc_set_dist_check(orc_system* s, int on) /* NeighborList::setEvery(every, dist_check): ends in forceUpdate() */
+    {
+    s->no_dist_check = !on;
+    s->force_update = 1;
     }
 void orc_get_nvt_state(orc_system* s, float* xi_eta) { xi_eta[0] = s->nvt_xi; xi_eta[1] = s->nvt_eta; }
 float orc_get_nvt_reservoir_energy(orc_system* s) /* TwoStepNVTMTK::getLogValue, TwoStepNVTMTK.cc:82-107 */

@@ -39,6 +39,7 @@ def lib():
         L.orc_add_nve.argtypes = [vp, C.c_int, C.c_float, C.c_int]
         L.orc_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
         L.orc_add_nvt.argtypes = [vp, C.c_float, C.c_float]
+        L.orc_set_dist_check.argtypes = [vp, C.c_int]
         L.orc_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
         L.orc_get_box.argtypes = [vp, vp]
         L.orc_get_nvt_state.argtypes = [vp, vp]
@@ -178,6 +179,9 @@ class OracleSystem:
         out = np.zeros(3, np.float32)
         lib().orc_get_box(self.h, _ptr(out))
         return out
+
+    def set_dist_check(self, on=True):
+        lib().orc_set_dist_check(self.h, int(on))
 
     def add_nvt(self, kT, tau):
         lib().orc_add_nvt(self.h, C.c_float(kT), C.c_float(tau))

@@ -37,6 +37,7 @@ def lib():
         _lib.ref_setup_pair.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_int]
         _lib.ref_add_nvt.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        _lib.ref_set_dist_check.argtypes = [C.c_void_p, C.c_int]
         _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
         _lib.ref_get_box.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_get_nvt_state.argtypes = [C.c_void_p, C.c_void_p]
@@ -172,6 +173,9 @@ class RefSystem:
         out = np.zeros(3, np.float32)
         lib().ref_get_box(self.h, _ptr(out))
         return out
+
+    def set_dist_check(self, on=True):
+        self._check(lib().ref_set_dist_check(self.h, int(on)))
 
     def add_nvt(self, kT, tau):
         self._check(lib().ref_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))

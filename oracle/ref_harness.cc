@@ -49,6 +49,7 @@ struct RefSystem
     std::shared_ptr<TwoStepNVE> nve;
     std::shared_ptr<TwoStepLangevin> langevin;
     std::shared_ptr<SFCPackUpdater> sorter;
+    unsigned int check_period = 1;
     std::shared_ptr<ComputeThermo> thermo;
     std::shared_ptr<ComputeThermo> thermo_nvt; // the method's own compute (hoomd/md/integrate.py:370-372)
     std::shared_ptr<TwoStepNVTMTK> nvt;
@@ -253,6 +254,7 @@ int ref_setup_lj(void* h, float r_buff, int check_period, int full_storage, cons
     unsigned int nt = s->pdata->getNTypes();
     s->cl = std::shared_ptr<CellList>(new CellList(s->sysdef));
     s->nlist = std::shared_ptr<NeighborListBinned>(new NeighborListBinned(s->sysdef, Scalar(0.0), r_buff, s->cl));
+    s->check_period = check_period;
     s->nlist->setEvery(check_period, true);
     s->nlist->setStorageMode(full_storage ? NeighborList::full : NeighborList::half);
     std::shared_ptr<PotentialPairLJ> lj(new PotentialPairLJ(s->sysdef, s->nlist));
@@ -280,6 +282,7 @@ int ref_setup_pair(void* h, int evaluator, float r_buff, int check_period, int f
     REF_TRY(s)
     s->cl = std::shared_ptr<CellList>(new CellList(s->sysdef));
     s->nlist = std::shared_ptr<NeighborListBinned>(new NeighborListBinned(s->sysdef, Scalar(0.0), r_buff, s->cl));
+    s->check_period = check_period;
     s->nlist->setEvery(check_period, true);
     s->nlist->setStorageMode(full_storage ? NeighborList::full : NeighborList::half);
     switch (evaluator)
@@ -420,6 +423,16 @@ int ref_get_nvt_reservoir_energy(void* h, float* out)
     bool mine = false;
     *out = s->nvt->getLogValue("nvt_mtk_reservoir_energy", s->timestep, mine);
     if (!mine) throw std::runtime_error("nvt_mtk_reservoir_energy is not provided by the method");
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! md.nlist.cell(dist_check=...): NeighborList::setEvery(every, dist_check) (hoomd/md/nlist.py:188-196)
+int ref_set_dist_check(void* h, int on)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->nlist->setEvery(s->check_period, on != 0);
     REF_CATCH(s, 1)
     return 0;
     }

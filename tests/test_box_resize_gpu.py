@@ -132,3 +132,26 @@ def test_errors(hb):
     s.set_box(5.0, 9.0, 9.0)  # shrunk below 2 (r_cut + r_buff): the next build must refuse, as NeighborListBinned does
     with pytest.raises(RuntimeError, match="too small"):
         s.run(5)
+
+
+@pytest.mark.parametrize("every", [0, 1, 5])
+@pytest.mark.parametrize("use_graph", [0, 2])
+def test_dist_check_off(hb, every, use_graph):
+    """md.nlist.cell(dist_check=False) (NeighborList::setEvery): the same number of list builds as the restatement in the
+    host-driven and the device-driven loop (k_decide / the last CTA of k_md_step take the period decision)"""
+    from oracle import oracle_c
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.4) ** (1.0 / 3.0), kT=1.5, seed=77)
+    o = oracle_c.OracleSystem(pos, (L, L, L), ntypes=1, vel4=vel)
+    g = hb.System(pos, (L, L, L), vel4=vel)
+    g.set_tuning(use_graph=use_graph)
+    for s in (o, g):
+        s.setup_lj(r_cut=2.5, r_buff=0.4, check_period=every)
+        s.setup_integrator(0.005)
+        s.add_nve()
+        s.run(20)
+        s.set_dist_check(False)
+        s.run(60)
+    so = o.nlist_stats()
+    assert so["updates"] + so["forced"] == _builds(g), (so, g.stats())
+    a, b = o.particles(), g.particles()
+    assert np.abs(a["pos"][:, :3] - b["pos"][np.argsort(b["tag"])][:, :3]).max() < 2e-4

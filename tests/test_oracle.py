@@ -214,3 +214,26 @@ def test_nvt_restatement_matches_reference_bitwise():
 def test_box_resize_golden_bit_exact():
     """BoxResizeUpdater + lambda-scaled distance check + cell-list re-dimensioning restated (tests/golden/box_resize.npz)"""
     G.check_box_resize(make, bit_exact=True, updates=lambda s: s.nlist_stats()["updates"])
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+@pytest.mark.parametrize("every", [0, 1, 5])
+def test_dist_check_off_matches_reference_bitwise(every):
+    """md.nlist.cell(dist_check=False): period 0 rebuilds every step, period 1 still runs the distance check, period 5
+    rebuilds when the period is hit (hoomd/md/NeighborList.cc:1126-1135).  (Switching it BETWEEN two runs forces a build:
+    the restatement and the engine do it at the current step, in prepRun's force evaluation, the reference one step later
+    because its ForceCompute skips a repeated compute(ts) -- so the switch is made before the first run here.)"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.4) ** (1.0 / 3.0), kT=1.5, seed=77)
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (L, L, L), ntypes=1, vel4=vel)
+        s.setup_lj(full=True, r_cut=2.5, r_buff=0.4, check_period=every)
+        s.setup_integrator(0.005)
+        s.add_nve()
+        s.set_dist_check(False)
+        s.run(80)
+        outs.append((s.particles(), s.nlist_stats()["updates"]))
+    (pa, ua), (pb, ub) = outs
+    for k in ("pos", "vel", "accel", "image"):
+        assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
+    assert ua == ub

@@ -322,6 +322,19 @@ def test_box_resize_script_matches_reference():
     assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 3e-3
 
 
+def test_nlist_dist_check_is_forwarded():
+    hoomd = _fresh()
+    from hoomd import md
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    nl = md.nlist.cell(check_period=5, dist_check=False)
+    assert nl.dist_check is False and nl.check_period == 5
+    nl.set_params(dist_check=True)
+    assert nl.dist_check is True
+    import inspect
+    from hoomd_b200 import script
+    assert "set_dist_check(lj.nlist.dist_check)" in inspect.getsource(script._configure_engine)
+
+
 def test_dpd_conservative_surface_without_gpu():
     hoomd = _fresh()
     from hoomd import md
