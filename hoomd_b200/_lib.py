@@ -93,7 +93,7 @@ SYMBOLS = [
     "b200_compute_thermo", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
     "b200_sys_set_accel", "b200_sys_get_particles", "b200_sys_setup_lj", "b200_sys_set_virial",
     "b200_sys_setup_integrator", "b200_sys_add_nve", "b200_sys_add_langevin", "b200_sys_set_sorter",
-    "b200_sys_set_dist_check", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
+    "b200_sys_set_dist_check", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
     "b200_sys_add_nvt", "b200_sys_get_nvt_state", "b200_sys_set_nvt_state", "b200_nvt_mtk_step_one", "b200_nvt_mtk_step_two", "b200_nvt_mtk_advance",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
     "b200_sys_set_pair_mode", "b200_sys_get_pair_mode",
@@ -203,6 +203,7 @@ def lib():
     L.b200_sys_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
     L.b200_sys_add_nvt.argtypes = [vp, C.c_float, C.c_float]
     L.b200_sys_set_dist_check.argtypes = [vp, C.c_int]
+    L.b200_sys_set_temperature.argtypes = [vp, C.c_float]
     L.b200_sys_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
     L.b200_sys_get_box.argtypes = [vp, vp]
     L.b200_sys_get_box.restype = None

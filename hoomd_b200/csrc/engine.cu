@@ -1731,6 +1731,22 @@ void b200_sys_get_box(b200_system* s, float* L3)
     for (int d = 0; d < 3; d++) L3[d] = s->box.L[d];
     }
 
+// method.set_params(kT=...) / a temperature variant evaluated by the caller once per step: TwoStepLangevinBase::setT,
+// TwoStepNVTMTK::setT.  The set point is a by-value argument of the captured kernels, so the step graph is invalidated; chunks
+// of <= 16 steps behind an invalid graph launch their kernels directly (run_chunk_device).
+int b200_sys_set_temperature(b200_system* s, float kT)
+    {
+    SYS_TRY(s)
+    if (s->method != 2 && s->method != 3) throw std::runtime_error("integrate: the active method has no temperature");
+    if (s->method == 3 && !(kT > 0.0f)) throw std::runtime_error("integrate.nvt: kT must be positive");
+    if (kT != s->kT)
+        {
+        s->kT = kT;
+        invalidate_graph(s);
+        }
+    SYS_CATCH(s)
+    }
+
 // md.nlist.cell(dist_check=...) / nlist.set_params(dist_check=...): NeighborList::setEvery(every, dist_check)
 int b200_sys_set_dist_check(b200_system* s, int on)
     {

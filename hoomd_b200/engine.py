@@ -156,6 +156,12 @@ class System:
         _lib.lib().b200_sys_get_box(self.h, _p(out))
         return out
 
+    def set_kT(self, kT):
+        """set point of the active langevin / nvt method (setT); a variant is evaluated by the caller, once per step"""
+        self._check(_lib.lib().b200_sys_set_temperature(self.h, C.c_float(kT)))
+        if hasattr(self, "_nvt"):
+            self._nvt = (np.float32(kT), self._nvt[1])
+
     def set_dist_check(self, on=True):
         """md.nlist.cell(dist_check=...): off = rebuild whenever the check period is hit"""
         self._check(_lib.lib().b200_sys_set_dist_check(self.h, int(on)))

@@ -710,6 +710,15 @@ class _Method:
         self.enabled = True
         context.current.engine_dirty = True
 
+    @property
+    def kT(self):
+        """set point at the current time step: kT may be a hoomd.variant (Scalar T = m_T->getValue(timestep))"""
+        return float(np.float32(self.kT_variant.getValue(context.current.timestep)))
+
+    @property
+    def kT_is_variable(self):
+        return not isinstance(getattr(self, "kT_variant", None), (_VariantConst, type(None)))
+
 
 class _NVE(_Method):
     """md.integrate.nve (hoomd/md/integrate.py:729)"""
@@ -733,12 +742,12 @@ class _Langevin(_Method):
         super().__init__(group)
         if dscale:
             raise RuntimeError("hoomd_b200: dscale (gamma = lambda * diameter) is out of scope")
-        self.kT, self.seed, self.noiseless_t = float(kT), int(seed), bool(noiseless_t)
+        self.kT_variant, self.seed, self.noiseless_t = _setup_variant_input(kT), int(seed), bool(noiseless_t)
         self.gamma = {}
 
     def set_params(self, kT=None, tally=None):
         if kT is not None:
-            self.kT = float(kT)
+            self.kT_variant = _setup_variant_input(kT)
             context.current.engine_dirty = True
 
     def set_gamma(self, a, gamma):
@@ -757,11 +766,11 @@ class _NVT(_Method):
 
     def __init__(self, group, kT, tau):
         super().__init__(group)
-        self.kT, self.tau = float(kT), float(tau)
+        self.kT_variant, self.tau = _setup_variant_input(kT), float(tau)
 
     def set_params(self, kT=None, tau=None):
         if kT is not None:
-            self.kT = float(kT)
+            self.kT_variant = _setup_variant_input(kT)
         if tau is not None:
             self.tau = float(tau)
         context.current.engine_dirty = True
@@ -882,6 +891,9 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
         for br in ctx.box_resizers:
             if br.enabled:
                 nxt = min(nxt, br._next(ts))
+        ramp = [m for m in ctx.integration_methods if m.enabled and m.kT_is_variable]
+        if ramp:  # a temperature variant is evaluated at every step, like m_T->getValue(timestep) in the reference
+            nxt = 1
         # System::run order within a step: analyzers, updaters, integrator (hoomd/System.cc:484-599)
         for lg in ctx.loggers:
             if ts % lg.period == 0:
@@ -892,6 +904,8 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
             if br._due(ts):
                 br._apply(ts)
                 eng = ctx.engine
+        for m in ramp:
+            eng.set_kT(np.float32(m.kT_variant.getValue(ts)))
         eng.run(nxt)
         done += nxt
     ctx.timestep = eng.timestep

@@ -422,6 +422,8 @@ B200_API int b200_sys_setup_integrator(b200_system* s, float dt);
 B200_API int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force);
 /* md.integrate.langevin(group=all, kT, seed) + set_gamma per type (gamma NULL = 1.0) */
 B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
+/* langevin / nvt set_params(kT=...), or a temperature variant evaluated by the caller per step (setT of the method) */
+B200_API int b200_sys_set_temperature(b200_system* s, float kT);
 /* md.nlist.cell(dist_check=False): rebuild when the check period is hit instead of when a particle moved r_buff/2
  * (NeighborList::setEvery(every, dist_check), hoomd/md/NeighborList.cc:1126-1135); default on */
 B200_API int b200_sys_set_dist_check(b200_system* s, int on);

@@ -1133,6 +1133,7 @@ void orc_set_dist_check(orc_system* s, int on) /* NeighborList::setEvery(every, 
     s->no_dist_check = !on;
     s->force_update = 1;
     }
+void orc_set_kT(orc_system* s, float kT) { s->kT = kT; } /* TwoStepLangevinBase::setT / TwoStepNVTMTK::setT */
 void orc_get_nvt_state(orc_system* s, float* xi_eta) { xi_eta[0] = s->nvt_xi; xi_eta[1] = s->nvt_eta; }
 float orc_get_nvt_reservoir_energy(orc_system* s) /* TwoStepNVTMTK::getLogValue, TwoStepNVTMTK.cc:82-107 */
     {

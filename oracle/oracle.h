@@ -42,6 +42,7 @@ int orc_setup_integrator(orc_system* s, float dt);
 int orc_add_nve(orc_system* s, int limit, float limit_val, int zero_force);
 int orc_add_langevin(orc_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
 void orc_set_dist_check(orc_system* s, int on);
+void orc_set_kT(orc_system* s, float kT);
 int orc_add_nvt(orc_system* s, float kT, float tau);
 int orc_set_box(orc_system* s, float Lx, float Ly, float Lz, int scale_particles);
 void orc_get_box(orc_system* s, float* L3);

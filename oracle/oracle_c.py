@@ -40,6 +40,7 @@ def lib():
         L.orc_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
         L.orc_add_nvt.argtypes = [vp, C.c_float, C.c_float]
         L.orc_set_dist_check.argtypes = [vp, C.c_int]
+        L.orc_set_kT.argtypes = [vp, C.c_float]
         L.orc_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
         L.orc_get_box.argtypes = [vp, vp]
         L.orc_get_nvt_state.argtypes = [vp, vp]
@@ -179,6 +180,9 @@ class OracleSystem:
         out = np.zeros(3, np.float32)
         lib().orc_get_box(self.h, _ptr(out))
         return out
+
+    def set_kT(self, kT):
+        lib().orc_set_kT(self.h, C.c_float(kT))
 
     def set_dist_check(self, on=True):
         lib().orc_set_dist_check(self.h, int(on))

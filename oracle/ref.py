@@ -38,6 +38,7 @@ def lib():
                                         C.c_void_p, C.c_int]
         _lib.ref_add_nvt.argtypes = [C.c_void_p, C.c_float, C.c_float]
         _lib.ref_set_dist_check.argtypes = [C.c_void_p, C.c_int]
+        _lib.ref_set_kT.argtypes = [C.c_void_p, C.c_float]
         _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
         _lib.ref_get_box.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_get_nvt_state.argtypes = [C.c_void_p, C.c_void_p]
@@ -173,6 +174,9 @@ class RefSystem:
         out = np.zeros(3, np.float32)
         lib().ref_get_box(self.h, _ptr(out))
         return out
+
+    def set_kT(self, kT):
+        self._check(lib().ref_set_kT(self.h, C.c_float(kT)))
 
     def set_dist_check(self, on=True):
         self._check(lib().ref_set_dist_check(self.h, int(on)))

@@ -427,6 +427,18 @@ int ref_get_nvt_reservoir_energy(void* h, float* out)
     return 0;
     }
 
+//! method.set_params(kT=...) / a temperature variant evaluated by the caller: setT on the active method
+int ref_set_kT(void* h, float kT)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<Variant> T(new VariantConst(kT));
+    if (s->langevin) s->langevin->setT(T);
+    if (s->nvt) s->nvt->setT(T);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
 //! md.nlist.cell(dist_check=...): NeighborList::setEvery(every, dist_check) (hoomd/md/nlist.py:188-196)
 int ref_set_dist_check(void* h, int on)
     {

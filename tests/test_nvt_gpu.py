@@ -164,3 +164,29 @@ def test_errors(hb):
         s.add_nvt(0.0, 0.5)
     with pytest.raises(RuntimeError):
         s.nvt_state()
+
+
+@pytest.mark.parametrize("method", ["langevin", "nvt"])
+def test_temperature_ramp(hb, oc, method):
+    """b200_sys_set_temperature once per step (what a hoomd.variant set point amounts to) against the restatement"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.4) ** (1.0 / 3.0), kT=2.0, seed=5)
+    o = oc.OracleSystem(pos, (L, L, L), ntypes=1, vel4=vel)
+    g = hb.System(pos, (L, L, L), vel4=vel)
+    for s in (o, g):
+        s.setup_lj(r_cut=2.5, r_buff=0.4)
+        s.setup_integrator(0.005)
+        s.add_langevin(2.0, 11) if method == "langevin" else s.add_nvt(2.0, 0.4)
+        for ts in range(60):
+            s.set_kT(np.float32(2.0 - 1.2 * ts / 60.0))
+            s.run(1)
+    a, b = o.particles(), g.particles()
+    assert np.abs(a["pos"][:, :3] - b["pos"][:, :3]).max() < 2e-4
+    assert np.abs(a["vel"][:, :3] - b["vel"][:, :3]).max() < 2e-3
+    if method == "nvt":
+        assert np.allclose(o.nvt_state(), g.nvt_state(), rtol=2e-5, atol=1e-7)
+    with pytest.raises(RuntimeError):
+        n = hb.System(pos, (L, L, L), vel4=vel)
+        n.setup_lj(r_cut=2.5, r_buff=0.4)
+        n.setup_integrator(0.005)
+        n.add_nve()
+        n.set_kT(1.0)

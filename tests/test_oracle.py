@@ -237,3 +237,22 @@ def test_dist_check_off_matches_reference_bitwise(every):
     for k in ("pos", "vel", "accel", "image"):
         assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
     assert ua == ub
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libhoomd_ref.so not built")
+@pytest.mark.parametrize("method", ["langevin", "nvt"])
+def test_temperature_ramp_matches_reference_bitwise(method):
+    """a temperature variant = setT with the value of every step (Scalar T = m_T->getValue(timestep))"""
+    pos, vel, L = workloads.sc_lattice(9, (1.0 / 0.4) ** (1.0 / 3.0), kT=2.0, seed=5)
+    outs = []
+    for cls in (ref.RefSystem, oracle_c.OracleSystem):
+        s = cls(pos, (L, L, L), ntypes=1, vel4=vel)
+        s.setup_lj(full=True, r_cut=2.5, r_buff=0.4)
+        s.setup_integrator(0.005)
+        s.add_langevin(2.0, 11) if method == "langevin" else s.add_nvt(2.0, 0.4)
+        for ts in range(60):
+            s.set_kT(np.float32(2.0 - 1.2 * ts / 60.0))
+            s.run(1)
+        outs.append(s.particles())
+    for k in ("pos", "vel", "accel", "image"):
+        assert np.array_equal(outs[0][k].view(np.uint32), outs[1][k].view(np.uint32)), k

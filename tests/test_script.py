@@ -349,3 +349,50 @@ def test_dpd_conservative_surface_without_gpu():
     from hoomd_b200 import _lib
     p = _lib.pair_params("dpd_conservative", 1, A=25.0)
     assert p.shape == (1, 1, 4) and p[0, 0, 0] == 25.0 and p[0, 0, 1] == 0.0  # (A, gamma = 0)
+
+
+def test_temperature_variant_surface_without_gpu():
+    hoomd = _fresh()
+    from hoomd import md
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    ramp = hoomd.variant.linear_interp([(0, 2.0), (100, 1.0)])
+    lv = md.integrate.langevin(group=hoomd.group.all(), kT=ramp, seed=1)
+    assert lv.kT == 2.0 and lv.kT_is_variable
+    lv.set_params(kT=1.5)
+    assert lv.kT == 1.5 and not lv.kT_is_variable
+    lv.disable()
+    nvt = md.integrate.nvt(group=hoomd.group.all(), kT=ramp, tau=0.5)
+    assert nvt.kT_is_variable and nvt.kT == 2.0
+
+
+@pytest.mark.gpu
+def test_temperature_ramp_script_matches_reference():
+    """md.integrate.langevin(kT=variant.linear_interp(...)): the set point follows the variant step by step"""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    from hoomd_b200 import workloads
+    hoomd = _fresh()
+    from hoomd import md
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=1.6, type_name="A"), n=9)
+    nl = md.nlist.cell()
+    lj = md.pair.lj(r_cut=2.5, nlist=nl)
+    lj.pair_coeff.set("A", "A", epsilon=1.0, sigma=1.0)
+    md.integrate.mode_standard(dt=0.005)
+    md.integrate.langevin(group=hoomd.group.all(), kT=hoomd.variant.linear_interp([(0, 2.0), (50, 0.8)]), seed=3)
+    hoomd.run(60)
+    snap = hoomd.context.current.system.take_snapshot()
+    pos, vel, L = workloads.sc_lattice(9, 1.6)
+    r = R.RefSystem(pos, (L, L, L), vel4=vel)
+    r.setup_lj(r_cut=2.5, r_buff=0.4, full=True)
+    r.setup_integrator(0.005)
+    r.add_langevin(2.0, 3)
+    r.set_sorter(300)
+    for ts in range(60):
+        f = min(ts, 50) / 50.0
+        r.set_kT(np.float32((1.0 - f) * 2.0 + f * 0.8))
+        r.run(1)
+    a = r.particles()
+    order = np.argsort(a["tag"])
+    assert np.abs(a["pos"][order][:, :3] - snap.particles.position).max() < 2e-4
+    assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
