@@ -788,14 +788,30 @@ analyze = types.ModuleType("hoomd.analyze")
 class _Log:
     QUANTITIES = {"temperature": "T", "kinetic_energy": "ke", "potential_energy": "pe", "pressure": "P"}
 
-    def __init__(self, filename=None, quantities=(), period=1, **kw):
+    def __init__(self, filename=None, quantities=(), period=1, header_prefix="", overwrite=False, phase=0, **kw):
         _require_context()
         for q in quantities:
             if q not in self.QUANTITIES and q not in ("pair_lj_energy", "nvt_mtk_reservoir_energy_all"):
                 raise RuntimeError("Unknown log quantity " + q)
         self.quantities, self.period, self.filename, self.rows = list(quantities), int(period), filename, []
+        self.header_prefix, self.overwrite, self._opened = header_prefix, bool(overwrite), False
         context.current.loggers.append(self)
         context.current.engine_dirty = True
+
+    def _write(self, row):
+        """plain-text log file in the reference's format (hoomd/LogPlainTXT.cc:100-195): tab-delimited, a header line for a
+        new file, values with 10 significant digits; an existing file is appended to unless overwrite is set"""
+        if self.filename is None:
+            return
+        import os
+        if not self._opened:
+            new = self.overwrite or not os.path.exists(self.filename)
+            with open(self.filename, "w" if new else "a") as f:
+                if new:
+                    f.write(self.header_prefix + "\t".join(["timestep"] + self.quantities) + "\n")
+            self._opened = True
+        with open(self.filename, "a") as f:
+            f.write("\t".join(["%d" % row[0]] + ["%.10g" % v for v in row[1:]]) + "\n")
 
     def query(self, quantity):
         if quantity == "nvt_mtk_reservoir_energy_all":  # provided by md.integrate.nvt (log name + "_" + group name)
@@ -898,6 +914,7 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
         for lg in ctx.loggers:
             if ts % lg.period == 0:
                 lg.rows.append([ts] + [lg.query(q) for q in lg.quantities])
+                lg._write(lg.rows[-1])
         if callback and callback_period and ts % callback_period == 0:
             callback(ts)
         for br in ctx.box_resizers:

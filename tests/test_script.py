@@ -396,3 +396,23 @@ def test_temperature_ramp_script_matches_reference():
     order = np.argsort(a["tag"])
     assert np.abs(a["pos"][order][:, :3] - snap.particles.position).max() < 2e-4
     assert np.abs(a["vel"][order][:, :3] - snap.particles.velocity).max() < 2e-3
+
+
+def test_log_file_format(tmp_path):
+    """analyze.log writes the reference's plain-text format (hoomd/LogPlainTXT.cc): header for a new file, tab-delimited
+    rows with 10 significant digits, appending to an existing file unless overwrite=True"""
+    hoomd = _fresh()
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    fn = str(tmp_path / "log.txt")
+    lg = hoomd.analyze.log(filename=fn, quantities=["temperature", "potential_energy"], period=10, header_prefix="#")
+    lg._write([0, 1.25, -3.0])
+    lg._write([10, 1.0 / 3.0, 2.5e-7])
+    lines = open(fn).read().splitlines()
+    assert lines[0] == "#timestep\ttemperature\tpotential_energy"
+    assert lines[1] == "0\t1.25\t-3" and lines[2] == "10\t0.3333333333\t2.5e-07"
+    lg2 = hoomd.analyze.log(filename=fn, quantities=["temperature"], period=10)
+    lg2._write([20, 2.0])
+    assert open(fn).read().splitlines()[-1] == "20\t2" and len(open(fn).read().splitlines()) == 4
+    lg3 = hoomd.analyze.log(filename=fn, quantities=["temperature"], period=10, overwrite=True)
+    lg3._write([0, 1.0])
+    assert open(fn).read().splitlines() == ["timestep\ttemperature", "0\t1"]
