@@ -90,7 +90,7 @@ SYMBOLS = [
     "b200_sys_get_force_component",
     "b200_integrator_sum_net_force", "b200_nve_step_one", "b200_nve_step_two", "b200_langevin_hash_seed",
     "b200_langevin_step_two", "b200_saru_draw", "b200_sfc_generate_sorted_order", "b200_sfc_apply_sorted_order",
-    "b200_compute_thermo", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
+    "b200_compute_thermo", "b200_compute_thermo_static", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
     "b200_sys_set_accel", "b200_sys_get_particles", "b200_sys_setup_lj", "b200_sys_set_virial",
     "b200_sys_setup_integrator", "b200_sys_add_nve", "b200_sys_add_langevin", "b200_sys_set_sorter",
     "b200_sys_set_dist_check", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
@@ -186,6 +186,7 @@ def lib():
                                                  C.POINTER(Box), C.c_uint, vp]
     L.b200_sfc_apply_sorted_order.argtypes = [C.POINTER(PDataArrays), C.POINTER(PDataArrays), vp, vp, C.c_uint, vp]
     L.b200_compute_thermo.argtypes = [vp, vp, C.c_uint, vp, vp, vp, C.c_uint, vp, C.c_uint, vp]
+    L.b200_compute_thermo_static.argtypes = [vp, C.c_uint, vp, vp, vp, C.c_uint, vp, C.c_uint, vp]
     # engine
     L.b200_sys_create.argtypes = [C.c_uint, C.POINTER(Box), C.c_uint, C.c_int]
     L.b200_sys_create.restype = vp

@@ -6,6 +6,8 @@
 #include "common.cuh"
 #include "integrate_body.cuh"
 #include "kernels.h"
+#include <cstdio>
+#include <mutex>
 
 namespace b200
 {
@@ -433,3 +435,64 @@ int b200_compute_thermo(double* d_out, double* d_partial, unsigned int n_partial
     }
 
 } // extern "C"
+
+// ---- ComputeThermo without any allocation (no counterpart in the reference; see include/hoomd_b200.h) ---------------------
+// The per-CTA partial sums of k_thermo_partial live in a file-scope __device__ array instead of a caller buffer.  In host
+// code the array's NAME is only a stand-in for the symbol: the device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and cached; the kernels get the looked-up pointer.
+namespace b200
+{
+static __device__ __align__(256) double g_thermo_static_scratch[B200_THERMO_STATIC_MAX_BLOCKS * TH_NQ];
+constexpr int THERMO_STATIC_MAX_DEVICES = 64;
+static double* g_thermo_static_ptr[THERMO_STATIC_MAX_DEVICES] = {nullptr};
+static std::mutex g_thermo_static_mutex;
+
+// device address of the scratch array on the CURRENT device (set-up: first call per device)
+static cudaError_t thermo_static_scratch(double** out)
+    {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= THERMO_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_thermo_static_mutex);
+    if (!g_thermo_static_ptr[dev])
+        {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_thermo_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_thermo_static_ptr[dev] = (double*)p;
+        }
+    *out = g_thermo_static_ptr[dev];
+    return cudaSuccess;
+    }
+} // namespace b200
+
+extern "C" int b200_compute_thermo_static(double* d_out, unsigned int n_partial_blocks, const float* d_vel,
+                                          const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                                          const unsigned int* d_group_members, unsigned int group_size,
+                                          b200_stream_t stream_)
+    {
+    using namespace b200;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n_partial_blocks == 0 || n_partial_blocks > B200_THERMO_STATIC_MAX_BLOCKS)
+        {
+        fprintf(stderr, "b200_compute_thermo_static: n_partial_blocks = %u is outside [1, %u] (the built-in scratch array "
+                        "holds %u partial sums); use b200_compute_thermo with a caller buffer for more\n",
+                n_partial_blocks, (unsigned int)B200_THERMO_STATIC_MAX_BLOCKS, (unsigned int)B200_THERMO_STATIC_MAX_BLOCKS);
+        return (int)cudaErrorInvalidValue;
+        }
+    double* scratch = nullptr;
+    const cudaError_t e = thermo_static_scratch(&scratch);
+    if (e != cudaSuccess)
+        {
+        fprintf(stderr, "b200_compute_thermo_static: cudaGetSymbolAddress of the scratch array failed: %s\n",
+                cudaGetErrorString(e));
+        return (int)e;
+        }
+    // every partial row [0, n_partial_blocks) is overwritten by pass 1 before pass 2 reads it: nothing has to start at zero,
+    // rows beyond n_partial_blocks (left by an earlier, larger call) are never read
+    k_thermo_partial<<<n_partial_blocks, 256, 0, stream>>>(scratch, (const float4*)d_vel, (const float4*)d_net_force,
+                                                          d_net_virial, virial_pitch, d_group_members, group_size);
+    k_thermo_final<<<1, 32, 0, stream>>>(d_out, scratch, n_partial_blocks);
+    return (int)cudaGetLastError();
+    }

@@ -374,6 +374,23 @@ B200_API int b200_compute_thermo(double* d_out, double* d_partial, unsigned int 
                                  const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
                                  const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream);
 
+/* b200_compute_thermo WITHOUT a caller scratch buffer and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels, same fixed summation order => the same bits as
+ * b200_compute_thermo with the same n_partial_blocks.  The partial sums live in a file-scope `static __device__` array of
+ * B200_THERMO_STATIC_MAX_BLOCKS x 9 doubles (72 KiB, held by every GPU that loads the library until the process exits);
+ * its device address is looked up with cudaGetSymbolAddress on the first call per device (with that device current --
+ * make that first call outside a stream capture).  The call itself launches two kernels on `stream` and calls no
+ * cudaMalloc / cudaFree / allocating library routine.  n_partial_blocks outside [1, B200_THERMO_STATIC_MAX_BLOCKS] is
+ * rejected: cudaErrorInvalidValue (1) and a message on stderr.  EVERY call on a device shares the one array (it keeps the
+ * last call's partial sums; every row that is read is overwritten first, so nothing needs clearing): calls that overlap
+ * on the GPU -- different streams, different host threads -- race; calls ordered on one stream are safe. */
+#define B200_THERMO_STATIC_MAX_BLOCKS 1024u
+B200_API int b200_compute_thermo_static(double* d_out, unsigned int n_partial_blocks, const float* d_vel,
+                                        const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                                        const unsigned int* d_group_members, unsigned int group_size,
+                                        b200_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * ENGINE: device-resident system with the reference's object graph and step semantics
  * ------------------------------------------------------------------------------------------------------------- */
