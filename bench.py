@@ -4,11 +4,18 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload lj64k|lj1m|ka256k|lj8m]
 
 One bench "step" = one System::run of --md-steps MD timesteps (NVE, LJ r_cut 3.0, r_buff 0.4, dt 0.005) of the synthetic
-LJ liquid (N = 64,000, rho = 0.2, lattice start, Langevin-equilibrated with this engine).
+LJ liquid (N = 64,000, rho = 0.2).  BOTH arms start from the same equilibrated snapshot
+tests/golden/lj64k_equil.npz (made by the unmodified reference: lattice start + 10,000 Langevin steps,
+tests/golden/make_lj64k_equil.py).
 `value` = MD timesteps / second with the state resident in HBM (CUDA events on the engine stream);
 `e2e` = the same through the public host-buffer API (hoomd_b200.System: set_particles H2D, run, particles()+thermo D2H).
+N > 1 (torchrun): BASELINE configs[4], LJ liquid 8M particles domain-decomposed over the N GPUs; before timing every rank
+takes part in a 64k parity pass against the reference's CPU classes (tests/mg_check.py:parity_pass) whose result rides in
+the line (parity_checked, max_force_err); rank 0 also measures the same 8M system on ONE GPU with the same protocol, so
+`strong_scaling.efficiency` = tps_N / (N * tps_1) is reproducible from the record.
 --impl reference times the reference's own CPU classes (oracle/_ref, HOOMD-blue 2.3.0 SINGLE_PRECISION, serial: the MD
-CPU path has no threading and there is no MPI on the box) on a bounded sample of the same workload.
+CPU path has no threading and there is no MPI on the box) on a bounded sample of the same workload; it never loads
+libhoomd_b200.so.
 """
 import argparse
 import json
@@ -32,10 +39,58 @@ WORKLOADS = {
     # BASELINE configs[3]: 10,000 chains x 100 beads, WCA (LJ r_cut 2^(1/6), shift) + FENE (K 30, r0 1.5), bond exclusions
     "kg1m": (100, 0.85, 1.0, "Kremer-Grest polymer melt 1,000,000 beads (10,000 x 100), rho 0.85, WCA + FENE, r_buff 0.4, "
                              "NVE dt 0.005"),
-    # BASELINE configs[2]: 80:20 binary mixture (64^3 = 262,144 particles, the closest cube to 256k), per-pair r_cut, Langevin
-    "ka256k": (64, 1.2, 1.0, "Kob-Andersen 80:20 binary LJ 262,144 particles, rho 1.2, r_cut 2.5 sigma_ab (shifted), r_buff 0.4, "
+    # BASELINE configs[2]: 80:20 binary mixture, 256,000 particles (fcc 40^3 start), per-pair r_cut, Langevin
+    "ka256k": (40, 1.2, 1.0, "Kob-Andersen 80:20 binary LJ 256,000 particles, rho 1.2, r_cut 2.5 sigma_ab (shifted), r_buff 0.4, "
                              "Langevin kT 1.0 dt 0.005"),
 }
+EQUIL_SNAPSHOT = os.path.join(ROOT, "tests", "golden", "lj64k_equil.npz")
+
+
+def workloads_module():
+    """hoomd_b200/workloads.py (pure numpy) loaded by path: the reference arm must not import the hoomd_b200 package"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_b200_workloads", os.path.join(ROOT, "hoomd_b200", "workloads.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def n_particles(workload):
+    n_side = WORKLOADS[workload][0]
+    return 4 * n_side ** 3 if workload.startswith("ka") else n_side ** 3
+
+
+def default_md_steps(N):
+    return 2000 if N <= 100000 else (400 if N <= 2000000 else 200)
+
+
+def make_config(workload, world, grid=None):
+    """the `config` both arms print (what is measured, not how one arm runs it)"""
+    N = n_particles(workload)
+    if world > 1 and grid is None:
+        L = (N / WORKLOADS[workload][1]) ** (1.0 / 3.0)
+        # DomainDecomposition::findDecomposition for a cube (hoomd/DomainDecomposition.cc:323-372): pure arithmetic
+        best, area = None, None
+        for nx in range(1, world + 1):
+            for ny in range(1, world // nx + 1):
+                nz = world // (nx * ny)
+                if nx * ny * nz != world:
+                    continue
+                a = L * L * ((nz - 1) + (ny - 1) + (nx - 1))
+                if area is None or a < area:
+                    best, area = (nx, ny, nz), a
+        grid = best
+    return {"workload": WORKLOADS[workload][3], "N": N,
+            "parallelism": "1 domain" if world == 1 else
+            "spatial domain decomposition %s over %d GPUs, ghosts + migration over NVLink peer memory" % (
+                "x".join(str(g) for g in grid), world),
+            "start_state": ("equilibrated snapshot tests/golden/lj64k_equil.npz (made by the reference: sc lattice + 10,000 "
+                            "Langevin steps kT 1.2)") if workload == "lj64k" else
+            "lattice start, Gaussian velocities (numpy default_rng(42)); the CUDA arm melts it first (untimed)",
+            "l2": "L2 flushed (256 MiB write) between timed iterations" + (
+                "; within an iteration the 64k working set is L2-resident, which is the workload"
+                if N <= 100000 else "; per-GPU working set exceeds L2"),
+            "nlist": {"r_buff": 0.4, "check_period": 1}}
 KG_CHAIN = 100
 
 
@@ -114,23 +169,27 @@ USE_GRAPH = int(os.environ.get("HOOMD_B200_USE_GRAPH", "2"))  # 0 host-driven, 1
 
 
 def _lj_snapshot(workload):
-    from hoomd_b200 import workloads
     n_side, rho, kT, _ = WORKLOADS[workload]
-    return workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
+    return workloads_module().sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42)
 
 
 def _snapshot(workload):
     """(pos4, vel4, L, bonds or None)"""
-    from hoomd_b200 import workloads
+    workloads = workloads_module()
     n_side, rho, kT, _ = WORKLOADS[workload]
     if workload.startswith("kg"):
         return workloads.polymer_lattice(n_side, KG_CHAIN, rho=rho, kT=kT, seed=42)
     if workload.startswith("ka"):
-        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=42, ntypes=2,
-                                           type_fractions=[0.8, 0.2])
-        pos[:, :3] += np.random.default_rng(3).normal(0, 0.03, (len(pos), 3)).astype(np.float32)
+        pos, vel, L = workloads.fcc_lattice(n_side, rho, kT=kT, seed=42, ntypes=2, type_fractions=[0.8, 0.2])
         return pos, vel, L, None
     return _lj_snapshot(workload) + (None,)
+
+
+def load_equil_snapshot():
+    """the 64k start state of both arms (tag order)"""
+    g = np.load(EQUIL_SNAPSHOT)
+    return dict(pos=np.ascontiguousarray(g["pos"]), vel=np.ascontiguousarray(g["vel"]),
+                image=np.ascontiguousarray(g["image"].astype(np.int32)), bonds=None), float(g["L"])
 
 
 def setup_forces(s, workload, bonds, **kw):
@@ -141,14 +200,16 @@ def setup_forces(s, workload, bonds, **kw):
         s.setup_fene(k=30.0, r0=1.5)
         s.exclusions_from_bonds(True)
     elif workload.startswith("ka"):
-        from hoomd_b200 import workloads
-        s.setup_lj(shift_mode=1, r_buff=0.4, **workloads.KA_PARAMS, **kw)
+        s.setup_lj(shift_mode=1, r_buff=0.4, **workloads_module().KA_PARAMS, **kw)
     else:
         s.setup_lj(r_cut=3.0, r_buff=0.4, **kw)
 
 
 def make_state(workload, rank=0):
-    """Lattice start + Langevin equilibration ON THE GPU ENGINE (not timed); returns host arrays + box length."""
+    """lj64k: the committed equilibrated snapshot.  Other workloads: lattice start + Langevin equilibration ON THE GPU
+    ENGINE (not timed); returns host arrays + box length."""
+    if workload == "lj64k" and EQUIL_STEPS is None:
+        return load_equil_snapshot()
     import hoomd_b200
     _, _, kT, _ = WORKLOADS[workload]
     pos, vel, L, bonds = _snapshot(workload)
@@ -205,23 +266,20 @@ def new_domain_system(workload, local_rank):
 
 
 def run_reference(args):
-    """reference arm: the reference's own CPU classes on the box's host cores, bounded sample per step."""
+    """reference arm: the reference's own CPU classes on the box's host cores, bounded sample per step.  Never imports the
+    hoomd_b200 package / loads libhoomd_b200.so: the 64k start state is the committed snapshot, other workloads start from
+    the lattice."""
     from oracle import ref, oracle_c
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    workload = args.workload or "lj64k"
+    workload = args.workload or ("lj64k" if world == 1 else "lj8m")  # the same choice as the CUDA arm
     n_side, rho, kT, desc = WORKLOADS[workload]
-    from hoomd_b200 import workloads
-    md_steps = args.ref_md_steps
-    have_gpu = False
-    try:
-        import torch
-        have_gpu = torch.cuda.is_available()
-    except Exception:
-        pass
-    if have_gpu:
-        state, L = make_state(workload)  # same equilibrated liquid as the CUDA arm (equilibration is not timed)
+    N = n_particles(workload)
+    md_steps = args.ref_md_steps or (20 if N <= 100000 else (2 if N <= 2000000 else 1))
+    if workload == "lj64k":
+        state, L = load_equil_snapshot()
     else:
         pos, vel, L, bonds = _snapshot(workload)
         state = dict(pos=pos, vel=vel, image=np.zeros((len(pos), 3), np.int32), bonds=bonds)
@@ -249,14 +307,14 @@ def run_reference(args):
         t.append(time.perf_counter() - t0)
     total = sum(t)
     tps = md_steps * args.steps / total
-    N = len(state["pos"])
     sample = "%d MD steps per bench step x %d steps of the %d-particle workload, %s" % (
         md_steps, args.steps, N, "HOOMD-blue 2.3.0 CPU classes (oracle/_ref), half neighbor list, 1 core (no MPI on the box)"
         if kind == "reference" else "C restatement (oracle/oracle.c) with OpenMP")
     line = {"impl": "reference", "metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "md_steps_per_step": md_steps, "N": N},
+            "config": make_config(workload, world),
+            "md_steps_per_step": md_steps,
             "particle_steps_per_sec": tps * N,
             "cpu_baseline": {"value": tps, "unit": "timesteps/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": tps, "unit": "timesteps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -306,10 +364,12 @@ def main():
                     help="default: lj64k on 1 GPU (BASELINE configs[1]), lj8m domain-decomposed on N > 1 (configs[4])")
     ap.add_argument("--no-scale-ref", action="store_true", help="skip the 1-GPU 8M-particle reference point")
     ap.add_argument("--md-steps", type=int, default=0, help="MD timesteps per bench step (0 = by workload)")
-    ap.add_argument("--ref-md-steps", type=int, default=20)
+    ap.add_argument("--ref-md-steps", type=int, default=0, help="MD timesteps per bench step of the reference arm (0 = by size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--equil-steps", type=int, default=None)
     ap.add_argument("--no-flush", action="store_true", help="profiling only: skip the L2 flush between timed iterations")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the parity pass against the reference classes")
+    ap.add_argument("--parity-steps", type=int, default=100, help="NVE steps of the N > 1 parity pass")
     args = ap.parse_args()
     global EQUIL_STEPS
     EQUIL_STEPS = args.equil_steps
@@ -331,9 +391,74 @@ def main():
 
     workload = args.workload or ("lj64k" if world == 1 else "lj8m")
     n_side, rho, kT, desc = WORKLOADS[workload]
-    N = n_side ** 3
-    md_steps = args.md_steps or (2000 if N <= 100000 else (400 if N <= 2000000 else 200))
+    N = n_particles(workload)
+    md_steps = args.md_steps or default_md_steps(N)
     hbm_peak, peak_src = peaks()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+
+    def barrier(collective=True):
+        torch.cuda.synchronize()
+        if world > 1 and collective:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def measure(sys_, steps_per_run, collective=True):
+        """W untimed warm-up runs, then K timed runs bracketed by barrier + synchronize; CUDA-event milliseconds per run on
+        the engine stream, summed and (domain-decomposed) taken as the max over ranks"""
+        for _ in range(args.warmup):
+            sys_.run(steps_per_run)
+        barrier(collective)
+        ms_runs, n_launch = [], 0
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            if not args.no_flush:
+                flush.fill_(1)       # evict L2 between timed iterations (the 15 MB working set re-warms in < 1 MD step)
+                torch.cuda.synchronize()
+            _, ms = sys_.run(steps_per_run)
+            ms_runs.append(ms)
+            n_launch += sys_.stats()["kernels_last_run"]
+        barrier(collective)
+        wall = time.perf_counter() - t0
+        tot = sum(ms_runs)
+        if world > 1 and collective:
+            t = torch.tensor([tot], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            tot = float(t.item())
+        return tot, ms_runs, n_launch, wall
+
+    def measure_e2e(sys_, steps_per_run, collective=True):
+        """the same through the host-buffer API: H2D of the step's inputs, run, D2H of the result, every bench step"""
+        host = sys_.particles()
+        e2e_t, h2d, d2h, th = [], 0, 0, None
+        for it in range(max(1, args.steps)):
+            t0 = time.perf_counter()
+            sys_.set_particles(host["pos"], host["vel"], host["image"])     # H2D of the step's inputs
+            sys_.run(steps_per_run)
+            host = sys_.particles()                                          # D2H of the step's result
+            th = sys_.thermo()
+            e2e_t.append(time.perf_counter() - t0)
+            h2d = host["pos"].nbytes + host["vel"].nbytes + host["image"].nbytes
+            d2h = sum(host[k].nbytes for k in host) + 5 * 8
+        tot = sum(e2e_t)
+        if world > 1 and collective:
+            t = torch.tensor([tot], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            tot = float(t.item())
+        return {"value": steps_per_run * len(e2e_t) / tot, "unit": "timesteps/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "thermo_T": th["T"], "ms_runs": [1e3 * x for x in e2e_t]}
+
+    # ---- N > 1: parity of the domain-decomposed path against the reference's CPU classes, before anything is timed -------
+    parity = None
+    if world > 1 and not args.no_parity:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import mg_check
+        st64, L64 = load_equil_snapshot()
+        parity = mg_check.parity_pass(st64["pos"], st64["vel"], st64["image"], L64, args.parity_steps, local_rank,
+                                      check_ghosts=False, verbose=False)
+        parity.pop("mg_stats", None)
+        parity["workload"] = ("LJ liquid 64,000 (tests/golden/lj64k_equil.npz) on the same %d-GPU decomposition vs HOOMD-blue "
+                              "2.3.0 CPU classes: forces / energies within 1e-5 of sum|pair terms|, neighbor-list row lengths "
+                              "equal, %d NVE steps with equal rebuild counts" % (world, args.parity_steps))
 
     if world == 1:
         state, L = make_state(workload, rank)
@@ -341,37 +466,12 @@ def main():
     else:
         state = None
         s, L = new_domain_system(workload, local_rank)
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     # ---- device-resident throughput ---------------------------------------------------------------------------------
-    for _ in range(args.warmup):
-        s.run(md_steps)
     sampler = ClockSampler(local_rank)
-    barrier()
     sampler.start()
-    gpu_ms, launches = [], 0
-    t_wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        if not args.no_flush:
-            flush.fill_(1)           # evict L2 between timed iterations (the 15 MB working set re-warms in < 1 MD step)
-            torch.cuda.synchronize()
-        _, ms = s.run(md_steps)
-        gpu_ms.append(ms)
-        launches += s.stats()["kernels_last_run"]
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
+    total_ms, gpu_ms, launches, t_wall = measure(s, md_steps)
     clocks = sampler.stop()
-    total_ms = sum(gpu_ms)
-    if world > 1:
-        t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
     tps_rank = md_steps * args.steps / (total_ms * 1e-3)
     tps = tps_rank  # one domain-decomposed system: every rank advances the same timesteps
     stats = s.stats()
@@ -418,79 +518,78 @@ def main():
                         "per-rank figures (local particles of rank 0)"}
 
     # ---- end to end through the host-buffer API ----------------------------------------------------------------------
-    host = s.particles()
-    e2e_t, h2d, d2h = [], 0, 0
-    for it in range(max(1, args.steps)):
-        t0 = time.perf_counter()
-        s.set_particles(host["pos"], host["vel"], host["image"])         # H2D of the step's inputs
-        s.run(md_steps)
-        host = s.particles()                                              # D2H of the step's result
-        th = s.thermo()
-        e2e_t.append(time.perf_counter() - t0)
-        h2d = host["pos"].nbytes + host["vel"].nbytes + host["image"].nbytes
-        d2h = sum(host[k].nbytes for k in host) + 5 * 8
-    e2e_tps = md_steps * len(e2e_t) / sum(e2e_t)
-    if world > 1:
-        t = torch.tensor([sum(e2e_t)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_tps = md_steps * len(e2e_t) / float(t.item())
+    e2e = measure_e2e(s, md_steps)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(state, L, workload=workload)
 
-    # 1-GPU reference point of the multi-GPU workload (BASELINE configs[4]: parallel efficiency = TPS_n / (n * TPS_1)
-    # with TPS_1 measured at 8M on one GPU), short run, reported beside the headline
-    scale_ref = None
     mg_stats = None
-    if world == 1 and workload == "lj64k" and not args.no_scale_ref:
-        s.close()
-        s = None
-        st8, L8 = make_state("lj8m")
-        s8 = new_system(st8, L8, device=local_rank)
-        s8.run(200)
-        ms8 = min(s8.run(200)[1] for _ in range(2))
-        scale_ref = {"workload": WORKLOADS["lj8m"][3], "n_gpus": 1, "value": 200.0 / (ms8 * 1e-3), "unit": "timesteps/s",
-                     "particle_steps_per_sec": 200.0 / (ms8 * 1e-3) * 8e6, "md_steps": 200,
-                     "k_md_step_ms": s8.time_kernel(2, 10), "nlist_rebuild_ms": s8.time_kernel(1, 5)}
-        s8.close()
     if world > 1:
         mg_stats = s.mg_stats()
         mg_stats["grid"] = list(s.grid)
+    s.close()
+    s = None
+
+    # ---- the 1-GPU point of the multi-GPU workload (BASELINE configs[4]: parallel efficiency = TPS_n / (n * TPS_1) with
+    # TPS_1 measured at 8M on one GPU), SAME protocol as the N > 1 runs (warm-up W, K x md_steps, sum of the
+    # CUDA-event times, e2e).  At N = 1 it rides beside the 64k headline as `scale_ref`; at N > 1 rank 0 measures it on its
+    # own GPU after the timed region (the other ranks wait), so every line carries its own denominator.
+    scale_ref, strong = None, None
+    want_ref = (world == 1 and workload == "lj64k") or (world > 1 and workload == "lj8m")
+    if want_ref and not args.no_scale_ref:
+        if rank == 0:
+            st8, L8 = make_state("lj8m")
+            s8 = new_system(st8, L8, device=local_rank, workload="lj8m")
+            md8 = default_md_steps(n_particles("lj8m"))
+            tot8, ms8, _, _ = measure(s8, md8, collective=False)
+            tps8 = md8 * args.steps / (tot8 * 1e-3)
+            scale_ref = {"workload": WORKLOADS["lj8m"][3], "n_gpus": 1, "value": tps8, "unit": "timesteps/s",
+                         "particle_steps_per_sec": tps8 * 8e6, "md_steps_per_step": md8, "steps": args.steps,
+                         "warmup": args.warmup, "ms_runs": ms8, "k_md_step_ms": s8.time_kernel(2, 10),
+                         "nlist_rebuild_ms": s8.time_kernel(1, 5),
+                         "e2e": measure_e2e(s8, md8, collective=False)}
+            s8.close()
+            if world > 1:
+                strong = {"workload": "lj8m", "tps_1": tps8, "tps_n": tps, "n": world, "efficiency": tps / (world * tps8),
+                          "e2e_efficiency": e2e["value"] / (world * scale_ref["e2e"]["value"]),
+                          "how": "tps_1: the same 8M-particle system on ONE GPU (rank 0's, after the timed region), same "
+                                 "warm-up / steps / md_steps protocol; efficiency = tps_n / (n * tps_1)"}
+        if world > 1:
+            dist.barrier()
 
     if rank == 0:
+        cfg = make_config(workload, world, mg_stats["grid"] if mg_stats else None)
+        if METHOD_OVERRIDE:
+            cfg["workload"] += " [integration method overridden: %s]" % METHOD_OVERRIDE
         line = {"metric": "timesteps/sec", "value": tps, "unit": "timesteps/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": desc + (" [integration method overridden: %s]" % METHOD_OVERRIDE
-                                               if METHOD_OVERRIDE else ""), "N": N, "md_steps_per_step": md_steps,
-                           "parallelism": "1 GPU" if world == 1 else
-                           "spatial domain decomposition %s, ghosts + migration over NVLink peer memory" % (
-                               "x".join(str(g) for g in mg_stats["grid"])),
-                           "l2": "L2 flushed (256 MiB write) between timed iterations" + (
-                               "; within an iteration the 64k working set is L2-resident, which is the workload"
-                               if N <= 100000 else "; per-GPU working set exceeds L2"),
-                           "sorter_period": 300,
+                "config": cfg,
+                "md_steps_per_step": md_steps,
+                "engine": {"sorter_period": 300,
                            "stepping": {0: "host-driven", 1: "CUDA graph, early-exit rebuild kernels",
                                         2: "CUDA graph, conditional IF node",
                                         3: "stream launches of the graph kernels"}[USE_GRAPH],
-                           "nlist": {"r_buff": 0.4, "check_period": 1,
-                                     "rebuilds_total": stats["updates"] + stats["forced"], "Nmax": stats["Nmax0"]}},
+                           "rebuilds_total": stats["updates"] + stats["forced"], "Nmax": stats["Nmax0"]},
                 "particle_steps_per_sec": tps * N,
                 "wall_tps": md_steps * args.steps / t_wall,
                 "gpu_launches": launches, "ms_runs": gpu_ms, "nlist_overflows": stats["overflows"],
                 "clocks": clocks,
                 "roofline": roofline,
-                "e2e": {"value": e2e_tps, "unit": "timesteps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "thermo_T": th["T"], "ms_runs": [1e3 * x for x in e2e_t]},
+                "e2e": e2e,
                 "cpu_baseline": cpu}
         if scale_ref:
             line["scale_ref"] = scale_ref
+        if strong:
+            line["strong_scaling"] = strong
+        if parity:
+            line["parity_checked"] = True
+            line["max_force_err"] = parity["max_force_err"]
+            line["parity"] = parity
         if mg_stats:
             line["domain"] = mg_stats
         print(json.dumps(line))
-    if s is not None:
-        s.close()
     if world > 1:
         dist.destroy_process_group()
 

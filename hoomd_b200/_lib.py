@@ -93,7 +93,8 @@ SYMBOLS = [
     "b200_compute_thermo", "b200_compute_thermo_static", "b200_sys_create", "b200_sys_destroy", "b200_sys_last_error", "b200_sys_set_particles",
     "b200_sys_set_accel", "b200_sys_get_particles", "b200_sys_setup_lj", "b200_sys_set_virial",
     "b200_sys_setup_integrator", "b200_sys_add_nve", "b200_sys_add_langevin", "b200_sys_set_sorter",
-    "b200_sys_set_dist_check", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
+    "b200_sys_set_dist_check", "b200_sys_set_langevin_options", "b200_sys_set_diameters",
+    "b200_sys_get_langevin_reservoir_energy", "b200_sys_set_group", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
     "b200_sys_add_nvt", "b200_sys_get_nvt_state", "b200_sys_set_nvt_state", "b200_nvt_mtk_step_one", "b200_nvt_mtk_step_two", "b200_nvt_mtk_advance",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
     "b200_sys_set_pair_mode", "b200_sys_get_pair_mode",
@@ -101,7 +102,7 @@ SYMBOLS = [
     "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
     "b200_sys_get_thermo", "b200_sys_time_kernel",
     "b200_sys_create_mg", "b200_sys_mg_export", "b200_sys_mg_connect", "b200_sys_get_n", "b200_sys_set_tags",
-    "b200_sys_mg_stats", "b200_sys_mg_get_ghosts",
+    "b200_sys_mg_stats", "b200_sys_mg_timing", "b200_sys_mg_get_ghosts",
 ]
 
 # enum B200_PAIR_* (hoomd/md/AllPairPotentials.h)
@@ -204,6 +205,10 @@ def lib():
     L.b200_sys_add_langevin.argtypes = [vp, C.c_float, C.c_uint, vp, C.c_int]
     L.b200_sys_add_nvt.argtypes = [vp, C.c_float, C.c_float]
     L.b200_sys_set_dist_check.argtypes = [vp, C.c_int]
+    L.b200_sys_set_langevin_options.argtypes = [vp, C.c_int, C.c_float, C.c_int]
+    L.b200_sys_set_diameters.argtypes = [vp, vp]
+    L.b200_sys_get_langevin_reservoir_energy.argtypes = [vp, c_double_p]
+    L.b200_sys_set_group.argtypes = [vp, vp, C.c_uint]
     L.b200_sys_set_temperature.argtypes = [vp, C.c_float]
     L.b200_sys_set_box.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_int]
     L.b200_sys_get_box.argtypes = [vp, vp]
@@ -244,6 +249,7 @@ def lib():
     L.b200_sys_set_tags.argtypes = [vp, vp]
     L.b200_sys_mg_stats.argtypes = [vp, C.POINTER(C.c_ulonglong)]
     L.b200_sys_mg_get_ghosts.argtypes = [vp, vp, vp]
+    L.b200_sys_mg_timing.argtypes = [vp, C.POINTER(C.c_ulonglong)]
     _lib = L
     return L
 

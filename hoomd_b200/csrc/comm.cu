@@ -6,60 +6,9 @@
 
 namespace b200
 {
-__device__ __forceinline__ unsigned long long globaltimer_ns()
-    {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-    }
-
-__device__ __forceinline__ void st_flag(unsigned long long* p, unsigned long long v)
-    {
-    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-    }
-
-__device__ __forceinline__ unsigned long long ld_flag(const unsigned long long* p)
-    {
-    unsigned long long v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-    }
-
-// All-ranks barrier, executed by ONE warp.  Flag word = (epoch << 1) | payload bit.  Two slots per kind (epoch parity):
-// a fast rank may already publish epoch+1 while a slow one still reads epoch.  Returns the OR of the payload bits.
-// A peer that never arrives (crashed process) must not hang the GPU: after `timeout_ns` the wait gives up and sets the
-// sticky error bit 8; the host reports it at the end of the chunk.
 __device__ __forceinline__ bool warp_barrier(const MgConst& c, MgState* ms, int kind, bool payload)
     {
-    const unsigned int lane = threadIdx.x & 31;
-    const unsigned long long epoch = ms->epoch[kind] + 1ull;
-    const unsigned int slot = ((unsigned int)kind * 2u + (unsigned int)(epoch & 1ull)) * MG_MAX_RANKS;
-    __threadfence_system(); // everything this rank wrote (ghosts, migrants, counts) is visible before the flag is
-    __syncwarp();
-    if (lane < c.world) st_flag(c.flags[lane] + slot + c.rank, (epoch << 1) | (payload ? 1ull : 0ull));
-    bool bit = false;
-    if (lane < c.world)
-        {
-        const unsigned long long* mine = c.flags[c.rank] + slot + lane;
-        const unsigned long long t0 = globaltimer_ns();
-        unsigned long long v = ld_flag(mine);
-        while ((v >> 1) < epoch)
-            {
-            if (globaltimer_ns() - t0 > 4000000000ull)
-                {
-                atomicOr(&ms->error, 8u);
-                break;
-                }
-            v = ld_flag(mine);
-            }
-        bit = (v & 1ull) != 0ull;
-        }
-    const bool any = __any_sync(0xffffffffu, bit);
-    __threadfence_system();
-    __syncwarp();
-    if (lane == 0) ms->epoch[kind] = epoch;
-    __syncwarp();
-    return any;
+    return mg_warp_barrier(c.world, c.rank, c.flags, ms, kind, payload);
     }
 
 __global__ void __launch_bounds__(32) k_mg_step_barrier(const __grid_constant__ MgConst c, MgState* ms, StepState* st,
@@ -106,11 +55,13 @@ __global__ void __launch_bounds__(32) k_mg_rebuild_vote(const __grid_constant__ 
 // fills this time must not be binned: a far-away position is ignored by the cell list like any out-of-range ghost,
 // hoomd/CellList.cc:494-498)
 __global__ void __launch_bounds__(256) k_mg_begin(const __grid_constant__ MgConst c, MgState* ms, float4* __restrict__ pos,
+                                                  unsigned int* __restrict__ chunk_flag, unsigned int nchunks,
                                                   const unsigned int* __restrict__ enable)
     {
     if (enable && !*enable) return;
     const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < c.Gcap) pos[c.Ncap + t] = make_float4(1.0e30f, 1.0e30f, 1.0e30f, 0.0f);
+    if (t < nchunks) chunk_flag[t] = 0u;
     if (t < MG_NDIR)
         {
         ms->send_cnt[t] = 0u;
@@ -303,14 +254,19 @@ __global__ void __launch_bounds__(256) k_mg_ghost_plan(const __grid_constant__ M
     const float4 p = active ? pos[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     const float x[3] = {p.x, p.y, p.z};
     bool nlo[3], nhi[3];
-    bool any = false;
+    bool any = false, near = false;
+    // a particle can have a ghost in its neighbor list only when it sits within r_list = r_ghost of a split face at build
+    // time; slightly widened (FP32 rounding of the shifted ghost positions), it marks its chunk as a boundary chunk
+    const float wide = c.r_ghost * 1.00001f + 1.0e-4f;
 #pragma unroll
     for (int a = 0; a < 3; a++)
         {
         nlo[a] = active && c.split[a] && (x[a] < c.lo[a] + c.r_ghost);
         nhi[a] = active && c.split[a] && (x[a] >= c.hi[a] - c.r_ghost);
         any |= nlo[a] | nhi[a];
+        near |= active && c.split[a] && (x[a] <= c.lo[a] + wide || x[a] >= c.hi[a] - wide);
         }
+    if (near) l.chunk_flag[i / l.ppb] = 1u; // same-value stores
     if (!__any_sync(0xffffffffu, any))
         {
         if (active) l.pplan_n[i] = 0; // interior warp
@@ -347,6 +303,52 @@ __global__ void __launch_bounds__(256) k_mg_ghost_plan(const __grid_constant__ M
             }
         }
     if (active) l.pplan_n[i] = (unsigned char)nplan;
+    }
+
+// boundary chunks first: ordered compaction of the chunk flags by one CTA (a few thousand chunks: per-thread ranges + a block
+// scan), so consecutive CTAs of k_md_step still work on consecutive chunks
+__global__ void __launch_bounds__(1024) k_mg_cta_order(const MgLocal l, const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    __shared__ unsigned int s_warp[32];
+    __shared__ unsigned int s_total;
+    const unsigned int n = l.nchunks, per = (n + 1023u) / 1024u;
+    const unsigned int b = threadIdx.x * per, e = min(n, b + per);
+    unsigned int cnt = 0;
+    for (unsigned int k = b; k < e; k++) cnt += l.chunk_flag[k] ? 1u : 0u;
+    // exclusive block scan of cnt
+    unsigned int incl = cnt;
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += t;
+        }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0)
+        {
+        unsigned int w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if ((int)lane >= o) wi += t;
+            }
+        s_warp[lane] = wi - w;
+        if (lane == 31) s_total = wi;
+        }
+    __syncthreads();
+    const unsigned int nb = s_total;
+    unsigned int ob = s_warp[warp] + incl - cnt; // boundary chunks before this thread's range
+    unsigned int oi = nb + (b < n ? b : n) - ob; // interior chunks before it, placed behind all boundary chunks
+    for (unsigned int k = b; k < e; k++)
+        {
+        if (l.chunk_flag[k]) l.cta_order[ob++] = k;
+        else l.cta_order[oi++] = k;
+        }
+    if (threadIdx.x == 0) l.ms->n_bchunks = nb;
     }
 
 // every MD step: one store per (boundary particle, destination) into the neighbor's position buffer
@@ -397,8 +399,8 @@ cudaError_t launch_mg_rebuild_vote(const MgConst& c, const MgLocal& l, int buffe
 cudaError_t launch_mg_migrate(const MgConst& c, const MgLocal& l, float4* pos, const unsigned int* enable,
                               cudaStream_t stream)
     {
-    const unsigned int nb = (std::max(c.Gcap, (unsigned int)MG_NDIR) + 255u) / 256u;
-    k_mg_begin<<<nb, 256, 0, stream>>>(c, l.ms, pos, enable);
+    const unsigned int nb = (std::max(std::max(c.Gcap, l.nchunks), (unsigned int)MG_NDIR) + 255u) / 256u;
+    k_mg_begin<<<nb, 256, 0, stream>>>(c, l.ms, pos, l.chunk_flag, l.nchunks, enable);
     k_mg_migrate_mark<<<(c.Ncap + 255u) / 256u, 256, 0, stream>>>(c, l, pos, enable);
     k_mg_migrate_publish<<<1, 32, 0, stream>>>(c, l.ms, enable);
     k_mg_migrate_count<<<1, 32, 0, stream>>>(c, l, enable);
@@ -421,6 +423,7 @@ cudaError_t launch_mg_ghost_plan(const MgConst& c, const MgLocal& l, float4* pos
                                  cudaStream_t stream)
     {
     k_mg_ghost_plan<<<(c.Ncap + 255u) / 256u, 256, 0, stream>>>(c, l, pos, enable);
+    k_mg_cta_order<<<1, 1024, 0, stream>>>(l, enable);
     cudaError_t e = launch_mg_ghost_send(c, l, pos, buffer, enable, stream);
     if (e != cudaSuccess) return e;
     return launch_mg_barrier(c, l, 2, enable, stream);

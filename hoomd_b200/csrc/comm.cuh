@@ -44,6 +44,9 @@ struct MgState
     unsigned int rebuild_id;                 // incremented per rebuild (stamps hole marks)
     unsigned int error;                      // sticky: 1 migrate overflow, 2 ghost overflow, 4 local capacity overflow
     unsigned int max_send, max_gsend, max_N; // high-water marks for capacity tuning
+    unsigned int n_bchunks;                  // particle chunks of k_md_step that touch the ghost layer (scheduled first)
+    unsigned long long wait_ns[MG_NBARRIER]; // time spent between arriving at a barrier and seeing every rank, per kind
+    unsigned long long wait_cnt[MG_NBARRIER];
     };
 
 // By-value kernel argument: geometry + peer pointers (constant between reconnects)
@@ -88,7 +91,73 @@ struct MgLocal // plain device arrays of the owner used by the rebuild kernels
     const unsigned char* slot_dir; // [sum seg_cap] direction code of each ghost slot (constant)
     unsigned int* pplan;       // [7 * Ncap] reverse plan: ghost slots fed by particle i (k_md_step's fused ghost update)
     unsigned char* pplan_n;    // [Ncap]
+    unsigned int* chunk_flag;  // [nchunks] chunk of `ppb` consecutive particles holds one within the ghost layer of a split face
+    unsigned int* cta_order;   // [nchunks] boundary chunks first (ascending), then the others (ascending)
+    unsigned int ppb, nchunks; // particles per CTA of k_md_step, ceil(Ncap / ppb)
     };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+    {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+    }
+
+__device__ __forceinline__ void st_flag(unsigned long long* p, unsigned long long v)
+    {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    }
+
+__device__ __forceinline__ unsigned long long ld_flag(const unsigned long long* p)
+    {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+    }
+
+// All-ranks barrier, executed by ONE warp (all 32 lanes must call it).  Flag word = (epoch << 1) | payload bit.  Two slots per
+// kind (epoch parity): a fast rank may already publish epoch+1 while a slow one still reads epoch.  Returns the OR of the
+// payload bits.  A peer that never arrives (crashed process) must not hang the GPU: after 4 s the wait gives up and sets the
+// sticky error bit 8; the host reports it at the end of the chunk.  flags[q] = rank q's flag array,
+// flags[q][(kind*2 + parity) * MG_MAX_RANKS + writer].
+__device__ __forceinline__ bool mg_warp_barrier(unsigned int world, unsigned int rank, unsigned long long* const* flags,
+                                                MgState* ms, int kind, bool payload)
+    {
+    const unsigned int lane = threadIdx.x & 31;
+    const unsigned long long epoch = ms->epoch[kind] + 1ull;
+    const unsigned int slot = ((unsigned int)kind * 2u + (unsigned int)(epoch & 1ull)) * MG_MAX_RANKS;
+    __threadfence_system(); // everything this rank wrote (ghosts, migrants, counts) is visible before the flag is
+    __syncwarp();
+    const unsigned long long t0 = globaltimer_ns();
+    if (lane < world) st_flag(flags[lane] + slot + rank, (epoch << 1) | (payload ? 1ull : 0ull));
+    bool bit = false;
+    if (lane < world)
+        {
+        const unsigned long long* mine = flags[rank] + slot + lane;
+        unsigned long long v = ld_flag(mine);
+        while ((v >> 1) < epoch)
+            {
+            if (globaltimer_ns() - t0 > 4000000000ull)
+                {
+                atomicOr(&ms->error, 8u);
+                break;
+                }
+            v = ld_flag(mine);
+            }
+        bit = (v & 1ull) != 0ull;
+        }
+    const bool any = __any_sync(0xffffffffu, bit);
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0)
+        {
+        ms->epoch[kind] = epoch;
+        ms->wait_ns[kind] += globaltimer_ns() - t0;
+        ms->wait_cnt[kind] += 1ull;
+        }
+    __syncwarp();
+    return any;
+    }
 
 // all-ranks barrier of kind k; kind 0 also carries the distance-check vote and takes the rebuild decision
 cudaError_t launch_mg_step_barrier(const MgConst& c, const MgLocal& l, unsigned long long cond_handle, int use_cond,

@@ -183,6 +183,19 @@ struct b200_system
     double nvt_scale = 1.0;
     static constexpr unsigned int NVT_BLOCKS = 592; // CTAs of the stand-alone kinetic-energy pass (4 per SM)
 
+    // ParticleGroup of the integration method (hoomd/ParticleGroup.h): 1 byte per TAG; empty = group.all().  group_idx is
+    // ParticleGroup::getIndexArray (sorted member indices), rebuilt after every particle sort, for the stand-alone drivers.
+    DevBuf<unsigned char> group_flag;
+    DevBuf<unsigned int> group_idx, group_cnt;
+    unsigned int group_size = 0;         // members (0 with an empty group_flag: all N)
+    bool group_idx_dirty = true;
+    // md.integrate.langevin(dscale=lambda, tally=True)
+    DevBuf<float> diameter;              // per TAG (ParticleData default 1.0 when empty)
+    int use_lambda = 0, tally = 0;
+    float lambda = 0.0f;
+    DevBuf<double> tally_acc, ck_tally;  // {running sum of E_step, E of even steps, E of odd steps}
+    DevBuf<float> tally_tmp;
+
     // ---- SFCPackUpdater ---------------------------------------------------------------------------------------
     unsigned int sorter_period = 0, sorter_next = 0, sorter_grid = 256;
     DevBuf<unsigned int> sort_order, sort_keys, sort_scratch;
@@ -222,11 +235,12 @@ struct b200_system
     MgState* h_ms = nullptr;         // pinned
     DevBuf<unsigned int> holes, low_holes, hole_mark, plan_src;
     DevBuf<unsigned char> slot_dir, pplan_n;
-    DevBuf<unsigned int> pplan;
+    DevBuf<unsigned int> pplan, chunk_flag, cta_order;
     DevBuf<GhostSendTable> gs_table;
-    // ghost update inside k_md_step (HOOMD_B200_FUSED_GHOSTS=1).  Off by default: measured 1-3 % slower than the
-    // stand-alone k_mg_ghost_send (LJ 8M on 8 B200: 3735 vs 3860 TPS; LJ 1M on 2: 6946 vs 7031) -- see DESIGN.md section 6
-    bool fused_ghosts = false;
+    unsigned int mg_tpp = 2;         // lanes per particle of k_md_step under decomposition (fixes the chunk size of cta_order)
+    // Ghost update + all-ranks step barrier inside k_md_step, boundary chunks scheduled first (the default).
+    // HOOMD_B200_FUSED_GHOSTS=0: the round-1 sequence barrier kernel -> k_md_step -> k_mg_ghost_send, kept for A/B runs.
+    bool fused_ghosts = true;
 
     // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
     int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
@@ -314,7 +328,7 @@ static void pair_args(b200_system* s, b200_pair_args& a)
     a.ntypes = s->ntypes;
     a.shift_mode = (unsigned int)s->shift_mode;
     a.compute_virial = s->compute_virial ? 1u : 0u;
-    a.threads_per_particle = s->pair_tpp;
+    a.threads_per_particle = s->mg ? s->mg_tpp : s->pair_tpp; // decomposition: fixed, it shapes cta_order
     a.block_size = 0;
     // listed pairs are at most r_list apart at build time and each partner drifts < r_buff/2 (+ one step) before the
     // next rebuild: r_cut + 2 r_buff bounds every |r_i - r_j| the kernel will see
@@ -328,14 +342,31 @@ static const void* pair_params_ptr(b200_system* s)
     }
 
 // IntegratorTwoStep::getNDOF for one method on all particles (hoomd/md/IntegratorTwoStep.cc:270-283): D N - D
-static unsigned int nvt_ndof(const b200_system* s) { return 3u * s->N - 3u; }
+static unsigned int method_group_size(const b200_system* s) { return s->group_flag.n ? s->group_size : s->N; }
+static unsigned int nvt_ndof(const b200_system* s) { return 3u * method_group_size(s) - 3u; }
+
+// ParticleGroup::getIndexArray of the method's group (NULL = all particles): rebuilt when the particle order changed
+static const unsigned int* group_index(b200_system* s)
+    {
+    if (!s->group_flag.n) return nullptr;
+    if (s->group_idx_dirty)
+        {
+        if (s->group_idx.n < s->N) s->group_idx.alloc(s->N, false);
+        if (!s->group_cnt.n) s->group_cnt.alloc(1);
+        CUDA_OK(launch_group_index(s->group_idx.p, s->group_cnt.p, s->group_flag.p, s->tag.p, s->N, s->stream));
+        s->kernels_last_run += 1;
+        s->group_idx_dirty = false;
+        }
+    return s->group_idx.p;
+    }
 
 // ComputeThermo (kinetic energy of the half-step velocities) + TwoStepNVTMTK::advanceThermostat, on the device
 static void nvt_advance(b200_system* s)
     {
     // tagged with the timestep: the step kernel that runs step two of this update finds its factor ready
-    CUDA_OK(launch_nvt_advance(s->d_nvt.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p, nullptr,
-                               s->N, nvt_ndof(s), s->kT, s->nvt_tau, s->dt, s->timestep, s->stream));
+    CUDA_OK(launch_nvt_advance(s->d_nvt.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p,
+                               group_index(s), method_group_size(s), nvt_ndof(s), s->kT, s->nvt_tau, s->dt, s->timestep,
+                               s->stream));
     s->kernels_last_run += 2;
     }
 
@@ -346,7 +377,8 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.net_force = s->net_force.p; a.last_pos = s->last_pos.p; a.tag = s->tag.p;
     a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p; a.maxsq = s->d_maxsq.p;
     a.N = s->mg ? s->Ncap : s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
-    a.d_N = s->mg ? &s->d_state.p->N : nullptr; a.mg = s->mg ? 1 : 0;
+    a.d_N = s->mg ? &s->d_state.p->N : nullptr;
+    a.mg = s->mg ? ((s->fused_ghosts && s->mg_connected) ? 2 : 1) : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
     for (int d = 0; d < 3; d++) a.lambda[d] = (s->mg || !s->have_nlist) ? 1.0f : s->box.L[d] / s->last_L[d];
@@ -355,6 +387,7 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         {
         a.gs.tab = s->gs_table.p; a.gs.pplan = s->pplan.p; a.gs.pplan_n = s->pplan_n.p; a.gs.slot_dir = s->slot_dir.p;
         a.gs.pitch = s->Ncap;
+        a.gs.cta_order = s->cta_order.p;
         }
     if (s->bond_kind >= 0)
         {
@@ -364,6 +397,12 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         {
         a.nvt_state = s->d_nvt.p; a.nvt_acc = s->nvt_acc.p; a.nvt_scale = s->nvt_scale; a.nvt_ndof = nvt_ndof(s);
         a.nvt_tau = s->nvt_tau;
+        }
+    a.group_flag = s->group_flag.n ? s->group_flag.p : nullptr;
+    if (s->method == 2)
+        {
+        a.use_lambda = s->use_lambda; a.gamma_lambda = s->lambda; a.diameter = s->diameter.p;
+        a.tally_acc = s->tally ? s->tally_acc.p : nullptr;
         }
     }
 
@@ -717,15 +756,15 @@ static void integrate_step_one(b200_system* s, unsigned int ts)
     if (s->method == 3)
         {
         CUDA_OK(b200_nvt_mtk_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p,
-                                      nullptr, s->N, &s->box, s->d_nvt.p, s->dt, s->stream));
+                                      group_index(s), method_group_size(s), &s->box, s->d_nvt.p, s->dt, s->stream));
         s->kernels_last_run += 1;
         nvt_advance(s);
         return;
         }
     const bool nve = s->method == 1;
-    CUDA_OK(b200_nve_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p, nullptr,
-                              s->N, &s->box, s->dt, nve ? s->limit : 0, s->limit_val, nve ? s->zero_force : 0,
-                              s->stream));
+    CUDA_OK(b200_nve_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p,
+                              group_index(s), method_group_size(s), &s->box, s->dt, nve ? s->limit : 0, s->limit_val,
+                              nve ? s->zero_force : 0, s->stream));
     s->kernels_last_run += 1;
     }
 
@@ -741,15 +780,35 @@ static void integrate_step_two(b200_system* s, unsigned int ts)
         la.timestep = ts;
         la.seed = s->seed_hashed;
         la.noiseless_t = s->noiseless_t;
-        CUDA_OK(b200_langevin_step_two((const float*)s->pos.p, (float*)s->vel.p, (float*)s->accel.p, nullptr, s->tag.p,
-                                       nullptr, s->N, (const float*)s->net_force.p, &la, s->dt, 3, s->stream));
+        la.use_lambda = s->use_lambda;
+        la.lambda = s->lambda;
+        la.tally = s->tally;
+        la.d_sum_bdenergy = s->tally ? s->tally_tmp.p : nullptr;
+        // the driver indexes diameter by particle index; the engine keeps it by tag: gather through the tag array first
+        const float* diam = nullptr;
+        if (s->use_lambda)
+            {
+            if (s->tally_tmp.n < 1 + (size_t)s->N) s->tally_tmp.resize(1 + (size_t)s->N);
+            la.d_sum_bdenergy = s->tally ? s->tally_tmp.p : nullptr;
+            CUDA_OK(launch_gather_by_tag(s->tally_tmp.p + 1, s->diameter.p, s->tag.p, s->N, s->stream));
+            diam = s->tally_tmp.p + 1;
+            s->kernels_last_run += 1;
+            }
+        CUDA_OK(b200_langevin_step_two((const float*)s->pos.p, (float*)s->vel.p, (float*)s->accel.p, diam, s->tag.p,
+                                       group_index(s), method_group_size(s), (const float*)s->net_force.p, &la, s->dt, 3,
+                                       s->stream));
+        if (s->tally)
+            {
+            CUDA_OK(launch_tally_fold(s->tally_acc.p, s->tally_tmp.p, ts, s->stream));
+            s->kernels_last_run += 1;
+            }
         }
     else if (s->method == 3)
-        CUDA_OK(b200_nvt_mtk_step_two((float*)s->vel.p, (float*)s->accel.p, nullptr, s->N, (const float*)s->net_force.p,
-                                      s->d_nvt.p, s->dt, s->stream));
+        CUDA_OK(b200_nvt_mtk_step_two((float*)s->vel.p, (float*)s->accel.p, group_index(s), method_group_size(s),
+                                      (const float*)s->net_force.p, s->d_nvt.p, s->dt, s->stream));
     else
-        CUDA_OK(b200_nve_step_two((float*)s->vel.p, (float*)s->accel.p, nullptr, s->N, (const float*)s->net_force.p,
-                                  s->dt, s->limit, s->limit_val, s->zero_force, s->stream));
+        CUDA_OK(b200_nve_step_two((float*)s->vel.p, (float*)s->accel.p, group_index(s), method_group_size(s),
+                                  (const float*)s->net_force.p, s->dt, s->limit, s->limit_val, s->zero_force, s->stream));
     s->kernels_last_run += 1;
     }
 
@@ -814,6 +873,7 @@ static void sorter_update(b200_system* s, bool periodic = true)
     s->force_update = true;
     s->cl_force = true;
     s->idx_tables_dirty = true;
+    s->group_idx_dirty = true;
     }
 } // namespace b200
 
@@ -1029,6 +1089,12 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         CUDA_OK(cudaMemcpyAsync(s->ck_nvt.p, s->d_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
         }
+    if (s->method == 2 && s->tally)
+        {
+        // the first k_md_step of the chunk runs step two of update(timestep): its E slot starts at zero
+        CUDA_OK(cudaMemsetAsync(s->tally_acc.p + 1u + (s->timestep & 1u), 0, sizeof(double), s->stream));
+        CUDA_OK(cudaMemcpyAsync(s->ck_tally.p, s->tally_acc.p, sizeof(double) * 3, cudaMemcpyDeviceToDevice, s->stream));
+        }
 
     // The box changed since the last list build (update.box_resize): the distance checks of this chunk use the lambda-scaled
     // row of the table until the first rebuild decision clears StepState::box_scaled.  The list in force was built in the OLD
@@ -1105,6 +1171,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
                                     s->stream));
             if (s->method == 3)
                 CUDA_OK(cudaMemcpyAsync(s->d_nvt.p, s->ck_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
+            if (s->method == 2 && s->tally)
+                CUDA_OK(cudaMemcpyAsync(s->tally_acc.p, s->ck_tally.p, sizeof(double) * 3, cudaMemcpyDeviceToDevice, s->stream));
             CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
             s->force_update = ck_force_update;
             s->cl_force = true;
@@ -1118,6 +1186,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         CUDA_OK(cudaMemcpyAsync(s->image.p, s->ck_image.p, sizeof(i3) * N, cudaMemcpyDeviceToDevice, s->stream));
         if (s->method == 3)
             CUDA_OK(cudaMemcpyAsync(s->d_nvt.p, s->ck_nvt.p, sizeof(float) * 4, cudaMemcpyDeviceToDevice, s->stream));
+        if (s->method == 2 && s->tally)
+            CUDA_OK(cudaMemcpyAsync(s->tally_acc.p, s->ck_tally.p, sizeof(double) * 3, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
         s->force_update = ck_force_update;
         if (s->tile_on)
@@ -1341,6 +1411,23 @@ int b200_sys_mg_stats(b200_system* s, unsigned long long* out8)
     for (int d = 0; d < MG_NDIR; d++) g += std::min(s->h_ms->gsend_cnt[d], s->mgc.seg_cap[d]);
     out8[6] = g;
     out8[7] = s->h_ms->epoch[0];
+    SYS_CATCH(s)
+    }
+
+/* {wait ns, count} of the four barrier kinds (0 = MD step, 1..3 = rebuild phases), boundary chunks, chunks */
+int b200_sys_mg_timing(b200_system* s, unsigned long long* out10)
+    {
+    SYS_TRY(s)
+    if (!s->mg) throw std::runtime_error("comm: not a domain-decomposed system");
+    CUDA_OK(cudaMemcpyAsync(s->h_ms, s->d_ms.p, sizeof(MgState), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    for (int k = 0; k < MG_NBARRIER; k++)
+        {
+        out10[2 * k] = s->h_ms->wait_ns[k];
+        out10[2 * k + 1] = s->h_ms->wait_cnt[k];
+        }
+    out10[8] = s->h_ms->n_bchunks;
+    out10[9] = s->mgl.nchunks;
     SYS_CATCH(s)
     }
 
@@ -1680,6 +1767,96 @@ int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const flo
     s->d_gamma.alloc(s->ntypes);
     s->d_gamma.upload(g.data(), s->ntypes, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+// md.integrate.langevin(..., dscale=lambda, tally=...) (hoomd/md/integrate.py:844-940; TwoStepLangevinBase use_lambda / lambda,
+// TwoStepLangevin::setTally).  Call after b200_sys_add_langevin.
+int b200_sys_set_langevin_options(b200_system* s, int use_lambda, float lambda, int tally)
+    {
+    SYS_TRY(s)
+    if (s->method != 2) throw std::runtime_error("integrate.langevin: no Langevin method set");
+    if (s->mg && (use_lambda || tally)) throw std::runtime_error("integrate.langevin: dscale / tally are not available under domain decomposition yet");
+    if (s->tile_on && (use_lambda || tally)) throw std::runtime_error("integrate.langevin: dscale / tally are not available on the cell-tile path");
+    s->use_lambda = use_lambda != 0;
+    s->lambda = lambda;
+    s->tally = tally != 0;
+    if (s->use_lambda && !s->diameter.n)
+        {
+        std::vector<float> one(s->N, 1.0f); // ParticleData default diameter
+        s->diameter.alloc(s->N);
+        s->diameter.upload(one.data(), s->N, s->stream);
+        }
+    if (!s->tally_acc.n)
+        {
+        s->tally_acc.alloc(3);
+        s->ck_tally.alloc(3);
+        s->tally_tmp.alloc(1);
+        }
+    CUDA_OK(cudaMemsetAsync(s->tally_acc.p, 0, sizeof(double) * 3, s->stream)); // m_reservoir_energy(0), m_extra_energy_overdeltaT(0)
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+// per-particle diameters by TAG (ParticleData::setDiameter); only md.integrate.langevin(dscale=...) reads them on this path
+int b200_sys_set_diameters(b200_system* s, const float* diameter_by_tag)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("particle diameters are not carried under domain decomposition yet");
+    if (!s->diameter.n) s->diameter.alloc(s->N);
+    s->diameter.upload(diameter_by_tag, s->N, s->stream);
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+// the "langevin_reservoir_energy" log quantity (TwoStepLangevin::getLogValue, hoomd/md/TwoStepLangevin.cc:71-80):
+// m_reservoir_energy + m_extra_energy_overdeltaT * dt with m_reservoir_energy = -dt * sum over steps of E_step and
+// m_extra_energy_overdeltaT = E_last / 2 (:416-417)
+int b200_sys_get_langevin_reservoir_energy(b200_system* s, double* out)
+    {
+    SYS_TRY(s)
+    if (s->method != 2 || !s->tally) throw std::runtime_error("integrate.langevin: tally is not enabled");
+    double h[3];
+    CUDA_OK(cudaStreamSynchronize(s->stream));
+    CUDA_OK(cudaMemcpy(h, s->tally_acc.p, sizeof(h), cudaMemcpyDeviceToHost));
+    const double e_last = s->timestep ? h[1u + ((s->timestep - 1u) & 1u)] : 0.0;
+    *out = (double)(float)(-(double)s->dt * h[0] + 0.5 * e_last * (double)s->dt);
+    SYS_CATCH(s)
+    }
+
+// hoomd.group.*: the particles the integration method acts on, as member TAGS (ParticleGroup, hoomd/ParticleGroup.h); n = 0
+// restores group.all().  Non-members keep their position and velocity; forces on them are still computed and reported.
+int b200_sys_set_group(b200_system* s, const unsigned int* member_tags, unsigned int n)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("group: integration groups other than all are not available under domain decomposition yet");
+    if (s->tile_on) throw std::runtime_error("group: integration groups other than all are not available on the cell-tile path");
+    if (n == 0 || !member_tags)
+        {
+        s->group_flag.release();
+        s->group_size = 0;
+        }
+    else
+        {
+        std::vector<unsigned char> f(s->N, 0);
+        unsigned int cnt = 0;
+        for (unsigned int k = 0; k < n; k++)
+            {
+            if (member_tags[k] >= s->N) throw std::runtime_error("group: particle tag out of bounds");
+            if (!f[member_tags[k]]) cnt++;
+            f[member_tags[k]] = 1;
+            }
+        s->group_flag.alloc(s->N);
+        s->group_flag.upload(f.data(), s->N, s->stream);
+        s->group_size = cnt;
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        }
+    s->group_idx_dirty = true;
+    if (s->method == 3) // NDOF of the thermostat follows the group (IntegratorTwoStep::getNDOF)
+        s->nvt_scale = std::exp2(std::floor(42.0 - std::log2((double)nvt_ndof(s) * (double)s->kT)));
     invalidate_graph(s);
     SYS_CATCH(s)
     }
@@ -2060,7 +2237,8 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         CUDA_OK(cudaMemcpyAsync(s->d_state.p, s->h_state, sizeof(StepState), cudaMemcpyHostToDevice, s->stream));
         FusedStepArgs fa;
         fused_args(s, fa);
-        fa.gs.tab = nullptr; // scratch steps must not write into the neighbors' ghost regions
+        fa.gs.tab = nullptr; // scratch steps must not write into the neighbors' ghost regions nor take the step barrier
+        if (fa.mg) fa.mg = 1;
         CUDA_OK(cudaStreamSynchronize(s->stream));
         CUDA_OK(cudaEventRecord(e0, s->stream));
         for (unsigned int k = 0; k < iters; k++) enqueue_md_step(s, fa, (int)(k & 1), 0ull, 0);
@@ -2122,7 +2300,7 @@ int b200_sys_get_thermo(b200_system* s, double* out5)
     double h[9];
     s->th_out.download(h, 9, s->stream);
     // IntegratorTwoStep::getNDOF: D*N - D (hoomd/md/IntegratorTwoStep.cc:270-283); ComputeThermo stores FP32 properties
-    const double ndof = 3.0 * s->N - 3.0;
+    const double ndof = 3.0 * method_group_size(s) - 3.0; // DOF of the integrated particles within group all
     const float ke = (float)h[0], pe = (float)h[1];
     const double volume = (double)(s->box.L[0] * s->box.L[1] * s->box.L[2]);
     const double W = (1.0f / 3.0f) * h[2];

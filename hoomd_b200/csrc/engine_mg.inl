@@ -138,6 +138,16 @@ static void mg_setup(b200_system* s, const b200_mg_params& p)
     s->pplan.alloc(7 * (size_t)s->Ncap);
     s->pplan_n.alloc(s->Ncap);
     s->gs_table.alloc(1);
+    // chunk size of k_md_step = particles per CTA: fixed for the life of the system (it shapes cta_order)
+    // (2 or 8 lanes per particle: the widths every pair evaluator is instantiated for)
+    s->mg_tpp = pick_pair_tpp(std::max(1u, p.N_global / p.world)) <= 2u ? 2u : 8u;
+    const unsigned int ppb = md_step_block() / s->mg_tpp;
+    const unsigned int nchunks = (s->Ncap + ppb - 1) / ppb;
+    s->chunk_flag.alloc(nchunks);
+    s->cta_order.alloc(nchunks);
+    std::vector<unsigned int> ident(nchunks);
+    for (unsigned int k = 0; k < nchunks; k++) ident[k] = k;
+    s->cta_order.upload(ident.data(), nchunks, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     }
 
@@ -157,6 +167,10 @@ static void mg_bind_local(b200_system* s)
     l.slot_dir = s->slot_dir.p;
     l.pplan = s->pplan.p;
     l.pplan_n = s->pplan_n.p;
+    l.chunk_flag = s->chunk_flag.p;
+    l.cta_order = s->cta_order.p;
+    l.ppb = md_step_block() / s->mg_tpp;
+    l.nchunks = (unsigned int)s->cta_order.n;
     }
 
 static void mg_connect(b200_system* s, const unsigned char* handles)
@@ -193,6 +207,10 @@ static void mg_connect(b200_system* s, const unsigned char* handles)
         t.peer_posA[d] = c.peer_posA[d];
         t.peer_posB[d] = c.peer_posB[d];
         }
+    t.world = c.world;
+    t.rank = c.rank;
+    for (unsigned int q = 0; q < c.world; q++) t.flags[q] = c.flags[q];
+    t.ms = s->d_ms.p;
     s->gs_table.upload(&t, 1, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     mg_bind_local(s);
@@ -217,7 +235,7 @@ static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream, hook));
     CUDA_OK(launch_mg_rebuild_vote(s->mgc, s->mgl, buffer, enable, s->stream));
     }
-constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 3 + 4 + 2; // migrate, ghost plan, cell list, nlist + vote
+constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 4 + 4 + 2; // migrate, ghost plan + CTA order, cell list, nlist + vote
 
 static void mg_upload_state(b200_system* s, unsigned int steps_left)
     {
@@ -299,13 +317,17 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
         }
     }
 
-// graph of two MD steps:  barrier -> IF{rebuild from A} -> k_md_step(A->B) -> ghosts(B)
-//                         barrier -> IF{rebuild from B} -> k_md_step(B->A) -> ghosts(A)
+// graph of two MD steps.  Default (ghost update + step barrier inside k_md_step, FusedStepArgs::mg == 2):
+//     [arm h0 from need_rebuild] -> IF{rebuild from A} -> k_md_step(A->B) -> IF{rebuild from B} -> k_md_step(B->A)
+// -- the single-GPU graph with the collective rebuild bracket in the IF bodies: the LAST CTA of k_md_step takes the all-ranks
+// barrier, the vote and the rebuild decision and arms the next IF node.  HOOMD_B200_FUSED_GHOSTS=0 (round-1 sequence):
+//     barrier -> IF{rebuild from A} -> k_md_step(A->B) -> ghosts(B) -> barrier -> IF{rebuild from B} -> k_md_step(B->A) -> ghosts(A)
 static void mg_build_graph(b200_system* s)
     {
 #if (CUDART_VERSION >= 12040)
     FusedStepArgs fa;
     fused_args(s, fa);
+    const bool fused = fa.mg == 2;
     const unsigned int* enable = &s->d_state.p->need_rebuild;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
@@ -318,14 +340,20 @@ static void mg_build_graph(b200_system* s)
         CUDA_OK(cudaGraphConditionalHandleCreate(&h1, graph, 0, cudaGraphCondAssignDefault));
         CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
         capturing = true;
-        CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
+        if (fused)
+            CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h0, s->stream));
+        else
+            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
         cudaGraph_t body0 = add_if_node(s, graph, h0);
-        enqueue_md_step(s, fa, 0, 0ull, 0);
-        if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-        CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
+        enqueue_md_step(s, fa, 0, fused ? (unsigned long long)h1 : 0ull, fused ? 1 : 0);
+        if (!fused)
+            {
+            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
+            }
         cudaGraph_t body1 = add_if_node(s, graph, h1);
         enqueue_md_step(s, fa, 1, 0ull, 0);
-        if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        if (!fused) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
         cudaGraph_t out = nullptr;
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
@@ -376,23 +404,30 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_upload_state(s, remaining);
         FusedStepArgs fa;
         fused_args(s, fa);
-        // prologue: step one of the first update() + its ghost update; the first barrier of the graph takes the vote
+        // prologue: step one of the first update() + its ghost update.  Fused mode: one stand-alone barrier takes the first
+        // vote and decision (every later one is taken by the last CTA of k_md_step); round-1 mode: the first barrier of the
+        // graph does.
+        const bool fused = fa.mg == 2;
         if (!resume) CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
         CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        if (fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
         const unsigned int nreplay = (remaining + 1) / 2;
         if (s->use_graph == 3)
             {
             const unsigned int* enable = &s->d_state.p->need_rebuild;
             for (unsigned int k = 0; k < nreplay; k++)
                 {
-                CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
                 mg_enqueue_rebuild(s, enable, s->pos.p, 0);
                 enqueue_md_step(s, fa, 0, 0ull, 0);
-                if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-                CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                if (!fused)
+                    {
+                    CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+                    CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                    }
                 mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
                 enqueue_md_step(s, fa, 1, 0ull, 0);
-                if (!fa.gs.tab) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+                if (!fused) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
                 }
             }
         else
@@ -402,7 +437,7 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_check_errors(s);
         cell_list_check_conditions(s);
         const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-        s->kernels_last_run += 2ull + (fa.gs.tab ? 4ull : 6ull) * nreplay
+        s->kernels_last_run += (fused ? 3ull : 2ull) + (fused ? 3ull : 6ull) * nreplay
                                + (MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u) * rebuilds;
         s->num_updates += st.num_updates;
         s->num_forced += st.num_forced;

@@ -18,12 +18,14 @@ __global__ void __launch_bounds__(256) k_fused_step_one(float4* __restrict__ pos
                                                         float dt, float r_buff, bool limit, float limit_val,
                                                         bool zero_force, StepState* __restrict__ st,
                                                         const unsigned int* __restrict__ d_N,
-                                                        const NvtState* __restrict__ nvt, float3 lambda, float lambda_min)
+                                                        const NvtState* __restrict__ nvt, float3 lambda, float lambda_min,
+                                                        const unsigned char* __restrict__ group_flag,
+                                                        const unsigned int* __restrict__ tag)
     {
     unsigned int j = blockIdx.x * blockDim.x + threadIdx.x;
     bool moved = false;
     if (d_N) N = *d_N;
-    if (j < N)
+    if (j < N && !(group_flag && !group_flag[tag[j]])) // members of the method's group only
         {
         float4 p = pos[j];
         float4 v = vel[j];
@@ -88,9 +90,12 @@ cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStr
                                                             a.r_buff, nve && a.limit, a.limit_val, nve && a.zero_force,
                                                             st, a.d_N,
                                                             a.method == 3 ? (const NvtState*)a.nvt_state : nullptr,
-                                                            make_float3(a.lambda[0], a.lambda[1], a.lambda[2]), a.lambda_min);
+                                                            make_float3(a.lambda[0], a.lambda[1], a.lambda[2]), a.lambda_min,
+                                                            a.group_flag, a.tag);
     return cudaGetLastError();
     }
+
+unsigned int md_step_block() { return (unsigned int)MD_BLOCK; }
 
 cudaError_t launch_decide(StepState* st, cudaStream_t stream)
     {
@@ -164,6 +169,79 @@ cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, un
     {
     if (N == 0) return cudaSuccess;
     k_merge_xyz_w<<<(N + 255) / 256, 256, 0, stream>>>(out, a, b, N);
+    return cudaGetLastError();
+    }
+
+// ordered compaction by one CTA (runs after a particle sort only): thread t owns a contiguous range of indices
+__global__ void __launch_bounds__(1024) k_group_index(unsigned int* __restrict__ idx, unsigned int* __restrict__ count,
+                                                      const unsigned char* __restrict__ group_flag,
+                                                      const unsigned int* __restrict__ tag, unsigned int N)
+    {
+    __shared__ unsigned int s_warp[32];
+    const unsigned int per = (N + 1023u) / 1024u;
+    const unsigned int b = min(N, threadIdx.x * per), e = min(N, b + per);
+    unsigned int cnt = 0;
+    for (unsigned int k = b; k < e; k++) cnt += group_flag[tag[k]] ? 1u : 0u;
+    unsigned int incl = cnt;
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += t;
+        }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0)
+        {
+        const unsigned int w = s_warp[lane];
+        unsigned int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if ((int)lane >= o) wi += t;
+            }
+        s_warp[lane] = wi - w;
+        if (lane == 31) *count = wi;
+        }
+    __syncthreads();
+    unsigned int o = s_warp[warp] + incl - cnt;
+    for (unsigned int k = b; k < e; k++)
+        if (group_flag[tag[k]]) idx[o++] = k;
+    }
+
+cudaError_t launch_group_index(unsigned int* idx, unsigned int* count, const unsigned char* group_flag,
+                               const unsigned int* tag, unsigned int N, cudaStream_t stream)
+    {
+    k_group_index<<<1, 1024, 0, stream>>>(idx, count, group_flag, tag, N);
+    return cudaGetLastError();
+    }
+
+__global__ void __launch_bounds__(256) k_gather_by_tag(float* __restrict__ out, const float* __restrict__ by_tag,
+                                                       const unsigned int* __restrict__ tag, unsigned int N)
+    {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) out[i] = by_tag[tag[i]];
+    }
+
+cudaError_t launch_gather_by_tag(float* out, const float* by_tag, const unsigned int* tag, unsigned int N,
+                                 cudaStream_t stream)
+    {
+    if (N == 0) return cudaSuccess;
+    k_gather_by_tag<<<(N + 255) / 256, 256, 0, stream>>>(out, by_tag, tag, N);
+    return cudaGetLastError();
+    }
+
+__global__ void k_tally_fold(double* __restrict__ acc, const float* __restrict__ e, unsigned int ts)
+    {
+    acc[0] += (double)*e;
+    acc[1u + (ts & 1u)] = (double)*e;
+    }
+
+cudaError_t launch_tally_fold(double* acc, const float* e, unsigned int ts, cudaStream_t stream)
+    {
+    k_tally_fold<<<1, 1, 0, stream>>>(acc, e, ts);
     return cudaGetLastError();
     }
 } // namespace b200

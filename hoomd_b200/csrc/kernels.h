@@ -55,16 +55,22 @@ struct OverflowHook
 cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* enable, cudaStream_t stream,
                                 OverflowHook hook = OverflowHook());
 unsigned int pick_pair_tpp(unsigned int N);
+unsigned int md_step_block(); // threads per CTA of k_md_step (particles per CTA = md_step_block() / lanes per particle)
 
 // Multi-GPU: ghost update fused into the MD step.  The owner of a boundary particle writes its new position (+ the
 // periodic shift of the direction) straight into the neighbor ranks' position buffers over NVLink, from the same lane
 // that has just integrated it -- the stores of the first CTAs overlap the force work of the CTAs still running.
 // (hoomd/CommunicatorGPU.cc:2500-2870 beginUpdateGhosts / finishUpdateGhosts: pack, MPI send/recv, unpack.)
+struct MgState;
 struct GhostSendTable            // device-resident, constant between reconnects
     {
     float shift[27][3];
     float4* peer_posA[27];
     float4* peer_posB[27];
+    // the all-ranks step barrier taken by the LAST CTA of k_md_step (comm.cuh:mg_warp_barrier): flag arrays of every rank
+    unsigned int world, rank;
+    unsigned long long* flags[8];
+    MgState* ms;
     };
 struct GhostSendArgs
     {
@@ -73,6 +79,9 @@ struct GhostSendArgs
     const unsigned char* pplan_n;
     const unsigned char* slot_dir;
     unsigned int pitch;          // local capacity Ncap == ghost base of every rank's position buffer
+    // boundary-first scheduling: CTA b works on particle chunk cta_order[b]; the chunks that hold a particle within the ghost
+    // layer of a split face come first, so their ghost stores cross NVLink while the interior chunks still compute
+    const unsigned int* cta_order;
     };
 
 // fused_step.cu -- kernels of the device-driven step loop (group = all particles)
@@ -97,6 +106,12 @@ struct FusedStepArgs
     // (2 parities x NVT_SLOTS slots, NVT_SLOT_STRIDE words apart) and their scale (a power of two); NDOF of the group,
     // coupling period tau; kT above is the set point
     float* nvt_state; unsigned long long* nvt_acc; double nvt_scale; unsigned int nvt_ndof; float nvt_tau;
+    // the integration method's ParticleGroup (NULL = group.all()): 1 byte per particle TAG, non-members are not integrated
+    // (the reference iterates m_group->getIndexArray(), hoomd/md/TwoStepNVEGPU.cc:48-70)
+    const unsigned char* group_flag;
+    // md.integrate.langevin(dscale=lambda): gamma = lambda * diameter[tag]; tally: reservoir energy bookkeeping
+    // (hoomd/md/TwoStepLangevin.cc:287-318,416-417): acc[0] = running sum of E_step, acc[1 + (ts & 1)] = E of step ts
+    const float* diameter; int use_lambda; float gamma_lambda; double* tally_acc;
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);
@@ -144,4 +159,12 @@ cudaError_t launch_rekey_tables(unsigned int* bond_n_idx, unsigned int* bond_lis
 cudaError_t launch_add_force(float4* net, float* net_virial, unsigned int net_pitch, const float4* f, const float* v,
                              unsigned int v_pitch, unsigned int N, bool virial, cudaStream_t stream);
 cudaError_t launch_merge_xyz_w(float4* out, const float4* a, const float4* b, unsigned int N, cudaStream_t stream);
+// sorted index array of the group members (ParticleGroup::getIndexArray after a particle sort): idx[k] ascending, *count
+cudaError_t launch_group_index(unsigned int* idx, unsigned int* count, const unsigned char* group_flag,
+                               const unsigned int* tag, unsigned int N, cudaStream_t stream);
+// out[i] = by_tag[tag[i]] (a per-tag table in the current particle order)
+cudaError_t launch_gather_by_tag(float* out, const float* by_tag, const unsigned int* tag, unsigned int N,
+                                 cudaStream_t stream);
+// host-driven Langevin step: fold the step's energy transfer *e into the tally (acc[0] += e, acc[1 + (ts & 1)] = e)
+cudaError_t launch_tally_fold(double* acc, const float* e, unsigned int ts, cudaStream_t stream);
 }

@@ -9,6 +9,7 @@
 #include "kernels.h"
 #include "decide.cuh"
 #include "tile.h"
+#include "comm.cuh"
 
 namespace b200
 {
@@ -31,7 +32,8 @@ template<class Evaluator> struct MdStepArgs
     int method; int limit; float limit_val; int zero_force; float kT; unsigned int seed; int noiseless_t;
     int copy_pos_on_last;     // this launch reads the alternate buffer: the final positions must land in pos_out
     const unsigned int* d_N;  // multi-GPU: live local particle count (N is the capacity the grid was sized for)
-    int mg;                   // multi-GPU: leave the rebuild decision to the all-ranks step barrier
+    int mg;                   // multi-GPU: 1 = the rebuild decision is left to the stand-alone step-barrier kernel; 2 = the
+                              // LAST CTA of this launch takes the all-ranks barrier (vote + decision) itself
     StepState* st; cudaGraphConditionalHandle handle; int use_cond;
     // cell-tile path (tile.cu)
     TileGeom tile; const unsigned int* cell_start; const uint4* ell4; unsigned int ell_pitch, ell_nmax;
@@ -39,6 +41,8 @@ template<class Evaluator> struct MdStepArgs
     const float4* extra_force; const float* extra_virial; unsigned int extra_virial_pitch; // second ForceCompute (bonds)
     GhostSendArgs gs; int gs_buffer; // multi-GPU: fused ghost update into the peers' buffer gs_buffer (0 = A, 1 = B)
     NvtState* nvt; unsigned long long* nvt_acc; double nvt_scale; unsigned int nvt_ndof; float nvt_tau; // TwoStepNVTMTK
+    const unsigned char* group_flag;                                  // the method's group by tag (NULL = all)
+    const float* diameter; int use_lambda; float gamma_lambda; double* tally_acc; // langevin dscale / tally
     };
 
 // write particle i's position into every ghost slot it feeds on the neighbor ranks (plain stores over NVLink)
@@ -94,6 +98,13 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
             }
         }
     const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
+    if (a.group_flag && !a.group_flag[a.tag[i]])
+        {
+        // not in the integration method's group: the force is reported, nothing moves (the ping-pong buffer still needs
+        // the unchanged position; a particle at rest never trips the distance check)
+        if (!last || a.copy_pos_on_last) a.pos_out[i] = pi4;
+        return false;
+        }
     const bool nve = a.method == 1, nvt = a.method == 3;
     // exp_fac: ONE thermostat factor serves step two(ts) and step one(ts+1) -- advanceThermostat runs between step one and
     // step two of the same update() (hoomd/md/TwoStepNVTMTK.cc:296), i.e. between two launches (md_step_nvt_begin)
@@ -104,7 +115,12 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     else if (nvt)
         nvt_step_two_body(v, acc, F, a.dt, exp_fac);
     else
-        langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
+        {
+        const unsigned int ptag = a.tag[i];
+        const float gamma = a.use_lambda ? __fmul_rn(a.gamma_lambda, a.diameter[ptag]) : a.gamma[type_i];
+        const float e = langevin_step_two_body(v, acc, F, ptag, ts2, a.seed, gamma, a.kT, a.dt, a.noiseless_t != 0, 3u);
+        if (a.tally_acc) mv2 = (double)e; // energy handed to the particle by the bath this step (md_step_finish sums it)
+        }
     a.accel[i] = acc;
     if (!last)
         {
@@ -199,6 +215,17 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
                                                unsigned int ts2 = 0)
     {
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    if (a.method == 2 && a.tally_acc)
+        {
+        // reservoir-energy tally: sum_j F_bd . v' of this step (double atomics: a diagnostic, order-dependent in the last bits)
+        for (int o = 16; o > 0; o >>= 1) mv2 += __shfl_xor_sync(0xffffffffu, mv2, o);
+        if ((threadIdx.x & 31) == 0 && mv2 != 0.0)
+            {
+            atomicAdd(a.tally_acc, mv2);
+            atomicAdd(a.tally_acc + 1u + (ts2 & 1u), mv2);
+            }
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.tally_acc[1u + ((ts2 + 1u) & 1u)] = 0.0; // slot of the next step
+        }
     if (a.method == 3 && !last)
         {
         // this CTA's share of sum(m v^2): warp shuffles, then one fixed-point atomic per warp that integrated particles
@@ -218,18 +245,22 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
                 }
             }
         }
+    __shared__ int s_is_last;
     if (threadIdx.x == 0)
         {
         // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
+        if (a.mg == 2) __threadfence_system(); // this CTA's ghost stores (ordered by the barrier above) before its ticket
         const unsigned long long old = atomicAdd(&st->ticket, inc);
-        if ((unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1)
+        const bool is_last = (unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1;
+        s_is_last = is_last ? 1 : 0;
+        if (is_last)
             {
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
             st->steps_left = steps_left - 1u;
             if (a.mg)
-                ; // the vote needs every rank: k_mg_step_barrier decides
+                ; // the vote needs every rank: the step barrier decides (below, or k_mg_step_barrier)
             else if (!last)
                 decide_body(st);
             else
@@ -238,8 +269,38 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
                 st->moved = 0u;
                 }
 #if (CUDART_VERSION >= 12040)
-            if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
+            if (a.use_cond && a.mg != 2) cudaGraphSetConditional(a.handle, st->need_rebuild);
 #endif
+            }
+        }
+    if (a.mg == 2)
+        {
+        // Multi-GPU: the last CTA of this rank to finish takes the all-ranks step barrier.  Every CTA's ghost stores into the
+        // peers' buffers are fenced before its ticket, so the flag this warp publishes orders them (RAW for the neighbors'
+        // next force phase); the wait orders every rank's reads of this step before anybody's next ghost stores (WAR); the
+        // payload bit is the global distance-check vote (hoomd/md/NeighborListGPU.cc:117-122), after which every rank takes
+        // the same NeighborList::needsUpdating decision.  The boundary chunks ran FIRST (cta_order), so their NVLink stores
+        // have long landed when the barrier is reached: the exchange overlaps the interior force work.
+        __syncthreads();
+        if (s_is_last && threadIdx.x < 32)
+            {
+            const GhostSendTable* t = a.gs.tab;
+            const bool moved_any = mg_warp_barrier(t->world, t->rank, t->flags, t->ms, 0,
+                                                   !last && *((volatile unsigned int*)&st->moved) != 0u);
+            if (threadIdx.x == 0)
+                {
+                st->moved = moved_any ? 1u : 0u;
+                if (!last && !st->abort)
+                    decide_body(st);
+                else
+                    {
+                    st->need_rebuild = 0u;
+                    st->moved = 0u;
+                    }
+#if (CUDART_VERSION >= 12040)
+                if (a.use_cond) cudaGraphSetConditional(a.handle, st->need_rebuild);
+#endif
+                }
             }
         }
     }
@@ -267,6 +328,8 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.gs = fa.gs; a.gs_buffer = copy_pos_on_last ? 0 : 1; // phase 0 writes B, phase 1 writes A
     a.nvt = (NvtState*)fa.nvt_state; a.nvt_acc = fa.nvt_acc; a.nvt_scale = fa.nvt_scale; a.nvt_ndof = fa.nvt_ndof;
     a.nvt_tau = fa.nvt_tau;
+    a.group_flag = fa.group_flag;
+    a.diameter = fa.diameter; a.use_lambda = fa.use_lambda; a.gamma_lambda = fa.gamma_lambda; a.tally_acc = fa.tally_acc;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

@@ -35,6 +35,8 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
     const unsigned int N = a.d_N ? *a.d_N : a.N;
+    // multi-GPU: chunks that touch the ghost layer are scheduled first (their ghost stores overlap the interior chunks)
+    const unsigned int chunk = a.gs.cta_order ? a.gs.cta_order[blockIdx.x] : blockIdx.x;
     __shared__ float s_exp_fac;
     md_step_nvt_begin(a, st, ts2); // NVT: thread 0 of block 0 advances the thermostat for this launch (no-op otherwise)
 
@@ -43,7 +45,7 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     pair_tables_load<Evaluator, SHIFT_MODE, MULTI_TYPE>(T, smem_raw, a.params, a.rcutsq, a.ronsq, a.ntypes);
         {
         const unsigned int slot = threadIdx.x / TPP;
-        const unsigned int i = blockIdx.x * PPB + slot;
+        const unsigned int i = chunk * PPB + slot;
         const unsigned int sub = threadIdx.x % TPP;
         const bool active = i < N;
         const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -72,7 +74,7 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
     bool moved = false;
     double mv2 = 0.0;
-    const unsigned int i = blockIdx.x * PPB + threadIdx.x;
+    const unsigned int i = chunk * PPB + threadIdx.x;
     if (threadIdx.x < PPB && i < N)
         {
         float vir[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};

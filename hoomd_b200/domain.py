@@ -143,6 +143,19 @@ class DomainSystem(System):
         return dict(N=int(out[0]), Ncap=int(out[1]), Gcap=int(out[2]), max_N=int(out[3]), max_migrants=int(out[4]),
                     max_ghosts_dir=int(out[5]), ghosts_sent=int(out[6]), step_barriers=int(out[7]))
 
+    def mg_timing(self):
+        """device-measured barrier waits: per kind (step, migrate, ghost plan, overflow vote) total microseconds, count and
+        mean microseconds per barrier; boundary / total chunks of the step kernel"""
+        out = (C.c_ulonglong * 10)()
+        self._check(_lib.lib().b200_sys_mg_timing(self.h, out))
+        names = ("step", "migrate", "ghost_plan", "overflow_vote")
+        res = {}
+        for k, n in enumerate(names):
+            ns, cnt = int(out[2 * k]), int(out[2 * k + 1])
+            res[n] = dict(total_us=ns * 1e-3, count=cnt, mean_us=(ns * 1e-3 / cnt) if cnt else 0.0)
+        res["boundary_chunks"], res["chunks"] = int(out[8]), int(out[9])
+        return res
+
     def ghosts(self):
         pos = np.empty((self.Gcap, 4), np.float32)
         tag = np.empty(self.Gcap, np.uint32)

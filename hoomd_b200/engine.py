@@ -142,9 +142,30 @@ class System:
         self._check(_lib.lib().b200_sys_add_nve(self.h, int(limit is not None), C.c_float(limit or 0.0),
                                                 int(zero_force)))
 
-    def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
+    def add_langevin(self, kT, seed, gamma=None, noiseless_t=False, dscale=None, tally=False):
+        """md.integrate.langevin(group, kT, seed, dscale, tally, noiseless_t); dscale = lambda: gamma = lambda * diameter"""
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(_lib.lib().b200_sys_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _p(g), int(noiseless_t)))
+        if dscale is not None or tally:
+            self._check(_lib.lib().b200_sys_set_langevin_options(self.h, int(dscale is not None),
+                                                                 C.c_float(dscale or 0.0), int(bool(tally))))
+
+    add_langevin_ex = add_langevin  # the name oracle.ref.RefSystem uses for the extended form
+
+    def langevin_reservoir_energy(self):
+        out = C.c_double(0)
+        self._check(_lib.lib().b200_sys_get_langevin_reservoir_energy(self.h, C.byref(out)))
+        return out.value
+
+    def set_diameters(self, diameter_by_tag):
+        d = np.ascontiguousarray(diameter_by_tag, np.float32)
+        assert len(d) == self.N
+        self._check(_lib.lib().b200_sys_set_diameters(self.h, _p(d)))
+
+    def set_group(self, tags=None):
+        """the ParticleGroup of the integration method: member tags (hoomd.group.tag_list / tags / type), None = group.all()"""
+        t = np.zeros(0, np.uint32) if tags is None else np.ascontiguousarray(tags, np.uint32)
+        self._check(_lib.lib().b200_sys_set_group(self.h, _p(t) if len(t) else None, len(t)))
 
     def set_box(self, Lx, Ly, Lz, scale_particles=True):
         """hoomd.update.box_resize at a period boundary: one BoxResizeUpdater::update towards the box (Lx, Ly, Lz)"""

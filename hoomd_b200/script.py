@@ -98,6 +98,7 @@ class _ParticleSnapshot:
         self.acceleration = np.zeros((N, 3), np.float32)
         self.typeid = np.zeros(N, np.uint32)
         self.mass = np.ones(N, np.float32)
+        self.diameter = np.ones(N, np.float32)
         self.image = np.zeros((N, 3), np.int32)
 
 
@@ -183,6 +184,7 @@ class _SystemData:
         self.vel4[:, :3] = p.velocity
         self.vel4[:, 3] = p.mass
         self.image = np.array(p.image, np.int32)
+        self.diameter = np.array(getattr(p, "diameter", np.ones(self.N)), np.float32)
         self.particles = _Particles(self)
         b = getattr(snapshot, "bonds", None) or _BondSnapshot()
         self.bond_types = list(b.types)
@@ -210,6 +212,7 @@ class _SystemData:
         q.mass[:] = self.vel4[:, 3]
         q.typeid[:] = self.pos4[:, 3].view(np.int32)
         q.image[:] = self.image
+        q.diameter[:] = self.diameter
         q.acceleration[:] = accel
         return snap
 
@@ -264,16 +267,68 @@ group = types.ModuleType("hoomd.group")
 
 
 class _Group:
-    def __init__(self, name):
+    """hoomd.group (hoomd/group.py): a named set of particle TAGS (ParticleGroup, hoomd/ParticleGroup.h); tags None = all"""
+
+    def __init__(self, name, tags=None):
+        _require_context()
+        if context.current.system is None:
+            raise RuntimeError("Cannot create a group before initialization")
         self.name = name
+        self.tags = None if tags is None else np.unique(np.asarray(tags, np.uint32))
+        if self.tags is not None and len(self.tags) and self.tags.max() >= context.current.system.N:
+            raise RuntimeError("Error creating group: particle tag out of bounds")
 
     def __len__(self):
-        return context.current.system.N
+        return context.current.system.N if self.tags is None else len(self.tags)
+
+    def is_all(self):
+        return self.tags is None or len(self.tags) == context.current.system.N
+
+
+def _group_type(type, name=None, update=False):
+    """group.type(type): every particle of that type at creation (hoomd/group.py:329-372)"""
+    sysd = context.current.system
+    if type not in sysd.types:
+        raise RuntimeError("Error creating group: type " + str(type) + " not found")
+    sysd.take_snapshot()
+    tid = sysd.pos4[:, 3].view(np.int32)
+    return _Group(name or ("type " + type), np.nonzero(tid == sysd.types.index(type))[0])
 
 
 group.all = lambda: _Group("all")
+group.tag_list = lambda name, tags: _Group(name, tags)                                   # hoomd/group.py:297-327
+group.tags = lambda tag_min, tag_max=None, name=None, update=False: _Group(              # hoomd/group.py:260-295
+    name or "tags %d-%d" % (tag_min, tag_min if tag_max is None else tag_max),
+    np.arange(tag_min, (tag_min if tag_max is None else tag_max) + 1))
+group.type = _group_type
 
 # ---- hoomd.update ---------------------------------------------------------------------------------------------------------
+
+class _Scheduled:
+    """period / phase bookkeeping of an analyzer or updater exactly as System::addAnalyzer / addUpdater and
+    analyzer_item::shouldExecute keep it (hoomd/System.cc:69-95,212-243, hoomd/System.h:205-266): the first execution is
+    start_step = ceil(cur / period) * period + phase (phase -1: the current step), every execution adds `period`."""
+
+    def _schedule(self, period, phase):
+        cur = context.current.timestep
+        self.period, self.phase = int(period), int(phase)
+        if self.phase >= 0:
+            self.next_execute = (cur // self.period + (1 if cur % self.period else 0)) * self.period + self.phase
+        else:
+            self.next_execute = cur
+
+    def should_execute(self, ts):
+        """true on the scheduled step; maintains state like shouldExecute (call once per step)"""
+        if ts == self.next_execute:
+            self.next_execute += self.period
+            return True
+        return False
+
+    def steps_until(self, ts):
+        """steps from ts to the next execution (None when it lies in the past and will never fire)"""
+        return self.next_execute - ts if self.next_execute > ts else None
+
+
 update = types.ModuleType("hoomd.update")
 
 
@@ -359,7 +414,7 @@ variant.linear_interp = _LinearInterp
 variant._setup_variant_input = _setup_variant_input
 
 
-class _BoxResize:
+class _BoxResize(_Scheduled):
     """hoomd.update.box_resize (hoomd/update.py:281-390, hoomd/BoxResizeUpdater.cc): every `period` steps the box is set to
     the variants' values and the particles are scaled with it (or wrapped into it).  Orthorhombic boxes only."""
 
@@ -384,27 +439,13 @@ class _BoxResize:
         self.enabled = True
         self.period = None if period is None else int(period)
         self.phase = int(phase)
-        self.created = ctx.timestep
         if period is None:
             self._apply(ctx.timestep)  # applied immediately, no periodic updates (hoomd/update.py:386-387)
         else:
             if self.period < 1:
                 raise RuntimeError("update.box_resize: period must be a positive integer")
+            self._schedule(self.period, self.phase)  # System::addUpdater
             ctx.box_resizers.append(self)
-
-    def _due(self, ts):
-        if not self.enabled or self.period is None:
-            return False
-        if self.phase < 0:
-            return (ts - self.created) % self.period == 0
-        return (ts + self.phase) % self.period == 0
-
-    def _next(self, ts):
-        """steps until this updater is due again, counted from ts (0 < n <= period)"""
-        for n in range(1, self.period + 1):
-            if self._due(ts + n):
-                return n
-        return self.period
 
     def _apply(self, ts):
         ctx = context.current
@@ -415,13 +456,15 @@ class _BoxResize:
         ctx.system.box = _BoxDim(float(L3[0]), float(L3[1]), float(L3[2]))
 
     def disable(self):
-        self.enabled = False
+        self.enabled = False  # the reference removes the updater from the system (hoomd/update.py:108-125)
 
     def enable(self):
+        if not self.enabled and self.period is not None:
+            self._schedule(self.period, self.phase)  # re-added with addUpdater (hoomd/update.py:127-145)
         self.enabled = True
 
     def set_period(self, period):
-        self.period = int(period)
+        self._schedule(int(period), self.phase)  # System::setUpdaterPeriod (hoomd/update.py:147-175)
 
 
 update.box_resize = _BoxResize
@@ -522,8 +565,8 @@ class _Pair:
         _require_context()
         if context.current.system is None:
             raise RuntimeError("Cannot create force before initialization")
-        if any(isinstance(f, _Pair) for f in context.current.forces):
-            raise RuntimeError("hoomd_b200: one pair force per system in this round")
+        if any(isinstance(f, _Pair) and f.enabled for f in context.current.forces):
+            raise RuntimeError("hoomd_b200: one enabled pair force per system in this round")
         self.global_r_cut, self.nlist, self.shift_mode = float(r_cut), nlist, 0
         self.pair_coeff = _Coeff()
         for k, v in self.defaults.items():
@@ -559,7 +602,9 @@ class _Pair:
         return out
 
     def get_energy(self, group=None):
-        f, _ = context.current.engine.forces(False)
+        """calcEnergySum of this ForceCompute alone (the pair component, not the net force)"""
+        _ensure_forces(components=True)
+        f, _ = context.current.engine.force_component(0)
         return float(f[:, 3].astype(np.float64).sum())
 
 
@@ -606,10 +651,8 @@ class _DPDConservative(_Pair):
     kind, required_coeffs = "dpd_conservative", ["A"]
 
     def set_params(self, coeff=None, mode=None):
-        if mode is not None:  # hoomd/md/pair.py:1502-1511: the potential is continuous at r_cut by construction
-            raise RuntimeError("Error setting DPD params: not possible to set energy shift mode for this potential")
-        if coeff is not None:
-            super().set_params(coeff=coeff)
+        """dpd_conservative has no energy shift modes (hoomd/md/pair.py:1518-1522 raises unconditionally)"""
+        raise RuntimeError("Not implemented for DPD Conservative")
 
 
 md.pair.dpd_conservative = _DPDConservative
@@ -659,6 +702,8 @@ class _Bond:
         context.current.engine_dirty = True
 
     def get_energy(self, group=None):
+        """calcEnergySum of the bond ForceCompute alone"""
+        _ensure_forces(components=True)
         f, _ = context.current.engine.force_component(1)
         return float(f[:, 3].astype(np.float64).sum())
 
@@ -696,8 +741,9 @@ class _ModeStandard:
 class _Method:
     def __init__(self, group_):
         _require_context()
-        if group_ is None or group_.name != "all":
-            raise RuntimeError("hoomd_b200: integration methods act on group.all() in this round")
+        if group_ is None or not isinstance(group_, _Group):
+            raise RuntimeError("integrate: a hoomd.group is required")
+        self.group = group_
         context.current.integration_methods.append(self)
         context.current.engine_dirty = True
         self.enabled = True
@@ -740,14 +786,18 @@ class _Langevin(_Method):
 
     def __init__(self, group, kT, seed, dscale=False, tally=False, noiseless_t=False, noiseless_r=False):
         super().__init__(group)
-        if dscale:
-            raise RuntimeError("hoomd_b200: dscale (gamma = lambda * diameter) is out of scope")
+        # dscale = False, or lambda: gamma = lambda * diameter (use_lambda, hoomd/md/integrate.py:905-916)
+        self.dscale = None if (dscale is False or dscale is None) else float(dscale)
+        self.tally = bool(tally)
         self.kT_variant, self.seed, self.noiseless_t = _setup_variant_input(kT), int(seed), bool(noiseless_t)
         self.gamma = {}
 
     def set_params(self, kT=None, tally=None):
         if kT is not None:
             self.kT_variant = _setup_variant_input(kT)
+            context.current.engine_dirty = True
+        if tally is not None:
+            self.tally = bool(tally)
             context.current.engine_dirty = True
 
     def set_gamma(self, a, gamma):
@@ -785,18 +835,38 @@ md.integrate.langevin = _Langevin
 analyze = types.ModuleType("hoomd.analyze")
 
 
-class _Log:
+class _Log(_Scheduled):
     QUANTITIES = {"temperature": "T", "kinetic_energy": "ke", "potential_energy": "pe", "pressure": "P"}
 
     def __init__(self, filename=None, quantities=(), period=1, header_prefix="", overwrite=False, phase=0, **kw):
         _require_context()
+        import re
         for q in quantities:
-            if q not in self.QUANTITIES and q not in ("pair_lj_energy", "nvt_mtk_reservoir_energy_all"):
+            # per-force energies are logged under "<force name>_energy": pair_<kind>_energy (hoomd/md/PotentialPair.h:200-215),
+            # bond_<kind>_energy (hoomd/md/PotentialBond.h:118-133); whether that force exists is checked when it is queried
+            if q not in self.QUANTITIES and q not in ("nvt_mtk_reservoir_energy_all", "langevin_reservoir_energy_all") \
+                    and not re.fullmatch(r"(pair|bond)_[a-z_]+_energy", q):
                 raise RuntimeError("Unknown log quantity " + q)
-        self.quantities, self.period, self.filename, self.rows = list(quantities), int(period), filename, []
+        self.quantities, self.filename, self.rows = list(quantities), filename, []
         self.header_prefix, self.overwrite, self._opened = header_prefix, bool(overwrite), False
+        self.enabled = True
+        self._schedule(int(period), int(phase))  # System::addAnalyzer
         context.current.loggers.append(self)
-        context.current.engine_dirty = True
+        # the virial is only evaluated when a logger asks for the pressure (pdata flags, hoomd/System.cc:855): a new
+        # pressure logger re-configures the engine, any other logger only reads what the engine computes anyway
+        if "pressure" in self.quantities:
+            context.current.engine_dirty = True
+
+    def set_period(self, period):
+        self._schedule(int(period), self.phase)  # System::setAnalyzerPeriod
+
+    def disable(self):
+        self.enabled = False
+
+    def enable(self):
+        if not self.enabled:
+            self._schedule(self.period, self.phase)
+        self.enabled = True
 
     def _write(self, row):
         """plain-text log file in the reference's format (hoomd/LogPlainTXT.cc:100-195): tab-delimited, a header line for a
@@ -814,11 +884,20 @@ class _Log:
             f.write("\t".join(["%d" % row[0]] + ["%.10g" % v for v in row[1:]]) + "\n")
 
     def query(self, quantity):
+        if quantity == "langevin_reservoir_energy_all":  # md.integrate.langevin(tally=True) (hoomd/md/integrate.py:918-921)
+            return context.current.engine.langevin_reservoir_energy()
         if quantity == "nvt_mtk_reservoir_energy_all":  # provided by md.integrate.nvt (log name + "_" + group name)
             return context.current.engine.nvt_reservoir_energy()
-        th = context.current.engine.thermo()
-        th["pair_lj_energy"] = th["pe"]
-        return float(th[self.QUANTITIES.get(quantity, quantity)])
+        ctx = context.current
+        if quantity not in self.QUANTITIES:
+            # the energy of ONE ForceCompute (ForceCompute::calcEnergySum, hoomd/ForceCompute.cc:82-102), not the total
+            kind, name = quantity.split("_", 1)[0], quantity[:-len("_energy")].split("_", 1)[1]
+            cls = _Pair if kind == "pair" else _Bond
+            active = [f for f in ctx.forces if isinstance(f, cls) and f.enabled and f.kind == name]
+            if not active:
+                raise RuntimeError("Unknown log quantity " + quantity + ": no such force is defined")
+            return active[0].get_energy()
+        return float(ctx.engine.thermo()[self.QUANTITIES[quantity]])
 
 
 analyze.log = _Log
@@ -840,8 +919,11 @@ def _configure_engine():
     if len(ljs) != 1:
         raise RuntimeError("hoomd_b200: exactly one md.pair force is supported, got %d" % len(ljs))
     lj = ljs[0]
+    accel = None
     if ctx.engine is not None:  # carry the state over
-        sysd.take_snapshot()
+        # accelerations too: for Langevin the stored a(t) contains the previous step's random and drag force, which step one
+        # of the next run must see (prepRun only computes a = F/m when no acceleration is set, IntegratorTwoStep.cc:379-392)
+        accel = sysd.take_snapshot().particles.acceleration.astype(np.float32)
         for m in methods:  # IntegratorVariables live in the SystemDefinition, not in the method (hoomd/IntegratorData.h)
             if isinstance(m, _NVT) and getattr(ctx.engine, "_has_nvt", False):
                 m._state = tuple(ctx.engine.nvt_state())
@@ -881,10 +963,33 @@ def _configure_engine():
             eng.set_nvt_state(*m._state)
     else:
         gamma = [m.gamma.get(tn, 1.0) for tn in sysd.types]
-        eng.add_langevin(m.kT, m.seed, gamma=gamma, noiseless_t=m.noiseless_t)
-    eng.set_sorter(ctx.sorter.period if ctx.sorter.enabled else 0)
+        eng.add_langevin(m.kT, m.seed, gamma=gamma, noiseless_t=m.noiseless_t, dscale=m.dscale, tally=m.tally)
+        if m.dscale is not None:
+            eng.set_diameters(sysd.diameter)
+    if not m.group.is_all():
+        eng.set_group(m.group.tags)
+    # the sorter is an updater created at step 0 with phase 0: it runs on multiples of its period (System::addUpdater), also
+    # after a re-configuration in the middle of a job.  b200_sys_set_sorter schedules from the engine's current time step.
+    sp = ctx.sorter.period if ctx.sorter.enabled else 0
+    eng.set_timestep((ctx.timestep + sp - 1) // sp * sp if sp else ctx.timestep)
+    eng.set_sorter(sp)
     eng.set_timestep(ctx.timestep)
-    ctx.engine, ctx.engine_dirty = eng, False
+    if accel is not None:
+        eng.set_accel(accel)
+    ctx.engine, ctx.engine_dirty, ctx.forces_stale = eng, False, True
+
+
+def _ensure_forces(components=False):
+    """The reference computes the forces in prepRun before the first step of a run, so analyzers at that step (and
+    force.get_energy right after a run) see real values; here the first force evaluation of a freshly configured engine is
+    made explicit.  components: the per-ForceCompute arrays are wanted -- the single-kernel MD step only keeps the NET
+    force, so they are re-evaluated at the current step (same neighbor list: NeighborList::compute is memoised per step)."""
+    ctx = context.current
+    if ctx.engine is None or ctx.engine_dirty:
+        _configure_engine()
+    if getattr(ctx, "forces_stale", False) or components:
+        ctx.engine.compute_forces(ctx.engine.timestep)
+        ctx.forces_stale = False
 
 
 def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_period=0, callback=None, quiet=False):
@@ -897,35 +1002,45 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
         _configure_engine()
     eng = ctx.engine
     tsteps = int(tsteps)
-    periods = [lg.period for lg in ctx.loggers] + ([int(callback_period)] if callback and callback_period else [])
+    cb_period = int(callback_period) if callback else 0
     done = 0
     while done < tsteps:
         ts = eng.timestep
-        nxt = tsteps - done
-        for p in periods:
-            nxt = min(nxt, p - ts % p)
-        for br in ctx.box_resizers:
-            if br.enabled:
-                nxt = min(nxt, br._next(ts))
-        ramp = [m for m in ctx.integration_methods if m.enabled and m.kT_is_variable]
-        if ramp:  # a temperature variant is evaluated at every step, like m_T->getValue(timestep) in the reference
-            nxt = 1
-        # System::run order within a step: analyzers, updaters, integrator (hoomd/System.cc:484-599)
+        # System::run order within a step (hoomd/System.cc:552-610): callback, analyzers, updaters, integrator
+        if callback and cb_period > 0 and ts % cb_period == 0:
+            rv = callback(ts)
+            if rv is not None and int(rv) < 0:
+                break  # a negative return value ends the run
         for lg in ctx.loggers:
-            if ts % lg.period == 0:
+            if lg.enabled and lg.should_execute(ts):
+                _ensure_forces()
+                eng = ctx.engine
                 lg.rows.append([ts] + [lg.query(q) for q in lg.quantities])
                 lg._write(lg.rows[-1])
-        if callback and callback_period and ts % callback_period == 0:
-            callback(ts)
         for br in ctx.box_resizers:
-            if br._due(ts):
+            if br.enabled and br.should_execute(ts):
                 br._apply(ts)
                 eng = ctx.engine
+        ramp = [m for m in ctx.integration_methods if m.enabled and m.kT_is_variable]
         for m in ramp:
             eng.set_kT(np.float32(m.kT_variant.getValue(ts)))
+        # advance to the next scheduled event
+        nxt = tsteps - done
+        if ramp:  # a temperature variant is evaluated at every step, like m_T->getValue(timestep) in the reference
+            nxt = 1
+        if cb_period > 0:
+            nxt = min(nxt, cb_period - ts % cb_period)
+        for item in list(ctx.loggers) + list(ctx.box_resizers):
+            if item.enabled:
+                n = item.steps_until(ts)
+                if n is not None:
+                    nxt = min(nxt, n)
         eng.run(nxt)
+        ctx.forces_stale = False
         done += nxt
     ctx.timestep = eng.timestep
+    if callback and cb_period == 0:
+        callback(ctx.timestep)  # callback_period 0: called once at the end of the run (hoomd/System.cc:617-621)
 
 
 def get_step():

@@ -35,6 +35,37 @@ def sc_lattice(n_side, a, kT=None, seed=42, ntypes=1, type_fractions=None):
     return pos, vel, float(L)
 
 
+def fcc_lattice(n_cells, rho, kT=None, seed=42, ntypes=1, type_fractions=None):
+    """4 * n_cells^3 particles on a face-centred cubic lattice at number density rho in a cubic box (hoomd.lattice.fcc +
+    hoomd.init.create_lattice, hoomd/lattice.py / hoomd/init.py:32-93).  n_cells = 40 gives BASELINE's 256,000 particles.
+    Types, velocities and the return value as sc_lattice."""
+    N = 4 * n_cells ** 3
+    a = (4.0 / rho) ** (1.0 / 3.0)
+    L = np.float32(n_cells * a)
+    g = np.arange(n_cells, dtype=np.float64) * a - n_cells * a / 2.0
+    x, y, z = np.meshgrid(g, g, g, indexing="ij")
+    corner = np.stack([x.ravel(), y.ravel(), z.ravel()], axis=1)
+    basis = np.array([[0.25, 0.25, 0.25], [0.25, 0.75, 0.75], [0.75, 0.25, 0.75], [0.75, 0.75, 0.25]]) * a
+    pos = np.zeros((N, 4), np.float32)
+    pos[:, :3] = (corner[:, None, :] + basis[None, :, :]).reshape(N, 3)
+    types = np.zeros(N, np.int32)
+    rng = np.random.default_rng(seed)
+    if ntypes > 1:
+        fr = np.asarray(type_fractions, np.float64)
+        counts = np.floor(fr * N).astype(int)
+        counts[0] += N - counts.sum()
+        types = np.repeat(np.arange(ntypes, dtype=np.int32), counts)
+        types = types[rng.permutation(N)]
+    pos[:, 3] = types.view(np.float32)
+    vel = np.zeros((N, 4), np.float32)
+    vel[:, 3] = 1.0
+    if kT is not None:
+        v = rng.normal(0.0, np.sqrt(kT), size=(N, 3))
+        v -= v.mean(axis=0)
+        vel[:, :3] = v
+    return pos, vel, float(L)
+
+
 def lj_liquid(N, rho=0.2, kT=1.2, seed=42):
     """LJ liquid initial lattice: N must be a cube; L = (N/rho)^(1/3)."""
     n_side = int(round(N ** (1.0 / 3.0)))

@@ -439,6 +439,18 @@ B200_API int b200_sys_setup_integrator(b200_system* s, float dt);
 B200_API int b200_sys_add_nve(b200_system* s, int limit, float limit_val, int zero_force);
 /* md.integrate.langevin(group=all, kT, seed) + set_gamma per type (gamma NULL = 1.0) */
 B200_API int b200_sys_add_langevin(b200_system* s, float kT, unsigned int seed, const float* gamma, int noiseless_t);
+/* md.integrate.langevin(..., dscale=lambda, tally=...) (hoomd/md/integrate.py:844-940): use_lambda: gamma = lambda * diameter
+ * instead of the per-type gamma (TwoStepLangevinBase.cc:29-70); tally: keep the reservoir energy (TwoStepLangevin::setTally).
+ * Call after b200_sys_add_langevin; resets the tally to zero. */
+B200_API int b200_sys_set_langevin_options(b200_system* s, int use_lambda, float lambda, int tally);
+/* ParticleData diameters by particle TAG (HOST pointer, N floats; default 1.0) -- read by langevin(dscale=...) */
+B200_API int b200_sys_set_diameters(b200_system* s, const float* diameter_by_tag);
+/* the "langevin_reservoir_energy" log quantity (TwoStepLangevin::getLogValue, hoomd/md/TwoStepLangevin.cc:61-80,416-417) */
+B200_API int b200_sys_get_langevin_reservoir_energy(b200_system* s, double* out);
+/* hoomd.group.*: the ParticleGroup the integration method acts on, as n member TAGS (HOST pointer); n = 0: group.all().
+ * The reference integrates m_group->getIndexArray() (hoomd/md/TwoStepNVEGPU.cc:48-70); non-members keep position and
+ * velocity, forces on them are still computed; NDOF = 3 * members - 3 (IntegratorTwoStep::getNDOF). */
+B200_API int b200_sys_set_group(b200_system* s, const unsigned int* member_tags, unsigned int n);
 /* langevin / nvt set_params(kT=...), or a temperature variant evaluated by the caller per step (setT of the method) */
 B200_API int b200_sys_set_temperature(b200_system* s, float kT);
 /* md.nlist.cell(dist_check=False): rebuild when the check period is hit instead of when a particle moved r_buff/2
@@ -533,6 +545,10 @@ B200_API unsigned int b200_sys_get_n(b200_system* s);
 B200_API int b200_sys_set_tags(b200_system* s, const unsigned int* tags);
 /* out: {N local, Ncap, Gcap, max N seen, max migrants/direction, max ghosts/direction, ghosts sent now, step barriers} */
 B200_API int b200_sys_mg_stats(b200_system* s, unsigned long long* out8);
+/* out10: {wait ns, count} of the four barrier kinds (0 = the per-step all-ranks barrier, 1..3 = the rebuild phases:
+ * migration, ghost plan, overflow vote) measured on the device from arriving at the barrier to seeing every rank, then the
+ * number of boundary chunks of k_md_step and the total number of chunks (Communicator profiling, hoomd/Communicator.cc) */
+B200_API int b200_sys_mg_timing(b200_system* s, unsigned long long* out10);
 /* this rank's ghost region (Gcap entries; unused slots hold x = 1e30): positions and global tags */
 B200_API int b200_sys_mg_get_ghosts(b200_system* s, float* pos4, unsigned int* tag);
 

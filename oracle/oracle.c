@@ -493,18 +493,9 @@ static int nl_compute(orc_system* s, unsigned int ts) /* NeighborList::compute, 
     return 0;
     }
 
-/* ---- PotentialBond<evaluator>::computeForces (PotentialBond.h:155-300) + EvaluatorBondFENE.h:95-133 /
- * EvaluatorBondHarmonic.h:75-92, then Integrator::computeNetForce (Integrator.cc:308-420): net = pair + bond ------------- */
-static int compute_bond_forces(orc_system* s)
+/* one bond: dx = minImage(pos_b - pos_a), force_divr and the FULL bond energy; returns 1 on "bond out of bounds" */
+static int bond_eval(orc_system* s, unsigned int b, f3* dx_out, float* force_divr_out, float* bond_eng_out)
     {
-    const unsigned int N = s->N;
-    const int compute_virial = s->compute_virial;
-    memcpy(s->pair_force, s->net_force, sizeof(f4) * N);
-    memcpy(s->pair_virial, s->net_virial, sizeof(float) * 6 * (size_t)N);
-    memset(s->bond_force, 0, sizeof(f4) * N);
-    memset(s->bond_virial, 0, sizeof(float) * 6 * (size_t)N);
-    for (unsigned int b = 0; b < s->nbonds; b++)
-        {
         const unsigned int ia = s->bond_a[b], ib = s->bond_b[b], t = s->bond_type[b]; /* rtag == identity */
         f3 dx = {s->pos[ib].x - s->pos[ia].x, s->pos[ib].y - s->pos[ia].y, s->pos[ib].z - s->pos[ia].z};
         dx = box_min_image(&s->box, dx);
@@ -551,6 +542,28 @@ static int compute_bond_forces(orc_system* s)
             if (!isfinite(force_divr)) force_divr = 0.0f;
             bond_eng = 0.5f * K * (r_0 - r) * (r_0 - r);
             }
+    *dx_out = dx;
+    *force_divr_out = force_divr;
+    *bond_eng_out = bond_eng;
+    return 0;
+    }
+
+/* ---- PotentialBond<evaluator>::computeForces (PotentialBond.h:155-300) + EvaluatorBondFENE.h:95-133 /
+ * EvaluatorBondHarmonic.h:75-92, then Integrator::computeNetForce (Integrator.cc:308-420): net = pair + bond ------------- */
+static int compute_bond_forces(orc_system* s)
+    {
+    const unsigned int N = s->N;
+    const int compute_virial = s->compute_virial;
+    memcpy(s->pair_force, s->net_force, sizeof(f4) * N);
+    memcpy(s->pair_virial, s->net_virial, sizeof(float) * 6 * (size_t)N);
+    memset(s->bond_force, 0, sizeof(f4) * N);
+    memset(s->bond_virial, 0, sizeof(float) * 6 * (size_t)N);
+    for (unsigned int b = 0; b < s->nbonds; b++)
+        {
+        const unsigned int ia = s->bond_a[b], ib = s->bond_b[b];
+        f3 dx;
+        float force_divr = 0.0f, bond_eng = 0.0f;
+        if (bond_eval(s, b, &dx, &force_divr, &bond_eng)) return 1;
         bond_eng *= 0.5f;
         {
         float bv[6] = {0, 0, 0, 0, 0, 0};
@@ -707,11 +720,48 @@ static int pair_eval(int kind, float rsq, float rcutsq, float p1, float p2, floa
     return 1;
     }
 
+/* one listed pair (i, j) of PotentialPair::computeForces (PotentialPair.h:361-470): dx = minImage(pos_i - pos_j), the
+ * evaluator, then the XPLOR smoothing; returns 0 when the pair does not contribute */
+static int pair_ij(const orc_system* s, f3 pi, unsigned int typei, unsigned int j, f3* dx_out, float* force_divr_out,
+                   float* pair_eng_out)
+    {
+    const unsigned int nt = s->ntypes;
+    f3 dx = {pi.x - s->pos[j].x, pi.y - s->pos[j].y, pi.z - s->pos[j].z};
+    const unsigned int typej = as_uint(s->pos[j].w);
+    dx = box_min_image(&s->box, dx);
+    const float rsq = dot3(dx);
+    const unsigned int tp = typei * nt + typej;
+    const float rcutsq = s->rcutsq[tp];
+    float ronsq = 0.0f;
+    int energy_shift = 0;
+    if (s->shift_mode == 2) ronsq = s->ronsq[tp];
+    if (s->shift_mode == 1) energy_shift = 1;
+    else if (s->shift_mode == 2 && ronsq > rcutsq) energy_shift = 1;
+    float force_divr = 0.0f, pair_eng = 0.0f;
+    if (!pair_eval(s->pair_kind, rsq, rcutsq, s->lj1[tp], s->lj2[tp], s->p3 ? s->p3[tp] : 0.0f,
+                   s->p4 ? s->p4[tp] : 0.0f, energy_shift, &force_divr, &pair_eng))
+        return 0;
+    if (s->shift_mode == 2 && rsq >= ronsq && rsq < rcutsq)
+        {
+        float old_pair_eng = pair_eng, old_force_divr = force_divr;
+        float xplor_denom_inv = 1.0f / ((rcutsq - ronsq) * (rcutsq - ronsq) * (rcutsq - ronsq));
+        float rsq_minus_r_cut_sq = rsq - rcutsq;
+        float sw = rsq_minus_r_cut_sq * rsq_minus_r_cut_sq * (rcutsq + 2.0f * rsq - 3.0f * ronsq) * xplor_denom_inv;
+        float ds_dr_divr = 12.0f * (rsq - ronsq) * rsq_minus_r_cut_sq * xplor_denom_inv;
+        pair_eng = old_pair_eng * sw;
+        force_divr = sw * old_force_divr - ds_dr_divr * old_pair_eng;
+        }
+    *dx_out = dx;
+    *force_divr_out = force_divr;
+    *pair_eng_out = pair_eng;
+    return 1;
+    }
+
 /* ---- PotentialPair<EvaluatorPairLJ>::computeForces (PotentialPair.h:309-522, EvaluatorPairLJ.h:137-158), full list ------ */
 static int compute_forces(orc_system* s, unsigned int ts)
     {
     if (nl_compute(s, ts)) return 1;
-    const unsigned int nt = s->ntypes, N = s->N;
+    const unsigned int N = s->N;
     const int compute_virial = s->compute_virial;
     memset(s->net_force, 0, sizeof(f4) * N);
     memset(s->net_virial, 0, sizeof(float) * 6 * (size_t)N);
@@ -725,32 +775,10 @@ static int compute_forces(orc_system* s, unsigned int ts)
         const unsigned int head = s->head[i], size = s->n_neigh[i];
         for (unsigned int k = 0; k < size; k++)
             {
-            const unsigned int j = s->nlist[head + k];
-            f3 dx = {pi.x - s->pos[j].x, pi.y - s->pos[j].y, pi.z - s->pos[j].z};
-            const unsigned int typej = as_uint(s->pos[j].w);
-            dx = box_min_image(&s->box, dx);
-            const float rsq = dot3(dx);
-            const unsigned int tp = typei * nt + typej;
-            const float rcutsq = s->rcutsq[tp];
-            float ronsq = 0.0f;
-            int energy_shift = 0;
-            if (s->shift_mode == 2) ronsq = s->ronsq[tp];
-            if (s->shift_mode == 1) energy_shift = 1;
-            else if (s->shift_mode == 2 && ronsq > rcutsq) energy_shift = 1;
+            f3 dx;
             float force_divr = 0.0f, pair_eng = 0.0f;
-            if (pair_eval(s->pair_kind, rsq, rcutsq, s->lj1[tp], s->lj2[tp], s->p3 ? s->p3[tp] : 0.0f,
-                          s->p4 ? s->p4[tp] : 0.0f, energy_shift, &force_divr, &pair_eng))
+            if (pair_ij(s, pi, typei, s->nlist[head + k], &dx, &force_divr, &pair_eng))
                 {
-                if (s->shift_mode == 2 && rsq >= ronsq && rsq < rcutsq)
-                    {
-                    float old_pair_eng = pair_eng, old_force_divr = force_divr;
-                    float xplor_denom_inv = 1.0f / ((rcutsq - ronsq) * (rcutsq - ronsq) * (rcutsq - ronsq));
-                    float rsq_minus_r_cut_sq = rsq - rcutsq;
-                    float sw = rsq_minus_r_cut_sq * rsq_minus_r_cut_sq * (rcutsq + 2.0f * rsq - 3.0f * ronsq) * xplor_denom_inv;
-                    float ds_dr_divr = 12.0f * (rsq - ronsq) * rsq_minus_r_cut_sq * xplor_denom_inv;
-                    pair_eng = old_pair_eng * sw;
-                    force_divr = sw * old_force_divr - ds_dr_divr * old_pair_eng;
-                    }
                 {
                 float force_div2r = force_divr * 0.5f;
                 fi.x += dx.x * force_divr; fi.y += dx.y * force_divr; fi.z += dx.z * force_divr;
@@ -1238,6 +1266,52 @@ void orc_get_cell_list(orc_system* s, unsigned int* cell_size, float* xyzf4)
     {
     if (cell_size) memcpy(cell_size, s->cell_size, 4 * (size_t)s->ncells);
     if (xyzf4) memcpy(xyzf4, s->xyzf, sizeof(f4) * (size_t)s->ncells * s->cl_Nmax);
+    }
+
+/* Parity-test scale (not a reference quantity): per particle the sums of ABSOLUTE pair / bond contributions that make up
+ * its force, energy and virial on the current neighbor list and bond set -- out[0*N+i] = sum_j |f_ij| (vector norm),
+ * out[1*N+i] = sum_j |V_ij / 2|, out[(2+c)*N+i] = sum_j |virial_c term|, in double.  |a - b| <= 1e-5 * scale is the FP32
+ * "1e-5 relative" bar of BASELINE.json for sums whose terms cancel.  Call after orc_compute_forces. */
+void orc_get_force_scales(orc_system* s, int which /* 1 pair, 2 bond, 3 both */, double* out8N)
+    {
+    const unsigned int N = s->N;
+    memset(out8N, 0, sizeof(double) * 8 * (size_t)N);
+    for (unsigned int i = 0; (which & 1) && i < N; i++)
+        {
+        const f3 pi = {s->pos[i].x, s->pos[i].y, s->pos[i].z};
+        const unsigned int typei = as_uint(s->pos[i].w);
+        const unsigned int head = s->head[i], size = s->n_neigh[i];
+        for (unsigned int k = 0; k < size; k++)
+            {
+            f3 dx;
+            float force_divr = 0.0f, pair_eng = 0.0f;
+            if (!pair_ij(s, pi, typei, s->nlist[head + k], &dx, &force_divr, &pair_eng)) continue;
+            const double fd = fabs((double)force_divr);
+            out8N[0 * (size_t)N + i] += fd * sqrt((double)dx.x * dx.x + (double)dx.y * dx.y + (double)dx.z * dx.z);
+            out8N[1 * (size_t)N + i] += 0.5 * fabs((double)pair_eng);
+            const double c[6] = {(double)dx.x * dx.x, (double)dx.x * dx.y, (double)dx.x * dx.z, (double)dx.y * dx.y,
+                                 (double)dx.y * dx.z, (double)dx.z * dx.z};
+            for (int q = 0; q < 6; q++) out8N[(2 + q) * (size_t)N + i] += 0.5 * fd * fabs(c[q]);
+            }
+        }
+    if (s->bond_kind >= 0 && (which & 2))
+        for (unsigned int b = 0; b < s->nbonds; b++)
+            {
+            f3 dx;
+            float force_divr = 0.0f, bond_eng = 0.0f;
+            if (bond_eval(s, b, &dx, &force_divr, &bond_eng)) continue;
+            const double fd = fabs((double)force_divr);
+            const double c[6] = {(double)dx.x * dx.x, (double)dx.x * dx.y, (double)dx.x * dx.z, (double)dx.y * dx.y,
+                                 (double)dx.y * dx.z, (double)dx.z * dx.z};
+            const unsigned int ab[2] = {s->bond_a[b], s->bond_b[b]};
+            for (int e = 0; e < 2; e++)
+                {
+                const unsigned int i = ab[e];
+                out8N[0 * (size_t)N + i] += fd * sqrt(c[0] + c[3] + c[5]);
+                out8N[1 * (size_t)N + i] += 0.5 * fabs((double)bond_eng);
+                for (int q = 0; q < 6; q++) out8N[(2 + q) * (size_t)N + i] += 0.5 * fd * fabs(c[q]);
+                }
+            }
     }
 
 void orc_get_thermo(orc_system* s, double* out5) /* ComputeThermo.cc:195-380, FP32 properties */

@@ -56,6 +56,8 @@ int orc_run(orc_system* s, unsigned int nsteps, double* elapsed_s);
 int orc_step_one(orc_system* s, unsigned int ts);
 int orc_step_two(orc_system* s, unsigned int ts, const float* net_force4);
 void orc_get_forces(orc_system* s, float* force4, float* virial6 /* [6*N] */);
+/* parity-test scales: sums of absolute pair / bond contributions per particle, double[8*N] (see oracle.c) */
+void orc_get_force_scales(orc_system* s, int which /* 1 pair, 2 bond, 3 both */, double* out8N);
 unsigned int orc_get_nlist_size(orc_system* s);
 void orc_get_nlist(orc_system* s, unsigned int* n_neigh, unsigned int* head, unsigned int* nlist, unsigned int len);
 void orc_get_stats(orc_system* s, unsigned long long* out4); /* updates, forced, dim.x, Nmax[0] */

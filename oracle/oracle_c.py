@@ -54,6 +54,7 @@ def lib():
         L.orc_step_one.argtypes = [vp, C.c_uint]
         L.orc_step_two.argtypes = [vp, C.c_uint, vp]
         L.orc_get_forces.argtypes = [vp, vp, vp]
+        L.orc_get_force_scales.argtypes = [vp, C.c_int, vp]
         L.orc_get_nlist_size.argtypes = [vp]
         L.orc_get_nlist.argtypes = [vp, vp, vp, vp, C.c_uint]
         L.orc_get_stats.argtypes = [vp, vp]
@@ -236,6 +237,13 @@ class OracleSystem:
         v = np.empty((6, self.N), np.float32) if virial else None
         lib().orc_get_forces(self.h, _ptr(f), _ptr(v))
         return f, v
+
+    def force_scales(self, which=3):
+        """parity-test scales (call after compute_forces): sum_j |f_ij| [N], sum_j |V_ij/2| [N], sum_j |virial term| [6, N]
+        over the pair (which & 1) and bond (which & 2) contributions"""
+        out = np.zeros((8, self.N), np.float64)
+        lib().orc_get_force_scales(self.h, which, _ptr(out))
+        return out[0], out[1], out[2:]
 
     def nlist(self):
         n = np.empty(self.N, np.uint32)

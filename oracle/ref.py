@@ -45,6 +45,14 @@ def lib():
         _lib.ref_get_nvt_reservoir_energy.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_last_error.restype = C.c_char_p
         _lib.ref_get_lj_energy.restype = C.c_double
+        _lib.ref_get_langevin_reservoir_energy.restype = C.c_double
+        _lib.ref_get_langevin_reservoir_energy.argtypes = [C.c_void_p]
+        _lib.ref_set_group_tags.argtypes = [C.c_void_p, C.c_void_p, C.c_uint]
+        _lib.ref_set_diameters.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.ref_cell_compute_tdb.argtypes = [C.c_void_p, C.c_uint]
+        _lib.ref_get_cell_tdb.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.ref_add_langevin_ex.argtypes = [C.c_void_p, C.c_float, C.c_uint, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                             C.c_int]
         for name in ("ref_destroy", "ref_last_error", "ref_get_N", "ref_get_timestep", "ref_get_virial_pitch",
                      "ref_get_nlist_size", "ref_get_lj_energy", "ref_sort_now"):
             getattr(_lib, name).argtypes = [C.c_void_p]
@@ -162,6 +170,25 @@ class RefSystem:
     def add_nve(self, limit=None, zero_force=False):
         self._check(lib().ref_add_nve(self.h, int(limit is not None), C.c_float(limit or 0.0), int(zero_force)))
 
+    def set_group(self, tags=None):
+        """the group of the integration methods added AFTER this call: member tags (hoomd.group.tag_list), None = all"""
+        t = np.zeros(0, np.uint32) if tags is None else np.ascontiguousarray(tags, np.uint32)
+        self._check(lib().ref_set_group_tags(self.h, _ptr(t), C.c_uint(len(t))))
+
+    def set_diameters(self, diameter):
+        d = np.ascontiguousarray(diameter, np.float32)
+        assert len(d) == self.N
+        lib().ref_set_diameters(self.h, _ptr(d))
+
+    def add_langevin_ex(self, kT, seed, gamma=None, noiseless_t=False, dscale=None, tally=False):
+        """md.integrate.langevin(..., dscale=lambda, tally=...): gamma = lambda * diameter when dscale is given"""
+        g = None if gamma is None else np.ascontiguousarray(gamma, np.float32)
+        self._check(lib().ref_add_langevin_ex(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), C.c_int(bool(noiseless_t)),
+                                              C.c_int(dscale is not None), C.c_float(dscale or 0.0), C.c_int(bool(tally))))
+
+    def langevin_reservoir_energy(self):
+        return float(lib().ref_get_langevin_reservoir_energy(self.h))
+
     def add_langevin(self, kT, seed, gamma=None, noiseless_t=False):
         g = None if gamma is None else np.ascontiguousarray(np.broadcast_to(gamma, (self.ntypes,)), np.float32)
         self._check(lib().ref_add_langevin(self.h, C.c_float(kT), C.c_uint(seed), _ptr(g), int(noiseless_t)))
@@ -270,6 +297,16 @@ class RefSystem:
         adj = np.empty((ncell, nadj), np.uint32)
         lib().ref_get_cell_list(self.h, _ptr(size), _ptr(xyzf), _ptr(adj))
         return dict(dim=dim, Nmax=nmax, cell_size=size, xyzf=xyzf, cell_adj=adj)
+
+    def cell_tdb(self, ts=0):
+        """switches CellList::setComputeTDB(true), recomputes the cell list at ts and returns the (ncell, Nmax, 4)
+        (type, diameter, body, 0) entries; cell_list() afterwards returns the matching cell_size / xyzf"""
+        self._check(lib().ref_cell_compute_tdb(self.h, C.c_uint(ts)))
+        d = np.zeros(5, np.uint32)
+        lib().ref_get_cell_dims(self.h, _ptr(d))
+        tdb = np.empty((int(d[0]) * int(d[1]) * int(d[2]), int(d[3]), 4), np.float32)
+        lib().ref_get_cell_tdb(self.h, _ptr(tdb))
+        return tdb
 
     def thermo(self, ts=None):
         out = np.zeros(5, np.float64)

@@ -41,6 +41,7 @@ struct RefSystem
     std::shared_ptr<SystemDefinition> sysdef;
     std::shared_ptr<ParticleData> pdata;
     std::shared_ptr<ParticleGroup> group_all;
+    std::shared_ptr<ParticleGroup> group_method; // the group the integration method acts on (default: all)
     std::shared_ptr<CellList> cl;
     std::shared_ptr<NeighborListBinned> nlist;
     std::shared_ptr<ForceCompute> lj;     // the pair force: PotentialPairLJ or another PotentialPair<evaluator>
@@ -323,7 +324,7 @@ int ref_add_nve(void* h, int limit, float limit_val, int zero_force)
     {
     RefSystem* s = static_cast<RefSystem*>(h);
     REF_TRY(s)
-    s->nve = std::shared_ptr<TwoStepNVE>(new TwoStepNVE(s->sysdef, s->group_all, true));
+    s->nve = std::shared_ptr<TwoStepNVE>(new TwoStepNVE(s->sysdef, s->group_method ? s->group_method : s->group_all, true));
     if (limit) s->nve->setLimit(limit_val);
     s->nve->setZeroForce(zero_force);
     s->integrator->removeAllIntegrationMethods();
@@ -338,12 +339,67 @@ int ref_add_langevin(void* h, float kT, unsigned int seed, const float* gamma, i
     REF_TRY(s)
     std::shared_ptr<Variant> T(new VariantConst(kT));
     s->langevin = std::shared_ptr<TwoStepLangevin>(
-        new TwoStepLangevin(s->sysdef, s->group_all, T, seed, false, Scalar(0.0), noiseless_t, false, ""));
+        new TwoStepLangevin(s->sysdef, s->group_method ? s->group_method : s->group_all, T, seed, false, Scalar(0.0),
+                            noiseless_t, false, ""));
     if (gamma)
         for (unsigned int t = 0; t < s->pdata->getNTypes(); t++)
             s->langevin->setGamma(t, gamma[t]);
     s->integrator->removeAllIntegrationMethods();
     s->integrator->addIntegrationMethod(s->langevin);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! md.integrate.langevin(group, kT, seed, dscale=lambda, tally) (hoomd/md/integrate.py:844-940): gamma = lambda * diameter
+//! when use_lambda, the reservoir energy is tallied when tally (TwoStepLangevin::setTally)
+int ref_add_langevin_ex(void* h, float kT, unsigned int seed, const float* gamma, int noiseless_t, int use_lambda,
+                        float lambda, int tally)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<Variant> T(new VariantConst(kT));
+    s->langevin = std::shared_ptr<TwoStepLangevin>(
+        new TwoStepLangevin(s->sysdef, s->group_method ? s->group_method : s->group_all, T, seed, use_lambda != 0,
+                            Scalar(lambda), noiseless_t, false, ""));
+    if (gamma)
+        for (unsigned int t = 0; t < s->pdata->getNTypes(); t++)
+            s->langevin->setGamma(t, gamma[t]);
+    s->langevin->setTally(tally != 0);
+    s->integrator->removeAllIntegrationMethods();
+    s->integrator->addIntegrationMethod(s->langevin);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! the "langevin_reservoir_energy" log quantity (TwoStepLangevin::getLogValue, hoomd/md/TwoStepLangevin.cc:61-73)
+double ref_get_langevin_reservoir_energy(void* h)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    bool my = false;
+    return s->langevin ? (double)s->langevin->getLogValue("langevin_reservoir_energy", s->timestep, my) : 0.0;
+    }
+
+//! per-particle diameters (ParticleData::getDiameters), index order
+void ref_set_diameters(void* h, const float* diameter)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    ArrayHandle<Scalar> d(s->pdata->getDiameters(), access_location::host, access_mode::overwrite);
+    for (unsigned int i = 0; i < s->pdata->getN(); i++) d.data[i] = diameter[i];
+    }
+
+//! hoomd.group.tag_list: the integration methods created AFTER this call act on these member tags
+//! (ParticleGroup(sysdef, member_tags), hoomd/ParticleGroup.cc); n = 0 restores group.all()
+int ref_set_group_tags(void* h, const unsigned int* tags, unsigned int n)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    if (n == 0)
+        s->group_method.reset();
+    else
+        {
+        std::vector<unsigned int> members(tags, tags + n);
+        s->group_method = std::shared_ptr<ParticleGroup>(new ParticleGroup(s->sysdef, members));
+        }
     REF_CATCH(s, 1)
     return 0;
     }
@@ -355,11 +411,12 @@ int ref_add_nvt(void* h, float kT, float tau)
     RefSystem* s = static_cast<RefSystem*>(h);
     REF_TRY(s)
     std::shared_ptr<Variant> T(new VariantConst(kT));
-    s->thermo_nvt = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, s->group_all, "nvt"));
-    s->nvt = std::shared_ptr<TwoStepNVTMTK>(new TwoStepNVTMTK(s->sysdef, s->group_all, s->thermo_nvt, tau, T, ""));
+    std::shared_ptr<ParticleGroup> grp = s->group_method ? s->group_method : s->group_all;
+    s->thermo_nvt = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, grp, "nvt"));
+    s->nvt = std::shared_ptr<TwoStepNVTMTK>(new TwoStepNVTMTK(s->sysdef, grp, s->thermo_nvt, tau, T, ""));
     s->integrator->removeAllIntegrationMethods();
     s->integrator->addIntegrationMethod(s->nvt);
-    s->thermo_nvt->setNDOF(s->integrator->getNDOF(s->group_all));
+    s->thermo_nvt->setNDOF(s->integrator->getNDOF(grp));
     REF_CATCH(s, 1)
     return 0;
     }
@@ -690,6 +747,26 @@ void ref_get_cell_list(void* h, unsigned int* cell_size, float* xyzf4, unsigned 
         ArrayHandle<unsigned int> a(s->cl->getCellAdjArray(), access_location::host, access_mode::read);
         memcpy(cell_adj, a.data, sizeof(unsigned int) * s->cl->getCellAdjIndexer().getNumElements());
         }
+    }
+
+//! CellList::setComputeTDB(true) (what NeighborListGPUBinned asks for, hoomd/md/NeighborListGPUBinned.cc:30-33) and a
+//! recompute of the cell list at \a ts; read the geometry (ref_get_cell_dims) and the arrays afterwards
+int ref_cell_compute_tdb(void* h, unsigned int ts)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    s->cl->setComputeTDB(true);
+    s->cl->compute(ts);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! getTDBArray(): (type, diameter, body, 0) per cell-list slot, [Nmax * ncell] Scalar4
+void ref_get_cell_tdb(void* h, float* tdb4)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    ArrayHandle<Scalar4> a(s->cl->getTDBArray(), access_location::host, access_mode::read);
+    memcpy(tdb4, a.data, sizeof(Scalar4) * s->cl->getCellListIndexer().getNumElements());
     }
 
 //! ComputeThermo at timestep ts: out = {KE, PE, temperature, pressure, ndof}

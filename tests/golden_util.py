@@ -46,6 +46,56 @@ def _cmp_nlist(s, g, exact_order):
             assert np.array_equal(np.sort(seg), np.sort(want)), i
 
 
+
+# ---- the north_star bar: "forces, energies and virials must agree within 1e-5 relative in FP32" ----------------------------
+# A per-particle force is a sum of ~30 pair terms that largely cancel, so "relative" is taken against what the sum is made
+# of: |a_i - b_i| <= 1e-5 * sum_j |term_ij| (force: vector norms |f_ij|; energy: |V_ij / 2|; virial component c: the
+# |virial_c term|).  The sums of absolute terms come from the C restatement (oracle.c:orc_get_force_scales), evaluated on the
+# same state with the same force field.
+PARITY_RTOL = 1e-5
+
+
+def abs_scales(configure, pos, box, ntypes=1, n_bond_types=0, which=3):
+    """configure(system) applies the force field (setup_lj / setup_pair / set_bonds / ...) to an OracleSystem built on
+    (pos, box); returns (sum|f_ij| [N], sum|V_ij/2| [N], sum|virial term| [6, N]) in index order."""
+    from oracle import oracle_c
+    o = oracle_c.OracleSystem(pos, box, ntypes=ntypes, n_bond_types=n_bond_types, threads=os.cpu_count() or 1)
+    configure(o)
+    o.set_virial(True)
+    o.compute_forces(0)
+    return o.force_scales(which)
+
+
+def assert_parity(fr, vr, f, v, scales, what="", rtol=PARITY_RTOL, verbose=True):
+    """|f - fr| <= rtol * scale per particle for force vectors, energies and (when given) virial components; totals of the
+    energy and of the virial trace within rtol of the sum of absolute terms as well.  Returns the measured maxima."""
+    sf, se, sv = scales
+    f64 = np.float64
+    df = np.linalg.norm(fr[:, :3].astype(f64) - f[:, :3].astype(f64), axis=1)
+    de = np.abs(fr[:, 3].astype(f64) - f[:, 3].astype(f64))
+    out = {}
+
+    def ratio(d, sc, name):
+        assert np.all(d[sc == 0.0] == 0.0), "%s %s: difference where nothing contributes" % (what, name)
+        m = sc > 0.0
+        r = float((d[m] / sc[m]).max()) if m.any() else 0.0
+        out[name] = r
+        assert r <= rtol, "%s: %s differs by %.3g of sum|terms| (bar %.1g)" % (what, name, r, rtol)
+
+    ratio(df, sf, "force")
+    ratio(de, se, "energy")
+    out["energy_total"] = abs(float(fr[:, 3].astype(f64).sum() - f[:, 3].astype(f64).sum())) / max(float(se.sum()), 1e-300)
+    assert out["energy_total"] <= rtol, (what, out)
+    if v is not None and vr is not None:
+        dv = np.abs(vr.astype(f64) - v.astype(f64))
+        ratio(dv.reshape(-1), sv.reshape(-1), "virial")
+        tr = lambda x: (x[0].astype(f64) + x[3] + x[5]).sum()
+        out["virial_total"] = abs(float(tr(vr) - tr(v))) / max(float((sv[0] + sv[3] + sv[5]).sum()), 1e-300)
+        assert out["virial_total"] <= rtol, (what, out)
+    if verbose:
+        print("parity %s: max |d| / sum|terms|: %s (bar %.0e)" % (what, ", ".join("%s %.2e" % kv for kv in out.items()), rtol))
+    return out
+
 def check_forces(make, rtol, bit_exact=False):
     g = load("liquid_forces")
     L = float(g["L"])
@@ -60,16 +110,9 @@ def check_forces(make, rtol, bit_exact=False):
             assert np.array_equal(f.view(np.uint32), fr.view(np.uint32)), name
             assert np.array_equal(v.view(np.uint32), vr.view(np.uint32)), name
             continue
-        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-        assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, name
-        escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
-        assert (np.abs(fr[:, 3] - f[:, 3]) / escale).max() < rtol, name
-        vscale = np.maximum(np.abs(vr), np.abs(vr).mean())
-        assert (np.abs(vr - v) / vscale).max() < rtol, name
-        # totals: 1e-5 relative (north_star)
-        for a, b in ((fr[:, 3], f[:, 3]), (vr[0] + vr[3] + vr[5], v[0] + v[3] + v[5])):
-            sa, sb = a.astype(np.float64).sum(), b.astype(np.float64).sum()
-            assert abs(sa - sb) < 1e-5 * abs(sa), name
+        sc = abs_scales(lambda o: o.setup_lj(r_cut=3.0, r_buff=0.4, shift_mode=mode, r_on=2.0 if mode == 2 else None),
+                        g["pos"], (L, L, L))
+        assert_parity(fr, vr, f, v, sc, "liquid_forces/" + name, rtol)
 
 
 def check_half_steps(make):
@@ -122,15 +165,18 @@ def check_trajectories(make, bit_exact, pos_tol=2e-4, vel_tol=2e-3):
             assert abs(th[k] - w) <= 2e-4 * abs(w), (method, k, th[k], w)
 
 
+def _kg_fields(s, g):
+    s.set_bonds(g["bonds"])
+    s.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, shift_mode=1)
+    s.setup_fene(k=30.0, r0=1.5)
+    s.exclusions_from_bonds(True)
+
+
 def make_kg(make, g, vel=True, image=False):
     """Kremer-Grest system of the kremer_grest fixture on implementation `make` (WCA + FENE + bond exclusions)."""
     L = float(g["L"])
-    rc = 2.0 ** (1.0 / 6.0)
     s = make(g["pos"], (L, L, L), 1, vel=g["vel"] if vel else None, image=g["image"] if image else None, n_bond_types=1)
-    s.set_bonds(g["bonds"])
-    s.setup_lj(r_cut=rc, r_buff=0.4, shift_mode=1)
-    s.setup_fene(k=30.0, r0=1.5)
-    s.exclusions_from_bonds(True)
+    _kg_fields(s, g)
     return s
 
 
@@ -142,6 +188,7 @@ def _rel(a, b):
 def check_kremer_grest(make, rtol, bit_exact=False, traj_bit_exact=False, pos_tol=2e-4, vel_tol=2e-3):
     """filtered neighbor list (exact, incl. order), per-ForceCompute forces / virials, net force, 40-step trajectories"""
     g = load("kremer_grest")
+    L = float(g["L"])
     s = make_kg(make, g)
     s.set_virial(True)
     s.compute_forces(0)
@@ -156,14 +203,11 @@ def check_kremer_grest(make, rtol, bit_exact=False, traj_bit_exact=False, pos_to
             # the energy goes through logf: allow the last bit
             assert np.abs(f[:, 3] - fr[:, 3]).max() <= 4e-6 * np.abs(fr[:, 3]).max(), name
             continue
-        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-        assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, name
-        assert _rel(f[:, 3], fr[:, 3]) < rtol, name
-        assert _rel(v, vr) < rtol, name
-    want = g["force_pair"] + g["force_bond"]
-    fscale = np.maximum(np.linalg.norm(want[:, :3], axis=1, keepdims=True), np.abs(want[:, :3]).mean())
-    assert (np.abs(want[:, :3] - fnet[:, :3]) / fscale).max() < max(rtol, 1e-6)
-    assert _rel(vnet, g["virial_pair"] + g["virial_bond"]) < max(rtol, 1e-6)
+        sc = abs_scales(lambda o: _kg_fields(o, g), g["pos"], (L, L, L), n_bond_types=1, which=which + 1)
+        assert_parity(fr, vr, f, v, sc, "kremer_grest/" + name, rtol)
+    sc = abs_scales(lambda o: _kg_fields(o, g), g["pos"], (L, L, L), n_bond_types=1)
+    assert_parity(g["force_pair"] + g["force_bond"], g["virial_pair"] + g["virial_bond"], fnet, vnet, sc,
+                  "kremer_grest/net", max(rtol, 1e-6))
     for method in ("nve", "langevin"):
         s = make_kg(make, g, image=True)
         s.set_virial(True)
@@ -213,10 +257,9 @@ def check_pair_evaluators(make, rtol, bit_exact=False, kinds=None, pos_tol=2e-4,
             if bit_exact:
                 assert eq(f, fr) and eq(v, vr), (kind, name)
                 continue
-            fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-            assert (np.abs(fr[:, :3] - f[:, :3]) / fscale).max() < rtol, (kind, name)
-            assert _rel(f[:, 3], fr[:, 3]) < rtol, (kind, name)
-            assert _rel(v, vr) < rtol, (kind, name)
+            sc = abs_scales(lambda o: o.setup_pair(kind, r_cut=rc, r_buff=0.4, shift_mode=mode,
+                                                   r_on=ron if mode == 2 else None, **co), g["pos"], (L, L, L))
+            assert_parity(fr, vr, f, v, sc, "%s/%s" % (kind, name), rtol)
         s = make(g["pos"], (L, L, L), 1, vel=g["vel"], image=g["image"])
         s.setup_pair(kind, r_cut=rc, r_buff=0.4, shift_mode=1, **co)
         s.setup_integrator(0.005)

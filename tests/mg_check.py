@@ -3,9 +3,17 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
         tests/mg_check.py [n_side] [steps]
 
-The domain-decomposed engine (ghosts/migration over NVLink) against the single-GPU engine on the same global snapshot:
-ghost sets equal to a brute-force numpy construction, forces within 1e-5 relative, particle count conserved through
-migrations, trajectories agreeing to FP32 round-off growth, same rebuild count.  Prints MG_CHECK_OK on rank 0.
+The domain-decomposed engine (ghosts / migration over NVLink) against the UNMODIFIED reference CPU classes
+(oracle/_ref, RefSystem) on the same global snapshot, every comparison keyed by particle TAG:
+  * ghost sets equal to a brute-force numpy construction, ghost positions are periodic images of their owners;
+  * forces and per-particle energies within 1e-5 of the sums of absolute pair terms (north_star bar,
+    golden_util.assert_parity) -- neighbor sets are therefore the reference's: a missing or extra pair inside r_cut would
+    show up at 1e-2;
+  * neighbor-list row lengths equal to the reference's per tag (ghost rows included through their owners);
+  * after `steps` NVE steps: particle count conserved through migrations, EQUAL number of list rebuilds, trajectories
+    agreeing to FP32 round-off growth.
+`parity_pass()` is also what `bench.py --gpus N` runs before timing (its line carries parity_checked / max_force_err).
+Prints MG_CHECK_OK on rank 0.
 """
 import os
 import sys
@@ -14,6 +22,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def expected_ghost_tags(pos, L, lo, hi, per, r_ghost):
@@ -36,98 +45,113 @@ def expected_ghost_tags(pos, L, lo, hi, per, r_ghost):
     return np.sort(np.concatenate(out))
 
 
-def main():
-    import torch
+def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, check_ghosts=True, verbose=True):
+    """One domain-decomposed system against RefSystem on the same snapshot (every rank calls this; torch.distributed must be
+    initialised).  Returns a dict of measured maxima; raises AssertionError on a parity failure."""
     import torch.distributed as dist
-    import hoomd_b200
-    from hoomd_b200 import workloads, domain
+    import golden_util as G
+    from hoomd_b200 import domain
+    from oracle import ref as R
 
-    n_side = int(sys.argv[1]) if len(sys.argv) > 1 else 24
-    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    torch.cuda.set_device(local_rank)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    rho, kT, r_cut, r_buff = 0.2, 1.2, 3.0, 0.4
-    pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
-    rng = np.random.default_rng(5)
-    pos[:, :3] += rng.normal(0, 0.12, (len(pos), 3)).astype(np.float32)
-    pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+    rank, world = dist.get_rank(), dist.get_world_size()
     N = len(pos)
     box = (L, L, L)
+    if not R.available():
+        raise RuntimeError("oracle/_ref/libhoomd_ref.so is missing: the multi-GPU parity pass needs the reference classes")
 
-    # ---- single-GPU reference on every rank's own GPU (cheap at this size) ----
-    ref = hoomd_b200.System(pos, box, vel4=vel, device=local_rank)
-    ref.set_pair_mode(0)
-    ref.setup_lj(r_cut=r_cut, r_buff=r_buff)
-    ref.compute_forces(0)
-    f_ref = ref.forces(False)[0]
-
-    mg = domain.DomainSystem(pos, box, r_ghost=r_cut + r_buff, vel4=vel, device=local_rank)
+    mg = domain.DomainSystem(pos, box, r_ghost=r_cut + r_buff, vel4=vel, image=image, device=local_rank)
     mg.setup_lj(r_cut=r_cut, r_buff=r_buff)
     mg.compute_forces(0)
     counts = [None] * world
     dist.all_gather_object(counts, mg._sync_n())
     assert sum(counts) == N, counts
 
-    # ghosts vs brute force
-    lo, hi, per = domain.local_bounds(box, mg.grid, rank)
-    gpos, gtag = mg.ghosts()
-    exp = expected_ghost_tags(pos, box, lo, hi, per, np.float32(r_cut + r_buff))
-    assert np.array_equal(np.sort(gtag), exp), (len(gtag), len(exp))
-    # ghost positions are periodic images of their owners
-    d = gpos[:, :3] - pos[gtag, :3]
-    d -= np.round(d / np.float32(L)) * np.float32(L)
-    assert np.abs(d).max() < 1e-5
+    if check_ghosts:
+        lo, hi, per = domain.local_bounds(box, mg.grid, rank)
+        gpos, gtag = mg.ghosts()
+        exp = expected_ghost_tags(pos, box, lo, hi, per, np.float32(r_cut + r_buff))
+        assert np.array_equal(np.sort(gtag), exp), (len(gtag), len(exp))
+        d = gpos[:, :3] - pos[gtag, :3]
+        d -= np.round(d / np.float32(L)) * np.float32(L)
+        assert np.abs(d).max() < 1e-5
 
-    # forces by tag
+    # ---- the reference's answer (CPU classes, full list) and the scales of the 1e-5 bar, on every rank's host cores ----
+    r = R.RefSystem(pos, box, vel4=vel, image=image)
+    r.setup_lj(r_cut=r_cut, r_buff=r_buff, full=True)
+    r.compute_forces(0)
+    f_ref = r.forces(False)[0]
+    rn = r.nlist()[0]
+    sc = G.abs_scales(lambda o: o.setup_lj(r_cut=r_cut, r_buff=r_buff), pos, box)
+
     p = mg.particles()
+    tag = p["tag"]
     f_mg = mg.forces(False)[0]
-    fr = f_ref[p["tag"]]
-    scale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-    err = (np.abs(fr[:, :3] - f_mg[:, :3]) / scale).max()
-    assert err < 1e-4, err
-    eerr = np.abs(fr[:, 3] - f_mg[:, 3]).max() / np.abs(fr[:, 3]).mean()
-    assert eerr < 1e-4, eerr
+    out = G.assert_parity(f_ref[tag], None, f_mg, None, (sc[0][tag], sc[1][tag], sc[2][:, tag]),
+                          "rank %d of %d vs reference" % (rank, world), verbose=False)
+    gn = mg.nlist(counts_only=True)[0][:mg.N]
+    assert np.array_equal(gn, rn[tag]), "neighbor-list row lengths differ from the reference's"
 
     # ---- trajectories ----
-    for s in (ref, mg):
-        s.setup_integrator(0.005)
-        s.add_nve()
-        s.set_sorter(100)
-    ref.run(steps)
-    mg.run(steps)
-    counts = [None] * world
-    dist.all_gather_object(counts, mg._sync_n())
-    assert sum(counts) == N, counts
-    g = mg.gather()
-    assert np.array_equal(g["tag"], np.arange(N, dtype=np.uint32)), "particles lost or duplicated"
-    a = ref.particles()
-    order = np.argsort(a["tag"])
-    rp, rv, ri = a["pos"][order], a["vel"][order], a["image"][order]
-    # unwrapped positions (migration re-wraps; compare modulo the box)
-    dpos = g["pos"][:, :3] - rp[:, :3]
-    dpos -= np.round(dpos / np.float32(L)) * np.float32(L)
-    perr, verr = np.abs(dpos).max(), np.abs(g["vel"][:, :3] - rv[:, :3]).max()
-    unw_mg = g["pos"][:, :3].astype(np.float64) + g["image"] * float(L)
-    unw_rf = rp[:, :3].astype(np.float64) + ri * float(L)
-    uerr = np.abs(unw_mg - unw_rf).max()
-    st_ref, st_mg, ms = ref.stats(), mg.stats(), mg.mg_stats()
-    if rank == 0:
-        print("N=%d grid=%s counts=%s force_err=%.2e pe_err=%.2e pos_err=%.2e vel_err=%.2e unwrapped_err=%.2e "
-              "rebuilds ref=%d mg=%d mg_stats=%s" % (N, mg.grid, counts, err, eerr, perr, verr, uerr,
-                                                     st_ref["updates"], st_mg["updates"], ms), flush=True)
-    tol = 5e-3 * max(1.0, steps / 300.0)
-    assert perr < tol and uerr < tol, (perr, uerr)
-    assert abs(st_ref["updates"] - st_mg["updates"]) <= max(1, st_ref["updates"] // 20)
-    assert ms["max_migrants"] > 0 or steps < 100, "no particle ever migrated: the test did not exercise migration"
+    res = dict(max_force_err=out["force"], max_energy_err=out["energy"])
+    if steps:
+        for s in (r, mg):
+            s.setup_integrator(0.005)
+            s.add_nve()
+            s.set_sorter(100)
+        r.run(steps)
+        mg.run(steps)
+        dist.all_gather_object(counts, mg._sync_n())
+        assert sum(counts) == N, counts
+        g = mg.gather()
+        assert np.array_equal(g["tag"], np.arange(N, dtype=np.uint32)), "particles lost or duplicated"
+        a = r.particles()
+        order = np.argsort(a["tag"])
+        rp, rv, ri = a["pos"][order], a["vel"][order], a["image"][order]
+        dpos = g["pos"][:, :3] - rp[:, :3]
+        dpos -= np.round(dpos / np.float32(L)) * np.float32(L)     # migration re-wraps: compare modulo the box
+        unw_mg = g["pos"][:, :3].astype(np.float64) + g["image"] * float(L)
+        unw_rf = rp[:, :3].astype(np.float64) + ri * float(L)
+        res.update(pos_err=float(np.abs(dpos).max()), vel_err=float(np.abs(g["vel"][:, :3] - rv[:, :3]).max()),
+                   unwrapped_err=float(np.abs(unw_mg - unw_rf).max()), rebuilds_ref=int(r.nlist_stats()["updates"]),
+                   rebuilds_mg=int(mg.stats()["updates"]), mg_stats=mg.mg_stats())
+        tol = 5e-3 * max(1.0, steps / 300.0)
+        assert res["pos_err"] < tol and res["unwrapped_err"] < tol, res
+        assert res["rebuilds_ref"] == res["rebuilds_mg"], res
+    # the worst rank's figures
+    allres = [None] * world
+    dist.all_gather_object(allres, {k: v for k, v in res.items() if k != "mg_stats"})
+    for k in ("max_force_err", "max_energy_err", "pos_err", "vel_err", "unwrapped_err"):
+        if k in res:
+            res[k] = max(q[k] for q in allres)
+    res.update(N=N, grid=list(mg.grid), counts=counts, steps=steps)
+    if verbose and rank == 0:
+        print("mg parity vs reference: %s" % res, flush=True)
+    mg.close()
+    return res
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from hoomd_b200 import workloads
+
+    n_side = int(sys.argv[1]) if len(sys.argv) > 1 else 24
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    rho, kT = 0.2, 1.2
+    pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
+    rng = np.random.default_rng(5)
+    pos[:, :3] += rng.normal(0, 0.12, (len(pos), 3)).astype(np.float32)
+    pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+    res = parity_pass(pos, vel, None, L, steps, local_rank)
+    assert res["mg_stats"]["max_migrants"] > 0 or steps < 100, "no particle ever migrated: migration was not exercised"
     dist.barrier()
     if rank == 0:
         print("MG_CHECK_OK", flush=True)
-    mg.close()
-    ref.close()
     dist.destroy_process_group()
 
 

@@ -90,12 +90,17 @@ def test_forces_and_list_vs_reference(hb, ref, kind, excl):
     assert np.array_equal(rn, gn) and np.array_equal(rh, gh)
     for i in range(len(rn)):
         assert np.array_equal(rl[rh[i]:rh[i] + rn[i]], gl[gh[i]:gh[i] + gn[i]]), i
+    from oracle import oracle_c
+    o, _ = _melt(oracle_c.OracleSystem, kind, excl, 0)
+    o.set_particles(st["pos"], st["vel"], st["image"])
+    o.compute_forces(0)
     for which in (0, 1):
         fr, vr = r2.force_component(which, True)
         fg, vg = g.force_component(which, True)
-        assert (np.abs(fr[:, :3] - fg[:, :3]) / _fscale(fr)).max() < 1e-5, which
-        assert G._rel(fg[:, 3], fr[:, 3]) < 1e-5, which
-        assert G._rel(vg, vr) < 1e-5, which
+        G.assert_parity(fr, vr, fg, vg, o.force_scales(which + 1), "%s excl=%s %s force" % (kind, excl, ("pair", "bond")[which]))
+    # Integrator::computeNetForce: net = pair + bond in FP32, in the order the forces were added
+    (fp, vp), (fb, vb) = r2.force_component(0, True), r2.force_component(1, True)
+    G.assert_parity(fp + fb, vp + vb, g.forces()[0], g.forces()[1], o.force_scales(3), "net force")
     # Newton's third law over the bond force and over the pair force: the totals vanish
     fb = g.force_component(1)[0][:, :3].astype(np.float64)
     assert np.abs(fb.sum(axis=0)).max() < 1e-3 * np.abs(fb).sum(axis=0).max() / len(fb) ** 0.5

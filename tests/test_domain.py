@@ -114,8 +114,9 @@ def test_world_size_2_gloo(tmp_path):
 
 
 @pytest.mark.gpu
-def test_multigpu_parity_vs_single_gpu():
-    """tests/mg_check.py under torchrun on 2 GPUs: ghosts, forces, migration, trajectories vs the single-GPU engine."""
+def test_multigpu_parity_vs_reference():
+    """tests/mg_check.py under torchrun on 2 GPUs: ghosts, forces, list row lengths, migration, rebuild counts and
+    trajectories of the domain-decomposed engine vs the reference's CPU classes (oracle/_ref)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")

@@ -71,9 +71,8 @@ def test_two_types_vs_reference_and_modes(hb, ref, kind):
     g.compute_forces(0)
     fr, vr = r.forces()
     fg, vg = g.forces()
-    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-    assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < 1e-5
-    assert G._rel(fg[:, 3], fr[:, 3]) < 1e-5 and G._rel(vg, vr) < 1e-5
+    sc = G.abs_scales(lambda o: o.setup_pair(kind, r_cut=rc, r_buff=0.3, shift_mode=1, **co), pos, (L, L, L), ntypes=2)
+    G.assert_parity(fr, vr, fg, vg, sc, "two-type " + kind)
     r.setup_integrator(0.004)
     r.add_langevin(1.0, 9, gamma=[1.0, 2.0])
     r.run(120)

@@ -7,9 +7,13 @@ forces / energies / virials within 1e-5 relative in FP32, integration half steps
 import numpy as np
 import pytest
 
+import golden_util as G
+
 pytestmark = pytest.mark.gpu
 
-FORCE_RTOL = 1e-5  # relative to the per-particle scale sum_j |f_ij| (FP32 summation-order bound), see _force_scale
+# north_star: 1e-5 relative in FP32, against the sums of absolute pair terms sum_j |f_ij| / |V_ij/2| / |virial term| that a
+# particle's force / energy / virial is made of (golden_util.assert_parity; scales from oracle.c:orc_get_force_scales)
+FORCE_RTOL = G.PARITY_RTOL
 
 
 def _have_gpu():
@@ -144,23 +148,12 @@ def test_forces_liquid_1e5(ref, hb):
         s.compute_forces(0)
     _assert_nlist_equal(r2, g)
     fr, vr = r2.forces()
+    sc = G.abs_scales(lambda o: o.setup_lj(**lj), st["pos"], (L, L, L))
     for tpp in (1, 2, 4, 8, 16, 32):
         g.set_tuning(pair_tpp=tpp)
         g.compute_forces(0)
         fg, vg = g.forces()
-        fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-        assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < FORCE_RTOL * 10, tpp
-        # energies: relative to |pe_i| floor'd by the mean
-        escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
-        assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < FORCE_RTOL * 10, tpp
-        vscale = np.maximum(np.abs(vr), np.abs(vr).mean())
-        assert (np.abs(vr - vg) / vscale).max() < FORCE_RTOL * 10, tpp
-        # totals within 1e-5 relative
-        assert abs(fr[:, 3].astype(np.float64).sum() - fg[:, 3].astype(np.float64).sum()) \
-            < FORCE_RTOL * abs(fr[:, 3].astype(np.float64).sum()), tpp
-        W_r = (vr[0] + vr[3] + vr[5]).astype(np.float64).sum()
-        W_g = (vg[0] + vg[3] + vg[5]).astype(np.float64).sum()
-        assert abs(W_r - W_g) < FORCE_RTOL * abs(W_r), tpp
+        G.assert_parity(fr, vr, fg, vg, sc, "liquid tpp %d" % tpp, FORCE_RTOL)
 
 
 @pytest.mark.parametrize("mode", [1, 2])
@@ -174,10 +167,8 @@ def test_shift_modes(ref, hb, mode):
         s.compute_forces(0)
     fr, _ = r.forces(False)
     fg, _ = g.forces(False)
-    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-    assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < 1e-4
-    escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
-    assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < 1e-4
+    G.assert_parity(fr, None, fg, None, G.abs_scales(lambda o: o.setup_lj(**lj), pos, (L, L, L)), "shift mode %d" % mode,
+                    FORCE_RTOL)
 
 
 def test_nve_half_steps_bit_exact(ref, hb):
@@ -403,12 +394,8 @@ def test_kob_andersen_small_vs_reference(ref, hb):
     _assert_nlist_equal(r, g)
     fr, vr = r.forces()
     fg, vg = g.forces()
-    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-    assert (np.abs(fr[:, :3] - fg[:, :3]) / fscale).max() < FORCE_RTOL * 10
-    escale = np.maximum(np.abs(fr[:, 3]), np.abs(fr[:, 3]).mean())
-    assert (np.abs(fr[:, 3] - fg[:, 3]) / escale).max() < FORCE_RTOL * 10
-    assert abs(fr[:, 3].astype(np.float64).sum() - fg[:, 3].astype(np.float64).sum()) \
-        < FORCE_RTOL * abs(fr[:, 3].astype(np.float64).sum())
+    G.assert_parity(fr, vr, fg, vg, G.abs_scales(lambda o: o.setup_lj(**lj), pos, (L, L, L), ntypes=2), "Kob-Andersen 1728",
+                    FORCE_RTOL)
     for s in (r, g):
         s.setup_integrator(0.002)
         s.add_langevin(1.0, 7, gamma=[1.0, 1.5])
@@ -457,8 +444,8 @@ def test_full_size_lj64k_properties(hb):
 
 
 def test_full_size_ka256k_properties(hb):
-    """BASELINE config 3 at full size (N = 262,144 = 64^3, closest cube to 256k), Langevin kT = 1.0"""
-    pos, vel, L = _ka_system(hb, 64)
+    """BASELINE config 3 at full size (N = 256,000: fcc 40^3 start), Langevin kT = 1.0"""
+    pos, vel, L = hb.workloads.fcc_lattice(40, 1.2, kT=1.0, seed=42, ntypes=2, type_fractions=[0.8, 0.2])
     pos[:, :3] += np.random.default_rng(3).normal(0, 0.03, (len(pos), 3)).astype(np.float32)
     g = hb.System(pos, (L, L, L), ntypes=2, vel4=vel)
     g.setup_lj(shift_mode=1, r_buff=0.3, **hb.workloads.KA_PARAMS)

@@ -284,8 +284,20 @@ def test_variant_and_box_resize_surface_without_gpu():
         hoomd.update.box_resize()  # nothing to resize (hoomd/update.py:344-346)
     with pytest.raises(RuntimeError):
         hoomd.update.box_resize(xy=0.5)  # triclinic: out of scope
+    # scheduling as System::addUpdater / updater_item::shouldExecute (hoomd/System.cc:212-243, System.h:205-242)
     br = hoomd.update.box_resize(L=hoomd.variant.linear_interp([(0, 8.0), (100, 6.0)]), period=10)
-    assert br._due(0) and not br._due(5) and br._due(20) and br._next(3) == 7 and br._next(10) == 10
+    assert br.next_execute == 0 and br.should_execute(0) and br.next_execute == 10
+    assert not br.should_execute(5) and br.steps_until(3) == 7 and br.steps_until(10) is None
+    # phase: start_step = ceil(cur / period) * period + phase, then += period: 3, 13, 23 (not 7, 17)
+    b3 = hoomd.update.box_resize(L=7.0, period=10, phase=3)
+    fired = [t for t in range(30) if b3.should_execute(t)]
+    assert fired == [3, 13, 23]
+    lg = hoomd.analyze.log(filename=None, quantities=["temperature"], period=5, phase=2)
+    assert [t for t in range(20) if lg.should_execute(t)] == [2, 7, 12, 17]
+    b3.disable(); lg.disable()
+    # phase -1: starts on the current step
+    bm = hoomd.update.box_resize(L=7.0, period=4, phase=-1)
+    assert [t for t in range(10) if bm.should_execute(t)] == [0, 4, 8]
 
 
 @pytest.mark.gpu
@@ -416,3 +428,63 @@ def test_log_file_format(tmp_path):
     lg3 = hoomd.analyze.log(filename=fn, quantities=["temperature"], period=10, overwrite=True)
     lg3._write([0, 1.0])
     assert open(fn).read().splitlines() == ["timestep\ttemperature", "0\t1"]
+
+
+@pytest.mark.gpu
+def test_first_logged_row_sees_real_forces_and_per_force_energies():
+    """The reference computes forces in prepRun before the step loop, so analyze.log's row at the first step holds the real
+    potential energy and a pressure with its virial term; pair_lj_energy / bond_fene_energy are the energies of ONE
+    ForceCompute each (ForceCompute::calcEnergySum), not the total."""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref/libhoomd_ref.so not built")
+    from hoomd_b200 import workloads
+    hoomd = _fresh()
+    from hoomd import md
+    pos, vel, L, bonds = workloads.polymer_lattice(6, 8, rho=0.85, kT=1.0, seed=3)
+    pos[:, :3] += np.random.default_rng(1).normal(0, 0.03, (len(pos), 3)).astype(np.float32)
+    snap = hoomd.data.make_snapshot(N=len(pos), box=hoomd.data.boxdim(L=L), particle_types=["A"], bond_types=["polymer"])
+    snap.particles.position[:] = pos[:, :3]
+    snap.particles.velocity[:] = vel[:, :3]
+    snap.bonds.resize(len(bonds))
+    snap.bonds.group[:] = bonds
+    hoomd.init.read_snapshot(snap)
+    nl = md.nlist.cell()
+    wca = md.pair.lj(r_cut=2.0 ** (1.0 / 6.0), nlist=nl)
+    wca.pair_coeff.set("A", "A", epsilon=1.0, sigma=1.0)
+    wca.set_params(mode="shift")
+    fene = md.bond.fene()
+    fene.bond_coeff.set("polymer", k=30.0, r0=1.5, sigma=1.0, epsilon=1.0)
+    md.integrate.mode_standard(dt=0.005)
+    md.integrate.nve(group=hoomd.group.all())
+    log = hoomd.analyze.log(filename=None, period=10, quantities=["potential_energy", "pressure", "pair_lj_energy",
+                                                                 "bond_fene_energy", "kinetic_energy"])
+    with pytest.raises(RuntimeError):
+        hoomd.analyze.log(filename=None, quantities=["bogus_quantity"], period=10)
+    hoomd.run(10)
+    row0 = dict(zip(["ts"] + log.quantities, log.rows[0]))
+    assert row0["ts"] == 0 and len(log.rows) == 1
+    # the same state on the reference's CPU classes
+    r = R.RefSystem(pos, (L, L, L), vel4=vel, n_bond_types=1)
+    r.set_bonds(bonds)
+    r.setup_lj(r_cut=2.0 ** (1.0 / 6.0), r_buff=0.4, full=True, shift_mode=1)
+    r.setup_fene(k=30.0, r0=1.5)
+    r.exclusions_from_bonds(True)
+    r.set_virial(True)
+    r.setup_integrator(0.005)
+    r.add_nve()
+    r.run(0)  # prepRun only
+    th = r.thermo()
+    pe_pair = float(r.force_component(0)[0][:, 3].astype(np.float64).sum())
+    pe_bond = float(r.force_component(1)[0][:, 3].astype(np.float64).sum())
+    assert pe_bond > 1.0 and abs(pe_pair) > 1e-3  # both contribute in this state
+    assert abs(row0["potential_energy"] - th["pe"]) <= 2e-5 * abs(th["pe"])
+    assert abs(row0["pressure"] - th["P"]) <= 2e-5 * abs(th["P"])
+    assert abs(row0["kinetic_energy"] - th["ke"]) <= 2e-5 * abs(th["ke"])
+    assert abs(row0["pair_lj_energy"] - pe_pair) <= 2e-5 * abs(pe_pair) + 1e-6
+    assert abs(row0["bond_fene_energy"] - pe_bond) <= 2e-5 * abs(pe_bond)
+    assert abs(row0["pair_lj_energy"] + row0["bond_fene_energy"] - row0["potential_energy"]) <= 1e-4 * abs(th["pe"])
+    assert abs(wca.get_energy() + fene.get_energy() - hoomd.context.current.engine.thermo()["pe"]) \
+        <= 1e-4 * abs(th["pe"])
+    with pytest.raises(RuntimeError):
+        log.query("pair_gauss_energy")  # no such force

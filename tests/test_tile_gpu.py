@@ -6,6 +6,7 @@ same rebuild decisions, trajectories within FP32 round-off growth.
 import numpy as np
 import pytest
 
+import golden_util as G
 from test_parity_gpu import FORCE_RTOL, _ka_system, _liquid, hb, ref  # noqa: F401 (fixtures)
 
 pytestmark = pytest.mark.gpu
@@ -34,26 +35,21 @@ def _melted(ref, hb, n_side=12, steps=300):
     return st["pos"][o], st["vel"][o], L
 
 
-def _assert_forces(r, g, rtol=FORCE_RTOL * 10, virial=True):
+def _assert_forces(r, g, L, lj, ntypes=1, virial=True, what="tile"):
+    """by tag, against the sums of absolute pair terms (north_star: 1e-5 relative, golden_util.assert_parity)"""
     fr, vr = r.forces(virial)
     fg, vg = g.forces(virial)
-    tg, tr = g.particles()["tag"], r.particles()["tag"]
+    pr = r.particles()
+    tg, tr = g.particles()["tag"], pr["tag"]
     fr2 = np.empty_like(fr); fr2[tr] = fr
     fg2 = np.empty_like(fg); fg2[tg] = fg
-    fscale = np.maximum(np.linalg.norm(fr2[:, :3], axis=1, keepdims=True), np.abs(fr2[:, :3]).mean())
-    assert (np.abs(fr2[:, :3] - fg2[:, :3]) / fscale).max() < rtol
-    escale = np.maximum(np.abs(fr2[:, 3]), np.abs(fr2[:, 3]).mean())
-    assert (np.abs(fr2[:, 3] - fg2[:, 3]) / escale).max() < rtol
-    assert abs(fr2[:, 3].astype(np.float64).sum() - fg2[:, 3].astype(np.float64).sum()) \
-        < FORCE_RTOL * abs(fr2[:, 3].astype(np.float64).sum())
+    vr2 = vg2 = None
     if virial:
         vr2 = np.empty_like(vr); vr2[:, tr] = vr
         vg2 = np.empty_like(vg); vg2[:, tg] = vg
-        vscale = np.maximum(np.abs(vr2), np.abs(vr2).mean())
-        assert (np.abs(vr2 - vg2) / vscale).max() < rtol
-        W_r = (vr2[0] + vr2[3] + vr2[5]).astype(np.float64).sum()
-        W_g = (vg2[0] + vg2[3] + vg2[5]).astype(np.float64).sum()
-        assert abs(W_r - W_g) < FORCE_RTOL * abs(W_r)
+    pos_by_tag = np.empty_like(pr["pos"]); pos_by_tag[tr] = pr["pos"]
+    sc = G.abs_scales(lambda o: o.setup_lj(**lj), pos_by_tag, (L, L, L), ntypes=ntypes)
+    return G.assert_parity(fr2, vr2, fg2, vg2, sc, what, FORCE_RTOL)
 
 
 def _assert_nlist_sets(r, g):
@@ -79,7 +75,7 @@ def test_tile_nlist_sets_and_forces(ref, hb, tile, tpp=0):
     if tile[0]:
         assert pm["cells_per_tile"] == tile
     _assert_nlist_sets(r, g)
-    _assert_forces(r, g)
+    _assert_forces(r, g, L, dict(r_cut=3.0, r_buff=0.4))
     # the particles are stored in cell order now: positions are a permutation of the input, tags say which
     p = g.particles()
     assert np.array_equal(p["pos"][np.argsort(p["tag"])].view(np.uint32), pos.view(np.uint32))
@@ -94,7 +90,7 @@ def test_tile_shift_modes(ref, hb, mode):
     r, g = _pair(ref, hb, pos, L, **lj)
     for s in (r, g):
         s.compute_forces(0)
-    _assert_forces(r, g, rtol=1e-4, virial=False)
+    _assert_forces(r, g, L, lj, virial=False, what="tile shift mode %d" % mode)
 
 
 def _compare_state(r, g, ptol, vtol):
@@ -134,7 +130,7 @@ def test_tile_kob_andersen_vs_reference(ref, hb):
         s.set_virial(True)
         s.compute_forces(0)
     _assert_nlist_sets(r, g)
-    _assert_forces(r, g)
+    _assert_forces(r, g, L, lj, ntypes=2, what="tile Kob-Andersen")
     for s in (r, g):
         s.setup_integrator(0.002)
         s.add_langevin(1.0, 7, gamma=[1.0, 1.5])
@@ -176,12 +172,7 @@ def test_tile_clustered_density(ref, hb):
     for s in (r, g):
         s.compute_forces(0)
     _assert_nlist_sets(r, g)
-    fr, _ = r.forces(False)
-    fg, _ = g.forces(False)
-    tg = g.particles()["tag"]
-    fg2 = np.empty_like(fg); fg2[tg] = fg
-    fscale = np.maximum(np.linalg.norm(fr[:, :3], axis=1, keepdims=True), np.abs(fr[:, :3]).mean())
-    assert (np.abs(fr[:, :3] - fg2[:, :3]) / fscale).max() < 1e-3  # overlapping pairs: huge cancelling terms
+    _assert_forces(r, g, L, lj, virial=False, what="tile clustered")  # overlapping pairs: huge cancelling terms
 
 
 def test_tile_mode_refuses_small_boxes(hb):
