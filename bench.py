@@ -166,6 +166,7 @@ class ClockSampler:
 
 EQUIL_STEPS = None  # --equil-steps override (profiling runs)
 USE_GRAPH = int(os.environ.get("HOOMD_B200_USE_GRAPH", "2"))  # 0 host-driven, 1 plain graph, 2 conditional graph
+PAIR_TPP = int(os.environ.get("HOOMD_B200_PAIR_TPP", "0"))     # A/B sweeps only: lanes per particle (0 = the engine's choice)
 
 
 def _lj_snapshot(workload):
@@ -243,7 +244,7 @@ def new_system(state, L, device=0, workload="lj64k"):
     s.setup_integrator(0.005)
     add_method(s, workload, WORKLOADS[workload][2])
     s.set_sorter(300)  # hoomd.update.sort default period on the GPU (hoomd/update.py:258-263)
-    s.set_tuning(use_graph=USE_GRAPH)
+    s.set_tuning(pair_tpp=PAIR_TPP, use_graph=USE_GRAPH)
     return s
 
 
@@ -456,6 +457,7 @@ def main():
         parity = mg_check.parity_pass(st64["pos"], st64["vel"], st64["image"], L64, args.parity_steps, local_rank,
                                       check_ghosts=False, verbose=False)
         parity.pop("mg_stats", None)
+        parity.pop("mg_timing", None)
         parity["workload"] = ("LJ liquid 64,000 (tests/golden/lj64k_equil.npz) on the same %d-GPU decomposition vs HOOMD-blue "
                               "2.3.0 CPU classes: forces / energies within 1e-5 of sum|pair terms|, neighbor-list row lengths "
                               "equal, %d NVE steps with equal rebuild counts" % (world, args.parity_steps))
@@ -484,6 +486,7 @@ def main():
     step_ms = s.time_kernel(2, 20)
     pair_ms = s.time_kernel(0, 200)
     nlist_ms = s.time_kernel(1, 20)
+    cell_only_ms, nlist_only_ms = s.time_kernel(3, 20), s.time_kernel(4, 20)
     n_neigh = s.nlist(counts_only=True)[0][:n_local]
     nbar = float(n_neigh.mean())
     step_bytes = (124.0 + 4.0 * nbar) * n_local
@@ -511,7 +514,7 @@ def main():
                 "fp32_tflops": step_flops / (step_ms * 1e-3) / 1e12,
                 "fp32_peak_tflops": 148 * 128 * 2 * 1.965e9 / 1e12,
                 "pair_kernel_ms": pair_ms, "pair_kernel_gbs": (40.0 + 4.0 * nbar) * n_local / (pair_ms * 1e-3) / 1e9,
-                "nlist_rebuild_ms": nlist_ms,
+                "nlist_rebuild_ms": nlist_ms, "cell_list_ms": cell_only_ms, "nlist_kernel_ms": nlist_only_ms,
                 "step_hbm_frac": BYTES_PER_PARTICLE_STEP * n_local * tps_rank / (hbm_peak * 1e9),
                 "note": ("working set at 64k is L2-resident (15 MB < 126 MB L2): the step is launch/latency bound, "
                          "the HBM fraction is low by construction (SURVEY 8d)") if N <= 100000 else
@@ -528,6 +531,7 @@ def main():
     if world > 1:
         mg_stats = s.mg_stats()
         mg_stats["grid"] = list(s.grid)
+        mg_stats["barrier_wait"] = s.mg_timing()  # device-measured: arrival at a barrier -> every rank seen
     s.close()
     s = None
 

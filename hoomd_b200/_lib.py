@@ -33,14 +33,15 @@ class CellListArgs(C.Structure):
                 ("d_conditions", vp), ("d_cell_count", vp), ("d_particle_cell", vp), ("d_particle_slot", vp),
                 ("d_scratch_idx", vp), ("d_pos", vp), ("d_charge", vp), ("N", C.c_uint), ("n_ghost", C.c_uint),
                 ("flag_charge", C.c_int), ("flag_type", C.c_int), ("box", Box), ("dim", Dim3),
-                ("ghost_width", C.c_float * 3)]
+                ("ghost_width", C.c_float * 3), ("d_ghost_dir", vp), ("d_ghost_shift", vp)]
 
 
 class NlistArgs(C.Structure):
     _fields_ = [("d_nlist", vp), ("d_n_neigh", vp), ("d_last_pos", vp), ("d_conditions", vp), ("d_Nmax", vp),
                 ("d_head_list", vp), ("d_pos", vp), ("N", C.c_uint), ("d_cell_start", vp), ("d_cell_xyzf", vp),
                 ("d_cell_type", vp), ("dim", Dim3), ("box", Box), ("ghost_width", C.c_float * 3), ("d_r_cut", vp),
-                ("d_r_listsq", vp), ("ntypes", C.c_uint), ("half_storage", C.c_int), ("cand_hint", C.c_uint)]
+                ("d_r_listsq", vp), ("ntypes", C.c_uint), ("half_storage", C.c_int), ("cand_hint", C.c_uint),
+                ("image_box", C.POINTER(Box))]
 
 
 class PairArgs(C.Structure):

@@ -17,7 +17,9 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
                                                   const float4* __restrict__ pos, unsigned int N, unsigned int n_ghost,
                                                   Box box, uint3 dim, float3 ghost_width,
                                                   const unsigned int* __restrict__ enable,
-                                                  const unsigned int* __restrict__ d_N)
+                                                  const unsigned int* __restrict__ d_N,
+                                                  const unsigned char* __restrict__ ghost_dir,
+                                                  const float* __restrict__ ghost_shift)
     {
     pdl_trigger(); // first kernel of the rebuild chain: let the scan's CTAs be scheduled behind this grid
     if (enable && !*enable) return; // device-driven stepping: the rebuild was not requested this step
@@ -34,6 +36,14 @@ __global__ void __launch_bounds__(256) k_cell_bin(unsigned int* __restrict__ cel
             }
         }
     float4 p = pos[n];
+    if (ghost_dir && n >= N)
+        {
+        // a ghost with raw coordinates is binned at its periodic image next to the local box
+        const float* sh = ghost_shift + 3u * ghost_dir[n - N];
+        p.x = __fadd_rn(p.x, sh[0]);
+        p.y = __fadd_rn(p.y, sh[1]);
+        p.z = __fadd_rn(p.z, sh[2]);
+        }
     unsigned int cell = B200_NOT_BINNED, slot = 0;
     if (isnan(p.x) || isnan(p.y) || isnan(p.z))
         atomicMax(&conditions[1], n + 1);
@@ -601,7 +611,7 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
     if (!enable) cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
-    if (cell_use_fused(ncells, ntot))
+    if (cell_use_fused(ncells, ntot) && !a->d_ghost_dir) // (the opt-in cooperative build bins ghosts where they are)
         {
         unsigned int grid = (ntot + CF_BLOCK - 1) / CF_BLOCK;
         if (grid > cell_fused_max_ctas()) grid = cell_fused_max_ctas();
@@ -618,7 +628,7 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     if (ntot)
         k_cell_bin<<<(ntot + 255) / 256, 256, 0, stream>>>(a->d_cell_count, a->d_particle_cell, a->d_particle_slot,
                                                             a->d_conditions, (const float4*)a->d_pos, a->N, a->n_ghost,
-                                                            box, dim, gw, enable, d_N);
+                                                            box, dim, gw, enable, d_N, a->d_ghost_dir, a->d_ghost_shift);
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     // device-driven rebuild: the dependent kernels are scheduled behind their predecessor (see launch_chain)
     const bool pdl = enable && pdl_enabled();

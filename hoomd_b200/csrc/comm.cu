@@ -365,12 +365,10 @@ __global__ void __launch_bounds__(256) k_mg_ghost_send(const __grid_constant__ M
     const unsigned int n = min(l.ms->gsend_cnt[d], c.seg_cap[d]);
     if (slot >= n) return;
     const unsigned int i = l.plan_src[t];
-    float4 p = pos[i];
-    p.x = __fadd_rn(p.x, c.shift[d][0]);
-    p.y = __fadd_rn(p.y, c.shift[d][1]);
-    p.z = __fadd_rn(p.z, c.shift[d][2]);
+    // raw coordinates: the receiver bins the ghost at its periodic image (b200_cell_list_args.d_ghost_shift) and takes
+    // minimum images in the global box, so a ghost pair is evaluated with the single-domain arithmetic
     float4* dst = buffer ? c.peer_posB[d] : c.peer_posA[d];
-    dst[c.Ncap + t] = p;
+    dst[c.Ncap + t] = pos[i];
     if (slot == 0) atomicMax(&l.ms->max_gsend, n);
     }
 

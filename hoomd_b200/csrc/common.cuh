@@ -38,10 +38,18 @@ inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block,
 #endif
 bool pdl_enabled(); // HOOMD_B200_PDL (cell_list.cu)
 
+// The box a kernel works in: `lo/hi/L/Linv/periodic` locate particles (binning, wrapping); the i-fields are the box MINIMUM
+// IMAGES are taken in.  On one GPU both are the same box.  Under domain decomposition the first is the rank's local box
+// (non-periodic along split axes) and the second the GLOBAL box: ghosts hold their owners' raw coordinates and a pair
+// separation is pos_i - pos_j followed by the global minimum image -- the arithmetic of the single-domain reference
+// (hoomd/md/PotentialPair.h:337 takes getGlobalBox() as well), so results do not depend on the decomposition.
+// iforce: axes on which every cell may hold raw ghosts from across the global boundary (split axes).
 struct Box
     {
     float3 lo, hi, L, Linv;
     uchar3 periodic;
+    float3 ilo, ihi, iL, iLinv;
+    uchar3 iperiodic, iforce;
     };
 
 __host__ __device__ inline Box make_box(const b200_box& b)
@@ -52,6 +60,26 @@ __host__ __device__ inline Box make_box(const b200_box& b)
     r.L = make_float3(b.L[0], b.L[1], b.L[2]);
     r.Linv = make_float3(b.Linv[0], b.Linv[1], b.Linv[2]);
     r.periodic = make_uchar3(b.periodic[0], b.periodic[1], b.periodic[2]);
+    r.ilo = r.lo; r.ihi = r.hi; r.iL = r.L; r.iLinv = r.Linv;
+    r.iperiodic = r.periodic;
+    r.iforce = make_uchar3(0, 0, 0);
+    return r;
+    }
+
+// local box `b` for locating particles, minimum images in `img` (NULL: in `b` itself)
+__host__ __device__ inline Box make_box_image(const b200_box& b, const b200_box* img)
+    {
+    Box r = make_box(b);
+    if (img)
+        {
+        r.ilo = make_float3(img->lo[0], img->lo[1], img->lo[2]);
+        r.ihi = make_float3(img->hi[0], img->hi[1], img->hi[2]);
+        r.iL = make_float3(img->L[0], img->L[1], img->L[2]);
+        r.iLinv = make_float3(img->Linv[0], img->Linv[1], img->Linv[2]);
+        r.iperiodic = make_uchar3(img->periodic[0], img->periodic[1], img->periodic[2]);
+        r.iforce = make_uchar3(img->periodic[0] && !b.periodic[0], img->periodic[1] && !b.periodic[1],
+                               img->periodic[2] && !b.periodic[2]);
+        }
     return r;
     }
 
@@ -87,9 +115,9 @@ __device__ __forceinline__ float min_image_1d(float w, float lo, float hi, float
 // Exact oracle form (used where membership is decided: neighbor list, distance check)
 __device__ __forceinline__ float3 min_image_exact(float3 w, const Box& box)
     {
-    if (box.periodic.z) w.z = min_image_1d(w.z, box.lo.z, box.hi.z, box.L.z, box.Linv.z, false);
-    if (box.periodic.y) w.y = min_image_1d(w.y, box.lo.y, box.hi.y, box.L.y, box.Linv.y, true);
-    if (box.periodic.x) w.x = min_image_1d(w.x, box.lo.x, box.hi.x, box.L.x, box.Linv.x, true);
+    if (box.iperiodic.z) w.z = min_image_1d(w.z, box.ilo.z, box.ihi.z, box.iL.z, box.iLinv.z, false);
+    if (box.iperiodic.y) w.y = min_image_1d(w.y, box.ilo.y, box.ihi.y, box.iL.y, box.iLinv.y, true);
+    if (box.iperiodic.x) w.x = min_image_1d(w.x, box.ilo.x, box.ihi.x, box.iL.x, box.iLinv.x, true);
     return w;
     }
 
@@ -110,10 +138,17 @@ __device__ __forceinline__ float min_image_1d_sel(float w, float lo, float hi, f
 
 __device__ __forceinline__ float3 min_image_exact_sel(float3 w, const Box& box, bool wx, bool wy, bool wz)
     {
-    if (wz) w.z = min_image_1d_sel(w.z, box.lo.z, box.hi.z, box.L.z, box.Linv.z, false);
-    if (wy) w.y = min_image_1d_sel(w.y, box.lo.y, box.hi.y, box.L.y, box.Linv.y, true);
-    if (wx) w.x = min_image_1d_sel(w.x, box.lo.x, box.hi.x, box.L.x, box.Linv.x, true);
+    if (wz) w.z = min_image_1d_sel(w.z, box.ilo.z, box.ihi.z, box.iL.z, box.iLinv.z, false);
+    if (wy) w.y = min_image_1d_sel(w.y, box.ilo.y, box.ihi.y, box.iL.y, box.iLinv.y, true);
+    if (wx) w.x = min_image_1d_sel(w.x, box.ilo.x, box.ihi.x, box.iL.x, box.iLinv.x, true);
     return w;
+    }
+
+// which axes of a cell's candidates need the minimum image at all: cells on a periodic face of the image box, short axes,
+// and -- under domain decomposition -- every cell of a split axis (its ghost cells hold raw coordinates)
+__device__ __forceinline__ bool cell_needs_image(bool iperiodic, bool iforce, unsigned int dim, unsigned int b)
+    {
+    return iperiodic && (iforce || dim < 5 || b == 0 || b == dim - 1);
     }
 
 // Branch-free form for the force kernel: w -= L * rint(w / L), the reference's DEVICE minImage (hoomd/BoxDim.h:281-300).
@@ -121,9 +156,9 @@ __device__ __forceinline__ float3 min_image_exact_sel(float3 w, const Box& box, 
 // wider than 2*r_list, hoomd/md/NeighborListBinned.cc:109-115).
 __device__ __forceinline__ float3 min_image_fast(float3 w, const Box& box)
     {
-    if (box.periodic.z) w.z = __fmaf_rn(-box.L.z, rintf(__fmul_rn(w.z, box.Linv.z)), w.z);
-    if (box.periodic.y) w.y = __fmaf_rn(-box.L.y, rintf(__fmul_rn(w.y, box.Linv.y)), w.y);
-    if (box.periodic.x) w.x = __fmaf_rn(-box.L.x, rintf(__fmul_rn(w.x, box.Linv.x)), w.x);
+    if (box.iperiodic.z) w.z = __fmaf_rn(-box.iL.z, rintf(__fmul_rn(w.z, box.iLinv.z)), w.z);
+    if (box.iperiodic.y) w.y = __fmaf_rn(-box.iL.y, rintf(__fmul_rn(w.y, box.iLinv.y)), w.y);
+    if (box.iperiodic.x) w.x = __fmaf_rn(-box.iL.x, rintf(__fmul_rn(w.x, box.iLinv.x)), w.x);
     return w;
     }
 
@@ -132,9 +167,9 @@ __device__ __forceinline__ bool box_interior(float4 p, const Box& box, float mar
     {
     if (!(margin > 0.0f)) return false;
     bool in = true;
-    if (box.periodic.x) in &= (p.x >= box.lo.x + margin) && (p.x < box.hi.x - margin);
-    if (box.periodic.y) in &= (p.y >= box.lo.y + margin) && (p.y < box.hi.y - margin);
-    if (box.periodic.z) in &= (p.z >= box.lo.z + margin) && (p.z < box.hi.z - margin);
+    if (box.iperiodic.x) in &= (p.x >= box.ilo.x + margin) && (p.x < box.ihi.x - margin);
+    if (box.iperiodic.y) in &= (p.y >= box.ilo.y + margin) && (p.y < box.ihi.y - margin);
+    if (box.iperiodic.z) in &= (p.z >= box.ilo.z + margin) && (p.z < box.ihi.z - margin);
     return in;
     }
 

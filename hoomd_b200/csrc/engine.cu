@@ -236,11 +236,15 @@ struct b200_system
     DevBuf<unsigned int> holes, low_holes, hole_mark, plan_src;
     DevBuf<unsigned char> slot_dir, pplan_n;
     DevBuf<unsigned int> pplan, chunk_flag, cta_order;
+    DevBuf<float> recv_shift;        // [27 * 3] periodic image shift of the ghosts received in segment d (binning only)
     DevBuf<GhostSendTable> gs_table;
     unsigned int mg_tpp = 2;         // lanes per particle of k_md_step under decomposition (fixes the chunk size of cta_order)
     // Ghost update + all-ranks step barrier inside k_md_step, boundary chunks scheduled first (the default).
     // HOOMD_B200_FUSED_GHOSTS=0: the round-1 sequence barrier kernel -> k_md_step -> k_mg_ghost_send, kept for A/B runs.
     bool fused_ghosts = true;
+    // HOOMD_B200_MG_MODE (A/B and debugging): bit 0 = ghost stores inside k_md_step, bit 1 = boundary-first CTA order,
+    // bit 2 = the step barrier inside k_md_step's last CTA (needs bit 0); default 7
+    int mg_mode = 7;
 
     // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
     int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
@@ -283,6 +287,12 @@ static void cell_list_args(b200_system* s, b200_cell_list_args& a)
     a.box = s->box;
     a.dim = s->dim;
     for (int d = 0; d < 3; d++) a.ghost_width[d] = s->ghost_width[d];
+    if (s->mg)
+        {
+        // ghosts hold raw coordinates: bin them at their periodic image next to the local box
+        a.d_ghost_dir = s->slot_dir.p;
+        a.d_ghost_shift = s->recv_shift.p;
+        }
     }
 
 static void nlist_args(b200_system* s, b200_nlist_args& a)
@@ -306,6 +316,7 @@ static void nlist_args(b200_system* s, b200_nlist_args& a)
     a.d_r_listsq = s->d_r_listsq.p;
     a.ntypes = s->ntypes;
     a.half_storage = 0;
+    a.image_box = s->mg ? &s->global_box : nullptr; // decomposition: minimum images in the global box (raw ghost coordinates)
     // staging capacity of a build pass: the mean 27-cell population with head room for density fluctuations
     const double per_cell = (double)(s->N + (s->mg ? s->Gcap / 2 : 0)) / ((double)s->dim.x * s->dim.y * s->dim.z);
     a.cand_hint = (unsigned int)std::min(1024.0, 27.0 * per_cell * 1.5 + 48.0);
@@ -319,7 +330,7 @@ static void pair_args(b200_system* s, b200_pair_args& a)
     a.virial_pitch = s->virial_pitch;
     a.N = s->N;
     a.d_pos = (const float*)s->pos.p;
-    a.box = s->box;
+    a.box = s->mg ? s->global_box : s->box; // the box minimum images are taken in (PotentialPair.h:337: getGlobalBox())
     a.d_n_neigh = s->n_neigh.p;
     a.d_nlist = s->nlist.p;
     a.d_head_list = s->head_list.p;
@@ -378,7 +389,7 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
     a.rcut_max = s->d_rcut_max.p; a.gamma = s->d_gamma.p; a.maxsq = s->d_maxsq.p;
     a.N = s->mg ? s->Ncap : s->N; a.box = s->box; a.dt = s->dt; a.r_buff = s->r_buff;
     a.d_N = s->mg ? &s->d_state.p->N : nullptr;
-    a.mg = s->mg ? ((s->fused_ghosts && s->mg_connected) ? 2 : 1) : 0;
+    a.mg = s->mg ? ((s->fused_ghosts && s->mg_connected && (s->mg_mode & 4)) ? 2 : 1) : 0;
     a.method = s->method; a.limit = s->limit; a.limit_val = s->limit_val; a.zero_force = s->zero_force;
     a.kT = s->kT; a.seed = s->seed_hashed; a.noiseless_t = s->noiseless_t;
     for (int d = 0; d < 3; d++) a.lambda[d] = (s->mg || !s->have_nlist) ? 1.0f : s->box.L[d] / s->last_L[d];
@@ -387,7 +398,7 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         {
         a.gs.tab = s->gs_table.p; a.gs.pplan = s->pplan.p; a.gs.pplan_n = s->pplan_n.p; a.gs.slot_dir = s->slot_dir.p;
         a.gs.pitch = s->Ncap;
-        a.gs.cta_order = s->cta_order.p;
+        a.gs.cta_order = (s->mg_mode & 2) ? s->cta_order.p : nullptr;
         }
     if (s->bond_kind >= 0)
         {
@@ -399,6 +410,10 @@ static void fused_args(b200_system* s, FusedStepArgs& a)
         a.nvt_tau = s->nvt_tau;
         }
     a.group_flag = s->group_flag.n ? s->group_flag.p : nullptr;
+    static const int head_arith = getenv("HOOMD_B200_HEAD_ARITH") ? atoi(getenv("HOOMD_B200_HEAD_ARITH")) : 1;
+    static const int prefetch = getenv("HOOMD_B200_PREFETCH") ? atoi(getenv("HOOMD_B200_PREFETCH")) : 1;
+    a.nmax_uniform = (head_arith && s->ntypes == 1 && !s->h_Nmax.empty()) ? s->h_Nmax[0] : 0u; // baked into the step graph
+    a.prefetch = prefetch;
     if (s->method == 2)
         {
         a.use_lambda = s->use_lambda; a.gamma_lambda = s->lambda; a.diameter = s->diameter.p;
@@ -598,6 +613,7 @@ static bool nlist_check_conditions(b200_system* s)
         {
         s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
         CUDA_OK(cudaStreamSynchronize(s->stream));
+        invalidate_graph(s); // Nmax[0] is a by-value argument of the captured step kernels (FusedStepArgs::nmax_uniform)
         }
     return result;
     }
@@ -1271,6 +1287,10 @@ static void sys_open_device(b200_system* s)
     // developer overrides of the pair path: HOOMD_B200_PAIR_MODE = -1 | 0 | 1, HOOMD_B200_TILE = "bx,by,bz,tpp"
     if (const char* m = getenv("HOOMD_B200_PAIR_MODE")) s->pair_mode = atoi(m);
     if (const char* m = getenv("HOOMD_B200_FUSED_GHOSTS")) s->fused_ghosts = atoi(m) != 0;
+    if (const char* m = getenv("HOOMD_B200_MG_MODE")) s->mg_mode = atoi(m);
+    if (!s->fused_ghosts) s->mg_mode = 0;
+    s->fused_ghosts = (s->mg_mode & 1) != 0;
+    if (!s->fused_ghosts) s->mg_mode = 0;
     if (const char* m = getenv("HOOMD_B200_TAG_TABLES")) s->idx_tables = atoi(m) == 0; // A/B: tag-keyed bond / exclusion rows
     if (const char* t = getenv("HOOMD_B200_TILE"))
         {
@@ -2275,9 +2295,13 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
             CUDA_OK(b200_compute_pair_forces(s->pair_kind, &pa, pair_params_ptr(s), s->stream));
         else
             {
-            CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, s->mg ? &s->d_state.p->N : nullptr));
-            CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
-            enqueue_nlist_filter(s, nullptr);
+            // 1: the whole rebuild; 3: the cell list alone; 4: the neighbor-list kernel (+ exclusion filter) alone
+            if (which != 4) CUDA_OK(launch_cell_list(&ca, nullptr, s->stream, s->mg ? &s->d_state.p->N : nullptr));
+            if (which != 3)
+                {
+                CUDA_OK(launch_nlist_binned(&na, nullptr, s->stream));
+                enqueue_nlist_filter(s, nullptr);
+                }
             }
         }
     CUDA_OK(cudaEventRecord(e1, s->stream));

@@ -100,6 +100,21 @@ static void mg_setup(b200_system* s, const b200_mg_params& p)
         }
     s->Gcap = off;
     c.Gcap = off;
+    // receiver side: segment d is filled by the neighbor this rank lies in direction d of; its particles need +-L to sit next
+    // to the local box when that step crossed the global periodic boundary (dd = -1 into the last domain, +1 into the first)
+    std::vector<float> rs(MG_NDIR * 3, 0.0f);
+    for (int d = 0; d < MG_NDIR; d++)
+        {
+        if (c.dir_rank[d] < 0) continue;
+        const int dd[3] = {d % 3 - 1, (d / 3) % 3 - 1, d / 9 - 1};
+        for (int a = 0; a < 3; a++)
+            {
+            if (dd[a] == -1 && s->mg_pos[a] + 1 == p.grid[a]) rs[3 * d + a] = c.Lg[a];
+            if (dd[a] == 1 && s->mg_pos[a] == 0) rs[3 * d + a] = -c.Lg[a];
+            }
+        }
+    s->recv_shift.alloc(MG_NDIR * 3);
+    s->recv_shift.upload(rs.data(), rs.size(), s->stream);
     const unsigned int expect = p.N_global / p.world + 1;
     s->Ncap = p.Ncap ? p.Ncap : (unsigned int)(1.25 * expect) + 8192u;
     if (p.N_local > s->Ncap) throw std::runtime_error("comm: more local particles than Ncap");
@@ -290,6 +305,7 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
                 for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 9u / 8u) + 7u) & ~7u;
                 s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
                 CUDA_OK(cudaStreamSynchronize(s->stream));
+                invalidate_graph(s);
                 s->num_overflows += 1;
                 nlist_build_head_list(s);
                 CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
@@ -299,7 +315,9 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
         s->nl_first_compute = false;
         s->cl_first = false;
         s->cl_force = false;
-        s->num_forced += 1;
+        // NeighborList::needsUpdating counts a forced update only when the step has not been checked yet -- and
+        // m_last_checked_tstep starts at 0, so the very first build at time step 0 is not counted (NeighborList.cc:1082-1091)
+        if (s->last_checked_tstep != ts) s->num_forced += 1;
         s->last_updated_tstep = ts;
         s->kernels_last_run += MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u;
         }
@@ -327,7 +345,8 @@ static void mg_build_graph(b200_system* s)
 #if (CUDART_VERSION >= 12040)
     FusedStepArgs fa;
     fused_args(s, fa);
-    const bool fused = fa.mg == 2;
+    const bool fused = fa.mg == 2;          // step barrier inside k_md_step
+    const bool push = fa.gs.tab != nullptr; // ghost stores inside k_md_step
     const unsigned int* enable = &s->d_state.p->need_rebuild;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
@@ -346,14 +365,11 @@ static void mg_build_graph(b200_system* s)
             CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
         cudaGraph_t body0 = add_if_node(s, graph, h0);
         enqueue_md_step(s, fa, 0, fused ? (unsigned long long)h1 : 0ull, fused ? 1 : 0);
-        if (!fused)
-            {
-            CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
-            }
+        if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+        if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
         cudaGraph_t body1 = add_if_node(s, graph, h1);
         enqueue_md_step(s, fa, 1, 0ull, 0);
-        if (!fused) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+        if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
         cudaGraph_t out = nullptr;
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
@@ -408,6 +424,7 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         // vote and decision (every later one is taken by the last CTA of k_md_step); round-1 mode: the first barrier of the
         // graph does.
         const bool fused = fa.mg == 2;
+        const bool push = fa.gs.tab != nullptr;
         if (!resume) CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
         CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
         if (fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
@@ -420,14 +437,11 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
                 if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
                 mg_enqueue_rebuild(s, enable, s->pos.p, 0);
                 enqueue_md_step(s, fa, 0, 0ull, 0);
-                if (!fused)
-                    {
-                    CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-                    CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
-                    }
+                if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
+                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
                 mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
                 enqueue_md_step(s, fa, 1, 0ull, 0);
-                if (!fused) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
+                if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
                 }
             }
         else
@@ -437,7 +451,7 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_check_errors(s);
         cell_list_check_conditions(s);
         const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
-        s->kernels_last_run += (fused ? 3ull : 2ull) + (fused ? 3ull : 6ull) * nreplay
+        s->kernels_last_run += (fused ? 3ull : 2ull) + (fused ? 3ull : (push ? 4ull : 6ull)) * nreplay
                                + (MG_REBUILD_KERNELS + cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->Ncap + s->Gcap) - 4u) * rebuilds;
         s->num_updates += st.num_updates;
         s->num_forced += st.num_forced;
@@ -453,9 +467,13 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
                 for (unsigned int t = 0; t < s->ntypes; t++) s->h_Nmax[t] = ((s->h_Nmax[t] * 9u / 8u) + 7u) & ~7u;
                 s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
                 CUDA_OK(cudaStreamSynchronize(s->stream));
+                invalidate_graph(s);
                 }
             CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
             s->num_overflows += 1;
+            // the redo below is counted as one more forced update: the reference's overflow loop rebuilds inside ONE
+            // NeighborList::compute and counts it once (hoomd/md/NeighborList.cc:226-244)
+            s->num_forced -= 1;
             s->timestep = st.timestep - 1u; // the decision of the aborted step is taken again
             s->last_updated_tstep = st.last_updated;
             s->force_update = true;

@@ -61,7 +61,7 @@ __global__ void k_decide(StepState* st)
 __global__ void k_graph_pre(StepState* st, cudaGraphConditionalHandle handle)
     {
 #if (CUDART_VERSION >= 12040)
-    cudaGraphSetConditional(handle, (st->steps_left && st->need_rebuild) ? 1u : 0u);
+    cudaGraphSetConditional(handle, (st->steps_left && st->need_rebuild && !st->abort) ? 1u : 0u);
 #endif
     }
 

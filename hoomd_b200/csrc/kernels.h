@@ -112,6 +112,10 @@ struct FusedStepArgs
     // md.integrate.langevin(dscale=lambda): gamma = lambda * diameter[tag]; tally: reservoir energy bookkeeping
     // (hoomd/md/TwoStepLangevin.cc:287-318,416-417): acc[0] = running sum of E_step, acc[1 + (ts & 1)] = E of step ts
     const float* diameter; int use_lambda; float gamma_lambda; double* tally_acc;
+    // latency trims of k_md_step: nmax_uniform != 0 (one particle type): head_list[i] == i * Nmax[0] (the exclusive scan of
+    // a constant), so the first index chunk of a row can be requested without waiting for the head list; prefetch != 0: the
+    // integration phase's operands (velocity, image, last position) are pulled into L1 while the neighbor walk runs
+    unsigned int nmax_uniform; int prefetch;
     };
 // step one (+ distance check into st->moved)
 cudaError_t launch_fused_step_one(const FusedStepArgs& a, StepState* st, cudaStream_t stream);

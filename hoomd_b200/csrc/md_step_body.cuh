@@ -43,24 +43,27 @@ template<class Evaluator> struct MdStepArgs
     NvtState* nvt; unsigned long long* nvt_acc; double nvt_scale; unsigned int nvt_ndof; float nvt_tau; // TwoStepNVTMTK
     const unsigned char* group_flag;                                  // the method's group by tag (NULL = all)
     const float* diameter; int use_lambda; float gamma_lambda; double* tally_acc; // langevin dscale / tally
+    unsigned int nmax_uniform; int prefetch;                          // see FusedStepArgs
     };
+
+__device__ __forceinline__ void prefetch_l1(const void* p)
+    {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+    }
 
 // write particle i's position into every ghost slot it feeds on the neighbor ranks (plain stores over NVLink)
 template<class Evaluator>
-__device__ __forceinline__ void md_step_send_ghosts(const MdStepArgs<Evaluator>& a, unsigned int i, const float4 p)
+__device__ __forceinline__ bool md_step_send_ghosts(const MdStepArgs<Evaluator>& a, unsigned int i, const float4 p)
     {
     const unsigned int n = a.gs.pplan_n[i];
     for (unsigned int k = 0; k < n; k++)
         {
         const unsigned int e = a.gs.pplan[(size_t)k * a.gs.pitch + i]; // direction in the top 5 bits, slot below
         const unsigned int t = e & 0x07ffffffu, d = e >> 27;
-        float4 q = p;
-        q.x = __fadd_rn(q.x, a.gs.tab->shift[d][0]);
-        q.y = __fadd_rn(q.y, a.gs.tab->shift[d][1]);
-        q.z = __fadd_rn(q.z, a.gs.tab->shift[d][2]);
         float4* dst = a.gs_buffer ? a.gs.tab->peer_posB[d] : a.gs.tab->peer_posA[d];
-        dst[a.gs.pitch + t] = q;
+        dst[a.gs.pitch + t] = p; // raw coordinates (see k_mg_ghost_send)
         }
+    return n != 0u;
     }
 
 #ifndef B200_MD_BLOCK
@@ -73,7 +76,8 @@ constexpr int MD_BLOCK = B200_MD_BLOCK; // threads per CTA of k_md_step (B200 sw
 template<class Evaluator, bool VIRIAL>
 __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, float4 F,
                                                   const float4 pi4, float (&vir)[6], unsigned int ts2, bool last,
-                                                  bool store_force, double& mv2, float exp_fac = 1.0f)
+                                                  bool store_force, double& mv2, float exp_fac = 1.0f,
+                                                  bool* pushed = nullptr)
     {
     bool moved = false;
     float4 v = a.vel[i];
@@ -136,7 +140,11 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         else
             nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
         a.pos_out[i] = p;
-        if (a.gs.tab) md_step_send_ghosts(a, i, p);
+        if (a.gs.tab)
+            {
+            const bool sent = md_step_send_ghosts(a, i, p);
+            if (pushed) *pushed = sent;
+            }
         a.image[i] = img;
         // ---- NeighborList::distanceCheck (hoomd/md/NeighborList.cc:981-1016): row 0 of the table for a fixed box
         // (lambda = 1), row 1 while the box differs from the one the list was built in ----
@@ -151,7 +159,11 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     else if (a.copy_pos_on_last)
         {
         a.pos_out[i] = pi4;
-        if (a.gs.tab) md_step_send_ghosts(a, i, pi4);
+        if (a.gs.tab)
+            {
+            const bool sent = md_step_send_ghosts(a, i, pi4);
+            if (pushed) *pushed = sent;
+            }
         }
     a.vel[i] = v;
     return moved;
@@ -212,9 +224,12 @@ __device__ __forceinline__ void md_step_nvt_wait(const MdStepArgs<Evaluator>& a,
 template<class Evaluator>
 __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, StepState* st, bool moved,
                                                unsigned int steps_left, bool last, double mv2 = 0.0,
-                                               unsigned int ts2 = 0)
+                                               unsigned int ts2 = 0, bool pushed = false)
     {
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    // multi-GPU: did this CTA store ghosts into a peer's buffer?  Only those CTAs (the boundary chunks, scheduled first) pay
+    // for a system-scope fence; a fence in every CTA cost 15-20 % of the kernel (profiles/r2e_*)
+    const int any_pushed = (a.mg == 2) ? __syncthreads_or(pushed ? 1 : 0) : 0;
     if (a.method == 2 && a.tally_acc)
         {
         // reservoir-energy tally: sum_j F_bd . v' of this step (double atomics: a diagnostic, order-dependent in the last bits)
@@ -250,7 +265,7 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
         {
         // one 64-bit atomic carries both the ticket and this CTA's distance-check result: no fence, no second atomic
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
-        if (a.mg == 2) __threadfence_system(); // this CTA's ghost stores (ordered by the barrier above) before its ticket
+        if (any_pushed) __threadfence_system(); // this CTA's ghost stores (ordered by the barrier above) before its ticket
         const unsigned long long old = atomicAdd(&st->ticket, inc);
         const bool is_last = (unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1;
         s_is_last = is_last ? 1 : 0;
@@ -318,7 +333,8 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.params = (const typename Evaluator::param_type*)d_params; a.rcutsq = pa.d_rcutsq; a.ronsq = pa.d_ronsq;
     a.ntypes = pa.ntypes;
     a.maxsq = fa.maxsq; a.gamma = fa.gamma;
-    a.N = fa.N; a.box = make_box(fa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
+    // fa.box locates and wraps the particles (the local box); pa.box is the box minimum images are taken in
+    a.N = fa.N; a.box = make_box_image(fa.box, &pa.box); a.dt = fa.dt; a.r_buff = fa.r_buff;
     a.wrap_skip_margin = pa.wrap_skip_margin;
     a.method = fa.method; a.limit = fa.limit; a.limit_val = fa.limit_val; a.zero_force = fa.zero_force;
     a.kT = fa.kT; a.seed = fa.seed; a.noiseless_t = fa.noiseless_t;
@@ -330,6 +346,7 @@ inline void fill_md_step_args(MdStepArgs<Evaluator>& a, const b200_pair_args& pa
     a.nvt_tau = fa.nvt_tau;
     a.group_flag = fa.group_flag;
     a.diameter = fa.diameter; a.use_lambda = fa.use_lambda; a.gamma_lambda = fa.gamma_lambda; a.tally_acc = fa.tally_acc;
+    a.nmax_uniform = fa.nmax_uniform; a.prefetch = fa.prefetch;
     a.st = st; a.handle = (cudaGraphConditionalHandle)cond_handle; a.use_cond = use_cond;
     }
 } // namespace b200

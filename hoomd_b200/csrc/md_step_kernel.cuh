@@ -30,7 +30,14 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     __shared__ float s_virial[VIRIAL ? 6 * PPB : 1];
     StepState* st = a.st;
     const unsigned int steps_left = st->steps_left;
-    if (steps_left == 0 || st->abort) return; // padding launch of an odd-length chunk / aborted chunk (grid-uniform)
+    if (steps_left == 0 || st->abort)
+        {
+        // padding launch of an odd-length chunk / aborted chunk (grid-uniform).  After a collective abort (Nmax overflow
+        // vote) nothing may run until the host has grown Nmax -- in particular not another rebuild bracket, which would
+        // migrate from the other, older position buffer: withdraw the pending rebuild request.
+        if (st->abort && blockIdx.x == 0 && threadIdx.x == 0) st->need_rebuild = 0u;
+        return;
+        }
     const bool last = steps_left == 1;
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
@@ -48,9 +55,21 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
         const unsigned int i = chunk * PPB + slot;
         const unsigned int sub = threadIdx.x % TPP;
         const bool active = i < N;
+        if (a.prefetch && threadIdx.x < PPB)
+            {
+            // operands of the integration phase of particle chunk*PPB + threadIdx.x: in L1 by the time the walk is done
+            const unsigned int i2 = chunk * PPB + threadIdx.x;
+            if (i2 < N)
+                {
+                prefetch_l1(a.vel + i2);
+                prefetch_l1(a.image + i2);
+                prefetch_l1(a.last_pos + i2);
+                }
+            }
         const float4 pi4 = active ? a.pos_in[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         const unsigned int size = active ? a.n_neigh[i] : 0u;
-        const unsigned int head = active ? a.head_list[i] : 0u;
+        // one type: the head list is the exclusive scan of a constant, no load on the way to the first index chunk
+        const unsigned int head = !active ? 0u : ((!MULTI_TYPE && a.nmax_uniform) ? i * a.nmax_uniform : a.head_list[i]);
         const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, VIRIAL, MULTI_TYPE>(
             pi4, size, head, sub, a.pos_in, a.box, a.nlist, T, a.ntypes,
             !active || box_interior(pi4, a.box, a.wrap_skip_margin));
@@ -72,7 +91,7 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     __syncthreads();
 
     // ---- phase 2: one lane per particle integrates (full warps, coalesced) instead of one lane in TPP ----
-    bool moved = false;
+    bool moved = false, pushed = false;
     double mv2 = 0.0;
     const unsigned int i = chunk * PPB + threadIdx.x;
     if (threadIdx.x < PPB && i < N)
@@ -84,9 +103,9 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
             for (int c = 0; c < 6; c++) vir[c] = s_virial[c * PPB + threadIdx.x];
             }
         moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force,
-                                                     mv2, a.method == 3 ? s_exp_fac : 1.0f);
+                                                     mv2, a.method == 3 ? s_exp_fac : 1.0f, &pushed);
         }
-    md_step_finish(a, st, moved, steps_left, last, mv2, ts2);
+    md_step_finish(a, st, moved, steps_left, last, mv2, ts2, pushed);
     }
 
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>

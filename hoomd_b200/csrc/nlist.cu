@@ -272,9 +272,9 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
     // A candidate of an interior cell is less than two cell widths away along every axis; with >= 5 cells per axis that is
     // inside [lo, hi) and minImage is the identity: only cells on a periodic face pay for it (CTA-uniform).
-    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
-    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
-    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NL_CAP)
@@ -427,9 +427,9 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
     __syncwarp();
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
-    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
-    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
-    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NW_CAP)
@@ -613,9 +613,9 @@ __global__ void __launch_bounds__(NC_BLOCK) k_nlist_cellscan(unsigned int* __res
     const unsigned int total = s_off[nr];
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
-    const bool wx = box.periodic.x && (dim.x < 5 || bx == 0 || bx == dim.x - 1);
-    const bool wy = box.periodic.y && (dim.y < 5 || by == 0 || by == dim.y - 1);
-    const bool wz = box.periodic.z && (dim.z < 5 || bz == 0 || bz == dim.z - 1);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
     const unsigned int slot = threadIdx.x / NC_G, sub = threadIdx.x % NC_G;
     unsigned int parity = 0;
@@ -918,7 +918,7 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
     if (!box_is_orthorhombic(a->box)) return cudaErrorNotSupported;
     if (a->N == 0) return cudaSuccess;
     if (a->ntypes > 1 && !a->d_cell_type) return cudaErrorInvalidValue;
-    Box box = make_box(a->box);
+    Box box = make_box_image(a->box, a->image_box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
     const bool pdl = enable && pdl_enabled(); // chained behind k_cell_rank (launch_chain, common.cuh)

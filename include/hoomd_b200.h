@@ -95,6 +95,11 @@ typedef struct b200_cell_list_args
     b200_box      box;
     b200_dim3     dim;            /* CellList::getDim() */
     float         ghost_width[3]; /* CellList::getGhostWidth() */
+    /* domain decomposition with RAW ghost coordinates (see b200_nlist_args.image_box): ghost g (particle N + g) is binned at
+     * pos + d_ghost_shift[3 * d_ghost_dir[g] ...] -- the periodic image that lies next to the local box -- while the stored
+     * entry keeps the raw position.  Both NULL: ghosts are binned where they are (the reference's pre-wrapped ghosts). */
+    const unsigned char* d_ghost_dir;   /* [n_ghost] or NULL */
+    const float*         d_ghost_shift; /* [3 * 27] or NULL */
     } b200_cell_list_args;
 
 B200_API int b200_compute_cell_list(const b200_cell_list_args* args, b200_stream_t stream);
@@ -157,6 +162,12 @@ typedef struct b200_nlist_args
     int           half_storage;      /* 1: keep only i<j (NeighborList::half); GPU classes always use 0 */
     unsigned int  cand_hint;         /* tuning only: expected particles in a cell's <=27-cell neighborhood (sizes the
                                         shared-memory staging of a pass; 0 = 512).  Larger neighborhoods take more passes. */
+    const b200_box* image_box;       /* NULL: minimum images in `box`.  Domain decomposition: the GLOBAL box -- `box` (the local
+                                        box, non-periodic along split axes) only locates cells, separations are pos_i - pos_j
+                                        followed by the global minimum image, as the single-domain reference forms them; ghosts
+                                        then carry their owners' raw coordinates and the list does not depend on the
+                                        decomposition.  (The reference pre-wraps ghosts instead, hoomd/Communicator.cc
+                                        exchangeGhosts + getShiftedBox, which rounds their coordinates once more.) */
     } b200_nlist_args;
 
 B200_API int b200_compute_nlist_binned(const b200_nlist_args* args, b200_stream_t stream);
@@ -503,8 +514,8 @@ B200_API int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned 
  *       dim.x, dim.y, dim.z, Nmax[0]} */
 B200_API int b200_sys_get_stats(b200_system* s, unsigned long long* out8);
 /* Micro-benchmarks in the spirit of Compute::benchmark (hoomd/ForceCompute.cc:153-180, hoomd/md/NeighborList.cc:260-289):
- * launches kernel `which` (0 = pair force on the current list, 1 = cell list + neighbor list build, 2 = the single-kernel
- * MD step on a scratch copy of the integrator state) `iters` times on the system's stream between two CUDA events and
+ * launches kernel `which` (0 = pair force on the current list, 1 = cell list + neighbor list build, 3 / 4 = its cell-list /
+ * neighbor-list half alone, 2 = the single-kernel MD step on a scratch copy of the integrator state) `iters` times on the system's stream between two CUDA events and
  * returns the average milliseconds per launch.  State is not advanced. */
 B200_API int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* avg_ms);
 /* ComputeThermo at the current step: out = {KE, PE, temperature, pressure, ndof} */

@@ -37,6 +37,10 @@ def lib():
         _lib.ref_setup_pair.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_int]
         _lib.ref_add_nvt.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        _lib.ref_add_npt.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_uint, C.c_int,
+                                     C.c_int, C.c_float]
+        _lib.ref_get_npt_state.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.ref_get_pressure_tensor.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
         _lib.ref_set_dist_check.argtypes = [C.c_void_p, C.c_int]
         _lib.ref_set_kT.argtypes = [C.c_void_p, C.c_float]
         _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
@@ -210,6 +214,26 @@ class RefSystem:
 
     def add_nvt(self, kT, tau):
         self._check(lib().ref_add_nvt(self.h, C.c_float(kT), C.c_float(tau)))
+
+    COUPLE = {"none": 0, "xy": 1, "xz": 2, "yz": 3, "xyz": 4}
+
+    def add_npt(self, kT, tau, P, tauP, couple="xyz", x=True, y=True, z=True, nph=False, rescale_all=False, gamma=0.0):
+        """md.integrate.npt on the method group (TwoStepNPTMTK, orthorhombic degrees of freedom)"""
+        flags = (1 if x else 0) | (2 if y else 0) | (4 if z else 0)
+        self._check(lib().ref_add_npt(self.h, C.c_float(kT), C.c_float(tau), C.c_float(P), C.c_float(tauP),
+                                      self.COUPLE[couple], flags, int(nph), int(rescale_all), C.c_float(gamma)))
+
+    def npt_state(self):
+        """{eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot, thermostat energy, barostat energy}"""
+        out = np.zeros(12, np.float32)
+        self._check(lib().ref_get_npt_state(self.h, _ptr(out)))
+        return out
+
+    def pressure_tensor(self, ts=None):
+        """{Pxx, Pxy, Pxz, Pyy, Pyz, Pzz, P, KE} from the full-step ComputeThermo"""
+        out = np.zeros(8, np.float32)
+        self._check(lib().ref_get_pressure_tensor(self.h, self.timestep if ts is None else ts, _ptr(out)))
+        return out
 
     def nvt_state(self):
         """Thermostat variables (xi, eta) of the NVT method."""

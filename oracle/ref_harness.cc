@@ -19,6 +19,7 @@
 #include "hoomd/SFCPackUpdater.h"
 #include "hoomd/ComputeThermo.h"
 #include "hoomd/md/TwoStepNVTMTK.h"
+#include "hoomd/md/TwoStepNPTMTK.h"
 #include "hoomd/BoxResizeUpdater.h"
 #include "hoomd/Saru.h"
 #include "hoomd/md/NeighborListBinned.h"
@@ -54,6 +55,8 @@ struct RefSystem
     std::shared_ptr<ComputeThermo> thermo;
     std::shared_ptr<ComputeThermo> thermo_nvt; // the method's own compute (hoomd/md/integrate.py:370-372)
     std::shared_ptr<TwoStepNVTMTK> nvt;
+    std::shared_ptr<ComputeThermo> thermo_npt, thermo_npt_t; // half-step / full-step computes of md.integrate.npt
+    std::shared_ptr<TwoStepNPTMTK> npt;
     unsigned int sorter_period = 0;
     unsigned int sorter_next = 0;
     unsigned int timestep = 0;
@@ -421,6 +424,71 @@ int ref_add_nvt(void* h, float kT, float tau)
     return 0;
     }
 
+//! md.integrate.npt(group, kT, tau, P, tauP, couple, x, y, z, nph, rescale_all, gamma) (hoomd/md/integrate.py:406-506):
+//! TwoStepNPTMTK with a half-step ComputeThermo of its own and a full-step one, both given the integrator's NDOF
+//! (hoomd/md/integrate.py:152-160); the method requests the pressure tensor (TwoStepNPTMTK.h:152-163).
+//! couple: 0 none, 1 xy, 2 xz, 3 yz, 4 xyz; flags: baro_x 1 | baro_y 2 | baro_z 4 (the box stays orthorhombic).
+int ref_add_npt(void* h, float kT, float tau, float P, float tauP, int couple, unsigned int flags, int nph, int rescale_all,
+                float gamma)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    if (flags & ~7u) throw std::runtime_error("ref_add_npt: tilt degrees of freedom are outside the harness");
+    std::shared_ptr<Variant> T(new VariantConst(kT));
+    std::shared_ptr<Variant> Pv(new VariantConst(P));
+    std::shared_ptr<ParticleGroup> grp = s->group_method ? s->group_method : s->group_all;
+    s->thermo_npt = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, grp, "npt"));
+    s->thermo_npt_t = std::shared_ptr<ComputeThermo>(new ComputeThermo(s->sysdef, grp, "npt_t"));
+    s->npt = std::shared_ptr<TwoStepNPTMTK>(new TwoStepNPTMTK(s->sysdef, grp, s->thermo_npt, s->thermo_npt_t, tau, tauP, T, Pv,
+                                                              (TwoStepNPTMTK::couplingMode)couple, flags, nph != 0));
+    s->npt->setRescaleAll(rescale_all != 0);
+    s->npt->setGamma(gamma);
+    s->integrator->removeAllIntegrationMethods();
+    s->integrator->addIntegrationMethod(s->npt);
+    s->thermo_npt->setNDOF(s->integrator->getNDOF(grp));
+    s->thermo_npt_t->setNDOF(s->integrator->getNDOF(grp));
+    s->virial = true;
+    apply_flags(s);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! the method's IntegratorVariables {eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot} and its two log
+//! quantities {npt_thermostat_energy, npt_barostat_energy} (hoomd/md/TwoStepNPTMTK.cc:593-636)
+int ref_get_npt_state(void* h, float* out12)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<IntegratorData> idata = s->sysdef->getIntegratorData();
+    for (int k = 0; k < 12; k++) out12[k] = 0.0f;
+    for (unsigned int i = 0; i < idata->getNumIntegrators(); i++)
+        {
+        const IntegratorVariables& v = idata->getIntegratorVariables(i);
+        if (v.type == "npt_mtk" && v.variable.size() >= 10)
+            for (int k = 0; k < 10; k++) out12[k] = v.variable[k];
+        }
+    bool mine = false;
+    out12[10] = s->npt->getLogValue("npt_thermostat_energy", s->timestep, mine);
+    out12[11] = s->npt->getLogValue("npt_barostat_energy", s->timestep, mine);
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! the full-step compute's pressure tensor {xx, xy, xz, yy, yz, zz}, pressure and translational kinetic energy at ts
+int ref_get_pressure_tensor(void* h, unsigned int ts, float* out8)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<ComputeThermo> t = s->thermo_npt_t ? s->thermo_npt_t : s->thermo;
+    t->compute(ts);
+    PressureTensor P = t->getPressureTensor();
+    out8[0] = P.xx; out8[1] = P.xy; out8[2] = P.xz; out8[3] = P.yy; out8[4] = P.yz; out8[5] = P.zz;
+    out8[6] = t->getPressure();
+    out8[7] = t->getTranslationalKineticEnergy();
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
 //! thermostat state {xi, eta} (IntegratorVariables of the method, hoomd/md/TwoStepNVTMTK.cc:387-404)
 int ref_get_nvt_state(void* h, float* xi_eta)
     {
@@ -492,6 +560,7 @@ int ref_set_kT(void* h, float kT)
     std::shared_ptr<Variant> T(new VariantConst(kT));
     if (s->langevin) s->langevin->setT(T);
     if (s->nvt) s->nvt->setT(T);
+    if (s->npt) s->npt->setT(T);
     REF_CATCH(s, 1)
     return 0;
     }

@@ -113,13 +113,15 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
         unw_rf = rp[:, :3].astype(np.float64) + ri * float(L)
         res.update(pos_err=float(np.abs(dpos).max()), vel_err=float(np.abs(g["vel"][:, :3] - rv[:, :3]).max()),
                    unwrapped_err=float(np.abs(unw_mg - unw_rf).max()), rebuilds_ref=int(r.nlist_stats()["updates"]),
-                   rebuilds_mg=int(mg.stats()["updates"]), mg_stats=mg.mg_stats())
+                   # NeighborList::getNumUpdates = normal + forced updates (hoomd/md/NeighborList.h:423-426)
+                   rebuilds_mg=int(mg.stats()["updates"] + mg.stats()["forced"]), mg_stats=mg.mg_stats(),
+                   mg_timing=mg.mg_timing())
         tol = 5e-3 * max(1.0, steps / 300.0)
         assert res["pos_err"] < tol and res["unwrapped_err"] < tol, res
         assert res["rebuilds_ref"] == res["rebuilds_mg"], res
     # the worst rank's figures
     allres = [None] * world
-    dist.all_gather_object(allres, {k: v for k, v in res.items() if k != "mg_stats"})
+    dist.all_gather_object(allres, {k: v for k, v in res.items() if k not in ("mg_stats", "mg_timing")})
     for k in ("max_force_err", "max_energy_err", "pos_err", "vel_err", "unwrapped_err"):
         if k in res:
             res[k] = max(q[k] for q in allres)
