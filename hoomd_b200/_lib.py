@@ -97,6 +97,8 @@ SYMBOLS = [
     "b200_sys_set_dist_check", "b200_sys_set_langevin_options", "b200_sys_set_diameters",
     "b200_sys_get_langevin_reservoir_energy", "b200_sys_set_group", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
     "b200_sys_add_nvt", "b200_sys_get_nvt_state", "b200_sys_set_nvt_state", "b200_nvt_mtk_step_one", "b200_nvt_mtk_step_two", "b200_nvt_mtk_advance",
+    "b200_sys_add_npt", "b200_sys_get_npt_state", "b200_sys_set_npt_state", "b200_sys_get_pressure_tensor",
+    "b200_npt_mtk_step_one", "b200_npt_mtk_wrap", "b200_npt_mtk_step_two", "b200_npt_mtk_rescale", "b200_compute_thermo_tensor",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
     "b200_sys_set_pair_mode", "b200_sys_get_pair_mode",
     "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
@@ -220,6 +222,16 @@ def lib():
     L.b200_nvt_mtk_step_one.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.POINTER(Box), vp, C.c_float, vp]
     L.b200_nvt_mtk_step_two.argtypes = [vp, vp, vp, C.c_uint, vp, vp, C.c_float, vp]
     L.b200_nvt_mtk_advance.argtypes = [vp, vp, C.c_uint, vp, vp, C.c_uint, C.c_uint, C.c_float, C.c_float, C.c_float, vp]
+    L.b200_sys_add_npt.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_uint, C.c_int, C.c_int,
+                                   C.c_float]
+    L.b200_sys_get_npt_state.argtypes = [vp, vp]
+    L.b200_sys_set_npt_state.argtypes = [vp, vp]
+    L.b200_sys_get_pressure_tensor.argtypes = [vp, vp]
+    L.b200_npt_mtk_step_one.argtypes = [vp, vp, vp, vp, C.c_uint, C.c_float, vp, vp, vp, C.c_float, C.c_int, vp]
+    L.b200_npt_mtk_wrap.argtypes = [C.c_uint, vp, vp, C.POINTER(Box), vp]
+    L.b200_npt_mtk_step_two.argtypes = [vp, vp, vp, C.c_uint, vp, vp, C.c_float, C.c_float, vp]
+    L.b200_npt_mtk_rescale.argtypes = [C.c_uint, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, vp]
+    L.b200_compute_thermo_tensor.argtypes = [vp, vp, C.c_uint, vp, vp, vp, C.c_uint, vp, C.c_uint, vp]
     L.b200_sys_set_sorter.argtypes = [vp, C.c_uint]
     L.b200_sys_sort_now.argtypes = [vp]
     L.b200_sys_set_timestep.argtypes = [vp, C.c_uint]

@@ -43,13 +43,15 @@ bool pdl_enabled(); // HOOMD_B200_PDL (cell_list.cu)
 // (non-periodic along split axes) and the second the GLOBAL box: ghosts hold their owners' raw coordinates and a pair
 // separation is pos_i - pos_j followed by the global minimum image -- the arithmetic of the single-domain reference
 // (hoomd/md/PotentialPair.h:337 takes getGlobalBox() as well), so results do not depend on the decomposition.
-// iforce: axes on which every cell may hold raw ghosts from across the global boundary (split axes).
+// iforce (split axes): bit 0 / bit 1 = the local box's low / high face lies on the global periodic boundary, so the ghost
+// cells on that side hold raw coordinates from the far side of the global box; ighost = how many cell layers from that face
+// have such a cell among their neighbors (set by the neighbor-list launcher from the ghost width; 255 = all).
 struct Box
     {
     float3 lo, hi, L, Linv;
     uchar3 periodic;
     float3 ilo, ihi, iL, iLinv;
-    uchar3 iperiodic, iforce;
+    uchar3 iperiodic, iforce, ighost;
     };
 
 __host__ __device__ inline Box make_box(const b200_box& b)
@@ -63,6 +65,7 @@ __host__ __device__ inline Box make_box(const b200_box& b)
     r.ilo = r.lo; r.ihi = r.hi; r.iL = r.L; r.iLinv = r.Linv;
     r.iperiodic = r.periodic;
     r.iforce = make_uchar3(0, 0, 0);
+    r.ighost = make_uchar3(255, 255, 255);
     return r;
     }
 
@@ -77,8 +80,10 @@ __host__ __device__ inline Box make_box_image(const b200_box& b, const b200_box*
         r.iL = make_float3(img->L[0], img->L[1], img->L[2]);
         r.iLinv = make_float3(img->Linv[0], img->Linv[1], img->Linv[2]);
         r.iperiodic = make_uchar3(img->periodic[0], img->periodic[1], img->periodic[2]);
-        r.iforce = make_uchar3(img->periodic[0] && !b.periodic[0], img->periodic[1] && !b.periodic[1],
-                               img->periodic[2] && !b.periodic[2]);
+        unsigned char f[3];
+        for (int a = 0; a < 3; a++)
+            f[a] = (img->periodic[a] && !b.periodic[a]) ? (unsigned char)((b.lo[a] <= img->lo[a] ? 1 : 0) | (b.hi[a] >= img->hi[a] ? 2 : 0)) : (unsigned char)0;
+        r.iforce = make_uchar3(f[0], f[1], f[2]);
         }
     return r;
     }
@@ -145,10 +150,15 @@ __device__ __forceinline__ float3 min_image_exact_sel(float3 w, const Box& box, 
     }
 
 // which axes of a cell's candidates need the minimum image at all: cells on a periodic face of the image box, short axes,
-// and -- under domain decomposition -- every cell of a split axis (its ghost cells hold raw coordinates)
-__device__ __forceinline__ bool cell_needs_image(bool iperiodic, bool iforce, unsigned int dim, unsigned int b)
+// and -- under domain decomposition -- the cell layers of a split axis whose neighbors include ghost cells with raw
+// coordinates from across the global boundary
+__device__ __forceinline__ bool cell_needs_image(bool iperiodic, bool local_periodic, unsigned int iforce, unsigned int ighost,
+                                                 unsigned int dim, unsigned int b)
     {
-    return iperiodic && (iforce || dim < 5 || b == 0 || b == dim - 1);
+    if (!iperiodic) return false;
+    if (local_periodic) return dim < 5 || b == 0 || b == dim - 1;
+    // split axis: only next to a face that coincides with the global boundary
+    return ((iforce & 1u) && b <= ighost) || ((iforce & 2u) && b + ighost + 1u >= dim);
     }
 
 // Branch-free form for the force kernel: w -= L * rint(w / L), the reference's DEVICE minImage (hoomd/BoxDim.h:281-300).

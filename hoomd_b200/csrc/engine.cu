@@ -167,7 +167,7 @@ struct b200_system
     // ---- IntegratorTwoStep + method ---------------------------------------------------------------------------
     bool have_integrator = false;
     float dt = 0.005f;
-    int method = 0; // 0 none, 1 TwoStepNVE, 2 TwoStepLangevin, 3 TwoStepNVTMTK
+    int method = 0; // 0 none, 1 TwoStepNVE, 2 TwoStepLangevin, 3 TwoStepNVTMTK, 4 TwoStepNPTMTK
     int limit = 0, zero_force = 0;
     float limit_val = 0.0f;
     float kT = 0.0f;
@@ -182,6 +182,24 @@ struct b200_system
     DevBuf<unsigned long long> nvt_acc;
     double nvt_scale = 1.0;
     static constexpr unsigned int NVT_BLOCKS = 592; // CTAs of the stand-alone kinetic-energy pass (4 per SM)
+    // TwoStepNPTMTK (method 4): IntegratorVariables and propagator on the host, as in the reference (steps are host-driven:
+    // every step changes the box and needs two thermo read-backs)
+    struct Npt
+        {
+        float eta = 0.0f, xi = 0.0f, nuxx = 0.0f, nuyy = 0.0f, nuzz = 0.0f; // the tilt momenta stay 0 (orthorhombic boxes)
+        float tau = 1.0f, tauP = 1.0f, P = 0.0f, gamma = 0.0f;
+        int couple = 4;           // 0 none, 1 xy, 2 xz, 3 yz, 4 xyz (TwoStepNPTMTK::couplingMode)
+        unsigned int flags = 7;   // baro_x 1 | baro_y 2 | baro_z 4
+        bool nph = false, rescale_all = false;
+        float mat_exp_v[6], mat_exp_r[6], mat_exp_r_int[6];
+        float V = 0.0f;
+        unsigned int ndof = 0;
+        // the full-step ComputeThermo caches its result per time step (Compute::shouldCompute)
+        bool th_valid = false;
+        unsigned int th_ts = 0;
+        float Pt[6] = {0, 0, 0, 0, 0, 0}, ke_t = 0.0f; // {xx, xy, xz, yy, yz, zz}
+        } npt;
+    DevBuf<double> npt_partial, npt_out;
 
     // ParticleGroup of the integration method (hoomd/ParticleGroup.h): 1 byte per TAG; empty = group.all().  group_idx is
     // ParticleGroup::getIndexArray (sorted member indices), rebuilt after every particle sort, for the stand-alone drivers.
@@ -212,6 +230,8 @@ struct b200_system
     cudaGraphExec_t graph_exec = nullptr;
     bool graph_valid = false;
     int graph_uses_cond = 0;
+    // MD steps per launch of the conditional graph (even; HOOMD_B200_GRAPH_UNROLL): [k_graph_pre] -> U x (IF{rebuild} -> k_md_step)
+    unsigned int graph_unroll = 2, graph_steps = 2;
     unsigned long long kernels_last_run = 0;
     // checkpoint of the device-driven chunk
     DevBuf<float4> ck_pos, ck_vel, ck_last_pos;
@@ -239,12 +259,15 @@ struct b200_system
     DevBuf<float> recv_shift;        // [27 * 3] periodic image shift of the ghosts received in segment d (binning only)
     DevBuf<GhostSendTable> gs_table;
     unsigned int mg_tpp = 2;         // lanes per particle of k_md_step under decomposition (fixes the chunk size of cta_order)
-    // Ghost update + all-ranks step barrier inside k_md_step, boundary chunks scheduled first (the default).
-    // HOOMD_B200_FUSED_GHOSTS=0: the round-1 sequence barrier kernel -> k_md_step -> k_mg_ghost_send, kept for A/B runs.
+    // Ghost update inside k_md_step with the boundary chunks scheduled first, so the NVLink stores overlap the interior force
+    // work (the default).  HOOMD_B200_FUSED_GHOSTS=0: the round-1 sequence barrier kernel -> k_md_step ->
+    // k_mg_ghost_send, kept for A/B runs.
     bool fused_ghosts = true;
     // HOOMD_B200_MG_MODE (A/B and debugging): bit 0 = ghost stores inside k_md_step, bit 1 = boundary-first CTA order,
-    // bit 2 = the step barrier inside k_md_step's last CTA (needs bit 0); default 7
-    int mg_mode = 7;
+    // bit 2 = the step barrier inside k_md_step's last CTA (needs bit 0).  Default 3: measured on 8 B200 (profiles/r2h_*) the
+    // in-kernel barrier (7) is slower than the one-warp barrier kernel -- a rank's last CTA spins while its SMs are
+    // otherwise idle either way, and the ranks reach it less aligned -- 3059 vs 3275 TPS.
+    int mg_mode = 3;
 
     // ---- cell-tile path (tile.cu): neighbor positions from shared memory, particles kept in cell order -------------
     int pair_mode = -1;              // -1 auto (tile when supported), 0 CSR walk, 1 tile (error when unsupported)
@@ -766,9 +789,190 @@ static void compute_net_force(b200_system* s, unsigned int ts)
         }
     }
 
+// ---- TwoStepNPTMTK, host part (hoomd/md/TwoStepNPTMTK.cc).  Scalar is float; Variant::getValue returns double, so the
+// expressions that touch m_T / m_S inline are evaluated in double exactly where the C++ promotion rules put them. ----------
+static void apply_new_box(b200_system* s, const b200_box& nb);
+
+// ComputeThermo::computeProperties with the pressure-tensor flag (hoomd/ComputeThermo.cc:224-240,300-372)
+static void npt_thermo(b200_system* s, bool with_virial, float* P6, float* ke)
+    {
+    const unsigned int nblocks = std::max(1u, std::min(1024u, (method_group_size(s) + 255u) / 256u));
+    if (s->npt_partial.n < 13u * 1024u)
+        {
+        s->npt_partial.alloc(13u * 1024u);
+        s->npt_out.alloc(13);
+        }
+    CUDA_OK(b200_compute_thermo_tensor(s->npt_out.p, s->npt_partial.p, nblocks, (const float*)s->vel.p, nullptr,
+                                       with_virial ? s->net_virial.p : nullptr, s->virial_pitch, group_index(s),
+                                       method_group_size(s), s->stream));
+    s->kernels_last_run += 2;
+    double h[13];
+    s->npt_out.download(h, 13, s->stream);
+    const double ke_trans_total = 0.5f * (h[0] + h[3] + h[5]);
+    *ke = (float)ke_trans_total;
+    if (P6)
+        {
+        const float volume = s->box.L[0] * s->box.L[1] * s->box.L[2];
+        for (int k = 0; k < 6; k++) P6[k] = (float)((h[k] + h[7 + k]) / volume);
+        }
+    }
+
+// m_thermo_group_t->compute(timestep): once per time step
+static void npt_thermo_full_step(b200_system* s, unsigned int ts)
+    {
+    b200_system::Npt& n = s->npt;
+    if (n.th_valid && n.th_ts == ts) return;
+    npt_thermo(s, true, n.Pt, &n.ke_t);
+    n.th_valid = true;
+    n.th_ts = ts;
+    }
+
+// TwoStepNPTMTK::advanceBarostat (TwoStepNPTMTK.cc:751-893)
+static void npt_advance_barostat(b200_system* s, unsigned int ts)
+    {
+    b200_system::Npt& n = s->npt;
+    npt_thermo_full_step(s, ts);
+    float Pxx = n.Pt[0], Pyy = n.Pt[3], Pzz = n.Pt[5];
+    bool bad = false;
+    for (int k = 0; k < 6; k++) bad = bad || std::isnan(n.Pt[k]);
+    const double S = (double)n.P, T = (double)s->kT;
+    if (bad) Pxx = Pyy = Pzz = (float)S;
+    const unsigned int d = 3;
+    const float W = (float)((double)((float)(n.ndof + d) / (float)d) * T * n.tauP * n.tauP);
+    float mtk_term = 2.0f * n.ke_t;
+    mtk_term *= 0.5f * s->dt / (float)n.ndof / W;
+    int couple = n.couple;
+    if (!(n.flags & 1u))
+        {
+        if (couple == 4) couple = 3;
+        if (couple == 1 || couple == 2) couple = 0;
+        }
+    if (!(n.flags & 2u))
+        {
+        if (couple == 4) couple = 2;
+        if (couple == 3 || couple == 1) couple = 0;
+        }
+    if (!(n.flags & 4u))
+        {
+        if (couple == 4) couple = 1;
+        if (couple == 3 || couple == 2) couple = 0;
+        }
+    float Px = Pxx, Py = Pyy, Pz = Pzz;
+    if (couple == 1) Px = Py = 0.5f * (Pxx + Pyy);
+    else if (couple == 2) Px = Pz = 0.5f * (Pxx + Pzz);
+    else if (couple == 3) Py = Pz = 0.5f * (Pyy + Pzz);
+    else if (couple == 4) Px = Py = Pz = (float)(1.0 / 3.0) * (Pxx + Pyy + Pzz);
+    const float pref = 0.5f * s->dt * n.V / W;
+    if (n.flags & 1u)
+        {
+        n.nuxx = (float)((double)n.nuxx + ((double)pref * ((double)Px - S) + (double)mtk_term));
+        n.nuxx -= n.gamma * n.nuxx;
+        }
+    if (n.flags & 2u)
+        {
+        n.nuyy = (float)((double)n.nuyy + ((double)pref * ((double)Py - S) + (double)mtk_term));
+        n.nuyy -= n.gamma * n.nuyy;
+        }
+    if (n.flags & 4u)
+        {
+        n.nuzz = (float)((double)n.nuzz + ((double)pref * ((double)Pz - S) + (double)mtk_term));
+        n.nuzz -= n.gamma * n.nuzz;
+        }
+    }
+
+// TwoStepNPTMTK::updatePropagator (TwoStepNPTMTK.cc:644-748) with nuxy = nuxz = nuyz = 0: the off-diagonal entries vanish
+static void npt_update_propagator(b200_system* s)
+    {
+    b200_system::Npt& n = s->npt;
+    static const float f_coeff[6] = {float(1.0), float(1.0 / 6.0), float(1.0 / 120.0), float(1.0 / 5040.0),
+                                     float(1.0 / 362880.0), float(1.0 / 39916800.0)};
+    const float dt = s->dt;
+    const float nu[3] = {n.nuxx, n.nuyy, n.nuzz};
+    for (int k = 0; k < 6; k++) n.mat_exp_v[k] = n.mat_exp_r[k] = n.mat_exp_r_int[k] = 0.0f;
+    const int diag[3] = {0, 3, 5};
+    for (int a = 0; a < 3; a++)
+        {
+        const float v_fac = -float(1.0 / 4.0) * nu[a];
+        const float exp_v_fac_2 = expf(2.0f * v_fac * dt);
+        const float r_fac = float(1.0 / 2.0) * nu[a];
+        const float exp_r_fac = expf(float(1.0 / 2.0) * nu[a] * dt);
+        const float exp_r_fac_2 = expf(nu[a] * dt);
+        const float arg_r = r_fac * dt;
+        float f_r = 0.0f, term_r = 1.0f;
+        for (unsigned int i = 0; i < 6; i++)
+            {
+            f_r += f_coeff[i] * term_r;
+            term_r = term_r * arg_r * arg_r;
+            }
+        n.mat_exp_v[diag[a]] = exp_v_fac_2;
+        n.mat_exp_r[diag[a]] = exp_r_fac_2;
+        n.mat_exp_r_int[diag[a]] = dt * exp_r_fac * f_r;
+        }
+    }
+
+// TwoStepNPTMTK::advanceThermostat (TwoStepNPTMTK.cc:895-930): half-step temperature from the method's own ComputeThermo
+static void npt_advance_thermostat(b200_system* s)
+    {
+    b200_system::Npt& n = s->npt;
+    float ke;
+    npt_thermo(s, false, nullptr, &ke);
+    const float curr_T_trans = 2.0f / (float)n.ndof * ke;
+    const float T = s->kT;
+    const float xi_prime = n.xi + float(1.0 / 2.0) * s->dt / n.tau / n.tau * (curr_T_trans / T - 1.0f);
+    n.xi = xi_prime + float(1.0 / 2.0) * s->dt / n.tau / n.tau * (curr_T_trans / T - 1.0f);
+    n.eta += xi_prime * s->dt;
+    }
+
+// TwoStepNPTMTK::integrateStepOne (TwoStepNPTMTK.cc:177-466)
+static void npt_step_one(b200_system* s, unsigned int ts)
+    {
+    b200_system::Npt& n = s->npt;
+    if (method_group_size(s) == 0) throw std::runtime_error("integrate.npt(): Integration group empty.");
+    n.V = s->box.L[0] * s->box.L[1] * s->box.L[2];
+    n.ndof = nvt_ndof(s);
+    npt_advance_barostat(s, ts);
+    const float mtk = (n.nuxx + n.nuyy + n.nuzz) / (float)n.ndof;
+    npt_update_propagator(s);
+    // advance the box lengths: the lattice vectors times the (diagonal) position propagator; BoxDim::setL
+    b200_box nb;
+    b200_box_init(&nb, n.mat_exp_r[0] * s->box.L[0], n.mat_exp_r[3] * s->box.L[1], n.mat_exp_r[5] * s->box.L[2]);
+    for (int d = 0; d < 3; d++) nb.periodic[d] = s->box.periodic[d];
+    apply_new_box(s, nb);
+    n.V = s->box.L[0] * s->box.L[1] * s->box.L[2];
+    if (n.rescale_all)
+        {
+        CUDA_OK(b200_npt_mtk_rescale(s->N, (float*)s->pos.p, n.mat_exp_r[0], n.mat_exp_r[1], n.mat_exp_r[2],
+                                     n.mat_exp_r[3], n.mat_exp_r[4], n.mat_exp_r[5], s->stream));
+        s->kernels_last_run += 1;
+        }
+    const float exp_thermo_fac = expf(-float(1.0 / 2.0) * (n.xi + mtk) * s->dt);
+    CUDA_OK(b200_npt_mtk_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, group_index(s),
+                                  method_group_size(s), exp_thermo_fac, n.mat_exp_v, n.mat_exp_r, n.mat_exp_r_int, s->dt,
+                                  n.rescale_all ? 1 : 0, s->stream));
+    CUDA_OK(b200_npt_mtk_wrap(s->N, (float*)s->pos.p, (int*)s->image.p, &s->box, s->stream));
+    s->kernels_last_run += 2;
+    if (!n.nph) npt_advance_thermostat(s);
+    }
+
+// TwoStepNPTMTK::integrateStepTwo (TwoStepNPTMTK.cc:471-580)
+static void npt_step_two(b200_system* s, unsigned int ts)
+    {
+    b200_system::Npt& n = s->npt;
+    const float mtk = (n.nuxx + n.nuyy + n.nuzz) / (float)n.ndof;
+    const float exp_thermo_fac = expf(-float(1.0 / 2.0) * (n.xi + mtk) * s->dt);
+    CUDA_OK(b200_npt_mtk_step_two((float*)s->vel.p, (float*)s->accel.p, group_index(s), method_group_size(s),
+                                  (const float*)s->net_force.p, n.mat_exp_v, s->dt, exp_thermo_fac, s->stream));
+    s->kernels_last_run += 1;
+    npt_advance_barostat(s, ts + 1);
+    }
+
 static void integrate_step_one(b200_system* s, unsigned int ts)
     {
-    (void)ts;
+    if (s->method == 4)
+        {
+        npt_step_one(s, ts);
+        return;
+        }
     if (s->method == 3)
         {
         CUDA_OK(b200_nvt_mtk_step_one((float*)s->pos.p, (float*)s->vel.p, (const float*)s->accel.p, (int*)s->image.p,
@@ -786,6 +990,11 @@ static void integrate_step_one(b200_system* s, unsigned int ts)
 
 static void integrate_step_two(b200_system* s, unsigned int ts)
     {
+    if (s->method == 4)
+        {
+        npt_step_two(s, ts);
+        return;
+        }
     if (s->method == 2)
         {
         b200_langevin_args la;
@@ -826,6 +1035,30 @@ static void integrate_step_two(b200_system* s, unsigned int ts)
         CUDA_OK(b200_nve_step_two((float*)s->vel.p, (float*)s->accel.p, group_index(s), method_group_size(s),
                                   (const float*)s->net_force.p, s->dt, s->limit, s->limit_val, s->zero_force, s->stream));
     s->kernels_last_run += 1;
+    }
+
+// ParticleData::setGlobalBox and its box-change signal: the cell list re-dimensions itself (CellList.cc:151-171), the
+// neighbor list's distance check sees lambda = L_new / L_last_build from then on
+static void apply_new_box(b200_system* s, const b200_box& nb)
+    {
+    s->box = nb;
+    s->global_box = nb;
+    if (s->have_nlist)
+        {
+        // same bin counts => only the width changes
+        b200_dim3 nd;
+        b200_cell_list_dimensions(&s->box, s->nominal_width, 1, 0.0f, &nd, s->ghost_width);
+        if (nd.x != s->dim.x || nd.y != s->dim.y || nd.z != s->dim.z)
+            {
+            CUDA_OK(cudaStreamSynchronize(s->stream));
+            s->dim = nd;
+            const size_t ncells = (size_t)nd.x * nd.y * nd.z;
+            s->cell_count.alloc(ncells);
+            s->cell_start.alloc(ncells + 1);
+            }
+        s->cl_force = true;
+        }
+    invalidate_graph(s); // the box is a by-value argument of the captured kernels
     }
 
 // IntegratorTwoStep::prepRun (hoomd/md/IntegratorTwoStep.cc:336-398)
@@ -979,31 +1212,37 @@ static bool build_graph_conditional(b200_system* s)
     try
         {
         CUDA_OK(cudaGraphCreate(&graph, 0));
-        cudaGraphConditionalHandle h0, h1;
-        CUDA_OK(cudaGraphConditionalHandleCreate(&h0, graph, 0, cudaGraphCondAssignDefault));
-        CUDA_OK(cudaGraphConditionalHandleCreate(&h1, graph, 0, cudaGraphCondAssignDefault));
+        const unsigned int U = std::max(2u, std::min(32u, s->graph_unroll & ~1u));
+        std::vector<cudaGraphConditionalHandle> h(U);
+        std::vector<cudaGraph_t> body(U);
+        for (unsigned int k = 0; k < U; k++)
+            CUDA_OK(cudaGraphConditionalHandleCreate(&h[k], graph, 0, cudaGraphCondAssignDefault));
         CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
         capturing = true;
-        CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h0, s->stream));
-        cudaGraph_t body0 = add_if_node(s, graph, h0);
-        enqueue_md_step(s, fa, 0, (unsigned long long)h1, 1);
-        cudaGraph_t body1 = add_if_node(s, graph, h1);
-        enqueue_md_step(s, fa, 1, 0ull, 0);
+        CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h[0], s->stream));
+        for (unsigned int k = 0; k < U; k++)
+            {
+            // every step kernel arms the IF node of the step behind it; the last one leaves that to the next launch's pre
+            body[k] = add_if_node(s, graph, h[k]);
+            if (k + 1 < U)
+                enqueue_md_step(s, fa, (int)(k & 1u), (unsigned long long)h[k + 1], 1);
+            else
+                enqueue_md_step(s, fa, (int)(k & 1u), 0ull, 0);
+            }
         cudaGraph_t out = nullptr;
         CUDA_OK(cudaStreamEndCapture(s->stream, &out));
         capturing = false;
         // bodies of the IF nodes
-        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body0, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
-        capturing = true;
-        enqueue_rebuild(s, enable, s->pos.p);
-        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
-        capturing = false;
-        CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body1, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
-        capturing = true;
-        enqueue_rebuild(s, enable, s->pos_alt.p);
-        CUDA_OK(cudaStreamEndCapture(s->stream, &out));
-        capturing = false;
+        for (unsigned int k = 0; k < U; k++)
+            {
+            CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body[k], nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+            capturing = true;
+            enqueue_rebuild(s, enable, (k & 1u) ? s->pos_alt.p : s->pos.p);
+            CUDA_OK(cudaStreamEndCapture(s->stream, &out));
+            capturing = false;
+            }
         CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+        s->graph_steps = U;
         }
     catch (const std::exception& e)
         {
@@ -1049,6 +1288,7 @@ static void build_graph_plain(b200_system* s)
         }
     CUDA_OK(cudaStreamEndCapture(s->stream, &s->graph));
     CUDA_OK(cudaGraphInstantiate(&s->graph_exec, s->graph, 0));
+    s->graph_steps = 2;
     s->graph_uses_cond = 0;
     s->graph_valid = true;
     }
@@ -1143,7 +1383,10 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
     if (s->method == 3) nvt_advance(s); // thermostat of the prologue's step one; the later ones run inside k_md_step
     CUDA_OK(launch_decide(s->d_state.p, s->stream));
-    const unsigned int nreplay = (chunk + 1) / 2;
+    // kernels behind the end of the chunk return at once (steps_left == 0): a chunk need not be a multiple of the graph
+    const unsigned int per_launch = direct ? 2u : s->graph_steps;
+    const unsigned int nlaunch = (chunk + per_launch - 1u) / per_launch;
+    const unsigned int nreplay = nlaunch * (per_launch / 2u); // pairs of step kernels launched
     if (direct)
         {
         // same kernel sequence as the plain graph, launched directly on the stream (profilers see every kernel)
@@ -1157,7 +1400,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
             }
         }
     else
-        for (unsigned int k = 0; k < nreplay; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+        for (unsigned int k = 0; k < nlaunch; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
     if (st.nvt_error)
@@ -1252,7 +1495,7 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
-    s->kernels_last_run += 2ull + ((s->graph_uses_cond && !direct) ? (3ull * nreplay + rk * rebuilds)
+    s->kernels_last_run += 2ull + ((s->graph_uses_cond && !direct) ? (2ull * nreplay + nlaunch + rk * rebuilds)
                                                                              : (2ull + 2ull * rk) * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
@@ -1305,6 +1548,10 @@ static void sys_open_device(b200_system* s)
 // ghost region under domain decomposition)
 static void sys_alloc_common(b200_system* s)
     {
+    // Small systems are bound by the gaps between graph launches (6.9 us per step at 64k with two steps per launch): 16 steps
+    // per launch, 28.8k -> 30.7k TPS (profiles/r2j_*).  Large systems gain nothing and keep the short graph.
+    s->graph_unroll = s->N <= 150000u ? 16u : 2u;
+    if (const char* e = getenv("HOOMD_B200_GRAPH_UNROLL")) s->graph_unroll = (unsigned int)std::max(2, atoi(e));
     const unsigned int N = s->N, C = s->Ncap;
     s->vel.alloc(C); s->net_force.alloc(C); s->accel.alloc(C); s->image.alloc(C);
     s->rtag.alloc(C); s->last_pos.alloc(C);
@@ -1901,24 +2148,7 @@ int b200_sys_set_box(b200_system* s, float Lx, float Ly, float Lz, int scale_par
     for (int d = 0; d < 3; d++) nb.periodic[d] = s->box.periodic[d];
     CUDA_OK(b200_box_resize_particles((float*)s->pos.p, (int*)s->image.p, s->N, &s->box, &nb, scale_particles, s->stream));
     s->kernels_last_run += 1;
-    s->box = nb;
-    s->global_box = nb;
-    if (s->have_nlist)
-        {
-        // CellList::compute on m_box_changed (CellList.cc:151-171): same bin counts => only the width changes
-        b200_dim3 nd;
-        b200_cell_list_dimensions(&s->box, s->nominal_width, 1, 0.0f, &nd, s->ghost_width);
-        if (nd.x != s->dim.x || nd.y != s->dim.y || nd.z != s->dim.z)
-            {
-            CUDA_OK(cudaStreamSynchronize(s->stream));
-            s->dim = nd;
-            const size_t ncells = (size_t)nd.x * nd.y * nd.z;
-            s->cell_count.alloc(ncells);
-            s->cell_start.alloc(ncells + 1);
-            }
-        s->cl_force = true;
-        }
-    invalidate_graph(s); // the box is a by-value argument of the captured kernels
+    apply_new_box(s, nb);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     SYS_CATCH(s)
     }
@@ -1934,8 +2164,9 @@ void b200_sys_get_box(b200_system* s, float* L3)
 int b200_sys_set_temperature(b200_system* s, float kT)
     {
     SYS_TRY(s)
-    if (s->method != 2 && s->method != 3) throw std::runtime_error("integrate: the active method has no temperature");
-    if (s->method == 3 && !(kT > 0.0f)) throw std::runtime_error("integrate.nvt: kT must be positive");
+    if (s->method != 2 && s->method != 3 && s->method != 4)
+        throw std::runtime_error("integrate: the active method has no temperature");
+    if (s->method >= 3 && !(kT > 0.0f)) throw std::runtime_error("integrate.nvt / npt: kT must be positive");
     if (kT != s->kT)
         {
         s->kT = kT;
@@ -2008,6 +2239,86 @@ int b200_sys_get_nvt_state(b200_system* s, float* xi_eta)
     CUDA_OK(cudaMemcpy(h, s->d_nvt.p, sizeof(h), cudaMemcpyDeviceToHost));
     xi_eta[0] = h[0];
     xi_eta[1] = h[1];
+    SYS_CATCH(s)
+    }
+
+// md.integrate.npt(group, kT, tau, P, tauP, couple, x, y, z, nph, rescale_all, gamma) (hoomd/md/integrate.py:406-506)
+int b200_sys_add_npt(b200_system* s, float kT, float tau, float P, float tauP, int couple, unsigned int flags, int nph,
+                     int rescale_all, float gamma)
+    {
+    SYS_TRY(s)
+    if (s->mg) throw std::runtime_error("integrate.npt: not available under domain decomposition yet");
+    if (s->tile_on) throw std::runtime_error("integrate.npt: not available on the cell-tile path");
+    if (flags & ~7u) throw std::runtime_error("integrate.npt: tilt degrees of freedom (xy, xz, yz) need triclinic boxes");
+    if (couple < 0 || couple > 4) throw std::runtime_error("integrate.npt: Invalid coupling mode.");
+    if (!nph && !(kT > 0.0f)) throw std::runtime_error("integrate.npt: kT must be positive");
+    if (tau <= 0.0f) fprintf(stderr, "*Warning*: integrate.npt: tau set less than 0.0\n");   // TwoStepNPTMTK.cc:67-70
+    if (tauP <= 0.0f) fprintf(stderr, "*Warning*: integrate.npt: tauP set less than 0.0\n");
+    if (flags == 0) fprintf(stderr, "*Warning*: integrate.npt: No barostat couplings specified.\n");
+    s->method = 4;
+    s->limit = 0;
+    s->zero_force = 0;
+    s->kT = kT;
+    s->npt = b200_system::Npt();
+    s->npt.tau = tau;
+    s->npt.tauP = tauP;
+    s->npt.P = P;
+    s->npt.couple = couple;
+    s->npt.flags = flags;
+    s->npt.nph = nph != 0;
+    s->npt.rescale_all = rescale_all != 0;
+    s->npt.gamma = gamma;
+    // the method requests the pressure tensor on every step (TwoStepNPTMTK.h:152-163)
+    s->compute_virial = 1;
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
+/* out12: the method's IntegratorVariables {eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot} and its log
+ * quantities {npt_thermostat_energy, npt_barostat_energy} (TwoStepNPTMTK.cc:593-636) */
+int b200_sys_get_npt_state(b200_system* s, float* out12)
+    {
+    SYS_TRY(s)
+    if (s->method != 4) throw std::runtime_error("integrate.npt: no NPT method set");
+    const b200_system::Npt& n = s->npt;
+    const float v[10] = {n.eta, n.xi, n.nuxx, 0.0f, 0.0f, n.nuyy, 0.0f, n.nuzz, 0.0f, 0.0f};
+    for (int k = 0; k < 10; k++) out12[k] = v[k];
+    const unsigned int ndof = nvt_ndof(s), d = 3;
+    const double T = (double)s->kT;
+    out12[10] = (float)((double)ndof * T * (double)(n.eta + n.tau * n.tau * n.xi * n.xi / 2.0f));
+    const float W = (float)((double)((float)(n.ndof + d) / (float)d) * T * n.tauP * n.tauP);
+    out12[11] = W * (n.nuxx * n.nuxx + n.nuyy * n.nuyy + n.nuzz * n.nuzz + 0.0f + 0.0f + 0.0f) / 2.0f;
+    SYS_CATCH(s)
+    }
+
+int b200_sys_set_npt_state(b200_system* s, const float* vars10)
+    {
+    SYS_TRY(s)
+    if (s->method != 4) throw std::runtime_error("integrate.npt: no NPT method set");
+    s->npt.eta = vars10[0];
+    s->npt.xi = vars10[1];
+    s->npt.nuxx = vars10[2];
+    s->npt.nuyy = vars10[5];
+    s->npt.nuzz = vars10[7];
+    SYS_CATCH(s)
+    }
+
+/* ComputeThermo::getPressureTensor of the integration group at the current step: {xx, xy, xz, yy, yz, zz, P, KE} */
+int b200_sys_get_pressure_tensor(b200_system* s, float* out8)
+    {
+    SYS_TRY(s)
+    if (!s->compute_virial) throw std::runtime_error("compute.thermo: the pressure tensor needs the virial (b200_sys_set_virial)");
+    float P6[6], ke;
+    npt_thermo(s, true, P6, &ke);
+    for (int k = 0; k < 6; k++) out8[k] = P6[k];
+    // ComputeThermo.cc:352: isotropic pressure from the same sums (W = trace of the virial / 3)
+    double h[13];
+    s->npt_out.download(h, 13, s->stream);
+    const float volume = s->box.L[0] * s->box.L[1] * s->box.L[2];
+    const double ke_d = 0.5f * (h[0] + h[3] + h[5]);
+    const double W = (float)(1. / 3.) * (h[7] + h[10] + h[12]);
+    out8[6] = (float)((2.0 * ke_d / 3.0f + W) / volume);
+    out8[7] = ke;
     SYS_CATCH(s)
     }
 
@@ -2115,7 +2426,7 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
         if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
         if (s->mg)
             mg_run_chunk(s, chunk);
-        else if (s->use_graph)
+        else if (s->use_graph && s->method != 4)
             run_chunk_device(s, chunk);
         else
             for (unsigned int k = 0; k < chunk; k++) host_step(s);

@@ -496,3 +496,241 @@ extern "C" int b200_compute_thermo_static(double* d_out, unsigned int n_partial_
     k_thermo_final<<<1, 32, 0, stream>>>(d_out, scratch, n_partial_blocks);
     return (int)cudaGetLastError();
     }
+
+// ---- TwoStepNPTMTK (hoomd/md/TwoStepNPTMTK.cc:177-330,471-533, hoomd/md/TwoStepNPTMTKGPU.cu): the particle loops of the
+// Martyna-Tobias-Klein barostat/thermostat.  The propagator matrices (upper triangular, {xx, xy, xz, yy, yz, zz}) and the
+// thermostat factor are computed by the caller on the host, exactly as the reference does (updatePropagator); the kernels
+// restate the per-particle arithmetic operation by operation (no FMA contraction) so that trajectories follow the
+// reference's to the last bit of every half step.
+namespace b200
+{
+struct NptMat { float v[6], r[6], ri[6]; };
+
+// a.x*m0 + a.y*m1 + a.z*m2 evaluated left to right like the C++ expression m0*x + m1*y + m2*z
+__device__ __forceinline__ float npt_row3(float m0, float x, float m1, float y, float m2, float z)
+    {
+    return __fadd_rn(__fadd_rn(__fmul_rn(m0, x), __fmul_rn(m1, y)), __fmul_rn(m2, z));
+    }
+__device__ __forceinline__ float npt_row2(float m0, float x, float m1, float y)
+    {
+    return __fadd_rn(__fmul_rn(m0, x), __fmul_rn(m1, y));
+    }
+
+__global__ void __launch_bounds__(256) k_npt_step_one(float4* __restrict__ pos, float4* __restrict__ vel,
+                                                      const float3s* __restrict__ accel,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      const NptMat m, float exp_thermo_fac, float dt, int rescale_all)
+    {
+    const unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 p = pos[j], v = vel[j];
+    const float3s a = accel[j];
+    // v += deltaT/2 * accel
+    const float hdt = __fdiv_rn(dt, 2.0f);
+    v.x = __fadd_rn(v.x, __fmul_rn(hdt, a.x));
+    v.y = __fadd_rn(v.y, __fmul_rn(hdt, a.y));
+    v.z = __fadd_rn(v.z, __fmul_rn(hdt, a.z));
+    // barostat: multiply with the matrix exponential (each row reads the not yet overwritten components)
+    v.x = npt_row3(m.v[0], v.x, m.v[1], v.y, m.v[2], v.z);
+    v.y = npt_row2(m.v[3], v.y, m.v[4], v.z);
+    v.z = __fmul_rn(m.v[5], v.z);
+    // thermostat
+    v.x = __fmul_rn(v.x, exp_thermo_fac);
+    v.y = __fmul_rn(v.y, exp_thermo_fac);
+    v.z = __fmul_rn(v.z, exp_thermo_fac);
+    if (!rescale_all)
+        {
+        p.x = npt_row3(m.r[0], p.x, m.r[1], p.y, m.r[2], p.z);
+        p.y = npt_row2(m.r[3], p.y, m.r[4], p.z);
+        p.z = __fmul_rn(m.r[5], p.z);
+        }
+    p.x = __fadd_rn(p.x, npt_row3(m.ri[0], v.x, m.ri[1], v.y, m.ri[2], v.z));
+    p.y = __fadd_rn(p.y, npt_row2(m.ri[3], v.y, m.ri[4], v.z));
+    p.z = __fadd_rn(p.z, __fmul_rn(m.ri[5], v.z));
+    pos[j] = p;
+    vel[j] = v;
+    }
+
+__global__ void __launch_bounds__(256) k_npt_rescale(float4* __restrict__ pos, unsigned int N, float rxx, float rxy,
+                                                     float rxz, float ryy, float ryz, float rzz)
+    {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    float4 p = pos[i];
+    p.x = npt_row3(rxx, p.x, rxy, p.y, rxz, p.z);
+    p.y = npt_row2(ryy, p.y, ryz, p.z);
+    p.z = __fmul_rn(rzz, p.z);
+    pos[i] = p;
+    }
+
+__global__ void __launch_bounds__(256) k_npt_wrap(float4* __restrict__ pos, int3* __restrict__ image, unsigned int N,
+                                                  Box box)
+    {
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    float4 p = pos[i];
+    int3 img = image[i];
+    box_wrap(p.x, p.y, p.z, img, box);
+    pos[i] = p;
+    image[i] = img;
+    }
+
+__global__ void __launch_bounds__(256) k_npt_step_two(float4* __restrict__ vel, float3s* __restrict__ accel,
+                                                      const unsigned int* __restrict__ group, unsigned int group_size,
+                                                      const float4* __restrict__ net_force, const NptMat m, float dt,
+                                                      float exp_thermo_fac)
+    {
+    const unsigned int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= group_size) return;
+    const unsigned int j = group ? group[g] : g;
+    float4 v = vel[j];
+    const float4 f = net_force[j];
+    const float minv = __fdiv_rn(1.0f, v.w);
+    float3s a;
+    a.x = __fmul_rn(f.x, minv);
+    a.y = __fmul_rn(f.y, minv);
+    a.z = __fmul_rn(f.z, minv);
+    v.x = __fmul_rn(v.x, exp_thermo_fac);
+    v.y = __fmul_rn(v.y, exp_thermo_fac);
+    v.z = __fmul_rn(v.z, exp_thermo_fac);
+    v.x = npt_row3(m.v[0], v.x, m.v[1], v.y, m.v[2], v.z);
+    v.y = npt_row2(m.v[3], v.y, m.v[4], v.z);
+    v.z = __fmul_rn(m.v[5], v.z);
+    const float hdt = __fdiv_rn(dt, 2.0f);
+    v.x = __fadd_rn(v.x, __fmul_rn(hdt, a.x));
+    v.y = __fadd_rn(v.y, __fmul_rn(hdt, a.y));
+    v.z = __fadd_rn(v.z, __fmul_rn(hdt, a.z));
+    vel[j] = v;
+    accel[j] = a;
+    }
+
+// ComputeThermo with pdata_flag::pressure_tensor (hoomd/ComputeThermo.cc:224-240,300-318): the six components of
+// sum(m v v) and of the virial, and the potential energy, in double
+constexpr int TT_NQ = 13;
+__global__ void __launch_bounds__(256) k_thermo_tensor_partial(double* __restrict__ partial, const float4* __restrict__ vel,
+                                                               const float4* __restrict__ net_force,
+                                                               const float* __restrict__ net_virial,
+                                                               unsigned int virial_pitch,
+                                                               const unsigned int* __restrict__ group,
+                                                               unsigned int group_size)
+    {
+    double acc[TT_NQ];
+#pragma unroll
+    for (int q = 0; q < TT_NQ; q++) acc[q] = 0.0;
+    for (unsigned int g = blockIdx.x * blockDim.x + threadIdx.x; g < group_size; g += gridDim.x * blockDim.x)
+        {
+        const unsigned int j = group ? group[g] : g;
+        const float4 v = vel[j];
+        const double mass = (double)v.w, x = (double)v.x, y = (double)v.y, z = (double)v.z;
+        acc[0] += mass * (x * x);
+        acc[1] += mass * (x * y);
+        acc[2] += mass * (x * z);
+        acc[3] += mass * (y * y);
+        acc[4] += mass * (y * z);
+        acc[5] += mass * (z * z);
+        if (net_force) acc[6] += (double)net_force[j].w;
+        if (net_virial)
+            {
+#pragma unroll
+            for (int k = 0; k < 6; k++) acc[7 + k] += (double)net_virial[k * virial_pitch + j];
+            }
+        }
+    __shared__ double s[8][TT_NQ];
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int q = 0; q < TT_NQ; q++)
+        {
+        double x = acc[q];
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) s[warp][q] = x;
+        }
+    __syncthreads();
+    if (threadIdx.x < TT_NQ)
+        {
+        double x = 0.0;
+        for (int w = 0; w < 8; w++) x += s[w][threadIdx.x];
+        partial[(size_t)blockIdx.x * TT_NQ + threadIdx.x] = x;
+        }
+    }
+
+__global__ void k_thermo_tensor_final(double* __restrict__ out, const double* __restrict__ partial, unsigned int nblocks)
+    {
+    if (threadIdx.x < TT_NQ)
+        {
+        double x = 0.0;
+        for (unsigned int b = 0; b < nblocks; b++) x += partial[(size_t)b * TT_NQ + threadIdx.x];
+        out[threadIdx.x] = x;
+        }
+    }
+} // namespace b200
+
+extern "C" {
+
+int b200_npt_mtk_step_one(float* d_pos, float* d_vel, const float* d_accel, const unsigned int* d_group_members,
+                          unsigned int group_size, float exp_thermo_fac, const float* mat_exp_v, const float* mat_exp_r,
+                          const float* mat_exp_r_int, float deltaT, int rescale_all, b200_stream_t stream)
+    {
+    if (group_size == 0) return 0;
+    NptMat m;
+    for (int k = 0; k < 6; k++)
+        {
+        m.v[k] = mat_exp_v[k];
+        m.r[k] = mat_exp_r[k];
+        m.ri[k] = mat_exp_r_int[k];
+        }
+    k_npt_step_one<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_pos, (float4*)d_vel, (const float3s*)d_accel, d_group_members, group_size, m, exp_thermo_fac, deltaT,
+        rescale_all);
+    return (int)cudaGetLastError();
+    }
+
+int b200_npt_mtk_wrap(unsigned int N, float* d_pos, int* d_image, const b200_box* box, b200_stream_t stream)
+    {
+    if (N == 0) return 0;
+    if (!box_is_orthorhombic(*box)) return (int)cudaErrorNotSupported;
+    k_npt_wrap<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)d_pos, (int3*)d_image, N, make_box(*box));
+    return (int)cudaGetLastError();
+    }
+
+int b200_npt_mtk_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members, unsigned int group_size,
+                          const float* d_net_force, const float* mat_exp_v, float deltaT, float exp_thermo_fac,
+                          b200_stream_t stream)
+    {
+    if (group_size == 0) return 0;
+    NptMat m;
+    for (int k = 0; k < 6; k++)
+        {
+        m.v[k] = mat_exp_v[k];
+        m.r[k] = m.ri[k] = 0.0f;
+        }
+    k_npt_step_two<<<(group_size + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        (float4*)d_vel, (float3s*)d_accel, d_group_members, group_size, (const float4*)d_net_force, m, deltaT,
+        exp_thermo_fac);
+    return (int)cudaGetLastError();
+    }
+
+int b200_npt_mtk_rescale(unsigned int N, float* d_pos, float mat_exp_r_xx, float mat_exp_r_xy, float mat_exp_r_xz,
+                         float mat_exp_r_yy, float mat_exp_r_yz, float mat_exp_r_zz, b200_stream_t stream)
+    {
+    if (N == 0) return 0;
+    k_npt_rescale<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)d_pos, N, mat_exp_r_xx, mat_exp_r_xy,
+                                                                    mat_exp_r_xz, mat_exp_r_yy, mat_exp_r_yz,
+                                                                    mat_exp_r_zz);
+    return (int)cudaGetLastError();
+    }
+
+int b200_compute_thermo_tensor(double* d_out, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                               const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                               const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream_)
+    {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n_partial_blocks == 0 || !d_partial || !d_out) return (int)cudaErrorInvalidValue;
+    k_thermo_tensor_partial<<<n_partial_blocks, 256, 0, stream>>>(d_partial, (const float4*)d_vel,
+                                                                 (const float4*)d_net_force, d_net_virial, virial_pitch,
+                                                                 d_group_members, group_size);
+    k_thermo_tensor_final<<<1, 32, 0, stream>>>(d_out, d_partial, n_partial_blocks);
+    return (int)cudaGetLastError();
+    }
+
+} // extern "C"

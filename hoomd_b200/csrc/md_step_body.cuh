@@ -73,7 +73,9 @@ constexpr int MD_BLOCK = B200_MD_BLOCK; // threads per CTA of k_md_step (B200 sw
 
 // phase 2 of the step for particle i: net force F -> step two(ts2) -> step one(ts2+1) -> distance check.  Returns the
 // particle's distance-check result.
-template<class Evaluator, bool VIRIAL>
+// EXTRAS = false compiles out the integration group, the Langevin dscale / tally options and the multi-GPU ghost stores:
+// the plain single-GPU variants keep their 48-register budget without spills (md_step_kernel.cuh)
+template<class Evaluator, bool VIRIAL, bool EXTRAS = true>
 __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a, unsigned int i, float4 F,
                                                   const float4 pi4, float (&vir)[6], unsigned int ts2, bool last,
                                                   bool store_force, double& mv2, float exp_fac = 1.0f,
@@ -102,7 +104,7 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
             }
         }
     const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
-    if (a.group_flag && !a.group_flag[a.tag[i]])
+    if (EXTRAS && a.group_flag && !a.group_flag[a.tag[i]])
         {
         // not in the integration method's group: the force is reported, nothing moves (the ping-pong buffer still needs
         // the unchanged position; a particle at rest never trips the distance check)
@@ -121,9 +123,9 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     else
         {
         const unsigned int ptag = a.tag[i];
-        const float gamma = a.use_lambda ? __fmul_rn(a.gamma_lambda, a.diameter[ptag]) : a.gamma[type_i];
+        const float gamma = (EXTRAS && a.use_lambda) ? __fmul_rn(a.gamma_lambda, a.diameter[ptag]) : a.gamma[type_i];
         const float e = langevin_step_two_body(v, acc, F, ptag, ts2, a.seed, gamma, a.kT, a.dt, a.noiseless_t != 0, 3u);
-        if (a.tally_acc) mv2 = (double)e; // energy handed to the particle by the bath this step (md_step_finish sums it)
+        if (EXTRAS && a.tally_acc) mv2 = (double)e; // energy handed to the particle by the bath this step (md_step_finish sums it)
         }
     a.accel[i] = acc;
     if (!last)
@@ -140,7 +142,7 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
         else
             nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
         a.pos_out[i] = p;
-        if (a.gs.tab)
+        if (EXTRAS && a.gs.tab)
             {
             const bool sent = md_step_send_ghosts(a, i, p);
             if (pushed) *pushed = sent;
@@ -159,7 +161,7 @@ __device__ __forceinline__ bool md_step_integrate(const MdStepArgs<Evaluator>& a
     else if (a.copy_pos_on_last)
         {
         a.pos_out[i] = pi4;
-        if (a.gs.tab)
+        if (EXTRAS && a.gs.tab)
             {
             const bool sent = md_step_send_ghosts(a, i, pi4);
             if (pushed) *pushed = sent;
@@ -221,7 +223,7 @@ __device__ __forceinline__ void md_step_nvt_wait(const MdStepArgs<Evaluator>& a,
     }
 
 // last CTA to finish takes the rebuild decision for the next launch (every thread of the CTA must call this).
-template<class Evaluator>
+template<class Evaluator, bool EXTRAS = true>
 __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, StepState* st, bool moved,
                                                unsigned int steps_left, bool last, double mv2 = 0.0,
                                                unsigned int ts2 = 0, bool pushed = false)
@@ -229,8 +231,8 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
     // multi-GPU: did this CTA store ghosts into a peer's buffer?  Only those CTAs (the boundary chunks, scheduled first) pay
     // for a system-scope fence; a fence in every CTA cost 15-20 % of the kernel (profiles/r2e_*)
-    const int any_pushed = (a.mg == 2) ? __syncthreads_or(pushed ? 1 : 0) : 0;
-    if (a.method == 2 && a.tally_acc)
+    const int any_pushed = (EXTRAS && a.mg == 2) ? __syncthreads_or(pushed ? 1 : 0) : 0;
+    if (EXTRAS && a.method == 2 && a.tally_acc)
         {
         // reservoir-energy tally: sum_j F_bd . v' of this step (double atomics: a diagnostic, order-dependent in the last bits)
         for (int o = 16; o > 0; o >>= 1) mv2 += __shfl_xor_sync(0xffffffffu, mv2, o);
@@ -274,7 +276,7 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
             st->steps_left = steps_left - 1u;
-            if (a.mg)
+            if (EXTRAS && a.mg)
                 ; // the vote needs every rank: the step barrier decides (below, or k_mg_step_barrier)
             else if (!last)
                 decide_body(st);
@@ -284,11 +286,11 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
                 st->moved = 0u;
                 }
 #if (CUDART_VERSION >= 12040)
-            if (a.use_cond && a.mg != 2) cudaGraphSetConditional(a.handle, st->need_rebuild);
+            if (a.use_cond && !(EXTRAS && a.mg == 2)) cudaGraphSetConditional(a.handle, st->need_rebuild);
 #endif
             }
         }
-    if (a.mg == 2)
+    if (EXTRAS && a.mg == 2)
         {
         // Multi-GPU: the last CTA of this rank to finish takes the all-ranks step barrier.  Every CTA's ghost stores into the
         // peers' buffers are fenced before its ticket, so the flag this warp publishes orders them (RAW for the neighbors'

@@ -19,7 +19,7 @@ template<class Evaluator, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE> struct M
     static constexpr bool value = !MULTI_TYPE && !VIRIAL && SHIFT_MODE != 2 && std::is_same<Evaluator, EvaluatorPairLJ>::value;
     };
 
-template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE, int OCC = 0>
+template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL, bool MULTI_TYPE, int OCC = 0, bool EXTRAS = true>
 __global__ void __launch_bounds__(MD_BLOCK, !MdStepPlain<Evaluator, SHIFT_MODE, VIRIAL, MULTI_TYPE>::value
                                                 ? 1 : (OCC ? 1536 / MD_BLOCK : 1280 / MD_BLOCK))
 k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
@@ -41,9 +41,9 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
     const bool last = steps_left == 1;
     const unsigned int ts2 = st->ts_step_two;
     const bool store_force = last || st->store_force;
-    const unsigned int N = a.d_N ? *a.d_N : a.N;
+    const unsigned int N = (EXTRAS && a.d_N) ? *a.d_N : a.N;
     // multi-GPU: chunks that touch the ghost layer are scheduled first (their ghost stores overlap the interior chunks)
-    const unsigned int chunk = a.gs.cta_order ? a.gs.cta_order[blockIdx.x] : blockIdx.x;
+    const unsigned int chunk = (EXTRAS && a.gs.cta_order) ? a.gs.cta_order[blockIdx.x] : blockIdx.x;
     __shared__ float s_exp_fac;
     md_step_nvt_begin(a, st, ts2); // NVT: thread 0 of block 0 advances the thermostat for this launch (no-op otherwise)
 
@@ -102,10 +102,10 @@ k_md_step(const __grid_constant__ MdStepArgs<Evaluator> a)
 #pragma unroll
             for (int c = 0; c < 6; c++) vir[c] = s_virial[c * PPB + threadIdx.x];
             }
-        moved = md_step_integrate<Evaluator, VIRIAL>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last, store_force,
-                                                     mv2, a.method == 3 ? s_exp_fac : 1.0f, &pushed);
+        moved = md_step_integrate<Evaluator, VIRIAL, EXTRAS>(a, i, s_force[threadIdx.x], a.pos_in[i], vir, ts2, last,
+                                                             store_force, mv2, a.method == 3 ? s_exp_fac : 1.0f, &pushed);
         }
-    md_step_finish(a, st, moved, steps_left, last, mv2, ts2, pushed);
+    md_step_finish<Evaluator, EXTRAS>(a, st, moved, steps_left, last, mv2, ts2, pushed);
     }
 
 template<class Evaluator, int TPP, int SHIFT_MODE, bool VIRIAL>
@@ -138,9 +138,19 @@ static cudaError_t md_step_mt(const MdStepArgs<Evaluator>& a, cudaStream_t strea
             // large systems are latency bound on the neighbor gathers: trade 8 registers for 2 more CTAs per SM
             static const char* occ_env = getenv("HOOMD_B200_MD_OCC");
             const bool high_occ = occ_env ? atoi(occ_env) != 0 : a.N >= 200000u;
+            // group / dscale / tally / domain decomposition: the variants that carry those paths (a few registers more)
+            const bool extras = a.group_flag || a.tally_acc || a.use_lambda || a.mg || a.gs.tab || a.gs.cta_order || a.d_N;
             if (high_occ)
                 {
-                k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false, 1><<<grid, bs, 0, stream>>>(a);
+                if (extras)
+                    k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false, 1, true><<<grid, bs, 0, stream>>>(a);
+                else
+                    k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false, 1, false><<<grid, bs, 0, stream>>>(a);
+                return cudaGetLastError();
+                }
+            if (!extras)
+                {
+                k_md_step<Evaluator, TPP, SHIFT_MODE, VIRIAL, false, 0, false><<<grid, bs, 0, stream>>>(a);
                 return cudaGetLastError();
                 }
             }

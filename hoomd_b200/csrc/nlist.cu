@@ -2,6 +2,8 @@
 // cell-sorted array (x-adjacent cells are adjacent in memory), 32 candidates per coalesced 512 B load, ballot/popc
 // compaction into the CSR list.  Membership arithmetic and entry order are those of the CPU oracle
 // hoomd/md/NeighborListBinned.cc:144-236 (see include/hoomd_b200.h).
+#include <cmath>
+#include <algorithm>
 #include "common.cuh"
 #include "kernels.h"
 #include "bulk_copy.cuh"
@@ -272,9 +274,9 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
     // A candidate of an interior cell is less than two cell widths away along every axis; with >= 5 cells per axis that is
     // inside [lo, hi) and minImage is the identity: only cells on a periodic face pay for it (CTA-uniform).
-    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
-    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
-    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.periodic.x, box.iforce.x, box.ighost.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.periodic.y, box.iforce.y, box.ighost.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.periodic.z, box.iforce.z, box.ighost.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NL_CAP)
@@ -427,9 +429,9 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
     __syncwarp();
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
-    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
-    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
-    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.periodic.x, box.iforce.x, box.ighost.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.periodic.y, box.iforce.y, box.ighost.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.periodic.z, box.iforce.z, box.ighost.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
 
     for (unsigned int pass = 0; pass < total; pass += NW_CAP)
@@ -613,9 +615,9 @@ __global__ void __launch_bounds__(NC_BLOCK) k_nlist_cellscan(unsigned int* __res
     const unsigned int total = s_off[nr];
     const float rcut_00 = MULTI_TYPE ? 0.0f : r_cut[0];
     const float rlsq_00 = MULTI_TYPE ? 0.0f : r_listsq[0];
-    const bool wx = cell_needs_image(box.iperiodic.x, box.iforce.x, dim.x, bx);
-    const bool wy = cell_needs_image(box.iperiodic.y, box.iforce.y, dim.y, by);
-    const bool wz = cell_needs_image(box.iperiodic.z, box.iforce.z, dim.z, bz);
+    const bool wx = cell_needs_image(box.iperiodic.x, box.periodic.x, box.iforce.x, box.ighost.x, dim.x, bx);
+    const bool wy = cell_needs_image(box.iperiodic.y, box.periodic.y, box.iforce.y, box.ighost.y, dim.y, by);
+    const bool wz = cell_needs_image(box.iperiodic.z, box.periodic.z, box.iforce.z, box.ighost.z, dim.z, bz);
     const bool wrap_any = wx || wy || wz;
     const unsigned int slot = threadIdx.x / NC_G, sub = threadIdx.x % NC_G;
     unsigned int parity = 0;
@@ -921,6 +923,19 @@ cudaError_t launch_nlist_binned(const b200_nlist_args* a, const unsigned int* en
     Box box = make_box_image(a->box, a->image_box);
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
+        {
+        // ghost cells on a face: those below ghost_width / cell_width (bins span [lo - gw, hi + gw)); one more layer has them
+        // among its neighbors
+        unsigned char ig[3];
+        const unsigned int d3[3] = {a->dim.x, a->dim.y, a->dim.z};
+        for (int ax = 0; ax < 3; ax++)
+            {
+            const float cw = (a->box.L[ax] + 2.0f * a->ghost_width[ax]) / (float)d3[ax];
+            const float layers = a->ghost_width[ax] > 0.0f ? a->ghost_width[ax] / cw + 1e-3f : 0.0f;
+            ig[ax] = (unsigned char)std::min(254.0f, std::floor(layers) + 1.0f);
+            }
+        box.ighost = make_uchar3(ig[0], ig[1], ig[2]);
+        }
     const bool pdl = enable && pdl_enabled(); // chained behind k_cell_rank (launch_chain, common.cuh)
     static const bool use_warp_kernel = getenv("HOOMD_B200_NLIST_WARP") != nullptr; // A/B switches for profiling
     // the cell-scan kernel executes ~2.5x fewer instructions than the tiled one but is latency-bound per CTA and measured

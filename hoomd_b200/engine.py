@@ -212,6 +212,32 @@ class System:
         self._check(_lib.lib().b200_sys_get_nvt_state(self.h, _p(out)))
         return out
 
+    COUPLE = {"none": 0, "xy": 1, "xz": 2, "yz": 3, "xyz": 4}
+
+    def add_npt(self, kT, tau, P, tauP, couple="xyz", x=True, y=True, z=True, nph=False, rescale_all=False, gamma=0.0):
+        """md.integrate.npt(group, kT, tau, P, tauP, couple, x, y, z, nph, rescale_all, gamma): TwoStepNPTMTK on an
+        orthorhombic box (hoomd/md/integrate.py:406-506).  Steps are host-driven: the box changes every step."""
+        flags = (1 if x else 0) | (2 if y else 0) | (4 if z else 0)
+        self._check(_lib.lib().b200_sys_add_npt(self.h, C.c_float(kT), C.c_float(tau), C.c_float(P), C.c_float(tauP),
+                                                self.COUPLE[couple], flags, int(nph), int(rescale_all), C.c_float(gamma)))
+
+    def npt_state(self):
+        """{eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot, npt_thermostat_energy, npt_barostat_energy}"""
+        out = np.zeros(12, np.float32)
+        self._check(_lib.lib().b200_sys_get_npt_state(self.h, _p(out)))
+        return out
+
+    def set_npt_state(self, vars10):
+        st = np.ascontiguousarray(vars10, np.float32)
+        assert st.size >= 10
+        self._check(_lib.lib().b200_sys_set_npt_state(self.h, _p(st)))
+
+    def pressure_tensor(self):
+        """{Pxx, Pxy, Pxz, Pyy, Pyz, Pzz, P, KE} of the integration group at the current step (needs set_virial)"""
+        out = np.zeros(8, np.float32)
+        self._check(_lib.lib().b200_sys_get_pressure_tensor(self.h, _p(out)))
+        return out
+
     def set_sorter(self, period):
         self._check(_lib.lib().b200_sys_set_sorter(self.h, int(period)))
 

@@ -826,8 +826,63 @@ class _NVT(_Method):
         context.current.engine_dirty = True
 
 
+class _NPT(_Method):
+    """md.integrate.npt (hoomd/md/integrate.py:262-620): Martyna-Tobias-Klein barostat + Nose-Hoover thermostat
+    (TwoStepNPTMTK).  Orthorhombic boxes: the tilt degrees of freedom xy / xz / yz (and all=True) raise."""
+
+    def __init__(self, group, kT=None, tau=None, S=None, P=None, tauP=None, couple="xyz", x=True, y=True, z=True,
+                 xy=False, xz=False, yz=False, all=False, nph=False, rescale_all=None, gamma=None):
+        if kT is None or tau is None:
+            if nph is False:
+                raise RuntimeError("Error setting up NPT integration.")  # integrate.npt: Need temperature T and tau
+            kT, tau = 1.0, 1.0  # "use dummy values" (hoomd/md/integrate.py:414-417)
+        if tauP is None:
+            raise RuntimeError("Error setting up NPT integration.")      # integrate.npt: Need barostat time scale tauP
+        if P is not None:
+            S = [P, P, P, 0, 0, 0]
+        elif S is None or len(S) != 6:
+            raise RuntimeError("Unrecognized stress tensor form")
+        if couple not in ("none", "xy", "xz", "yz", "xyz"):
+            raise RuntimeError("Error setting up NPT integration.")      # Invalid coupling mode
+        if xy or xz or yz or all:
+            raise RuntimeError("hoomd_b200: integrate.npt with tilt degrees of freedom needs triclinic boxes")
+        if any(float(v) != float(S[0]) for v in S[1:3]) or any(float(v) != 0.0 for v in S[3:]):
+            raise RuntimeError("hoomd_b200: integrate.npt supports an isotropic pressure set point (S = [P, P, P, 0, 0, 0])")
+        super().__init__(group)
+        self.kT_variant, self.tau, self.tauP = _setup_variant_input(kT), float(tau), float(tauP)
+        self.P_variant = _setup_variant_input(S[0])
+        if not isinstance(self.P_variant, _VariantConst):
+            raise RuntimeError("hoomd_b200: integrate.npt takes a constant pressure set point (no pressure ramps yet)")
+        self.couple, self.x, self.y, self.z = couple, bool(x), bool(y), bool(z)
+        self.nph, self.rescale_all = bool(nph), bool(rescale_all) if rescale_all is not None else False
+        self.gamma = 0.0 if gamma is None else float(gamma)
+        self._state = None
+
+    def set_params(self, kT=None, tau=None, S=None, P=None, tauP=None, rescale_all=None, gamma=None):
+        if kT is not None:
+            self.kT_variant = _setup_variant_input(kT)
+        if tau is not None:
+            self.tau = float(tau)
+        if P is not None:
+            self.P_variant = _setup_variant_input(P)
+        elif S is not None:
+            self.P_variant = _setup_variant_input(S[0])
+        if tauP is not None:
+            self.tauP = float(tauP)
+        if rescale_all is not None:
+            self.rescale_all = bool(rescale_all)
+        if gamma is not None:
+            self.gamma = float(gamma)
+        context.current.engine_dirty = True
+
+    @property
+    def P(self):
+        return float(np.float32(self.P_variant.getValue(context.current.timestep)))
+
+
 md.integrate.mode_standard = _ModeStandard
 md.integrate.nvt = _NVT
+md.integrate.npt = _NPT
 md.integrate.nve = _NVE
 md.integrate.langevin = _Langevin
 
@@ -844,7 +899,9 @@ class _Log(_Scheduled):
         for q in quantities:
             # per-force energies are logged under "<force name>_energy": pair_<kind>_energy (hoomd/md/PotentialPair.h:200-215),
             # bond_<kind>_energy (hoomd/md/PotentialBond.h:118-133); whether that force exists is checked when it is queried
-            if q not in self.QUANTITIES and q not in ("nvt_mtk_reservoir_energy_all", "langevin_reservoir_energy_all") \
+            if q not in self.QUANTITIES and q not in ("nvt_mtk_reservoir_energy_all", "langevin_reservoir_energy_all",
+                                                      "npt_thermostat_energy", "npt_barostat_energy", "volume", "lx", "ly",
+                                                      "lz") \
                     and not re.fullmatch(r"(pair|bond)_[a-z_]+_energy", q):
                 raise RuntimeError("Unknown log quantity " + q)
         self.quantities, self.filename, self.rows = list(quantities), filename, []
@@ -888,6 +945,11 @@ class _Log(_Scheduled):
             return context.current.engine.langevin_reservoir_energy()
         if quantity == "nvt_mtk_reservoir_energy_all":  # provided by md.integrate.nvt (log name + "_" + group name)
             return context.current.engine.nvt_reservoir_energy()
+        if quantity in ("npt_thermostat_energy", "npt_barostat_energy"):  # TwoStepNPTMTK::getLogValue
+            return float(context.current.engine.npt_state()[10 if quantity == "npt_thermostat_energy" else 11])
+        if quantity in ("volume", "lx", "ly", "lz"):  # System-provided box quantities (hoomd/System.cc / analyze.log docs)
+            L3 = [float(v) for v in context.current.engine.box_lengths()]
+            return L3[0] * L3[1] * L3[2] if quantity == "volume" else L3["xyz".index(quantity[1])]
         ctx = context.current
         if quantity not in self.QUANTITIES:
             # the energy of ONE ForceCompute (ForceCompute::calcEnergySum, hoomd/ForceCompute.cc:82-102), not the total
@@ -927,11 +989,13 @@ def _configure_engine():
         for m in methods:  # IntegratorVariables live in the SystemDefinition, not in the method (hoomd/IntegratorData.h)
             if isinstance(m, _NVT) and getattr(ctx.engine, "_has_nvt", False):
                 m._state = tuple(ctx.engine.nvt_state())
+            if isinstance(m, _NPT) and getattr(ctx.engine, "_has_npt", False):
+                m._state = ctx.engine.npt_state()[:10].copy()
         ctx.engine.close()
     eng = System(sysd.pos4, (sysd.box.Lx, sysd.box.Ly, sysd.box.Lz), ntypes=len(sysd.types), vel4=sysd.vel4,
                  image=sysd.image)
     t = lj.tables(sysd.types)
-    need_virial = any("pressure" in lg.quantities for lg in ctx.loggers)
+    need_virial = any("pressure" in lg.quantities for lg in ctx.loggers) or any(isinstance(m, _NPT) for m in methods)
     if lj.kind == "lj":
         eng.setup_lj(r_cut=t["r_cut"], epsilon=t["epsilon"], sigma=t["sigma"], alpha=t["alpha"], r_buff=lj.nlist.r_buff,
                      check_period=lj.nlist.check_period, shift_mode=lj.shift_mode,
@@ -961,6 +1025,12 @@ def _configure_engine():
         eng._has_nvt = True
         if getattr(m, "_state", None) is not None:
             eng.set_nvt_state(*m._state)
+    elif isinstance(m, _NPT):
+        eng.add_npt(m.kT, m.tau, m.P, m.tauP, couple=m.couple, x=m.x, y=m.y, z=m.z, nph=m.nph,
+                    rescale_all=m.rescale_all, gamma=m.gamma)
+        eng._has_npt = True
+        if m._state is not None:
+            eng.set_npt_state(m._state)
     else:
         gamma = [m.gamma.get(tn, 1.0) for tn in sysd.types]
         eng.add_langevin(m.kT, m.seed, gamma=gamma, noiseless_t=m.noiseless_t, dscale=m.dscale, tally=m.tally)
@@ -1038,6 +1108,9 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
         eng.run(nxt)
         ctx.forces_stale = False
         done += nxt
+        if getattr(eng, "_has_npt", False):  # the barostat moves the box every step (ParticleData::setGlobalBox)
+            L3 = [float(v) for v in eng.box_lengths()]
+            ctx.system.box = _BoxDim(L3[0], L3[1], L3[2])
     ctx.timestep = eng.timestep
     if callback and cb_period == 0:
         callback(ctx.timestep)  # callback_period 0: called once at the end of the run (hoomd/System.cc:617-621)

@@ -342,6 +342,27 @@ B200_API int b200_nvt_mtk_advance(float* d_nvt_state, double* d_partial, unsigne
                                   float T, float tau, float deltaT, b200_stream_t stream);
 
 /* -----------------------------------------------------------------------------------------------------------------------
+ * TwoStepNPTMTK (Martyna-Tobias-Klein barostat + Nose-Hoover thermostat, point particles) -- replaces
+ * gpu_npt_mtk_step_one / gpu_npt_mtk_wrap / gpu_npt_mtk_step_two / gpu_npt_mtk_rescale
+ * (hoomd/md/TwoStepNPTMTKGPU.cuh:20-58, called from hoomd/md/TwoStepNPTMTKGPU.cc).  Same operands: the three upper-
+ * triangular propagator matrices {xx, xy, xz, yy, yz, zz} are HOST arrays of 6 values (TwoStepNPTMTK::updatePropagator,
+ * hoomd/md/TwoStepNPTMTK.cc:644-748, computed by the caller), exp_thermo_fac = exp(-(xi + mtk) dt / 2).  Step one moves the
+ * group (velocity half kick, barostat matrix, thermostat factor, position scale + drift); the caller then wraps ALL particles
+ * into the new box with b200_npt_mtk_wrap.  rescale_all != 0: the caller scales every position with b200_npt_mtk_rescale
+ * before step one, which then skips the position scale (TwoStepNPTMTK.cc:251-270).  Per-particle arithmetic follows the
+ * reference's CPU loops operation by operation. */
+B200_API int b200_npt_mtk_step_one(float* d_pos, float* d_vel, const float* d_accel, const unsigned int* d_group_members,
+                                   unsigned int group_size, float exp_thermo_fac, const float* mat_exp_v,
+                                   const float* mat_exp_r, const float* mat_exp_r_int, float deltaT, int rescale_all,
+                                   b200_stream_t stream);
+B200_API int b200_npt_mtk_wrap(unsigned int N, float* d_pos, int* d_image, const b200_box* box, b200_stream_t stream);
+B200_API int b200_npt_mtk_step_two(float* d_vel, float* d_accel, const unsigned int* d_group_members,
+                                   unsigned int group_size, const float* d_net_force, const float* mat_exp_v, float deltaT,
+                                   float exp_thermo_fac, b200_stream_t stream);
+B200_API int b200_npt_mtk_rescale(unsigned int N, float* d_pos, float mat_exp_r_xx, float mat_exp_r_xy, float mat_exp_r_xz,
+                                  float mat_exp_r_yy, float mat_exp_r_yz, float mat_exp_r_zz, b200_stream_t stream);
+
+/* -----------------------------------------------------------------------------------------------------------------------
  * BoxResizeUpdater::update, particle part (hoomd/BoxResizeUpdater.cc:98-131; the reference does this on the host):
  * scale_particles != 0: pos = new_box.makeCoordinates(old_box.makeFraction(pos)); else wrap pos into new_box and update
  * the image flags.  The caller sets the new global box afterwards (ParticleData::setGlobalBox) -- the cell list then
@@ -384,6 +405,14 @@ B200_API int b200_sfc_apply_sorted_order(const b200_pdata_arrays* out, const b20
 B200_API int b200_compute_thermo(double* d_out, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
                                  const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
                                  const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream);
+
+/* ComputeThermo with pdata_flag::pressure_tensor set (hoomd/ComputeThermo.cc:224-240,300-318; gpu_compute_thermo with
+ * compute_pressure_tensor, hoomd/ComputeThermoGPU.cu): d_out = double[13] {sum m vx vx, m vx vy, m vx vz, m vy vy, m vy vz,
+ * m vz vz, sum of net_force.w, sum of the six virial rows xx, xy, xz, yy, yz, zz}; d_partial = double[13 * n_partial_blocks].
+ * The caller forms KE = (xx + yy + zz) / 2 and P_ab = (kinetic_ab + virial_ab) / V as ComputeThermo.cc:352-372 does. */
+B200_API int b200_compute_thermo_tensor(double* d_out, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                                        const float* d_net_force, const float* d_net_virial, unsigned int virial_pitch,
+                                        const unsigned int* d_group_members, unsigned int group_size, b200_stream_t stream);
 
 /* b200_compute_thermo WITHOUT a caller scratch buffer and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
@@ -472,6 +501,17 @@ B200_API int b200_sys_set_dist_check(b200_system* s, int on);
 B200_API int b200_sys_add_nvt(b200_system* s, float kT, float tau);
 B200_API int b200_sys_get_nvt_state(b200_system* s, float* xi_eta);
 B200_API int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta);
+/* md.integrate.npt(group, kT, tau, P, tauP, couple, x, y, z, nph, rescale_all, gamma): TwoStepNPTMTK
+ * (hoomd/md/TwoStepNPTMTK.cc) on an orthorhombic box.  couple: 0 none, 1 xy, 2 xz, 3 yz, 4 xyz; flags: baro_x 1 | baro_y 2 |
+ * baro_z 4 (the tilt degrees of freedom need triclinic boxes and are rejected).  The barostat / thermostat variables and the
+ * propagator stay on the host as in the reference; the steps are host-driven (b200_npt_mtk_* + b200_compute_thermo_tensor).
+ * get_npt_state: out12 = IntegratorVariables {eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot} and the log
+ * quantities {npt_thermostat_energy, npt_barostat_energy}; get_pressure_tensor: {xx, xy, xz, yy, yz, zz, P, KE}. */
+B200_API int b200_sys_add_npt(b200_system* s, float kT, float tau, float P, float tauP, int couple, unsigned int flags,
+                              int nph, int rescale_all, float gamma);
+B200_API int b200_sys_get_npt_state(b200_system* s, float* out12);
+B200_API int b200_sys_set_npt_state(b200_system* s, const float* vars10);
+B200_API int b200_sys_get_pressure_tensor(b200_system* s, float* out8);
 /* hoomd.update.box_resize at a period boundary: one BoxResizeUpdater::update towards the orthorhombic box (Lx, Ly, Lz).
  * Steps run host-driven until the next neighbor-list build (the reference's lambda-scaled distance check decides it), then
  * device-driven again in the new box. */

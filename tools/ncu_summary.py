@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Summarise ncu outputs brought back in gpurun_out/ into small tracked text files under profiles/.
 
-  python scratch/ncu_summary.py launches gpurun_out/launches_r1.csv profiles/r1_launches.md
-  python scratch/ncu_summary.py full gpurun_out/prof_pair_r1.ncu-rep profiles/r1_pair_full.md
+  python tools/ncu_summary.py launches gpurun_out/launches_r1.csv profiles/r1_launches.md
+  python tools/ncu_summary.py full gpurun_out/prof_pair_r1.ncu-rep profiles/r1_pair_full.md
 """
 import collections
 import csv
