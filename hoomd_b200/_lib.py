@@ -100,7 +100,7 @@ SYMBOLS = [
     "b200_sys_add_npt", "b200_sys_get_npt_state", "b200_sys_set_npt_state", "b200_sys_get_pressure_tensor",
     "b200_npt_mtk_step_one", "b200_npt_mtk_wrap", "b200_npt_mtk_step_two", "b200_npt_mtk_rescale", "b200_compute_thermo_tensor",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
-    "b200_sys_set_pair_mode", "b200_sys_get_pair_mode",
+    "b200_sys_set_pair_mode", "b200_sys_get_pair_mode", "b200_sys_get_stepping", "b200_sys_set_multistep",
     "b200_sys_compute_nlist", "b200_sys_compute_forces", "b200_sys_run", "b200_sys_step_one", "b200_sys_step_two",
     "b200_sys_get_forces", "b200_sys_get_nlist_size", "b200_sys_get_nlist", "b200_sys_get_stats",
     "b200_sys_get_thermo", "b200_sys_time_kernel",
@@ -232,6 +232,8 @@ def lib():
     L.b200_npt_mtk_step_two.argtypes = [vp, vp, vp, C.c_uint, vp, vp, C.c_float, C.c_float, vp]
     L.b200_npt_mtk_rescale.argtypes = [C.c_uint, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, vp]
     L.b200_compute_thermo_tensor.argtypes = [vp, vp, C.c_uint, vp, vp, vp, C.c_uint, vp, C.c_uint, vp]
+    L.b200_sys_get_stepping.argtypes = [vp, vp]
+    L.b200_sys_set_multistep.argtypes = [vp, C.c_int]
     L.b200_sys_set_sorter.argtypes = [vp, C.c_uint]
     L.b200_sys_sort_now.argtypes = [vp]
     L.b200_sys_set_timestep.argtypes = [vp, C.c_uint]

@@ -87,6 +87,28 @@ struct i3 { int x, y, z; };
 
 using namespace b200;
 
+// a pair of CUDA events that is destroyed on every way out of the scope (exceptions included)
+struct EventPair
+    {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    EventPair()
+        {
+        if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess)
+            {
+            if (e0) cudaEventDestroy(e0);
+            e0 = e1 = nullptr;
+            throw std::runtime_error("cudaEventCreate failed");
+            }
+        }
+    ~EventPair()
+        {
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        }
+    EventPair(const EventPair&) = delete;
+    EventPair& operator=(const EventPair&) = delete;
+    };
+
 struct b200_system
     {
     int device = 0;
@@ -232,6 +254,12 @@ struct b200_system
     int graph_uses_cond = 0;
     // MD steps per launch of the conditional graph (even; HOOMD_B200_GRAPH_UNROLL): [k_graph_pre] -> U x (IF{rebuild} -> k_md_step)
     unsigned int graph_unroll = 2, graph_steps = 2;
+    // Multi-step launches (k_md_steps, md_steps_persist.cuh): every graph unit is [k_graph_pre] -> IF{rebuild} -> k_md_steps,
+    // which runs until the next rebuild.  persist_mode: -1 auto (on when the configuration and the grid allow it), 0 off
+    int persist_mode = -1;
+    bool graph_persist = false;
+    double persist_steps_per_unit = 4.0; // running estimate of the MD steps one unit advances (the rebuild interval)
+    unsigned long long persist_units_last_run = 0;
     unsigned long long kernels_last_run = 0;
     // checkpoint of the device-driven chunk
     DevBuf<float4> ck_pos, ck_vel, ck_last_pos;
@@ -1212,16 +1240,39 @@ static bool build_graph_conditional(b200_system* s)
     try
         {
         CUDA_OK(cudaGraphCreate(&graph, 0));
-        const unsigned int U = std::max(2u, std::min(32u, s->graph_unroll & ~1u));
+        // multi-step launches: plain LJ configurations whose whole grid is co-resident
+        bool persist = false;
+        if (s->persist_mode != 0 && s->pair_kind == B200_PAIR_LJ && !s->tile_on && s->bond_kind < 0)
+            {
+            b200_pair_args ppa;
+            pair_args(s, ppa);
+            persist = launch_md_steps_lj(ppa, (const float*)s->d_params.p, fa, s->pos.p, s->pos_alt.p, s->d_state.p, 1, 0ull, 0,
+                                         s->stream) == cudaSuccess;
+            cudaGetLastError();
+            }
+        s->graph_persist = persist;
+        const unsigned int U = persist ? 8u : std::max(2u, std::min(32u, s->graph_unroll & ~1u));
         std::vector<cudaGraphConditionalHandle> h(U);
         std::vector<cudaGraph_t> body(U);
         for (unsigned int k = 0; k < U; k++)
             CUDA_OK(cudaGraphConditionalHandleCreate(&h[k], graph, 0, cudaGraphCondAssignDefault));
         CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
         capturing = true;
-        CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h[0], s->stream));
+        if (!persist) CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h[0], s->stream));
         for (unsigned int k = 0; k < U; k++)
             {
+            if (persist)
+                {
+                // unit = rebuild from buffer A if wanted, then step until the next rebuild is wanted (the kernel leaves the
+                // current positions in A and arms the next unit's IF node; the first one is armed from the pending decision)
+                if (k == 0) CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h[0], s->stream));
+                body[k] = add_if_node(s, graph, h[k]);
+                b200_pair_args ppa;
+                pair_args(s, ppa);
+                CUDA_OK(launch_md_steps_lj(ppa, (const float*)s->d_params.p, fa, s->pos.p, s->pos_alt.p, s->d_state.p, 0,
+                                           k + 1 < U ? (unsigned long long)h[k + 1] : 0ull, k + 1 < U ? 1 : 0, s->stream));
+                continue;
+                }
             // every step kernel arms the IF node of the step behind it; the last one leaves that to the next launch's pre
             body[k] = add_if_node(s, graph, h[k]);
             if (k + 1 < U)
@@ -1237,7 +1288,7 @@ static bool build_graph_conditional(b200_system* s)
             {
             CUDA_OK(cudaStreamBeginCaptureToGraph(s->stream, body[k], nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
             capturing = true;
-            enqueue_rebuild(s, enable, (k & 1u) ? s->pos_alt.p : s->pos.p);
+            enqueue_rebuild(s, enable, (!persist && (k & 1u)) ? s->pos_alt.p : s->pos.p);
             CUDA_OK(cudaStreamEndCapture(s->stream, &out));
             capturing = false;
             }
@@ -1289,6 +1340,7 @@ static void build_graph_plain(b200_system* s)
     CUDA_OK(cudaStreamEndCapture(s->stream, &s->graph));
     CUDA_OK(cudaGraphInstantiate(&s->graph_exec, s->graph, 0));
     s->graph_steps = 2;
+    s->graph_persist = false;
     s->graph_uses_cond = 0;
     s->graph_valid = true;
     }
@@ -1399,10 +1451,37 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
             enqueue_md_step(s, fa, 1, 0ull, 0);
             }
         }
+    else if (s->graph_persist)
+        {
+        // every unit advances a data-dependent number of steps (until the next rebuild): launch what the running estimate
+        // of the rebuild interval asks for plus head room (an idle unit costs three empty launches), look at steps_left, and
+        // top up in the rare case it was not enough
+        unsigned int todo = chunk;
+        double per_unit = std::max(1.0, 0.8 * s->persist_steps_per_unit);
+        s->persist_units_last_run = 0;
+        while (true)
+            {
+            const unsigned int units = (unsigned int)std::ceil(todo / per_unit) + 2u;
+            const unsigned int nl = (units + s->graph_steps - 1u) / s->graph_steps;
+            for (unsigned int k = 0; k < nl; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
+            s->persist_units_last_run += (unsigned long long)nl * s->graph_steps;
+            CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
+            CUDA_OK(cudaStreamSynchronize(s->stream));
+            if (st.steps_left == 0u || st.overflow || st.abort || st.nvt_error) break;
+            todo = st.steps_left;
+            per_unit = std::max(1.0, 0.5 * per_unit);
+            }
+        if (!st.overflow && !st.nvt_error)
+            {
+            const double seen = (double)chunk / (double)(st.num_updates + st.num_forced + 1u);
+            s->persist_steps_per_unit = 0.5 * s->persist_steps_per_unit + 0.5 * seen;
+            }
+        }
     else
         for (unsigned int k = 0; k < nlaunch; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
+    if (st.nvt_error == 3u) throw std::runtime_error("integrate: a CTA of the multi-step kernel never reached the grid barrier");
     if (st.nvt_error)
         throw std::runtime_error(st.nvt_error == 1u
                                      ? "integrate.nvt: kinetic energy is more than 2^20 times the set point (diverged?)"
@@ -1495,8 +1574,12 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
-    s->kernels_last_run += 2ull + ((s->graph_uses_cond && !direct) ? (2ull * nreplay + nlaunch + rk * rebuilds)
-                                                                             : (2ull + 2ull * rk) * nreplay);
+    if (s->graph_persist && !direct)
+        s->kernels_last_run += 2ull + s->persist_units_last_run + s->persist_units_last_run / s->graph_steps
+                               + rk * rebuilds; // k_md_steps per unit, k_graph_pre per graph launch
+    else
+        s->kernels_last_run += 2ull + ((s->graph_uses_cond && !direct) ? (2ull * nreplay + nlaunch + rk * rebuilds)
+                                                                                 : (2ull + 2ull * rk) * nreplay);
     s->timestep = st.timestep;
     s->last_updated_tstep = st.last_updated;
     s->num_updates += st.num_updates;
@@ -1551,6 +1634,7 @@ static void sys_alloc_common(b200_system* s)
     // Small systems are bound by the gaps between graph launches (6.9 us per step at 64k with two steps per launch): 16 steps
     // per launch, 28.8k -> 30.7k TPS (profiles/r2j_*).  Large systems gain nothing and keep the short graph.
     s->graph_unroll = s->N <= 150000u ? 16u : 2u;
+    if (const char* e = getenv("HOOMD_B200_PERSIST")) s->persist_mode = atoi(e) ? -1 : 0;
     if (const char* e = getenv("HOOMD_B200_GRAPH_UNROLL")) s->graph_unroll = (unsigned int)std::max(2, atoi(e));
     const unsigned int N = s->N, C = s->Ncap;
     s->vel.alloc(C); s->net_force.alloc(C); s->accel.alloc(C); s->image.alloc(C);
@@ -2376,6 +2460,25 @@ int b200_sys_get_pair_mode(b200_system* s, unsigned int* out8)
     return 0;
     }
 
+/* out4: {stepping mode (b200_sys_set_tuning's use_graph), MD steps per graph unit (0 = data dependent: multi-step kernel),
+ * 1 when the multi-step kernel k_md_steps drives the graph, graph units launched by the last run} */
+int b200_sys_get_stepping(b200_system* s, unsigned int* out4)
+    {
+    out4[0] = (unsigned int)s->use_graph;
+    out4[1] = (s->graph_valid && s->graph_persist) ? 0u : s->graph_steps;
+    out4[2] = (s->graph_valid && s->graph_persist) ? 1u : 0u;
+    out4[3] = (unsigned int)std::min<unsigned long long>(s->persist_units_last_run, 0xffffffffull);
+    return 0;
+    }
+
+/* multi-step launches (k_md_steps): -1 automatic (default), 0 off.  Takes effect at the next graph build. */
+int b200_sys_set_multistep(b200_system* s, int mode)
+    {
+    s->persist_mode = mode ? -1 : 0;
+    invalidate_graph(s);
+    return 0;
+    }
+
 int b200_sys_compute_nlist(b200_system* s, unsigned int ts)
     {
     SYS_TRY(s)
@@ -2408,9 +2511,8 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
     else
         prep_run(s, s->timestep);
     CUDA_OK(cudaStreamSynchronize(s->stream));
-    cudaEvent_t e0, e1;
-    CUDA_OK(cudaEventCreate(&e0));
-    CUDA_OK(cudaEventCreate(&e1));
+    EventPair ev;
+    const cudaEvent_t e0 = ev.e0, e1 = ev.e1;
     auto t0 = std::chrono::steady_clock::now();
     CUDA_OK(cudaEventRecord(e0, s->stream));
     unsigned int remaining = nsteps;
@@ -2437,8 +2539,6 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
     auto t1 = std::chrono::steady_clock::now();
     float ms = 0.0f;
     CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     if (elapsed_s) *elapsed_s = std::chrono::duration<double>(t1 - t0).count();
     if (gpu_ms) *gpu_ms = ms;
     SYS_CATCH(s)
@@ -2525,18 +2625,17 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
     if (!s->have_nlist) throw std::runtime_error("nlist: not set up");
     if (iters == 0) iters = 1;
     ensure_idx_tables(s);
-    cudaEvent_t e0, e1;
-    CUDA_OK(cudaEventCreate(&e0));
-    CUDA_OK(cudaEventCreate(&e1));
+    EventPair ev;
+    const cudaEvent_t e0 = ev.e0, e1 = ev.e1;
     b200_pair_args pa;
     pair_args(s, pa);
     b200_cell_list_args ca;
     cell_list_args(s, ca);
     b200_nlist_args na;
     nlist_args(s, na);
-    if (which == 2)
+    if (which == 2 || which == 5)
         {
-        // the single-kernel MD step itself: `iters` back-to-back launches (alternating ping-pong phase, no rebuild in
+        // the single-kernel MD step itself (5: `iters` steps inside ONE launch of the multi-step kernel k_md_steps): `iters` back-to-back launches (alternating ping-pong phase, no rebuild in
         // between, never the chunk's last step) on a scratch copy of the integrator state, which is restored afterwards
         if (!s->method) throw std::runtime_error("integrate: no integration method set");
         const unsigned int N = s->N;
@@ -2554,7 +2653,7 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         st.last_updated = s->timestep;
         st.every = 0x7fffffffu; // no rebuild decision can fire
         st.ntypes = s->ntypes;
-        st.steps_left = iters + 1;
+        st.steps_left = which == 5 ? iters : iters + 1; // the multi-step launch ends with the chunk's (cheaper) last step
         st.N = s->N;
         float nvt_saved[4] = {0.0f, 0.0f, 1.0f, 0.0f};
         if (s->method == 3)
@@ -2571,8 +2670,15 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         fa.gs.tab = nullptr; // scratch steps must not write into the neighbors' ghost regions nor take the step barrier
         if (fa.mg) fa.mg = 1;
         CUDA_OK(cudaStreamSynchronize(s->stream));
+        cudaError_t multi = cudaSuccess;
         CUDA_OK(cudaEventRecord(e0, s->stream));
-        for (unsigned int k = 0; k < iters; k++) enqueue_md_step(s, fa, (int)(k & 1), 0ull, 0);
+        if (which == 5)
+            multi = (s->pair_kind == B200_PAIR_LJ && !s->tile_on && s->bond_kind < 0)
+                        ? launch_md_steps_lj(pa, (const float*)s->d_params.p, fa, s->pos.p, s->pos_alt.p, s->d_state.p, 0, 0ull, 0,
+                                             s->stream)
+                        : cudaErrorNotSupported;
+        else
+            for (unsigned int k = 0; k < iters; k++) enqueue_md_step(s, fa, (int)(k & 1), 0ull, 0);
         CUDA_OK(cudaEventRecord(e1, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->pos.p, s->ck_pos.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
         CUDA_OK(cudaMemcpyAsync(s->vel.p, s->ck_vel.p, sizeof(float4) * N, cudaMemcpyDeviceToDevice, s->stream));
@@ -2582,8 +2688,8 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
         if (s->method == 3) CUDA_OK(cudaMemcpy(s->d_nvt.p, nvt_saved, sizeof(nvt_saved), cudaMemcpyHostToDevice));
         float ms2 = 0.0f;
         CUDA_OK(cudaEventElapsedTime(&ms2, e0, e1));
-        cudaEventDestroy(e0);
-        cudaEventDestroy(e1);
+        cudaGetLastError();
+        if (multi != cudaSuccess) throw std::runtime_error("time_kernel(5): the multi-step kernel does not apply to this system");
         *avg_ms = (double)ms2 / iters;
         return 0;
         }
@@ -2619,8 +2725,6 @@ int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* 
     CUDA_OK(cudaStreamSynchronize(s->stream));
     float ms = 0.0f;
     CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     *avg_ms = (double)ms / iters;
     SYS_CATCH(s)
     }

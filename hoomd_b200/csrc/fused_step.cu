@@ -8,6 +8,7 @@
 // Per-particle arithmetic is the shared body of integrate_body.cuh / pair_body.cuh => bit-identical to the driver kernels.
 #include "common.cuh"
 #include "md_step_kernel.cuh"
+#include "md_steps_persist.cuh"
 
 namespace b200
 {
@@ -115,6 +116,14 @@ cudaError_t launch_md_step_lj(const b200_pair_args& pa, const float* d_params, c
     {
     return launch_md_step_t<EvaluatorPairLJ, true>(pa, d_params, fa, pos_in, pos_out, copy_pos_on_last, st, cond_handle,
                                                    use_cond, stream);
+    }
+
+cudaError_t launch_md_steps_lj(const b200_pair_args& pa, const float* d_params, const FusedStepArgs& fa, const float4* pos_a,
+                               float4* pos_b, StepState* st, int probe_only, unsigned long long next_handle, int use_cond,
+                               cudaStream_t stream)
+    {
+    return launch_md_steps_t<EvaluatorPairLJ>(pa, d_params, fa, pos_a, pos_b, st, probe_only != 0, next_handle, use_cond,
+                                              stream);
     }
 
 // the same step with another pair evaluator (pair_ev.cu holds the instantiations)

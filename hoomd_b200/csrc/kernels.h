@@ -23,7 +23,7 @@ struct StepState
     unsigned int overflow;        // sticky: some n_neigh exceeded Nmax during a device-driven rebuild
     unsigned int ntypes;
     unsigned int steps_left;      // MD steps still to run in this chunk (k_md_step counts it down; 0 = launches are no-ops)
-    unsigned int _pad0;
+    unsigned int epoch;           // k_md_steps: grid-wide release word, +1 per MD step of a multi-step launch
     unsigned long long ticket;    // k_md_step: low word = CTAs finished, high word = CTAs that saw a mover (one atomic)
     unsigned int store_force;     // write net_force/virial every step (otherwise only in the last step of a chunk)
     unsigned int N;               // local particle count (multi-GPU: changes at every migration)
@@ -140,6 +140,12 @@ B200_DECL_EV(fslj)
 B200_DECL_EV(morse)
 B200_DECL_EV(dpd)
 #undef B200_DECL_EV
+// Several MD steps per launch (md_steps_persist.cuh): runs from buffer A until a rebuild is wanted or the chunk ends; the
+// current positions are back in A when it returns.  cudaErrorNotSupported: not a plain LJ configuration, or the grid is not
+// co-resident -- keep the one-step kernel.  probe_only: only answer that question.
+cudaError_t launch_md_steps_lj(const b200_pair_args& pa, const float* d_params, const FusedStepArgs& fa, const float4* pos_a,
+                               float4* pos_b, StepState* st, int probe_only, unsigned long long next_handle, int use_cond,
+                               cudaStream_t stream); // use_cond: arm the conditional node `next_handle` with the exit decision
 cudaError_t launch_md_step_kind(int evaluator, const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,
                                 const float4* pos_in, float4* pos_out, int copy_pos_on_last, StepState* st,
                                 unsigned long long cond_handle, int use_cond, cudaStream_t stream);

@@ -1,0 +1,263 @@
+// Several MD steps per launch for SMALL systems (the whole grid co-resident): k_md_steps runs the single-kernel MD step in a
+// loop until the neighbor list needs a rebuild or the chunk ends.  At 64k particles a step kernel runs 17 us and the gap
+// between two graph nodes (conditional IF evaluation + kernel launch) 4-7 us: the loop replaces that gap by a grid-wide
+// barrier built on the ticket the step already takes for its rebuild decision.
+//
+//   per step:   phase 1 (neighbor walk on buffer X) -> phase 2 (step two, step one into buffer Y, distance check)
+//               -> ticket; the LAST CTA takes NeighborList::needsUpdating for the next step (decide_body) and releases the
+//               epoch word; every CTA waits for it, re-reads the control block, swaps X and Y.
+//   exit:       rebuild wanted / chunk finished / abort.  The caller's rebuild bracket and the next launch always start from
+//               buffer A (a.pos_in): a launch that stops with the current positions in B copies its own particles back.
+//
+// Arithmetic per particle is that of k_md_step (same bodies, same order): trajectories are bit-identical to the one-step
+// kernel's.  Plain variants only: one particle type, no virial, LJ, NVE or Langevin without options, no second force, no
+// group, single GPU -- everything else keeps the one-step kernel.  The launch is cooperative (co-residency guaranteed by
+// the runtime); the epoch wait is bounded all the same, so a lost CTA turns into an error instead of a hung GPU.
+#pragma once
+#include "md_step_kernel.cuh"
+
+namespace b200
+{
+constexpr unsigned int PERSIST_STOP_DONE = 1u, PERSIST_STOP_REBUILD = 2u, PERSIST_STOP_ERROR = 4u;
+
+// control words are read at GPU scope (a plain volatile load is system scope)
+__device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p)
+    {
+    unsigned int v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+    }
+// release / acquire fence at GPU scope (the acquire side also drops this SM's L1 lines: the next step's neighbor gathers
+// must see the positions the other CTAs just stored)
+__device__ __forceinline__ void persist_fence() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// thread 0: the control words of the step about to run
+__device__ __forceinline__ void persist_read_ctl(StepState* st, unsigned int* s_ctl)
+    {
+    s_ctl[0] = ld_volatile_u32(&st->steps_left);
+    s_ctl[1] = ld_volatile_u32(&st->ts_step_two);
+    s_ctl[2] = (ld_volatile_u32(&st->store_force) ? 1u : 0u) | (ld_volatile_u32(&st->box_scaled) ? 2u : 0u);
+    s_ctl[3] = (ld_volatile_u32(&st->need_rebuild) ? PERSIST_STOP_REBUILD : 0u)
+               | ((ld_volatile_u32(&st->abort) || ld_volatile_u32(&st->nvt_error)) ? PERSIST_STOP_ERROR : 0u);
+    }
+
+// one MD step reading buffer X = (ODD ? a.pos_out : a.pos_in), writing the other.  Returns 0 to go on, else the stop reason.
+template<class Evaluator, int TPP, int SHIFT_MODE, bool ODD>
+__device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluator>& a, StepState* st,
+                                                        const PairTables<Evaluator>& T, float4* s_force,
+                                                        unsigned int* s_ctl, unsigned int& epoch)
+    {
+    constexpr int PPB = MD_BLOCK / TPP;
+    const float4* pin = ODD ? a.pos_out : a.pos_in;
+    float4* pout = ODD ? const_cast<float4*>(a.pos_in) : a.pos_out;
+    const unsigned int steps_left = s_ctl[0], ts2 = s_ctl[1];
+    const bool box_scaled = (s_ctl[2] & 2u) != 0u;
+    const bool last = steps_left == 1u;
+    const bool store_force = last || (s_ctl[2] & 1u);
+    const unsigned int N = a.N;
+
+    // ---- phase 1 (as in k_md_step) ----
+        {
+        const unsigned int slot = threadIdx.x / TPP;
+        const unsigned int i = blockIdx.x * PPB + slot;
+        const unsigned int sub = threadIdx.x % TPP;
+        const bool active = i < N;
+        const float4 pi4 = active ? pin[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const unsigned int size = active ? a.n_neigh[i] : 0u;
+        const unsigned int head = !active ? 0u : (a.nmax_uniform ? i * a.nmax_uniform : a.head_list[i]);
+        const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, false, false>(
+            pi4, size, head, sub, pin, a.box, a.nlist, T, a.ntypes, !active || box_interior(pi4, a.box, a.wrap_skip_margin));
+        if (sub == 0) s_force[slot] = make_float4(r.fx, r.fy, r.fz, r.pe);
+        }
+    __syncthreads();
+
+    // ---- phase 2: md_step_integrate for the plain case ----
+    bool moved = false;
+    const unsigned int i = blockIdx.x * PPB + threadIdx.x;
+    if (threadIdx.x < PPB && i < N)
+        {
+        const float4 F = s_force[threadIdx.x];
+        const float4 pi4 = pin[i];
+        float4 v = a.vel[i];
+        if (store_force) a.net_force[i] = F;
+        const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
+        const bool nve = a.method == 1;
+        float3s acc;
+        if (nve)
+            nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
+        else
+            langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
+        a.accel[i] = acc;
+        if (!last)
+            {
+            float4 p = pi4;
+            int3 img = a.image[i];
+            const float4 lp = a.last_pos[i];
+            nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
+            pout[i] = p;
+            a.image[i] = img;
+            const float* tab = a.maxsq + (box_scaled ? a.ntypes + 3u : 0u);
+            const float maxsq = tab[type_i];
+            float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(tab[a.ntypes], lp.x)),
+                                    __fsub_rn(p.y, __fmul_rn(tab[a.ntypes + 1u], lp.y)),
+                                    __fsub_rn(p.z, __fmul_rn(tab[a.ntypes + 2u], lp.z)));
+            dx = min_image_exact_sel(dx, a.box, a.box.periodic.x, a.box.periodic.y, a.box.periodic.z);
+            moved = dot_exact(dx) >= maxsq;
+            }
+        else if (ODD)
+            pout[i] = pi4; // the chunk's final positions must be in buffer A
+        a.vel[i] = v;
+        }
+
+    // ---- ticket + rebuild decision by the last CTA + grid-wide release ----
+    const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    if (threadIdx.x == 0)
+        {
+        // release: this CTA's position stores (ordered before by the barrier above) before its ticket.  A release ATOMIC, not a
+        // fence: the fence would also drop the SM's L1 lines under the CTAs that are still walking their neighbor rows
+        const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
+        unsigned long long old;
+        asm volatile("atom.release.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(&st->ticket), "l"(inc) : "memory");
+        if ((unsigned int)old == gridDim.x - 1u)
+            {
+            if ((old + inc) >> 32) st->moved = 1u;
+            st->ticket = 0ull;
+            st->steps_left = steps_left - 1u;
+            if (!last)
+                decide_body(st);
+            else
+                {
+                st->need_rebuild = 0u;
+                st->moved = 0u;
+                }
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&st->epoch), "r"(epoch + 1u) : "memory");
+            }
+        unsigned int spins = 0;
+        bool lost = false;
+        while (ld_volatile_u32(&st->epoch) != epoch + 1u)
+            {
+            if (++spins > (1u << 22)) // seconds: a CTA of this grid never arrived
+                {
+                lost = true;
+                break;
+                }
+            }
+        persist_fence(); // acquire: the other CTAs' position stores of this step are visible to this SM from here on
+        persist_read_ctl(st, s_ctl);
+        if (lost)
+            {
+            st->nvt_error = 3u;
+            s_ctl[3] |= PERSIST_STOP_ERROR;
+            }
+        }
+    epoch += 1u;
+    __syncthreads();
+    unsigned int stop = s_ctl[3];
+    if (s_ctl[0] == 0u) stop |= PERSIST_STOP_DONE;
+    if (last) stop |= PERSIST_STOP_DONE;
+    return stop;
+    }
+
+template<class Evaluator, int TPP, int SHIFT_MODE>
+__global__ void __launch_bounds__(MD_BLOCK, 1280 / MD_BLOCK) k_md_steps(const __grid_constant__ MdStepArgs<Evaluator> a)
+    {
+    constexpr int PPB = MD_BLOCK / TPP;
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ float4 s_force[PPB];
+    __shared__ unsigned int s_ctl[4];
+    __shared__ unsigned int s_epoch;
+    StepState* st = a.st;
+    if (threadIdx.x == 0)
+        {
+        persist_read_ctl(st, s_ctl);
+        s_epoch = ld_volatile_u32(&st->epoch);
+        }
+    __syncthreads();
+    // grid-uniform: the control block only changes after EVERY CTA has taken its first ticket
+    if (s_ctl[0] == 0u || (s_ctl[3] & PERSIST_STOP_ERROR)) return;
+    unsigned int epoch = s_epoch;
+    PairTables<Evaluator> T;
+    pair_tables_load<Evaluator, SHIFT_MODE, false>(T, smem_raw, a.params, a.rcutsq, a.ronsq, a.ntypes);
+    while (true)
+        {
+        const bool was_last = s_ctl[0] == 1u;
+        unsigned int stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, false>(a, st, T, s_force, s_ctl, epoch);
+        if (stop)
+            {
+            // stopped after an A -> B step that moved the particles: put this CTA's particles back into A (every CTA's reads of
+            // A for that step are behind the barrier)
+            const unsigned int i = blockIdx.x * PPB + threadIdx.x;
+            if (!was_last && threadIdx.x < PPB && i < a.N) const_cast<float4*>(a.pos_in)[i] = a.pos_out[i];
+            break;
+            }
+        stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, true>(a, st, T, s_force, s_ctl, epoch);
+        if (stop) break;
+        }
+#if (CUDART_VERSION >= 12040)
+    // arm the IF node of the graph unit behind this one (its rebuild bracket); s_ctl holds the control block as of the exit
+    if (a.use_cond && blockIdx.x == 0 && threadIdx.x == 0)
+        cudaGraphSetConditional(a.handle, (s_ctl[0] != 0u && s_ctl[3] == PERSIST_STOP_REBUILD) ? 1u : 0u);
+#endif
+    }
+
+// co-resident CTAs of k_md_steps on the current device (0: cooperative launch unavailable)
+template<class Evaluator, int TPP, int SHIFT_MODE> static unsigned int md_steps_max_ctas()
+    {
+    static int cached = -1;
+    if (cached < 0)
+        {
+        cached = 0;
+        int dev = 0, coop = 0, sms = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess
+            && cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop
+            && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess
+            && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_md_steps<Evaluator, TPP, SHIFT_MODE>, MD_BLOCK, 0)
+                   == cudaSuccess)
+            cached = sms * per_sm;
+        }
+    return (unsigned int)cached;
+    }
+
+template<class Evaluator, int TPP, int SHIFT_MODE>
+static cudaError_t md_steps_launch(const MdStepArgs<Evaluator>& a, bool probe_only, cudaStream_t stream)
+    {
+    const unsigned int per_block = MD_BLOCK / TPP;
+    const unsigned int grid = (a.N + per_block - 1) / per_block;
+    if (grid == 0 || grid > md_steps_max_ctas<Evaluator, TPP, SHIFT_MODE>()) return cudaErrorNotSupported;
+    if (probe_only) return cudaSuccess;
+    void* args[] = {(void*)&a};
+    return cudaLaunchCooperativeKernel((const void*)k_md_steps<Evaluator, TPP, SHIFT_MODE>, dim3(grid), dim3(MD_BLOCK), args, 0,
+                                       stream);
+    }
+
+// cudaErrorNotSupported: this system / configuration keeps the one-step kernel
+template<class Evaluator>
+static cudaError_t launch_md_steps_t(const b200_pair_args& pa, const void* d_params, const FusedStepArgs& fa,
+                                     const float4* pos_a, float4* pos_b, StepState* st, bool probe_only,
+                                     unsigned long long next_handle, int use_cond, cudaStream_t stream)
+    {
+    if (fa.N == 0 || !box_is_orthorhombic(pa.box)) return cudaErrorNotSupported;
+    const bool extras = fa.group_flag || fa.tally_acc || fa.use_lambda || fa.mg || fa.gs.tab || fa.gs.cta_order || fa.d_N;
+    if (extras || pa.ntypes != 1 || pa.compute_virial || pa.shift_mode == B200_SHIFT_XPLOR || fa.extra_force
+        || (fa.method != 1 && fa.method != 2))
+        return cudaErrorNotSupported;
+    MdStepArgs<Evaluator> a;
+    fill_md_step_args(a, pa, (const float*)d_params, fa, pos_a, pos_b, 0, st, next_handle, use_cond);
+    const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);
+    const bool shift = pa.shift_mode == B200_SHIFT_SHIFT;
+    switch (tpp)
+        {
+        case 2:
+            return shift ? md_steps_launch<Evaluator, 2, B200_SHIFT_SHIFT>(a, probe_only, stream)
+                         : md_steps_launch<Evaluator, 2, B200_SHIFT_NONE>(a, probe_only, stream);
+        case 4:
+            return shift ? md_steps_launch<Evaluator, 4, B200_SHIFT_SHIFT>(a, probe_only, stream)
+                         : md_steps_launch<Evaluator, 4, B200_SHIFT_NONE>(a, probe_only, stream);
+        case 8:
+            return shift ? md_steps_launch<Evaluator, 8, B200_SHIFT_SHIFT>(a, probe_only, stream)
+                         : md_steps_launch<Evaluator, 8, B200_SHIFT_NONE>(a, probe_only, stream);
+        default:
+            return cudaErrorNotSupported;
+        }
+    }
+} // namespace b200

@@ -259,6 +259,17 @@ class System:
         return dict(tile=bool(out[0]), cells_per_tile=(int(out[1]), int(out[2]), int(out[3])), cap=int(out[4]),
                     tpp=int(out[5]), row_capacity=int(out[6]), tiles=int(out[7]))
 
+    def stepping(self):
+        """how the last run stepped: use_graph mode, MD steps per graph unit (0 = data dependent), multi-step kernel on/off,
+        graph units launched by the last run"""
+        out = (C.c_uint * 4)()
+        _lib.lib().b200_sys_get_stepping(self.h, out)
+        return dict(use_graph=int(out[0]), steps_per_unit=int(out[1]), multistep=bool(out[2]), units_last_run=int(out[3]))
+
+    def set_multistep(self, on=True):
+        """several MD steps per launch (k_md_steps) where it applies (default on); off = the one-step kernel everywhere"""
+        self._check(_lib.lib().b200_sys_set_multistep(self.h, int(bool(on))))
+
     def set_timestep(self, ts):
         _lib.lib().b200_sys_set_timestep(self.h, int(ts))
 

@@ -553,9 +553,16 @@ B200_API int b200_sys_get_nlist(b200_system* s, unsigned int* n_neigh, unsigned 
 /* out: {num updates (distance-check triggered), forced updates, nlist overflows, kernels launched in the last run,
  *       dim.x, dim.y, dim.z, Nmax[0]} */
 B200_API int b200_sys_get_stats(b200_system* s, unsigned long long* out8);
+/* How the last run stepped.  out4 = {stepping mode (set_tuning's use_graph), MD steps per graph unit (0: data dependent),
+ * 1 when the multi-step kernel k_md_steps (several MD steps per launch, until the next list rebuild; plain LJ systems whose
+ * whole grid is co-resident) drives the graph, graph units launched by the last run}.
+ * b200_sys_set_multistep(0) keeps the one-step kernel everywhere (A/B, debugging); nonzero = automatic (default). */
+B200_API int b200_sys_get_stepping(b200_system* s, unsigned int* out4);
+B200_API int b200_sys_set_multistep(b200_system* s, int mode);
 /* Micro-benchmarks in the spirit of Compute::benchmark (hoomd/ForceCompute.cc:153-180, hoomd/md/NeighborList.cc:260-289):
  * launches kernel `which` (0 = pair force on the current list, 1 = cell list + neighbor list build, 3 / 4 = its cell-list /
- * neighbor-list half alone, 2 = the single-kernel MD step on a scratch copy of the integrator state) `iters` times on the system's stream between two CUDA events and
+ * neighbor-list half alone, 2 = the single-kernel MD step on a scratch copy of the integrator state, 5 = the same `iters` steps
+ * inside ONE launch of the multi-step kernel: per-step time incl. its grid-wide barrier; error when it does not apply) `iters` times on the system's stream between two CUDA events and
  * returns the average milliseconds per launch.  State is not advanced. */
 B200_API int b200_sys_time_kernel(b200_system* s, int which, unsigned int iters, double* avg_ms);
 /* ComputeThermo at the current step: out = {KE, PE, temperature, pressure, ndof} */

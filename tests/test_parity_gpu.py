@@ -458,3 +458,37 @@ def test_full_size_ka256k_properties(hb):
     # the sc start at rho 1.2 is far from equilibrium: the melt heats up before the thermostat (gamma 1) pulls it back
     assert 0.5 < th["T"] < 8.0 and np.isfinite(th["pe"]), th
     assert g.stats()["updates"] > 0
+
+
+@pytest.mark.parametrize("n_side,method", [(24, "nve"), (30, "langevin"), (38, "nve")])
+def test_multistep_kernel_bit_identical_to_one_step_kernel(hb, n_side, method):
+    """k_md_steps (several MD steps per launch, grid-wide barrier instead of a kernel boundary; 8 / 4 / 2 lanes per particle
+    at these sizes) against the one-step kernel in the same conditional graph: identical bits after 260 steps with list
+    rebuilds, a particle sort and two run() calls, equal rebuild counts; the switch and the stepping query work."""
+    pos, vel, L = hb.workloads.sc_lattice(n_side, (1.0 / 0.2) ** (1.0 / 3.0), kT=1.2, seed=21)
+    pos[:, :3] += np.random.default_rng(3).normal(0, 0.1, (len(pos), 3)).astype(np.float32)
+    out = []
+    for multi in (True, False):
+        s = hb.System(pos, (L, L, L), vel4=vel)
+        s.setup_lj(r_cut=3.0, r_buff=0.4)
+        s.setup_integrator(0.005)
+        if method == "nve":
+            s.add_nve()
+        else:
+            s.add_langevin(1.2, 5)
+        s.set_sorter(100)
+        s.set_multistep(multi)
+        s.run(130)
+        s.run(130)
+        st = s.stepping()
+        assert st["multistep"] == multi and st["use_graph"] == 2, st
+        assert (st["steps_per_unit"] == 0) == multi
+        p = s.particles()
+        out.append((p, s.stats(), s.forces(False)[0]))
+        s.close()
+    (pa, sa, fa), (pb, sb, fb) = out
+    for k in ("pos", "vel", "image", "tag", "accel"):
+        assert np.array_equal(pa[k].view(np.uint32), pb[k].view(np.uint32)), k
+    assert np.array_equal(fa.view(np.uint32), fb.view(np.uint32))
+    assert (sa["updates"], sa["forced"]) == (sb["updates"], sb["forced"]) and sa["updates"] >= 5
+    assert sa["kernels_last_run"] < sb["kernels_last_run"]    # fewer launches is the point
