@@ -41,6 +41,7 @@ class _Context:
         self.integration_methods = []
         self.sorter = update.sort() if "update" in globals() else None
         self.loggers = []
+        self.dumpers = []
         self.box_resizers = []
         self.engine = None
         self.engine_dirty = True
@@ -258,9 +259,45 @@ def _create_lattice(unitcell, n):
     return _read_snapshot(snap)
 
 
+def _gsd_snapshot(filename, frame=0):
+    """hoomd.data.gsd_snapshot (hoomd/data.py, GSDReader): one frame of a GSD file as a snapshot"""
+    from . import gsd_io
+    fr = gsd_io.read_hoomd_frame(filename, frame)
+    b = fr["box"]
+    if b[3] != 0.0 or b[4] != 0.0 or b[5] != 0.0:
+        raise RuntimeError("hoomd_b200: triclinic boxes are not supported (tilt factors in " + filename + ")")
+    snap = _Snapshot(fr["N"], _BoxDim(float(b[0]), float(b[1]), float(b[2]), dimensions=fr["dimensions"]), fr["types"],
+                     fr["bond_types"])
+    q = snap.particles
+    q.position[:], q.velocity[:], q.image[:] = fr["position"], fr["velocity"], fr["image"]
+    q.typeid[:], q.mass[:], q.diameter[:] = fr["typeid"], fr["mass"], fr["diameter"]
+    snap.bonds.resize(fr["bonds_N"])
+    if fr["bonds_N"]:
+        snap.bonds.group[:], snap.bonds.typeid[:] = fr["bonds_group"], fr["bonds_typeid"]
+    snap._gsd_step = fr["step"]
+    return snap
+
+
+def _read_gsd(filename, restart=None, frame=0, time_step=None):
+    """hoomd.init.read_gsd (hoomd/init.py:256-313): initialise from `filename`, or from `restart` (its frame 0) when that
+    file exists; the time step comes from the file unless given"""
+    import os
+    _require_context()
+    if context.current.system is not None:
+        raise RuntimeError("Cannot initialize more than once")
+    reading = filename
+    if restart is not None and os.path.exists(restart):
+        reading, frame = restart, 0
+    snap = _gsd_snapshot(reading, frame)
+    context.current.timestep = int(snap._gsd_step if time_step is None else time_step)
+    return _read_snapshot(snap)
+
+
+data.gsd_snapshot = _gsd_snapshot
 init = types.ModuleType("hoomd.init")
 init.read_snapshot = _read_snapshot
 init.create_lattice = _create_lattice
+init.read_gsd = _read_gsd
 
 # ---- hoomd.group ---------------------------------------------------------------------------------------------------------
 group = types.ModuleType("hoomd.group")
@@ -964,6 +1001,75 @@ class _Log(_Scheduled):
 
 analyze.log = _Log
 
+# ---- hoomd.dump.gsd ----------------------------------------------------------------------------------------------------------
+dump = types.ModuleType("hoomd.dump")
+
+
+class _GSD(_Scheduled):
+    """hoomd.dump.gsd (hoomd/dump.py:501-660, GSDDumpWriter): trajectory / restart frames of the HOOMD GSD schema written from
+    the device-resident state (one download per frame).  period=None writes one frame now; truncate=True keeps rewriting
+    frame 0 (restart files); `dynamic` / `static` select the chunk categories written after frame 0."""
+
+    def __init__(self, filename, period, group, overwrite=False, truncate=False, phase=0, time_step=None, static=None,
+                 dynamic=None):
+        from . import gsd_io
+        _require_context()
+        if static is not None and dynamic is not None:
+            raise ValueError("Cannot specify both static and dynamic arguments")
+        if group is None or not isinstance(group, _Group):
+            raise RuntimeError("dump.gsd: a hoomd.group is required")
+        dyn = ["property"]
+        if static is not None:
+            dyn = [c for c in gsd_io.CATEGORIES if c not in static]
+        if dynamic is not None:
+            dyn = ["property"] + list(dynamic)
+        self.filename, self.group, self.period, self.phase = filename, group, period, int(phase)
+        self._writer_args = dict(overwrite=bool(overwrite), truncate=bool(truncate), dynamic=tuple(dyn))
+        self._writer = None
+        self.enabled = True
+        ctx = context.current
+        if period is not None:
+            if int(period) < 1:
+                raise RuntimeError("dump.gsd: period must be a positive integer")
+            self._schedule(int(period), int(phase))  # System::addAnalyzer
+            ctx.dumpers.append(self)
+        else:
+            self._analyze(ctx.timestep if time_step is None else int(time_step))
+
+    def _analyze(self, ts):
+        from . import gsd_io
+        ctx = context.current
+        if self._writer is None:  # GSDDumpWriter::initFileIO on the first frame
+            self._writer = gsd_io.HoomdGSDWriter(self.filename, application="HOOMD-blue 2.3.0 (hoomd_b200)",
+                                                 **self._writer_args)
+        snap = ctx.system.take_snapshot()
+        q = snap.particles
+        tags = np.arange(q.N) if self.group.is_all() else np.asarray(self.group.tags, np.int64)
+        frame = dict(position=q.position[tags], velocity=q.velocity[tags], image=q.image[tags], typeid=q.typeid[tags],
+                     mass=q.mass[tags], diameter=q.diameter[tags], types=list(q.types))
+        if self.group.is_all():  # topology is only meaningful for the all group (GSDDumpWriter.cc:245)
+            frame.update(bonds_group=snap.bonds.group, bonds_typeid=snap.bonds.typeid, bond_types=list(snap.bonds.types))
+        box = ctx.system.box
+        self._writer.write_frame(ts, (box.Lx, box.Ly, box.Lz, 0.0, 0.0, 0.0), frame, dimensions=box.dimensions)
+
+    def write_restart(self):
+        """one frame at the current time step (restart files with truncate=True at the end of a job)"""
+        self._analyze(context.current.timestep if context.current.engine is None else context.current.engine.timestep)
+
+    def set_period(self, period):
+        self._schedule(int(period), self.phase)
+
+    def disable(self):
+        self.enabled = False
+
+    def enable(self):
+        if not self.enabled and self.period is not None:
+            self._schedule(self.period, self.phase)
+        self.enabled = True
+
+
+dump.gsd = _GSD
+
 
 # ---- hoomd.run ------------------------------------------------------------------------------------------------------------
 def _configure_engine():
@@ -1087,6 +1193,9 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
                 eng = ctx.engine
                 lg.rows.append([ts] + [lg.query(q) for q in lg.quantities])
                 lg._write(lg.rows[-1])
+        for dp in ctx.dumpers:
+            if dp.enabled and dp.should_execute(ts):
+                dp._analyze(ts)
         for br in ctx.box_resizers:
             if br.enabled and br.should_execute(ts):
                 br._apply(ts)
@@ -1100,7 +1209,7 @@ def run(tsteps, profile=False, limit_hours=None, limit_multiple=1, callback_peri
             nxt = 1
         if cb_period > 0:
             nxt = min(nxt, cb_period - ts % cb_period)
-        for item in list(ctx.loggers) + list(ctx.box_resizers):
+        for item in list(ctx.loggers) + list(ctx.dumpers) + list(ctx.box_resizers):
             if item.enabled:
                 n = item.steps_until(ts)
                 if n is not None:
@@ -1128,7 +1237,7 @@ def install():
     me = sys.modules[__name__]
     sys.modules["hoomd"] = me
     for name, mod in (("context", context), ("init", init), ("lattice", lattice), ("data", data), ("group", group),
-                      ("update", update), ("variant", variant), ("md", md), ("analyze", analyze)):
+                      ("update", update), ("variant", variant), ("md", md), ("analyze", analyze), ("dump", dump)):
         sys.modules["hoomd." + name] = mod
     for name, mod in (("nlist", md.nlist), ("pair", md.pair), ("integrate", md.integrate), ("bond", md.bond)):
         sys.modules["hoomd.md." + name] = mod

@@ -488,3 +488,92 @@ def test_first_logged_row_sees_real_forces_and_per_force_energies():
         <= 1e-4 * abs(th["pe"])
     with pytest.raises(RuntimeError):
         log.query("pair_gauss_energy")  # no such force
+
+
+def test_gsd_surface_without_gpu(tmp_path):
+    """dump.gsd(period=None) writes the initial configuration without an engine; init.read_gsd / data.gsd_snapshot read it back,
+    restart= takes precedence when that file exists, the time step comes from the file"""
+    from hoomd_b200 import gsd_io
+    hoomd = _fresh()
+    sysd = hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=2.0, type_name="A"), n=4)
+    snap = sysd.take_snapshot()
+    snap.particles.velocity[:] = np.random.default_rng(1).normal(0, 1, (64, 3))
+    snap.particles.mass[:] = 2.0
+    sysd.restore_snapshot(snap)
+    init_file, restart_file = str(tmp_path / "init.gsd"), str(tmp_path / "restart.gsd")
+    with pytest.raises(ValueError):
+        hoomd.dump.gsd(init_file, period=None, group=hoomd.group.all(), static=["attribute"], dynamic=["momentum"])
+    hoomd.dump.gsd(init_file, period=None, group=hoomd.group.all(), overwrite=True, time_step=77)
+    fr = gsd_io.read_hoomd_frame(init_file)
+    assert fr["step"] == 77 and fr["N"] == 64 and np.allclose(fr["box"][:3], 8.0) and (fr["mass"] == 2.0).all()
+    assert np.array_equal(fr["velocity"], snap.particles.velocity)
+    s2 = hoomd.data.gsd_snapshot(init_file)
+    assert np.array_equal(s2.particles.position, snap.particles.position) and s2.box.Lx == 8.0
+    # a sub-group: N of the file is the group size, no topology
+    hoomd.dump.gsd(str(tmp_path / "grp.gsd"), period=None, group=hoomd.group.tags(10, 19), overwrite=True)
+    g = gsd_io.read_hoomd_frame(str(tmp_path / "grp.gsd"))
+    assert g["N"] == 10 and np.array_equal(g["position"], snap.particles.position[10:20])
+    # read_gsd: restart file wins when present
+    hoomd = _fresh()
+    hoomd.init.read_gsd(init_file, restart=restart_file)
+    assert hoomd.context.current.timestep == 77 and hoomd.get_step() == 77
+    hoomd = _fresh()
+    w = gsd_io.HoomdGSDWriter(restart_file, overwrite=True, truncate=True)
+    w.write_frame(500, (9, 9, 9), dict(position=np.zeros((5, 3), np.float32)))
+    w.close()
+    sysd = hoomd.init.read_gsd(init_file, restart=restart_file)
+    assert hoomd.context.current.timestep == 500 and len(sysd.particles) == 5 and sysd.box.Lx == 9.0
+    hoomd = _fresh()
+    hoomd.init.read_gsd(init_file, time_step=3)
+    assert hoomd.context.current.timestep == 3
+
+
+@pytest.mark.gpu
+def test_gsd_trajectory_and_restart(tmp_path):
+    """dump.gsd as an analyzer on the device-resident state: frames at the scheduled steps, and a job restarted from its
+    truncate=True restart file continues the trajectory (NVE: a(t) = F(t)/m is recomputed from the restored positions, as the
+    reference does for a file without accelerations)."""
+    from hoomd_b200 import gsd_io
+    traj, restart = str(tmp_path / "traj.gsd"), str(tmp_path / "restart.gsd")
+
+    def setup(hoomd):
+        nl = hoomd.md.nlist.cell()
+        lj = hoomd.md.pair.lj(r_cut=2.5, nlist=nl)
+        lj.pair_coeff.set("A", "A", epsilon=1.0, sigma=1.0)
+        hoomd.md.integrate.mode_standard(dt=0.005)
+        hoomd.md.integrate.nve(group=hoomd.group.all())
+
+    hoomd = _fresh()
+    hoomd.init.create_lattice(unitcell=hoomd.lattice.sc(a=1.5, type_name="A"), n=8)
+    snap = hoomd.context.current.system.take_snapshot()
+    snap.particles.velocity[:] = np.random.default_rng(2).normal(0, 1.0, (512, 3))
+    hoomd.context.current.system.restore_snapshot(snap)
+    setup(hoomd)
+    hoomd.dump.gsd(traj, period=40, group=hoomd.group.all(), overwrite=True, dynamic=["momentum"])
+    rs = hoomd.dump.gsd(restart, period=100, group=hoomd.group.all(), overwrite=True, truncate=True, phase=0)
+    hoomd.run(100)
+    rs.write_restart()                       # frame at step 100
+    mid = hoomd.context.current.system.take_snapshot()
+    hoomd.run(60)
+    end = hoomd.context.current.system.take_snapshot()
+    with gsd_io.GSDFile(traj) as f:
+        assert f.nframes == 4                # steps 0, 40, 80, 120 (160 is the first step of the NEXT run)
+        assert [int(f.read_chunk(k, "configuration/step")[0, 0]) for k in range(4)] == [0, 40, 80, 120]
+        assert f.find_chunk(2, "particles/velocity") is not None and f.find_chunk(2, "particles/mass") is None
+    fr = gsd_io.read_hoomd_frame(restart)
+    assert fr["step"] == 100
+    assert np.array_equal(fr["position"], mid.particles.position) and np.array_equal(fr["image"], mid.particles.image)
+
+    # second job: restart from the file
+    hoomd = _fresh()
+    hoomd.init.read_gsd(traj, restart=restart)
+    assert hoomd.get_step() == 100
+    setup(hoomd)
+    hoomd.run(60)
+    again = hoomd.context.current.system.take_snapshot()
+    assert hoomd.get_step() == 160
+    # same state to FP32 round-off growth: the restarted job holds its particles in tag order until the next sort, so the
+    # neighbor rows (and with them the order of the force sums) differ from the uninterrupted job's
+    assert np.abs(again.particles.position - end.particles.position).max() < 2e-5
+    assert np.abs(again.particles.velocity - end.particles.velocity).max() < 2e-4
+    assert np.array_equal(again.particles.image, end.particles.image)
