@@ -631,9 +631,11 @@ static void nlist_update_rlist(b200_system* s)
 static void nlist_build_head_list(b200_system* s)
     {
     if (s->tile_on) return; // ELL rows: no head list
+    // domain decomposition keeps Nmax equal for all types (nlist_check_conditions): the head list is i * Nmax whatever the
+    // types of the slots are -- and the unused capacity slots hold no valid type to look up
     CUDA_OK(b200_nlist_build_head_list(s->head_list.p, s->d_req_size.p, s->d_Nmax.p, (const float*)s->pos.p,
                                        s->mg ? s->Ncap : s->N,
-                                       s->ntypes, s->stream));
+                                       s->mg ? 1u : s->ntypes, s->stream));
     s->kernels_last_run += (s->ntypes == 1) ? 1 : 3;
     unsigned int size = 0;
     s->d_req_size.download(&size, 1, s->stream);
@@ -662,6 +664,14 @@ static bool nlist_check_conditions(b200_system* s)
             }
     if (result)
         {
+        if (s->mg)
+            {
+            // Domain decomposition: ONE row capacity for every type.  Local slots change their type at every migration (on the
+            // device), and with equal Nmax the head list i * Nmax does not depend on the types, so it never has to be rebuilt
+            // inside the rebuild bracket.  (Rows are a little longer than the reference's per-type Nmax; contents are the same.)
+            const unsigned int m = *std::max_element(s->h_Nmax.begin(), s->h_Nmax.end());
+            std::fill(s->h_Nmax.begin(), s->h_Nmax.end(), m);
+            }
         s->d_Nmax.upload(s->h_Nmax.data(), s->ntypes, s->stream);
         CUDA_OK(cudaStreamSynchronize(s->stream));
         invalidate_graph(s); // Nmax[0] is a by-value argument of the captured step kernels (FusedStepArgs::nmax_uniform)

@@ -279,7 +279,6 @@ static void mg_download_state(b200_system* s)
 static void mg_prep_run(b200_system* s, unsigned int ts)
     {
     if (!s->mg_connected) throw std::runtime_error("comm: peers not attached (b200_sys_mg_connect)");
-    if (s->ntypes != 1) throw std::runtime_error("comm: one particle type supported under domain decomposition");
     if (s->force_update || s->nl_first_compute)
         {
         nlist_build_head_list(s);

@@ -76,14 +76,14 @@ class DomainSystem(System):
     deterministically on each rank) and keeps the particles it owns; tags are the global particle indices."""
 
     def __init__(self, pos4, box, r_ghost, vel4=None, image=None, grid=None, rank=None, world=None, device=None,
-                 ncap=0, capacity_factor=0.0, connect=True):
+                 ncap=0, capacity_factor=0.0, connect=True, ntypes=1):
         import torch.distributed as dist
         L = _lib.lib()
         self.world = dist.get_world_size() if world is None else int(world)
         self.rank = dist.get_rank() if rank is None else int(rank)
         pos4 = np.ascontiguousarray(pos4, np.float32)
         self.N_global = int(pos4.shape[0])
-        self.ntypes = 1
+        self.ntypes = int(ntypes)
         self.grid = tuple(grid) if grid is not None else find_decomposition(box, self.world)
         self.global_L = tuple(float(v) for v in box)
         owner = place_particles(pos4[:, :3], box, self.grid)
@@ -94,7 +94,7 @@ class DomainSystem(System):
         p.grid = (C.c_uint * 3)(*self.grid)
         p.global_box = _lib.make_box(*self.global_L)
         p.N_global, p.N_local, p.Ncap = self.N_global, self.N, int(ncap)
-        p.r_ghost, p.capacity_factor, p.ntypes = float(r_ghost), float(capacity_factor), 1
+        p.r_ghost, p.capacity_factor, p.ntypes = float(r_ghost), float(capacity_factor), int(ntypes)
         p.device = int(self.rank if device is None else device)
         self.h = C.c_void_p(L.b200_sys_create_mg(C.byref(p)))
         self._check(0)

@@ -45,9 +45,12 @@ def expected_ghost_tags(pos, L, lo, hi, per, r_ghost):
     return np.sort(np.concatenate(out))
 
 
-def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, check_ghosts=True, verbose=True):
+def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, check_ghosts=True, verbose=True, ntypes=1,
+                lj=None, method="nve"):
     """One domain-decomposed system against RefSystem on the same snapshot (every rank calls this; torch.distributed must be
-    initialised).  Returns a dict of measured maxima; raises AssertionError on a parity failure."""
+    initialised).  Returns a dict of measured maxima; raises AssertionError on a parity failure.  ntypes / lj: a mixture with
+    per-pair coefficients (type ids in pos[:, 3]); method "langevin": the noise is keyed by global tag, so the decomposed
+    trajectory follows the single-domain reference as well."""
     import torch.distributed as dist
     import golden_util as G
     from hoomd_b200 import domain
@@ -59,8 +62,11 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
     if not R.available():
         raise RuntimeError("oracle/_ref/libhoomd_ref.so is missing: the multi-GPU parity pass needs the reference classes")
 
-    mg = domain.DomainSystem(pos, box, r_ghost=r_cut + r_buff, vel4=vel, image=image, device=local_rank)
-    mg.setup_lj(r_cut=r_cut, r_buff=r_buff)
+    lj = dict(lj or {})
+    r_cut_max = float(np.max(lj.get("r_cut", r_cut)))
+    lj.setdefault("r_cut", r_cut)
+    mg = domain.DomainSystem(pos, box, r_ghost=r_cut_max + r_buff, vel4=vel, image=image, device=local_rank, ntypes=ntypes)
+    mg.setup_lj(r_buff=r_buff, **lj)
     mg.compute_forces(0)
     counts = [None] * world
     dist.all_gather_object(counts, mg._sync_n())
@@ -69,19 +75,19 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
     if check_ghosts:
         lo, hi, per = domain.local_bounds(box, mg.grid, rank)
         gpos, gtag = mg.ghosts()
-        exp = expected_ghost_tags(pos, box, lo, hi, per, np.float32(r_cut + r_buff))
+        exp = expected_ghost_tags(pos, box, lo, hi, per, np.float32(r_cut_max + r_buff))
         assert np.array_equal(np.sort(gtag), exp), (len(gtag), len(exp))
         d = gpos[:, :3] - pos[gtag, :3]
         d -= np.round(d / np.float32(L)) * np.float32(L)
         assert np.abs(d).max() < 1e-5
 
     # ---- the reference's answer (CPU classes, full list) and the scales of the 1e-5 bar, on every rank's host cores ----
-    r = R.RefSystem(pos, box, vel4=vel, image=image)
-    r.setup_lj(r_cut=r_cut, r_buff=r_buff, full=True)
+    r = R.RefSystem(pos, box, ntypes=ntypes, vel4=vel, image=image)
+    r.setup_lj(r_buff=r_buff, full=True, **lj)
     r.compute_forces(0)
     f_ref = r.forces(False)[0]
     rn = r.nlist()[0]
-    sc = G.abs_scales(lambda o: o.setup_lj(r_cut=r_cut, r_buff=r_buff), pos, box)
+    sc = G.abs_scales(lambda o: o.setup_lj(r_buff=r_buff, **lj), pos, box, ntypes=ntypes)
 
     p = mg.particles()
     tag = p["tag"]
@@ -96,7 +102,10 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
     if steps:
         for s in (r, mg):
             s.setup_integrator(0.005)
-            s.add_nve()
+            if method == "langevin":
+                s.add_langevin(1.0, 11, gamma=[1.0, 0.5][:ntypes] if ntypes <= 2 else [1.0] * ntypes)
+            else:
+                s.add_nve()
             s.set_sorter(100)
         r.run(steps)
         mg.run(steps)
@@ -139,17 +148,27 @@ def main():
 
     n_side = int(sys.argv[1]) if len(sys.argv) > 1 else 24
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+    ntypes = int(sys.argv[3]) if len(sys.argv) > 3 else 1     # 2: Kob-Andersen-like mixture under Langevin
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     rho, kT = 0.2, 1.2
-    pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
+    kw = {}
+    if ntypes == 2:
+        rho = 0.6
+        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11, ntypes=2,
+                                           type_fractions=[0.8, 0.2])
+        kw = dict(ntypes=2, method="langevin", r_cut=2.5,
+                  lj=dict(r_cut=[[2.5, 2.0], [2.0, 2.2]], epsilon=[[1.0, 1.5], [1.5, 0.5]], sigma=[[1.0, 0.8], [0.8, 0.88]],
+                          shift_mode=1))
+    else:
+        pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
     rng = np.random.default_rng(5)
-    pos[:, :3] += rng.normal(0, 0.12, (len(pos), 3)).astype(np.float32)
+    pos[:, :3] += rng.normal(0, 0.12 if ntypes == 1 else 0.05, (len(pos), 3)).astype(np.float32)
     pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
-    res = parity_pass(pos, vel, None, L, steps, local_rank)
+    res = parity_pass(pos, vel, None, L, steps, local_rank, **kw)
     assert res["mg_stats"]["max_migrants"] > 0 or steps < 100, "no particle ever migrated: migration was not exercised"
     dist.barrier()
     if rank == 0:
