@@ -33,7 +33,7 @@ class CellListArgs(C.Structure):
                 ("d_conditions", vp), ("d_cell_count", vp), ("d_particle_cell", vp), ("d_particle_slot", vp),
                 ("d_scratch_idx", vp), ("d_pos", vp), ("d_charge", vp), ("N", C.c_uint), ("n_ghost", C.c_uint),
                 ("flag_charge", C.c_int), ("flag_type", C.c_int), ("box", Box), ("dim", Dim3),
-                ("ghost_width", C.c_float * 3), ("d_ghost_dir", vp), ("d_ghost_shift", vp)]
+                ("ghost_width", C.c_float * 3), ("d_ghost_dir", vp), ("d_ghost_shift", vp), ("d_fused_barrier", vp)]
 
 
 class NlistArgs(C.Structure):

@@ -290,16 +290,44 @@ __global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyz
 constexpr unsigned int CF_BLOCK = 512;
 constexpr unsigned int CF_MAX_CELLS = 4 * SCAN_TILE;
 
+// Grid-wide barrier of a cooperative launch on two caller-owned words {arrivals, epoch} (b200_cell_list_args.d_fused_barrier):
+// release atomic on arrival, the last CTA resets the count and publishes the next epoch, the others spin on it at GPU scope,
+// one acquire fence per CTA (the same construction carries k_md_steps, md_steps_persist.cuh).
+__device__ __forceinline__ void cf_grid_barrier(unsigned int* bar)
+    {
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+        unsigned int epoch, old;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(epoch) : "l"(bar + 1) : "memory");
+        asm volatile("atom.release.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(bar) : "memory");
+        if (old == gridDim.x - 1u)
+            {
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(bar), "r"(0u) : "memory");
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(bar + 1), "r"(epoch + 1u) : "memory");
+            }
+        else
+            {
+            unsigned int now, spins = 0;
+            do
+                {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(now) : "l"(bar + 1) : "memory");
+                } while (now == epoch && ++spins < (1u << 22)); // bounded: a lost CTA must not hang the GPU
+            }
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        }
+    __syncthreads();
+    }
+
 __global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
     unsigned int* __restrict__ cell_count, unsigned int* __restrict__ cell_start, unsigned int* __restrict__ particle_cell,
     unsigned int* __restrict__ particle_slot, unsigned int* __restrict__ scratch_idx, float4* __restrict__ cell_xyzf,
     unsigned int* __restrict__ cell_type, unsigned int* __restrict__ cell_idx, unsigned int* __restrict__ conditions,
     const float4* __restrict__ pos, const float* __restrict__ charge, unsigned int N, unsigned int n_ghost, Box box,
     uint3 dim, float3 ghost_width, int flag_charge, int flag_type, const unsigned int* __restrict__ enable,
-    const unsigned int* __restrict__ d_N)
+    const unsigned int* __restrict__ d_N, unsigned int* barrier)
     {
-    if (enable && !*enable) return; // uniform over the grid: nobody reaches a grid.sync
-    cg::grid_group grid = cg::this_grid();
+    if (enable && !*enable) return; // uniform over the grid: nobody reaches a barrier
     const unsigned int ntot = N + n_ghost;
     const unsigned int ncells = dim.x * dim.y * dim.z;
     const unsigned int stride = gridDim.x * blockDim.x;
@@ -331,7 +359,7 @@ __global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
         particle_cell[n] = cell;
         particle_slot[n] = slot;
         }
-    grid.sync();
+    cf_grid_barrier(barrier);
     // phase 2: exclusive scan of the occupancies by CTA 0 (k_cell_scan; 8 cells per thread and tile), self-cleaning counts
     if (blockIdx.x == 0)
         {
@@ -391,7 +419,7 @@ __global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
         for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
         if (lane == 0 && max_occ) atomicMax(&conditions[0], max_occ);
         }
-    grid.sync();
+    cf_grid_barrier(barrier);
     // phase 3: scatter (k_cell_scatter).  cell_start was written by another CTA in this launch: no read-only path
     for (unsigned int n = tid; n < ntot; n += stride)
         {
@@ -399,7 +427,7 @@ __global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
         if (cell == B200_NOT_BINNED) continue;
         scratch_idx[__ldcg(cell_start + cell) + particle_slot[n]] = n;
         }
-    grid.sync();
+    cf_grid_barrier(barrier);
     // phase 4: in-cell rank by particle index, final arrays (k_cell_rank)
     const unsigned int nbinned = __ldcg(cell_start + ncells);
     for (unsigned int e = tid; e < nbinned; e += stride)
@@ -571,9 +599,10 @@ static unsigned int cell_fused_max_ctas()
     if (cached < 0)
         {
         cached = 0;
-        // measured SLOWER than the 4-kernel build inside the conditional graph body (LJ 64k: 31.5k vs 32.9k timesteps/s,
-        // Kob-Andersen 262k: 5.83k vs 6.19k; profiles/r1p_*): the cooperative launch and three grid-wide barriers cost more
-        // than the three launch gaps they remove.  Kept behind HOOMD_B200_CELL_FUSED=1 for A/B runs.
+        // Measured SLOWER than the 4-kernel build inside the conditional graph body, with cooperative_groups' grid.sync() (LJ
+        // 64k: 31.5k vs 32.9k timesteps/s, profiles/r1p_*) and with the microsecond barrier above as well (34.1k vs 35.4k, cell
+        // list 27.6 vs 24.9 us, profiles/r2q_*): the four phases are chains of dependent atomics / loads of 64k threads, not
+        // launch gaps, and one CTA per 512 particles leaves SMs idle.  Kept behind HOOMD_B200_CELL_FUSED=1 for A/B runs.
         const char* env = getenv("HOOMD_B200_CELL_FUSED");
         int dev = 0, coop = 0, sms = 0, per_sm = 0;
         if (env && atoi(env) != 0 && cudaGetDevice(&dev) == cudaSuccess
@@ -585,16 +614,16 @@ static unsigned int cell_fused_max_ctas()
     return (unsigned int)cached;
     }
 
-static bool cell_use_fused(unsigned int ncells, unsigned int ntot)
+static bool cell_use_fused(unsigned int ncells, unsigned int ntot, bool have_barrier)
     {
     // launch-bound sizes only: beyond a few hundred thousand particles the kernels dwarf the launch gaps
-    return ntot > 0 && ncells <= CF_MAX_CELLS && ntot <= 262144u && cell_fused_max_ctas() > 0;
+    return have_barrier && ntot > 0 && ncells <= CF_MAX_CELLS && ntot <= 262144u && cell_fused_max_ctas() > 0;
     }
 
 // launches per cell-list build: the multi-CTA scan (one launch more) pays off beyond a few tiles
-unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot)
+unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot, bool have_barrier)
     {
-    if (cell_use_fused(ncells, ntot)) return 1u;
+    if (cell_use_fused(ncells, ntot, have_barrier)) return 1u;
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     return (ntiles > 4 && ntiles <= ntot) ? 5u : 4u;
     }
@@ -611,7 +640,8 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
     if (!enable) cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
-    if (cell_use_fused(ncells, ntot) && !a->d_ghost_dir) // (the opt-in cooperative build bins ghosts where they are)
+    const bool fused = cell_use_fused(ncells, ntot, a->d_fused_barrier != nullptr) && !a->d_ghost_dir; // (bins ghosts where they are)
+    if (fused)
         {
         unsigned int grid = (ntot + CF_BLOCK - 1) / CF_BLOCK;
         if (grid > cell_fused_max_ctas()) grid = cell_fused_max_ctas();
@@ -622,7 +652,7 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
         void* args[] = {(void*)&a->d_cell_count, (void*)&a->d_cell_start, (void*)&a->d_particle_cell,
                         (void*)&a->d_particle_slot, (void*)&a->d_scratch_idx, &xyzf, (void*)&a->d_cell_type,
                         (void*)&a->d_cell_idx, (void*)&a->d_conditions, &pos, (void*)&a->d_charge, &N, &n_ghost, &box,
-                        &dim, &gw, &flag_charge, &flag_type, &enable, &d_N};
+                        &dim, &gw, &flag_charge, &flag_type, &enable, &d_N, (void*)&a->d_fused_barrier};
         return cudaLaunchCooperativeKernel((const void*)k_cell_list_fused, dim3(grid), dim3(CF_BLOCK), args, 0, stream);
         }
     if (ntot)
@@ -632,7 +662,7 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     // device-driven rebuild: the dependent kernels are scheduled behind their predecessor (see launch_chain)
     const bool pdl = enable && pdl_enabled();
-    if (cell_list_kernels(ncells, ntot) == 5)
+    if (cell_list_kernels(ncells, ntot, false) == 5)
         {
         // tile totals live in d_scratch_idx, which is not needed before k_cell_scatter
         launch_chain(k_cell_scan_tiles, dim3(ntiles), dim3(1024), 0, stream, pdl, a->d_cell_start, a->d_cell_count, ncells,

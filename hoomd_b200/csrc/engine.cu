@@ -328,6 +328,7 @@ static void cell_list_args(b200_system* s, b200_cell_list_args& a)
     a.d_cell_idx = s->tile_on ? s->tile_perm.p : nullptr;
     a.flag_type = s->tile_on ? 1 : 0; // tile path: cell_xyzf is the cell-sorted copy of pos (type in w)
     a.d_conditions = s->cl_conditions.p;
+    a.d_fused_barrier = s->mg ? nullptr : s->cl_conditions.p + 4; // (ghost shifts under decomposition: four-launch build)
     a.d_cell_count = s->cell_count.p;
     a.d_particle_cell = s->particle_cell.p;
     a.d_particle_slot = s->particle_slot.p;
@@ -569,7 +570,7 @@ static void cell_list_compute(b200_system* s, unsigned int ts)
     b200_cell_list_args a;
     cell_list_args(s, a);
     CUDA_OK(launch_cell_list(&a, nullptr, s->stream));
-    s->kernels_last_run += cell_list_kernels(a.dim.x * a.dim.y * a.dim.z, a.N + a.n_ghost);
+    s->kernels_last_run += cell_list_kernels(a.dim.x * a.dim.y * a.dim.z, a.N + a.n_ghost, a.d_fused_barrier != nullptr);
     cell_list_check_conditions(s);
     }
 
@@ -1580,8 +1581,8 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
     const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
     if (rebuilds)
         for (int d = 0; d < 3; d++) s->last_L[d] = s->box.L[d]; // setLastUpdatedPos of the device-side builds
-    const unsigned long long cl_extra = cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->N) - 4u;
-    const unsigned long long rk = (s->tile_on ? 8ull : 5ull) + cl_extra
+    const long long cl_extra = (long long)cell_list_kernels(s->dim.x * s->dim.y * s->dim.z, s->N, true) - 4;
+    const unsigned long long rk = (unsigned long long)((s->tile_on ? 8ll : 5ll) + cl_extra)
                                   + ((s->exclusions_set && s->ex_max) ? 1ull : 0ull); // kernels per rebuild
     if (s->bond_kind >= 0) s->kernels_last_run += 2ull * nreplay;
     if (s->graph_persist && !direct)
@@ -1662,7 +1663,7 @@ static void sys_alloc_common(b200_system* s)
     s->d_flag.alloc(4);
     s->d_state.alloc(1);
     s->d_req_size.alloc(1);
-    s->cl_conditions.alloc(3);
+    s->cl_conditions.alloc(8); // {max occupancy, NaN, out of box} + pad + the two barrier words of the one-launch build
     CUDA_OK(cudaHostAlloc((void**)&s->h_flag, 4 * sizeof(unsigned int), cudaHostAllocDefault));
     CUDA_OK(cudaHostAlloc((void**)&s->h_state, sizeof(StepState), cudaHostAllocDefault));
     s->th_partial.alloc(9 * 1024);

@@ -37,7 +37,8 @@ struct StepState
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,
                              const unsigned int* d_N = nullptr);
-unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot); // launches of one launch_cell_list
+// launches of one launch_cell_list (have_barrier: the caller passes b200_cell_list_args.d_fused_barrier and no ghost shifts)
+unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot, bool have_barrier = false);
 // Device-driven stepping: the build kernel itself raises StepState::overflow when a row exceeds Nmax (what the host's
 // checkConditions does after the fact, hoomd/md/NeighborList.cc:1389-1405) and, on a single GPU, zeroes steps_left so the
 // rest of the chunk turns into no-ops and `conditions` keeps exactly the counts of the overflowing rebuild.

@@ -100,6 +100,11 @@ typedef struct b200_cell_list_args
      * entry keeps the raw position.  Both NULL: ghosts are binned where they are (the reference's pre-wrapped ghosts). */
     const unsigned char* d_ghost_dir;   /* [n_ghost] or NULL */
     const float*         d_ghost_shift; /* [3 * 27] or NULL */
+    /* NULL, or two words {0, 0} owned by the caller (zeroed ONCE, then left alone): with HOOMD_B200_CELL_FUSED=1 small systems
+     * (<= 262,144 entries) are built by ONE cooperative launch -- bin, scan, scatter, rank separated by a grid-wide barrier on
+     * these words -- instead of four launches; same result bit for bit, measured slower, so opt-in.
+     * Builds that may overlap on the device must not share the words. */
+    unsigned int*        d_fused_barrier;
     } b200_cell_list_args;
 
 B200_API int b200_compute_cell_list(const b200_cell_list_args* args, b200_stream_t stream);
