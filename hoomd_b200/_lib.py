@@ -51,6 +51,11 @@ class PairArgs(C.Structure):
                 ("threads_per_particle", C.c_uint), ("block_size", C.c_uint), ("wrap_skip_margin", C.c_float)]
 
 
+class DpdThermoArgs(C.Structure):
+    _fields_ = [("d_vel", vp), ("d_tag", vp), ("seed", C.c_uint), ("timestep", C.c_uint), ("T", C.c_float),
+                ("deltaT", C.c_float)]
+
+
 class ForceList(C.Structure):
     _fields_ = [("f", vp * 6), ("v", vp * 6), ("vpitch", C.c_uint * 6)]
 
@@ -97,6 +102,7 @@ SYMBOLS = [
     "b200_sys_set_dist_check", "b200_sys_set_langevin_options", "b200_sys_set_diameters",
     "b200_sys_get_langevin_reservoir_energy", "b200_sys_set_group", "b200_sys_set_temperature", "b200_sys_set_box", "b200_sys_get_box", "b200_box_resize_particles",
     "b200_sys_add_nvt", "b200_sys_get_nvt_state", "b200_sys_set_nvt_state", "b200_nvt_mtk_step_one", "b200_nvt_mtk_step_two", "b200_nvt_mtk_advance",
+    "b200_compute_dpd_thermo_forces", "b200_sys_set_dpd_thermostat",
     "b200_sys_add_npt", "b200_sys_get_npt_state", "b200_sys_set_npt_state", "b200_sys_get_pressure_tensor",
     "b200_npt_mtk_step_one", "b200_npt_mtk_wrap", "b200_npt_mtk_step_two", "b200_npt_mtk_rescale", "b200_compute_thermo_tensor",
     "b200_sys_sort_now", "b200_sys_set_timestep", "b200_sys_get_timestep", "b200_sys_set_tuning",
@@ -109,7 +115,8 @@ SYMBOLS = [
 ]
 
 # enum B200_PAIR_* (hoomd/md/AllPairPotentials.h)
-PAIR_KINDS = {"lj": 0, "gauss": 1, "yukawa": 2, "mie": 3, "force_shifted_lj": 4, "morse": 5, "dpd_conservative": 6}
+# "dpd": the same evaluator slot with gamma in the second parameter; the engine's thermostat switch uses it
+PAIR_KINDS = {"lj": 0, "gauss": 1, "yukawa": 2, "mie": 3, "force_shifted_lj": 4, "morse": 5, "dpd_conservative": 6, "dpd": 6}
 
 
 def pair_params(kind, nt, **c):
@@ -135,6 +142,8 @@ def pair_params(kind, nt, **c):
         p[..., 0], p[..., 1], p[..., 2] = bc(c["D0"]), bc(c["alpha"]), bc(c["r0"])
     elif kind == "dpd_conservative":  # (A, gamma = 0), hoomd/md/pair.py:1513-1516
         p[..., 0] = bc(c["A"])
+    elif kind == "dpd":               # (A, gamma), hoomd/md/pair.py:1384-1388
+        p[..., 0], p[..., 1] = bc(c["A"]), bc(c["gamma"])
     else:
         raise ValueError("unknown pair potential " + str(kind))
     return np.ascontiguousarray(p.astype(np.float32))
@@ -222,6 +231,8 @@ def lib():
     L.b200_nvt_mtk_step_one.argtypes = [vp, vp, vp, vp, vp, C.c_uint, C.POINTER(Box), vp, C.c_float, vp]
     L.b200_nvt_mtk_step_two.argtypes = [vp, vp, vp, C.c_uint, vp, vp, C.c_float, vp]
     L.b200_nvt_mtk_advance.argtypes = [vp, vp, C.c_uint, vp, vp, C.c_uint, C.c_uint, C.c_float, C.c_float, C.c_float, vp]
+    L.b200_compute_dpd_thermo_forces.argtypes = [C.POINTER(PairArgs), vp, C.POINTER(DpdThermoArgs), vp]
+    L.b200_sys_set_dpd_thermostat.argtypes = [vp, C.c_float, C.c_uint]
     L.b200_sys_add_npt.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_uint, C.c_int, C.c_int,
                                    C.c_float]
     L.b200_sys_get_npt_state.argtypes = [vp, vp]

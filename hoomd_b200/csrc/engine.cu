@@ -223,6 +223,11 @@ struct b200_system
         } npt;
     DevBuf<double> npt_partial, npt_out;
 
+    // md.pair.dpd: the DPD pair force as a thermostat (b200_sys_set_dpd_thermostat); steps are host-driven then
+    bool dpd_thermo = false;
+    float dpd_kT = 0.0f;
+    unsigned int dpd_seed = 0;
+
     // ParticleGroup of the integration method (hoomd/ParticleGroup.h): 1 byte per TAG; empty = group.all().  group_idx is
     // ParticleGroup::getIndexArray (sorted member indices), rebuilt after every particle sort, for the stand-alone drivers.
     DevBuf<unsigned char> group_flag;
@@ -806,6 +811,18 @@ static void compute_net_force(b200_system* s, unsigned int ts)
         tile_step_args(s, ta, 1);
         CUDA_OK(launch_md_step_tile_lj(a, (const float*)s->d_params.p, fa, ta, s->pos.p, nullptr, 0, s->d_state.p, 0ull, 0,
                                        s->stream));
+        }
+    else if (s->dpd_thermo)
+        {
+        b200_dpd_thermo_args t;
+        t.d_vel = (const float*)s->vel.p;
+        t.d_tag = s->tag.p;
+        t.seed = s->dpd_seed;
+        t.timestep = ts;
+        t.T = s->dpd_kT;
+        t.deltaT = s->dt;
+        a.threads_per_particle = 0; // the kernel's own default
+        CUDA_OK(b200_compute_dpd_thermo_forces(&a, (const float*)pair_params_ptr(s), &t, s->stream));
         }
     else
         CUDA_OK(b200_compute_pair_forces(s->pair_kind, &a, pair_params_ptr(s), s->stream));
@@ -2337,6 +2354,23 @@ int b200_sys_get_nvt_state(b200_system* s, float* xi_eta)
     SYS_CATCH(s)
     }
 
+int b200_sys_set_dpd_thermostat(b200_system* s, float kT, unsigned int seed)
+    {
+    SYS_TRY(s)
+    if (kT > 0.0f)
+        {
+        if (!s->have_nlist || s->pair_kind != B200_PAIR_DPD)
+            throw std::runtime_error("pair.dpd: set up the DPD pair force first (b200_sys_setup_pair with B200_PAIR_DPD)");
+        if (s->mg) throw std::runtime_error("pair.dpd: not available under domain decomposition yet");
+        if (s->tile_on) throw std::runtime_error("pair.dpd: not available on the cell-tile path");
+        }
+    s->dpd_thermo = kT > 0.0f;
+    s->dpd_kT = kT;
+    s->dpd_seed = b200_langevin_hash_seed(seed); // PotentialPairDPDThermo::setSeed hashes the user seed the same way
+    invalidate_graph(s);
+    SYS_CATCH(s)
+    }
+
 // md.integrate.npt(group, kT, tau, P, tauP, couple, x, y, z, nph, rescale_all, gamma) (hoomd/md/integrate.py:406-506)
 int b200_sys_add_npt(b200_system* s, float kT, float tau, float P, float tauP, int couple, unsigned int flags, int nph,
                      int rescale_all, float gamma)
@@ -2539,7 +2573,7 @@ int b200_sys_run(b200_system* s, unsigned int nsteps, double* elapsed_s, double*
         if (s->sorter_period && s->sorter_next > s->timestep) chunk = std::min(chunk, s->sorter_next - s->timestep);
         if (s->mg)
             mg_run_chunk(s, chunk);
-        else if (s->use_graph && s->method != 4)
+        else if (s->use_graph && s->method != 4 && !s->dpd_thermo)
             run_chunk_device(s, chunk);
         else
             for (unsigned int k = 0; k < chunk; k++) host_step(s);

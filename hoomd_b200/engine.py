@@ -212,6 +212,11 @@ class System:
         self._check(_lib.lib().b200_sys_get_nvt_state(self.h, _p(out)))
         return out
 
+    def set_dpd_thermostat(self, kT, seed):
+        """md.pair.dpd(kT, seed): the DPD pair force set up with setup_pair("dpd_conservative", A=..., gamma=...) becomes the
+        pairwise thermostat (drag + random forces per pair); kT <= 0 switches back to the conservative force"""
+        self._check(_lib.lib().b200_sys_set_dpd_thermostat(self.h, C.c_float(kT), C.c_uint(seed)))
+
     COUPLE = {"none": 0, "xy": 1, "xz": 2, "yz": 3, "xyz": 4}
 
     def add_npt(self, kT, tau, P, tauP, couple="xyz", x=True, y=True, z=True, nph=False, rescale_all=False, gamma=0.0):

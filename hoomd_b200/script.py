@@ -695,6 +695,35 @@ class _DPDConservative(_Pair):
 md.pair.dpd_conservative = _DPDConservative
 
 
+class _DPD(_Pair):
+    """md.pair.dpd (hoomd/md/pair.py:1282-1438): conservative force + pairwise drag and random forces -- the DPD thermostat,
+    to be used with md.integrate.nve.  kT must be a constant here (a variant would be evaluated per step by the caller)."""
+    kind, required_coeffs = "dpd", ["A", "gamma"]
+
+    def __init__(self, r_cut, nlist, kT, seed, name=None):
+        super().__init__(r_cut, nlist, name)
+        self.seed = int(seed)
+        self.kT_variant = _setup_variant_input(kT)
+        if not isinstance(self.kT_variant, _VariantConst):
+            raise RuntimeError("hoomd_b200: pair.dpd takes a constant kT")
+
+    def set_params(self, kT=None, mode=None):
+        if mode is not None:
+            raise RuntimeError("pair.dpd has no energy shift modes")
+        if kT is not None:
+            self.kT_variant = _setup_variant_input(kT)
+            if not isinstance(self.kT_variant, _VariantConst):
+                raise RuntimeError("hoomd_b200: pair.dpd takes a constant kT")
+            context.current.engine_dirty = True
+
+    @property
+    def kT(self):
+        return float(np.float32(self.kT_variant.getValue(context.current.timestep)))
+
+
+md.pair.dpd = _DPD
+
+
 class _BondCoeff:
     """bond.coeff (hoomd/md/bond.py:22-164): per-bond-type table"""
 
@@ -1110,6 +1139,8 @@ def _configure_engine():
         eng.setup_pair(lj.kind, r_cut=t["r_cut"], r_buff=lj.nlist.r_buff, check_period=lj.nlist.check_period,
                        shift_mode=lj.shift_mode, r_on=t["r_on"] if lj.shift_mode == 2 else None,
                        **{k: t[k] for k in lj.required_coeffs})
+    if isinstance(lj, _DPD):
+        eng.set_dpd_thermostat(lj.kT, lj.seed)
     bonds = [f for f in ctx.forces if isinstance(f, _Bond) and f.enabled]
     if len(sysd.bond_group):
         eng.set_bonds(sysd.bond_group, sysd.bond_typeid, n_bond_types=len(sysd.bond_types))

@@ -230,6 +230,25 @@ enum { B200_PAIR_LJ = 0, B200_PAIR_GAUSS = 1, B200_PAIR_YUKAWA = 2, B200_PAIR_MI
 B200_API int b200_compute_pair_forces(int evaluator, const b200_pair_args* args, const void* d_params,
                                       b200_stream_t stream);
 
+/* PotentialPairDPDThermoDPD -- md.pair.dpd, the pairwise DPD thermostat -- replaces gpu_compute_dpdthermodpd_forces
+ * (hoomd/md/AllDriverPotentialPairGPU.cuh, dpd_pair_args_t of hoomd/md/PotentialPairDPDThermoGPU.cuh; CPU loop
+ * hoomd/md/PotentialPairDPDThermo.h:116-270, evaluator hoomd/md/EvaluatorPairDPDThermo.h:161-230).  Same operands as the pair
+ * force plus what dpd_pair_args_t adds: neighbor velocities and tags, the user seed, the time step, kT and deltaT.  d_params =
+ * Scalar2 (A, gamma) per type pair.  The random number of a pair comes from Saru(min tag, max tag, seed + timestep), so both
+ * rows of a full neighbor list get the same draw; energy and virial are those of the conservative part.  No energy shift. */
+typedef struct b200_dpd_thermo_args
+    {
+    const float*        d_vel;      /* Scalar4[N + n_ghost] */
+    const unsigned int* d_tag;      /* [N + n_ghost] */
+    unsigned int        seed;       /* m_seed: the user seed AFTER PotentialPairDPDThermo::setSeed's hash
+                                       (PotentialPairDPDThermo.h:93-105; same hash as b200_langevin_hash_seed) */
+    unsigned int        timestep;
+    float               T;          /* m_T->getValue(timestep) */
+    float               deltaT;
+    } b200_dpd_thermo_args;
+B200_API int b200_compute_dpd_thermo_forces(const b200_pair_args* args, const float* d_params,
+                                            const b200_dpd_thermo_args* thermo, b200_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * NeighborList exclusions  -- replaces gpu_nlist_filter (hoomd/md/NeighborListGPU.cu:140-240); semantics of
  * NeighborList::filterNlist (hoomd/md/NeighborList.cc:1275-1328): every row is rewritten in place without its excluded
@@ -512,6 +531,11 @@ B200_API int b200_sys_set_nvt_state(b200_system* s, const float* xi_eta);
  * propagator stay on the host as in the reference; the steps are host-driven (b200_npt_mtk_* + b200_compute_thermo_tensor).
  * get_npt_state: out12 = IntegratorVariables {eta, xi, nuxx, nuxy, nuxz, nuyy, nuyz, nuzz, xi_rot, eta_rot} and the log
  * quantities {npt_thermostat_energy, npt_barostat_energy}; get_pressure_tensor: {xx, xy, xz, yy, yz, zz, P, KE}. */
+/* md.pair.dpd(r_cut, nlist, kT, seed): turns the conservative DPD pair force set up with b200_sys_setup_pair(B200_PAIR_DPD, ...)
+ * into the DPD THERMOSTAT (drag + random pair forces; integrate with md.integrate.nve).  The force depends on the
+ * half-step velocities of both particles, so steps are host-driven (step one -> force -> step two as separate launches).
+ * kT <= 0 switches back to the conservative force. */
+B200_API int b200_sys_set_dpd_thermostat(b200_system* s, float kT, unsigned int seed);
 B200_API int b200_sys_add_npt(b200_system* s, float kT, float tau, float P, float tauP, int couple, unsigned int flags,
                               int nph, int rescale_all, float gamma);
 B200_API int b200_sys_get_npt_state(b200_system* s, float* out12);

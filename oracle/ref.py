@@ -41,6 +41,7 @@ def lib():
                                      C.c_int, C.c_float]
         _lib.ref_get_npt_state.argtypes = [C.c_void_p, C.c_void_p]
         _lib.ref_get_pressure_tensor.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+        _lib.ref_set_dpd_thermostat.argtypes = [C.c_void_p, C.c_float, C.c_uint]
         _lib.ref_set_dist_check.argtypes = [C.c_void_p, C.c_int]
         _lib.ref_set_kT.argtypes = [C.c_void_p, C.c_float]
         _lib.ref_set_box.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int]
@@ -164,6 +165,16 @@ class RefSystem:
         ron = None if r_on is None else np.ascontiguousarray(bc(r_on).astype(np.float32))
         self._check(lib().ref_setup_pair(self.h, B.PAIR_KINDS[kind], C.c_float(r_buff), int(check_period), int(full),
                                          _ptr(rc), _ptr(prm), _ptr(ron), int(shift_mode)))
+
+    def setup_dpd_thermostat(self, r_cut, A, gamma, kT, seed, r_buff=0.4, check_period=1, full=True):
+        """md.pair.dpd(r_cut, nlist, kT, seed) + pair_coeff.set(A=, gamma=): PotentialPairDPDThermoDPD"""
+        from hoomd_b200 import _lib as B
+        nt = self.ntypes
+        bc = lambda x: np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), (nt, nt)))
+        prm = B.pair_params("dpd", nt, A=A, gamma=gamma)
+        rc = np.ascontiguousarray(bc(r_cut).astype(np.float32))
+        self._check(lib().ref_setup_pair(self.h, 7, C.c_float(r_buff), int(check_period), int(full), _ptr(rc), _ptr(prm), None, 0))
+        self._check(lib().ref_set_dpd_thermostat(self.h, C.c_float(kT), C.c_uint(seed)))
 
     def set_virial(self, on=True):
         lib().ref_set_virial(self.h, int(on))

@@ -298,8 +298,23 @@ int ref_setup_pair(void* h, int evaluator, float r_buff, int check_period, int f
         case 4: s->lj = make_pair<PotentialPairForceShiftedLJ>(s, rcut, params4, ron, shift_mode); break;
         case 5: s->lj = make_pair<PotentialPairMorse>(s, rcut, params4, ron, shift_mode); break;
         case 6: s->lj = make_pair<PotentialPairDPD>(s, rcut, params4, ron, shift_mode); break;
+        case 7: s->lj = make_pair<PotentialPairDPDThermoDPD>(s, rcut, params4, ron, shift_mode); break; // md.pair.dpd
         default: throw std::runtime_error("unknown pair evaluator");
         }
+    REF_CATCH(s, 1)
+    return 0;
+    }
+
+//! md.pair.dpd(kT, seed): temperature and seed of the DPD thermostat created by ref_setup_pair(evaluator = 7)
+//! (PotentialPairDPDThermo::setT / setSeed, hoomd/md/PotentialPairDPDThermo.h:60-70)
+int ref_set_dpd_thermostat(void* h, float kT, unsigned int seed)
+    {
+    RefSystem* s = static_cast<RefSystem*>(h);
+    REF_TRY(s)
+    std::shared_ptr<PotentialPairDPDThermoDPD> f = std::dynamic_pointer_cast<PotentialPairDPDThermoDPD>(s->lj);
+    if (!f) throw std::runtime_error("ref_set_dpd_thermostat: the pair force is not PotentialPairDPDThermoDPD");
+    f->setSeed(seed);
+    f->setT(std::shared_ptr<Variant>(new VariantConst(kT)));
     REF_CATCH(s, 1)
     return 0;
     }
