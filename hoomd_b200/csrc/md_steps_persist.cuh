@@ -55,13 +55,15 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
     const bool last = steps_left == 1u;
     const bool store_force = last || (s_ctl[2] & 1u);
     const unsigned int N = a.N;
+    // particles per CTA: PPB unless the launcher chose a larger, SM-count-aligned grid (HOOMD_B200_PERSIST_EVEN)
+    const unsigned int ppb = (N + gridDim.x - 1u) / gridDim.x;
 
     // ---- phase 1 (as in k_md_step) ----
         {
         const unsigned int slot = threadIdx.x / TPP;
-        const unsigned int i = blockIdx.x * PPB + slot;
+        const unsigned int i = blockIdx.x * ppb + slot;
         const unsigned int sub = threadIdx.x % TPP;
-        const bool active = i < N;
+        const bool active = slot < ppb && i < N;
         const float4 pi4 = active ? pin[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         const unsigned int size = active ? a.n_neigh[i] : 0u;
         const unsigned int head = !active ? 0u : (a.nmax_uniform ? i * a.nmax_uniform : a.head_list[i]);
@@ -73,8 +75,8 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
 
     // ---- phase 2: md_step_integrate for the plain case ----
     bool moved = false;
-    const unsigned int i = blockIdx.x * PPB + threadIdx.x;
-    if (threadIdx.x < PPB && i < N)
+    const unsigned int i = blockIdx.x * ppb + threadIdx.x;
+    if (threadIdx.x < ppb && i < N)
         {
         const float4 F = s_force[threadIdx.x];
         const float4 pi4 = pin[i];
@@ -186,8 +188,9 @@ __global__ void __launch_bounds__(MD_BLOCK, 1280 / MD_BLOCK) k_md_steps(const __
             {
             // stopped after an A -> B step that moved the particles: put this CTA's particles back into A (every CTA's reads of
             // A for that step are behind the barrier)
-            const unsigned int i = blockIdx.x * PPB + threadIdx.x;
-            if (!was_last && threadIdx.x < PPB && i < a.N) const_cast<float4*>(a.pos_in)[i] = a.pos_out[i];
+            const unsigned int ppb = (a.N + gridDim.x - 1u) / gridDim.x;
+            const unsigned int i = blockIdx.x * ppb + threadIdx.x;
+            if (!was_last && threadIdx.x < ppb && i < a.N) const_cast<float4*>(a.pos_in)[i] = a.pos_out[i];
             break;
             }
         stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, true>(a, st, T, s_force, s_ctl, epoch);
@@ -218,12 +221,33 @@ template<class Evaluator, int TPP, int SHIFT_MODE> static unsigned int md_steps_
     return (unsigned int)cached;
     }
 
+static unsigned int md_steps_sm_count()
+    {
+    static int sms = -1;
+    if (sms < 0)
+        {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess
+            || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            sms = 1;
+        }
+    return (unsigned int)sms;
+    }
+
 template<class Evaluator, int TPP, int SHIFT_MODE>
 static cudaError_t md_steps_launch(const MdStepArgs<Evaluator>& a, bool probe_only, cudaStream_t stream)
     {
     const unsigned int per_block = MD_BLOCK / TPP;
-    const unsigned int grid = (a.N + per_block - 1) / per_block;
-    if (grid == 0 || grid > md_steps_max_ctas<Evaluator, TPP, SHIFT_MODE>()) return cudaErrorNotSupported;
+    unsigned int grid = (a.N + per_block - 1) / per_block;
+    const unsigned int max_ctas = md_steps_max_ctas<Evaluator, TPP, SHIFT_MODE>();
+    if (grid == 0 || grid > max_ctas) return cudaErrorNotSupported;
+    // HOOMD_B200_PERSIST_EVEN=1: a grid that is a multiple of the SM count, the particles spread evenly over it (62 instead of
+    // 64 per CTA at 64k, 7 CTAs on every SM instead of 7 on some and 6 on others).  Measured no better: 35.2k vs 35.5k TPS,
+    // 17.25 vs 17.0 us per step (profiles/r2r_*) -- the ragged CTAs cost what the balance gains.  Off by default.
+    const unsigned int sms = md_steps_sm_count();
+    const unsigned int even = (grid + sms - 1u) / sms * sms;
+    static const bool spread = getenv("HOOMD_B200_PERSIST_EVEN") && atoi(getenv("HOOMD_B200_PERSIST_EVEN")) != 0;
+    if (spread && even <= max_ctas) grid = even;
     if (probe_only) return cudaSuccess;
     void* args[] = {(void*)&a};
     return cudaLaunchCooperativeKernel((const void*)k_md_steps<Evaluator, TPP, SHIFT_MODE>, dim3(grid), dim3(MD_BLOCK), args, 0,
