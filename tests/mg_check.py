@@ -46,11 +46,12 @@ def expected_ghost_tags(pos, L, lo, hi, per, r_ghost):
 
 
 def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, check_ghosts=True, verbose=True, ntypes=1,
-                lj=None, method="nve"):
+                lj=None, method="nve", pair=None):
     """One domain-decomposed system against RefSystem on the same snapshot (every rank calls this; torch.distributed must be
     initialised).  Returns a dict of measured maxima; raises AssertionError on a parity failure.  ntypes / lj: a mixture with
     per-pair coefficients (type ids in pos[:, 3]); method "langevin": the noise is keyed by global tag, so the decomposed
-    trajectory follows the single-domain reference as well."""
+    trajectory follows the single-domain reference as well.  pair = (kind, coefficients): another pair evaluator
+    (md.pair.gauss / yukawa / mie / force_shifted_lj / morse) through setup_pair on all three sides."""
     import torch.distributed as dist
     import golden_util as G
     from hoomd_b200 import domain
@@ -66,7 +67,13 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
     r_cut_max = float(np.max(lj.get("r_cut", r_cut)))
     lj.setdefault("r_cut", r_cut)
     mg = domain.DomainSystem(pos, box, r_ghost=r_cut_max + r_buff, vel4=vel, image=image, device=local_rank, ntypes=ntypes)
-    mg.setup_lj(r_buff=r_buff, **lj)
+    def configure(sys_, **extra):
+        if pair is not None:
+            sys_.setup_pair(pair[0], r_cut=lj["r_cut"], r_buff=r_buff, **pair[1], **extra)
+        else:
+            sys_.setup_lj(r_buff=r_buff, **lj, **extra)
+
+    configure(mg)
     mg.compute_forces(0)
     counts = [None] * world
     dist.all_gather_object(counts, mg._sync_n())
@@ -83,11 +90,11 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
 
     # ---- the reference's answer (CPU classes, full list) and the scales of the 1e-5 bar, on every rank's host cores ----
     r = R.RefSystem(pos, box, ntypes=ntypes, vel4=vel, image=image)
-    r.setup_lj(r_buff=r_buff, full=True, **lj)
+    configure(r, full=True)
     r.compute_forces(0)
     f_ref = r.forces(False)[0]
     rn = r.nlist()[0]
-    sc = G.abs_scales(lambda o: o.setup_lj(r_buff=r_buff, **lj), pos, box, ntypes=ntypes)
+    sc = G.abs_scales(configure, pos, box, ntypes=ntypes)
 
     p = mg.particles()
     tag = p["tag"]
@@ -149,6 +156,7 @@ def main():
     n_side = int(sys.argv[1]) if len(sys.argv) > 1 else 24
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
     ntypes = int(sys.argv[3]) if len(sys.argv) > 3 else 1     # 2: Kob-Andersen-like mixture under Langevin
+    pair_kind = sys.argv[4] if len(sys.argv) > 4 else "lj"    # morse | yukawa | gauss: another evaluator (one type, NVE)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
@@ -165,6 +173,10 @@ def main():
                           shift_mode=1))
     else:
         pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
+        coeffs = {"morse": dict(D0=1.0, alpha=3.0, r0=1.2), "yukawa": dict(epsilon=2.0, kappa=1.5),
+                  "gauss": dict(epsilon=1.5, sigma=0.9)}
+        if pair_kind != "lj":
+            kw = dict(pair=(pair_kind, coeffs[pair_kind]), r_cut=2.5)
     rng = np.random.default_rng(5)
     pos[:, :3] += rng.normal(0, 0.12 if ntypes == 1 else 0.05, (len(pos), 3)).astype(np.float32)
     pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
