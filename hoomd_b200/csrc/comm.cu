@@ -12,10 +12,27 @@ __device__ __forceinline__ bool warp_barrier(const MgConst& c, MgState* ms, int 
     }
 
 __global__ void __launch_bounds__(32) k_mg_step_barrier(const __grid_constant__ MgConst c, MgState* ms, StepState* st,
-                                                        cudaGraphConditionalHandle handle, int use_cond)
+                                                        cudaGraphConditionalHandle handle, int use_cond,
+                                                        unsigned long long* nvt_acc)
     {
-    // the vote: did any particle of any rank move more than r_buff/2 (hoomd/md/NeighborListGPU.cc:117-122)
-    const bool moved = warp_barrier(c, ms, 0, st->moved != 0u);
+    bool moved;
+    if (nvt_acc)
+        {
+        // TwoStepNVTMTK under decomposition: the thermostat needs sum(m v^2) of ALL ranks.  The step kernel left this rank's
+        // share in the fixed-point accumulators of the parity the NEXT launch reads (its ts_step_two = the current
+        // timestep); the barrier adds up the ranks' totals and leaves the world total in slot 0, so md_step_nvt_begin of
+        // every rank advances its copy of the thermostat with the same bits.
+        unsigned long long* acc = nvt_acc + (size_t)(st->timestep & 1u) * NVT_SLOTS * NVT_SLOT_STRIDE;
+        unsigned long long v = threadIdx.x < NVT_SLOTS ? acc[threadIdx.x * NVT_SLOT_STRIDE] : 0ull;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        unsigned long long total = 0ull;
+        moved = mg_warp_barrier(c.world, c.rank, c.flags, ms, 0, st->moved != 0u, v, &total);
+        if (threadIdx.x < NVT_SLOTS) acc[threadIdx.x * NVT_SLOT_STRIDE] = threadIdx.x == 0 ? total : 0ull;
+        __syncwarp();
+        }
+    else
+        // the vote: did any particle of any rank move more than r_buff/2 (hoomd/md/NeighborListGPU.cc:117-122)
+        moved = warp_barrier(c, ms, 0, st->moved != 0u);
     if (threadIdx.x == 0)
         {
         st->moved = moved ? 1u : 0u;
@@ -374,9 +391,9 @@ __global__ void __launch_bounds__(256) k_mg_ghost_send(const __grid_constant__ M
 
 // ---- launchers ------------------------------------------------------------------------------------------------------------
 cudaError_t launch_mg_step_barrier(const MgConst& c, const MgLocal& l, unsigned long long cond_handle, int use_cond,
-                                   cudaStream_t stream)
+                                   cudaStream_t stream, unsigned long long* nvt_acc)
     {
-    k_mg_step_barrier<<<1, 32, 0, stream>>>(c, l.ms, l.st, (cudaGraphConditionalHandle)cond_handle, use_cond);
+    k_mg_step_barrier<<<1, 32, 0, stream>>>(c, l.ms, l.st, (cudaGraphConditionalHandle)cond_handle, use_cond, nvt_acc);
     return cudaGetLastError();
     }
 

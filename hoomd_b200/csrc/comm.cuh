@@ -120,12 +120,18 @@ __device__ __forceinline__ unsigned long long ld_flag(const unsigned long long* 
 // payload bits.  A peer that never arrives (crashed process) must not hang the GPU: after 4 s the wait gives up and sets the
 // sticky error bit 8; the host reports it at the end of the chunk.  flags[q] = rank q's flag array,
 // flags[q][(kind*2 + parity) * MG_MAX_RANKS + writer].
+// value / sum_out (optional): an all-reduce riding on the barrier -- every rank deposits one 64-bit integer in every rank's
+// value slots (behind the flag words, same indexing) before its flag, and adds up the world's deposits after the wait.  Integer
+// addition: every rank gets the same bits (TwoStepNVTMTK's kinetic energy under decomposition, fixed point).
 __device__ __forceinline__ bool mg_warp_barrier(unsigned int world, unsigned int rank, unsigned long long* const* flags,
-                                                MgState* ms, int kind, bool payload)
+                                                MgState* ms, int kind, bool payload, unsigned long long value = 0ull,
+                                                unsigned long long* sum_out = nullptr)
     {
     const unsigned int lane = threadIdx.x & 31;
     const unsigned long long epoch = ms->epoch[kind] + 1ull;
     const unsigned int slot = ((unsigned int)kind * 2u + (unsigned int)(epoch & 1ull)) * MG_MAX_RANKS;
+    constexpr unsigned int VAL0 = MG_NBARRIER * 2u * MG_MAX_RANKS; // value slots follow the flag words
+    if (sum_out && lane < world) st_flag(flags[lane] + VAL0 + slot + rank, value);
     __threadfence_system(); // everything this rank wrote (ghosts, migrants, counts) is visible before the flag is
     __syncwarp();
     const unsigned long long t0 = globaltimer_ns();
@@ -149,6 +155,12 @@ __device__ __forceinline__ bool mg_warp_barrier(unsigned int world, unsigned int
     const bool any = __any_sync(0xffffffffu, bit);
     __threadfence_system();
     __syncwarp();
+    if (sum_out)
+        {
+        unsigned long long v = lane < world ? ld_flag(flags[rank] + VAL0 + slot + lane) : 0ull;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        *sum_out = v;
+        }
     if (lane == 0)
         {
         ms->epoch[kind] = epoch;
@@ -160,8 +172,9 @@ __device__ __forceinline__ bool mg_warp_barrier(unsigned int world, unsigned int
     }
 
 // all-ranks barrier of kind k; kind 0 also carries the distance-check vote and takes the rebuild decision
+// nvt_acc != NULL (TwoStepNVTMTK): the barrier also sums the ranks' kinetic-energy accumulators of the step about to run
 cudaError_t launch_mg_step_barrier(const MgConst& c, const MgLocal& l, unsigned long long cond_handle, int use_cond,
-                                   cudaStream_t stream);
+                                   cudaStream_t stream, unsigned long long* nvt_acc = nullptr);
 cudaError_t launch_mg_barrier(const MgConst& c, const MgLocal& l, int kind, const unsigned int* enable,
                               cudaStream_t stream);
 // rebuild bracket, last: collective Nmax-overflow vote (sets st->abort on every rank)

@@ -291,6 +291,7 @@ struct b200_system
     DevBuf<unsigned int> pplan, chunk_flag, cta_order;
     DevBuf<float> recv_shift;        // [27 * 3] periodic image shift of the ghosts received in segment d (binning only)
     DevBuf<GhostSendTable> gs_table;
+    unsigned int mg_n_global = 0;    // particles of all ranks (thermostat degrees of freedom)
     unsigned int mg_tpp = 2;         // lanes per particle of k_md_step under decomposition (fixes the chunk size of cta_order)
     // Ghost update inside k_md_step with the boundary chunks scheduled first, so the NVLink stores overlap the interior force
     // work (the default).  HOOMD_B200_FUSED_GHOSTS=0: the round-1 sequence barrier kernel -> k_md_step ->
@@ -411,7 +412,8 @@ static const void* pair_params_ptr(b200_system* s)
 
 // IntegratorTwoStep::getNDOF for one method on all particles (hoomd/md/IntegratorTwoStep.cc:270-283): D N - D
 static unsigned int method_group_size(const b200_system* s) { return s->group_flag.n ? s->group_size : s->N; }
-static unsigned int nvt_ndof(const b200_system* s) { return 3u * method_group_size(s) - 3u; }
+// (domain decomposition: the group is all particles of ALL ranks)
+static unsigned int nvt_ndof(const b200_system* s) { return 3u * (s->mg ? s->mg_n_global : method_group_size(s)) - 3u; }
 
 // ParticleGroup::getIndexArray of the method's group (NULL = all particles): rebuilt when the particle order changed
 static const unsigned int* group_index(b200_system* s)
@@ -2300,9 +2302,11 @@ int b200_sys_set_dist_check(b200_system* s, int on)
 int b200_sys_add_nvt(b200_system* s, float kT, float tau)
     {
     SYS_TRY(s)
-    if (s->mg) throw std::runtime_error("integrate.nvt: not available under domain decomposition yet");
+    if (s->mg && s->group_flag.n) throw std::runtime_error("integrate.nvt: groups are not available under domain decomposition");
     if (s->tile_on) throw std::runtime_error("integrate.nvt: not available on the cell-tile path");
     if (!(kT > 0.0f)) throw std::runtime_error("integrate.nvt: kT must be positive");
+    // under decomposition the kinetic energy is summed over the ranks by the stand-alone step barrier (comm.cu)
+    if (s->mg) s->mg_mode &= ~4;
     if (tau <= 0.0f) fprintf(stderr, "*Warning*: integrate.nvt: tau set less than 0.0\n"); // TwoStepNVTMTK.cc:46-47
     s->method = 3;
     s->limit = 0;

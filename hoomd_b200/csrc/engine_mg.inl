@@ -129,7 +129,8 @@ static void mg_setup(b200_system* s, const b200_mg_params& p)
     s->off_tag = o; o = align_up(o + ntot * sizeof(unsigned int), 256);
     s->off_mig = o; o = align_up(o + (size_t)MG_NDIR * c.mig_cap * sizeof(MigElem), 256);
     s->off_migcnt = o; o = align_up(o + MG_NDIR * sizeof(unsigned int), 256);
-    s->off_flags = o; o = align_up(o + (size_t)MG_NBARRIER * 2 * MG_MAX_RANKS * sizeof(unsigned long long), 256);
+    // flag words, then as many value words (the all-reduce that rides on a barrier, comm.cuh:mg_warp_barrier)
+    s->off_flags = o; o = align_up(o + (size_t)2 * MG_NBARRIER * 2 * MG_MAX_RANKS * sizeof(unsigned long long), 256);
     s->slab_bytes = o;
     CUDA_OK(cudaMalloc(&s->slab, s->slab_bytes));
     CUDA_OK(cudaMemset(s->slab, 0, s->slab_bytes));
@@ -155,6 +156,7 @@ static void mg_setup(b200_system* s, const b200_mg_params& p)
     s->gs_table.alloc(1);
     // chunk size of k_md_step = particles per CTA: fixed for the life of the system (it shapes cta_order)
     // (2 or 8 lanes per particle: the widths every pair evaluator is instantiated for)
+    s->mg_n_global = p.N_global;
     s->mg_tpp = pick_pair_tpp(std::max(1u, p.N_global / p.world)) <= 2u ? 2u : 8u;
     const unsigned int ppb = md_step_block() / s->mg_tpp;
     const unsigned int nchunks = (s->Ncap + ppb - 1) / ppb;
@@ -339,6 +341,8 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
 // -- the single-GPU graph with the collective rebuild bracket in the IF bodies: the LAST CTA of k_md_step takes the all-ranks
 // barrier, the vote and the rebuild decision and arms the next IF node.  HOOMD_B200_FUSED_GHOSTS=0 (round-1 sequence):
 //     barrier -> IF{rebuild from A} -> k_md_step(A->B) -> ghosts(B) -> barrier -> IF{rebuild from B} -> k_md_step(B->A) -> ghosts(A)
+static unsigned long long* mg_nvt_acc(b200_system* s) { return s->method == 3 ? s->nvt_acc.p : nullptr; }
+
 static void mg_build_graph(b200_system* s)
     {
 #if (CUDART_VERSION >= 12040)
@@ -361,11 +365,11 @@ static void mg_build_graph(b200_system* s)
         if (fused)
             CUDA_OK(launch_graph_pre(s->d_state.p, (unsigned long long)h0, s->stream));
         else
-            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream));
+            CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h0, 1, s->stream, mg_nvt_acc(s)));
         cudaGraph_t body0 = add_if_node(s, graph, h0);
         enqueue_md_step(s, fa, 0, fused ? (unsigned long long)h1 : 0ull, fused ? 1 : 0);
         if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-        if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream));
+        if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, (unsigned long long)h1, 1, s->stream, mg_nvt_acc(s)));
         cudaGraph_t body1 = add_if_node(s, graph, h1);
         enqueue_md_step(s, fa, 1, 0ull, 0);
         if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
@@ -425,19 +429,28 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         const bool fused = fa.mg == 2;
         const bool push = fa.gs.tab != nullptr;
         if (!resume) CUDA_OK(launch_fused_step_one(fa, s->d_state.p, s->stream));
+        if (s->method == 3)
+            {
+            // TwoStepNVTMTK: this rank's kinetic energy of the half-step velocities goes into the accumulators the first step
+            // kernel reads; the first step barrier adds up the ranks (k_mg_step_barrier), the kernel advances the thermostat
+            CUDA_OK(cudaMemsetAsync(s->nvt_acc.p, 0, sizeof(unsigned long long) * s->nvt_acc.n, s->stream));
+            CUDA_OK(launch_nvt_seed(s->nvt_acc.p, s->nvt_partial.p, b200_system::NVT_BLOCKS, (const float*)s->vel.p, nullptr,
+                                    s->N, s->nvt_scale, s->timestep & 1u, s->stream));
+            s->kernels_last_run += 2;
+            }
         CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));
-        if (fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+        if (fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream, mg_nvt_acc(s)));
         const unsigned int nreplay = (remaining + 1) / 2;
         if (s->use_graph == 3)
             {
             const unsigned int* enable = &s->d_state.p->need_rebuild;
             for (unsigned int k = 0; k < nreplay; k++)
                 {
-                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream, mg_nvt_acc(s)));
                 mg_enqueue_rebuild(s, enable, s->pos.p, 0);
                 enqueue_md_step(s, fa, 0, 0ull, 0);
                 if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos_alt.p, 1, nullptr, s->stream));
-                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream));
+                if (!fused) CUDA_OK(launch_mg_step_barrier(s->mgc, s->mgl, 0ull, 0, s->stream, mg_nvt_acc(s)));
                 mg_enqueue_rebuild(s, enable, s->pos_alt.p, 1);
                 enqueue_md_step(s, fa, 1, 0ull, 0);
                 if (!push) CUDA_OK(launch_mg_ghost_send(s->mgc, s->mgl, s->pos.p, 0, nullptr, s->stream));

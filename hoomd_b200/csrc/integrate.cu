@@ -266,6 +266,29 @@ __global__ void k_nvt_advance(NvtState* __restrict__ state, const double* __rest
         }
     }
 
+// Domain decomposition: this rank's sum(m v^2) in fixed point into slot 0 of the accumulators of `parity` (the other slots of
+// that parity zeroed); the step barrier adds up the ranks, md_step_nvt_begin advances the thermostat (fused_step.cu)
+__global__ void k_nvt_seed(unsigned long long* __restrict__ acc, const double* __restrict__ partial, unsigned int nblocks,
+                           double scale, unsigned int parity)
+    {
+    double x = 0.0;
+    for (unsigned int b = threadIdx.x; b < nblocks; b += 32) x += partial[b];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    unsigned long long* a = acc + (size_t)parity * NVT_SLOTS * NVT_SLOT_STRIDE;
+    if (threadIdx.x < NVT_SLOTS)
+        a[threadIdx.x * NVT_SLOT_STRIDE] = threadIdx.x == 0 ? (unsigned long long)__double2ll_rn(x * scale) : 0ull;
+    }
+
+cudaError_t launch_nvt_seed(unsigned long long* d_acc, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                            const unsigned int* d_group, unsigned int group_size, double scale, unsigned int parity,
+                            cudaStream_t stream)
+    {
+    if (n_partial_blocks == 0 || !d_partial || !d_acc) return cudaErrorInvalidValue;
+    k_nvt_ke_partial<<<n_partial_blocks, 256, 0, stream>>>(d_partial, (const float4*)d_vel, d_group, group_size);
+    k_nvt_seed<<<1, 32, 0, stream>>>(d_acc, d_partial, n_partial_blocks, scale, parity);
+    return cudaGetLastError();
+    }
+
 cudaError_t launch_nvt_advance(float* d_nvt_state, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
                                const unsigned int* d_group, unsigned int group_size, unsigned int ndof, float T, float tau,
                                float dt, unsigned int gen, cudaStream_t stream)

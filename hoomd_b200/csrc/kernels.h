@@ -48,6 +48,10 @@ cudaError_t launch_nvt_advance(float* d_nvt_state, double* d_partial, unsigned i
                                const unsigned int* d_group, unsigned int group_size, unsigned int ndof, float T, float tau,
                                float dt, unsigned int gen, cudaStream_t stream);
 
+cudaError_t launch_nvt_seed(unsigned long long* d_acc, double* d_partial, unsigned int n_partial_blocks, const float* d_vel,
+                            const unsigned int* d_group, unsigned int group_size, double scale, unsigned int parity,
+                            cudaStream_t stream);
+
 struct OverflowHook
     {
     unsigned int* overflow = nullptr;   // set to 1 on overflow

@@ -111,6 +111,8 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
             s.setup_integrator(0.005)
             if method == "langevin":
                 s.add_langevin(1.0, 11, gamma=[1.0, 0.5][:ntypes] if ntypes <= 2 else [1.0] * ntypes)
+            elif method == "nvt":
+                s.add_nvt(1.0, 0.4)
             else:
                 s.add_nve()
             s.set_sorter(100)
@@ -132,6 +134,11 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
                    # NeighborList::getNumUpdates = normal + forced updates (hoomd/md/NeighborList.h:423-426)
                    rebuilds_mg=int(mg.stats()["updates"] + mg.stats()["forced"]), mg_stats=mg.mg_stats(),
                    mg_timing=mg.mg_timing())
+        if method == "nvt":
+            # the thermostat variables of every rank follow the single-domain reference (kinetic energy summed over the ranks)
+            res.update(nvt_ref=[float(x) for x in r.nvt_state()], nvt_mg=[float(x) for x in mg.nvt_state()])
+            assert np.allclose(res["nvt_mg"], res["nvt_ref"], rtol=1e-3, atol=1e-5), res
+            assert abs(res["nvt_ref"][0]) > 1e-3, "the thermostat did not act"
         tol = 5e-3 * max(1.0, steps / 300.0)
         assert res["pos_err"] < tol and res["unwrapped_err"] < tol, res
         assert res["rebuilds_ref"] == res["rebuilds_mg"], res
@@ -157,6 +164,7 @@ def main():
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
     ntypes = int(sys.argv[3]) if len(sys.argv) > 3 else 1     # 2: Kob-Andersen-like mixture under Langevin
     pair_kind = sys.argv[4] if len(sys.argv) > 4 else "lj"    # morse | yukawa | gauss: another evaluator (one type, NVE)
+    method = sys.argv[5] if len(sys.argv) > 5 else ""         # nvt: Nose-Hoover thermostat (one type)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
@@ -180,6 +188,8 @@ def main():
     rng = np.random.default_rng(5)
     pos[:, :3] += rng.normal(0, 0.12 if ntypes == 1 else 0.05, (len(pos), 3)).astype(np.float32)
     pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+    if method:
+        kw["method"] = method
     res = parity_pass(pos, vel, None, L, steps, local_rank, **kw)
     assert res["mg_stats"]["max_migrants"] > 0 or steps < 100, "no particle ever migrated: migration was not exercised"
     dist.barrier()
