@@ -88,7 +88,8 @@ __global__ void __launch_bounds__(256) k_bond_forces(float4* __restrict__ force,
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     const unsigned int row = TAGKEYED ? tag[i] : i;
-    const unsigned int nb = n_bonds[row];
+    // (domain decomposition: unused local slots carry the tag 0xffffffff)
+    const unsigned int nb = (TAGKEYED && row == 0xffffffffu) ? 0u : n_bonds[row];
     const float4 pi4 = pos[i];
     const float di = diameter ? diameter[i] : 1.0f;
     float4 F = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -97,6 +98,11 @@ __global__ void __launch_bounds__(256) k_bond_forces(float4* __restrict__ force,
         {
         const uint2 e = blist[(size_t)k * pitch + row];
         const unsigned int j = TAGKEYED ? rtag[e.x] : e.x;
+        if (TAGKEYED && j == 0xffffffffu)
+            {
+            *flags = 2u; // domain decomposition: the partner is neither local nor a ghost ("bond incomplete")
+            return;
+            }
         const float4 pj4 = pos[j];
         const float dj = diameter ? diameter[j] : 1.0f;
         float3 dx = make_float3(__fsub_rn(pi4.x, pj4.x), __fsub_rn(pi4.y, pj4.y), __fsub_rn(pi4.z, pj4.z));
@@ -180,7 +186,7 @@ __global__ void __launch_bounds__(256) k_nlist_filter(unsigned int* __restrict__
     if (live)
         {
         row = TAGKEYED ? tag[i] : i;
-        nex = n_ex[row];
+        nex = (TAGKEYED && row == 0xffffffffu) ? 0u : n_ex[row];
         }
     const bool work = live && ex_start < nex;
     if (!__any_sync(0xffffffffu, work)) return;

@@ -389,6 +389,50 @@ __global__ void __launch_bounds__(256) k_mg_ghost_send(const __grid_constant__ M
     if (slot == 0) atomicMax(&l.ms->max_gsend, n);
     }
 
+// ---- tag -> index map over locals AND ghosts (bonded forces / exclusions under decomposition) ---------------------------------
+// Bond and exclusion tables stay keyed by GLOBAL tag on every rank (replicated, like the reference's BondData before
+// GroupCommunicator scatters it); a bond partner that lives on another rank is reached through its ghost copy.  Unused local
+// slots [N, Ncap) get the tag NO_TAG so that the tag-keyed kernels skip them.
+__global__ void __launch_bounds__(256) k_mg_rtag_clear(unsigned int* __restrict__ rtag, unsigned int ntags,
+                                                       const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < ntags) rtag[t] = 0xffffffffu;
+    }
+
+__global__ void __launch_bounds__(256) k_mg_rtag_fill(const __grid_constant__ MgConst c, const MgLocal l,
+                                                      const float4* __restrict__ pos, unsigned int* __restrict__ rtag,
+                                                      unsigned int ntags, const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return;
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c.Ncap + c.Gcap) return;
+    const unsigned int N = l.st->N;
+    if (i < c.Ncap)
+        {
+        if (i >= N)
+            {
+            l.tag[i] = 0xffffffffu;
+            return;
+            }
+        }
+    else if (!(pos[i].x < 1.0e29f))
+        return; // blank ghost slot
+    const unsigned int t = l.tag[i];
+    // locals win over ghost copies of the same particle (none exist for legal domain widths); among copies any one serves:
+    // they hold the same raw coordinates
+    if (t < ntags && (i < c.Ncap || rtag[t] == 0xffffffffu)) rtag[t] = i;
+    }
+
+cudaError_t launch_mg_rtag(const MgConst& c, const MgLocal& l, const float4* pos, unsigned int* rtag, unsigned int ntags,
+                           const unsigned int* enable, cudaStream_t stream)
+    {
+    k_mg_rtag_clear<<<(ntags + 255u) / 256u, 256, 0, stream>>>(rtag, ntags, enable);
+    k_mg_rtag_fill<<<(c.Ncap + c.Gcap + 255u) / 256u, 256, 0, stream>>>(c, l, pos, rtag, ntags, enable);
+    return cudaGetLastError();
+    }
+
 // ---- launchers ------------------------------------------------------------------------------------------------------------
 cudaError_t launch_mg_step_barrier(const MgConst& c, const MgLocal& l, unsigned long long cond_handle, int use_cond,
                                    cudaStream_t stream, unsigned long long* nvt_acc)

@@ -186,6 +186,9 @@ cudaError_t launch_mg_migrate(const MgConst& c, const MgLocal& l, float4* pos, c
 // rebuild bracket, part 2: ghost plan + first ghost write (+ tags) ... barrier
 cudaError_t launch_mg_ghost_plan(const MgConst& c, const MgLocal& l, float4* pos, int buffer, const unsigned int* enable,
                                  cudaStream_t stream);
+// rebuild bracket, after the ghost plan: tag -> index over locals and ghosts (bonds / exclusions keyed by global tag)
+cudaError_t launch_mg_rtag(const MgConst& c, const MgLocal& l, const float4* pos, unsigned int* rtag, unsigned int ntags,
+                           const unsigned int* enable, cudaStream_t stream);
 // every step: owners write their boundary particles into the neighbors' ghost slots of buffer `buffer` (0 = A, 1 = B)
 cudaError_t launch_mg_ghost_send(const MgConst& c, const MgLocal& l, const float4* pos, int buffer,
                                  const unsigned int* enable, cudaStream_t stream);

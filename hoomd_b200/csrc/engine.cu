@@ -505,6 +505,13 @@ static void enqueue_bond_forces(b200_system* s, const float4* pos)
     memset(&a, 0, sizeof(a));
     a.d_force = (float*)s->bond_force.p; a.d_virial = s->bond_virial.p; a.virial_pitch = s->virial_pitch;
     a.N = s->N; a.d_pos = (const float*)pos; a.d_diameter = nullptr; a.box = s->box;
+    if (s->mg)
+        {
+        // every slot of the local capacity (unused ones carry NO_TAG and are skipped: the live count changes on the device);
+        // partners may be ghosts with raw coordinates: minimum images in the GLOBAL box
+        a.N = s->Ncap;
+        a.box = s->global_box;
+        }
     a.d_bond_list = (const unsigned int*)s->bond_list.p; a.pitch = s->bond_pitch; a.d_n_bonds = s->bond_n.p;
     a.n_bond_types = s->n_bond_types; a.compute_virial = s->compute_virial ? 1u : 0u;
     a.d_tag = s->tag.p; a.d_rtag = s->rtag.p;
@@ -528,6 +535,9 @@ static void check_bond_flags(b200_system* s)
     if (f)
         {
         CUDA_OK(cudaMemsetAsync(s->bond_flags.p, 0, sizeof(unsigned int), s->stream));
+        if (f == 2u)
+            throw std::runtime_error("bond: a bond partner is neither a local particle nor a ghost of this rank (bond longer "
+                                     "than the ghost layer?)");
         throw std::runtime_error(std::string("bond.") + (s->bond_kind == 0 ? "fene" : "harmonic")
                                  + ": bond out of bounds. Error in bond calculation");
         }
@@ -542,7 +552,7 @@ static void enqueue_nlist_filter(b200_system* s, const unsigned int* enable)
                                     s->ex_max, nullptr, nullptr, s->N, enable, s->stream, s->h_Nmax[0]));
     else
         CUDA_OK(launch_nlist_filter(s->n_neigh.p, s->nlist.p, s->head_list.p, s->ex_n.p, s->ex_list.p, s->ex_pitch,
-                                    s->ex_max, s->tag.p, s->rtag.p, s->N, enable, s->stream, s->h_Nmax[0]));
+                                    s->ex_max, s->tag.p, s->rtag.p, s->mg ? s->Ncap : s->N, enable, s->stream, s->h_Nmax[0]));
     }
 } // namespace b200
 
@@ -1961,8 +1971,14 @@ int b200_sys_set_bonds(b200_system* s, unsigned int nbonds, const unsigned int* 
                        unsigned int n_bond_types)
     {
     SYS_TRY(s)
-    if (s->mg) throw std::runtime_error("bond: bonded forces under domain decomposition are not supported in this round");
-    const unsigned int N = s->N;
+    // domain decomposition: the table covers the GLOBAL tags on every rank and stays keyed by tag (a partner on another rank
+    // is reached through its ghost copy, comm.cu:k_mg_rtag_fill)
+    const unsigned int N = s->mg ? s->mg_n_global : s->N;
+    if (s->mg)
+        {
+        s->idx_tables = false;
+        if (s->rtag.n < N) s->rtag.alloc(N);
+        }
     if (nbonds && n_bond_types == 0) throw std::runtime_error("bond: no bond types defined");
     if (n_bond_types > 256) throw std::runtime_error("bond: more than 256 bond types");
     std::vector<unsigned int> cnt(N, 0u);
@@ -2024,6 +2040,10 @@ int b200_sys_setup_bond_force(b200_system* s, int kind, const float* K, const fl
         s->bond_params2.alloc(nb);
         s->bond_params2.upload(p.data(), nb, s->stream);
         }
+    if (s->mg && kind == 0)
+        for (unsigned int t = 0; t < nb; t++)
+            if (r0[t] > s->r_ghost)
+                throw std::runtime_error("bond.fene: r0 exceeds the ghost layer width (r_cut + r_buff) of the decomposition");
     s->bond_force.alloc(s->Ncap);
     s->pair_force_copy.alloc(s->Ncap);
     s->bond_virial.alloc(6 * (size_t)s->virial_pitch);
@@ -2039,7 +2059,6 @@ int b200_sys_setup_bond_force(b200_system* s, int kind, const float* K, const fl
 int b200_sys_nlist_exclusions_from_bonds(b200_system* s, int on)
     {
     SYS_TRY(s)
-    if (s->mg) throw std::runtime_error("nlist: exclusions under domain decomposition are not supported in this round");
     if (s->tile_on) throw std::runtime_error("nlist: the cell-tile pair path does not filter exclusions (use pair mode 0)");
     invalidate_graph(s);
     s->force_update = true;
@@ -2050,7 +2069,12 @@ int b200_sys_nlist_exclusions_from_bonds(b200_system* s, int on)
         }
     else
         {
-        const unsigned int N = s->N;
+        const unsigned int N = s->mg ? s->mg_n_global : s->N;
+        if (s->mg)
+            {
+            s->idx_tables = false;
+            if (s->rtag.n < N) s->rtag.alloc(N);
+            }
         const size_t nbonds = s->h_bond_types.size();
         // NeighborList::addExclusion per bond, duplicates skipped (hoomd/md/NeighborList.cc:431-470)
         std::vector<std::vector<unsigned int>> ex(N);

@@ -236,6 +236,18 @@ static void mg_connect(b200_system* s, const unsigned char* handles)
     }
 
 // the rebuild bracket of one rank: migrate -> ghost plan + first ghost write -> cell list -> neighbor list
+// bonded forces / exclusions: tag -> index over locals and ghosts, then NeighborList::filterNlist on the fresh rows
+static bool mg_has_tag_tables(const b200_system* s)
+    {
+    return s->bond_n.n != 0 || (s->exclusions_set && s->ex_max);
+    }
+static void mg_enqueue_tag_maps(b200_system* s, const unsigned int* enable, const float4* pos)
+    {
+    if (!mg_has_tag_tables(s)) return;
+    CUDA_OK(launch_mg_rtag(s->mgc, s->mgl, pos, s->rtag.p, s->mg_n_global, enable, s->stream));
+    enqueue_nlist_filter(s, enable);
+    }
+
 static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float4* pos, int buffer)
     {
     CUDA_OK(launch_mg_migrate(s->mgc, s->mgl, pos, enable, s->stream));
@@ -250,6 +262,7 @@ static void mg_enqueue_rebuild(b200_system* s, const unsigned int* enable, float
     OverflowHook hook; // every rank must keep stepping to the barrier: raise the flag only
     hook.overflow = &s->d_state.p->overflow;
     CUDA_OK(launch_nlist_binned(&na, enable, s->stream, hook));
+    mg_enqueue_tag_maps(s, enable, pos);
     CUDA_OK(launch_mg_rebuild_vote(s->mgc, s->mgl, buffer, enable, s->stream));
     }
 constexpr unsigned long long MG_REBUILD_KERNELS = 8 + 4 + 4 + 2; // migrate, ghost plan + CTA order, cell list, nlist + vote
@@ -312,6 +325,7 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
                 CUDA_OK(cudaMemsetAsync(s->nl_conditions.p, 0, sizeof(unsigned int) * s->ntypes, s->stream));
                 }
             } while (overflowed);
+        mg_enqueue_tag_maps(s, nullptr, s->pos.p);
         s->force_update = false;
         s->nl_first_compute = false;
         s->cl_first = false;
@@ -328,6 +342,20 @@ static void mg_prep_run(b200_system* s, unsigned int ts)
     pair_args(s, a);
     CUDA_OK(b200_compute_pair_forces(s->pair_kind, &a, pair_params_ptr(s), s->stream));
     s->kernels_last_run += 1;
+    if (s->bond_kind >= 0)
+        {
+        // second ForceCompute: net = pair + bond (Integrator::computeNetForce), as compute_net_force does on one GPU
+        CUDA_OK(cudaMemcpyAsync(s->pair_force_copy.p, s->net_force.p, sizeof(float4) * s->Ncap, cudaMemcpyDeviceToDevice,
+                                s->stream));
+        if (s->compute_virial)
+            CUDA_OK(cudaMemcpyAsync(s->pair_virial_copy.p, s->net_virial.p, sizeof(float) * 6 * (size_t)s->virial_pitch,
+                                    cudaMemcpyDeviceToDevice, s->stream));
+        enqueue_bond_forces(s, s->pos.p);
+        CUDA_OK(launch_add_force(s->net_force.p, s->net_virial.p, s->virial_pitch, s->bond_force.p, s->bond_virial.p,
+                                 s->virial_pitch, s->Ncap, s->compute_virial, s->stream));
+        s->kernels_last_run += 2;
+        check_bond_flags(s);
+        }
     if (!s->accel_set)
         {
         CUDA_OK(launch_compute_accel((float*)s->accel.p, s->net_force.p, s->vel.p, s->N, s->stream));
@@ -461,6 +489,7 @@ static void mg_run_chunk(b200_system* s, unsigned int chunk)
         mg_download_state(s);
         const StepState st = *s->h_state;
         mg_check_errors(s);
+        check_bond_flags(s);
         cell_list_check_conditions(s);
         const unsigned long long rebuilds = (unsigned long long)st.num_updates + st.num_forced;
         s->kernels_last_run += (fused ? 3ull : 2ull) + (fused ? 3ull : (push ? 4ull : 6ull)) * nreplay

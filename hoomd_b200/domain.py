@@ -84,6 +84,7 @@ class DomainSystem(System):
         pos4 = np.ascontiguousarray(pos4, np.float32)
         self.N_global = int(pos4.shape[0])
         self.ntypes = int(ntypes)
+        self.n_bond_types = 0
         self.grid = tuple(grid) if grid is not None else find_decomposition(box, self.world)
         self.global_L = tuple(float(v) for v in box)
         owner = place_particles(pos4[:, :3], box, self.grid)

@@ -46,12 +46,14 @@ def expected_ghost_tags(pos, L, lo, hi, per, r_ghost):
 
 
 def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, check_ghosts=True, verbose=True, ntypes=1,
-                lj=None, method="nve", pair=None):
+                lj=None, method="nve", pair=None, bonds=None):
     """One domain-decomposed system against RefSystem on the same snapshot (every rank calls this; torch.distributed must be
     initialised).  Returns a dict of measured maxima; raises AssertionError on a parity failure.  ntypes / lj: a mixture with
     per-pair coefficients (type ids in pos[:, 3]); method "langevin": the noise is keyed by global tag, so the decomposed
     trajectory follows the single-domain reference as well.  pair = (kind, coefficients): another pair evaluator
-    (md.pair.gauss / yukawa / mie / force_shifted_lj / morse) through setup_pair on all three sides."""
+    (md.pair.gauss / yukawa / mie / force_shifted_lj / morse) through setup_pair on all three sides.  bonds: (nbonds, 2)
+    GLOBAL tags -- FENE bonds + bond exclusions (Kremer-Grest): every rank holds the whole tag-keyed table and reaches a
+    partner on another rank through its ghost copy."""
     import torch.distributed as dist
     import golden_util as G
     from hoomd_b200 import domain
@@ -68,10 +70,15 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
     lj.setdefault("r_cut", r_cut)
     mg = domain.DomainSystem(pos, box, r_ghost=r_cut_max + r_buff, vel4=vel, image=image, device=local_rank, ntypes=ntypes)
     def configure(sys_, **extra):
+        if bonds is not None:
+            sys_.set_bonds(bonds)
         if pair is not None:
             sys_.setup_pair(pair[0], r_cut=lj["r_cut"], r_buff=r_buff, **pair[1], **extra)
         else:
             sys_.setup_lj(r_buff=r_buff, **lj, **extra)
+        if bonds is not None:
+            sys_.setup_fene(k=30.0, r0=1.5, epsilon=1.0, sigma=1.0)
+            sys_.exclusions_from_bonds(True)
 
     configure(mg)
     mg.compute_forces(0)
@@ -89,12 +96,14 @@ def parity_pass(pos, vel, image, L, steps, local_rank, r_cut=3.0, r_buff=0.4, ch
         assert np.abs(d).max() < 1e-5
 
     # ---- the reference's answer (CPU classes, full list) and the scales of the 1e-5 bar, on every rank's host cores ----
-    r = R.RefSystem(pos, box, ntypes=ntypes, vel4=vel, image=image)
+    r = R.RefSystem(pos, box, ntypes=ntypes, vel4=vel, image=image, **(dict(n_bond_types=1) if bonds is not None else {}))
     configure(r, full=True)
     r.compute_forces(0)
     f_ref = r.forces(False)[0]
+    if bonds is not None:  # Integrator::computeNetForce: net = pair + bond, added in FP32
+        f_ref = f_ref + r.force_component(1)[0]
     rn = r.nlist()[0]
-    sc = G.abs_scales(configure, pos, box, ntypes=ntypes)
+    sc = G.abs_scales(configure, pos, box, ntypes=ntypes, n_bond_types=1 if bonds is not None else 0)
 
     p = mg.particles()
     tag = p["tag"]
@@ -183,11 +192,18 @@ def main():
         pos, vel, L = workloads.sc_lattice(n_side, (1.0 / rho) ** (1.0 / 3.0), kT=kT, seed=11)
         coeffs = {"morse": dict(D0=1.0, alpha=3.0, r0=1.2), "yukawa": dict(epsilon=2.0, kappa=1.5),
                   "gauss": dict(epsilon=1.5, sigma=0.9)}
-        if pair_kind != "lj":
+        if pair_kind in coeffs:
             kw = dict(pair=(pair_kind, coeffs[pair_kind]), r_cut=2.5)
     rng = np.random.default_rng(5)
     pos[:, :3] += rng.normal(0, 0.12 if ntypes == 1 else 0.05, (len(pos), 3)).astype(np.float32)
     pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+    if pair_kind == "kg":
+        # Kremer-Grest: chains of 8 beads threaded through the lattice, WCA + FENE, bond exclusions
+        pos, vel, L, bonds = workloads.polymer_lattice(n_side, 8, rho=0.85, kT=1.0, seed=11)
+        rng = np.random.default_rng(5)
+        pos[:, :3] += rng.normal(0, 0.03, (len(pos), 3)).astype(np.float32)
+        pos[:, :3] = np.clip(pos[:, :3], -L / 2, np.nextafter(np.float32(L / 2), np.float32(0)))
+        kw = dict(bonds=bonds, r_cut=2.0 ** (1.0 / 6.0), lj=dict(r_cut=2.0 ** (1.0 / 6.0), shift_mode=1))
     if method:
         kw["method"] = method
     res = parity_pass(pos, vel, None, L, steps, local_rank, **kw)
