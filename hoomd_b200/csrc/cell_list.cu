@@ -448,6 +448,135 @@ __global__ void __launch_bounds__(CF_BLOCK) k_cell_list_fused(
         }
     }
 
+// ---- small systems: the four phases in ONE launch of a single thread-block cluster (opt-in experiment, see below) --------
+// The cooperative grid above loses because its three grid barriers and the cooperative launch cost what the launch gaps cost.
+// A cluster's hardware barrier (barrier.cluster) is a few hundred ns, and 8-16 CTAs x 1024 threads are enough threads for
+// <= 131k particles (the phases are chains of dependent loads / atomics, not bandwidth): each thread keeps the cell and slot
+// of its <= CC_PER particles in registers from the bin phase to the scatter phase, every CTA scans ALL occupancies itself
+// (ncells <= 8192: one 1024-thread block scan, result in shared memory), so only two cluster barriers remain -- after the
+// counts and after the scatter.  Same arithmetic and the same final order as the 4-kernel path (the in-cell rank fixes it).
+constexpr unsigned int CC_BLOCK = 1024;
+constexpr unsigned int CC_PER = 8;       // particles per thread
+constexpr unsigned int CC_CELLS_PER = 8; // cells per thread in the scan
+constexpr unsigned int CC_MAX_CELLS = CC_BLOCK * CC_CELLS_PER;
+
+__device__ __forceinline__ void cluster_barrier()
+    {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+
+__global__ void __launch_bounds__(CC_BLOCK, 1) k_cell_list_cluster(
+    unsigned int* __restrict__ cell_count, unsigned int* __restrict__ cell_start, unsigned int* __restrict__ particle_cell,
+    unsigned int* __restrict__ particle_slot, unsigned int* scratch_idx, float4* __restrict__ cell_xyzf,
+    unsigned int* __restrict__ cell_type, unsigned int* __restrict__ cell_idx, unsigned int* __restrict__ conditions,
+    const float4* __restrict__ pos, const float* __restrict__ charge, unsigned int N, unsigned int n_ghost, Box box,
+    uint3 dim, float3 ghost_width, int flag_charge, int flag_type, const unsigned int* __restrict__ enable)
+    {
+    if (enable && !*enable) return; // uniform over the cluster: nobody reaches a barrier
+    extern __shared__ unsigned int s_start[]; // [ncells + 1] exclusive scan of the occupancies
+    __shared__ unsigned int warp_sums[33];
+    const unsigned int ntot = N + n_ghost;
+    const unsigned int ncells = dim.x * dim.y * dim.z;
+    const unsigned int stride = gridDim.x * CC_BLOCK;
+    const unsigned int tid = blockIdx.x * CC_BLOCK + threadIdx.x;
+    // phase 1: bin (k_cell_bin); cell and slot stay in registers
+    unsigned int cell_r[CC_PER], slot_r[CC_PER];
+#pragma unroll
+    for (unsigned int k = 0; k < CC_PER; k++)
+        {
+        const unsigned int n = tid + k * stride;
+        cell_r[k] = B200_NOT_BINNED;
+        slot_r[k] = 0;
+        if (n < ntot)
+            {
+            const float4 p = pos[n];
+            if (isnan(p.x) || isnan(p.y) || isnan(p.z))
+                atomicMax(&conditions[1], n + 1);
+            else
+                {
+                int3 b;
+                if (particle_bin(make_float3(p.x, p.y, p.z), box, ghost_width, dim, b))
+                    {
+                    cell_r[k] = ((unsigned int)b.z * dim.y + (unsigned int)b.y) * dim.x + (unsigned int)b.x;
+                    slot_r[k] = atomicAdd(&cell_count[cell_r[k]], 1u);
+                    }
+                else if (n < N)
+                    atomicMax(&conditions[2], n + 1);
+                }
+            particle_cell[n] = cell_r[k];
+            particle_slot[n] = slot_r[k];
+            }
+        }
+    cluster_barrier();
+    // phase 2: every CTA scans all occupancies (the counts live in L2: atomics); CTA 0 publishes cell_start
+    const unsigned int i0 = threadIdx.x * CC_CELLS_PER;
+    unsigned int c[CC_CELLS_PER];
+    unsigned int tsum = 0, max_occ = 0;
+#pragma unroll
+    for (unsigned int k = 0; k < CC_CELLS_PER; k++)
+        {
+        c[k] = (i0 + k < ncells) ? __ldcg(cell_count + i0 + k) : 0u;
+        tsum += c[k];
+        max_occ = max(max_occ, c[k]);
+        }
+    unsigned int total;
+    unsigned int excl = block_scan_1024(tsum, warp_sums, total);
+#pragma unroll
+    for (unsigned int k = 0; k < CC_CELLS_PER; k++)
+        {
+        if (i0 + k < ncells)
+            {
+            s_start[i0 + k] = excl;
+            if (blockIdx.x == 0) cell_start[i0 + k] = excl;
+            }
+        excl += c[k];
+        }
+    if (threadIdx.x == 0)
+        {
+        s_start[ncells] = total;
+        if (blockIdx.x == 0) cell_start[ncells] = total;
+        }
+    if (blockIdx.x == 0)
+        {
+        for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
+        if ((threadIdx.x & 31) == 0 && max_occ) atomicMax(&conditions[0], max_occ);
+        }
+    __syncthreads();
+    // phase 3: scatter (k_cell_scatter)
+#pragma unroll
+    for (unsigned int k = 0; k < CC_PER; k++)
+        if (cell_r[k] != B200_NOT_BINNED) scratch_idx[s_start[cell_r[k]] + slot_r[k]] = tid + k * stride;
+    cluster_barrier();
+    // every CTA has read the counts: leave zeros behind for the next build (as k_cell_scan does)
+    if (blockIdx.x == 0)
+        {
+#pragma unroll
+        for (unsigned int k = 0; k < CC_CELLS_PER; k++)
+            if (i0 + k < ncells) cell_count[i0 + k] = 0u;
+        }
+    // phase 4: in-cell rank by particle index, final arrays (k_cell_rank)
+    const unsigned int nbinned = total;
+#pragma unroll 2
+    for (unsigned int k = 0; k < CC_PER; k++)
+        {
+        const unsigned int e = tid + k * stride;
+        if (e >= nbinned) break;
+        const unsigned int n = scratch_idx[e];
+        const unsigned int cell = __ldcg(particle_cell + n);
+        const unsigned int s = s_start[cell], t = s_start[cell + 1];
+        unsigned int rank = 0;
+        for (unsigned int q = s; q < t; q++) rank += (scratch_idx[q] < n) ? 1u : 0u;
+        const float4 p = pos[n];
+        float flag;
+        if (flag_charge) flag = charge[n];
+        else if (flag_type) flag = p.w;
+        else flag = __int_as_float((int)n);
+        cell_xyzf[s + rank] = make_float4(p.x, p.y, p.z, flag);
+        if (cell_type) cell_type[s + rank] = (unsigned int)__float_as_int(p.w);
+        if (cell_idx) cell_idx[s + rank] = n;
+        }
+    }
+
 // ---- export to the reference's padded layout ------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_cell_export(unsigned int* __restrict__ cell_size, float4* __restrict__ xyzf,
                                                      float4* __restrict__ tdb, unsigned int* __restrict__ conditions,
@@ -620,9 +749,61 @@ static bool cell_use_fused(unsigned int ncells, unsigned int ntot, bool have_bar
     return have_barrier && ntot > 0 && ncells <= CF_MAX_CELLS && ntot <= 262144u && cell_fused_max_ctas() > 0;
     }
 
+// CTAs of the one-cluster build on the current device (0: not requested or clusters unavailable): 16 where the device
+// schedules a non-portable cluster of that size, else 8
+static unsigned int cell_cluster_size()
+    {
+    static int cached = -1;
+    if (cached < 0)
+        {
+        cached = 0;
+        // Measured SLOWER than the 4-kernel build as well (LJ 64k, cell list alone: 32.0 us with 16 CTAs, 44.3 us with 8,
+        // against 25.7 us; 32.9k / 31.3k vs 35.0k timesteps/s, profiles/r2x_*): 16 SMs do not issue 64k returning atomics
+        // and 1M rank loads faster than 148 SMs pay four launch gaps.  Opt-in: HOOMD_B200_CELL_CLUSTER=8 | 16.
+        const char* env = getenv("HOOMD_B200_CELL_CLUSTER");
+        if (!env || atoi(env) < 8) return 0u;
+        const int want = atoi(env) >= 16 ? 16 : 8;
+        for (int cs = want; cs >= 8 && !cached; cs /= 2)
+            {
+            if (cs > 8
+                && cudaFuncSetAttribute(k_cell_list_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+                {
+                cudaGetLastError();
+                continue;
+                }
+            cudaLaunchConfig_t cfg = {};
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned int)cs;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.gridDim = dim3((unsigned int)cs);
+            cfg.blockDim = dim3(CC_BLOCK);
+            cfg.dynamicSmemBytes = sizeof(unsigned int) * (CC_MAX_CELLS + 1);
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            int nclusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&nclusters, k_cell_list_cluster, &cfg) == cudaSuccess && nclusters > 0)
+                cached = cs;
+            else
+                cudaGetLastError();
+            }
+        }
+    return (unsigned int)cached;
+    }
+
+// single: one domain (no live particle count on the device, no ghost shifts)
+static bool cell_use_cluster(unsigned int ncells, unsigned int ntot, bool single)
+    {
+    if (!single || ntot == 0 || ncells > CC_MAX_CELLS) return false;
+    const unsigned int cs = cell_cluster_size();
+    return cs > 0 && ntot <= cs * CC_BLOCK * CC_PER;
+    }
+
 // launches per cell-list build: the multi-CTA scan (one launch more) pays off beyond a few tiles
 unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot, bool have_barrier)
     {
+    if (cell_use_cluster(ncells, ntot, have_barrier)) return 1u;
     if (cell_use_fused(ncells, ntot, have_barrier)) return 1u;
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     return (ntiles > 4 && ntiles <= ntot) ? 5u : 4u;
@@ -640,6 +821,26 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     uint3 dim = make_uint3(a->dim.x, a->dim.y, a->dim.z);
     float3 gw = make_float3(a->ghost_width[0], a->ghost_width[1], a->ghost_width[2]);
     if (!enable) cudaMemsetAsync(a->d_cell_count, 0, sizeof(unsigned int) * ncells, stream);
+    if (cell_use_cluster(ncells, ntot, !d_N && !a->d_ghost_dir))
+        {
+        const unsigned int cs = cell_cluster_size();
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = cs;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(cs);
+        cfg.blockDim = dim3(CC_BLOCK);
+        cfg.dynamicSmemBytes = sizeof(unsigned int) * (ncells + 1);
+        cfg.stream = stream;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        return cudaLaunchKernelEx(&cfg, k_cell_list_cluster, a->d_cell_count, a->d_cell_start, a->d_particle_cell,
+                                  a->d_particle_slot, a->d_scratch_idx, (float4*)a->d_cell_xyzf, a->d_cell_type,
+                                  a->d_cell_idx, a->d_conditions, (const float4*)a->d_pos, (const float*)a->d_charge, a->N,
+                                  a->n_ghost, box, dim, gw, (int)a->flag_charge, (int)a->flag_type, enable);
+        }
     const bool fused = cell_use_fused(ncells, ntot, a->d_fused_barrier != nullptr) && !a->d_ghost_dir; // (bins ghosts where they are)
     if (fused)
         {

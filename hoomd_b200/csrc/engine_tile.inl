@@ -62,9 +62,8 @@ static void tile_configure(b200_system* s)
     {
     s->tile_on = false;
     invalidate_graph(s);
-    // auto (-1) currently resolves to the CSR walk: on B200 the tile step kernel is 2x faster than the CSR one at >= 1M
-    // particles (137 vs 270 us, profiles/r1h_*), but its list build is slower than the binned CSR build and at 64k
-    // particles both are latency-bound -- see DESIGN.md section 4b for the measurements and what is left to do
+    // auto (-1) resolves to the CSR walk: measured on the current tree the tile path loses at every size (LJ 1M: step kernel
+    // 153 vs 133 us, rebuild 0.84 vs 0.59 ms; DESIGN.md section 4b, profiles/r2w_*) -- explicit opt-in only
     if (!s->have_nlist || s->pair_mode != 1) return;
     if (s->bond_kind >= 0 || s->exclusions_set)
         throw std::runtime_error("tile: the cell-tile path carries neither bonded forces nor nlist exclusions");

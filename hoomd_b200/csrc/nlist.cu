@@ -152,6 +152,16 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
 constexpr int NL_BLOCK = 128;
 constexpr int NL_CAP = 1024; // staged candidates per pass (16 kB + 4 kB types); denser neighborhoods take several passes
 
+// row[k] = v with the address formed from the row pointer held in registers (the compiler otherwise rebuilds
+// nlist + head + k from the kernel parameter with five predicated 32-bit instructions per store: 16 % of the scan loop).
+// No other access to the list in these kernels, so the store needs no ordering against the surrounding loads.
+__device__ __forceinline__ void row_store(unsigned int* row, unsigned int k, unsigned int v)
+    {
+    unsigned long long addr;
+    asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(addr) : "r"(k), "l"(__cvta_generic_to_global(row)));
+    asm volatile("st.global.u32 [%0], %1;" ::"l"(addr), "r"(v));
+    }
+
 // One warp tests every staged candidate against particle i: 2 x 32 candidates per trip, ballot + popc compaction in the
 // staged (= oracle) order.  The tile is padded to a multiple of 64 with far-away sentinels, so there is no bounds test.
 template<bool MULTI_TYPE, bool WRAP, bool HALF, int U = 2>
@@ -195,7 +205,7 @@ __device__ __forceinline__ unsigned int nlist_scan_tile(unsigned int n, const fl
             {
             const unsigned int mask = __ballot_sync(0xffffffffu, hit[u]);
             const unsigned int k = n + __popc(mask & lanemask_lt);
-            if (hit[u] && k < Nmax_i) row[k] = jj[u];
+            if (hit[u] && k < Nmax_i) row_store(row, k, jj[u]);
             n += __popc(mask);
             }
         }
@@ -290,7 +300,9 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
             if (t < cnt)
                 {
                 const unsigned int g = pass + t;
-                // adjacent cell holding staged entry g: last r with s_off[r] <= g (<= 27 ranges: 5-step bisection)
+                // adjacent cell holding staged entry g: last r with s_off[r] <= g (<= 27 ranges: 5-step bisection; a half
+                // warp per adjacent cell instead needs fewer instructions but measured 6 % SLOWER at 1M -- its loads
+                // hang on three dependent shared-memory reads and leave half the lanes idle)
                 unsigned int lo = 0, hi = nr;
                 while (hi - lo > 1)
                     {

@@ -557,8 +557,8 @@ B200_API int b200_sys_set_tuning(b200_system* s, unsigned int pair_tpp, int use_
  * hoomd/md/PotentialPairGPU.cuh:100-330).  mode 1: cell tiles -- the particles are kept in CellList order (re-ordered at
  * every list rebuild), each CTA stages its cells + one halo layer in shared memory and the list stores 16-bit tile slots
  * (DESIGN.md section 4b); needs one GPU, a periodic orthorhombic box and >= 3 cells per axis, else an error.  mode -1
- * (default): the engine's choice -- currently always mode 0 (the tile step kernel wins at >= 1M particles, its list build
- * does not yet).  bx,by,bz = cells per tile (0 = auto), tpp = lanes per particle (0 = auto, 1, 2, 4).
+ * (default): the engine's choice -- always mode 0: on the current tree the tile path is slower at every size measured
+ * (LJ 1M: 3.5k vs 4.4k timesteps/s, DESIGN.md section 4b has the captures), it is kept as an opt-in experiment.  bx,by,bz = cells per tile (0 = auto), tpp = lanes per particle (0 = auto, 1, 2, 4).
  * Same pairs, same rebuild decisions; forces differ by FP32 summation order only. */
 B200_API int b200_sys_set_pair_mode(b200_system* s, int mode, unsigned int bx, unsigned int by, unsigned int bz,
                                     unsigned int tpp);
