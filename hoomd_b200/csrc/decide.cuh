@@ -4,8 +4,9 @@
 
 namespace b200
 {
-// NeighborList::needsUpdating(ts+1) for the force evaluation that follows (update(ts) computes forces at ts+1)
-__device__ __forceinline__ void decide_body(StepState* st)
+// NeighborList::needsUpdating(ts+1) for the force evaluation that follows (update(ts) computes forces at ts+1).
+// IN_MEMORY: `st` is the device-resident block (`moved` was set by other CTAs: re-read it); otherwise a register copy.
+template<bool IN_MEMORY = true> __device__ __forceinline__ void decide_body(StepState* st)
     {
     const unsigned int ts1 = st->timestep + 1u;
     bool result;
@@ -22,7 +23,7 @@ __device__ __forceinline__ void decide_body(StepState* st)
         {
         // distance checks off: the check period decides (every == 0: always); otherwise the distance check of the step
         const bool period_hit = st->no_dist_check && (st->every == 0u || (st->every > 1u && ts1 == st->last_updated + st->every));
-        result = st->r_buff_tiny || period_hit || *((volatile unsigned int*)&st->moved);
+        result = st->r_buff_tiny || period_hit || (IN_MEMORY ? *((volatile unsigned int*)&st->moved) : st->moved);
         if (result)
             {
             st->last_updated = ts1;

@@ -1690,7 +1690,7 @@ static void sys_alloc_common(b200_system* s)
     s->vel.upload(v.data(), C, s->stream);
     CUDA_OK(cudaStreamSynchronize(s->stream));
     s->d_flag.alloc(4);
-    s->d_state.alloc(1);
+    s->d_state.alloc(STEP_STATE_ALLOC); // slot 0 + the barrier lines of k_md_steps
     s->d_req_size.alloc(1);
     s->cl_conditions.alloc(8); // {max occupancy, NaN, out of box} + pad + the two barrier words of the one-launch build
     CUDA_OK(cudaHostAlloc((void**)&s->h_flag, 4 * sizeof(unsigned int), cudaHostAllocDefault));

@@ -254,3 +254,19 @@ cudaError_t launch_tally_fold(double* acc, const float* e, unsigned int ts, cuda
     return cudaGetLastError();
     }
 } // namespace b200
+
+#ifdef B200_PERSIST_TRACE
+// debugging builds only (see md_steps_persist.cuh): copy the phase stamps out and reset the per-CTA step counters
+extern "C" __attribute__((visibility("default"))) int b200_debug_persist_trace(unsigned long long* host, unsigned int* dims)
+    {
+    using namespace b200;
+    dims[0] = PERSIST_TRACE_CTAS; dims[1] = PERSIST_TRACE_STEPS; dims[2] = PERSIST_TRACE_MARKS;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (host && e == cudaSuccess)
+        e = cudaMemcpyFromSymbol(host, g_persist_trace, sizeof(unsigned long long) * PERSIST_TRACE_CTAS * PERSIST_TRACE_STEPS
+                                                             * PERSIST_TRACE_MARKS);
+    static unsigned int zeros[PERSIST_TRACE_CTAS];
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_persist_trace_step, zeros, sizeof(zeros));
+    return (int)e;
+    }
+#endif

@@ -32,7 +32,14 @@ struct StepState
     unsigned int no_dist_check;   // NeighborList::m_dist_check off: rebuild when the check period is hit (NeighborList.cc:1126-1135)
     unsigned int box_scaled;      // the box changed since the last list build: the distance check uses row 1 of the
                                   // threshold table (lambda-scaled, NeighborList.cc:981-1007); cleared by the rebuild decision
+    unsigned long long ctl64;     // (reserved)
     };
+// The engine allocates STEP_STATE_ALLOC StepState slots: slot 0 is the state; the bytes from STEP_SYNC_OFFSET on hold the
+// barrier lines of k_md_steps (md_steps_persist.cuh): its ticket on a 128-byte line of its own and STEP_SYNC_COPIES copies of
+// the release word, one line each.
+constexpr unsigned int STEP_STATE_ALLOC = 48, STEP_SYNC_OFFSET = 1024, STEP_SYNC_COPIES = 16, STEP_SYNC_LINE = 128;
+static_assert(STEP_SYNC_OFFSET + (1 + STEP_SYNC_COPIES) * STEP_SYNC_LINE <= STEP_STATE_ALLOC * sizeof(StepState),
+              "barrier lines of k_md_steps must fit behind the step state");
 
 // d_N != NULL (multi-GPU): a->N is the ghost base (local capacity) and *d_N the live local count
 cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* enable, cudaStream_t stream,

@@ -20,6 +20,46 @@ namespace b200
 {
 constexpr unsigned int PERSIST_STOP_DONE = 1u, PERSIST_STOP_REBUILD = 2u, PERSIST_STOP_ERROR = 4u;
 
+// -DB200_PERSIST_TRACE (tools/trace_persist.py, never in the shipped library): thread 0 of every CTA stamps clock64 at the
+// phase boundaries of its first PERSIST_TRACE_STEPS steps into a device array that b200_debug_persist_trace copies out
+#ifdef B200_PERSIST_TRACE
+constexpr unsigned int PERSIST_TRACE_STEPS = 64, PERSIST_TRACE_MARKS = 8, PERSIST_TRACE_CTAS = 1536;
+__device__ unsigned long long g_persist_trace[PERSIST_TRACE_CTAS * PERSIST_TRACE_STEPS * PERSIST_TRACE_MARKS];
+__device__ unsigned int g_persist_trace_step[PERSIST_TRACE_CTAS];
+#define PERSIST_MARK(m)                                                                                                     \
+    if (threadIdx.x == 0 && blockIdx.x < PERSIST_TRACE_CTAS && g_persist_trace_step[blockIdx.x] < PERSIST_TRACE_STEPS)        \
+        g_persist_trace[(blockIdx.x * PERSIST_TRACE_STEPS + g_persist_trace_step[blockIdx.x]) * PERSIST_TRACE_MARKS + (m)]   \
+            = (unsigned long long)clock64();
+#define PERSIST_MARK_END()                                                                                                  \
+    if (threadIdx.x == 0 && blockIdx.x < PERSIST_TRACE_CTAS && g_persist_trace_step[blockIdx.x] < PERSIST_TRACE_STEPS)        \
+        {                                                                                                                   \
+        unsigned int smid;                                                                                                  \
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));                                                                   \
+        g_persist_trace[(blockIdx.x * PERSIST_TRACE_STEPS + g_persist_trace_step[blockIdx.x]) * PERSIST_TRACE_MARKS + 7]     \
+            = smid;                                                                                                         \
+        g_persist_trace_step[blockIdx.x] += 1u;                                                                             \
+        }
+#else
+#define PERSIST_MARK(m)
+#define PERSIST_MARK_END()
+#endif
+
+__device__ __forceinline__ unsigned long long* persist_ticket(StepState* st)
+    {
+    return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(st) + STEP_SYNC_OFFSET);
+    }
+__device__ __forceinline__ unsigned long long* persist_release_word(StepState* st, unsigned int copy)
+    {
+    return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(st) + STEP_SYNC_OFFSET
+                                                 + (1u + copy % STEP_SYNC_COPIES) * STEP_SYNC_LINE);
+    }
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p)
+    {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+    }
+
 // control words are read at GPU scope (a plain volatile load is system scope)
 __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p)
     {
@@ -31,14 +71,43 @@ __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p)
 // must see the positions the other CTAs just stored)
 __device__ __forceinline__ void persist_fence() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
-// thread 0: the control words of the step about to run
+// The control block of a step as the k_md_steps CTAs need it -- s_ctl[0] steps left (0, 1 = last, 2 = more), [1] ts_step_two,
+// [2] store_force | box_scaled << 1, [3] stop reasons.  At launch it is read word by word; between the steps of a launch the
+// LAST CTA of a step packs it, together with the new epoch, into ONE 8-byte release word and every CTA gets it with the very
+// load it spins on: six dependent GPU-scope loads behind the barrier were 2 us of a 17 us step (profiles/r2y_trace_*).
+// The release word is replicated over STEP_SYNC_COPIES 128-byte lines behind the step state (CTA b spins on copy b mod 16)
+// and the ticket has a line of its own: with ticket, control block and release word in one line, the late CTAs' ticket
+// atomics queued behind a thousand spinning loads at one L2 slice.
+constexpr unsigned int CTL_STORE_FORCE = 1u, CTL_BOX_SCALED = 2u, CTL_REBUILD = 4u, CTL_ERROR = 8u, CTL_DONE = 16u,
+                       CTL_LAST = 32u;
+
 __device__ __forceinline__ void persist_read_ctl(StepState* st, unsigned int* s_ctl)
     {
-    s_ctl[0] = ld_volatile_u32(&st->steps_left);
+    const unsigned int left = ld_volatile_u32(&st->steps_left);
+    s_ctl[0] = left > 2u ? 2u : left;
     s_ctl[1] = ld_volatile_u32(&st->ts_step_two);
     s_ctl[2] = (ld_volatile_u32(&st->store_force) ? 1u : 0u) | (ld_volatile_u32(&st->box_scaled) ? 2u : 0u);
     s_ctl[3] = (ld_volatile_u32(&st->need_rebuild) ? PERSIST_STOP_REBUILD : 0u)
                | ((ld_volatile_u32(&st->abort) || ld_volatile_u32(&st->nvt_error)) ? PERSIST_STOP_ERROR : 0u);
+    }
+
+// last CTA of a step, after the rebuild decision: the next step's control block + the new epoch in one word
+__device__ __forceinline__ unsigned long long persist_pack_ctl(const StepState* st, unsigned int epoch)
+    {
+    const unsigned int left = st->steps_left;
+    const unsigned int flags = (st->store_force ? CTL_STORE_FORCE : 0u) | (st->box_scaled ? CTL_BOX_SCALED : 0u)
+                               | (st->need_rebuild ? CTL_REBUILD : 0u) | ((st->abort || st->nvt_error) ? CTL_ERROR : 0u)
+                               | (left == 0u ? CTL_DONE : 0u) | (left == 1u ? CTL_LAST : 0u);
+    return ((unsigned long long)(((epoch & 0xffffffu) << 8) | flags) << 32) | st->ts_step_two;
+    }
+
+__device__ __forceinline__ void persist_unpack_ctl(unsigned long long w, unsigned int* s_ctl)
+    {
+    const unsigned int flags = (unsigned int)(w >> 32) & 0xffu;
+    s_ctl[0] = (flags & CTL_DONE) ? 0u : ((flags & CTL_LAST) ? 1u : 2u);
+    s_ctl[1] = (unsigned int)w;
+    s_ctl[2] = flags & (CTL_STORE_FORCE | CTL_BOX_SCALED);
+    s_ctl[3] = ((flags & CTL_REBUILD) ? PERSIST_STOP_REBUILD : 0u) | ((flags & CTL_ERROR) ? PERSIST_STOP_ERROR : 0u);
     }
 
 // one MD step reading buffer X = (ODD ? a.pos_out : a.pos_in), writing the other.  Returns 0 to go on, else the stop reason.
@@ -58,6 +127,7 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
     // particles per CTA: PPB unless the launcher chose a larger, SM-count-aligned grid (HOOMD_B200_PERSIST_EVEN)
     const unsigned int ppb = (N + gridDim.x - 1u) / gridDim.x;
 
+    PERSIST_MARK(0)
     // ---- phase 1 (as in k_md_step) ----
         {
         const unsigned int slot = threadIdx.x / TPP;
@@ -70,8 +140,10 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
         const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, false, false>(
             pi4, size, head, sub, pin, a.box, a.nlist, T, a.ntypes, !active || box_interior(pi4, a.box, a.wrap_skip_margin));
         if (sub == 0) s_force[slot] = make_float4(r.fx, r.fy, r.fz, r.pe);
+        if (threadIdx.x == 0) { PERSIST_MARK(1) }
         }
     __syncthreads();
+    PERSIST_MARK(2)
 
     // ---- phase 2: md_step_integrate for the plain case ----
     bool moved = false;
@@ -113,39 +185,72 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
 
     // ---- ticket + rebuild decision by the last CTA + grid-wide release ----
     const int any_moved = __syncthreads_or(moved ? 1 : 0);
+    PERSIST_MARK(3)
     if (threadIdx.x == 0)
         {
         // release: this CTA's position stores (ordered before by the barrier above) before its ticket.  A release ATOMIC, not a
         // fence: the fence would also drop the SM's L1 lines under the CTAs that are still walking their neighbor rows
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
         unsigned long long old;
-        asm volatile("atom.release.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(&st->ticket), "l"(inc) : "memory");
+        asm volatile("atom.release.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(persist_ticket(st)), "l"(inc) : "memory");
+        PERSIST_MARK(4)
         if ((unsigned int)old == gridDim.x - 1u)
             {
-            if ((old + inc) >> 32) st->moved = 1u;
-            st->ticket = 0ull;
-            st->steps_left = steps_left - 1u;
+            // The LAST CTA takes the rebuild decision on a register copy of the control block (six independent 16-byte loads,
+            // one round trip) instead of walking it with a dozen dependent loads while 999 CTAs spin: that serial section was
+            // 4.7 us of a 17 us step (profiles/r2y_trace_*).  Nobody else writes the block while a launch runs.
+            StepState loc;
+            uint4* lq = reinterpret_cast<uint4*>(&loc);
+            static_assert(sizeof(StepState) == 96, "StepState is copied as six 16-byte words");
+#pragma unroll
+            for (int q = 0; q < 6; q++)
+                asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(lq[q].x), "=r"(lq[q].y), "=r"(lq[q].z), "=r"(lq[q].w)
+                             : "l"(reinterpret_cast<const uint4*>(st) + q)
+                             : "memory");
+            loc.moved = ((old + inc) >> 32) ? 1u : 0u;
+            loc.steps_left -= 1u;
             if (!last)
-                decide_body(st);
+                decide_body<false>(&loc);
             else
                 {
-                st->need_rebuild = 0u;
-                st->moved = 0u;
+                loc.need_rebuild = 0u;
+                loc.moved = 0u;
                 }
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&st->epoch), "r"(epoch + 1u) : "memory");
+            loc.epoch = epoch + 1u;
+            const unsigned long long w = persist_pack_ctl(&loc, epoch + 1u);
+            uint4* gq = reinterpret_cast<uint4*>(st);
+            gq[0] = lq[0]; // timestep, ts_step_two, moved, need_rebuild
+            gq[1] = lq[1]; // force_update, last_updated, every, r_buff_tiny
+            gq[2] = lq[2]; // num_updates, num_forced, overflow, ntypes
+            gq[3] = lq[3]; // steps_left, epoch, (the one-step kernel's ticket: untouched, zero)
+            st->box_scaled = loc.box_scaled;
+            *persist_ticket(st) = 0ull;
+            persist_fence(); // release: the block and the ticket reset before any copy of the release word
+#pragma unroll
+            for (unsigned int c = 0; c < STEP_SYNC_COPIES; c++)
+                asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(persist_release_word(st, c)), "l"(w) : "memory");
             }
         unsigned int spins = 0;
         bool lost = false;
-        while (ld_volatile_u32(&st->epoch) != epoch + 1u)
+        unsigned long long w;
+        const unsigned int want = (epoch + 1u) & 0xffffffu;
+        const unsigned long long* word = persist_release_word(st, blockIdx.x);
+        while (true)
             {
+            w = ld_relaxed_u64(word);
+            if ((unsigned int)(w >> 40) == want) break;
             if (++spins > (1u << 22)) // seconds: a CTA of this grid never arrived
                 {
                 lost = true;
                 break;
                 }
             }
+        PERSIST_MARK(5)
         persist_fence(); // acquire: the other CTAs' position stores of this step are visible to this SM from here on
-        persist_read_ctl(st, s_ctl);
+        persist_unpack_ctl(w, s_ctl);
+        PERSIST_MARK(6)
+        PERSIST_MARK_END()
         if (lost)
             {
             st->nvt_error = 3u;
@@ -172,7 +277,8 @@ __global__ void __launch_bounds__(MD_BLOCK, 1280 / MD_BLOCK) k_md_steps(const __
     if (threadIdx.x == 0)
         {
         persist_read_ctl(st, s_ctl);
-        s_epoch = ld_volatile_u32(&st->epoch);
+        // the epoch counts on from what the copies of the release word hold (all equal between launches)
+        s_epoch = (unsigned int)(ld_relaxed_u64(persist_release_word(st, blockIdx.x)) >> 40);
         }
     __syncthreads();
     // grid-uniform: the control block only changes after EVERY CTA has taken its first ticket
