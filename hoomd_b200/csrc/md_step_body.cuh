@@ -271,22 +271,44 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
         const unsigned long long old = atomicAdd(&st->ticket, inc);
         const bool is_last = (unsigned int)old == gridDim.x * gridDim.y * gridDim.z - 1;
         s_is_last = is_last ? 1 : 0;
-        if (is_last)
+        if (is_last && !(EXTRAS && a.mg))
+            {
+            // One GPU: the rebuild decision on a register copy of the control block (four independent 16-byte loads, one round
+            // trip, then four stores) instead of a dozen dependent loads at the tail of every launch; nobody else touches
+            // the block once every CTA has taken its ticket.  Same decision, same fields written.
+            StepState loc;
+            uint4* lq = reinterpret_cast<uint4*>(&loc);
+            const uint4* gq = reinterpret_cast<const uint4*>(st);
+#pragma unroll
+            for (int q = 0; q < 6; q++) lq[q] = __ldcg(gq + q);
+            loc.moved = ((old + inc) >> 32) ? 1u : 0u;
+            loc.ticket = 0ull;
+            loc.steps_left = steps_left - 1u;
+            if (!last)
+                decide_body<false>(&loc);
+            else
+                {
+                loc.need_rebuild = 0u;
+                loc.moved = 0u;
+                }
+            uint4* wq = reinterpret_cast<uint4*>(st);
+            wq[0] = lq[0]; // timestep, ts_step_two, moved, need_rebuild
+            wq[1] = lq[1]; // force_update, last_updated, every, r_buff_tiny
+            wq[2] = lq[2]; // num_updates, num_forced, overflow, ntypes
+            wq[3] = lq[3]; // steps_left, epoch, ticket
+            st->box_scaled = loc.box_scaled;
+#if (CUDART_VERSION >= 12040)
+            if (a.use_cond) cudaGraphSetConditional(a.handle, loc.need_rebuild);
+#endif
+            }
+        else if (is_last)
             {
             if ((old + inc) >> 32) st->moved = 1u;
             st->ticket = 0ull;
             st->steps_left = steps_left - 1u;
-            if (EXTRAS && a.mg)
-                ; // the vote needs every rank: the step barrier decides (below, or k_mg_step_barrier)
-            else if (!last)
-                decide_body(st);
-            else
-                {
-                st->need_rebuild = 0u;
-                st->moved = 0u;
-                }
+            // the vote needs every rank: the step barrier decides (below, or k_mg_step_barrier)
 #if (CUDART_VERSION >= 12040)
-            if (a.use_cond && !(EXTRAS && a.mg == 2)) cudaGraphSetConditional(a.handle, st->need_rebuild);
+            if (a.use_cond && a.mg != 2) cudaGraphSetConditional(a.handle, st->need_rebuild);
 #endif
             }
         }

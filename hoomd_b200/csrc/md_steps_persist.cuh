@@ -110,11 +110,85 @@ __device__ __forceinline__ void persist_unpack_ctl(unsigned long long w, unsigne
     s_ctl[3] = ((flags & CTL_REBUILD) ? PERSIST_STOP_REBUILD : 0u) | ((flags & CTL_ERROR) ? PERSIST_STOP_ERROR : 0u);
     }
 
+// What a CTA keeps on chip (registers for the walker role, shared memory for the integrator role) from one step of a launch
+// to the next.  Nothing else writes these while the launch runs:
+// the neighbor list (row length, row start, this lane's first chunk of indices) and last_pos change only in the rebuild
+// bracket between launches, and position / velocity / image of particle i are written by the thread that integrates i.
+// With them a step starts its position gathers at once and its integration needs no global load at all: the dependent
+// loads they replace were ~1.5 us of every CTA's 8 us of work per step (after each barrier the SM's L1 is empty, so every
+// one of them was an L2 round trip).  Arithmetic and its order are unchanged: bit-identical trajectories.
+struct PersistRegs // walker role: lane `sub` of particle slot threadIdx.x / TPP
+    {
+    unsigned int size, head;
+    uint4 first;
+    };
+template<int PPB> struct PersistShared // integrator role: particle threadIdx.x of the CTA (shared memory: 68 B per particle)
+    {
+    float4 pos[PPB]; // also what the walkers of the next step read for their own particle
+    float4 vel[PPB];
+    float4 lp[PPB];  // last_pos.xyz, w = this particle's (type's) squared distance-check threshold
+    int4 img[PPB];   // image.xyz, w = tag (Langevin)
+    float gamma[PPB];
+    float lam[3];            // lambda of the distance check (1 unless the box changed since the build) ...
+    unsigned int row_scaled; // ... taken from the scaled (1) or the plain (0) row of the table
+    };
+
+template<class Evaluator, int PPB>
+__device__ __forceinline__ void persist_load_check_row(const MdStepArgs<Evaluator>& a, PersistShared<PPB>& S, bool box_scaled,
+                                                       bool mine)
+    {
+    const float* tab = a.maxsq + (box_scaled ? a.ntypes + 3u : 0u);
+    if (mine) S.lp[threadIdx.x].w = tab[(unsigned int)__float_as_int(S.pos[threadIdx.x].w)];
+    if (threadIdx.x < 3) S.lam[threadIdx.x] = tab[a.ntypes + threadIdx.x];
+    if (threadIdx.x == 3) S.row_scaled = box_scaled ? 1u : 0u;
+    }
+
+template<class Evaluator, int TPP>
+__device__ __forceinline__ void persist_init(const MdStepArgs<Evaluator>& a, PersistRegs& R,
+                                             PersistShared<MD_BLOCK / TPP>& S, unsigned int ppb, bool box_scaled)
+    {
+    const unsigned int N = a.N;
+        {
+        const unsigned int slot = threadIdx.x / TPP, sub = threadIdx.x % TPP;
+        const unsigned int i = blockIdx.x * ppb + slot;
+        const bool active = slot < ppb && i < N;
+        R.size = active ? a.n_neigh[i] : 0u;
+        R.head = !active ? 0u : (a.nmax_uniform ? i * a.nmax_uniform : a.head_list[i]);
+        R.first = make_uint4(0u, 0u, 0u, 0u);
+        const bool aligned = (R.head & 3u) == 0u && (reinterpret_cast<unsigned long long>(a.nlist) & 15ull) == 0ull;
+        if (active && aligned && sub < ((R.size + 3u) >> 2))
+            R.first = ld_index4(reinterpret_cast<const uint4*>(a.nlist + R.head) + sub);
+        }
+    const unsigned int i = blockIdx.x * ppb + threadIdx.x;
+    const bool mine = threadIdx.x < ppb && i < N;
+    if (mine)
+        {
+        const float4 p = a.pos_in[i];
+        S.pos[threadIdx.x] = p;
+        S.vel[threadIdx.x] = a.vel[i];
+        const int3 im = a.image[i];
+        const float4 lp = a.last_pos[i];
+        S.lp[threadIdx.x] = make_float4(lp.x, lp.y, lp.z, 0.0f);
+        unsigned int tag = 0u;
+        float gamma = 0.0f;
+        if (a.method != 1)
+            {
+            tag = a.tag[i];
+            gamma = a.gamma[(unsigned int)__float_as_int(p.w)];
+            }
+        S.img[threadIdx.x] = make_int4(im.x, im.y, im.z, (int)tag);
+        S.gamma[threadIdx.x] = gamma;
+        }
+    persist_load_check_row(a, S, box_scaled, mine);
+    __syncthreads();
+    }
+
 // one MD step reading buffer X = (ODD ? a.pos_out : a.pos_in), writing the other.  Returns 0 to go on, else the stop reason.
 template<class Evaluator, int TPP, int SHIFT_MODE, bool ODD>
 __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluator>& a, StepState* st,
                                                         const PairTables<Evaluator>& T, float4* s_force,
-                                                        unsigned int* s_ctl, unsigned int& epoch)
+                                                        PersistShared<MD_BLOCK / TPP>& S, unsigned int* s_ctl,
+                                                        unsigned int& epoch, PersistRegs& R)
     {
     constexpr int PPB = MD_BLOCK / TPP;
     const float4* pin = ODD ? a.pos_out : a.pos_in;
@@ -127,6 +201,12 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
     // particles per CTA: PPB unless the launcher chose a larger, SM-count-aligned grid (HOOMD_B200_PERSIST_EVEN)
     const unsigned int ppb = (N + gridDim.x - 1u) / gridDim.x;
 
+    if ((S.row_scaled != 0u) != box_scaled) // (never inside a launch today: the flag only falls with a rebuild decision)
+        {
+        __syncthreads();
+        persist_load_check_row(a, S, box_scaled, threadIdx.x < ppb && blockIdx.x * ppb + threadIdx.x < N);
+        __syncthreads();
+        }
     PERSIST_MARK(0)
     // ---- phase 1 (as in k_md_step) ----
         {
@@ -134,11 +214,10 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
         const unsigned int i = blockIdx.x * ppb + slot;
         const unsigned int sub = threadIdx.x % TPP;
         const bool active = slot < ppb && i < N;
-        const float4 pi4 = active ? pin[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        const unsigned int size = active ? a.n_neigh[i] : 0u;
-        const unsigned int head = !active ? 0u : (a.nmax_uniform ? i * a.nmax_uniform : a.head_list[i]);
+        const float4 pi4 = active ? S.pos[slot] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         const PairAccum r = pair_accumulate<Evaluator, TPP, SHIFT_MODE, false, false>(
-            pi4, size, head, sub, pin, a.box, a.nlist, T, a.ntypes, !active || box_interior(pi4, a.box, a.wrap_skip_margin));
+            pi4, R.size, R.head, sub, pin, a.box, a.nlist, T, a.ntypes,
+            !active || box_interior(pi4, a.box, a.wrap_skip_margin), &R.first);
         if (sub == 0) s_force[slot] = make_float4(r.fx, r.fy, r.fz, r.pe);
         if (threadIdx.x == 0) { PERSIST_MARK(1) }
         }
@@ -151,36 +230,37 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
     if (threadIdx.x < ppb && i < N)
         {
         const float4 F = s_force[threadIdx.x];
-        const float4 pi4 = pin[i];
-        float4 v = a.vel[i];
+        const float4 pi4 = S.pos[threadIdx.x];
+        float4 v = S.vel[threadIdx.x];
         if (store_force) a.net_force[i] = F;
-        const unsigned int type_i = (unsigned int)__float_as_int(pi4.w);
         const bool nve = a.method == 1;
         float3s acc;
         if (nve)
             nve_step_two_body(v, acc, F, a.dt, a.limit != 0, a.limit_val, a.zero_force != 0);
         else
-            langevin_step_two_body(v, acc, F, a.tag[i], ts2, a.seed, a.gamma[type_i], a.kT, a.dt, a.noiseless_t != 0, 3u);
+            langevin_step_two_body(v, acc, F, (unsigned int)S.img[threadIdx.x].w, ts2, a.seed, S.gamma[threadIdx.x], a.kT, a.dt,
+                                   a.noiseless_t != 0, 3u);
         a.accel[i] = acc;
         if (!last)
             {
             float4 p = pi4;
-            int3 img = a.image[i];
-            const float4 lp = a.last_pos[i];
+            const int4 im4 = S.img[threadIdx.x];
+            int3 img = make_int3(im4.x, im4.y, im4.z);
             nve_step_one_body(p, v, acc, img, a.box, a.dt, nve && a.limit, a.limit_val);
             pout[i] = p;
             a.image[i] = img;
-            const float* tab = a.maxsq + (box_scaled ? a.ntypes + 3u : 0u);
-            const float maxsq = tab[type_i];
-            float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(tab[a.ntypes], lp.x)),
-                                    __fsub_rn(p.y, __fmul_rn(tab[a.ntypes + 1u], lp.y)),
-                                    __fsub_rn(p.z, __fmul_rn(tab[a.ntypes + 2u], lp.z)));
+            S.pos[threadIdx.x] = p; // this thread's next step, and the next step's walkers of this CTA (behind the barrier)
+            S.img[threadIdx.x] = make_int4(img.x, img.y, img.z, im4.w);
+            const float4 lp = S.lp[threadIdx.x];
+            float3 dx = make_float3(__fsub_rn(p.x, __fmul_rn(S.lam[0], lp.x)), __fsub_rn(p.y, __fmul_rn(S.lam[1], lp.y)),
+                                    __fsub_rn(p.z, __fmul_rn(S.lam[2], lp.z)));
             dx = min_image_exact_sel(dx, a.box, a.box.periodic.x, a.box.periodic.y, a.box.periodic.z);
-            moved = dot_exact(dx) >= maxsq;
+            moved = dot_exact(dx) >= lp.w;
             }
         else if (ODD)
             pout[i] = pi4; // the chunk's final positions must be in buffer A
         a.vel[i] = v;
+        S.vel[threadIdx.x] = v;
         }
 
     // ---- ticket + rebuild decision by the last CTA + grid-wide release ----
@@ -266,11 +346,12 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
     }
 
 template<class Evaluator, int TPP, int SHIFT_MODE>
-__global__ void __launch_bounds__(MD_BLOCK, 1280 / MD_BLOCK) k_md_steps(const __grid_constant__ MdStepArgs<Evaluator> a)
+__global__ void __launch_bounds__(MD_BLOCK, 7) k_md_steps(const __grid_constant__ MdStepArgs<Evaluator> a)
     {
     constexpr int PPB = MD_BLOCK / TPP;
     extern __shared__ unsigned char smem_raw[];
     __shared__ float4 s_force[PPB];
+    __shared__ PersistShared<PPB> S;
     __shared__ unsigned int s_ctl[4];
     __shared__ unsigned int s_epoch;
     StepState* st = a.st;
@@ -286,20 +367,22 @@ __global__ void __launch_bounds__(MD_BLOCK, 1280 / MD_BLOCK) k_md_steps(const __
     unsigned int epoch = s_epoch;
     PairTables<Evaluator> T;
     pair_tables_load<Evaluator, SHIFT_MODE, false>(T, smem_raw, a.params, a.rcutsq, a.ronsq, a.ntypes);
+    PersistRegs R;
+    persist_init<Evaluator, TPP>(a, R, S, (a.N + gridDim.x - 1u) / gridDim.x, (s_ctl[2] & 2u) != 0u);
     while (true)
         {
         const bool was_last = s_ctl[0] == 1u;
-        unsigned int stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, false>(a, st, T, s_force, s_ctl, epoch);
+        unsigned int stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, false>(a, st, T, s_force, S, s_ctl, epoch, R);
         if (stop)
             {
             // stopped after an A -> B step that moved the particles: put this CTA's particles back into A (every CTA's reads of
             // A for that step are behind the barrier)
             const unsigned int ppb = (a.N + gridDim.x - 1u) / gridDim.x;
             const unsigned int i = blockIdx.x * ppb + threadIdx.x;
-            if (!was_last && threadIdx.x < ppb && i < a.N) const_cast<float4*>(a.pos_in)[i] = a.pos_out[i];
+            if (!was_last && threadIdx.x < ppb && i < a.N) const_cast<float4*>(a.pos_in)[i] = S.pos[threadIdx.x];
             break;
             }
-        stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, true>(a, st, T, s_force, s_ctl, epoch);
+        stop = md_persist_step<Evaluator, TPP, SHIFT_MODE, true>(a, st, T, s_force, S, s_ctl, epoch, R);
         if (stop) break;
         }
 #if (CUDART_VERSION >= 12040)
