@@ -274,7 +274,8 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
         unsigned long long old;
         asm volatile("atom.release.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(persist_ticket(st)), "l"(inc) : "memory");
         PERSIST_MARK(4)
-        if ((unsigned int)old == gridDim.x - 1u)
+        const bool last_cta = (unsigned int)old == gridDim.x - 1u;
+        if (last_cta)
             {
             // The LAST CTA takes the rebuild decision on a register copy of the control block (six independent 16-byte loads,
             // one round trip) instead of walking it with a dozen dependent loads while 999 CTAs spin: that serial section was
@@ -311,6 +312,8 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
             for (unsigned int c = 0; c < STEP_SYNC_COPIES; c++)
                 asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(persist_release_word(st, c)), "l"(w) : "memory");
             }
+        else if (!a.persist_strict)
+            persist_fence(); // (experiment) the acquire side's L1 invalidation taken during the wait, see below
         unsigned int spins = 0;
         bool lost = false;
         unsigned long long w;
@@ -327,7 +330,14 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
                 }
             }
         PERSIST_MARK(5)
-        persist_fence(); // acquire: the other CTAs' position stores of this step are visible to this SM from here on
+        // acquire: the other CTAs' position stores of this step are visible to this SM from here on.
+        // HOOMD_B200_PERSIST_EARLY_FENCE=1 (experiment, off) takes this fence BEFORE the spin instead: the positions are double
+        // buffered, during a step the SM's CTAs read buffer X only, L1 is filled by demand loads alone and stores do not
+        // allocate, so the only stale sectors of the buffer read next are those of the step before, and every CTA's fence
+        // behind its own last read drops them -- the MEMBAR + CCTL.IVALL then runs while the CTA would spin anyway.  Same
+        // bits in every test, but it leans on how the hardware fills L1 rather than on the PTX memory model (which wants the
+        // fence behind the observing load), and it measured only 13.18 vs 13.38 us per step (profiles/r2y_*): not the default.
+        if (a.persist_strict) persist_fence();
         persist_unpack_ctl(w, s_ctl);
         PERSIST_MARK(6)
         PERSIST_MARK_END()
@@ -456,6 +466,8 @@ static cudaError_t launch_md_steps_t(const b200_pair_args& pa, const void* d_par
         return cudaErrorNotSupported;
     MdStepArgs<Evaluator> a;
     fill_md_step_args(a, pa, (const float*)d_params, fa, pos_a, pos_b, 0, st, next_handle, use_cond);
+    static const bool early = getenv("HOOMD_B200_PERSIST_EARLY_FENCE") && atoi(getenv("HOOMD_B200_PERSIST_EARLY_FENCE")) != 0;
+    a.persist_strict = early ? 0 : 1;
     const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);
     const bool shift = pa.shift_mode == B200_SHIFT_SHIFT;
     switch (tpp)

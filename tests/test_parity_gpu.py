@@ -460,7 +460,7 @@ def test_full_size_ka256k_properties(hb):
     assert g.stats()["updates"] > 0
 
 
-@pytest.mark.parametrize("n_side,method", [(24, "nve"), (30, "langevin"), (38, "nve")])
+@pytest.mark.parametrize("n_side,method", [(24, "nve"), (30, "langevin"), (38, "nve"), (40, "langevin")])
 def test_multistep_kernel_bit_identical_to_one_step_kernel(hb, n_side, method):
     """k_md_steps (several MD steps per launch, grid-wide barrier instead of a kernel boundary; 8 / 4 / 2 lanes per particle
     at these sizes) against the one-step kernel in the same conditional graph: identical bits after 260 steps with list

@@ -13,3 +13,9 @@ import json
 d=json.loads(open("gpurun_out/tr_bench_lj64k.json").read().strip().splitlines()[-1]); r=d["roofline"]
 print("lj64k TPS %.1f e2e %.1f kernel %.5f rebuild %.5f" % (d["value"], d["e2e"]["value"], r["kernel_ms"], r["nlist_rebuild_ms"]), d["e2e"]["ms_runs"])
 PY
+HOOMD_B200_PERSIST_EARLY_FENCE=1 timeout 600 python bench.py --no-scale-ref --no-cpu-baseline > gpurun_out/tr_bench_lj64k_earlyfence.json 2> gpurun_out/tr_bench_lj64k_earlyfence.err; echo "64k early-fence rc=$?"
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/tr_bench_lj64k_earlyfence.json").read().strip().splitlines()[-1]); r=d["roofline"]
+print("lj64k EARLY-FENCE TPS %.1f e2e %.1f kernel %.5f rebuild %.5f" % (d["value"], d["e2e"]["value"], r["kernel_ms"], r["nlist_rebuild_ms"]))
+PY
