@@ -249,6 +249,99 @@ __global__ void __launch_bounds__(256) k_cell_scatter(unsigned int* __restrict__
     scratch_idx[cell_start[cell] + particle_slot[n]] = n;
     }
 
+// ---- K2 + K3 in one launch for small grids -------------------------------------------------------------------------------------
+// At 64k particles (8000 cells) the single-CTA scan runs 3 us and costs one more dependent launch inside the rebuild body.
+// Here EVERY scatter CTA scans all occupancies itself (ncells <= SS_MAX_CELLS: <= 32 kB of L2-resident counts per CTA, one
+// 512-thread block scan, result in shared memory) and scatters its particles from that; CTA 0 also publishes cell_start and
+// the largest occupancy.  The counts cannot be cleaned here (other CTAs still read them): k_cell_rank does it.
+constexpr unsigned int SS_BLOCK = 512, SS_CELLS_PER = 16, SS_MAX_CELLS = SS_BLOCK * SS_CELLS_PER; // 8192 cells: 64k particles at rho 0.2
+
+__global__ void __launch_bounds__(SS_BLOCK) k_cell_scan_scatter(unsigned int* __restrict__ cell_start,
+                                                                const unsigned int* __restrict__ cell_count,
+                                                                unsigned int ncells, unsigned int* __restrict__ conditions,
+                                                                unsigned int* __restrict__ scratch_idx,
+                                                                const unsigned int* __restrict__ particle_cell,
+                                                                const unsigned int* __restrict__ particle_slot,
+                                                                unsigned int ntot, const unsigned int* __restrict__ enable)
+    {
+    pdl_wait();
+    pdl_trigger();
+    if (enable && !*enable) return;
+    __shared__ unsigned int s_start[SS_MAX_CELLS + 1];
+    __shared__ unsigned int warp_sums[SS_BLOCK / 32 + 1];
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // this thread's particle: requested before the scan so that the loads overlap it
+    const unsigned int n = blockIdx.x * SS_BLOCK + threadIdx.x;
+    unsigned int cell = B200_NOT_BINNED, slot = 0;
+    if (n < ntot)
+        {
+        cell = particle_cell[n];
+        slot = particle_slot[n];
+        }
+    const unsigned int i0 = threadIdx.x * SS_CELLS_PER;
+    unsigned int c[SS_CELLS_PER];
+    unsigned int tsum = 0, max_occ = 0;
+#pragma unroll
+    for (unsigned int k = 0; k < SS_CELLS_PER; k += 4)
+        {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (i0 + k + 3 < ncells)
+            v = *reinterpret_cast<const uint4*>(cell_count + i0 + k); // cudaMalloc base + multiple of 16 B
+        else
+            {
+            if (i0 + k < ncells) v.x = cell_count[i0 + k];
+            if (i0 + k + 1 < ncells) v.y = cell_count[i0 + k + 1];
+            if (i0 + k + 2 < ncells) v.z = cell_count[i0 + k + 2];
+            }
+        c[k] = v.x; c[k + 1] = v.y; c[k + 2] = v.z; c[k + 3] = v.w;
+        tsum += v.x + v.y + v.z + v.w;
+        max_occ = max(max(max_occ, max(v.x, v.y)), max(v.z, v.w));
+        }
+    unsigned int incl = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+        }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0)
+        {
+        const unsigned int w = lane < SS_BLOCK / 32 ? warp_sums[lane] : 0u;
+        unsigned int wi = w;
+#pragma unroll
+        for (int o = 1; o < SS_BLOCK / 32; o <<= 1)
+            {
+            const unsigned int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+            }
+        if (lane < SS_BLOCK / 32) warp_sums[lane] = wi - w; // exclusive
+        if (lane == SS_BLOCK / 32 - 1) warp_sums[SS_BLOCK / 32] = wi;
+        }
+    __syncthreads();
+    unsigned int excl = warp_sums[warp] + incl - tsum;
+    const bool publish = blockIdx.x == 0;
+#pragma unroll
+    for (unsigned int k = 0; k < SS_CELLS_PER; k++)
+        {
+        if (i0 + k < ncells)
+            {
+            s_start[i0 + k] = excl;
+            if (publish) cell_start[i0 + k] = excl;
+            }
+        excl += c[k];
+        }
+    if (publish)
+        {
+        if (threadIdx.x == 0) cell_start[ncells] = warp_sums[SS_BLOCK / 32];
+        for (int o = 16; o > 0; o >>= 1) max_occ = max(max_occ, __shfl_xor_sync(0xffffffffu, max_occ, o));
+        if (lane == 0 && max_occ) atomicMax(&conditions[0], max_occ);
+        }
+    __syncthreads();
+    if (cell != B200_NOT_BINNED) scratch_idx[s_start[cell] + slot] = n;
+    }
+
 // ---- K4: rank every entry inside its cell by particle index and emit the final cell-sorted arrays -------------------
 // 1 thread / entry.  A cell holds ~8 (rho=0.2) .. ~30 (rho=1.2) entries, so the rank loop is a handful of L1-resident
 // 4 B loads; output writes are 16 B and land inside one contiguous cell range.
@@ -259,12 +352,16 @@ __global__ void __launch_bounds__(256) k_cell_rank(float4* __restrict__ cell_xyz
                                                    const unsigned int* __restrict__ particle_cell,
                                                    const float4* __restrict__ pos, const float* __restrict__ charge,
                                                    unsigned int ncells, int flag_charge, int flag_type,
-                                                   const unsigned int* __restrict__ enable)
+                                                   const unsigned int* __restrict__ enable,
+                                                   unsigned int* __restrict__ clean_counts = nullptr)
     {
     pdl_wait();
     pdl_trigger();
     if (enable && !*enable) return;
     unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
+    // after k_cell_scan_scatter (which cannot clean the counts it shares between its CTAs): leave zeros for the next build
+    if (clean_counts)
+        for (unsigned int c = e; c < ncells; c += gridDim.x * blockDim.x) clean_counts[c] = 0u;
     unsigned int nbinned = cell_start[ncells];
     if (e >= nbinned) return;
     unsigned int n = scratch_idx[e];
@@ -800,11 +897,20 @@ static bool cell_use_cluster(unsigned int ncells, unsigned int ntot, bool single
     return cs > 0 && ntot <= cs * CC_BLOCK * CC_PER;
     }
 
+// scan folded into the scatter launch: small grids with enough particles to make the extra launch the larger cost
+static bool cell_use_scan_scatter(unsigned int ncells, unsigned int ntot)
+    {
+    static const char* env = getenv("HOOMD_B200_CELL_SCANSCATTER");
+    static const bool on = env ? atoi(env) != 0 : true;
+    return on && ntot > 0 && ncells <= SS_MAX_CELLS && ntot <= 262144u;
+    }
+
 // launches per cell-list build: the multi-CTA scan (one launch more) pays off beyond a few tiles
 unsigned int cell_list_kernels(unsigned int ncells, unsigned int ntot, bool have_barrier)
     {
     if (cell_use_cluster(ncells, ntot, have_barrier)) return 1u;
     if (cell_use_fused(ncells, ntot, have_barrier)) return 1u;
+    if (cell_use_scan_scatter(ncells, ntot)) return 3u;
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     return (ntiles > 4 && ntiles <= ntot) ? 5u : 4u;
     }
@@ -863,7 +969,12 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
     const unsigned int ntiles = (ncells + SCAN_TILE - 1) / SCAN_TILE;
     // device-driven rebuild: the dependent kernels are scheduled behind their predecessor (see launch_chain)
     const bool pdl = enable && pdl_enabled();
-    if (cell_list_kernels(ncells, ntot, false) == 5)
+    const bool scan_scatter = cell_use_scan_scatter(ncells, ntot);
+    if (scan_scatter)
+        launch_chain(k_cell_scan_scatter, dim3((ntot + SS_BLOCK - 1) / SS_BLOCK), dim3(SS_BLOCK), 0, stream, pdl,
+                     a->d_cell_start, (const unsigned int*)a->d_cell_count, ncells, a->d_conditions, a->d_scratch_idx,
+                     (const unsigned int*)a->d_particle_cell, (const unsigned int*)a->d_particle_slot, ntot, enable);
+    else if (cell_list_kernels(ncells, ntot, false) == 5)
         {
         // tile totals live in d_scratch_idx, which is not needed before k_cell_scatter
         launch_chain(k_cell_scan_tiles, dim3(ntiles), dim3(1024), 0, stream, pdl, a->d_cell_start, a->d_cell_count, ncells,
@@ -876,11 +987,13 @@ cudaError_t launch_cell_list(const b200_cell_list_args* a, const unsigned int* e
                      a->d_conditions, enable);
     if (ntot)
         {
-        launch_chain(k_cell_scatter, dim3((ntot + 255) / 256), dim3(256), 0, stream, pdl, a->d_scratch_idx,
-                     a->d_cell_start, a->d_particle_cell, a->d_particle_slot, ntot, enable);
+        if (!scan_scatter)
+            launch_chain(k_cell_scatter, dim3((ntot + 255) / 256), dim3(256), 0, stream, pdl, a->d_scratch_idx,
+                         a->d_cell_start, a->d_particle_cell, a->d_particle_slot, ntot, enable);
         launch_chain(k_cell_rank, dim3((ntot + 255) / 256), dim3(256), 0, stream, pdl, (float4*)a->d_cell_xyzf,
                      a->d_cell_type, a->d_cell_idx, a->d_scratch_idx, a->d_cell_start, a->d_particle_cell,
-                     (const float4*)a->d_pos, a->d_charge, ncells, a->flag_charge, a->flag_type, enable);
+                     (const float4*)a->d_pos, a->d_charge, ncells, a->flag_charge, a->flag_type, enable,
+                     scan_scatter ? a->d_cell_count : (unsigned int*)nullptr);
         }
     return cudaGetLastError();
     }

@@ -35,6 +35,25 @@ __device__ __forceinline__ int axis_set(int c, int m, bool periodic, int out[3])
     return n;
     }
 
+// the same set in registers (no local array, no insertion loop): c and its wrapped / clipped neighbors, duplicates dropped
+// (dim 1 or 2), ascending, absent entries at the end
+__device__ __forceinline__ int axis_set3(int c, int m, bool periodic, int& o0, int& o1, int& o2)
+    {
+    constexpr int ABSENT = 0x3fffffff;
+    int lo = c - 1, hi = c + 1;
+    bool vlo = true, vhi = true;
+    if (lo < 0) { vlo = periodic; lo += m; }
+    if (hi >= m) { vhi = periodic; hi -= m; }
+    if (lo == c) vlo = false;                // m == 1
+    if (hi == c || (vlo && hi == lo)) vhi = false; // m == 1, m == 2
+    const int a = vlo ? lo : ABSENT, b = vhi ? hi : ABSENT;
+    const int mn = min(min(a, b), c), mx = max(max(a, b), c);
+    o0 = mn;
+    o2 = mx;
+    o1 = a + b + c - mn - mx; // < 2^31: at most two ABSENT terms
+    return 1 + (vlo ? 1 : 0) + (vhi ? 1 : 0);
+    }
+
 // on overflow the true count goes to `conditions` (the host grows Nmax and rebuilds, NeighborList.cc:226-244)
 __device__ __forceinline__ void nlist_report_overflow(unsigned int* conditions, unsigned int type_i, unsigned int n,
                                                       const OverflowHook& hook)
@@ -149,7 +168,10 @@ __global__ void __launch_bounds__(128) k_nlist_binned(unsigned int* __restrict__
 // cell's particles round-robin, each lane striding the staged tile: 32 candidates per ballot, popc compaction.
 // Per particle this moves 27*occ*16/occ = 432 B through L2 instead of 27*occ*16 = 3.5 kB (rho = 0.2), and removes the
 // per-particle dependent cell_start -> xyzf chain.  Membership arithmetic is unchanged (bit-exact vs the oracle).
-constexpr int NL_BLOCK = 128;
+#ifndef B200_NL_BLOCK
+#define B200_NL_BLOCK 128
+#endif
+constexpr int NL_BLOCK = B200_NL_BLOCK; // threads per cell (A/B: -DB200_NL_BLOCK=256)
 constexpr int NL_CAP = 1024; // staged candidates per pass (16 kB + 4 kB types); denser neighborhoods take several passes
 
 // row[k] = v with the address formed from the row pointer held in registers (the compiler otherwise rebuilds
@@ -242,6 +264,8 @@ __global__ void __launch_bounds__(NL_BLOCK) k_nlist_tiled(unsigned int* __restri
 
     if (warp == 0)
         {
+        // (the register-only axis_set3 of the warp-per-cell kernel measured 1-2 us SLOWER here at 64k: 44 registers, or 40 with
+        // spills, against 40 with this 40-byte stack frame)
         int xs[3], ys[3], zs[3];
         const int nx = axis_set(bx, dim.x, box.periodic.x, xs);
         const int ny = axis_set(by, dim.y, box.periodic.y, ys);
@@ -408,19 +432,19 @@ __global__ void __launch_bounds__(NW_WARPS * 32) k_nlist_warpcell(unsigned int* 
     if (own_beg == own_end) return;
     const unsigned int bx = cell % dim.x, by = (cell / dim.x) % dim.y, bz = cell / (dim.x * dim.y);
 
-    int xs[3], ys[3], zs[3];
-    const int nx = axis_set(bx, dim.x, box.periodic.x, xs);
-    const int ny = axis_set(by, dim.y, box.periodic.y, ys);
-    const int nz = axis_set(bz, dim.z, box.periodic.z, zs);
+    int xs0, xs1, xs2, ys0, ys1, ys2, zs0, zs1, zs2;
+    const int nx = axis_set3(bx, dim.x, box.periodic.x, xs0, xs1, xs2);
+    const int ny = axis_set3(by, dim.y, box.periodic.y, ys0, ys1, ys2);
+    const int nz = axis_set3(bz, dim.z, box.periodic.z, zs0, zs1, zs2);
     const unsigned int nr = (unsigned int)(nx * ny * nz);
     unsigned int beg = 0, len = 0;
     if (lane < nr)
         {
         // (c, q, r) in lexicographic order == ascending cell id (id = (z*dimy + y)*dimx + x)
         const int r = lane % nx, q = (lane / nx) % ny, c = lane / (nx * ny);
-        const int x = (r == 0) ? xs[0] : (r == 1) ? xs[1] : xs[2];
-        const int y = (q == 0) ? ys[0] : (q == 1) ? ys[1] : ys[2];
-        const int z = (c == 0) ? zs[0] : (c == 1) ? zs[1] : zs[2];
+        const int x = (r == 0) ? xs0 : (r == 1) ? xs1 : xs2;
+        const int y = (q == 0) ? ys0 : (q == 1) ? ys1 : ys2;
+        const int z = (c == 0) ? zs0 : (c == 1) ? zs1 : zs2;
         const unsigned int nc = ((unsigned int)z * dim.y + (unsigned int)y) * dim.x + (unsigned int)x;
         beg = cell_start[nc];
         len = cell_start[nc + 1] - beg;
