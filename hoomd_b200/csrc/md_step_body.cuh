@@ -45,6 +45,7 @@ template<class Evaluator> struct MdStepArgs
     const float* diameter; int use_lambda; float gamma_lambda; double* tally_acc; // langevin dscale / tally
     unsigned int nmax_uniform; int prefetch;                          // see FusedStepArgs
     int persist_strict;                                               // k_md_steps: acquire fence behind the spin (md_steps_persist.cuh)
+    unsigned int persist_sleep_ns;                                    // k_md_steps: pause between two polls of the release word
     };
 
 __device__ __forceinline__ void prefetch_l1(const void* p)

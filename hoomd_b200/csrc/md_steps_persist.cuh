@@ -328,6 +328,10 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
                 lost = true;
                 break;
                 }
+            // a poll comes back in ~50 ns, so a thousand spinning threads put ~20 G loads/s on the 16 release lines and 14 % of
+            // the kernel's issued instructions are this loop (profiles/r2z_mdsteps_64k_lines.txt) -- yet a pause between polls
+            // buys nothing: 13.24 / 13.18 / 13.34 / 13.67 us per step with 0 / 100 / 300 / 1000 ns (profiles/r2y_*sleep*).  Off.
+            if (a.persist_sleep_ns) __nanosleep(a.persist_sleep_ns);
             }
         PERSIST_MARK(5)
         // acquire: the other CTAs' position stores of this step are visible to this SM from here on.
@@ -468,6 +472,8 @@ static cudaError_t launch_md_steps_t(const b200_pair_args& pa, const void* d_par
     fill_md_step_args(a, pa, (const float*)d_params, fa, pos_a, pos_b, 0, st, next_handle, use_cond);
     static const bool early = getenv("HOOMD_B200_PERSIST_EARLY_FENCE") && atoi(getenv("HOOMD_B200_PERSIST_EARLY_FENCE")) != 0;
     a.persist_strict = early ? 0 : 1;
+    static const int sleep_ns = getenv("HOOMD_B200_PERSIST_SLEEP") ? atoi(getenv("HOOMD_B200_PERSIST_SLEEP")) : 0;
+    a.persist_sleep_ns = (unsigned int)std::max(0, sleep_ns);
     const unsigned int tpp = pa.threads_per_particle ? pa.threads_per_particle : pick_pair_tpp(pa.N);
     const bool shift = pa.shift_mode == B200_SHIFT_SHIFT;
     switch (tpp)
