@@ -4,8 +4,11 @@
 // barrier built on the ticket the step already takes for its rebuild decision.
 //
 //   per step:   phase 1 (neighbor walk on buffer X) -> phase 2 (step two, step one into buffer Y, distance check)
-//               -> ticket; the LAST CTA takes NeighborList::needsUpdating for the next step (decide_body) and releases the
-//               epoch word; every CTA waits for it, re-reads the control block, swaps X and Y.
+//               -> ticket (a 128-byte line of its own); the LAST CTA takes NeighborList::needsUpdating for the next step
+//               (decide_body on a register copy of the control block) and publishes ONE 8-byte release word that carries
+//               the new epoch AND the next step's control block, replicated over 16 lines; every CTA spins on its copy,
+//               takes one acquire fence, swaps X and Y.  Row metadata and the CTA's particle state stay on chip
+//               (PersistRegs / PersistShared) from step to step.
 //   exit:       rebuild wanted / chunk finished / abort.  The caller's rebuild bracket and the next launch always start from
 //               buffer A (a.pos_in): a launch that stops with the current positions in B copies its own particles back.
 //
