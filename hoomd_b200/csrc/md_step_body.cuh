@@ -278,6 +278,7 @@ __device__ __forceinline__ void md_step_finish(const MdStepArgs<Evaluator>& a, S
             // One GPU: the rebuild decision on a register copy of the control block (four independent 16-byte loads, one round
             // trip, then four stores) instead of a dozen dependent loads at the tail of every launch; nobody else touches
             // the block once every CTA has taken its ticket.  Same decision, same fields written.
+            static_assert(sizeof(StepState) == 96, "StepState is copied as six 16-byte words");
             StepState loc;
             uint4* lq = reinterpret_cast<uint4*>(&loc);
             const uint4* gq = reinterpret_cast<const uint4*>(st);
