@@ -1,5 +1,6 @@
 // Internal (C++) declarations shared between the kernel translation units and the engine.  Not part of the C ABI.
 #pragma once
+#include <cstddef>
 #include <cuda_runtime.h>
 #include "../../include/hoomd_b200.h"
 
@@ -34,6 +35,15 @@ struct StepState
                                   // threshold table (lambda-scaled, NeighborList.cc:981-1007); cleared by the rebuild decision
     unsigned long long ctl64;     // (reserved)
     };
+// The step kernels copy the block as six 16-byte words and write back words 0-3 plus box_scaled (md_step_body.cuh,
+// md_steps_persist.cuh): the fields other kernels or CTAs may write while a step kernel's last CTA does so must stay outside
+// words 0-3 -- store_force, N, abort, nvt_error, no_dist_check -- and the layout below is what those copies assume.
+static_assert(sizeof(StepState) == 96 && offsetof(StepState, need_rebuild) == 12 && offsetof(StepState, num_updates) == 32
+                  && offsetof(StepState, overflow) == 40 && offsetof(StepState, steps_left) == 48
+                  && offsetof(StepState, ticket) == 56 && offsetof(StepState, store_force) == 64
+                  && offsetof(StepState, abort) == 72 && offsetof(StepState, nvt_error) == 76
+                  && offsetof(StepState, box_scaled) == 84 && offsetof(StepState, ctl64) == 88,
+              "StepState layout");
 // The engine allocates STEP_STATE_ALLOC StepState slots: slot 0 is the state; the bytes from STEP_SYNC_OFFSET on hold the
 // barrier lines of k_md_steps (md_steps_persist.cuh): its ticket on a 128-byte line of its own and STEP_SYNC_COPIES copies of
 // the release word, one line each.
