@@ -1521,7 +1521,14 @@ static void run_chunk_device(b200_system* s, unsigned int chunk)
         for (unsigned int k = 0; k < nlaunch; k++) CUDA_OK(cudaGraphLaunch(s->graph_exec, s->stream));
     CUDA_OK(cudaMemcpyAsync(s->h_state, s->d_state.p, sizeof(StepState), cudaMemcpyDeviceToHost, s->stream));
     CUDA_OK(cudaStreamSynchronize(s->stream));
-    if (st.nvt_error == 3u) throw std::runtime_error("integrate: a CTA of the multi-step kernel never reached the grid barrier");
+    if (st.nvt_error == 3u)
+        {
+        // the ticket line holds the arrivals of the step that never completed: clear it and the release words (epoch 0 again)
+        CUDA_OK(cudaMemsetAsync(reinterpret_cast<char*>(s->d_state.p) + STEP_SYNC_OFFSET, 0,
+                                (size_t)(1u + STEP_SYNC_COPIES) * STEP_SYNC_LINE, s->stream));
+        CUDA_OK(cudaStreamSynchronize(s->stream));
+        throw std::runtime_error("integrate: a CTA of the multi-step kernel never reached the grid barrier");
+        }
     if (st.nvt_error)
         throw std::runtime_error(st.nvt_error == 1u
                                      ? "integrate.nvt: kinetic energy is more than 2^20 times the set point (diverged?)"

@@ -270,3 +270,12 @@ extern "C" __attribute__((visibility("default"))) int b200_debug_persist_trace(u
     return (int)e;
     }
 #endif
+
+#ifdef B200_FAULT_INJECT
+// fault-injection builds only (see md_steps_persist.cuh): the next step of k_md_steps loses the ticket of CTA `cta`
+extern "C" __attribute__((visibility("default"))) int b200_debug_fault_lose_cta(unsigned int cta)
+    {
+    const unsigned int v = cta + 1u;
+    return (int)cudaMemcpyToSymbol(b200::g_fault_lose_cta, &v, sizeof(v));
+    }
+#endif

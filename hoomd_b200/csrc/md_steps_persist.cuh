@@ -47,6 +47,12 @@ __device__ unsigned int g_persist_trace_step[PERSIST_TRACE_CTAS];
 #define PERSIST_MARK_END()
 #endif
 
+// -DB200_FAULT_INJECT (tests/test_fault_gpu.py, never in the shipped library): CTA (g_fault_lose_cta - 1) skips its ticket
+// once, so that the bounded wait on the release word -- and the host's handling of the error it raises -- can be exercised
+#ifdef B200_FAULT_INJECT
+__device__ unsigned int g_fault_lose_cta;
+#endif
+
 __device__ __forceinline__ unsigned long long* persist_ticket(StepState* st)
     {
     return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(st) + STEP_SYNC_OFFSET);
@@ -274,7 +280,12 @@ __device__ __forceinline__ unsigned int md_persist_step(const MdStepArgs<Evaluat
         // release: this CTA's position stores (ordered before by the barrier above) before its ticket.  A release ATOMIC, not a
         // fence: the fence would also drop the SM's L1 lines under the CTAs that are still walking their neighbor rows
         const unsigned long long inc = 1ull | (any_moved ? (1ull << 32) : 0ull);
-        unsigned long long old;
+        unsigned long long old = 0ull;
+#ifdef B200_FAULT_INJECT
+        const bool lose = g_fault_lose_cta == blockIdx.x + 1u;
+        if (lose) g_fault_lose_cta = 0u;
+        if (!lose)
+#endif
         asm volatile("atom.release.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(persist_ticket(st)), "l"(inc) : "memory");
         PERSIST_MARK(4)
         const bool last_cta = (unsigned int)old == gridDim.x - 1u;
